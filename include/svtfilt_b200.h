@@ -1,0 +1,228 @@
+/*
+ * svtfilt_b200.h — Tier-1 C ABI of the B200-native in-loop filter path
+ * (deblock -> CDEF -> CCSO, plus the encoder's CDEF strength search).
+ *
+ * Plain C, plain pointers and sizes, no SVT-AV1 headers, no torch types.
+ * Every entry point names the reference interface it stands in for
+ * (paths relative to the reference tree, `Source/Lib/...`).  The Tier-2
+ * adapters that keep the reference's own function names/signatures
+ * (svt_av1_loop_filter_frame(pcs...), svt_av1_cdef_frame(scs,pcs), ...) are
+ * declared in include/svtfilt_b200_adapters.h and described in INTEGRATION.md.
+ *
+ * Conventions
+ *   - all functions return 0 on success and a negative SVTF_E_* code on error;
+ *     svtf_last_error() gives a human-readable message (per context).
+ *   - strides are in SAMPLES (like EbPictureBufferDesc::stride_y), plane
+ *     pointers address the visible origin (buffer + org_y*stride + org_x).
+ *   - sample_bytes 1 -> uint8_t samples (8-bit pipeline), 2 -> uint16_t
+ *     (10/12-bit or `is_16bit_pipeline`), exactly like the reference picks
+ *     recon_pic vs recon_pic_16bit (Encoder/Codec/EbRestProcess.c:135-153).
+ *   - 4:2:0 only (the encoder path is 4:2:0 only, Encoder/Codec/EbEncCdef.c:324-329).
+ *   - work is stream-ordered on the context's CUDA stream; host-visible
+ *     results are valid after svtf_sync() (download calls sync themselves
+ *     unless stated otherwise).
+ *   - there is NO CPU fallback: without a CUDA device every call fails with
+ *     SVTF_E_CUDA.
+ */
+#ifndef SVTFILT_B200_H
+#define SVTFILT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVTF_OK 0
+#define SVTF_E_ARG (-1)      /* bad argument / unsupported configuration            */
+#define SVTF_E_CUDA (-2)     /* CUDA runtime error (message in svtf_last_error)     */
+#define SVTF_E_STATE (-3)    /* call order violated (e.g. no frame uploaded)        */
+#define SVTF_E_NOMEM (-4)    /* host or device allocation failed                    */
+
+#define SVTF_MAX_SEGMENTS 8
+#define SVTF_SEG_LVL_MAX 8
+#define SVTF_REF_FRAMES 8
+#define SVTF_CDEF_MAX_STRENGTHS 16 /* CDEF_MAX_STRENGTHS, Common/Codec/EbAv1Structs.h:359-369 */
+#define SVTF_TOTAL_STRENGTHS 64    /* TOTAL_STRENGTHS,   Common/Codec/EbCdef.h:47            */
+#define SVTF_CCSO_BAND_NUM 128
+#define SVTF_CCSO_LUT_SIZE (SVTF_CCSO_BAND_NUM * 16)
+
+typedef struct svtf_ctx svtf_ctx;
+
+/* Frame geometry.  width/height: unpadded source size (deblock and CCSO limit,
+ * Encoder/Codec/EbDeblockingFilter.c:99-101,173-178); mi_cols/mi_rows: coded size in 4x4
+ * units (CDEF frame limit, Encoder/Codec/EbEncCdef.c:356-382). */
+typedef struct svtf_geom {
+    int32_t width, height;
+    int32_t mi_cols, mi_rows;
+    int32_t bit_depth;    /* 8, 10 or 12 */
+    int32_t sample_bytes; /* 1 or 2      */
+} svtf_geom;
+
+/* ---- per-4x4 ("mi") side info, one packed 32-bit word per unit ------------------
+ * Replaces the pointer chase through pcs->mi_grid_base[..]->mbmi (Encoder/Codec/
+ * EbDeblockingFilter.c:187-199, Encoder/Codec/EbEncCdef.c:238-280).
+ *   bits  0-2  log2(luma tx width)-2     bits  3-5  log2(luma tx height)-2
+ *   bits  6-8  log2(chroma tx width)-2   bits  9-11 log2(chroma tx height)-2
+ *   bits 12-14 log2(block width)-2       bits 15-17 log2(block height)-2
+ *   bit  18    skip && is_inter (deblock "skipped")   bit 19  skip (CDEF)
+ *   bits 20-22 ref_frame[0]              bit  23    mode_lf_lut[mode]
+ *   bits 24-26 segment_id                bits 27-31 reserved (0)
+ */
+typedef uint32_t svtf_mi_t;
+
+/* Encoder-side packer: same derivation as get_transform_size()
+ * (Encoder/Codec/EbDeblockingFilter.c:143-160): luma tx = tx_depth_to_tx_size[skip&&inter ? 0 :
+ * tx_depth][bsize], chroma tx = av1_get_max_uv_txsize(bsize,1,1).  Arrays hold n entries
+ * (BlockSize enum, tx_depth 0..2, skip 0/1, ref_frame[0] 0..7, PredictionMode 0..24, segment id). */
+int svtf_pack_mi_enc(size_t n, const uint8_t *bsize, const uint8_t *tx_depth, const uint8_t *skip,
+                     const uint8_t *ref_frame0, const uint8_t *mode, const uint8_t *segment_id, svtf_mi_t *out);
+/* Decoder-side packer: per-unit transform sizes are given explicitly as TxSize enums
+ * (LfCtxt.tx_size_l / tx_size_uv, Decoder/Codec/EbDecLF.c:133-145). */
+int svtf_pack_mi_dec(size_t n, const uint8_t *bsize, const uint8_t *tx_size_y, const uint8_t *tx_size_uv,
+                     const uint8_t *skip, const uint8_t *ref_frame0, const uint8_t *mode,
+                     const uint8_t *segment_id, svtf_mi_t *out);
+
+/* ---- deblock -----------------------------------------------------------------------------
+ * struct LoopFilter (Common/Codec/EbDefinitions.h:1903-1920), the LF part of
+ * SegmentationParams (Common/Codec/EbSegmentationParams.h) and DeltaLfParams
+ * (Common/Codec/EbAv1Structs.h:345-357) + ppcs->curr_delta_lf. */
+typedef struct svtf_lf_params {
+    int32_t filter_level[2];
+    int32_t filter_level_u, filter_level_v;
+    int32_t sharpness_level;
+    int32_t mode_ref_delta_enabled;
+    int8_t  ref_deltas[SVTF_REF_FRAMES];
+    int8_t  mode_deltas[2];
+    int32_t segmentation_enabled;
+    int16_t seg_feature_enabled[SVTF_MAX_SEGMENTS][SVTF_SEG_LVL_MAX];
+    int16_t seg_feature_data[SVTF_MAX_SEGMENTS][SVTF_SEG_LVL_MAX];
+    int32_t delta_lf_present, delta_lf_multi;
+    int32_t curr_delta_lf[4];
+} svtf_lf_params;
+
+/* ---- CDEF ---------------------------------------------------------------------------------
+ * CdefParams (Common/Codec/EbAv1Structs.h:359-369): strength byte v -> pri=v/4, sec=v%4 (3->4). */
+typedef struct svtf_cdef_params {
+    int32_t cdef_damping;
+    int32_t cdef_bits;
+    uint8_t cdef_y_strength[SVTF_CDEF_MAX_STRENGTHS];
+    uint8_t cdef_uv_strength[SVTF_CDEF_MAX_STRENGTHS];
+} svtf_cdef_params;
+
+/* CdefControls search lists (Encoder/Codec/EbPictureControlSet.h:592-628). */
+typedef struct svtf_cdef_search_cfg {
+    int32_t first_pass_fs_num;
+    int32_t default_second_pass_fs_num;
+    uint8_t default_first_pass_fs[SVTF_TOTAL_STRENGTHS];
+    uint8_t default_second_pass_fs[SVTF_TOTAL_STRENGTHS];
+    int8_t  default_first_pass_fs_uv[SVTF_TOTAL_STRENGTHS];  /* -1 = masked */
+    int8_t  default_second_pass_fs_uv[SVTF_TOTAL_STRENGTHS]; /* -1 = masked */
+    int32_t subsampling_factor; /* 1, 2 or 4 */
+    int32_t base_q_idx;         /* damping = 3 + (base_q_idx >> 6), Encoder/Codec/EbCdefProcess.c:147 */
+    int32_t zero_fs_cost_bias;  /* 0 = off; Encoder/Codec/EbEncCdef.c:845-851 */
+    uint32_t lambda;            /* full_lambda as produced by svt_aom_av1_lambda_assignment_function_table */
+} svtf_cdef_search_cfg;
+
+/* ---- CCSO ---------------------------------------------------------------------------------
+ * CcsoInfo (Common/Codec/EbAv1Structs.h:407-427). */
+typedef struct svtf_ccso_params {
+    uint8_t ccso_enable[3];
+    uint8_t ccso_bo_only[3];
+    uint8_t quant_idx[3];          /* thr = {16,8,32,64}[quant_idx], Common/Codec/EbCcso.c:636 */
+    uint8_t ext_filter_support[3]; /* 0..5, Common/Codec/EbCcso.c:204-234 */
+    uint8_t edge_clf[3];
+    uint8_t max_band_log2[3];
+    int8_t  filter_offset[3][SVTF_CCSO_LUT_SIZE];
+} svtf_ccso_params;
+
+/* ---- context ---------------------------------------------------------------------------- */
+/* One context = one picture in flight on one GPU: device surfaces for max_geom, side info,
+ * pinned staging and one CUDA stream.  Re-entrant per context (the reference is re-entrant per
+ * pcs, SURVEY §8b "Threading"). */
+int  svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx **out);
+void svtf_ctx_destroy(svtf_ctx *ctx);
+const char *svtf_last_error(const svtf_ctx *ctx); /* ctx may be NULL: last global error */
+int  svtf_sync(svtf_ctx *ctx);
+/* Number of this library's kernel launches issued on the context so far. */
+uint64_t svtf_launch_count(const svtf_ctx *ctx);
+
+/* Page-locked host memory for picture buffers: uploads/downloads from such buffers are true
+ * asynchronous DMA (a caller may equally cudaHostRegister its own recon buffers). */
+void *svtf_host_alloc(size_t bytes);
+void  svtf_host_free(void *p);
+
+/* Start a picture: sets the geometry (must fit max_geom) and resets the surface chain. */
+int svtf_frame_begin(svtf_ctx *ctx, const svtf_geom *geom);
+
+/* Host -> device copy of the reconstructed picture (the `frame_buffer` / recon_pic argument of
+ * the reference entry points).  Copies the coded area (mi_cols*4 x mi_rows*4). */
+int svtf_upload_frame(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
+                      const void *cr, int32_t stride_cr);
+/* Source picture (pcs->cdef_input_source / input_frame16bit) for the strength search. */
+int svtf_upload_source(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
+                       const void *cr, int32_t stride_cr);
+/* Packed mi grid, mi_rows x mi_cols entries with row stride mi_stride. */
+int svtf_set_mi(svtf_ctx *ctx, const svtf_mi_t *mi, int32_t mi_stride);
+/* Device -> host copy of the current end of the filter chain; synchronises. */
+int svtf_download_frame(svtf_ctx *ctx, void *y, int32_t stride_y, void *cb, int32_t stride_cb, void *cr,
+                        int32_t stride_cr);
+/* Rewind the chain to the uploaded (unfiltered) picture without copying — lets a benchmark
+ * re-run the chain on device-resident input. */
+int svtf_rewind(svtf_ctx *ctx);
+
+/* ---- filters ------------------------------------------------------------------------------ */
+/* svt_av1_loop_filter_frame(frame_buffer, pcs, plane_start, plane_end)
+ * (Encoder/Codec/EbDeblockingFilter.c:624) == svt_aom_dec_av1_loop_filter_frame
+ * (Decoder/Codec/EbDecLF.c:697) on the same side info. */
+int svtf_deblock_frame(svtf_ctx *ctx, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end);
+
+/* svt_av1_cdef_frame(scs, pcs) (Encoder/Codec/EbEncCdef.c:284) == svt_cdef_frame
+ * (Decoder/Codec/EbDecCdef.c:507).  fb_strength_idx: one int8 per 64x64 filter block
+ * (row-major, nvfb x nhfb) = mbmi.cdef_strength of its top-left mi. */
+int svtf_cdef_apply_frame(svtf_ctx *ctx, const svtf_cdef_params *cdef, const int8_t *fb_strength_idx);
+
+/* ccso_frame(frame, pcs, pd, ext_rec_y) (Common/Codec/EbCcso.c:626) on 8- or 16-bit samples.
+ * Luma classification input = the picture as it was before the last svtf_cdef_apply_frame
+ * (post-deblock / pre-CDEF, Encoder/Codec/EbCdefProcess.c:490-502); if no CDEF ran in this chain, the
+ * current picture.  blk_flags[p]: one byte per CCSO filter block of plane p (256x256 luma
+ * samples; row-major ceil(height/256) x ceil(width/256)) = mbmi.ccso_blk_{y,u,v}; NULL = all on. */
+int svtf_ccso_apply_frame(svtf_ctx *ctx, const svtf_ccso_params *ccso, const uint8_t *const blk_flags[3]);
+
+/* Whole post-reconstruction chain in one call (decoder order, Decoder/Codec/EbDecParseObu.c:2382-2433):
+ * deblock -> CDEF -> CCSO; any of lf / cdef / ccso may be NULL to skip that stage. */
+int svtf_filter_chain(svtf_ctx *ctx, const svtf_lf_params *lf, const svtf_cdef_params *cdef,
+                      const int8_t *fb_strength_idx, const svtf_ccso_params *ccso,
+                      const uint8_t *const blk_flags[3]);
+
+/* ---- CDEF strength search ------------------------------------------------------------------ */
+/* cdef_seg_search(pcs, scs, segment) over the whole frame (Encoder/Codec/EbCdefProcess.c:114).
+ * Input = current picture (post-deblock) + uploaded source.  Outputs (host, caller-owned, may be
+ * NULL):  mse[2][nfb][64] u64 laid out like pcs->mse_seg, skip[nfb] like pcs->skip_cdef_seg,
+ * dir[nfb][64] / var[nfb][64] = CdefDirData of each fb restricted to its 8x8 grid (by*8+bx). */
+int svtf_cdef_search_frame(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, uint64_t *mse, uint8_t *skip,
+                           uint8_t *dir, int32_t *var);
+/* finish_cdef_search(pcs) (Encoder/Codec/EbEncCdef.c:728) on the table left on the device by
+ * svtf_cdef_search_frame: picks cdef_bits, the strength pairs and the per-fb index.
+ * fb_strength_idx: nfb entries, -1 for fbs the search skipped. */
+int svtf_cdef_pick(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, svtf_cdef_params *out_params,
+                   int8_t *fb_strength_idx);
+/* Host-table variant (used by the multi-GPU stripe path after the mse allgather). */
+int svtf_cdef_pick_host(const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
+                        svtf_cdef_params *out_params, int8_t *fb_strength_idx);
+
+/* ---- device-side access for multi-GPU stripe exchange and device-resident benches ----------- */
+typedef struct svtf_dev_plane {
+    void   *ptr;   /* device pointer to sample (0,0) */
+    int32_t pitch; /* in samples */
+    int32_t width, height;
+} svtf_dev_plane;
+/* which: 0 = uploaded recon, 1 = current end of chain, 2 = source */
+int svtf_dev_planes(svtf_ctx *ctx, int which, svtf_dev_plane out[3]);
+void *svtf_cuda_stream(svtf_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVTFILT_B200_H */

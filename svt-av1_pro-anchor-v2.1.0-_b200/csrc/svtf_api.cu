@@ -1,0 +1,538 @@
+// svtf_api.cu — the Tier-1 C ABI (include/svtfilt_b200.h): context, surfaces, launches.
+// One context = one picture in flight on one CUDA stream.  No CPU fallback: every entry point that
+// needs the device fails with SVTF_E_CUDA when there is none.
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "svtf_kernels.cuh"
+#include "svtf_search.cuh"
+
+namespace svtf {
+
+static std::mutex  g_err_mutex;
+static std::string g_err;
+
+int set_global_error(int code, const char *msg) {
+    std::lock_guard<std::mutex> lk(g_err_mutex);
+    g_err = msg ? msg : "";
+    return code;
+}
+
+struct Surface {
+    void  *base[3] = {nullptr, nullptr, nullptr};
+    int    pitch[3] = {0, 0, 0}; // samples
+    Planes planes() const {
+        Planes p;
+        for (int i = 0; i < 3; i++) p.p[i] = base[i], p.pitch[i] = pitch[i];
+        return p;
+    }
+};
+
+} // namespace svtf
+
+using namespace svtf;
+
+struct svtf_ctx {
+    int          device = 0;
+    cudaStream_t stream = nullptr;
+    svtf_geom    max_geom{};
+    svtf_geom    geom{};
+    bool         have_geom = false, have_frame = false, have_mi = false, have_source = false, have_search = false;
+    Surface      surf[3];  // filter chain ping-pong
+    Surface      source;   // source picture for the search
+    int          cur = 0;  // surface holding the current end of the chain
+    int          pre_cdef = -1; // surface holding the picture before the last CDEF (-1: none)
+    svtf_mi_t   *d_mi = nullptr;
+    int          mi_stride = 0; // device mi stride == geom.mi_cols rounded
+    int8_t      *d_fb_idx = nullptr;
+    int8_t      *d_ccso_lut = nullptr;
+    uint8_t     *d_ccso_flags = nullptr; // 3 * max_blocks
+    int          max_ccso_blocks = 0;
+    uint64_t    *d_mse = nullptr;  // [2][nfb][64]
+    uint8_t     *d_skip = nullptr; // [nfb]
+    uint8_t     *d_dir = nullptr;  // [nfb][64]
+    int32_t     *d_var = nullptr;  // [nfb][64]
+    int          max_nfb = 0;
+    uint64_t     launches = 0;
+    std::string  err;
+
+    int fail(int code, const std::string &m) {
+        err = m;
+        set_global_error(code, m.c_str());
+        return code;
+    }
+    int cuda_fail(cudaError_t e, const char *what) {
+        return fail(SVTF_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    }
+};
+
+#define CUDA_TRY(ctx, call)                         \
+    do {                                            \
+        cudaError_t e_ = (call);                    \
+        if (e_ != cudaSuccess)                      \
+            return (ctx)->cuda_fail(e_, #call);     \
+    } while (0)
+
+static bool geom_ok(const svtf_geom *g) {
+    return g && g->width > 0 && g->height > 0 && g->mi_cols > 0 && g->mi_rows > 0 && !(g->mi_cols & 1) && !(g->mi_rows & 1) &&
+        g->width <= g->mi_cols * 4 && g->height <= g->mi_rows * 4 && (g->bit_depth == 8 || g->bit_depth == 10 || g->bit_depth == 12) &&
+        (g->sample_bytes == 1 || g->sample_bytes == 2) && !(g->sample_bytes == 1 && g->bit_depth != 8);
+}
+
+static int round_up(int v, int a) { return (v + a - 1) / a * a; }
+
+static cudaError_t alloc_surface(Surface &s, const svtf_geom &g) {
+    for (int p = 0; p < 3; p++) {
+        const int w = (g.mi_cols * 4) >> (p ? 1 : 0), h = (g.mi_rows * 4) >> (p ? 1 : 0);
+        s.pitch[p]  = round_up(w, 128);
+        cudaError_t e = cudaMalloc(&s.base[p], (size_t)s.pitch[p] * (h + 8) * g.sample_bytes);
+        if (e != cudaSuccess)
+            return e;
+    }
+    return cudaSuccess;
+}
+
+extern "C" const char *svtf_last_error(const svtf_ctx *ctx) {
+    if (ctx)
+        return ctx->err.c_str();
+    static thread_local std::string copy;
+    std::lock_guard<std::mutex> lk(g_err_mutex);
+    copy = g_err;
+    return copy.c_str();
+}
+
+extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx **out) {
+    if (!out || !geom_ok(max_geom))
+        return set_global_error(SVTF_E_ARG, "svtf_ctx_create: bad geometry");
+    int         ndev = 0;
+    cudaError_t e    = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+        std::string m = "svtf_ctx_create: no usable CUDA device (this library has no CPU fallback): ";
+        m += e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range";
+        return set_global_error(SVTF_E_CUDA, m.c_str());
+    }
+    svtf_ctx *c = new (std::nothrow) svtf_ctx();
+    if (!c)
+        return set_global_error(SVTF_E_NOMEM, "svtf_ctx_create: out of host memory");
+    c->device   = device;
+    c->max_geom = *max_geom;
+    auto bail   = [&](cudaError_t ce, const char *what) {
+        int r = c->cuda_fail(ce, what);
+        svtf_ctx_destroy(c);
+        return r;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    for (int i = 0; i < 3; i++)
+        if ((e = alloc_surface(c->surf[i], *max_geom)) != cudaSuccess) return bail(e, "cudaMalloc(surface)");
+    if ((e = alloc_surface(c->source, *max_geom)) != cudaSuccess) return bail(e, "cudaMalloc(source)");
+    const int nvfb = (max_geom->mi_rows + 15) / 16, nhfb = (max_geom->mi_cols + 15) / 16;
+    c->max_nfb     = nvfb * nhfb;
+    c->mi_stride   = round_up(max_geom->mi_cols, 32);
+    if ((e = cudaMalloc(&c->d_mi, sizeof(svtf_mi_t) * (size_t)c->mi_stride * max_geom->mi_rows)) != cudaSuccess) return bail(e, "cudaMalloc(mi)");
+    if ((e = cudaMalloc(&c->d_fb_idx, c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(fb_idx)");
+    if ((e = cudaMalloc(&c->d_ccso_lut, 3 * SVTF_CCSO_LUT_SIZE)) != cudaSuccess) return bail(e, "cudaMalloc(ccso lut)");
+    c->max_ccso_blocks = ((max_geom->width + 255) / 256) * ((max_geom->height + 255) / 256);
+    if ((e = cudaMalloc(&c->d_ccso_flags, 3 * (size_t)c->max_ccso_blocks)) != cudaSuccess) return bail(e, "cudaMalloc(ccso flags)");
+    if ((e = cudaMalloc(&c->d_mse, sizeof(uint64_t) * 2 * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(mse)");
+    if ((e = cudaMalloc(&c->d_skip, c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(skip)");
+    if ((e = cudaMalloc(&c->d_dir, 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(dir)");
+    if ((e = cudaMalloc(&c->d_var, sizeof(int32_t) * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(var)");
+    *out = c;
+    return SVTF_OK;
+}
+
+extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
+    if (!c)
+        return;
+    cudaSetDevice(c->device);
+    if (c->stream)
+        cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < 3; i++)
+        for (int p = 0; p < 3; p++) cudaFree(c->surf[i].base[p]);
+    for (int p = 0; p < 3; p++) cudaFree(c->source.base[p]);
+    cudaFree(c->d_mi), cudaFree(c->d_fb_idx), cudaFree(c->d_ccso_lut), cudaFree(c->d_ccso_flags);
+    cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
+    if (c->stream)
+        cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" int svtf_sync(svtf_ctx *c) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_sync: NULL context");
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return SVTF_OK;
+}
+
+extern "C" uint64_t svtf_launch_count(const svtf_ctx *c) { return c ? c->launches : 0; }
+extern "C" void    *svtf_cuda_stream(svtf_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+extern "C" void *svtf_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess)
+        return nullptr;
+    return p;
+}
+extern "C" void svtf_host_free(void *p) {
+    if (p)
+        cudaFreeHost(p);
+}
+
+extern "C" int svtf_frame_begin(svtf_ctx *c, const svtf_geom *g) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_frame_begin: NULL context");
+    if (!geom_ok(g) || g->mi_cols > c->max_geom.mi_cols || g->mi_rows > c->max_geom.mi_rows ||
+        g->sample_bytes != c->max_geom.sample_bytes)
+        return c->fail(SVTF_E_ARG, "svtf_frame_begin: geometry invalid or larger than the context's max_geom");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    c->geom      = *g;
+    c->have_geom = true;
+    c->have_frame = c->have_mi = c->have_source = c->have_search = false;
+    c->cur       = 0;
+    c->pre_cdef  = -1;
+    return SVTF_OK;
+}
+
+static int copy_planes(svtf_ctx *c, Surface &s, const void *const src[3], const int32_t stride[3], bool to_device) {
+    const svtf_geom &g = c->geom;
+    for (int p = 0; p < 3; p++) {
+        const int w = (g.mi_cols * 4) >> (p ? 1 : 0), h = (g.mi_rows * 4) >> (p ? 1 : 0);
+        if (!src[p] || stride[p] < w)
+            return c->fail(SVTF_E_ARG, "plane pointer NULL or stride smaller than the coded width");
+        const size_t sb = g.sample_bytes;
+        if (to_device)
+            CUDA_TRY(c, cudaMemcpy2DAsync(s.base[p], s.pitch[p] * sb, src[p], stride[p] * sb, w * sb, h, cudaMemcpyHostToDevice, c->stream));
+        else
+            CUDA_TRY(c, cudaMemcpy2DAsync(const_cast<void *>(src[p]), stride[p] * sb, s.base[p], s.pitch[p] * sb, w * sb, h,
+                                          cudaMemcpyDeviceToHost, c->stream));
+    }
+    return SVTF_OK;
+}
+
+extern "C" int svtf_upload_frame(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_upload_frame: NULL context");
+    if (!c->have_geom)
+        return c->fail(SVTF_E_STATE, "svtf_upload_frame: call svtf_frame_begin first");
+    const void   *src[3] = {y, cb, cr};
+    const int32_t st[3]  = {sy, scb, scr};
+    c->cur = 0, c->pre_cdef = -1;
+    int r = copy_planes(c, c->surf[0], src, st, true);
+    if (r == SVTF_OK)
+        c->have_frame = true;
+    return r;
+}
+
+extern "C" int svtf_upload_source(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_upload_source: NULL context");
+    if (!c->have_geom)
+        return c->fail(SVTF_E_STATE, "svtf_upload_source: call svtf_frame_begin first");
+    const void   *src[3] = {y, cb, cr};
+    const int32_t st[3]  = {sy, scb, scr};
+    int r = copy_planes(c, c->source, src, st, true);
+    if (r == SVTF_OK)
+        c->have_source = true;
+    return r;
+}
+
+extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_set_mi: NULL context");
+    if (!c->have_geom)
+        return c->fail(SVTF_E_STATE, "svtf_set_mi: call svtf_frame_begin first");
+    if (!mi || mi_stride < c->geom.mi_cols)
+        return c->fail(SVTF_E_ARG, "svtf_set_mi: NULL grid or stride smaller than mi_cols");
+    CUDA_TRY(c, cudaMemcpy2DAsync(c->d_mi, sizeof(svtf_mi_t) * c->mi_stride, mi, sizeof(svtf_mi_t) * mi_stride,
+                                  sizeof(svtf_mi_t) * c->geom.mi_cols, c->geom.mi_rows, cudaMemcpyHostToDevice, c->stream));
+    c->have_mi = true;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_download_frame(svtf_ctx *c, void *y, int32_t sy, void *cb, int32_t scb, void *cr, int32_t scr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_download_frame: NULL context");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_download_frame: no picture uploaded");
+    const void   *dst[3] = {y, cb, cr};
+    const int32_t st[3]  = {sy, scb, scr};
+    int r = copy_planes(c, c->surf[c->cur], dst, st, false);
+    if (r != SVTF_OK)
+        return r;
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return SVTF_OK;
+}
+
+extern "C" int svtf_rewind(svtf_ctx *c) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_rewind: NULL context");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_rewind: no picture uploaded");
+    c->cur = 0, c->pre_cdef = -1;
+    return SVTF_OK;
+}
+
+static Dims dims_of(const svtf_geom &g) {
+    Dims d;
+    d.width = g.width, d.height = g.height, d.mi_cols = g.mi_cols, d.mi_rows = g.mi_rows, d.bit_depth = g.bit_depth;
+    return d;
+}
+
+// surface to write next: any surface that is neither the current one nor the pre-CDEF one nor the upload (0)
+static int next_surface(const svtf_ctx *c) {
+    for (int i = 1; i < 3; i++)
+        if (i != c->cur && i != c->pre_cdef)
+            return i;
+    return c->cur == 1 ? 2 : 1;
+}
+
+static int need_frame_mi(svtf_ctx *c, const char *fn) {
+    if (!c->have_frame || !c->have_mi)
+        return c->fail(SVTF_E_STATE, std::string(fn) + ": upload a picture and its mi grid first");
+    return SVTF_OK;
+}
+
+extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_deblock_frame: NULL context");
+    if (!lf || plane_start < 0 || plane_end > 3 || plane_start > plane_end)
+        return c->fail(SVTF_E_ARG, "svtf_deblock_frame: bad arguments");
+    if (int r = need_frame_mi(c, "svtf_deblock_frame"))
+        return r;
+    // plane selection — svt_aom_loop_filter_sb, Encoder/Codec/EbDeblockingFilter.c:572-578: luma level 0
+    // breaks the plane loop (chroma skipped too), a zero chroma level skips that plane.
+    unsigned mask = 0;
+    for (int p = plane_start; p < plane_end; p++) {
+        if (p == 0 && !lf->filter_level[0] && !lf->filter_level[1])
+            break;
+        if (p == 1 && !lf->filter_level_u)
+            continue;
+        if (p == 2 && !lf->filter_level_v)
+            continue;
+        mask |= 1u << p;
+    }
+    if (!mask)
+        return SVTF_OK; // nothing to filter: the picture stays where it is
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    DeblockArgs a;
+    const int   nxt = next_surface(c);
+    a.in        = c->surf[c->cur].planes();
+    a.out       = c->surf[nxt].planes();
+    a.mi        = c->d_mi;
+    a.mi_stride = c->mi_stride;
+    a.d         = dims_of(c->geom);
+    int total   = 0;
+    for (int p = 0; p < 3; p++) {
+        const int w = (c->geom.mi_cols * 4) >> (p ? 1 : 0), h = (c->geom.mi_rows * 4) >> (p ? 1 : 0);
+        a.tiles_x[p]   = (w + 8 + DBK_TILE - 1) / DBK_TILE;
+        a.tiles_y[p]   = (h + 8 + DBK_TILE - 1) / DBK_TILE;
+        a.tile_base[p] = total;
+        total += a.tiles_x[p] * a.tiles_y[p];
+    }
+    a.plane_mask = mask;
+    build_lf_tables(*lf, a.t);
+    if (c->geom.sample_bytes == 1)
+        deblock_kernel<uint8_t><<<total, DBK_THREADS, 0, c->stream>>>(a);
+    else
+        deblock_kernel<uint16_t><<<total, DBK_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    c->cur = nxt;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_cdef_apply_frame(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t *fb_strength_idx) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL context");
+    if (!cp || !fb_strength_idx)
+        return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL argument");
+    if (int r = need_frame_mi(c, "svtf_cdef_apply_frame"))
+        return r;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16;
+    for (int i = 0; i < nvfb * nhfb; i++)
+        if (fb_strength_idx[i] >= SVTF_CDEF_MAX_STRENGTHS)
+            return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: strength index out of range");
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_fb_idx, fb_strength_idx, (size_t)nvfb * nhfb, cudaMemcpyHostToDevice, c->stream));
+    CdefArgs a;
+    const int nxt = next_surface(c);
+    a.in        = c->surf[c->cur].planes();
+    a.out       = c->surf[nxt].planes();
+    a.mi        = c->d_mi;
+    a.mi_stride = c->mi_stride;
+    a.d         = dims_of(c->geom);
+    a.fb_idx    = c->d_fb_idx;
+    a.damping   = cp->cdef_damping;
+    memcpy(a.y_strength, cp->cdef_y_strength, sizeof(a.y_strength));
+    memcpy(a.uv_strength, cp->cdef_uv_strength, sizeof(a.uv_strength));
+    dim3 grid(nhfb, nvfb);
+    if (c->geom.sample_bytes == 1)
+        cdef_kernel<uint8_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
+    else
+        cdef_kernel<uint16_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    c->pre_cdef = c->cur;
+    c->cur      = nxt;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL context");
+    if (!cc)
+        return c->fail(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL argument");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_ccso_apply_frame: no picture uploaded");
+    for (int p = 0; p < 3; p++)
+        if (cc->quant_idx[p] > 3 || cc->ext_filter_support[p] > 5 || cc->max_band_log2[p] > 7 || cc->edge_clf[p] > 1)
+            return c->fail(SVTF_E_ARG, "svtf_ccso_apply_frame: parameter out of range");
+    if (!(cc->ccso_enable[0] | cc->ccso_enable[1] | cc->ccso_enable[2]))
+        return SVTF_OK;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    static const uint8_t quant_sz[4] = {16, 8, 32, 64}; // Common/Codec/EbCcso.c:636
+    CcsoArgs a;
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_ccso_lut, cc->filter_offset, 3 * SVTF_CCSO_LUT_SIZE, cudaMemcpyHostToDevice, c->stream));
+    for (int p = 0; p < 3; p++) {
+        a.enable[p] = cc->ccso_enable[p] != 0, a.bo_only[p] = cc->ccso_bo_only[p] != 0;
+        a.thr[p] = quant_sz[cc->quant_idx[p]], a.support[p] = cc->ext_filter_support[p];
+        a.edge_clf[p] = cc->edge_clf[p], a.band_log2[p] = cc->max_band_log2[p];
+        a.blk_flags[p] = nullptr;
+        if (blk_flags && blk_flags[p]) {
+            const int pw = c->geom.width >> (p ? 1 : 0), ph = c->geom.height >> (p ? 1 : 0), bl = p ? 7 : 8;
+            const int n  = ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl);
+            uint8_t  *d  = c->d_ccso_flags + (size_t)p * c->max_ccso_blocks;
+            CUDA_TRY(c, cudaMemcpyAsync(d, blk_flags[p], n, cudaMemcpyHostToDevice, c->stream));
+            a.blk_flags[p] = d;
+        }
+    }
+    a.lut = c->d_ccso_lut;
+    a.d   = dims_of(c->geom);
+    a.in  = c->surf[c->cur].planes();
+    int nxt = c->cur;
+    if (c->pre_cdef >= 0) { // classify on the pre-CDEF luma, modify the post-CDEF picture in place
+        a.luma_src = c->surf[c->pre_cdef].planes();
+        a.out      = a.in;
+    } else { // no CDEF in this chain: luma is both classifier input and output -> go out of place
+        nxt        = next_surface(c);
+        a.luma_src = a.in;
+        a.out      = c->surf[nxt].planes();
+    }
+    dim3 grid((c->geom.mi_cols * 4 + 63) / 64, (c->geom.mi_rows * 4 + 63) / 64);
+    if (c->geom.sample_bytes == 1)
+        ccso_kernel<uint8_t><<<grid, CCSO_THREADS, 0, c->stream>>>(a);
+    else
+        ccso_kernel<uint16_t><<<grid, CCSO_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    c->cur = nxt;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_filter_chain(svtf_ctx *c, const svtf_lf_params *lf, const svtf_cdef_params *cdef, const int8_t *fb_strength_idx,
+                                 const svtf_ccso_params *ccso, const uint8_t *const blk_flags[3]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_filter_chain: NULL context");
+    int r = SVTF_OK;
+    if (lf && (r = svtf_deblock_frame(c, lf, 0, 3)) != SVTF_OK)
+        return r;
+    if (cdef && (r = svtf_cdef_apply_frame(c, cdef, fb_strength_idx)) != SVTF_OK)
+        return r;
+    if (ccso && (r = svtf_ccso_apply_frame(c, ccso, blk_flags)) != SVTF_OK)
+        return r;
+    return r;
+}
+
+extern "C" int svtf_dev_planes(svtf_ctx *c, int which, svtf_dev_plane out[3]) {
+    if (!c || !out || which < 0 || which > 2)
+        return set_global_error(SVTF_E_ARG, "svtf_dev_planes: bad argument");
+    if (!c->have_geom)
+        return c->fail(SVTF_E_STATE, "svtf_dev_planes: call svtf_frame_begin first");
+    const Surface &s = which == 0 ? c->surf[0] : (which == 1 ? c->surf[c->cur] : c->source);
+    for (int p = 0; p < 3; p++) {
+        out[p].ptr    = s.base[p];
+        out[p].pitch  = s.pitch[p];
+        out[p].width  = (c->geom.mi_cols * 4) >> (p ? 1 : 0);
+        out[p].height = (c->geom.mi_rows * 4) >> (p ? 1 : 0);
+    }
+    return SVTF_OK;
+}
+
+// ---- CDEF strength search ------------------------------------------------------------------------
+extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, uint64_t *mse, uint8_t *skip, uint8_t *dir,
+                                      int32_t *var) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_cdef_search_frame: NULL context");
+    if (!cfg)
+        return c->fail(SVTF_E_ARG, "svtf_cdef_search_frame: NULL cfg");
+    if (int r = need_frame_mi(c, "svtf_cdef_search_frame"))
+        return r;
+    if (!c->have_source)
+        return c->fail(SVTF_E_STATE, "svtf_cdef_search_frame: upload the source picture first");
+    const int n = cfg->first_pass_fs_num + cfg->default_second_pass_fs_num;
+    if (n <= 0 || n > SVTF_TOTAL_STRENGTHS || cfg->first_pass_fs_num < 0 || cfg->default_second_pass_fs_num < 0 ||
+        (cfg->subsampling_factor != 1 && cfg->subsampling_factor != 2 && cfg->subsampling_factor != 4))
+        return c->fail(SVTF_E_ARG, "svtf_cdef_search_frame: bad strength counts or subsampling factor");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
+    SearchArgs a;
+    a.rec = c->surf[c->cur].planes();
+    a.src = c->source.planes();
+    a.mi = c->d_mi, a.mi_stride = c->mi_stride;
+    a.d = dims_of(c->geom);
+    a.n = n;
+    for (int gi = 0; gi < n; gi++) {
+        const bool first = gi < cfg->first_pass_fs_num;
+        a.fs[gi]    = first ? cfg->default_first_pass_fs[gi] : cfg->default_second_pass_fs[gi - cfg->first_pass_fs_num];
+        a.fs_uv[gi] = first ? cfg->default_first_pass_fs_uv[gi] : cfg->default_second_pass_fs_uv[gi - cfg->first_pass_fs_num];
+    }
+    a.damping = 3 + (cfg->base_q_idx >> 6);
+    a.subsampling = cfg->subsampling_factor;
+    a.mse = c->d_mse, a.skip = c->d_skip, a.dir = c->d_dir, a.var = c->d_var;
+    a.nfb = nfb;
+    CUDA_TRY(c, cudaMemsetAsync(c->d_dir, 0, 64 * (size_t)nfb, c->stream));
+    CUDA_TRY(c, cudaMemsetAsync(c->d_var, 0, sizeof(int32_t) * 64 * (size_t)nfb, c->stream));
+    CUDA_TRY(c, cudaMemsetAsync(c->d_mse, 0, sizeof(uint64_t) * 128 * (size_t)nfb, c->stream));
+    dim3 grid(nhfb, nvfb);
+    if (c->geom.sample_bytes == 1)
+        cdef_search_kernel<uint8_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
+    else
+        cdef_search_kernel<uint16_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    c->have_search = true;
+    if (mse) CUDA_TRY(c, cudaMemcpyAsync(mse, c->d_mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
+    if (skip) CUDA_TRY(c, cudaMemcpyAsync(skip, c->d_skip, nfb, cudaMemcpyDeviceToHost, c->stream));
+    if (dir) CUDA_TRY(c, cudaMemcpyAsync(dir, c->d_dir, 64 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
+    if (var) CUDA_TRY(c, cudaMemcpyAsync(var, c->d_var, sizeof(int32_t) * 64 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
+    if (mse || skip || dir || var)
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return SVTF_OK;
+}
+
+extern "C" int svtf_cdef_pick(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, svtf_cdef_params *out_params, int8_t *fb_strength_idx) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_cdef_pick: NULL context");
+    if (!cfg || !out_params || !fb_strength_idx)
+        return c->fail(SVTF_E_ARG, "svtf_cdef_pick: NULL argument");
+    if (!c->have_search)
+        return c->fail(SVTF_E_STATE, "svtf_cdef_pick: run svtf_cdef_search_frame first");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
+    std::vector<uint64_t> mse((size_t)128 * nfb);
+    std::vector<uint8_t>  skip(nfb);
+    CUDA_TRY(c, cudaMemcpyAsync(mse.data(), c->d_mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(skip.data(), c->d_skip, nfb, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int r = svtf_cdef_pick_host(cfg, mse.data(), skip.data(), nfb, out_params, fb_strength_idx);
+    if (r != SVTF_OK)
+        c->err = svtf_last_error(nullptr);
+    return r;
+}

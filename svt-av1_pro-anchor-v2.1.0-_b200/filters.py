@@ -1,0 +1,281 @@
+"""Host-side mirror of the reference's frame-level filter interface, over the C ABI.
+
+Method names follow the reference entry points they replace:
+
+  FilterContext.loop_filter_frame   <- svt_av1_loop_filter_frame   (Encoder/Codec/EbDeblockingFilter.c:624)
+  FilterContext.cdef_frame          <- svt_av1_cdef_frame          (Encoder/Codec/EbEncCdef.c:284)
+  FilterContext.ccso_frame          <- ccso_frame                  (Common/Codec/EbCcso.c:626)
+  FilterContext.cdef_seg_search     <- cdef_seg_search             (Encoder/Codec/EbCdefProcess.c:114)
+  FilterContext.finish_cdef_search  <- finish_cdef_search          (Encoder/Codec/EbEncCdef.c:728)
+
+Pictures are numpy arrays (uint8 or uint16) in host memory; everything else is plain values.  This
+module only marshals; all arithmetic happens in libsvtfilt_b200.so on the GPU (no CPU fallback).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+class SvtfError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"svtf error {code}: {msg}")
+        self.code = code
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def make_geom(width, height, bit_depth, sample_bytes=None):
+    """Geometry of a picture: coded size = dimensions rounded up to 8 (mi_cols/mi_rows even)."""
+    if sample_bytes is None:
+        sample_bytes = 1 if bit_depth == 8 else 2
+    return L.Geom(width, height, 2 * ((width + 7) // 8), 2 * ((height + 7) // 8), bit_depth, sample_bytes)
+
+
+def lf_params(filter_level=(0, 0), filter_level_u=0, filter_level_v=0, sharpness_level=0, mode_ref_delta_enabled=0,
+              ref_deltas=(1, 0, 0, 0, -1, 0, -1, -1), mode_deltas=(0, 0), segmentation_enabled=0, seg_feature_enabled=None,
+              seg_feature_data=None, delta_lf_present=0, delta_lf_multi=0, curr_delta_lf=(0, 0, 0, 0)):
+    p = L.LfParams()
+    p.filter_level[0], p.filter_level[1] = filter_level
+    p.filter_level_u, p.filter_level_v, p.sharpness_level = filter_level_u, filter_level_v, sharpness_level
+    p.mode_ref_delta_enabled = mode_ref_delta_enabled
+    for i, v in enumerate(ref_deltas):
+        p.ref_deltas[i] = v
+    for i, v in enumerate(mode_deltas):
+        p.mode_deltas[i] = v
+    p.segmentation_enabled = segmentation_enabled
+    if seg_feature_enabled is not None:
+        for s in range(8):
+            for f in range(8):
+                p.seg_feature_enabled[s][f] = int(seg_feature_enabled[s][f])
+                p.seg_feature_data[s][f] = int(seg_feature_data[s][f])
+    p.delta_lf_present, p.delta_lf_multi = delta_lf_present, delta_lf_multi
+    for i, v in enumerate(curr_delta_lf):
+        p.curr_delta_lf[i] = v
+    return p
+
+
+def cdef_params(damping, y_strengths, uv_strengths):
+    p = L.CdefParams()
+    p.cdef_damping = damping
+    n = len(y_strengths)
+    p.cdef_bits = max(0, (n - 1).bit_length())
+    for i in range(n):
+        p.cdef_y_strength[i] = y_strengths[i]
+        p.cdef_uv_strength[i] = uv_strengths[i]
+    return p
+
+
+def cdef_search_cfg(first_pass, second_pass, first_pass_uv=None, second_pass_uv=None, subsampling_factor=1, base_q_idx=120,
+                    zero_fs_cost_bias=0, lambda_=0):
+    c = L.CdefSearchCfg()
+    c.first_pass_fs_num, c.default_second_pass_fs_num = len(first_pass), len(second_pass)
+    first_pass_uv = first_pass if first_pass_uv is None else first_pass_uv
+    second_pass_uv = second_pass if second_pass_uv is None else second_pass_uv
+    for i, v in enumerate(first_pass):
+        c.default_first_pass_fs[i] = v
+        c.default_first_pass_fs_uv[i] = first_pass_uv[i]
+    for i, v in enumerate(second_pass):
+        c.default_second_pass_fs[i] = v
+        c.default_second_pass_fs_uv[i] = second_pass_uv[i]
+    c.subsampling_factor, c.base_q_idx, c.zero_fs_cost_bias, c.lambda_ = subsampling_factor, base_q_idx, zero_fs_cost_bias, lambda_
+    return c
+
+
+def ccso_params(enable=(1, 1, 1), bo_only=(0, 0, 0), quant_idx=(0, 0, 0), ext_filter_support=(0, 0, 0), edge_clf=(0, 0, 0),
+                max_band_log2=(0, 0, 0), filter_offset=None):
+    p = L.CcsoParams()
+    for i in range(3):
+        p.ccso_enable[i], p.ccso_bo_only[i], p.quant_idx[i] = enable[i], bo_only[i], quant_idx[i]
+        p.ext_filter_support[i], p.edge_clf[i], p.max_band_log2[i] = ext_filter_support[i], edge_clf[i], max_band_log2[i]
+    if filter_offset is not None:
+        fo = np.ascontiguousarray(filter_offset, dtype=np.int8).reshape(3, L.CCSO_LUT_SIZE)
+        C.memmove(p.filter_offset, fo.ctypes.data, 3 * L.CCSO_LUT_SIZE)
+    return p
+
+
+def pack_mi_enc(bsize, tx_depth, skip, ref_frame0, mode, segment_id):
+    """svtf_pack_mi_enc over 2-D uint8 arrays of shape (mi_rows, mi_cols) -> uint32 grid."""
+    lib = L.load()
+    arrs = [np.ascontiguousarray(a, dtype=np.uint8) for a in (bsize, tx_depth, skip, ref_frame0, mode, segment_id)]
+    out = np.empty(arrs[0].shape, dtype=np.uint32)
+    r = lib.svtf_pack_mi_enc(arrs[0].size, *[_ptr(a) for a in arrs], _ptr(out))
+    if r:
+        raise SvtfError(r, lib.svtf_last_error(None).decode())
+    return out
+
+
+def pack_mi_dec(bsize, tx_size_y, tx_size_uv, skip, ref_frame0, mode, segment_id):
+    lib = L.load()
+    arrs = [np.ascontiguousarray(a, dtype=np.uint8) for a in (bsize, tx_size_y, tx_size_uv, skip, ref_frame0, mode, segment_id)]
+    out = np.empty(arrs[0].shape, dtype=np.uint32)
+    r = lib.svtf_pack_mi_dec(arrs[0].size, *[_ptr(a) for a in arrs], _ptr(out))
+    if r:
+        raise SvtfError(r, lib.svtf_last_error(None).decode())
+    return out
+
+
+def cdef_pick_host(cfg, mse, skip):
+    """svtf_cdef_pick_host: finish_cdef_search on a host table mse[2][nfb][64] (uint64), skip[nfb]."""
+    lib = L.load()
+    mse = np.ascontiguousarray(mse, dtype=np.uint64)
+    skip = np.ascontiguousarray(skip, dtype=np.uint8)
+    nfb = skip.size
+    out = L.CdefParams()
+    idx = np.empty(nfb, dtype=np.int8)
+    r = lib.svtf_cdef_pick_host(C.byref(cfg), _ptr(mse), _ptr(skip), nfb, C.byref(out), _ptr(idx))
+    if r:
+        raise SvtfError(r, lib.svtf_last_error(None).decode())
+    return out, idx
+
+
+class PinnedPicture:
+    """Three planes in page-locked host memory (svtf_host_alloc), exposed as numpy arrays."""
+
+    def __init__(self, geom):
+        lib = L.load()
+        self._lib = lib
+        dt = np.uint8 if geom.sample_bytes == 1 else np.uint16
+        self.planes, self._ptrs = [], []
+        for p in range(3):
+            w, h = (geom.mi_cols * 4) >> (1 if p else 0), (geom.mi_rows * 4) >> (1 if p else 0)
+            nbytes = w * h * geom.sample_bytes
+            ptr = lib.svtf_host_alloc(nbytes)
+            if not ptr:
+                raise SvtfError(L.E_NOMEM, "svtf_host_alloc failed")
+            self._ptrs.append(ptr)
+            buf = (C.c_uint8 * nbytes).from_address(ptr)
+            self.planes.append(np.frombuffer(buf, dtype=dt).reshape(h, w))
+
+    def close(self):
+        for ptr in self._ptrs:
+            self._lib.svtf_host_free(ptr)
+        self._ptrs, self.planes = [], []
+
+
+class FilterContext:
+    """One picture in flight on one GPU (svtf_ctx)."""
+
+    def __init__(self, max_geom, device=0):
+        self._lib = L.load()
+        self._h = C.c_void_p()
+        self.max_geom = max_geom
+        r = self._lib.svtf_ctx_create(device, C.byref(max_geom), C.byref(self._h))
+        if r:
+            raise SvtfError(r, self._lib.svtf_last_error(None).decode())
+        self.geom = None
+
+    def close(self):
+        if self._h:
+            self._lib.svtf_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, r):
+        if r:
+            raise SvtfError(r, self._lib.svtf_last_error(self._h).decode())
+
+    # ---- picture / side info ----
+    def begin(self, geom):
+        self.geom = geom
+        self._chk(self._lib.svtf_frame_begin(self._h, C.byref(geom)))
+
+    def _planes_args(self, planes):
+        args = []
+        for a in planes:
+            assert a.strides[1] == a.itemsize and a.itemsize == self.geom.sample_bytes
+            args += [_ptr(a), a.strides[0] // a.itemsize]
+        return args
+
+    def upload(self, planes):
+        self._chk(self._lib.svtf_upload_frame(self._h, *self._planes_args(planes)))
+
+    def upload_source(self, planes):
+        self._chk(self._lib.svtf_upload_source(self._h, *self._planes_args(planes)))
+
+    def set_mi(self, mi):
+        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        self._mi_keep = mi
+        self._chk(self._lib.svtf_set_mi(self._h, _ptr(mi), mi.shape[1]))
+
+    def download(self, out=None):
+        g = self.geom
+        if out is None:
+            dt = np.uint8 if g.sample_bytes == 1 else np.uint16
+            out = [np.empty(((g.mi_rows * 4) >> s, (g.mi_cols * 4) >> s), dtype=dt) for s in (0, 1, 1)]
+        self._chk(self._lib.svtf_download_frame(self._h, *self._planes_args(out)))
+        return out
+
+    def rewind(self):
+        self._chk(self._lib.svtf_rewind(self._h))
+
+    def sync(self):
+        self._chk(self._lib.svtf_sync(self._h))
+
+    @property
+    def launch_count(self):
+        return int(self._lib.svtf_launch_count(self._h))
+
+    @property
+    def cuda_stream(self):
+        return self._lib.svtf_cuda_stream(self._h)
+
+    def dev_planes(self, which=1):
+        arr = (L.DevPlane * 3)()
+        self._chk(self._lib.svtf_dev_planes(self._h, which, arr))
+        return [(arr[i].ptr, arr[i].pitch, arr[i].width, arr[i].height) for i in range(3)]
+
+    # ---- filters (reference entry-point names) ----
+    def loop_filter_frame(self, lf, plane_start=0, plane_end=3):
+        self._chk(self._lib.svtf_deblock_frame(self._h, C.byref(lf), plane_start, plane_end))
+
+    def cdef_frame(self, cdef, fb_strength_idx):
+        idx = np.ascontiguousarray(fb_strength_idx, dtype=np.int8)
+        self._chk(self._lib.svtf_cdef_apply_frame(self._h, C.byref(cdef), _ptr(idx)))
+
+    @staticmethod
+    def _flag_ptrs(blk_flags):
+        if blk_flags is None:
+            return None, None
+        keep = [None if f is None else np.ascontiguousarray(f, dtype=np.uint8) for f in blk_flags]
+        arr = (C.c_void_p * 3)(*[None if k is None else k.ctypes.data for k in keep])
+        return arr, keep
+
+    def ccso_frame(self, ccso, blk_flags=None):
+        arr, keep = self._flag_ptrs(blk_flags)
+        self._chk(self._lib.svtf_ccso_apply_frame(self._h, C.byref(ccso), arr))
+
+    def filter_chain(self, lf=None, cdef=None, fb_strength_idx=None, ccso=None, blk_flags=None):
+        idx = None if fb_strength_idx is None else np.ascontiguousarray(fb_strength_idx, dtype=np.int8)
+        arr, keep = self._flag_ptrs(blk_flags)
+        self._chk(self._lib.svtf_filter_chain(self._h, None if lf is None else C.byref(lf), None if cdef is None else C.byref(cdef),
+                                              _ptr(idx), None if ccso is None else C.byref(ccso), arr))
+
+    def cdef_seg_search(self, cfg, want_outputs=True):
+        g = self.geom
+        nfb = ((g.mi_rows + 15) // 16) * ((g.mi_cols + 15) // 16)
+        if not want_outputs:
+            self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), None, None, None, None))
+            return None
+        mse = np.zeros((2, nfb, 64), dtype=np.uint64)
+        skip = np.zeros(nfb, dtype=np.uint8)
+        dirs = np.zeros((nfb, 64), dtype=np.uint8)
+        var = np.zeros((nfb, 64), dtype=np.int32)
+        self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), _ptr(dirs), _ptr(var)))
+        return mse, skip, dirs, var
+
+    def finish_cdef_search(self, cfg):
+        g = self.geom
+        nfb = ((g.mi_rows + 15) // 16) * ((g.mi_cols + 15) // 16)
+        out = L.CdefParams()
+        idx = np.empty(nfb, dtype=np.int8)
+        self._chk(self._lib.svtf_cdef_pick(self._h, C.byref(cfg), C.byref(out), _ptr(idx)))
+        return out, idx

@@ -1,0 +1,378 @@
+"""Test/bench harness: seeded synthetic inputs and ctypes bindings of the two CPU checkers.
+
+  Oracle  — oracle/liborc.so   (oracle/svtf_oracle.c, the CPU restatement; always available)
+  Ref     — oracle/_ref/libsvtref.so (the reference's own C compiled from /root/reference by
+            oracle/Makefile; present wherever `make -C oracle` ran with the reference mounted, and
+            it travels to the GPU box as a built file)
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU legs import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+import svtfilt_b200 as S  # noqa: E402
+from svtfilt_b200 import _lib as L  # noqa: E402
+
+ORC_PATH = os.path.join(ROOT, "oracle", "liborc.so")
+REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libsvtref.so")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def build_oracle():
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "--no-print-directory"], check=True, stdout=subprocess.DEVNULL)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _planes(pl):
+    out = []
+    for a in pl:
+        assert a.strides[1] == a.itemsize
+        out += [_p(a), a.strides[0] // a.itemsize]
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic inputs (SURVEY §8d recipe)
+# ------------------------------------------------------------------------------------------------
+BLOCK_DIMS = [(4, 4), (4, 8), (8, 4), (8, 8), (8, 16), (16, 8), (16, 16), (16, 32), (32, 16), (32, 32), (32, 64), (64, 32),
+              (64, 64), (64, 128), (128, 64), (128, 128), (4, 16), (16, 4), (8, 32), (32, 8), (16, 64), (64, 16)]
+BSIZE_OF = {d: i for i, d in enumerate(BLOCK_DIMS)}
+
+
+def synth_picture(geom, seed, frame=0, noise=6, planes_like=None):
+    """Smooth sinusoid + 16x16 block DC steps + uniform noise, scaled to the bit depth."""
+    rng = np.random.default_rng(seed)
+    sh = geom.bit_depth - 8
+    dt = np.uint8 if geom.sample_bytes == 1 else np.uint16
+    out = []
+    for p in range(3):
+        s = 1 if p else 0
+        w, h = (geom.mi_cols * 4) >> s, (geom.mi_rows * 4) >> s
+        x = np.arange(w, dtype=np.float64)[None, :] * (1 << s)
+        y = np.arange(h, dtype=np.float64)[:, None] * (1 << s)
+        base = 128 + (60 - 20 * p) * np.sin((x + 3 * frame + 11 * p) / 17.0) + (40 - 10 * p) * np.cos((y - 2 * frame) / 11.0)
+        bs = 16 >> s
+        dc = rng.integers(-6, 7, size=((h + bs - 1) // bs, (w + bs - 1) // bs))
+        base = base + np.kron(dc, np.ones((bs, bs)))[:h, :w]
+        base = base + rng.integers(-noise, noise + 1, size=(h, w))
+        v = np.clip(np.rint(base), 0, 255).astype(np.int64) << sh
+        if sh:
+            v = v + rng.integers(0, 1 << sh, size=(h, w))
+        out.append(np.ascontiguousarray(v.astype(dt)))
+    return out
+
+
+def synth_source(geom, recon, seed, amp=8):
+    """Source picture = recon + uniform noise (for the search distortion)."""
+    rng = np.random.default_rng(seed ^ 0x5EED)
+    sh = geom.bit_depth - 8
+    mx = (1 << geom.bit_depth) - 1
+    return [np.ascontiguousarray(np.clip(r.astype(np.int64) + (rng.integers(-amp, amp + 1, size=r.shape) << sh), 0, mx).astype(r.dtype))
+            for r in recon]
+
+
+def synth_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=False):
+    """Valid AV1 partition of every 64x64 superblock (NONE / SPLIT / HORZ / VERT / HORZ_4 / VERT_4), with a
+    uniform tx_depth, skip, ref_frame, mode and segment per block.  Returns a dict of (mi_rows, mi_cols)
+    uint8 arrays."""
+    rng = np.random.default_rng(seed)
+    R, Cc = geom.mi_rows, geom.mi_cols
+    soa = {k: np.zeros((R, Cc), dtype=np.uint8) for k in ("bsize", "tx_depth", "skip", "ref_frame0", "mode", "segment_id")}
+
+    def put(r, c, w, h):
+        if r >= R or c >= Cc:
+            return
+        r1, c1 = min(R, r + h // 4), min(Cc, c + w // 4)
+        inter = rng.random() < p_inter
+        soa["bsize"][r:r1, c:c1] = BSIZE_OF[(w, h)]
+        soa["tx_depth"][r:r1, c:c1] = rng.integers(0, 3)
+        soa["skip"][r:r1, c:c1] = rng.random() < p_skip
+        soa["ref_frame0"][r:r1, c:c1] = rng.integers(1, 8) if inter else 0
+        soa["mode"][r:r1, c:c1] = rng.integers(13, 25) if inter else rng.integers(0, 13)
+        soa["segment_id"][r:r1, c:c1] = rng.integers(0, 8) if segments else 0
+
+    def part(r, c, s):
+        if r >= R or c >= Cc:
+            return
+        u = rng.random()
+        if s == 4 or (s > 8 and u >= p_split + 0.25) or (s == 8 and u >= p_split + 0.3):
+            put(r, c, s, s)
+        elif u < p_split:
+            if s == 8:
+                for dr, dc in ((0, 0), (0, 1), (1, 0), (1, 1)):
+                    put(r + dr, c + dc, 4, 4)
+            else:
+                h = s // 2
+                for dr, dc in ((0, 0), (0, h // 4), (h // 4, 0), (h // 4, h // 4)):
+                    part(r + dr, c + dc, h)
+        else:
+            k = rng.integers(0, 4 if s >= 16 else 2)
+            if k == 0:  # HORZ
+                put(r, c, s, s // 2), put(r + s // 8, c, s, s // 2)
+            elif k == 1:  # VERT
+                put(r, c, s // 2, s), put(r, c + s // 8, s // 2, s)
+            elif k == 2:  # HORZ_4
+                for i in range(4):
+                    put(r + i * s // 16, c, s, s // 4)
+            else:  # VERT_4
+                for i in range(4):
+                    put(r, c + i * s // 16, s // 4, s)
+
+    for r in range(0, R, 16):
+        for c in range(0, Cc, 16):
+            part(r, c, 64)
+    return soa
+
+
+def pack_mi(soa):
+    return S.pack_mi_enc(soa["bsize"], soa["tx_depth"], soa["skip"], soa["ref_frame0"], soa["mode"], soa["segment_id"])
+
+
+def nfb_of(geom):
+    return (geom.mi_rows + 15) // 16, (geom.mi_cols + 15) // 16
+
+
+def synth_cdef(geom, seed, n_strengths=8, damping=5, p_unset=0.0):
+    rng = np.random.default_rng(seed ^ 0xCDEF)
+    ys = [int(v) for v in rng.integers(0, 64, size=n_strengths)]
+    us = [int(v) for v in rng.integers(0, 64, size=n_strengths)]
+    ys[0] = 0
+    us[0] = 0  # one all-zero pair so the "strength (0,0,0,0)" path is exercised
+    nv, nh = nfb_of(geom)
+    idx = rng.integers(0, n_strengths, size=nv * nh).astype(np.int8)
+    return S.cdef_params(damping, ys, us), idx
+
+
+def synth_ccso(geom, seed, quant_idx=(0, 0, 0), support=(0, 1, 2), edge_clf=(0, 0, 0), band_log2=(2, 2, 2), bo_only=(0, 0, 0),
+               enable=(1, 1, 1), p_on=0.8):
+    rng = np.random.default_rng(seed ^ 0xCC50)
+    lut = rng.choice(np.array([-10, -7, -3, -1, 0, 1, 3, 7], dtype=np.int8), size=(3, L.CCSO_LUT_SIZE))
+    flags = []
+    for p in range(3):
+        pw, ph, bl = geom.width >> (1 if p else 0), geom.height >> (1 if p else 0), 7 if p else 8
+        n = ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl)
+        flags.append((rng.random(n) < p_on).astype(np.uint8))
+    return S.ccso_params(enable, bo_only, quant_idx, support, edge_clf, band_log2, lut), flags
+
+
+def cdef_level1_lists():
+    """cdef_level 1 (exhaustive, presets <= M0): 16 primary {0,4,..,60} then 48 secondary pri+{1,2,3}
+    (Encoder/Codec/EncModeConfig.c:871-910)."""
+    first = [4 * i for i in range(16)]
+    second = [4 * i + s for i in range(16) for s in (1, 2, 3)]
+    return first, second
+
+
+# ------------------------------------------------------------------------------------------------
+# the CPU restatement
+# ------------------------------------------------------------------------------------------------
+class Oracle:
+    def __init__(self):
+        if not os.path.exists(ORC_PATH):
+            build_oracle()
+        self.lib = C.CDLL(ORC_PATH)
+        self.lib.orc_cdef_dist.restype = C.c_uint64
+
+    def deblock(self, geom, planes, mi, lf, plane_start=0, plane_end=3):
+        out = [p.copy() for p in planes]
+        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        r = self.lib.orc_deblock_frame(C.byref(geom), *_planes(out), _p(mi), C.c_int(mi.shape[1]), C.byref(lf), plane_start, plane_end)
+        assert r == 0
+        return out
+
+    def cdef_apply(self, geom, planes, mi, cdef, fb_idx):
+        out = [p.copy() for p in planes]
+        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        idx = np.ascontiguousarray(fb_idx, dtype=np.int8)
+        r = self.lib.orc_cdef_apply_frame(C.byref(geom), *_planes(out), _p(mi), C.c_int(mi.shape[1]), C.byref(cdef), _p(idx))
+        assert r == 0
+        return out
+
+    def ccso_apply(self, geom, planes, pre_luma, ccso, flags):
+        out = [p.copy() for p in planes]
+        fl = (C.c_void_p * 3)(*[None if f is None else f.ctypes.data for f in (flags or [None] * 3)])
+        r = self.lib.orc_ccso_apply_frame(C.byref(geom), *_planes(out), _p(pre_luma), C.c_int(pre_luma.strides[0] // pre_luma.itemsize),
+                                          C.byref(ccso), fl if flags is not None else None)
+        assert r == 0
+        return out
+
+    def cdef_search(self, geom, rec, src, mi, cfg):
+        nv, nh = nfb_of(geom)
+        nfb = nv * nh
+        mse = np.zeros((2, nfb, 64), dtype=np.uint64)
+        skip = np.zeros(nfb, dtype=np.uint8)
+        dirs = np.zeros((nfb, 64), dtype=np.uint8)
+        var = np.zeros((nfb, 64), dtype=np.int32)
+        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        r = self.lib.orc_cdef_search_frame(C.byref(geom), *_planes(rec), *_planes(src), _p(mi), C.c_int(mi.shape[1]), C.byref(cfg),
+                                           _p(mse), _p(skip), _p(dirs), _p(var))
+        assert r == 0
+        return mse, skip, dirs, var
+
+    def cdef_pick(self, cfg, mse, skip):
+        mse = np.ascontiguousarray(mse, dtype=np.uint64).copy()
+        skip = np.ascontiguousarray(skip, dtype=np.uint8)
+        out = L.CdefParams()
+        idx = np.empty(skip.size, dtype=np.int8)
+        r = self.lib.orc_cdef_pick(C.byref(cfg), _p(mse), _p(skip), C.c_int(skip.size), C.byref(out), _p(idx))
+        assert r == 0
+        return out, idx
+
+    def lpf_edge(self, buf, offset, along, nxt, count, length, bd, blimit, limit, thresh):
+        """buf: 2-D array modified in place; offset: flat index of q0 of line 0."""
+        base = buf.ctypes.data + offset * buf.itemsize
+        self.lib.orc_lpf_edge(C.c_void_p(base), buf.itemsize, along, nxt, count, length, bd, blimit, limit, thresh)
+
+    def find_dir(self, img, coeff_shift):
+        img = np.ascontiguousarray(img, dtype=np.uint16)
+        var = C.c_int32()
+        d = self.lib.orc_cdef_find_dir(_p(img), C.c_int(img.shape[1]), C.byref(var), coeff_shift)
+        return d, var.value
+
+    def filter_block(self, tile, y, x, pri, sec, direction, pri_damping, sec_damping, bw, bh, coeff_shift, sub=1):
+        tile = np.ascontiguousarray(tile, dtype=np.uint16)
+        dst = np.zeros((bh, bw), dtype=np.uint16)
+        base = tile.ctypes.data + (y * tile.shape[1] + x) * 2
+        self.lib.orc_cdef_filter_block(_p(dst), bw, C.c_void_p(base), tile.shape[1], pri, sec, direction, pri_damping, sec_damping, bw, bh,
+                                       coeff_shift, sub)
+        return dst
+
+    def cdef_dist(self, src, flt, by, bx, bw, bh, coeff_shift, pli, sub):
+        by = np.ascontiguousarray(by, dtype=np.uint8)
+        bx = np.ascontiguousarray(bx, dtype=np.uint8)
+        flt = np.ascontiguousarray(flt, dtype=np.uint16)
+        return int(self.lib.orc_cdef_dist(_p(src), C.c_int(src.strides[0] // src.itemsize), src.itemsize, _p(flt), _p(by), _p(bx), len(by), bw, bh,
+                                          coeff_shift, pli, sub))
+
+
+# ------------------------------------------------------------------------------------------------
+# the real reference (compiled from /root/reference)
+# ------------------------------------------------------------------------------------------------
+class RefMiSoa(C.Structure):
+    _fields_ = [("bsize", C.c_void_p), ("tx_depth", C.c_void_p), ("skip", C.c_void_p), ("ref_frame0", C.c_void_p),
+                ("mode", C.c_void_p), ("segment_id", C.c_void_p), ("mi_stride", C.c_int32)]
+
+
+def ref_available():
+    return os.path.exists(REF_PATH)
+
+
+class Ref:
+    def __init__(self):
+        self.lib = C.CDLL(REF_PATH)
+        self.lib.ref_cdef_dist.restype = C.c_uint64
+
+    @staticmethod
+    def _soa(soa):
+        keep = {k: np.ascontiguousarray(v, dtype=np.uint8) for k, v in soa.items()}
+        s = RefMiSoa(*[keep[k].ctypes.data for k in ("bsize", "tx_depth", "skip", "ref_frame0", "mode", "segment_id")],
+                     keep["bsize"].shape[1])
+        return s, keep
+
+    def deblock(self, geom, planes, soa, lf, plane_start=0, plane_end=3):
+        out = [p.copy() for p in planes]
+        s, keep = self._soa(soa)
+        assert self.lib.ref_deblock_frame(C.byref(geom), *_planes(out), C.byref(s), C.byref(lf), plane_start, plane_end) == 0
+        return out
+
+    def cdef_apply(self, geom, planes, soa, cdef, fb_idx):
+        out = [p.copy() for p in planes]
+        s, keep = self._soa(soa)
+        idx = np.ascontiguousarray(fb_idx, dtype=np.int8)
+        assert self.lib.ref_cdef_apply_frame(C.byref(geom), *_planes(out), C.byref(s), C.byref(cdef), _p(idx)) == 0
+        return out
+
+    def ccso_apply(self, geom, planes, pre_luma, ccso, flags):
+        out = [p.copy() for p in planes]
+        fl = (C.c_void_p * 3)(*[None if f is None else f.ctypes.data for f in (flags or [None] * 3)])
+        assert self.lib.ref_ccso_apply_frame(C.byref(geom), *_planes(out), _p(pre_luma), C.c_int(pre_luma.strides[0] // pre_luma.itemsize),
+                                             C.byref(ccso), fl if flags is not None else None) == 0
+        return out
+
+    def cdef_search(self, geom, rec, src, soa, cfg):
+        nv, nh = nfb_of(geom)
+        nfb = nv * nh
+        mse = np.zeros((2, nfb, 64), dtype=np.uint64)
+        skip = np.zeros(nfb, dtype=np.uint8)
+        dirs = np.zeros((nfb, 64), dtype=np.uint8)
+        var = np.zeros((nfb, 64), dtype=np.int32)
+        s, keep = self._soa(soa)
+        assert self.lib.ref_cdef_search_frame(C.byref(geom), *_planes(rec), *_planes(src), C.byref(s), C.byref(cfg), _p(mse), _p(skip),
+                                              _p(dirs), _p(var)) == 0
+        return mse, skip, dirs, var
+
+    def cdef_pick(self, geom, soa, cfg, mse, skip):
+        mse = np.ascontiguousarray(mse, dtype=np.uint64)
+        skip = np.ascontiguousarray(skip, dtype=np.uint8)
+        out = L.CdefParams()
+        idx = np.empty(skip.size, dtype=np.int8)
+        s, keep = self._soa(soa)
+        assert self.lib.ref_cdef_pick(C.byref(geom), C.byref(s), C.byref(cfg), _p(mse), _p(skip), C.byref(out), _p(idx)) == 0
+        return out, idx
+
+    def lpf(self, buf, offset, pitch, vertical, length, bd, blimit, limit, thresh):
+        base = buf.ctypes.data + offset * buf.itemsize
+        self.lib.ref_lpf(C.c_void_p(base), buf.itemsize, pitch, vertical, length, bd, C.c_uint8(blimit), C.c_uint8(limit), C.c_uint8(thresh))
+
+    def find_dir(self, img, coeff_shift):
+        img = np.ascontiguousarray(img, dtype=np.uint16)
+        var = C.c_int32()
+        d = self.lib.ref_cdef_find_dir(_p(img), C.c_int(img.shape[1]), C.byref(var), coeff_shift)
+        return d, var.value
+
+    def bstride(self):
+        return self.lib.ref_cdef_bstride()
+
+    def filter_block(self, tile, y, x, pri, sec, direction, pri_damping, sec_damping, bw, bh, coeff_shift, sub=1):
+        """tile must have row stride CDEF_BSTRIDE."""
+        assert tile.shape[1] == self.bstride()
+        dst = np.zeros((bh, bw), dtype=np.uint16)
+        bsize = {(4, 4): 0, (4, 8): 1, (8, 4): 2, (8, 8): 3}[(bw, bh)]
+        base = tile.ctypes.data + (y * tile.shape[1] + x) * 2
+        self.lib.ref_cdef_filter_block(_p(dst), bw, C.c_void_p(base), pri, sec, direction, pri_damping, sec_damping, bsize, coeff_shift, sub)
+        return dst
+
+    def cdef_dist(self, src, flt, by, bx, bw, bh, coeff_shift, pli, sub):
+        by = np.ascontiguousarray(by, dtype=np.uint8)
+        bx = np.ascontiguousarray(bx, dtype=np.uint8)
+        bsize = {(4, 4): 0, (4, 8): 1, (8, 4): 2, (8, 8): 3}[(bw, bh)]
+        is16 = src.itemsize == 2
+        f = np.ascontiguousarray(flt, dtype=np.uint16 if is16 else np.uint8)
+        return int(self.lib.ref_cdef_dist(_p(src), C.c_int(src.strides[0] // src.itemsize), _p(f), _p(by), _p(bx), len(by), bsize, coeff_shift,
+                                          pli, sub, int(is16)))
+
+    def mi_tables(self, bsize, tx_depth):
+        v = [C.c_int() for _ in range(6)]
+        self.lib.ref_mi_tables(bsize, tx_depth, *[C.byref(x) for x in v])
+        return [x.value for x in v]
+
+    def mode_lf(self, mode):
+        return self.lib.ref_mode_lf_lut(mode)
+
+    def tx_dims(self, tx):
+        w, h = C.c_int(), C.c_int()
+        self.lib.ref_tx_size_dims(tx, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+
+def planes_equal(a, b):
+    return all(np.array_equal(x, y) for x, y in zip(a, b))
+
+
+def first_diff(a, b):
+    for p, (x, y) in enumerate(zip(a, b)):
+        d = np.argwhere(x != y)
+        if len(d):
+            r, c = d[0]
+            return f"plane {p}: {len(d)} diffs, first at (y={r}, x={c}): {x[r, c]} vs {y[r, c]}"
+    return "equal"
