@@ -145,6 +145,9 @@ int  svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx **out);
 void svtf_ctx_destroy(svtf_ctx *ctx);
 const char *svtf_last_error(const svtf_ctx *ctx); /* ctx may be NULL: last global error */
 int  svtf_sync(svtf_ctx *ctx);
+/* Run this context's work on a caller-owned CUDA stream (a cudaStream_t); NULL restores the
+ * context's own stream.  The caller keeps the stream alive while the context uses it. */
+int svtf_ctx_set_stream(svtf_ctx *ctx, void *cuda_stream);
 /* Number of this library's kernel launches issued on the context so far. */
 uint64_t svtf_launch_count(const svtf_ctx *ctx);
 

@@ -63,7 +63,7 @@ EXPORTS = [
     "svtf_launch_count", "svtf_frame_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_set_mi",
     "svtf_download_frame", "svtf_rewind", "svtf_deblock_frame", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_host", "svtf_dev_planes",
-    "svtf_cuda_stream", "svtf_host_alloc", "svtf_host_free",
+    "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free",
 ]
 
 _lib = None
@@ -104,6 +104,7 @@ def load():
     lib.svtf_dev_planes.argtypes = [vp, C.c_int, C.POINTER(DevPlane)]
     lib.svtf_cuda_stream.argtypes = [vp]
     lib.svtf_cuda_stream.restype = vp
+    lib.svtf_ctx_set_stream.argtypes = [vp, vp]
     lib.svtf_host_alloc.argtypes = [C.c_size_t]
     lib.svtf_host_alloc.restype = vp
     lib.svtf_host_free.argtypes = [vp]

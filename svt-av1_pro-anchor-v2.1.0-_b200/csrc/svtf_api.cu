@@ -40,7 +40,8 @@ using namespace svtf;
 
 struct svtf_ctx {
     int          device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;     // stream in use
+    cudaStream_t own_stream = nullptr; // the context's own stream
     svtf_geom    max_geom{};
     svtf_geom    geom{};
     bool         have_geom = false, have_frame = false, have_mi = false, have_source = false, have_search = false;
@@ -128,7 +129,8 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
         return r;
     };
     if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
-    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    c->stream = c->own_stream;
     for (int i = 0; i < 3; i++)
         if ((e = alloc_surface(c->surf[i], *max_geom)) != cudaSuccess) return bail(e, "cudaMalloc(surface)");
     if ((e = alloc_surface(c->source, *max_geom)) != cudaSuccess) return bail(e, "cudaMalloc(source)");
@@ -159,8 +161,8 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     for (int p = 0; p < 3; p++) cudaFree(c->source.base[p]);
     cudaFree(c->d_mi), cudaFree(c->d_fb_idx), cudaFree(c->d_ccso_lut), cudaFree(c->d_ccso_flags);
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
-    if (c->stream)
-        cudaStreamDestroy(c->stream);
+    if (c->own_stream)
+        cudaStreamDestroy(c->own_stream);
     delete c;
 }
 
@@ -168,6 +170,14 @@ extern "C" int svtf_sync(svtf_ctx *c) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_sync: NULL context");
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return SVTF_OK;
+}
+
+extern "C" int svtf_ctx_set_stream(svtf_ctx *c, void *cuda_stream) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_ctx_set_stream: NULL context");
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
     return SVTF_OK;
 }
 

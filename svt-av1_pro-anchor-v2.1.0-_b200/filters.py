@@ -228,6 +228,10 @@ class FilterContext:
     def cuda_stream(self):
         return self._lib.svtf_cuda_stream(self._h)
 
+    def set_stream(self, cuda_stream):
+        """Run on a caller-owned cudaStream_t (int handle, e.g. torch.cuda.Stream().cuda_stream); None = own stream."""
+        self._chk(self._lib.svtf_ctx_set_stream(self._h, C.c_void_p(cuda_stream) if cuda_stream else None))
+
     def dev_planes(self, which=1):
         arr = (L.DevPlane * 3)()
         self._chk(self._lib.svtf_dev_planes(self._h, which, arr))

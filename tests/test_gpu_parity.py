@@ -1,0 +1,174 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle — and against the real reference
+library when its prebuilt .so travelled with the repo — on seeded synthetic pictures."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CASES = [  # (width, height, bit_depth, sample_bytes)
+    (328, 200, 8, 1),
+    (328, 200, 10, 2),
+    (256, 192, 8, 2),   # 8-bit content in the 16-bit pipeline
+    (200, 136, 12, 2),
+    (64, 64, 10, 2),
+    (8, 8, 8, 1),
+    (1920, 1080, 8, 1),
+    (1920, 1080, 10, 2),
+]
+
+
+def _lf_variants(S):
+    return [
+        S.lf_params((24, 24), 12, 12),
+        S.lf_params((40, 10), 0, 33, sharpness_level=3),
+        S.lf_params((63, 63), 63, 63, sharpness_level=7, mode_ref_delta_enabled=1, mode_deltas=(0, 3)),
+        S.lf_params((0, 0), 20, 20),  # luma level 0 breaks the plane loop
+        S.lf_params((18, 30), 9, 9, delta_lf_present=1, delta_lf_multi=1, curr_delta_lf=(4, -6, 10, -3)),
+    ]
+
+
+@pytest.mark.parametrize("w,h,bd,sb", CASES)
+def test_deblock_matches_oracle(H, orc, w, h, bd, sb):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    rec = H.synth_picture(g, 100 + w + bd)
+    soa = H.synth_mode_info(g, 200 + h, segments=True)
+    mi = H.pack_mi(soa)
+    variants = _lf_variants(S) if w < 1000 else _lf_variants(S)[:1]
+    with S.FilterContext(g) as ctx:
+        for i, lf in enumerate(variants):
+            if i == 2:  # exercise segmentation features too
+                en = np.zeros((8, 8), np.int16)
+                da = np.zeros((8, 8), np.int16)
+                en[:, 1:5] = 1
+                da[:, 1:5] = np.arange(-16, 16).reshape(8, 4)
+                lf = S.lf_params((50, 45), 30, 28, sharpness_level=1, mode_ref_delta_enabled=1, mode_deltas=(0, 3),
+                                 segmentation_enabled=1, seg_feature_enabled=en, seg_feature_data=da)
+            ctx.begin(g)
+            ctx.upload(rec)
+            ctx.set_mi(mi)
+            ctx.loop_filter_frame(lf)
+            got = ctx.download()
+            exp = orc.deblock(g, rec, mi, lf)
+            assert H.planes_equal(got, exp), f"variant {i}: " + H.first_diff(got, exp)
+
+
+@pytest.mark.parametrize("w,h,bd,sb", CASES)
+def test_cdef_matches_oracle(H, orc, w, h, bd, sb):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    rec = H.synth_picture(g, 300 + w + bd)
+    soa = H.synth_mode_info(g, 400 + h, p_skip=0.5)
+    mi = H.pack_mi(soa)
+    with S.FilterContext(g) as ctx:
+        for damping in (3, 4, 5, 6) if w < 1000 else (5,):
+            cdef, idx = H.synth_cdef(g, 500 + damping, damping=damping)
+            idx[::7] = -1
+            ctx.begin(g)
+            ctx.upload(rec)
+            ctx.set_mi(mi)
+            ctx.cdef_frame(cdef, idx)
+            got = ctx.download()
+            exp = orc.cdef_apply(g, rec, mi, cdef, idx)
+            assert H.planes_equal(got, exp), f"damping {damping}: " + H.first_diff(got, exp)
+
+
+@pytest.mark.parametrize("w,h,bd,sb", CASES)
+def test_ccso_matches_oracle(H, orc, w, h, bd, sb):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    rec = H.synth_picture(g, 600 + w + bd)
+    pre = H.synth_picture(g, 601 + w + bd)
+    soa = H.synth_mode_info(g, 700 + h)
+    mi = H.pack_mi(soa)
+    combos = [((0, 0, 0), (0, 1, 2), (0, 0, 0), (2, 2, 2), (0, 0, 0)), ((1, 2, 3), (3, 4, 5), (1, 0, 1), (0, 3, 1), (0, 0, 0)),
+              ((3, 1, 0), (5, 0, 2), (0, 1, 0), (4, 0, 7), (1, 0, 1))]
+    with S.FilterContext(g) as ctx:
+        for q, sup, clf, band, bo in combos if w < 1000 else combos[:1]:
+            ccso, flags = H.synth_ccso(g, 800 + sum(q), q, sup, clf, band, bo)
+            # (a) standalone: luma classifier = the picture itself (out of place on the GPU)
+            ctx.begin(g)
+            ctx.upload(rec)
+            ctx.set_mi(mi)
+            ctx.ccso_frame(ccso, flags)
+            got = ctx.download()
+            exp = orc.ccso_apply(g, rec, rec[0], ccso, flags)
+            assert H.planes_equal(got, exp), "standalone: " + H.first_diff(got, exp)
+            # (b) after CDEF: classifier = pre-CDEF luma
+            cdef, idx = H.synth_cdef(g, 900)
+            ctx.begin(g)
+            ctx.upload(pre)
+            ctx.set_mi(mi)
+            ctx.cdef_frame(cdef, idx)
+            ctx.ccso_frame(ccso, None)
+            got = ctx.download()
+            e1 = orc.cdef_apply(g, pre, mi, cdef, idx)
+            exp = orc.ccso_apply(g, e1, pre[0], ccso, None)
+            assert H.planes_equal(got, exp), "after cdef: " + H.first_diff(got, exp)
+
+
+@pytest.mark.parametrize("w,h,bd,sb", [(328, 200, 8, 1), (328, 200, 10, 2), (1920, 1080, 10, 2)])
+def test_chain_matches_oracle_and_reference(H, orc, w, h, bd, sb):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    rec = H.synth_picture(g, 1000 + w + bd)
+    soa = H.synth_mode_info(g, 1100 + h)
+    mi = H.pack_mi(soa)
+    lf = S.lf_params((24, 24), 12, 12)
+    cdef, idx = H.synth_cdef(g, 1200)
+    ccso, flags = H.synth_ccso(g, 1300)
+    with S.FilterContext(g) as ctx:
+        ctx.begin(g)
+        ctx.upload(rec)
+        ctx.set_mi(mi)
+        ctx.filter_chain(lf, cdef, idx, ccso, flags)
+        got = ctx.download()
+        # idempotence of the device-resident re-run (rewind does not copy)
+        ctx.rewind()
+        ctx.filter_chain(lf, cdef, idx, ccso, flags)
+        again = ctx.download()
+    assert H.planes_equal(got, again)
+    e1 = orc.deblock(g, rec, mi, lf)
+    e2 = orc.cdef_apply(g, e1, mi, cdef, idx)
+    e3 = orc.ccso_apply(g, e2, e1[0], ccso, flags)
+    assert H.planes_equal(got, e3), H.first_diff(got, e3)
+    if H.ref_available():
+        ref = H.Ref()
+        r1 = ref.deblock(g, rec, soa, lf)
+        r2 = ref.cdef_apply(g, r1, soa, cdef, idx)
+        r3 = ref.ccso_apply(g, r2, r1[0], ccso, flags)
+        assert H.planes_equal(got, r3), "vs reference: " + H.first_diff(got, r3)
+
+
+@pytest.mark.parametrize("w,h,bd,sb,sub", [(328, 200, 8, 1, 1), (328, 200, 10, 2, 1), (200, 136, 10, 2, 2), (200, 136, 8, 1, 4),
+                                           (200, 136, 12, 2, 1)])
+def test_cdef_search_matches_oracle(H, orc, w, h, bd, sb, sub):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    src = H.synth_picture(g, 1400 + w + bd, noise=0)
+    rec = H.synth_source(g, src, 1500, amp=10)
+    soa = H.synth_mode_info(g, 1600 + h, p_skip=0.6)
+    mi = H.pack_mi(soa)
+    first, second = H.cdef_level1_lists()
+    suv = list(second)
+    suv[5] = -1
+    suv[17] = -1
+    cfg = S.cdef_search_cfg(first, second, first, suv, subsampling_factor=sub, base_q_idx=120, lambda_=4000)
+    with S.FilterContext(g) as ctx:
+        ctx.begin(g)
+        ctx.upload(rec)
+        ctx.upload_source(src)
+        ctx.set_mi(mi)
+        mse, skip, dirs, var = ctx.cdef_seg_search(cfg)
+        params, idx = ctx.finish_cdef_search(cfg)
+    e_mse, e_skip, e_dirs, e_var = orc.cdef_search(g, rec, src, mi, cfg)
+    assert np.array_equal(skip, e_skip)
+    assert np.array_equal(dirs, e_dirs)
+    assert np.array_equal(var, e_var)
+    bad = np.argwhere(mse != e_mse)
+    assert len(bad) == 0, f"{len(bad)} mse entries differ, first {bad[0]}: {mse[tuple(bad[0])]} vs {e_mse[tuple(bad[0])]}"
+    e_params, e_idx = orc.cdef_pick(cfg, e_mse, e_skip)
+    assert params.cdef_bits == e_params.cdef_bits and params.cdef_damping == e_params.cdef_damping
+    assert list(params.cdef_y_strength) == list(e_params.cdef_y_strength)
+    assert list(params.cdef_uv_strength) == list(e_params.cdef_uv_strength)
+    assert np.array_equal(idx, e_idx)
