@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py — filtered Mpixel/s of the in-loop filter chain (deblock -> CDEF -> CCSO).
+
+Workload at every N: BASELINE.json configs[1], "decoder post-recon filter chain on 4K 10-bit 4:2:0
+synthetic stream": a batch of distinct 3840x2160 10-bit pictures per GPU (kernel-level generator of
+SURVEY §8d C2: quadtree mode info, filter_level 24/24/12/12, 8 CDEF strength pairs, CCSO on all
+three planes).  One step = one pass of the chain over the batch.
+
+  value     device-resident: pictures and side info already in HBM, chain kernels only, timed with
+            CUDA events on the launching stream; batch > L2 (126 MB) so every step streams from HBM.
+  e2e       the same metric through the C ABI with HOST buffers: per picture upload (pinned) +
+            mi upload + chain + download, pipelined over several contexts/streams; wall clock
+            bracketed by device synchronisation.
+  roofline  dominant kernel of the chain: algorithmic bytes (deblock 3b+0.5, CDEF 3b,
+            CCSO 4b per luma pixel, b = bytes/sample) / its mean launch time (CUDA events inside the
+            timed region) against MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline  the reference's own C (oracle/_ref) — or the oracle port if that library is absent —
+            on the host cores over a bounded sample of the same workload.
+
+`--impl reference` times the reference CPU implementation alone (rank 0 only under torchrun).
+Multi-GPU: pictures shard by stream across ranks with no data-path collective ("weak" scaling).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+W4K, H4K, BD = 3840, 2160, 10
+METRIC = "filtered Mpixel/s (deblock+CDEF+CCSO)"
+UNIT = "Mpixel/s"
+
+
+def workload(H, geom, seed):
+    S = H.S
+    rec = H.synth_picture(geom, seed)
+    soa = H.synth_mode_info(geom, seed + 1, p_split=0.5, p_skip=0.3, p_inter=0.7)
+    mi = H.pack_mi(soa)
+    lf = S.lf_params((24, 24), 12, 12)
+    cdef, idx = H.synth_cdef(geom, seed + 2, n_strengths=8, damping=5)
+    ccso, flags = H.synth_ccso(geom, seed + 3, quant_idx=(0, 0, 0), support=(0, 1, 2), edge_clf=(0, 0, 0), band_log2=(2, 2, 2), p_on=0.8)
+    return dict(rec=rec, soa=soa, mi=mi, lf=lf, cdef=cdef, idx=idx, ccso=ccso, flags=flags)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs
+# ------------------------------------------------------------------------------------------------
+def cpu_chain_runner(H):
+    """Returns (kind, fn(geom, wl) -> None) running deblock->CDEF->CCSO on the CPU."""
+    if H.ref_available():
+        ref = H.Ref()
+
+        def run(geom, wl):
+            a = ref.deblock(geom, wl["rec"], wl["soa"], wl["lf"])
+            b = ref.cdef_apply(geom, a, wl["soa"], wl["cdef"], wl["idx"])
+            ref.ccso_apply(geom, b, a[0], wl["ccso"], wl["flags"])
+
+        return "reference", run
+    orc = H.Oracle()
+
+    def run(geom, wl):
+        a = orc.deblock(geom, wl["rec"], wl["mi"], wl["lf"])
+        b = orc.cdef_apply(geom, a, wl["mi"], wl["cdef"], wl["idx"])
+        orc.ccso_apply(geom, b, a[0], wl["ccso"], wl["flags"])
+
+    return "port", run
+
+
+def cpu_measure(H, band_h, threads, steps, warmup):
+    """Each step: `threads` host threads each filter one 3840 x band_h 10-bit band (ctypes releases the GIL)."""
+    S = H.S
+    geom = S.make_geom(W4K, band_h, BD)
+    wls = [workload(H, geom, 0xC2 + 16 * t) for t in range(threads)]
+    kind, run = cpu_chain_runner(H)
+
+    def step():
+        th = [threading.Thread(target=run, args=(geom, wls[t])) for t in range(threads)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    mpix = threads * W4K * band_h * steps / 1e6
+    return kind, mpix / dt, dt / steps, f"{threads} threads x one 3840x{band_h} 10-bit band per step, {steps} steps"
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import harness as H
+
+    threads = os.cpu_count() or 1
+    band_h = 256
+    # one untimed probe step sizes the band so K+W steps stay within ~2.5 minutes
+    _, _, probe, _ = cpu_measure(H, band_h, threads, 1, 0)
+    budget = 150.0 / max(1, args.steps + args.warmup)
+    while band_h < 2160 and probe * 2 < budget:
+        band_h = min(2160, band_h * 2)
+        probe *= 2
+    while band_h > 64 and probe > budget:
+        band_h //= 2
+        probe /= 2
+    band_h = 2160 if band_h > 2160 else band_h // 8 * 8
+    kind, val, per_step, sample = cpu_measure(H, band_h, threads, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(per_step * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+        "config": {"workload": "decoder post-recon filter chain, 4K (3840x2160) 10-bit 4:2:0, deblock+CDEF+CCSO", "sample": sample},
+        "cpu_baseline": {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,utilization.gpu,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        busy = []
+        for ln in self.f.read().splitlines():
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                c, m, u = float(parts[0]), float(parts[1]), float(parts[2])
+            except ValueError:
+                continue
+            sm.append(c)
+            mx.append(m)
+            if u > 0:
+                busy.append(c)
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        self.f.close()
+        os.unlink(self.f.name)
+        src = busy or sm
+        if src:
+            out["sm_mhz"] = statistics.median(src)
+            out["sm_max_mhz"] = max(mx)
+        out["reasons"] = sorted(reasons)
+        out["samples"] = len(sm)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=12, help="distinct 4K pictures resident per GPU (12 x 24.9 MB x 3 surfaces > L2)")
+    ap.add_argument("--e2e-inflight", type=int, default=4)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import numpy as np
+    import torch
+    import harness as H
+
+    S = H.S
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+
+    geom = S.make_geom(W4K, H4K, BD)
+    npx = W4K * H4K
+    B = args.batch
+    # a few distinct synthetic pictures, cycled over the batch with different seeds per rank
+    nsrc = min(B, 3)
+    wls = [workload(H, geom, 0xB200C2 + 97 * rank + 7 * i) for i in range(nsrc)]
+
+    stream = torch.cuda.Stream(device=dev)
+    ctxs = []
+    for i in range(B):
+        c = S.FilterContext(geom, device=local)
+        c.begin(geom)
+        wl = wls[i % nsrc]
+        c.upload(wl["rec"])
+        c.set_mi(wl["mi"])
+        c.sync()
+        c.set_stream(stream.cuda_stream)
+        ctxs.append(c)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step(stage_events=None):
+        for i, c in enumerate(ctxs):
+            wl = wls[i % nsrc]
+            c.rewind()
+            if stage_events is not None and i == 0:
+                e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+                e[0].record(stream)
+                c.loop_filter_frame(wl["lf"])
+                e[1].record(stream)
+                c.cdef_frame(wl["cdef"], wl["idx"])
+                e[2].record(stream)
+                c.ccso_frame(wl["ccso"], wl["flags"])
+                e[3].record(stream)
+                stage_events.append(e)
+            else:
+                c.filter_chain(wl["lf"], wl["cdef"], wl["idx"], wl["ccso"], wl["flags"])
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    l0 = sum(c.launch_count for c in ctxs)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage_events = []
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step(stage_events)
+    ev1.record(stream)
+    barrier()
+    launches = sum(c.launch_count for c in ctxs) - l0
+    ms = ev0.elapsed_time(ev1)
+    tt = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_max = float(tt.item())
+    value = world * B * npx * args.steps / (ms_max * 1e-3) / 1e6
+
+    stage_ms = [statistics.mean(e[k].elapsed_time(e[k + 1]) for e in stage_events) for k in range(3)]
+    b = geom.sample_bytes
+    alg_bytes = [(3 * b + 0.5) * npx, 3 * b * npx, 4 * b * npx]
+    names = ["deblock_kernel", "cdef_kernel", "ccso_kernel"]
+    dom = max(range(3), key=lambda k: stage_ms[k])
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    achieved = alg_bytes[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(names[dom])
+    roofline = {"bound": "hbm", "kernel": names[dom], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                "stages": {names[k]: {"ms": round(stage_ms[k], 4), "alg_GBps": round(alg_bytes[k] / (stage_ms[k] * 1e-3) / 1e9, 1)} for k in range(3)},
+                "chain_frac": round(sum(alg_bytes) / (sum(stage_ms) * 1e-3) / 1e9 / peak, 4)}
+
+    # ---- e2e: host buffers through the C ABI, several pictures in flight ----
+    for c in ctxs:
+        c.set_stream(None)
+    nin = min(args.e2e_inflight, B)
+    pins_in = [S.PinnedPicture(geom) for _ in range(nin)]
+    pins_out = [S.PinnedPicture(geom) for _ in range(nin)]
+    for k in range(nin):
+        for p in range(3):
+            pins_in[k].planes[p][...] = wls[k % nsrc]["rec"][p]
+    L = S._lib.load()
+    import ctypes as C
+
+    def e2e_submit(k):
+        c, wl = ctxs[k], wls[k % nsrc]
+        c.begin(geom)
+        c.upload(pins_in[k].planes)
+        c.set_mi(wl["mi"])
+        c.filter_chain(wl["lf"], wl["cdef"], wl["idx"], wl["ccso"], wl["flags"])
+        # asynchronous download into pinned memory; completion is awaited before the slot is reused
+        args_ = c._planes_args(pins_out[k].planes)
+        c._chk(L.svtf_download_frame_async(c._h, *args_))
+
+    def e2e_step():
+        for j in range(B):
+            k = j % nin
+            if j >= nin:
+                ctxs[k].sync()
+            e2e_submit(k)
+        for k in range(nin):
+            ctxs[k].sync()
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    tt = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    e2e_val = world * B * npx * args.steps / float(tt.item()) / 1e6
+    frame_bytes = int(npx * 1.5 * b)
+    mi_bytes = int(wls[0]["mi"].nbytes)
+    # check the last e2e output against the device-resident result (same picture, same parameters)
+    ctxs[0].begin(geom)
+    ctxs[0].upload(wls[0]["rec"])
+    ctxs[0].set_mi(wls[0]["mi"])
+    ctxs[0].filter_chain(wls[0]["lf"], wls[0]["cdef"], wls[0]["idx"], wls[0]["ccso"], wls[0]["flags"])
+    chk = ctxs[0].download()
+    e2e_ok = all(np.array_equal(chk[p], pins_out[0].planes[p]) for p in range(3))
+    clocks = sampler.stop() if sampler else None
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        kind, val, per_step, sample = cpu_measure(H, 272, threads, 3, 1)
+        cpu = {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": kind, "sample": sample}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_max / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u16", "data": "synthetic",
+            "config": {"workload": "decoder post-recon filter chain, 4K (3840x2160) 10-bit 4:2:0, deblock+CDEF+CCSO",
+                       "pictures_per_gpu_per_step": B, "l2": f"inputs larger than L2: {B} pictures x 3 surfaces x {frame_bytes / 1e6:.1f} MB resident",
+                       "sharding": f"{world} rank(s), pictures sharded by stream, no collective"},
+            "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
+                    "inflight": nin, "matches_device_path": bool(e2e_ok)},
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+        }
+        print(json.dumps(line))
+    for p in pins_in + pins_out:
+        p.close()
+    for c in ctxs:
+        c.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

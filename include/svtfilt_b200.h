@@ -102,6 +102,12 @@ typedef struct svtf_lf_params {
     int32_t curr_delta_lf[4];
 } svtf_lf_params;
 
+/* Host-side per-frame tables the deblock kernel consumes: lvl[plane][segment][dir][ref][mode_lf]
+ * (3*8*2*8*2 = 768 bytes; svt_av1_loop_filter_frame_init, Common/Codec/EbDeblockingCommon.c:76, or
+ * svt_aom_get_filter_level_delta_lf :37 when delta_lf_present) and the per-level thresholds
+ * (svt_aom_update_sharpness :554; hev = level >> 4, Encoder/Codec/EbDeblockingFilter.c:47). */
+int svtf_lf_build_tables(const svtf_lf_params *lf, uint8_t lvl[768], uint8_t lim[64], uint8_t mblim[64], uint8_t hev[64]);
+
 /* ---- CDEF ---------------------------------------------------------------------------------
  * CdefParams (Common/Codec/EbAv1Structs.h:359-369): strength byte v -> pri=v/4, sec=v%4 (3->4). */
 typedef struct svtf_cdef_params {
@@ -171,6 +177,9 @@ int svtf_set_mi(svtf_ctx *ctx, const svtf_mi_t *mi, int32_t mi_stride);
 /* Device -> host copy of the current end of the filter chain; synchronises. */
 int svtf_download_frame(svtf_ctx *ctx, void *y, int32_t stride_y, void *cb, int32_t stride_cb, void *cr,
                         int32_t stride_cr);
+/* Same copy, stream-ordered and NOT synchronised: the data is valid after svtf_sync(). */
+int svtf_download_frame_async(svtf_ctx *ctx, void *y, int32_t stride_y, void *cb, int32_t stride_cb, void *cr,
+                              int32_t stride_cr);
 /* Rewind the chain to the uploaded (unfiltered) picture without copying — lets a benchmark
  * re-run the chain on device-resident input. */
 int svtf_rewind(svtf_ctx *ctx);

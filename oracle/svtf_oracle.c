@@ -862,3 +862,13 @@ ORC_API int orc_ccso_apply_frame(const svtf_geom *g, void *y, int sy, void *cb, 
     }
     return 0;
 }
+
+/* table probe for tests: the oracle's own level/threshold tables */
+ORC_API void orc_lf_tables(const svtf_lf_params *lf, uint8_t *lvl768, uint8_t *lim, uint8_t *mblim, uint8_t *hev) {
+    lf_tables t;
+    orc_lf_build_tables(lf, &t);
+    memcpy(lvl768, t.lvl, 768);
+    memcpy(lim, t.lim, 64);
+    memcpy(mblim, t.mblim, 64);
+    memcpy(hev, t.hev, 64);
+}

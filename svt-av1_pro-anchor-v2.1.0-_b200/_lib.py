@@ -59,9 +59,9 @@ class DevPlane(C.Structure):
 
 # every symbol include/svtfilt_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
-    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
+    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
     "svtf_launch_count", "svtf_frame_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_set_mi",
-    "svtf_download_frame", "svtf_rewind", "svtf_deblock_frame", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
+    "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_host", "svtf_dev_planes",
     "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free",
 ]
@@ -81,6 +81,7 @@ def load():
     vp, i32, u8p, i8p = C.c_void_p, C.c_int32, C.POINTER(C.c_uint8), C.POINTER(C.c_int8)
     lib.svtf_pack_mi_enc.argtypes = [C.c_size_t, vp, vp, vp, vp, vp, vp, vp]
     lib.svtf_pack_mi_dec.argtypes = [C.c_size_t, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.svtf_lf_build_tables.argtypes = [C.POINTER(LfParams), vp, vp, vp, vp]
     lib.svtf_ctx_create.argtypes = [C.c_int, C.POINTER(Geom), C.POINTER(vp)]
     lib.svtf_ctx_destroy.argtypes = [vp]
     lib.svtf_ctx_destroy.restype = None
@@ -90,7 +91,7 @@ def load():
     lib.svtf_launch_count.argtypes = [vp]
     lib.svtf_launch_count.restype = C.c_uint64
     lib.svtf_frame_begin.argtypes = [vp, C.POINTER(Geom)]
-    for f in (lib.svtf_upload_frame, lib.svtf_upload_source, lib.svtf_download_frame):
+    for f in (lib.svtf_upload_frame, lib.svtf_upload_source, lib.svtf_download_frame, lib.svtf_download_frame_async):
         f.argtypes = [vp, vp, i32, vp, i32, vp, i32]
     lib.svtf_set_mi.argtypes = [vp, vp, i32]
     lib.svtf_rewind.argtypes = [vp]

@@ -266,14 +266,18 @@ extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) 
     return SVTF_OK;
 }
 
-extern "C" int svtf_download_frame(svtf_ctx *c, void *y, int32_t sy, void *cb, int32_t scb, void *cr, int32_t scr) {
+extern "C" int svtf_download_frame_async(svtf_ctx *c, void *y, int32_t sy, void *cb, int32_t scb, void *cr, int32_t scr) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_download_frame: NULL context");
     if (!c->have_frame)
         return c->fail(SVTF_E_STATE, "svtf_download_frame: no picture uploaded");
     const void   *dst[3] = {y, cb, cr};
     const int32_t st[3]  = {sy, scb, scr};
-    int r = copy_planes(c, c->surf[c->cur], dst, st, false);
+    return copy_planes(c, c->surf[c->cur], dst, st, false);
+}
+
+extern "C" int svtf_download_frame(svtf_ctx *c, void *y, int32_t sy, void *cb, int32_t scb, void *cr, int32_t scr) {
+    int r = svtf_download_frame_async(c, y, sy, cb, scb, cr, scr);
     if (r != SVTF_OK)
         return r;
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));

@@ -159,6 +159,19 @@ void build_lf_tables(const svtf_lf_params &lf, LfTables &t) {
 
 } // namespace svtf
 
+extern "C" int svtf_lf_build_tables(const svtf_lf_params *lf, uint8_t lvl[768], uint8_t lim[64], uint8_t mblim[64],
+                                    uint8_t hev[64]) {
+    if (!lf || !lvl || !lim || !mblim || !hev)
+        return svtf::set_global_error(SVTF_E_ARG, "svtf_lf_build_tables: NULL argument");
+    svtf::LfTables t;
+    svtf::build_lf_tables(*lf, t);
+    std::memcpy(lvl, t.lvl, 768);
+    std::memcpy(lim, t.lim, 64);
+    std::memcpy(mblim, t.mblim, 64);
+    std::memcpy(hev, t.hev, 64);
+    return SVTF_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Frame-level strength pick: finish_cdef_search (Encoder/Codec/EbEncCdef.c:728-925),
 // joint_strength_search_dual (:697-727), svt_search_one_dual_c (:627-684).
