@@ -217,6 +217,14 @@ static int copy_planes(svtf_ctx *c, Surface &s, const void *const src[3], const 
         if (!src[p] || stride[p] < w)
             return c->fail(SVTF_E_ARG, "plane pointer NULL or stride smaller than the coded width");
         const size_t sb = g.sample_bytes;
+        if (stride[p] == s.pitch[p]) { // same pitch on both sides: one linear DMA instead of a 2-D copy
+            const size_t bytes = ((size_t)(h - 1) * s.pitch[p] + w) * sb;
+            if (to_device)
+                CUDA_TRY(c, cudaMemcpyAsync(s.base[p], src[p], bytes, cudaMemcpyHostToDevice, c->stream));
+            else
+                CUDA_TRY(c, cudaMemcpyAsync(const_cast<void *>(src[p]), s.base[p], bytes, cudaMemcpyDeviceToHost, c->stream));
+            continue;
+        }
         if (to_device)
             CUDA_TRY(c, cudaMemcpy2DAsync(s.base[p], s.pitch[p] * sb, src[p], stride[p] * sb, w * sb, h, cudaMemcpyHostToDevice, c->stream));
         else
