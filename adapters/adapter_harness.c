@@ -1,0 +1,184 @@
+/*
+ * adapter_harness.c — TEST INFRASTRUCTURE: builds the same PictureControlSet graph oracle/ref_shim.c builds
+ * (oracle/ref_harness.h) and calls the Tier-2 adapters (adapters/svtf_enc_adapters.c) through the reference's own
+ * signatures, so tests can compare `svt_av1_loop_filter_frame(frame, pcs, 0, 3)` & co. of this repo with the
+ * real reference functions on identical structures.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "EbPictureControlSet.h"
+#include "EbSequenceControlSet.h"
+#include "EbEncCdef.h"
+#include "EbCdef.h"
+#include "EbDeblockingFilter.h"
+#include "EbDeblockingCommon.h"
+#include "EbCcso.h"
+#include "EbModeDecisionProcess.h"
+
+#include "../include/svtfilt_b200.h"
+#include "../include/svtfilt_b200_adapters.h"
+#include "../oracle/ref_harness.h"
+
+#define API __attribute__((visibility("default")))
+
+void svt_aom_get_recon_pic(PictureControlSet *pcs, EbPictureBufferDesc **recon_ptr, Bool is_highbd) {
+    *recon_ptr = is_highbd ? pcs->ppcs->enc_dec_ptr->recon_pic_16bit : pcs->ppcs->enc_dec_ptr->recon_pic;
+}
+static uint32_t g_lambda = 0;
+static void     h_lambda(PictureControlSet *pcs, uint32_t *fast_lambda, uint32_t *full_lambda, uint8_t bit_depth,
+                         uint16_t qp_index, Bool multiply_lambda) {
+    (void)pcs, (void)bit_depth, (void)qp_index, (void)multiply_lambda;
+    *fast_lambda = *full_lambda = g_lambda;
+}
+const EbAv1LambdaAssignFunc svt_aom_av1_lambda_assignment_function_table[4] = {h_lambda, h_lambda, h_lambda, h_lambda};
+
+static void fill_lf(harness *h, const svtf_lf_params *lf) {
+    FrameHeader       *fh = &h->ppcs->frm_hdr;
+    struct LoopFilter *l  = &fh->loop_filter_params;
+    l->filter_level[0] = lf->filter_level[0], l->filter_level[1] = lf->filter_level[1];
+    l->filter_level_u = lf->filter_level_u, l->filter_level_v = lf->filter_level_v;
+    l->sharpness_level        = lf->sharpness_level;
+    l->mode_ref_delta_enabled = (uint8_t)lf->mode_ref_delta_enabled;
+    memcpy(l->ref_deltas, lf->ref_deltas, sizeof(l->ref_deltas));
+    memcpy(l->mode_deltas, lf->mode_deltas, sizeof(l->mode_deltas));
+    fh->segmentation_params.segmentation_enabled = (uint8_t)lf->segmentation_enabled;
+    for (int s = 0; s < 8; s++)
+        for (int f = 0; f < 8; f++) {
+            fh->segmentation_params.feature_enabled[s][f] = lf->seg_feature_enabled[s][f];
+            fh->segmentation_params.feature_data[s][f]    = lf->seg_feature_data[s][f];
+        }
+    fh->delta_lf_params.delta_lf_present = (uint8_t)lf->delta_lf_present;
+    fh->delta_lf_params.delta_lf_multi   = (uint8_t)lf->delta_lf_multi;
+    for (int i = 0; i < 4; i++) h->ppcs->curr_delta_lf[i] = lf->curr_delta_lf[i];
+}
+
+API int adapt_deblock_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const ref_mi_soa *soa,
+                            const svtf_lf_params *lf, int plane_start, int plane_end) {
+    harness h;
+    if (harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    fill_lf(&h, lf);
+    svt_av1_loop_filter_frame(h.recon, h.pcs, plane_start, plane_end);
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}
+
+API int adapt_cdef_apply_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const ref_mi_soa *soa,
+                               const svtf_cdef_params *cp, const int8_t *fb_strength_idx) {
+    harness h;
+    if (harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    FrameHeader *fh              = &h.ppcs->frm_hdr;
+    fh->cdef_params.cdef_damping = (uint8_t)cp->cdef_damping;
+    fh->cdef_params.cdef_bits    = (uint8_t)cp->cdef_bits;
+    for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++) {
+        fh->cdef_params.cdef_y_strength[i]  = cp->cdef_y_strength[i];
+        fh->cdef_params.cdef_uv_strength[i] = cp->cdef_uv_strength[i];
+    }
+    const int nvfb = (g->mi_rows + 15) / 16, nhfb = (g->mi_cols + 15) / 16;
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++) {
+            int8_t idx = fb_strength_idx[fbr * nhfb + fbc];
+            h.mi[16 * fbr * soa->mi_stride + 16 * fbc].mbmi.cdef_strength = idx < 0 ? 0 : idx;
+        }
+    svt_av1_cdef_frame(h.scs, h.pcs);
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}
+
+/* search + pick through svtf_cdef_search_picture() and finish_cdef_search() */
+API int adapt_cdef_search_pick(const svtf_geom *g, void *ry, int rsy, void *rcb, int rscb, void *rcr, int rscr, void *oy, int osy,
+                               void *ocb, int oscb, void *ocr, int oscr, const ref_mi_soa *soa, const svtf_cdef_search_cfg *cfg,
+                               uint64_t *mse, uint8_t *skip, uint8_t *dir, int32_t *var, svtf_cdef_params *out, int8_t *fb_idx) {
+    harness h;
+    if (harness_init(&h, g, soa, ry, rsy, rcb, rscb, rcr, rscr))
+        return -1;
+    EbPictureBufferDesc *s = h.source;
+    *s                     = *h.recon;
+    s->buffer_y = oy, s->buffer_cb = ocb, s->buffer_cr = ocr;
+    s->stride_y = (uint16_t)osy, s->stride_cb = (uint16_t)oscb, s->stride_cr = (uint16_t)oscr;
+    h.pcs->input_frame16bit = s;
+    CdefControls *c           = &h.ppcs->cdef_ctrls;
+    c->first_pass_fs_num          = (uint8_t)cfg->first_pass_fs_num;
+    c->default_second_pass_fs_num = (uint8_t)cfg->default_second_pass_fs_num;
+    memcpy(c->default_first_pass_fs, cfg->default_first_pass_fs, 64);
+    memcpy(c->default_second_pass_fs, cfg->default_second_pass_fs, 64);
+    memcpy(c->default_first_pass_fs_uv, cfg->default_first_pass_fs_uv, 64);
+    memcpy(c->default_second_pass_fs_uv, cfg->default_second_pass_fs_uv, 64);
+    c->subsampling_factor                          = (uint8_t)cfg->subsampling_factor;
+    c->zero_fs_cost_bias                           = (uint16_t)cfg->zero_fs_cost_bias;
+    h.ppcs->frm_hdr.quantization_params.base_q_idx = (uint8_t)cfg->base_q_idx;
+    h.source->bit_depth                            = (EbBitDepth)g->bit_depth;
+    g_lambda                                       = cfg->lambda;
+    for (int i = 0; i < g->mi_rows * soa->mi_stride; i++) h.mi[i].mbmi.cdef_strength = -1;
+    svtf_cdef_search_picture(h.pcs, h.scs);
+    const int nvfb = (g->mi_rows + 15) / 16, nhfb = (g->mi_cols + 15) / 16, nfb = nvfb * nhfb;
+    memcpy(mse, h.pcs->mse_seg[0], sizeof(uint64_t) * 64 * nfb);
+    memcpy(mse + (size_t)64 * nfb, h.pcs->mse_seg[1], sizeof(uint64_t) * 64 * nfb);
+    memcpy(skip, h.pcs->skip_cdef_seg, nfb);
+    for (int fb = 0; fb < nfb; fb++)
+        for (int b = 0; b < 64; b++) {
+            dir[fb * 64 + b] = h.pcs->cdef_dir_data[fb].dir[b >> 3][b & 7];
+            var[fb * 64 + b] = h.pcs->cdef_dir_data[fb].var[b >> 3][b & 7];
+        }
+    finish_cdef_search(h.pcs);
+    memset(out, 0, sizeof(*out));
+    out->cdef_damping = h.ppcs->frm_hdr.cdef_params.cdef_damping;
+    out->cdef_bits    = h.ppcs->frm_hdr.cdef_params.cdef_bits;
+    for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++) {
+        out->cdef_y_strength[i]  = h.ppcs->frm_hdr.cdef_params.cdef_y_strength[i];
+        out->cdef_uv_strength[i] = h.ppcs->frm_hdr.cdef_params.cdef_uv_strength[i];
+    }
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++)
+            fb_idx[fbr * nhfb + fbc] = h.mi[16 * fbr * soa->mi_stride + 16 * fbc].mbmi.cdef_strength;
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}
+
+/* ccso_frame(frame, pcs, pd, ext_rec_y) with ext_rec_y built like Encoder/Codec/EbCdefProcess.c:480-502 */
+API int adapt_ccso_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const void *pre_y, int pre_sy,
+                         const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
+    harness    h;
+    ref_mi_soa soa = {0};
+    soa.mi_stride  = g->mi_cols;
+    if (harness_init(&h, g, &soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    CcsoInfo *ci = &h.ppcs->frm_hdr.ccso_info;
+    for (int p = 0; p < 3; p++) {
+        ci->ccso_enable[p] = cc->ccso_enable[p], ci->ccso_bo_only[p] = cc->ccso_bo_only[p], ci->quant_idx[p] = cc->quant_idx[p];
+        ci->ext_filter_support[p] = cc->ext_filter_support[p], ci->edge_clf[p] = cc->edge_clf[p];
+        ci->max_band_log2[p] = cc->max_band_log2[p];
+        memcpy(ci->filter_offset[p], cc->filter_offset[p], SVTF_CCSO_LUT_SIZE);
+        const int pw = g->width >> (p ? 1 : 0), ph = g->height >> (p ? 1 : 0), bl = p ? 7 : 8;
+        const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
+        for (int by = 0; by < nby; by++)
+            for (int bx = 0; bx < nbx; bx++) {
+                const int   f = (blk_flags && blk_flags[p]) ? blk_flags[p][by * nbx + bx] : 1;
+                MbModeInfo *m = &h.mi[64 * by * soa.mi_stride + 64 * bx].mbmi;
+                if (p == 0) m->ccso_blk_y = f;
+                if (p == 1) m->ccso_blk_u = f;
+                if (p == 2) m->ccso_blk_v = f;
+            }
+    }
+    const int is16 = g->sample_bytes == 2;
+    const int W = g->width, H = g->height, es = W + 10;
+    uint16_t *ext = calloc((size_t)es * (H + 10), sizeof(uint16_t));
+    for (int r = 0; r < H + 10; r++)
+        for (int c = 0; c < W + 10; c++) {
+            const int rr = r - 5 < 0 ? 0 : (r - 5 >= H ? H - 1 : r - 5), ccn = c - 5 < 0 ? 0 : (c - 5 >= W ? W - 1 : c - 5);
+            ext[r * es + c] = is16 ? ((const uint16_t *)pre_y)[rr * pre_sy + ccn] : ((const uint8_t *)pre_y)[rr * pre_sy + ccn];
+        }
+    struct MacroblockdPlane pd[3];
+    memset(pd, 0, sizeof(pd));
+    ccso_frame(h.recon, h.pcs, pd, ext);
+    free(ext);
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}

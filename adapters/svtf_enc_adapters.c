@@ -1,0 +1,370 @@
+/*
+ * svtf_enc_adapters.c — Tier-2 of the drop-in boundary: the reference's OWN frame-level entry points
+ * (same names, same signatures) implemented as thin marshalling over the Tier-1 C ABI
+ * (include/svtfilt_b200.h).  Compiled against the reference's headers; linked INSTEAD of the bodies in
+ *   Encoder/Codec/EbDeblockingFilter.c:624  svt_av1_loop_filter_frame
+ *   Encoder/Codec/EbEncCdef.c:284           svt_av1_cdef_frame
+ *   Encoder/Codec/EbEncCdef.c:728           finish_cdef_search
+ *   Encoder/Codec/EbCdefProcess.c:114       cdef_seg_search      (static there -> svtf_cdef_search_picture here)
+ *   Common/Codec/EbCcso.c:626               ccso_frame
+ * (see INTEGRATION.md for the three-line changes at the call sites).
+ *
+ * What an adapter does: (1) flatten pcs->mi_grid_base into the packed 4-byte mi words, (2) hand the recon
+ * picture's plane pointers/strides to svtf_upload_frame, (3) launch, (4) svtf_download_frame back into the
+ * same picture buffers (the reference filters in place).  Errors: the reference functions return void, so a
+ * failing Tier-1 call logs through SVT_ERROR-style stderr and aborts — there is no CPU fallback.
+ *
+ * One GPU context per PictureControlSet, created on first use and cached (a picture's DLF, CDEF search, CDEF
+ * apply and CCSO run on the same context, so the picture stays resident between stages:
+ * svtf_adapter_set_resident(1) skips the intermediate download/upload pairs).
+ */
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "EbPictureControlSet.h"
+#include "EbSequenceControlSet.h"
+#include "EbEncCdef.h"
+#include "EbCdef.h"
+#include "EbDeblockingFilter.h"
+#include "EbDeblockingCommon.h"
+#include "EbCcso.h"
+
+#include "../include/svtfilt_b200.h"
+#include "../include/svtfilt_b200_adapters.h"
+
+void svt_aom_get_recon_pic(PictureControlSet *pcs, EbPictureBufferDesc **recon_ptr, Bool is_highbd);
+
+#define SVTF_MAX_CACHED 64
+typedef struct {
+    const PictureControlSet *pcs;
+    svtf_ctx                *ctx;
+    svtf_geom                geom;
+    int                      resident; /* picture of this pcs currently on the device */
+} CtxSlot;
+static CtxSlot         g_slots[SVTF_MAX_CACHED];
+static pthread_mutex_t g_lock     = PTHREAD_MUTEX_INITIALIZER;
+static int             g_device   = 0;
+static int             g_resident = 0;
+
+void svtf_adapter_set_device(int device) { g_device = device; }
+void svtf_adapter_set_resident(int on) { g_resident = on; }
+
+static void die(const char *where, svtf_ctx *ctx) {
+    fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: %s failed: %s (no CPU fallback on this path)\n", where,
+            svtf_last_error(ctx));
+    abort();
+}
+#define CHECK(call, ctx)       \
+    do {                       \
+        if ((call) != SVTF_OK) \
+            die(#call, ctx);   \
+    } while (0)
+
+static svtf_geom geom_of(const PictureControlSet *pcs) {
+    const SequenceControlSet *scs = pcs->scs;
+    const Av1Common          *cm  = pcs->ppcs->av1_cm;
+    svtf_geom                 g;
+    /* unpadded size: the width/height svt_av1_setup_dst_planes gives the deblock (EbDeblockingFilter.c:99-101) */
+    g.width        = scs->max_input_luma_width - scs->max_input_pad_right;
+    g.height       = scs->max_input_luma_height - scs->max_input_pad_bottom;
+    g.mi_cols      = cm->mi_cols;
+    g.mi_rows      = cm->mi_rows;
+    g.bit_depth    = scs->static_config.encoder_bit_depth;
+    g.sample_bytes = scs->is_16bit_pipeline ? 2 : 1;
+    return g;
+}
+
+static CtxSlot *slot_for(const PictureControlSet *pcs) {
+    pthread_mutex_lock(&g_lock);
+    CtxSlot *free_slot = NULL, *s = NULL;
+    for (int i = 0; i < SVTF_MAX_CACHED; i++) {
+        if (g_slots[i].pcs == pcs) {
+            s = &g_slots[i];
+            break;
+        }
+        if (!g_slots[i].pcs && !free_slot)
+            free_slot = &g_slots[i];
+    }
+    if (!s) {
+        if (!free_slot) {
+            fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: more than %d pictures in flight\n", SVTF_MAX_CACHED);
+            abort();
+        }
+        s           = free_slot;
+        s->pcs      = pcs;
+        s->geom     = geom_of(pcs);
+        s->resident = 0;
+        if (svtf_ctx_create(g_device, &s->geom, &s->ctx) != SVTF_OK)
+            die("svtf_ctx_create", NULL);
+    }
+    pthread_mutex_unlock(&g_lock);
+    return s;
+}
+
+/* Release the cached context of a picture (call where the reference recycles the pcs). */
+void svtf_adapter_release(const PictureControlSet *pcs) {
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < SVTF_MAX_CACHED; i++)
+        if (g_slots[i].pcs == pcs) {
+            svtf_ctx_destroy(g_slots[i].ctx);
+            memset(&g_slots[i], 0, sizeof(g_slots[i]));
+        }
+    pthread_mutex_unlock(&g_lock);
+}
+
+/* mi_grid_base -> packed words (the fields set_lpf_parameters and svt_sb_compute_cdef_list read:
+ * EbDeblockingFilter.c:187-260, EbEncCdef.c:267-270). */
+static void send_mi(CtxSlot *s, const PictureControlSet *pcs) {
+    const int  rows = s->geom.mi_rows, cols = s->geom.mi_cols;
+    const size_t n  = (size_t)rows * cols;
+    uint8_t   *soa  = (uint8_t *)malloc(6 * n);
+    svtf_mi_t *mi   = (svtf_mi_t *)malloc(sizeof(svtf_mi_t) * n);
+    if (!soa || !mi)
+        die("malloc(mi)", s->ctx);
+    uint8_t *bsize = soa, *txd = soa + n, *skip = soa + 2 * n, *ref0 = soa + 3 * n, *mode = soa + 4 * n, *seg = soa + 5 * n;
+    for (int r = 0; r < rows; r++)
+        for (int c = 0; c < cols; c++) {
+            const BlockModeInfoEnc *b = &pcs->mi_grid_base[r * pcs->mi_stride + c]->mbmi.block_mi;
+            const size_t            i = (size_t)r * cols + c;
+            bsize[i] = (uint8_t)b->bsize, txd[i] = b->tx_depth, skip[i] = b->skip;
+            ref0[i] = (uint8_t)b->ref_frame[0], mode[i] = (uint8_t)b->mode, seg[i] = (uint8_t)b->segment_id;
+        }
+    CHECK(svtf_pack_mi_enc(n, bsize, txd, skip, ref0, mode, seg, mi), s->ctx);
+    CHECK(svtf_set_mi(s->ctx, mi, cols), s->ctx);
+    CHECK(svtf_sync(s->ctx), s->ctx); /* mi/soa are freed below */
+    free(soa);
+    free(mi);
+}
+
+static void plane_ptrs(const EbPictureBufferDesc *pic, int sb, void *p[3], int32_t st[3]) {
+    /* visible origin; chroma origin as the reference computes it (EbEncCdef.c:296-299, EbDeblockingFilter.c:116) */
+    p[0]  = pic->buffer_y + ((size_t)(pic->org_x + pic->org_y * pic->stride_y) * sb);
+    p[1]  = pic->buffer_cb + ((size_t)((pic->org_x + pic->org_y * pic->stride_cb) >> 1) * sb);
+    p[2]  = pic->buffer_cr + ((size_t)((pic->org_x + pic->org_y * pic->stride_cr) >> 1) * sb);
+    st[0] = pic->stride_y, st[1] = pic->stride_cb, st[2] = pic->stride_cr;
+}
+
+static void begin_picture(CtxSlot *s, const PictureControlSet *pcs, const EbPictureBufferDesc *pic) {
+    if (g_resident && s->resident)
+        return;
+    void   *p[3];
+    int32_t st[3];
+    plane_ptrs(pic, s->geom.sample_bytes, p, st);
+    CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+    CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    send_mi(s, pcs);
+    s->resident = 1;
+}
+
+static void end_picture(CtxSlot *s, const EbPictureBufferDesc *pic) {
+    void   *p[3];
+    int32_t st[3];
+    plane_ptrs(pic, s->geom.sample_bytes, p, st);
+    CHECK(svtf_download_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+}
+
+/* ---------------------------------------------------------------------------------------------------- */
+void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControlSet *pcs, int32_t plane_start,
+                               int32_t plane_end) {
+    CtxSlot                 *s  = slot_for(pcs);
+    const FrameHeader       *fh = &pcs->ppcs->frm_hdr;
+    const struct LoopFilter *l  = &fh->loop_filter_params;
+    svtf_lf_params           lf;
+    memset(&lf, 0, sizeof(lf));
+    lf.filter_level[0] = l->filter_level[0], lf.filter_level[1] = l->filter_level[1];
+    lf.filter_level_u = l->filter_level_u, lf.filter_level_v = l->filter_level_v;
+    lf.sharpness_level        = l->sharpness_level;
+    lf.mode_ref_delta_enabled = l->mode_ref_delta_enabled;
+    memcpy(lf.ref_deltas, l->ref_deltas, sizeof(lf.ref_deltas));
+    memcpy(lf.mode_deltas, l->mode_deltas, sizeof(lf.mode_deltas));
+    lf.segmentation_enabled = fh->segmentation_params.segmentation_enabled;
+    for (int i = 0; i < 8; i++)
+        for (int f = 0; f < 8; f++) {
+            lf.seg_feature_enabled[i][f] = fh->segmentation_params.feature_enabled[i][f];
+            lf.seg_feature_data[i][f]    = fh->segmentation_params.feature_data[i][f];
+        }
+    lf.delta_lf_present = fh->delta_lf_params.delta_lf_present;
+    lf.delta_lf_multi   = fh->delta_lf_params.delta_lf_multi;
+    for (int i = 0; i < 4; i++) lf.curr_delta_lf[i] = pcs->ppcs->curr_delta_lf[i];
+    begin_picture(s, pcs, frame_buffer);
+    CHECK(svtf_deblock_frame(s->ctx, &lf, plane_start, plane_end), s->ctx);
+    if (!g_resident)
+        end_picture(s, frame_buffer), s->resident = 0;
+}
+
+static void fb_indices(const PictureControlSet *pcs, const svtf_geom *g, int8_t *idx) {
+    const int nvfb = (g->mi_rows + 15) / 16, nhfb = (g->mi_cols + 15) / 16;
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++)
+            idx[fbr * nhfb + fbc] = pcs->mi_grid_base[16 * fbr * pcs->mi_stride + 16 * fbc]->mbmi.cdef_strength;
+}
+
+void svt_av1_cdef_frame(SequenceControlSet *scs, PictureControlSet *pcs) {
+    CtxSlot             *s = slot_for(pcs);
+    EbPictureBufferDesc *recon;
+    svt_aom_get_recon_pic(pcs, &recon, scs->is_16bit_pipeline);
+    const CdefParams *cp = &pcs->ppcs->frm_hdr.cdef_params;
+    svtf_cdef_params  p;
+    memset(&p, 0, sizeof(p));
+    p.cdef_damping = cp->cdef_damping, p.cdef_bits = cp->cdef_bits;
+    for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++)
+        p.cdef_y_strength[i] = cp->cdef_y_strength[i], p.cdef_uv_strength[i] = cp->cdef_uv_strength[i];
+    const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
+    int8_t   *idx = (int8_t *)malloc(nfb);
+    fb_indices(pcs, &s->geom, idx);
+    /* the reference reads a stale index for all-skip fbs and then skips them; clamp it into range */
+    for (int i = 0; i < nfb; i++)
+        if (idx[i] >= (1 << p.cdef_bits) || idx[i] < 0)
+            idx[i] = 0;
+    begin_picture(s, pcs, recon);
+    CHECK(svtf_cdef_apply_frame(s->ctx, &p, idx), s->ctx);
+    CHECK(svtf_sync(s->ctx), s->ctx);
+    free(idx);
+    if (!g_resident)
+        end_picture(s, recon), s->resident = 0;
+}
+
+static void search_cfg_of(const PictureControlSet *pcs, svtf_cdef_search_cfg *c) {
+    const CdefControls *cc = &pcs->ppcs->cdef_ctrls;
+    memset(c, 0, sizeof(*c));
+    c->first_pass_fs_num          = cc->first_pass_fs_num;
+    c->default_second_pass_fs_num = cc->default_second_pass_fs_num;
+    memcpy(c->default_first_pass_fs, cc->default_first_pass_fs, 64);
+    memcpy(c->default_second_pass_fs, cc->default_second_pass_fs, 64);
+    memcpy(c->default_first_pass_fs_uv, cc->default_first_pass_fs_uv, 64);
+    memcpy(c->default_second_pass_fs_uv, cc->default_second_pass_fs_uv, 64);
+    c->subsampling_factor = cc->subsampling_factor;
+    c->base_q_idx         = pcs->ppcs->frm_hdr.quantization_params.base_q_idx;
+    c->zero_fs_cost_bias  = cc->zero_fs_cost_bias;
+}
+
+/* cdef_seg_search over the whole picture (the first CDEF segment to arrive calls this, the others no-op):
+ * fills pcs->mse_seg, pcs->skip_cdef_seg and pcs->cdef_dir_data like the reference. */
+void svtf_cdef_search_picture(PictureControlSet *pcs, SequenceControlSet *scs) {
+    CtxSlot             *s = slot_for(pcs);
+    EbPictureBufferDesc *recon;
+    svt_aom_get_recon_pic(pcs, &recon, scs->is_16bit_pipeline);
+    const EbPictureBufferDesc *input = scs->is_16bit_pipeline ? pcs->input_frame16bit : pcs->ppcs->enhanced_pic;
+    svtf_cdef_search_cfg       cfg;
+    search_cfg_of(pcs, &cfg);
+    const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
+    begin_picture(s, pcs, recon);
+    void   *p[3];
+    int32_t st[3];
+    plane_ptrs(input, s->geom.sample_bytes, p, st);
+    CHECK(svtf_upload_source(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    uint64_t *mse = (uint64_t *)malloc(sizeof(uint64_t) * 128 * (size_t)nfb);
+    uint8_t  *dir = (uint8_t *)malloc(64 * (size_t)nfb);
+    int32_t  *var = (int32_t *)malloc(sizeof(int32_t) * 64 * (size_t)nfb);
+    CHECK(svtf_cdef_search_frame(s->ctx, &cfg, mse, pcs->skip_cdef_seg, dir, var), s->ctx);
+    memcpy(pcs->mse_seg[0], mse, sizeof(uint64_t) * 64 * (size_t)nfb);
+    memcpy(pcs->mse_seg[1], mse + (size_t)64 * nfb, sizeof(uint64_t) * 64 * (size_t)nfb);
+    for (int fb = 0; fb < nfb; fb++)
+        for (int b = 0; b < 64; b++) {
+            pcs->cdef_dir_data[fb].dir[b >> 3][b & 7] = dir[fb * 64 + b];
+            pcs->cdef_dir_data[fb].var[b >> 3][b & 7] = var[fb * 64 + b];
+        }
+    free(mse), free(dir), free(var);
+}
+
+void finish_cdef_search(PictureControlSet *pcs) {
+    CtxSlot                 *s    = slot_for(pcs);
+    PictureParentControlSet *ppcs = pcs->ppcs;
+    FrameHeader             *fh   = &ppcs->frm_hdr;
+    svtf_cdef_search_cfg     cfg;
+    search_cfg_of(pcs, &cfg);
+    uint32_t fast_lambda = 0, full_lambda = 0;
+    (*svt_aom_av1_lambda_assignment_function_table[ppcs->pred_structure])(
+        pcs, &fast_lambda, &full_lambda, (uint8_t)ppcs->enhanced_pic->bit_depth, fh->quantization_params.base_q_idx, FALSE);
+    cfg.lambda    = full_lambda;
+    const int nvfb = (s->geom.mi_rows + 15) / 16, nhfb = (s->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
+    /* the table lives in pcs->mse_seg (the reference's bias pass edits it in place; so do we) */
+    uint64_t *mse = (uint64_t *)malloc(sizeof(uint64_t) * 128 * (size_t)nfb);
+    memcpy(mse, pcs->mse_seg[0], sizeof(uint64_t) * 64 * (size_t)nfb);
+    memcpy(mse + (size_t)64 * nfb, pcs->mse_seg[1], sizeof(uint64_t) * 64 * (size_t)nfb);
+    svtf_cdef_params out;
+    int8_t          *idx = (int8_t *)malloc(nfb);
+    CHECK(svtf_cdef_pick_host(&cfg, mse, pcs->skip_cdef_seg, nfb, &out, idx), s->ctx);
+    if (cfg.zero_fs_cost_bias)
+        for (int fb = 0; fb < nfb; fb++)
+            if (!pcs->skip_cdef_seg[fb]) {
+                pcs->mse_seg[0][fb][0] = ((uint16_t)cfg.zero_fs_cost_bias * pcs->mse_seg[0][fb][0]) >> 6;
+                pcs->mse_seg[1][fb][0] = ((uint16_t)cfg.zero_fs_cost_bias * pcs->mse_seg[1][fb][0]) >> 6;
+            }
+    fh->cdef_params.cdef_bits    = (uint8_t)out.cdef_bits;
+    fh->cdef_params.cdef_damping = (uint8_t)out.cdef_damping;
+    ppcs->nb_cdef_strengths      = 1 << out.cdef_bits;
+    for (int i = 0; i < (1 << out.cdef_bits); i++) {
+        fh->cdef_params.cdef_y_strength[i]  = out.cdef_y_strength[i];
+        fh->cdef_params.cdef_uv_strength[i] = out.cdef_uv_strength[i];
+    }
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++)
+            if (idx[fbr * nhfb + fbc] >= 0)
+                pcs->mi_grid_base[16 * fbr * pcs->mi_stride + 16 * fbc]->mbmi.cdef_strength = idx[fbr * nhfb + fbc];
+    free(mse), free(idx);
+}
+
+void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdPlane *pd, uint16_t *ext_rec_y) {
+    (void)pd;
+    CtxSlot        *s  = slot_for(pcs);
+    const CcsoInfo *ci = &pcs->ppcs->frm_hdr.ccso_info;
+    svtf_ccso_params p;
+    memset(&p, 0, sizeof(p));
+    uint8_t *flags[3];
+    for (int pl = 0; pl < 3; pl++) {
+        p.ccso_enable[pl] = ci->ccso_enable[pl], p.ccso_bo_only[pl] = ci->ccso_bo_only[pl], p.quant_idx[pl] = ci->quant_idx[pl];
+        p.ext_filter_support[pl] = ci->ext_filter_support[pl], p.edge_clf[pl] = ci->edge_clf[pl];
+        p.max_band_log2[pl] = (uint8_t)ci->max_band_log2[pl];
+        memcpy(p.filter_offset[pl], ci->filter_offset[pl], SVTF_CCSO_LUT_SIZE);
+        const int pw = s->geom.width >> (pl ? 1 : 0), ph = s->geom.height >> (pl ? 1 : 0), bl = pl ? 7 : 8;
+        const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
+        flags[pl] = (uint8_t *)malloc((size_t)nbx * nby);
+        for (int by = 0; by < nby; by++)
+            for (int bx = 0; bx < nbx; bx++) { /* Common/Codec/EbCcso.c:317-322 */
+                const MbModeInfo *m = &pcs->mi_grid_base[64 * by * pcs->mi_stride + 64 * bx]->mbmi;
+                flags[pl][by * nbx + bx] = pl == 0 ? m->ccso_blk_y : (pl == 1 ? m->ccso_blk_u : m->ccso_blk_v);
+            }
+    }
+    if (g_resident && s->resident) {
+        /* post-CDEF picture and pre-CDEF luma are already on the device */
+    } else {
+        /* stand-alone call: the classifier input is the caller's ext_rec_y (pre-CDEF luma, 5-sample padded,
+         * Encoder/Codec/EbCdefProcess.c:480-502): stage it as the "pre-CDEF" picture by running an identity CDEF */
+        const int       W = s->geom.width, H = s->geom.height, cw = s->geom.mi_cols * 4, chh = s->geom.mi_rows * 4, es = W + 10;
+        const int       sb = s->geom.sample_bytes;
+        void           *pp[3];
+        int32_t         st[3];
+        plane_ptrs(frame, sb, pp, st);
+        uint8_t *ly = (uint8_t *)malloc((size_t)cw * chh * sb);
+        for (int r = 0; r < chh; r++)
+            for (int c = 0; c < cw; c++) {
+                const uint16_t v = ext_rec_y[(size_t)(5 + (r < H ? r : H - 1)) * es + 5 + (c < W ? c : W - 1)];
+                if (sb == 1)
+                    ly[(size_t)r * cw + c] = (uint8_t)v;
+                else
+                    ((uint16_t *)ly)[(size_t)r * cw + c] = v;
+            }
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, ly, cw, pp[1], st[1], pp[2], st[2]), s->ctx);
+        send_mi(s, pcs);
+        svtf_cdef_params idp;
+        memset(&idp, 0, sizeof(idp));
+        const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
+        int8_t   *idx = (int8_t *)calloc(nfb, 1);
+        CHECK(svtf_cdef_apply_frame(s->ctx, &idp, idx), s->ctx); /* strengths 0: copies, marks the pre-CDEF surface */
+        CHECK(svtf_sync(s->ctx), s->ctx);
+        free(idx), free(ly);
+        /* now overwrite the current (post-"CDEF") surface with the picture to be modified */
+        svtf_dev_plane dp[3];
+        CHECK(svtf_dev_planes(s->ctx, 1, dp), s->ctx);
+        CHECK(svtf_overwrite_current(s->ctx, pp[0], st[0], pp[1], st[1], pp[2], st[2]), s->ctx);
+    }
+    const uint8_t *cf[3] = {flags[0], flags[1], flags[2]};
+    CHECK(svtf_ccso_apply_frame(s->ctx, &p, cf), s->ctx);
+    end_picture(s, frame);
+    s->resident = 0;
+    for (int pl = 0; pl < 3; pl++) free(flags[pl]);
+}

@@ -169,6 +169,11 @@ int svtf_frame_begin(svtf_ctx *ctx, const svtf_geom *geom);
  * the reference entry points).  Copies the coded area (mi_cols*4 x mi_rows*4). */
 int svtf_upload_frame(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
                       const void *cr, int32_t stride_cr);
+/* Host -> device copy into the CURRENT end of the chain, keeping the chain state (in particular the
+ * remembered pre-CDEF picture).  Lets a caller that ran CDEF elsewhere hand over the post-CDEF picture while
+ * the pre-CDEF luma (ccso_frame's ext_rec_y argument) is the one uploaded before. */
+int svtf_overwrite_current(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
+                           const void *cr, int32_t stride_cr);
 /* Source picture (pcs->cdef_input_source / input_frame16bit) for the strength search. */
 int svtf_upload_source(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
                        const void *cr, int32_t stride_cr);

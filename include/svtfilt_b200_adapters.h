@@ -1,0 +1,39 @@
+/*
+ * svtfilt_b200_adapters.h — Tier 2 of the drop-in boundary: the reference's own frame-level entry points,
+ * re-implemented over the Tier-1 C ABI (adapters/svtf_enc_adapters.c).  Include AFTER the reference headers
+ * (EbPictureControlSet.h, EbSequenceControlSet.h, EbCcso.h); the prototypes below are the reference's own and
+ * are repeated only for documentation.
+ *
+ *   void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControlSet *pcs,
+ *                                  int32_t plane_start, int32_t plane_end);   Encoder/Codec/EbDeblockingFilter.c:624
+ *   void svt_av1_cdef_frame(SequenceControlSet *scs, PictureControlSet *pcs); Encoder/Codec/EbEncCdef.c:284
+ *   void finish_cdef_search(PictureControlSet *pcs);                          Encoder/Codec/EbEncCdef.c:728
+ *   void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdPlane *pd,
+ *                   uint16_t *ext_rec_y);                                     Common/Codec/EbCcso.c:626
+ */
+#ifndef SVTFILT_B200_ADAPTERS_H
+#define SVTFILT_B200_ADAPTERS_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct PictureControlSet;
+struct SequenceControlSet;
+
+/* Whole-picture replacement of the static cdef_seg_search (Encoder/Codec/EbCdefProcess.c:114): fills
+ * pcs->mse_seg, pcs->skip_cdef_seg and pcs->cdef_dir_data.  The first CDEF segment to arrive calls it. */
+void svtf_cdef_search_picture(struct PictureControlSet *pcs, struct SequenceControlSet *scs);
+
+/* CUDA device used by contexts the adapters create (default 0). */
+void svtf_adapter_set_device(int device);
+/* 1: keep the picture resident on the GPU between DLF, CDEF search, CDEF apply and CCSO of one pcs (no
+ * intermediate download/upload); ccso_frame (or svtf_adapter_download) brings it back.  0 (default): every entry
+ * point uploads and downloads, i.e. each is a stand-alone drop-in. */
+void svtf_adapter_set_resident(int on);
+/* Destroy the cached GPU context of a picture (call where the pipeline recycles the pcs). */
+void svtf_adapter_release(const struct PictureControlSet *pcs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -248,6 +248,16 @@ extern "C" int svtf_upload_frame(svtf_ctx *c, const void *y, int32_t sy, const v
     return r;
 }
 
+extern "C" int svtf_overwrite_current(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_overwrite_current: NULL context");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_overwrite_current: no picture uploaded");
+    const void   *src[3] = {y, cb, cr};
+    const int32_t st[3]  = {sy, scb, scr};
+    return copy_planes(c, c->surf[c->cur], src, st, true);
+}
+
 extern "C" int svtf_upload_source(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_upload_source: NULL context");

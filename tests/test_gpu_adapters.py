@@ -1,0 +1,92 @@
+"""GPU: the Tier-2 adapters — the reference's own entry points (svt_av1_loop_filter_frame(frame, pcs, ..),
+svt_av1_cdef_frame(scs, pcs), finish_cdef_search(pcs), ccso_frame(frame, pcs, pd, ext_rec_y)) implemented over
+the C ABI — called on real PictureControlSet structures and compared with the real reference functions called
+on identical structures (oracle/_ref) and with the oracle."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def adapt(H):
+    path = os.path.join(H.ROOT, "adapters", "_build", "libsvtadapt_test.so")
+    if not os.path.exists(path):
+        pytest.skip("adapters/_build/libsvtadapt_test.so not built (needs the reference headers)")
+    return C.CDLL(path)
+
+
+def _soa(H, soa):
+    return H.Ref._soa(soa)
+
+
+@pytest.mark.parametrize("w,h,bd,sb", [(200, 136, 8, 1), (328, 200, 10, 2), (136, 72, 12, 2)])
+def test_adapters_match_reference(H, orc, adapt, w, h, bd, sb):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    src = H.synth_picture(g, 2000 + w, noise=1)
+    rec = H.synth_source(g, src, 2001, amp=9)
+    soa = H.synth_mode_info(g, 2002, p_skip=0.4, segments=True)
+    mi = H.pack_mi(soa)
+    s, keep = _soa(H, soa)
+    ref = H.Ref() if H.ref_available() else None
+
+    # --- svt_av1_loop_filter_frame ---
+    lf = S.lf_params((30, 22), 14, 17, sharpness_level=2, mode_ref_delta_enabled=1, mode_deltas=(0, 2))
+    got = [p.copy() for p in rec]
+    assert adapt.adapt_deblock_frame(C.byref(g), *H._planes(got), C.byref(s), C.byref(lf), 0, 3) == 0
+    exp = orc.deblock(g, rec, mi, lf)
+    assert H.planes_equal(got, exp), "deblock vs oracle: " + H.first_diff(got, exp)
+    if ref:
+        assert H.planes_equal(got, ref.deblock(g, rec, soa, lf))
+    dbk = got
+
+    # --- cdef search + finish_cdef_search ---
+    first, second = H.cdef_level1_lists()
+    cfg = S.cdef_search_cfg(first, second, subsampling_factor=1, base_q_idx=130, zero_fs_cost_bias=0, lambda_=5000)
+    nv, nh = H.nfb_of(g)
+    nfb = nv * nh
+    mse = np.zeros((2, nfb, 64), np.uint64)
+    skip = np.zeros(nfb, np.uint8)
+    dirs = np.zeros((nfb, 64), np.uint8)
+    var = np.zeros((nfb, 64), np.int32)
+    out = H.L.CdefParams()
+    idx = np.zeros(nfb, np.int8)
+    assert adapt.adapt_cdef_search_pick(C.byref(g), *H._planes(dbk), *H._planes(src), C.byref(s), C.byref(cfg), H._p(mse), H._p(skip),
+                                        H._p(dirs), H._p(var), C.byref(out), H._p(idx)) == 0
+    e = orc.cdef_search(g, dbk, src, mi, cfg)
+    for a, b, name in zip((mse, skip, dirs, var), e, ("mse", "skip", "dir", "var")):
+        assert np.array_equal(a, b), name
+    ep, eidx = orc.cdef_pick(cfg, e[0], e[1])
+    assert (out.cdef_bits, out.cdef_damping, list(out.cdef_y_strength)[:8], list(out.cdef_uv_strength)[:8]) == \
+           (ep.cdef_bits, ep.cdef_damping, list(ep.cdef_y_strength)[:8], list(ep.cdef_uv_strength)[:8])
+    assert np.array_equal(idx, eidx)
+    if ref:
+        rp, ridx = ref.cdef_pick(g, soa, cfg, e[0], e[1])
+        assert (out.cdef_bits, list(out.cdef_y_strength)[:8], list(out.cdef_uv_strength)[:8]) == \
+               (rp.cdef_bits, list(rp.cdef_y_strength)[:8], list(rp.cdef_uv_strength)[:8])
+        assert np.array_equal(idx, ridx)
+
+    # --- svt_av1_cdef_frame with the picked strengths (and with random ones) ---
+    for cdef, fidx in ((out, idx), H.synth_cdef(g, 2003)):
+        got = [p.copy() for p in dbk]
+        fi = np.ascontiguousarray(fidx, np.int8)
+        assert adapt.adapt_cdef_apply_frame(C.byref(g), *H._planes(got), C.byref(s), C.byref(cdef), H._p(fi)) == 0
+        exp = orc.cdef_apply(g, dbk, mi, cdef, fi)
+        assert H.planes_equal(got, exp), "cdef vs oracle: " + H.first_diff(got, exp)
+        if ref:
+            assert H.planes_equal(got, ref.cdef_apply(g, dbk, soa, cdef, fi))
+    post = got
+
+    # --- ccso_frame (the reference wrapper is byte-only; the adapter handles 8- and 16-bit samples) ---
+    ccso, flags = H.synth_ccso(g, 2004, (0, 1, 2), (0, 3, 5), (0, 1, 0), (2, 0, 3))
+    got = [p.copy() for p in post]
+    fl = (C.c_void_p * 3)(*[f.ctypes.data for f in flags])
+    assert adapt.adapt_ccso_frame(C.byref(g), *H._planes(got), H._p(dbk[0]), C.c_int(dbk[0].strides[0] // dbk[0].itemsize), C.byref(ccso), fl) == 0
+    exp = orc.ccso_apply(g, post, dbk[0], ccso, flags)
+    assert H.planes_equal(got, exp), "ccso vs oracle: " + H.first_diff(got, exp)
+    if ref:
+        assert H.planes_equal(got, ref.ccso_apply(g, post, dbk[0], ccso, flags))
