@@ -6,8 +6,8 @@ The directory name is not a Python identifier; import it as ``svtfilt_b200`` (th
 the repository root registers this package under that name).
 """
 from . import _lib
-from .filters import (FilterContext, PinnedPicture, SvtfError, ccso_params, cdef_params, cdef_pick_host, cdef_search_cfg,
+from .filters import (FilterContext, PinnedArray, PinnedPicture, SvtfError, ccso_params, cdef_params, cdef_pick_host, cdef_search_cfg,
                       lf_params, make_geom, pack_mi_dec, pack_mi_enc)
 
-__all__ = ["FilterContext", "PinnedPicture", "SvtfError", "ccso_params", "cdef_params", "cdef_pick_host", "cdef_search_cfg",
+__all__ = ["FilterContext", "PinnedArray", "PinnedPicture", "SvtfError", "ccso_params", "cdef_params", "cdef_pick_host", "cdef_search_cfg",
            "lf_params", "make_geom", "pack_mi_dec", "pack_mi_enc", "_lib"]

@@ -12,6 +12,7 @@
 
 #include "svtf_kernels.cuh"
 #include "svtf_search.cuh"
+#include "svtf_cdef2.cuh"
 
 namespace svtf {
 
@@ -278,8 +279,12 @@ extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) 
         return c->fail(SVTF_E_STATE, "svtf_set_mi: call svtf_frame_begin first");
     if (!mi || mi_stride < c->geom.mi_cols)
         return c->fail(SVTF_E_ARG, "svtf_set_mi: NULL grid or stride smaller than mi_cols");
-    CUDA_TRY(c, cudaMemcpy2DAsync(c->d_mi, sizeof(svtf_mi_t) * c->mi_stride, mi, sizeof(svtf_mi_t) * mi_stride,
-                                  sizeof(svtf_mi_t) * c->geom.mi_cols, c->geom.mi_rows, cudaMemcpyHostToDevice, c->stream));
+    if (mi_stride == c->mi_stride) // same pitch: one linear DMA
+        CUDA_TRY(c, cudaMemcpyAsync(c->d_mi, mi, sizeof(svtf_mi_t) * ((size_t)(c->geom.mi_rows - 1) * mi_stride + c->geom.mi_cols),
+                                    cudaMemcpyHostToDevice, c->stream));
+    else
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->d_mi, sizeof(svtf_mi_t) * c->mi_stride, mi, sizeof(svtf_mi_t) * mi_stride,
+                                      sizeof(svtf_mi_t) * c->geom.mi_cols, c->geom.mi_rows, cudaMemcpyHostToDevice, c->stream));
     c->have_mi = true;
     return SVTF_OK;
 }
@@ -380,12 +385,42 @@ extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t
     return SVTF_OK;
 }
 
-extern "C" int svtf_cdef_apply_frame(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t *fb_strength_idx) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL context");
-    if (!cp || !fb_strength_idx)
-        return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL argument");
-    if (int r = need_frame_mi(c, "svtf_cdef_apply_frame"))
+// ---- CCSO parameters -> device (LUT + block flags) --------------------------------------------------
+static int ccso_check(svtf_ctx *c, const svtf_ccso_params *cc, const char *who) {
+    for (int p = 0; p < 3; p++)
+        if (cc->quant_idx[p] > 3 || cc->ext_filter_support[p] > 5 || cc->max_band_log2[p] > 7 || cc->edge_clf[p] > 1) {
+            char msg[96];
+            snprintf(msg, sizeof(msg), "%s: CCSO parameter out of range", who);
+            return c->fail(SVTF_E_ARG, msg);
+        }
+    return SVTF_OK;
+}
+
+static int ccso_stage(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3], CcsoFuse &f) {
+    static const uint8_t quant_sz[4] = {16, 8, 32, 64}; // Common/Codec/EbCcso.c:636
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_ccso_lut, cc->filter_offset, 3 * SVTF_CCSO_LUT_SIZE, cudaMemcpyHostToDevice, c->stream));
+    for (int p = 0; p < 3; p++) {
+        f.enable[p] = cc->ccso_enable[p] != 0, f.bo_only[p] = cc->ccso_bo_only[p] != 0;
+        f.thr[p] = quant_sz[cc->quant_idx[p]], f.support[p] = cc->ext_filter_support[p];
+        f.edge_clf[p] = cc->edge_clf[p], f.band_log2[p] = cc->max_band_log2[p];
+        f.blk_flags[p] = nullptr;
+        if (blk_flags && blk_flags[p]) {
+            const int pw = c->geom.width >> (p ? 1 : 0), ph = c->geom.height >> (p ? 1 : 0), bl = p ? 7 : 8;
+            const int n  = ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl);
+            uint8_t  *d  = c->d_ccso_flags + (size_t)p * c->max_ccso_blocks;
+            CUDA_TRY(c, cudaMemcpyAsync(d, blk_flags[p], n, cudaMemcpyHostToDevice, c->stream));
+            f.blk_flags[p] = d;
+        }
+    }
+    f.lut = c->d_ccso_lut;
+    f.on  = 1;
+    return SVTF_OK;
+}
+
+// CDEF apply; with `cc` the CCSO pass of the same picture runs in the kernel's epilogue (one launch, one write).
+static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t *fb_strength_idx, const svtf_ccso_params *cc,
+                           const uint8_t *const blk_flags[3], const char *who) {
+    if (int r = need_frame_mi(c, who))
         return r;
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16;
@@ -393,27 +428,47 @@ extern "C" int svtf_cdef_apply_frame(svtf_ctx *c, const svtf_cdef_params *cp, co
         if (fb_strength_idx[i] >= SVTF_CDEF_MAX_STRENGTHS)
             return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: strength index out of range");
     CUDA_TRY(c, cudaMemcpyAsync(c->d_fb_idx, fb_strength_idx, (size_t)nvfb * nhfb, cudaMemcpyHostToDevice, c->stream));
-    CdefArgs a;
     const int nxt = next_surface(c);
-    a.in        = c->surf[c->cur].planes();
-    a.out       = c->surf[nxt].planes();
-    a.mi        = c->d_mi;
-    a.mi_stride = c->mi_stride;
-    a.d         = dims_of(c->geom);
-    a.fb_idx    = c->d_fb_idx;
-    a.damping   = cp->cdef_damping;
-    memcpy(a.y_strength, cp->cdef_y_strength, sizeof(a.y_strength));
-    memcpy(a.uv_strength, cp->cdef_uv_strength, sizeof(a.uv_strength));
-    dim3 grid(nhfb, nvfb);
-    if (c->geom.sample_bytes == 1)
-        cdef_kernel<uint8_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
-    else
-        cdef_kernel<uint16_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
+    dim3      grid(nhfb, nvfb);
+    static const bool use_v1 = getenv("SVTF_CDEF_SCALAR") != nullptr; // A/B switch: the round-1 scalar kernel
+    if (use_v1 && !cc) {
+        CdefArgs a;
+        a.in = c->surf[c->cur].planes(), a.out = c->surf[nxt].planes();
+        a.mi = c->d_mi, a.mi_stride = c->mi_stride, a.d = dims_of(c->geom), a.fb_idx = c->d_fb_idx, a.damping = cp->cdef_damping;
+        memcpy(a.y_strength, cp->cdef_y_strength, sizeof(a.y_strength));
+        memcpy(a.uv_strength, cp->cdef_uv_strength, sizeof(a.uv_strength));
+        if (c->geom.sample_bytes == 1)
+            cdef_kernel<uint8_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
+        else
+            cdef_kernel<uint16_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
+    } else {
+        Cdef2Args b;
+        b.in = c->surf[c->cur].planes(), b.out = c->surf[nxt].planes();
+        b.mi = c->d_mi, b.mi_stride = c->mi_stride, b.d = dims_of(c->geom), b.fb_idx = c->d_fb_idx, b.damping = cp->cdef_damping;
+        memcpy(b.y_strength, cp->cdef_y_strength, sizeof(b.y_strength));
+        memcpy(b.uv_strength, cp->cdef_uv_strength, sizeof(b.uv_strength));
+        memset(&b.ccso, 0, sizeof(b.ccso));
+        if (cc)
+            if (int r = ccso_stage(c, cc, blk_flags, b.ccso))
+                return r;
+        if (c->geom.sample_bytes == 1)
+            cdef2_kernel<uint8_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
+        else
+            cdef2_kernel<uint16_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
+    }
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
     c->pre_cdef = c->cur;
     c->cur      = nxt;
     return SVTF_OK;
+}
+
+extern "C" int svtf_cdef_apply_frame(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t *fb_strength_idx) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL context");
+    if (!cp || !fb_strength_idx)
+        return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL argument");
+    return cdef_apply_impl(c, cp, fb_strength_idx, nullptr, nullptr, "svtf_cdef_apply_frame");
 }
 
 extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
@@ -423,29 +478,20 @@ extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, co
         return c->fail(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL argument");
     if (!c->have_frame)
         return c->fail(SVTF_E_STATE, "svtf_ccso_apply_frame: no picture uploaded");
-    for (int p = 0; p < 3; p++)
-        if (cc->quant_idx[p] > 3 || cc->ext_filter_support[p] > 5 || cc->max_band_log2[p] > 7 || cc->edge_clf[p] > 1)
-            return c->fail(SVTF_E_ARG, "svtf_ccso_apply_frame: parameter out of range");
+    if (int r = ccso_check(c, cc, "svtf_ccso_apply_frame"))
+        return r;
     if (!(cc->ccso_enable[0] | cc->ccso_enable[1] | cc->ccso_enable[2]))
         return SVTF_OK;
     CUDA_TRY(c, cudaSetDevice(c->device));
-    static const uint8_t quant_sz[4] = {16, 8, 32, 64}; // Common/Codec/EbCcso.c:636
+    CcsoFuse f;
+    if (int r = ccso_stage(c, cc, blk_flags, f))
+        return r;
     CcsoArgs a;
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_ccso_lut, cc->filter_offset, 3 * SVTF_CCSO_LUT_SIZE, cudaMemcpyHostToDevice, c->stream));
     for (int p = 0; p < 3; p++) {
-        a.enable[p] = cc->ccso_enable[p] != 0, a.bo_only[p] = cc->ccso_bo_only[p] != 0;
-        a.thr[p] = quant_sz[cc->quant_idx[p]], a.support[p] = cc->ext_filter_support[p];
-        a.edge_clf[p] = cc->edge_clf[p], a.band_log2[p] = cc->max_band_log2[p];
-        a.blk_flags[p] = nullptr;
-        if (blk_flags && blk_flags[p]) {
-            const int pw = c->geom.width >> (p ? 1 : 0), ph = c->geom.height >> (p ? 1 : 0), bl = p ? 7 : 8;
-            const int n  = ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl);
-            uint8_t  *d  = c->d_ccso_flags + (size_t)p * c->max_ccso_blocks;
-            CUDA_TRY(c, cudaMemcpyAsync(d, blk_flags[p], n, cudaMemcpyHostToDevice, c->stream));
-            a.blk_flags[p] = d;
-        }
+        a.enable[p] = f.enable[p], a.bo_only[p] = f.bo_only[p], a.thr[p] = f.thr[p], a.support[p] = f.support[p];
+        a.edge_clf[p] = f.edge_clf[p], a.band_log2[p] = f.band_log2[p], a.blk_flags[p] = f.blk_flags[p];
     }
-    a.lut = c->d_ccso_lut;
+    a.lut = f.lut;
     a.d   = dims_of(c->geom);
     a.in  = c->surf[c->cur].planes();
     int nxt = c->cur;
@@ -468,13 +514,25 @@ extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, co
     return SVTF_OK;
 }
 
+// Deblock -> CDEF -> CCSO on the uploaded picture.  CDEF and CCSO of the same picture run as ONE kernel (the CCSO
+// classifier input is the pre-CDEF luma tile the CDEF kernel already holds in shared memory); SVTF_CHAIN_UNFUSED=1
+// keeps them as separate launches for A/B measurements.
 extern "C" int svtf_filter_chain(svtf_ctx *c, const svtf_lf_params *lf, const svtf_cdef_params *cdef, const int8_t *fb_strength_idx,
                                  const svtf_ccso_params *ccso, const uint8_t *const blk_flags[3]) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_filter_chain: NULL context");
+    if (cdef && !fb_strength_idx)
+        return c->fail(SVTF_E_ARG, "svtf_filter_chain: CDEF needs fb_strength_idx");
     int r = SVTF_OK;
     if (lf && (r = svtf_deblock_frame(c, lf, 0, 3)) != SVTF_OK)
         return r;
+    static const bool unfused = getenv("SVTF_CHAIN_UNFUSED") != nullptr || getenv("SVTF_CDEF_SCALAR") != nullptr;
+    const bool        ccso_on = ccso && (ccso->ccso_enable[0] | ccso->ccso_enable[1] | ccso->ccso_enable[2]);
+    if (cdef && ccso_on && !unfused) {
+        if ((r = ccso_check(c, ccso, "svtf_filter_chain")) != SVTF_OK)
+            return r;
+        return cdef_apply_impl(c, cdef, fb_strength_idx, ccso, blk_flags, "svtf_filter_chain");
+    }
     if (cdef && (r = svtf_cdef_apply_frame(c, cdef, fb_strength_idx)) != SVTF_OK)
         return r;
     if (ccso && (r = svtf_ccso_apply_frame(c, ccso, blk_flags)) != SVTF_OK)

@@ -156,6 +156,25 @@ class PinnedPicture:
         self._ptrs, self.planes = [], []
 
 
+class PinnedArray:
+    """A numpy array in page-locked host memory (svtf_host_alloc): copies from it are real asynchronous DMA."""
+
+    def __init__(self, shape, dtype):
+        lib = L.load()
+        self._lib = lib
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._ptr = lib.svtf_host_alloc(nbytes)
+        if not self._ptr:
+            raise SvtfError(L.E_NOMEM, "svtf_host_alloc failed")
+        buf = (C.c_uint8 * nbytes).from_address(self._ptr)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def close(self):
+        if self._ptr:
+            self._lib.svtf_host_free(self._ptr)
+        self._ptr, self.array = None, None
+
+
 class FilterContext:
     """One picture in flight on one GPU (svtf_ctx)."""
 
@@ -202,7 +221,8 @@ class FilterContext:
         self._chk(self._lib.svtf_upload_source(self._h, *self._planes_args(planes)))
 
     def set_mi(self, mi):
-        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        if not (isinstance(mi, np.ndarray) and mi.dtype == np.uint32 and mi.flags.c_contiguous):
+            mi = np.ascontiguousarray(mi, dtype=np.uint32)
         self._mi_keep = mi
         self._chk(self._lib.svtf_set_mi(self._h, _ptr(mi), mi.shape[1]))
 

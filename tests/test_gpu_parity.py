@@ -107,6 +107,39 @@ def test_ccso_matches_oracle(H, orc, w, h, bd, sb):
             assert H.planes_equal(got, exp), "after cdef: " + H.first_diff(got, exp)
 
 
+@pytest.mark.parametrize("w,h,bd,sb", CASES)
+def test_fused_cdef_ccso_matches_oracle(H, orc, w, h, bd, sb):
+    """filter_chain(cdef + ccso) is ONE launch (CCSO in the CDEF kernel's epilogue); it must equal the two
+    separate passes of the oracle for every tap support / classifier / band / bo_only / block-flag combination,
+    including filter blocks CDEF skips (strength index -1, all-skip blocks) where only CCSO touches the samples."""
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    pre = H.synth_picture(g, 650 + w + bd)
+    soa = H.synth_mode_info(g, 750 + h)
+    mi = H.pack_mi(soa)
+    combos = [((0, 0, 0), (0, 1, 2), (0, 0, 0), (2, 2, 2), (0, 0, 0), (1, 1, 1)), ((1, 2, 3), (3, 4, 5), (1, 0, 1), (0, 3, 1), (0, 0, 0), (1, 1, 1)),
+              ((3, 1, 0), (5, 0, 2), (0, 1, 0), (4, 0, 7), (1, 0, 1), (1, 1, 1)), ((2, 2, 2), (4, 5, 3), (0, 0, 1), (7, 6, 5), (0, 1, 0), (1, 0, 1)),
+              ((0, 3, 1), (1, 2, 0), (1, 1, 0), (1, 1, 1), (0, 0, 0), (0, 1, 0))]
+    with S.FilterContext(g) as ctx:
+        for n, (q, sup, clf, band, bo, en) in enumerate(combos if w < 1000 else combos[:2]):
+            ccso, flags = H.synth_ccso(g, 850 + n, q, sup, clf, band, bo, en, p_on=0.7)
+            cdef, idx = H.synth_cdef(g, 950 + n)
+            if n == 1:
+                idx = idx.copy()
+                idx.reshape(-1)[::2] = -1  # half of the filter blocks: CDEF off, CCSO still on
+            for fl in (flags, None):
+                ctx.begin(g)
+                ctx.upload(pre)
+                ctx.set_mi(mi)
+                before = ctx.launch_count
+                ctx.filter_chain(None, cdef, idx, ccso, fl)
+                assert ctx.launch_count - before == 1
+                got = ctx.download()
+                e1 = orc.cdef_apply(g, pre, mi, cdef, idx)
+                exp = orc.ccso_apply(g, e1, pre[0], ccso, fl)
+                assert H.planes_equal(got, exp), f"combo {n} flags={'y' if fl else 'n'}: " + H.first_diff(got, exp)
+
+
 @pytest.mark.parametrize("w,h,bd,sb", [(328, 200, 8, 1), (328, 200, 10, 2), (1920, 1080, 10, 2)])
 def test_chain_matches_oracle_and_reference(H, orc, w, h, bd, sb):
     S = H.S
