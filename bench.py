@@ -337,16 +337,24 @@ def main():
         c.upload(pins_in[k].planes)
         c.set_mi(pins_mi[k].array)
         c.filter_chain(wl["lf"], wl["cdef"], wl["idx"], wl["ccso"], wl["flags"])
+
+    def e2e_fetch(k):
         # asynchronous download into pinned memory; completion is awaited before the slot is reused
-        args_ = c._planes_args(pins_out[k].planes)
-        c._chk(L.svtf_download_frame_async(c._h, *args_))
+        c = ctxs[k]
+        c._chk(L.svtf_download_frame_async(c._h, *c._planes_args(pins_out[k].planes)))
 
     def e2e_step():
+        # Software-pipelined submission: picture j's download is queued AFTER picture j+1's upload.  The copy queues
+        # issue in submission order across streams, so a download queued first (it has to wait for its kernels) would
+        # hold back the next upload for the length of the kernels (tools/e2e_timeline.py shows the lock-step).
         for j in range(B):
             k = j % nin
             if j >= nin:
                 ctxs[k].sync()
             e2e_submit(k)
+            if j >= 1:
+                e2e_fetch((j - 1) % nin)
+        e2e_fetch((B - 1) % nin)
         for k in range(nin):
             ctxs[k].sync()
 

@@ -165,6 +165,19 @@ void  svtf_host_free(void *p);
 /* Start a picture: sets the geometry (must fit max_geom) and resets the surface chain. */
 int svtf_frame_begin(svtf_ctx *ctx, const svtf_geom *geom);
 
+/* Start ONE HORIZONTAL STRIPE of a picture on this context (single-picture multi-GPU split): the context
+ * owns superblock rows [first_sb_row, first_sb_row + num_sb_rows), 64 luma rows each.  After this call every
+ * entry point keeps taking WHOLE-PICTURE host arrays (planes with their strides, the mi grid, fb_strength_idx, CCSO
+ * block flags, the search outputs) and reads/writes only the stripe's part: upload copies the stripe plus 8 rows
+ * beyond each interior boundary, download writes the stripe's rows only, svtf_cdef_search_frame fills the stripe's
+ * filter-block rows of mse/skip/dir/var.  N contexts (one per GPU), called with identical arguments and disjoint
+ * row ranges, produce the same bytes as one whole-picture context.  The boundary deblock edge is recomputed on both
+ * sides (the reference's serial raster order, Encoder/Codec/EbDeblockingFilter.c:624-660, has no such boundary); no
+ * inter-GPU exchange is needed when the input comes from the host.  max_geom must cover the stripe plus up to two
+ * superblock rows of context.  svtf_cdef_pick is not available on a striped context: gather mse/skip and call
+ * svtf_cdef_pick_host. */
+int svtf_stripe_begin(svtf_ctx *ctx, const svtf_geom *full_geom, int32_t first_sb_row, int32_t num_sb_rows);
+
 /* Host -> device copy of the reconstructed picture (the `frame_buffer` / recon_pic argument of
  * the reference entry points).  Copies the coded area (mi_cols*4 x mi_rows*4). */
 int svtf_upload_frame(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,

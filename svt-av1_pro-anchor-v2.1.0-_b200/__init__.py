@@ -5,9 +5,10 @@ include/svtfilt_b200.h); this package is the thin Python host used by tests and 
 The directory name is not a Python identifier; import it as ``svtfilt_b200`` (the loader module at
 the repository root registers this package under that name).
 """
-from . import _lib
+from . import _lib, stripes
 from .filters import (FilterContext, PinnedArray, PinnedPicture, SvtfError, ccso_params, cdef_params, cdef_pick_host, cdef_search_cfg,
-                      lf_params, make_geom, pack_mi_dec, pack_mi_enc)
+                      lf_params, make_geom, make_geom_coded, pack_mi_dec, pack_mi_enc)
+from .stripes import StripeFilter
 
 __all__ = ["FilterContext", "PinnedArray", "PinnedPicture", "SvtfError", "ccso_params", "cdef_params", "cdef_pick_host", "cdef_search_cfg",
-           "lf_params", "make_geom", "pack_mi_dec", "pack_mi_enc", "_lib"]
+           "lf_params", "make_geom", "make_geom_coded", "pack_mi_dec", "pack_mi_enc", "StripeFilter", "stripes", "_lib"]

@@ -2,6 +2,7 @@
 // One context = one picture in flight on one CUDA stream.  No CPU fallback: every entry point that
 // needs the device fails with SVTF_E_CUDA when there is none.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -48,14 +49,33 @@ struct svtf_ctx {
     bool         have_geom = false, have_frame = false, have_mi = false, have_source = false, have_search = false;
     Surface      surf[3];  // filter chain ping-pong
     Surface      source;   // source picture for the search
+    // Stripe window (svtf_stripe_begin): the context holds picture rows [glob_row0, glob_row0 + geom.mi_rows*4) of the
+    // FULL picture `full`; it owns local rows [own_lo, own_hi).  Whole-picture mode: glob_row0 = 0, own = everything.
+    svtf_geom    full{};
+    bool         striped = false;
+    int          glob_row0 = 0, own_lo = 0, own_hi = 0;
     int          cur = 0;  // surface holding the current end of the chain
     int          pre_cdef = -1; // surface holding the picture before the last CDEF (-1: none)
     svtf_mi_t   *d_mi = nullptr;
     int          mi_stride = 0; // device mi stride == geom.mi_cols rounded
-    int8_t      *d_fb_idx = nullptr;
-    int8_t      *d_ccso_lut = nullptr;
-    uint8_t     *d_ccso_flags = nullptr; // 3 * max_blocks
+    // Small per-picture parameters (CDEF strength index per filter block, CCSO LUT and block flags) live in ONE device
+    // block and are sent with ONE DMA from a pinned staging slot, issued before the first kernel of a chain: a small
+    // copy queued between two kernels would stall the H2D engine (and the next picture's upload behind it) until the
+    // first kernel finishes.
+    uint8_t     *d_params = nullptr;
+    int8_t      *d_fb_idx = nullptr;     // = d_params
+    int8_t      *d_ccso_lut = nullptr;   // = d_params + poff_lut
+    uint8_t     *d_ccso_flags = nullptr; // = d_params + poff_flags, 3 * max_blocks
     int          max_ccso_blocks = 0;
+    size_t       poff_lut = 0, poff_flags = 0, psize = 0;
+    struct ParamSlot {
+        uint8_t    *h = nullptr;
+        cudaEvent_t ev = nullptr;
+        bool        pending = false;
+    } pslot[2];
+    int    pcur = 0;
+    bool   popen = false;
+    size_t plo = 0, phi = 0;
     uint64_t    *d_mse = nullptr;  // [2][nfb][64]
     uint8_t     *d_skip = nullptr; // [nfb]
     uint8_t     *d_dir = nullptr;  // [nfb][64]
@@ -139,10 +159,19 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
     c->max_nfb     = nvfb * nhfb;
     c->mi_stride   = round_up(max_geom->mi_cols, 32);
     if ((e = cudaMalloc(&c->d_mi, sizeof(svtf_mi_t) * (size_t)c->mi_stride * max_geom->mi_rows)) != cudaSuccess) return bail(e, "cudaMalloc(mi)");
-    if ((e = cudaMalloc(&c->d_fb_idx, c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(fb_idx)");
-    if ((e = cudaMalloc(&c->d_ccso_lut, 3 * SVTF_CCSO_LUT_SIZE)) != cudaSuccess) return bail(e, "cudaMalloc(ccso lut)");
-    c->max_ccso_blocks = ((max_geom->width + 255) / 256) * ((max_geom->height + 255) / 256);
-    if ((e = cudaMalloc(&c->d_ccso_flags, 3 * (size_t)c->max_ccso_blocks)) != cudaSuccess) return bail(e, "cudaMalloc(ccso flags)");
+    // flags are indexed in whole-picture coordinates even when the context holds one stripe: size for 16K rows
+    c->max_ccso_blocks = ((max_geom->width + 255) / 256) * std::max((max_geom->height + 255) / 256, 64);
+    c->poff_lut        = (size_t)round_up(c->max_nfb, 16);
+    c->poff_flags      = c->poff_lut + 3 * SVTF_CCSO_LUT_SIZE;
+    c->psize           = c->poff_flags + (size_t)round_up(3 * c->max_ccso_blocks, 16);
+    if ((e = cudaMalloc(&c->d_params, c->psize)) != cudaSuccess) return bail(e, "cudaMalloc(params)");
+    c->d_fb_idx     = reinterpret_cast<int8_t *>(c->d_params);
+    c->d_ccso_lut   = reinterpret_cast<int8_t *>(c->d_params + c->poff_lut);
+    c->d_ccso_flags = c->d_params + c->poff_flags;
+    for (auto &sl : c->pslot) {
+        if ((e = cudaHostAlloc(reinterpret_cast<void **>(&sl.h), c->psize, cudaHostAllocDefault)) != cudaSuccess) return bail(e, "cudaHostAlloc(params)");
+        if ((e = cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    }
     if ((e = cudaMalloc(&c->d_mse, sizeof(uint64_t) * 2 * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(mse)");
     if ((e = cudaMalloc(&c->d_skip, c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(skip)");
     if ((e = cudaMalloc(&c->d_dir, 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(dir)");
@@ -160,7 +189,11 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     for (int i = 0; i < 3; i++)
         for (int p = 0; p < 3; p++) cudaFree(c->surf[i].base[p]);
     for (int p = 0; p < 3; p++) cudaFree(c->source.base[p]);
-    cudaFree(c->d_mi), cudaFree(c->d_fb_idx), cudaFree(c->d_ccso_lut), cudaFree(c->d_ccso_flags);
+    cudaFree(c->d_mi), cudaFree(c->d_params);
+    for (auto &sl : c->pslot) {
+        if (sl.h) cudaFreeHost(sl.h);
+        if (sl.ev) cudaEventDestroy(sl.ev);
+    }
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     if (c->own_stream)
         cudaStreamDestroy(c->own_stream);
@@ -204,6 +237,9 @@ extern "C" int svtf_frame_begin(svtf_ctx *c, const svtf_geom *g) {
         return c->fail(SVTF_E_ARG, "svtf_frame_begin: geometry invalid or larger than the context's max_geom");
     CUDA_TRY(c, cudaSetDevice(c->device));
     c->geom      = *g;
+    c->full      = *g;
+    c->striped   = false;
+    c->glob_row0 = 0, c->own_lo = 0, c->own_hi = g->mi_rows * 4;
     c->have_geom = true;
     c->have_frame = c->have_mi = c->have_source = c->have_search = false;
     c->cur       = 0;
@@ -211,29 +247,74 @@ extern "C" int svtf_frame_begin(svtf_ctx *c, const svtf_geom *g) {
     return SVTF_OK;
 }
 
-static int copy_planes(svtf_ctx *c, Surface &s, const void *const src[3], const int32_t stride[3], bool to_device) {
+// One horizontal stripe of a picture: the context owns superblock rows [first_sb_row, first_sb_row +
+// num_sb_rows) (64 luma rows each) and keeps one extra SB row of context above and below where the picture continues.
+// Every later call takes WHOLE-PICTURE host arrays (planes, mi grid, fb_strength_idx, CCSO flags, search outputs) and
+// touches only this stripe's part of them, so N contexts on N GPUs called with the same arguments filter one picture.
+// Bit-exactness: a horizontal edge reads <= 7 rows and writes <= 6 rows on each side and edges of one pass never
+// overlap (Common/Codec/EbDeblockingCommon.c:787-823), CDEF taps reach +-2 rows (Common/Codec/EbCdef.c:99-122), CCSO
+// +-1 row; with 8 input rows beyond the boundary the boundary edge is recomputed redundantly on both sides and every
+// row the stripe's own CDEF/CCSO reads is exact.  No write-back, no exchange when the input comes from the host.
+extern "C" int svtf_stripe_begin(svtf_ctx *c, const svtf_geom *full, int32_t first_sb_row, int32_t num_sb_rows) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_stripe_begin: NULL context");
+    if (!geom_ok(full) || full->sample_bytes != c->max_geom.sample_bytes)
+        return c->fail(SVTF_E_ARG, "svtf_stripe_begin: bad picture geometry");
+    const int rows = full->mi_rows * 4, sb_rows = (rows + 63) / 64;
+    if (first_sb_row < 0 || num_sb_rows <= 0 || first_sb_row + num_sb_rows > sb_rows)
+        return c->fail(SVTF_E_ARG, "svtf_stripe_begin: superblock rows outside the picture");
+    const int ht = first_sb_row > 0, hb = first_sb_row + num_sb_rows < sb_rows;
+    const int g0 = 64 * (first_sb_row - ht), g1 = std::min(rows, 64 * (first_sb_row + num_sb_rows + hb));
+    svtf_geom l = *full;
+    l.mi_rows   = (g1 - g0) / 4;
+    l.height    = std::min(full->height, g1) - g0;
+    if (l.height <= 0 || l.mi_cols > c->max_geom.mi_cols || l.mi_rows > c->max_geom.mi_rows)
+        return c->fail(SVTF_E_ARG, "svtf_stripe_begin: stripe larger than the context's max_geom");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    c->geom      = l;
+    c->full      = *full;
+    c->striped   = true;
+    c->glob_row0 = g0;
+    c->own_lo    = 64 * ht;
+    c->own_hi    = std::min(g1 - g0, 64 * (ht + num_sb_rows));
+    c->have_geom = true;
+    c->have_frame = c->have_mi = c->have_source = c->have_search = false;
+    c->cur       = 0;
+    c->pre_cdef  = -1;
+    return SVTF_OK;
+}
+
+// Copies local luma rows [lo, hi) (and the matching chroma rows) between the caller's WHOLE-PICTURE planes and a surface.
+static int copy_planes(svtf_ctx *c, Surface &s, const void *const src[3], const int32_t stride[3], bool to_device, int lo, int hi) {
     const svtf_geom &g = c->geom;
     for (int p = 0; p < 3; p++) {
-        const int w = (g.mi_cols * 4) >> (p ? 1 : 0), h = (g.mi_rows * 4) >> (p ? 1 : 0);
+        const int ss = p ? 1 : 0;
+        const int w = (g.mi_cols * 4) >> ss, r0 = lo >> ss, h = (hi >> ss) - r0;
         if (!src[p] || stride[p] < w)
             return c->fail(SVTF_E_ARG, "plane pointer NULL or stride smaller than the coded width");
+        if (h <= 0)
+            continue;
         const size_t sb = g.sample_bytes;
+        uint8_t     *dev = static_cast<uint8_t *>(s.base[p]) + (size_t)r0 * s.pitch[p] * sb;
+        uint8_t     *hst = static_cast<uint8_t *>(const_cast<void *>(src[p])) + ((size_t)(c->glob_row0 >> ss) + r0) * stride[p] * sb;
         if (stride[p] == s.pitch[p]) { // same pitch on both sides: one linear DMA instead of a 2-D copy
             const size_t bytes = ((size_t)(h - 1) * s.pitch[p] + w) * sb;
             if (to_device)
-                CUDA_TRY(c, cudaMemcpyAsync(s.base[p], src[p], bytes, cudaMemcpyHostToDevice, c->stream));
+                CUDA_TRY(c, cudaMemcpyAsync(dev, hst, bytes, cudaMemcpyHostToDevice, c->stream));
             else
-                CUDA_TRY(c, cudaMemcpyAsync(const_cast<void *>(src[p]), s.base[p], bytes, cudaMemcpyDeviceToHost, c->stream));
+                CUDA_TRY(c, cudaMemcpyAsync(hst, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
             continue;
         }
         if (to_device)
-            CUDA_TRY(c, cudaMemcpy2DAsync(s.base[p], s.pitch[p] * sb, src[p], stride[p] * sb, w * sb, h, cudaMemcpyHostToDevice, c->stream));
+            CUDA_TRY(c, cudaMemcpy2DAsync(dev, s.pitch[p] * sb, hst, stride[p] * sb, w * sb, h, cudaMemcpyHostToDevice, c->stream));
         else
-            CUDA_TRY(c, cudaMemcpy2DAsync(const_cast<void *>(src[p]), stride[p] * sb, s.base[p], s.pitch[p] * sb, w * sb, h,
-                                          cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaMemcpy2DAsync(hst, stride[p] * sb, dev, s.pitch[p] * sb, w * sb, h, cudaMemcpyDeviceToHost, c->stream));
     }
     return SVTF_OK;
 }
+// rows a stripe needs as input: its own plus 8 beyond each interior boundary
+static int in_lo(const svtf_ctx *c) { return std::max(0, c->own_lo - 8); }
+static int in_hi(const svtf_ctx *c) { return std::min(c->geom.mi_rows * 4, c->own_hi + 8); }
 
 extern "C" int svtf_upload_frame(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
     if (!c)
@@ -243,7 +324,7 @@ extern "C" int svtf_upload_frame(svtf_ctx *c, const void *y, int32_t sy, const v
     const void   *src[3] = {y, cb, cr};
     const int32_t st[3]  = {sy, scb, scr};
     c->cur = 0, c->pre_cdef = -1;
-    int r = copy_planes(c, c->surf[0], src, st, true);
+    int r = copy_planes(c, c->surf[0], src, st, true, in_lo(c), in_hi(c));
     if (r == SVTF_OK)
         c->have_frame = true;
     return r;
@@ -256,7 +337,7 @@ extern "C" int svtf_overwrite_current(svtf_ctx *c, const void *y, int32_t sy, co
         return c->fail(SVTF_E_STATE, "svtf_overwrite_current: no picture uploaded");
     const void   *src[3] = {y, cb, cr};
     const int32_t st[3]  = {sy, scb, scr};
-    return copy_planes(c, c->surf[c->cur], src, st, true);
+    return copy_planes(c, c->surf[c->cur], src, st, true, in_lo(c), in_hi(c));
 }
 
 extern "C" int svtf_upload_source(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
@@ -266,7 +347,7 @@ extern "C" int svtf_upload_source(svtf_ctx *c, const void *y, int32_t sy, const 
         return c->fail(SVTF_E_STATE, "svtf_upload_source: call svtf_frame_begin first");
     const void   *src[3] = {y, cb, cr};
     const int32_t st[3]  = {sy, scb, scr};
-    int r = copy_planes(c, c->source, src, st, true);
+    int r = copy_planes(c, c->source, src, st, true, c->own_lo, c->own_hi);
     if (r == SVTF_OK)
         c->have_source = true;
     return r;
@@ -279,6 +360,7 @@ extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) 
         return c->fail(SVTF_E_STATE, "svtf_set_mi: call svtf_frame_begin first");
     if (!mi || mi_stride < c->geom.mi_cols)
         return c->fail(SVTF_E_ARG, "svtf_set_mi: NULL grid or stride smaller than mi_cols");
+    mi += (size_t)(c->glob_row0 / 4) * mi_stride; // whole-picture grid -> this context's rows
     if (mi_stride == c->mi_stride) // same pitch: one linear DMA
         CUDA_TRY(c, cudaMemcpyAsync(c->d_mi, mi, sizeof(svtf_mi_t) * ((size_t)(c->geom.mi_rows - 1) * mi_stride + c->geom.mi_cols),
                                     cudaMemcpyHostToDevice, c->stream));
@@ -296,7 +378,7 @@ extern "C" int svtf_download_frame_async(svtf_ctx *c, void *y, int32_t sy, void 
         return c->fail(SVTF_E_STATE, "svtf_download_frame: no picture uploaded");
     const void   *dst[3] = {y, cb, cr};
     const int32_t st[3]  = {sy, scb, scr};
-    return copy_planes(c, c->surf[c->cur], dst, st, false);
+    return copy_planes(c, c->surf[c->cur], dst, st, false, c->own_lo, c->own_hi);
 }
 
 extern "C" int svtf_download_frame(svtf_ctx *c, void *y, int32_t sy, void *cb, int32_t scb, void *cr, int32_t scr) {
@@ -366,10 +448,16 @@ extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t
     a.mi_stride = c->mi_stride;
     a.d         = dims_of(c->geom);
     int total   = 0;
+    // rows to produce: the stripe's own plus the 8 beyond each interior boundary that its CDEF/CCSO read (tile t
+    // of a plane writes rows [64t-8, 64t+56) of that plane)
+    const int rows = c->geom.mi_rows * 4;
+    const int dlo = c->own_lo > 0 ? c->own_lo - 8 : 0, dhi = c->own_hi < rows ? c->own_hi + 8 : rows;
     for (int p = 0; p < 3; p++) {
-        const int w = (c->geom.mi_cols * 4) >> (p ? 1 : 0), h = (c->geom.mi_rows * 4) >> (p ? 1 : 0);
+        const int ss = p ? 1 : 0;
+        const int w = (c->geom.mi_cols * 4) >> ss;
         a.tiles_x[p]   = (w + 8 + DBK_TILE - 1) / DBK_TILE;
-        a.tiles_y[p]   = (h + 8 + DBK_TILE - 1) / DBK_TILE;
+        a.ty0[p]       = ((dlo >> ss) + 8) / DBK_TILE;
+        a.tiles_y[p]   = ((dhi >> ss) - 1 + 8) / DBK_TILE + 1 - a.ty0[p];
         a.tile_base[p] = total;
         total += a.tiles_x[p] * a.tiles_y[p];
     }
@@ -396,45 +484,98 @@ static int ccso_check(svtf_ctx *c, const svtf_ccso_params *cc, const char *who) 
     return SVTF_OK;
 }
 
-static int ccso_stage(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3], CcsoFuse &f) {
+// ---- parameter staging: host slot -> one DMA ---------------------------------------------------------
+static int params_open(svtf_ctx *c) {
+    if (c->popen)
+        return SVTF_OK;
+    svtf_ctx::ParamSlot &sl = c->pslot[c->pcur];
+    if (sl.pending) { // the DMA that last read this slot (two chains ago) must be done before it is rewritten
+        CUDA_TRY(c, cudaEventSynchronize(sl.ev));
+        sl.pending = false;
+    }
+    c->popen = true, c->plo = c->psize, c->phi = 0;
+    return SVTF_OK;
+}
+static void params_put(svtf_ctx *c, size_t off, const void *src, size_t n) {
+    memcpy(c->pslot[c->pcur].h + off, src, n);
+    c->plo = std::min(c->plo, off), c->phi = std::max(c->phi, off + n);
+}
+static int params_flush(svtf_ctx *c) {
+    if (!c->popen)
+        return SVTF_OK;
+    svtf_ctx::ParamSlot &sl = c->pslot[c->pcur];
+    c->popen = false;
+    if (c->phi > c->plo) {
+        CUDA_TRY(c, cudaMemcpyAsync(c->d_params + c->plo, sl.h + c->plo, c->phi - c->plo, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(c, cudaEventRecord(sl.ev, c->stream));
+        sl.pending = true;
+        c->pcur ^= 1;
+    }
+    return SVTF_OK;
+}
+
+static int ccso_nblocks(const svtf_ctx *c, int p) {
+    const int pw = c->full.width >> (p ? 1 : 0), ph = c->full.height >> (p ? 1 : 0), bl = p ? 7 : 8;
+    return ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl);
+}
+static void ccso_put(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
+    params_put(c, c->poff_lut, cc->filter_offset, 3 * SVTF_CCSO_LUT_SIZE);
+    for (int p = 0; p < 3; p++)
+        if (blk_flags && blk_flags[p])
+            params_put(c, c->poff_flags + (size_t)p * c->max_ccso_blocks, blk_flags[p], ccso_nblocks(c, p));
+}
+static void ccso_fill(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3], CcsoFuse &f) {
     static const uint8_t quant_sz[4] = {16, 8, 32, 64}; // Common/Codec/EbCcso.c:636
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_ccso_lut, cc->filter_offset, 3 * SVTF_CCSO_LUT_SIZE, cudaMemcpyHostToDevice, c->stream));
     for (int p = 0; p < 3; p++) {
         f.enable[p] = cc->ccso_enable[p] != 0, f.bo_only[p] = cc->ccso_bo_only[p] != 0;
         f.thr[p] = quant_sz[cc->quant_idx[p]], f.support[p] = cc->ext_filter_support[p];
         f.edge_clf[p] = cc->edge_clf[p], f.band_log2[p] = cc->max_band_log2[p];
-        f.blk_flags[p] = nullptr;
-        if (blk_flags && blk_flags[p]) {
-            const int pw = c->geom.width >> (p ? 1 : 0), ph = c->geom.height >> (p ? 1 : 0), bl = p ? 7 : 8;
-            const int n  = ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl);
-            uint8_t  *d  = c->d_ccso_flags + (size_t)p * c->max_ccso_blocks;
-            CUDA_TRY(c, cudaMemcpyAsync(d, blk_flags[p], n, cudaMemcpyHostToDevice, c->stream));
-            f.blk_flags[p] = d;
-        }
+        f.blk_flags[p] = (blk_flags && blk_flags[p]) ? c->d_ccso_flags + (size_t)p * c->max_ccso_blocks : nullptr;
     }
-    f.lut = c->d_ccso_lut;
-    f.on  = 1;
+    f.lut    = c->d_ccso_lut;
+    f.on     = 1;
+    f.y_glob = c->glob_row0;
+}
+// whole-picture per-filter-block array -> the rows this context holds
+static const int8_t *fb_local(const svtf_ctx *c, const int8_t *fb_strength_idx) {
+    return fb_strength_idx + (size_t)(c->glob_row0 / 64) * ((c->geom.mi_cols + 15) / 16);
+}
+static int fb_idx_check(svtf_ctx *c, const int8_t *fb_strength_idx) {
+    const int nfb = ((c->geom.mi_rows + 15) / 16) * ((c->geom.mi_cols + 15) / 16);
+    fb_strength_idx = fb_local(c, fb_strength_idx);
+    for (int i = 0; i < nfb; i++)
+        if (fb_strength_idx[i] >= SVTF_CDEF_MAX_STRENGTHS)
+            return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: strength index out of range");
     return SVTF_OK;
 }
 
 // CDEF apply; with `cc` the CCSO pass of the same picture runs in the kernel's epilogue (one launch, one write).
 static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t *fb_strength_idx, const svtf_ccso_params *cc,
-                           const uint8_t *const blk_flags[3], const char *who) {
+                           const uint8_t *const blk_flags[3], const char *who, bool staged) {
     if (int r = need_frame_mi(c, who))
         return r;
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16;
-    for (int i = 0; i < nvfb * nhfb; i++)
-        if (fb_strength_idx[i] >= SVTF_CDEF_MAX_STRENGTHS)
-            return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: strength index out of range");
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_fb_idx, fb_strength_idx, (size_t)nvfb * nhfb, cudaMemcpyHostToDevice, c->stream));
-    const int nxt = next_surface(c);
-    dim3      grid(nhfb, nvfb);
+    if (!staged) {
+        if (int r = fb_idx_check(c, fb_strength_idx))
+            return r;
+        if (int r = params_open(c))
+            return r;
+        params_put(c, 0, fb_local(c, fb_strength_idx), (size_t)nvfb * nhfb);
+        if (cc)
+            ccso_put(c, cc, blk_flags);
+        if (int r = params_flush(c))
+            return r;
+    }
+    const int nxt  = next_surface(c);
+    const int fbr0 = c->own_lo / 64;
+    dim3      grid(nhfb, (c->own_hi + 63) / 64 - fbr0);
+    (void)nvfb;
     static const bool use_v1 = getenv("SVTF_CDEF_SCALAR") != nullptr; // A/B switch: the round-1 scalar kernel
     if (use_v1 && !cc) {
         CdefArgs a;
         a.in = c->surf[c->cur].planes(), a.out = c->surf[nxt].planes();
-        a.mi = c->d_mi, a.mi_stride = c->mi_stride, a.d = dims_of(c->geom), a.fb_idx = c->d_fb_idx, a.damping = cp->cdef_damping;
+        a.mi = c->d_mi, a.mi_stride = c->mi_stride, a.d = dims_of(c->geom), a.fb_idx = c->d_fb_idx, a.fbr0 = fbr0, a.damping = cp->cdef_damping;
         memcpy(a.y_strength, cp->cdef_y_strength, sizeof(a.y_strength));
         memcpy(a.uv_strength, cp->cdef_uv_strength, sizeof(a.uv_strength));
         if (c->geom.sample_bytes == 1)
@@ -444,13 +585,12 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
     } else {
         Cdef2Args b;
         b.in = c->surf[c->cur].planes(), b.out = c->surf[nxt].planes();
-        b.mi = c->d_mi, b.mi_stride = c->mi_stride, b.d = dims_of(c->geom), b.fb_idx = c->d_fb_idx, b.damping = cp->cdef_damping;
+        b.mi = c->d_mi, b.mi_stride = c->mi_stride, b.d = dims_of(c->geom), b.fb_idx = c->d_fb_idx, b.fbr0 = fbr0, b.damping = cp->cdef_damping;
         memcpy(b.y_strength, cp->cdef_y_strength, sizeof(b.y_strength));
         memcpy(b.uv_strength, cp->cdef_uv_strength, sizeof(b.uv_strength));
         memset(&b.ccso, 0, sizeof(b.ccso));
         if (cc)
-            if (int r = ccso_stage(c, cc, blk_flags, b.ccso))
-                return r;
+            ccso_fill(c, cc, blk_flags, b.ccso);
         if (c->geom.sample_bytes == 1)
             cdef2_kernel<uint8_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
         else
@@ -468,14 +608,10 @@ extern "C" int svtf_cdef_apply_frame(svtf_ctx *c, const svtf_cdef_params *cp, co
         return set_global_error(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL context");
     if (!cp || !fb_strength_idx)
         return c->fail(SVTF_E_ARG, "svtf_cdef_apply_frame: NULL argument");
-    return cdef_apply_impl(c, cp, fb_strength_idx, nullptr, nullptr, "svtf_cdef_apply_frame");
+    return cdef_apply_impl(c, cp, fb_strength_idx, nullptr, nullptr, "svtf_cdef_apply_frame", false);
 }
 
-extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL context");
-    if (!cc)
-        return c->fail(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL argument");
+static int ccso_apply_impl(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3], bool staged) {
     if (!c->have_frame)
         return c->fail(SVTF_E_STATE, "svtf_ccso_apply_frame: no picture uploaded");
     if (int r = ccso_check(c, cc, "svtf_ccso_apply_frame"))
@@ -483,15 +619,22 @@ extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, co
     if (!(cc->ccso_enable[0] | cc->ccso_enable[1] | cc->ccso_enable[2]))
         return SVTF_OK;
     CUDA_TRY(c, cudaSetDevice(c->device));
+    if (!staged) {
+        if (int r = params_open(c))
+            return r;
+        ccso_put(c, cc, blk_flags);
+        if (int r = params_flush(c))
+            return r;
+    }
     CcsoFuse f;
-    if (int r = ccso_stage(c, cc, blk_flags, f))
-        return r;
+    ccso_fill(c, cc, blk_flags, f);
     CcsoArgs a;
     for (int p = 0; p < 3; p++) {
         a.enable[p] = f.enable[p], a.bo_only[p] = f.bo_only[p], a.thr[p] = f.thr[p], a.support[p] = f.support[p];
         a.edge_clf[p] = f.edge_clf[p], a.band_log2[p] = f.band_log2[p], a.blk_flags[p] = f.blk_flags[p];
     }
     a.lut = f.lut;
+    a.ty0 = c->own_lo / 64, a.y_glob = c->glob_row0;
     a.d   = dims_of(c->geom);
     a.in  = c->surf[c->cur].planes();
     int nxt = c->cur;
@@ -503,7 +646,7 @@ extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, co
         a.luma_src = a.in;
         a.out      = c->surf[nxt].planes();
     }
-    dim3 grid((c->geom.mi_cols * 4 + 63) / 64, (c->geom.mi_rows * 4 + 63) / 64);
+    dim3 grid((c->geom.mi_cols * 4 + 63) / 64, (c->own_hi + 63) / 64 - a.ty0);
     if (c->geom.sample_bytes == 1)
         ccso_kernel<uint8_t><<<grid, CCSO_THREADS, 0, c->stream>>>(a);
     else
@@ -514,28 +657,53 @@ extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, co
     return SVTF_OK;
 }
 
-// Deblock -> CDEF -> CCSO on the uploaded picture.  CDEF and CCSO of the same picture run as ONE kernel (the CCSO
-// classifier input is the pre-CDEF luma tile the CDEF kernel already holds in shared memory); SVTF_CHAIN_UNFUSED=1
-// keeps them as separate launches for A/B measurements.
+extern "C" int svtf_ccso_apply_frame(svtf_ctx *c, const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL context");
+    if (!cc)
+        return c->fail(SVTF_E_ARG, "svtf_ccso_apply_frame: NULL argument");
+    return ccso_apply_impl(c, cc, blk_flags, false);
+}
+
+// Deblock -> CDEF -> CCSO on the uploaded picture.  All small parameters go to the device in one DMA ahead of the
+// first kernel.  CDEF and CCSO of the same picture run as ONE kernel (the CCSO classifier input is the pre-CDEF luma
+// tile the CDEF kernel already holds in shared memory); SVTF_CHAIN_UNFUSED=1 keeps them as separate launches for
+// A/B measurements.
 extern "C" int svtf_filter_chain(svtf_ctx *c, const svtf_lf_params *lf, const svtf_cdef_params *cdef, const int8_t *fb_strength_idx,
                                  const svtf_ccso_params *ccso, const uint8_t *const blk_flags[3]) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_filter_chain: NULL context");
     if (cdef && !fb_strength_idx)
         return c->fail(SVTF_E_ARG, "svtf_filter_chain: CDEF needs fb_strength_idx");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_filter_chain: no picture uploaded");
     int r = SVTF_OK;
-    if (lf && (r = svtf_deblock_frame(c, lf, 0, 3)) != SVTF_OK)
-        return r;
     static const bool unfused = getenv("SVTF_CHAIN_UNFUSED") != nullptr || getenv("SVTF_CDEF_SCALAR") != nullptr;
     const bool        ccso_on = ccso && (ccso->ccso_enable[0] | ccso->ccso_enable[1] | ccso->ccso_enable[2]);
-    if (cdef && ccso_on && !unfused) {
-        if ((r = ccso_check(c, ccso, "svtf_filter_chain")) != SVTF_OK)
-            return r;
-        return cdef_apply_impl(c, cdef, fb_strength_idx, ccso, blk_flags, "svtf_filter_chain");
-    }
-    if (cdef && (r = svtf_cdef_apply_frame(c, cdef, fb_strength_idx)) != SVTF_OK)
+    if (ccso && (r = ccso_check(c, ccso, "svtf_filter_chain")) != SVTF_OK)
         return r;
-    if (ccso && (r = svtf_ccso_apply_frame(c, ccso, blk_flags)) != SVTF_OK)
+    if ((lf || cdef) && (r = need_frame_mi(c, "svtf_filter_chain")) != SVTF_OK)
+        return r;
+    if (cdef && (r = fb_idx_check(c, fb_strength_idx)) != SVTF_OK)
+        return r;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (cdef || ccso_on) {
+        if ((r = params_open(c)) != SVTF_OK)
+            return r;
+        if (cdef)
+            params_put(c, 0, fb_local(c, fb_strength_idx), (size_t)((c->geom.mi_rows + 15) / 16) * ((c->geom.mi_cols + 15) / 16));
+        if (ccso_on)
+            ccso_put(c, ccso, blk_flags);
+        if ((r = params_flush(c)) != SVTF_OK)
+            return r;
+    }
+    if (lf && (r = svtf_deblock_frame(c, lf, 0, 3)) != SVTF_OK)
+        return r;
+    if (cdef && ccso_on && !unfused)
+        return cdef_apply_impl(c, cdef, fb_strength_idx, ccso, blk_flags, "svtf_filter_chain", true);
+    if (cdef && (r = cdef_apply_impl(c, cdef, fb_strength_idx, nullptr, nullptr, "svtf_filter_chain", true)) != SVTF_OK)
+        return r;
+    if (ccso_on && (r = ccso_apply_impl(c, ccso, blk_flags, true)) != SVTF_OK)
         return r;
     return r;
 }
@@ -586,11 +754,12 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
     a.damping = 3 + (cfg->base_q_idx >> 6);
     a.subsampling = cfg->subsampling_factor;
     a.mse = c->d_mse, a.skip = c->d_skip, a.dir = c->d_dir, a.var = c->d_var;
-    a.nfb = nfb;
+    a.nfb  = nfb;
+    a.fbr0 = c->own_lo / 64;
     CUDA_TRY(c, cudaMemsetAsync(c->d_dir, 0, 64 * (size_t)nfb, c->stream));
     CUDA_TRY(c, cudaMemsetAsync(c->d_var, 0, sizeof(int32_t) * 64 * (size_t)nfb, c->stream));
     CUDA_TRY(c, cudaMemsetAsync(c->d_mse, 0, sizeof(uint64_t) * 128 * (size_t)nfb, c->stream));
-    dim3 grid(nhfb, nvfb);
+    dim3 grid(nhfb, (c->own_hi + 63) / 64 - a.fbr0);
     if (c->geom.sample_bytes == 1)
         cdef_search_kernel<uint8_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
     else
@@ -598,10 +767,17 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
     c->have_search = true;
-    if (mse) CUDA_TRY(c, cudaMemcpyAsync(mse, c->d_mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
-    if (skip) CUDA_TRY(c, cudaMemcpyAsync(skip, c->d_skip, nfb, cudaMemcpyDeviceToHost, c->stream));
-    if (dir) CUDA_TRY(c, cudaMemcpyAsync(dir, c->d_dir, 64 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
-    if (var) CUDA_TRY(c, cudaMemcpyAsync(var, c->d_var, sizeof(int32_t) * 64 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
+    // outputs are WHOLE-PICTURE arrays; this context fills the filter-block rows it owns
+    const size_t l0 = (size_t)a.fbr0 * nhfb, ln = (size_t)grid.y * nhfb;           // local first fb, count
+    const size_t g0 = l0 + (size_t)(c->glob_row0 / 64) * nhfb;                      // same fb in the picture
+    const size_t nfb_full = (size_t)((c->full.mi_rows + 15) / 16) * nhfb;
+    if (mse)
+        for (int pl = 0; pl < 2; pl++)
+            CUDA_TRY(c, cudaMemcpyAsync(mse + ((size_t)pl * nfb_full + g0) * 64, c->d_mse + ((size_t)pl * nfb + l0) * 64, sizeof(uint64_t) * 64 * ln,
+                                        cudaMemcpyDeviceToHost, c->stream));
+    if (skip) CUDA_TRY(c, cudaMemcpyAsync(skip + g0, c->d_skip + l0, ln, cudaMemcpyDeviceToHost, c->stream));
+    if (dir) CUDA_TRY(c, cudaMemcpyAsync(dir + g0 * 64, c->d_dir + l0 * 64, 64 * ln, cudaMemcpyDeviceToHost, c->stream));
+    if (var) CUDA_TRY(c, cudaMemcpyAsync(var + g0 * 64, c->d_var + l0 * 64, sizeof(int32_t) * 64 * ln, cudaMemcpyDeviceToHost, c->stream));
     if (mse || skip || dir || var)
         CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return SVTF_OK;
@@ -614,6 +790,8 @@ extern "C" int svtf_cdef_pick(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, svtf
         return c->fail(SVTF_E_ARG, "svtf_cdef_pick: NULL argument");
     if (!c->have_search)
         return c->fail(SVTF_E_STATE, "svtf_cdef_pick: run svtf_cdef_search_frame first");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_cdef_pick: this context holds one stripe; gather mse/skip and call svtf_cdef_pick_host");
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
     std::vector<uint64_t> mse((size_t)128 * nfb);

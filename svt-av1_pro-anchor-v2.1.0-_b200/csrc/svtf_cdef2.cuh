@@ -33,6 +33,7 @@ struct CcsoFuse {
     const int8_t  *lut;          // device [3][2048]
     const uint8_t *blk_flags[3]; // device or NULL
     uint8_t        enable[3], bo_only[3], thr[3], support[3], edge_clf[3], band_log2[3];
+    int            y_glob; // picture row of local row 0 (block flags are indexed in picture coordinates)
 };
 
 struct Cdef2Args {
@@ -41,6 +42,7 @@ struct Cdef2Args {
     int              mi_stride;
     Dims             d;
     const int8_t    *fb_idx;
+    int              fbr0; // first filter-block row of the launch (stripe window)
     int              damping;
     uint8_t          y_strength[SVTF_CDEF_MAX_STRENGTHS], uv_strength[SVTF_CDEF_MAX_STRENGTHS];
     CcsoFuse         ccso;
@@ -274,7 +276,7 @@ __global__ void __launch_bounds__(C2_THREADS, 3) cdef2_kernel(const __grid_const
     __shared__ uint8_t                s_lut[3][SVTF_CCSO_LUT_SIZE]; // CCSO offsets + 128
 
     const int tid = threadIdx.x;
-    const int fbc = blockIdx.x, fbr = blockIdx.y;
+    const int fbc = blockIdx.x, fbr = blockIdx.y + a.fbr0;
     const int nhfb = gridDim.x;
     const int cw = a.d.mi_cols * 4, ch = a.d.mi_rows * 4;
     const int x0 = fbc * 64, y0 = fbr * 64;
@@ -308,7 +310,7 @@ __global__ void __launch_bounds__(C2_THREADS, 3) cdef2_kernel(const __grid_const
         if (on && a.ccso.blk_flags[p]) { // one flag per 256x256 luma samples, row length = ceil(plane width / block)
             const int pwid = W >> (p ? 1 : 0), bl = p ? 7 : 8;
             const int nbx  = (pwid + (1 << bl) - 1) >> bl;
-            on             = (x0 >> 8) < nbx && a.ccso.blk_flags[p][(y0 >> 8) * nbx + (x0 >> 8)] != 0;
+            on             = (x0 >> 8) < nbx && a.ccso.blk_flags[p][((y0 + a.ccso.y_glob) >> 8) * nbx + (x0 >> 8)] != 0;
         }
         q_on |= (int)on << p;
     }

@@ -106,6 +106,7 @@ struct DeblockArgs {
     int              mi_stride;
     Dims             d;
     int              tiles_x[3], tiles_y[3], tile_base[3]; // linearised (plane, ty, tx) grid
+    int              ty0[3];                               // first tile row of the launch (stripe window)
     unsigned         plane_mask;                           // bit p: plane p is filtered (else copied)
     LfTables         t;
 };
@@ -234,7 +235,8 @@ __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_const
     const int bid   = blockIdx.x;
     const int plane = bid >= a.tile_base[2] ? 2 : (bid >= a.tile_base[1] ? 1 : 0);
     const int lb    = bid - a.tile_base[plane];
-    const int ty = lb / a.tiles_x[plane], tx = lb - ty * a.tiles_x[plane];
+    const int tyl = lb / a.tiles_x[plane], tx = lb - tyl * a.tiles_x[plane];
+    const int ty  = tyl + a.ty0[plane];
     const int ss = plane ? 1 : 0;
     const int cw = (a.d.mi_cols * 4) >> ss, ch = (a.d.mi_rows * 4) >> ss;
     const int pw = a.d.width >> ss, ph = a.d.height >> ss;
@@ -325,6 +327,7 @@ struct CdefArgs {
     int              mi_stride;
     Dims             d;
     const int8_t    *fb_idx; // [nvfb*nhfb]
+    int              fbr0;   // first filter-block row of the launch (stripe window)
     int              damping;
     uint8_t          y_strength[SVTF_CDEF_MAX_STRENGTHS], uv_strength[SVTF_CDEF_MAX_STRENGTHS];
 };
@@ -446,7 +449,7 @@ __global__ void __launch_bounds__(CDEF_THREADS) cdef_kernel(const __grid_constan
     __shared__ uint8_t                s_active[64];
 
     const int tid = threadIdx.x;
-    const int fbc = blockIdx.x, fbr = blockIdx.y;
+    const int fbc = blockIdx.x, fbr = blockIdx.y + a.fbr0;
     const int nhfb = gridDim.x;
     const int cw = a.d.mi_cols * 4, ch = a.d.mi_rows * 4;
     const int x0 = fbc * 64, y0 = fbr * 64;
@@ -620,6 +623,8 @@ struct CcsoArgs {
     const int8_t *lut;                 // device: [3][2048]
     const uint8_t *blk_flags[3];       // device or NULL (all on)
     uint8_t       enable[3], bo_only[3], thr[3], support[3], edge_clf[3], band_log2[3];
+    int           ty0;    // first 64-row tile row of the launch (stripe window)
+    int           y_glob; // picture row of local row 0 (block flags are indexed in picture coordinates)
 };
 
 // ccso_filter_block_hbd_wo_buf_c — Common/Codec/EbCcso.c:261-294 (classification cal_filter_support :238-259,
@@ -652,7 +657,7 @@ __global__ void __launch_bounds__(CCSO_THREADS) ccso_kernel(const __grid_constan
     __shared__ int8_t                 s_lut[3][SVTF_CCSO_LUT_SIZE];
 
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
+    const int x0 = blockIdx.x * 64, y0 = (blockIdx.y + a.ty0) * 64;
     const int W = a.d.width, H = a.d.height;
     const int cw = a.d.mi_cols * 4, ch = a.d.mi_rows * 4;
     const int max_val = (1 << a.d.bit_depth) - 1;
@@ -665,7 +670,7 @@ __global__ void __launch_bounds__(CCSO_THREADS) ccso_kernel(const __grid_constan
         if (on[p] && a.blk_flags[p]) {
             const int pwid = W >> (p ? 1 : 0), bl = p ? 7 : 8;
             const int nbx  = (pwid + (1 << bl) - 1) >> bl;
-            on[p]          = (x0 >> 8) < nbx && a.blk_flags[p][(y0 >> 8) * nbx + (x0 >> 8)] != 0;
+            on[p]          = (x0 >> 8) < nbx && a.blk_flags[p][((y0 + a.y_glob) >> 8) * nbx + (x0 >> 8)] != 0;
         }
     }
     const bool inplace = a.in.p[0] == a.out.p[0];

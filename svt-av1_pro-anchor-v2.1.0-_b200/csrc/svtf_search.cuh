@@ -32,6 +32,7 @@ struct SearchArgs {
     uint8_t         *dir;  // [nfb][64]
     int32_t         *var;  // [nfb][64]
     int              nfb;
+    int              fbr0; // first filter-block row of the launch (stripe window)
 };
 
 // dist_8xn_16bit_c / dist_8xn_8bit_c — Encoder/Codec/EbEncCdef.c:23-48, :76-101
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS) cdef_search_kernel(const __gri
     __shared__ unsigned long long     s_acc[3][SVTF_TOTAL_STRENGTHS];
 
     const int tid = threadIdx.x;
-    const int fbc = blockIdx.x, fbr = blockIdx.y;
+    const int fbc = blockIdx.x, fbr = blockIdx.y + a.fbr0;
     const int fb  = fbr * gridDim.x + fbc;
     const int cw = a.d.mi_cols * 4, ch = a.d.mi_rows * 4;
     const int x0 = fbc * 64, y0 = fbr * 64;

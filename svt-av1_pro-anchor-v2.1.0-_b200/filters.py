@@ -35,6 +35,11 @@ def make_geom(width, height, bit_depth, sample_bytes=None):
     return L.Geom(width, height, 2 * ((width + 7) // 8), 2 * ((height + 7) // 8), bit_depth, sample_bytes)
 
 
+def make_geom_coded(width, height, mi_cols, mi_rows, bit_depth, sample_bytes):
+    """Geometry with an explicit coded size (stripes: the coded rows are whole superblock rows)."""
+    return L.Geom(width, height, mi_cols, mi_rows, bit_depth, sample_bytes)
+
+
 def lf_params(filter_level=(0, 0), filter_level_u=0, filter_level_v=0, sharpness_level=0, mode_ref_delta_enabled=0,
               ref_deltas=(1, 0, 0, 0, -1, 0, -1, -1), mode_deltas=(0, 0), segmentation_enabled=0, seg_feature_enabled=None,
               seg_feature_data=None, delta_lf_present=0, delta_lf_multi=0, curr_delta_lf=(0, 0, 0, 0)):
@@ -207,6 +212,12 @@ class FilterContext:
         self.geom = geom
         self._chk(self._lib.svtf_frame_begin(self._h, C.byref(geom)))
 
+    def begin_stripe(self, full_geom, first_sb_row, num_sb_rows):
+        """This context filters superblock rows [first, first+num) of a picture (svtf_stripe_begin).  All later calls
+        keep taking whole-picture arrays; only the stripe's part of them is read or written."""
+        self.geom = full_geom
+        self._chk(self._lib.svtf_stripe_begin(self._h, C.byref(full_geom), first_sb_row, num_sb_rows))
+
     def _planes_args(self, planes):
         args = []
         for a in planes:
@@ -230,7 +241,7 @@ class FilterContext:
         g = self.geom
         if out is None:
             dt = np.uint8 if g.sample_bytes == 1 else np.uint16
-            out = [np.empty(((g.mi_rows * 4) >> s, (g.mi_cols * 4) >> s), dtype=dt) for s in (0, 1, 1)]
+            out = [np.zeros(((g.mi_rows * 4) >> s, (g.mi_cols * 4) >> s), dtype=dt) for s in (0, 1, 1)]
         self._chk(self._lib.svtf_download_frame(self._h, *self._planes_args(out)))
         return out
 
@@ -283,16 +294,20 @@ class FilterContext:
         self._chk(self._lib.svtf_filter_chain(self._h, None if lf is None else C.byref(lf), None if cdef is None else C.byref(cdef),
                                               _ptr(idx), None if ccso is None else C.byref(ccso), arr))
 
-    def cdef_seg_search(self, cfg, want_outputs=True):
+    def cdef_seg_search(self, cfg, want_outputs=True, out=None):
+        """out: optional (mse, skip, dirs, var) whole-picture arrays to fill (a striped context fills its rows)."""
         g = self.geom
         nfb = ((g.mi_rows + 15) // 16) * ((g.mi_cols + 15) // 16)
         if not want_outputs:
             self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), None, None, None, None))
             return None
-        mse = np.zeros((2, nfb, 64), dtype=np.uint64)
-        skip = np.zeros(nfb, dtype=np.uint8)
-        dirs = np.zeros((nfb, 64), dtype=np.uint8)
-        var = np.zeros((nfb, 64), dtype=np.int32)
+        if out is not None:
+            mse, skip, dirs, var = out
+        else:
+            mse = np.zeros((2, nfb, 64), dtype=np.uint64)
+            skip = np.zeros(nfb, dtype=np.uint8)
+            dirs = np.zeros((nfb, 64), dtype=np.uint8)
+            var = np.zeros((nfb, 64), dtype=np.int32)
         self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), _ptr(dirs), _ptr(var)))
         return mse, skip, dirs, var
 

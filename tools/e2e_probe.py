@@ -44,7 +44,8 @@ def main():
 
     def submit(k, mode):
         c = ctxs[k]
-        c.begin(g)
+        if mode in ("up", "up+down", "full"):
+            c.begin(g)  # (resets the mi grid: the no-mi variants keep the one set at start-up)
         c.upload(pin_in[k].planes)
         if mode in ("full", "full-nomi"):
             if mode == "full":
@@ -57,7 +58,7 @@ def main():
             c._chk(L.svtf_download_frame_async(c._h, *c._planes_args(pin_out[k].planes)))
 
     out = {}
-    for mode in ("up", "up+down", "kern", "full-nomi", "full"):
+    for mode in ("kern", "full-nomi", "up", "up+down", "full"):
         for rep in range(reps + 2):
             if rep == 2:
                 t0 = time.perf_counter()
