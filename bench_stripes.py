@@ -100,7 +100,7 @@ def main():
         whole = [np.zeros_like(p) for p in rec]
     if dist is not None:
         for p in range(3):
-            t = torch.from_numpy(whole[p].view(np.int16)).to(dev)
+            t = torch.from_numpy(whole[p].view(np.uint8)).to(dev)
             dist.broadcast(t, 0)
             whole[p] = t.cpu().numpy().view(np.uint16)
     same = all(np.array_equal(out[p][r0 >> s:r1 >> s], whole[p][r0 >> s:r1 >> s]) for p, s in ((0, 0), (1, 1), (2, 1)))
@@ -195,7 +195,7 @@ def main():
         def search_step():
             c.cdef_seg_search(cfg, out=bufs)
             m, s = S.stripes.gather_search(bufs[0], bufs[1], g, parts, rank, dist, dev)
-            return S.cdef_pick_host(cfg, m, s)
+            return c.pick_table(cfg, m, s)
 
         for _ in range(2):
             pick = search_step()

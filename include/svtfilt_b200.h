@@ -175,7 +175,7 @@ int svtf_frame_begin(svtf_ctx *ctx, const svtf_geom *geom);
  * sides (the reference's serial raster order, Encoder/Codec/EbDeblockingFilter.c:624-660, has no such boundary); no
  * inter-GPU exchange is needed when the input comes from the host.  max_geom must cover the stripe plus up to two
  * superblock rows of context.  svtf_cdef_pick is not available on a striped context: gather mse/skip and call
- * svtf_cdef_pick_host. */
+ * svtf_cdef_pick_table (GPU) or svtf_cdef_pick_host. */
 int svtf_stripe_begin(svtf_ctx *ctx, const svtf_geom *full_geom, int32_t first_sb_row, int32_t num_sb_rows);
 
 /* Host -> device copy of the reconstructed picture (the `frame_buffer` / recon_pic argument of
@@ -235,10 +235,16 @@ int svtf_cdef_search_frame(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, uint6
                            uint8_t *dir, int32_t *var);
 /* finish_cdef_search(pcs) (Encoder/Codec/EbEncCdef.c:728) on the table left on the device by
  * svtf_cdef_search_frame: picks cdef_bits, the strength pairs and the per-fb index.
- * fb_strength_idx: nfb entries, -1 for fbs the search skipped. */
+ * fb_strength_idx: nfb entries, -1 for fbs the search skipped.  Runs on the GPU: the 75 svt_search_one_dual passes
+ * (Encoder/Codec/EbEncCdef.c:627-727) are enqueued back to back, the greedy lists stay in device memory. */
 int svtf_cdef_pick(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, svtf_cdef_params *out_params,
                    int8_t *fb_strength_idx);
-/* Host-table variant (used by the multi-GPU stripe path after the mse allgather). */
+/* Same pick on the GPU from a caller-owned HOST table laid out like pcs->mse_seg / pcs->skip_cdef_seg (the reference's
+ * finish_cdef_search input; also the stripe path after the all-gather of the per-stripe rows).  Uploads 1 KiB per
+ * filter block, then runs as svtf_cdef_pick. */
+int svtf_cdef_pick_table(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
+                         svtf_cdef_params *out_params, int8_t *fb_strength_idx);
+/* Pure host implementation of the same pick (single thread, as the reference runs it); no context needed. */
 int svtf_cdef_pick_host(const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
                         svtf_cdef_params *out_params, int8_t *fb_strength_idx);
 

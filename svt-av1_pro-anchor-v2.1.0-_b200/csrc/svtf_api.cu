@@ -13,6 +13,8 @@
 
 #include "svtf_kernels.cuh"
 #include "svtf_search.cuh"
+#include "svtf_search2_kernel.cuh"
+#include "svtf_pick.cuh"
 #include "svtf_cdef2.cuh"
 
 namespace svtf {
@@ -81,6 +83,14 @@ struct svtf_ctx {
     uint8_t     *d_dir = nullptr;  // [nfb][64]
     int32_t     *d_var = nullptr;  // [nfb][64]
     int          max_nfb = 0;
+    // device-side pick (svtf_pick.cuh)
+    PickState   *d_pick_state = nullptr;
+    uint64_t    *d_pick_tot = nullptr;   // [64*64]
+    int8_t      *d_pick_idx = nullptr;   // [pick_cap]
+    uint64_t    *d_tab_mse = nullptr;    // table uploaded by svtf_cdef_pick_table, [2][pick_cap][64]
+    uint8_t     *d_tab_skip = nullptr;
+    int          pick_cap = 0, tab_cap = 0;
+    int          sm_count = 0;
     uint64_t     launches = 0;
     std::string  err;
 
@@ -176,6 +186,9 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
     if ((e = cudaMalloc(&c->d_skip, c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(skip)");
     if ((e = cudaMalloc(&c->d_dir, 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(dir)");
     if ((e = cudaMalloc(&c->d_var, sizeof(int32_t) * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(var)");
+    if ((e = cudaMalloc(&c->d_pick_state, sizeof(PickState))) != cudaSuccess) return bail(e, "cudaMalloc(pick state)");
+    if ((e = cudaMalloc(&c->d_pick_tot, sizeof(uint64_t) * 64 * 64)) != cudaSuccess) return bail(e, "cudaMalloc(pick tot)");
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
     *out = c;
     return SVTF_OK;
 }
@@ -195,6 +208,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
         if (sl.ev) cudaEventDestroy(sl.ev);
     }
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
+    cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
     if (c->own_stream)
         cudaStreamDestroy(c->own_stream);
     delete c;
@@ -760,10 +774,27 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
     CUDA_TRY(c, cudaMemsetAsync(c->d_var, 0, sizeof(int32_t) * 64 * (size_t)nfb, c->stream));
     CUDA_TRY(c, cudaMemsetAsync(c->d_mse, 0, sizeof(uint64_t) * 128 * (size_t)nfb, c->stream));
     dim3 grid(nhfb, (c->own_hi + 63) / 64 - a.fbr0);
-    if (c->geom.sample_bytes == 1)
-        cdef_search_kernel<uint8_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
-    else
-        cdef_search_kernel<uint16_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
+    // 8/10-bit: separable packed kernel (svtf_search2.cuh); 12-bit (filtered-minus-input does not fit int8) and the
+    // SVTF_SEARCH_SCALAR=1 A/B switch: the direct per-strength kernel
+    static const bool scalar = getenv("SVTF_SEARCH_SCALAR") != nullptr;
+    if (scalar || c->geom.bit_depth > 10) {
+        if (c->geom.sample_bytes == 1)
+            cdef_search_kernel<uint8_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
+        else
+            cdef_search_kernel<uint16_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
+    } else {
+        Search2Args b;
+        b.s = a, b.present_y = 0, b.present_uv = 0;
+        for (int gi = 0; gi < n; gi++) {
+            b.present_y |= 1ull << (a.fs[gi] & 63);
+            if (a.fs_uv[gi] != -1)
+                b.present_uv |= 1ull << (a.fs[gi] & 63);
+        }
+        if (c->geom.sample_bytes == 1)
+            cdef_search2_kernel<uint8_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
+        else
+            cdef_search2_kernel<uint16_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
+    }
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
     c->have_search = true;
@@ -783,6 +814,39 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
     return SVTF_OK;
 }
 
+// finish_cdef_search on the device (svtf_pick.cuh) over a table that is already in device memory.
+static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint64_t *d_mse, const uint8_t *d_skip, int nfb,
+                       svtf_cdef_params *out, int8_t *fb_strength_idx, const char *who) {
+    const int end_gi = cfg->first_pass_fs_num + cfg->default_second_pass_fs_num;
+    if (end_gi <= 0 || end_gi > SVTF_TOTAL_STRENGTHS || cfg->first_pass_fs_num < 0 || cfg->default_second_pass_fs_num < 0)
+        return c->fail(SVTF_E_ARG, std::string(who) + ": bad strength counts");
+    if (nfb > c->pick_cap) {
+        cudaFree(c->d_pick_idx);
+        c->d_pick_idx = nullptr, c->pick_cap = 0;
+        CUDA_TRY(c, cudaMalloc(&c->d_pick_idx, nfb));
+        c->pick_cap = nfb;
+    }
+    PickArgs a;
+    a.mse = d_mse, a.skip = d_skip, a.nfb = nfb, a.end_gi = end_gi, a.bias = cfg->zero_fs_cost_bias;
+    a.st = c->d_pick_state, a.tot = c->d_pick_tot;
+    CUDA_TRY(c, pick_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->sm_count, c->stream, &c->launches));
+    PickState st;
+    CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    memset(out, 0, sizeof(*out));
+    out->cdef_bits = st.best_bits;
+    auto map = [&](int i) { // index -> strength byte through the luma lists (Encoder/Codec/EbEncCdef.c:911-919)
+        return i < cfg->first_pass_fs_num ? cfg->default_first_pass_fs[i] : cfg->default_second_pass_fs[i - cfg->first_pass_fs_num];
+    };
+    for (int g = 0; g < (1 << st.best_bits); g++) {
+        out->cdef_y_strength[g]  = map(st.out0[g]);
+        out->cdef_uv_strength[g] = map(st.out1[g]);
+    }
+    out->cdef_damping = 3 + (cfg->base_q_idx >> 6);
+    return SVTF_OK;
+}
+
 extern "C" int svtf_cdef_pick(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, svtf_cdef_params *out_params, int8_t *fb_strength_idx) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_cdef_pick: NULL context");
@@ -791,16 +855,27 @@ extern "C" int svtf_cdef_pick(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, svtf
     if (!c->have_search)
         return c->fail(SVTF_E_STATE, "svtf_cdef_pick: run svtf_cdef_search_frame first");
     if (c->striped)
-        return c->fail(SVTF_E_STATE, "svtf_cdef_pick: this context holds one stripe; gather mse/skip and call svtf_cdef_pick_host");
+        return c->fail(SVTF_E_STATE, "svtf_cdef_pick: this context holds one stripe; gather mse/skip and call svtf_cdef_pick_table");
     CUDA_TRY(c, cudaSetDevice(c->device));
-    const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
-    std::vector<uint64_t> mse((size_t)128 * nfb);
-    std::vector<uint8_t>  skip(nfb);
-    CUDA_TRY(c, cudaMemcpyAsync(mse.data(), c->d_mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(c, cudaMemcpyAsync(skip.data(), c->d_skip, nfb, cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    int r = svtf_cdef_pick_host(cfg, mse.data(), skip.data(), nfb, out_params, fb_strength_idx);
-    if (r != SVTF_OK)
-        c->err = svtf_last_error(nullptr);
-    return r;
+    const int nfb = ((c->geom.mi_rows + 15) / 16) * ((c->geom.mi_cols + 15) / 16);
+    return pick_device(c, cfg, c->d_mse, c->d_skip, nfb, out_params, fb_strength_idx, "svtf_cdef_pick");
+}
+
+extern "C" int svtf_cdef_pick_table(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
+                                    svtf_cdef_params *out_params, int8_t *fb_strength_idx) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_cdef_pick_table: NULL context");
+    if (!cfg || !mse || !skip || !out_params || !fb_strength_idx || nfb <= 0)
+        return c->fail(SVTF_E_ARG, "svtf_cdef_pick_table: bad argument");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (nfb > c->tab_cap) {
+        cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
+        c->d_tab_mse = nullptr, c->d_tab_skip = nullptr, c->tab_cap = 0;
+        CUDA_TRY(c, cudaMalloc(&c->d_tab_mse, sizeof(uint64_t) * 128 * (size_t)nfb));
+        CUDA_TRY(c, cudaMalloc(&c->d_tab_skip, nfb));
+        c->tab_cap = nfb;
+    }
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_tab_mse, mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_tab_skip, skip, nfb, cudaMemcpyHostToDevice, c->stream));
+    return pick_device(c, cfg, c->d_tab_mse, c->d_tab_skip, nfb, out_params, fb_strength_idx, "svtf_cdef_pick_table");
 }

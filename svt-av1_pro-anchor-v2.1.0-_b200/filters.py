@@ -311,6 +311,15 @@ class FilterContext:
         self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), _ptr(dirs), _ptr(var)))
         return mse, skip, dirs, var
 
+    def pick_table(self, cfg, mse, skip):
+        """svtf_cdef_pick_table: finish_cdef_search on the GPU from a host table mse[2][nfb][64], skip[nfb]."""
+        mse = np.ascontiguousarray(mse, dtype=np.uint64)
+        skip = np.ascontiguousarray(skip, dtype=np.uint8)
+        out = L.CdefParams()
+        idx = np.empty(skip.size, dtype=np.int8)
+        self._chk(self._lib.svtf_cdef_pick_table(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), skip.size, C.byref(out), _ptr(idx)))
+        return out, idx
+
     def finish_cdef_search(self, cfg):
         g = self.geom
         nfb = ((g.mi_rows + 15) // 16) * ((g.mi_cols + 15) // 16)

@@ -126,5 +126,8 @@ class StripeFilter:
                 c.loop_filter_frame(lf)
             c.cdef_seg_search(cfg, out=(mse, skip, dirs, var))
         mse, skip = gather_search(mse, skip, g, self.parts, self.rank, dist, device)
-        params, idx = F.cdef_pick_host(cfg, mse, skip)
+        if self.ctx is not None:
+            params, idx = self.ctx.pick_table(cfg, mse, skip)  # GPU pick, identical on every rank
+        else:
+            params, idx = F.cdef_pick_host(cfg, mse, skip)
         return params, idx, mse, skip

@@ -205,3 +205,54 @@ def test_cdef_search_matches_oracle(H, orc, w, h, bd, sb, sub):
     assert list(params.cdef_y_strength) == list(e_params.cdef_y_strength)
     assert list(params.cdef_uv_strength) == list(e_params.cdef_uv_strength)
     assert np.array_equal(idx, e_idx)
+
+
+def _params_sig(p):
+    return [p.cdef_bits, p.cdef_damping, *p.cdef_y_strength, *p.cdef_uv_strength]
+
+
+def test_device_pick_matches_host_and_oracle(H, orc):
+    """finish_cdef_search on the GPU (svtf_cdef_pick_table) against the single-thread host implementation and the
+    oracle: random tables with ties (first index must win), zero-strength bias, skipped blocks, all blocks skipped,
+    short strength lists."""
+    S = H.S
+    rng = np.random.default_rng(7)
+    first, second = H.cdef_level1_lists()
+    g = S.make_geom(64, 64, 8)
+    with S.FilterContext(g) as ctx:
+        for it, (nfb, n1, n2, bias, pskip) in enumerate(((1, 16, 48, 0, 0.0), (7, 3, 3, 0, 0.2), (60, 16, 48, 40, 0.2), (130, 8, 8, 0, 0.3),
+                                                        (33, 1, 0, 0, 0.0), (2040, 16, 48, 0, 0.1), (500, 16, 20, 70, 1.0), (64, 2, 1, 0, 0.5))):
+            cfg = S.cdef_search_cfg(first[:n1], second[:n2], base_q_idx=int(rng.integers(0, 256)), zero_fs_cost_bias=bias,
+                                    lambda_=int(rng.integers(1, 50000)))
+            mse = rng.integers(0, 1 << 22, (2, nfb, 64)).astype(np.uint64)
+            mse[:, :, 0] += 1000
+            if it == 5:
+                mse = (mse >> 12) << 12  # coarse values: many exact ties between (j,k) pairs
+            skip = (rng.random(nfb) < pskip).astype(np.uint8)
+            if nfb > 3:
+                mse[:, 1] = mse[:, 0]
+            a = ctx.pick_table(cfg, mse, skip)
+            b = S.cdef_pick_host(cfg, mse, skip)
+            c = orc.cdef_pick(cfg, mse, skip)
+            assert _params_sig(a[0]) == _params_sig(b[0]) == _params_sig(c[0]), it
+            assert np.array_equal(a[1], b[1]) and np.array_equal(a[1], c[1]), it
+
+
+def test_device_pick_after_search(H, orc):
+    S = H.S
+    g = S.make_geom(328, 200, 10)
+    rec = H.synth_picture(g, 77)
+    src = H.synth_source(g, rec, 78)
+    mi = H.pack_mi(H.synth_mode_info(g, 79))
+    first, second = H.cdef_level1_lists()
+    cfg = S.cdef_search_cfg(first, second, base_q_idx=120, lambda_=4000)
+    with S.FilterContext(g) as ctx:
+        ctx.begin(g)
+        ctx.upload(rec)
+        ctx.upload_source(src)
+        ctx.set_mi(mi)
+        mse, skip, _, _ = ctx.cdef_seg_search(cfg)
+        a = ctx.finish_cdef_search(cfg)
+    b = orc.cdef_pick(cfg, mse, skip)
+    assert _params_sig(a[0]) == _params_sig(b[0])
+    assert np.array_equal(a[1], b[1])
