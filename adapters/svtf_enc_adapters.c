@@ -286,7 +286,8 @@ void finish_cdef_search(PictureControlSet *pcs) {
     memcpy(mse + (size_t)64 * nfb, pcs->mse_seg[1], sizeof(uint64_t) * 64 * (size_t)nfb);
     svtf_cdef_params out;
     int8_t          *idx = (int8_t *)malloc(nfb);
-    CHECK(svtf_cdef_pick_host(&cfg, mse, pcs->skip_cdef_seg, nfb, &out, idx), s->ctx);
+    /* GPU pick from the caller's table: 75 svt_search_one_dual passes without a host round trip */
+    CHECK(svtf_cdef_pick_table(s->ctx, &cfg, mse, pcs->skip_cdef_seg, nfb, &out, idx), s->ctx);
     if (cfg.zero_fs_cost_bias)
         for (int fb = 0; fb < nfb; fb++)
             if (!pcs->skip_cdef_seg[fb]) {

@@ -99,6 +99,89 @@ def cpu_measure(H, band_h, threads, steps, warmup):
     return kind, mpix / dt, dt / steps, f"{threads} threads x one 3840x{band_h} 10-bit band per step, {steps} steps"
 
 
+def cpu_search_measure(H, band_h, threads):
+    """CDEF strength search (64 strengths) + pick on the host: `threads` threads, one 3840 x band_h band each —
+    the reference's own segment split (EbEncHandle.c:503-506) is by filter-block rectangles like this."""
+    S = H.S
+    geom = S.make_geom(W4K, band_h, BD)
+    f1, f2 = H.cdef_level1_lists()
+    cfg = S.cdef_search_cfg(f1, f2, base_q_idx=120, lambda_=3000)
+    items = []
+    for t in range(threads):
+        rec = H.synth_picture(geom, 0xC3 + 16 * t)
+        soa = H.synth_mode_info(geom, 0xC3 + 16 * t + 1)
+        items.append((rec, H.synth_source(geom, rec, 0xC3 + 16 * t + 2), soa, H.pack_mi(soa)))
+    if H.ref_available():
+        ref, kind = H.Ref(), "reference"
+
+        def run(it):
+            mse, skip, _, _ = ref.cdef_search(geom, it[0], it[1], it[2], cfg)
+            ref.cdef_pick(geom, it[2], cfg, mse, skip)
+    else:
+        orc, kind = H.Oracle(), "port"
+
+        def run(it):
+            mse, skip, _, _ = orc.cdef_search(geom, it[0], it[1], it[3], cfg)
+            orc.cdef_pick(cfg, mse, skip)
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=run, args=(it,)) for it in items]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    nfb = threads * ((band_h + 63) // 64) * (W4K // 64)
+    return {"value": round(nfb / dt, 1), "unit": "filter blocks/s", "cores": threads, "kind": kind,
+            "sample": f"{threads} threads x one 3840x{band_h} 10-bit band, 64 strengths + pick, 1 step"}
+
+
+def gpu_search_leg(H, S, geom, wl, ctx, steps, np):
+    """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search."""
+    f1, f2 = H.cdef_level1_lists()
+    cfg = S.cdef_search_cfg(f1, f2, base_q_idx=120, lambda_=3000)
+    src = H.synth_source(geom, wl["rec"], 0xB200C3)
+    nfb = ((geom.mi_rows + 15) // 16) * ((geom.mi_cols + 15) // 16)
+    pin_rec, pin_src = S.PinnedPicture(geom), S.PinnedPicture(geom)
+    for p in range(3):
+        pin_rec.planes[p][...] = wl["rec"][p]
+        pin_src.planes[p][...] = src[p]
+    pin_mi = S.PinnedArray(wl["mi"].shape, np.uint32)
+    pin_mi.array[...] = wl["mi"]
+    ctx.begin(geom)
+    ctx.upload(pin_rec.planes)
+    ctx.upload_source(pin_src.planes)
+    ctx.set_mi(pin_mi.array)
+    ctx.sync()
+
+    def resident():
+        ctx.cdef_seg_search(cfg, want_outputs=False)
+        return ctx.finish_cdef_search(cfg)  # ends with the D2H of the picked strengths + per-fb indices (sync)
+
+    def e2e():
+        ctx.begin(geom)
+        ctx.upload(pin_rec.planes)
+        ctx.upload_source(pin_src.planes)
+        ctx.set_mi(pin_mi.array)
+        return resident()
+
+    out = {}
+    for name, fn in (("value", resident), ("e2e", e2e)):
+        for _ in range(2):
+            fn()
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            pick = fn()
+        ctx.sync()
+        out[name] = round(nfb * steps / (time.perf_counter() - t0), 1)
+    pin_rec.close()
+    pin_src.close()
+    pin_mi.close()
+    return {"metric": "CDEF-search filter blocks/s (64 strengths, 3 planes, + finish_cdef_search)", "value": out["value"], "e2e": out["e2e"],
+            "unit": "filter blocks/s", "workload": "4K 10-bit, cdef_level 1 list (16 primary + 48 secondary), subsampling 1",
+            "picked_cdef_bits": int(pick[0].cdef_bits)}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -381,11 +464,13 @@ def main():
     e2e_ok = all(np.array_equal(chk[p], pins_out[0].planes[p]) for p in range(3))
     clocks = sampler.stop() if sampler else None
 
-    cpu = None
+    search = gpu_search_leg(H, S, geom, wls[0], ctxs[0], max(3, args.steps // 2), np) if rank == 0 else None
+    cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         kind, val, per_step, sample = cpu_measure(H, 272, threads, 3, 1)
         cpu = {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": kind, "sample": sample}
+        search_cpu = cpu_search_measure(H, 64, threads)
 
     if rank == 0:
         line = {
@@ -398,6 +483,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:
