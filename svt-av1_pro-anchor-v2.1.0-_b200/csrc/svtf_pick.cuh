@@ -139,9 +139,19 @@ __global__ void __launch_bounds__(PICK_THREADS) pick_tot_kernel(const PickArgs a
     if (tid < PICK_CHUNK) {
         const int  fb = fb0 + tid;
         const bool ok = fb < a.nfb && !a.skip[fb];
-        uint64_t   best = PICK_INF;
-        if (ok)
-            for (int g = 0; g < nb; g++) best = min(best, pick_load(a, 0, fb, a.st->lev0[g + rot]) + pick_load(a, 1, fb, a.st->lev1[g + rot]));
+        // all list entries first, then all table loads: two dependent memory round trips instead of 2*nb
+        int l0[8], l1[8];
+#pragma unroll
+        for (int g = 0; g < 8; g++) l0[g] = a.st->lev0[min(g + rot, 7)], l1[g] = a.st->lev1[min(g + rot, 7)];
+        uint64_t va[8], vb[8];
+#pragma unroll
+        for (int g = 0; g < 8; g++) {
+            const bool use = ok && g < nb;
+            va[g] = use ? pick_load(a, 0, fb, l0[g]) : PICK_INF, vb[g] = use ? pick_load(a, 1, fb, l1[g]) : 0;
+        }
+        uint64_t best = PICK_INF;
+#pragma unroll
+        for (int g = 0; g < 8; g++) best = min(best, va[g] + vb[g]);
         sbest[tid]  = best;
         svalid[tid] = ok;
     }
