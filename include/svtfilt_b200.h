@@ -226,6 +226,16 @@ int svtf_filter_chain(svtf_ctx *ctx, const svtf_lf_params *lf, const svtf_cdef_p
                       const int8_t *fb_strength_idx, const svtf_ccso_params *ccso,
                       const uint8_t *const blk_flags[3]);
 
+/* ccso_search / derive_ccso_filter (Encoder/Codec/EbPickccso.c:785, :464) for planes [plane_start, plane_end) on the
+ * context's surfaces: classifier = the luma before the last CDEF pass (ext_rec_y), rec = the current picture (rec_uv),
+ * org = the uploaded source (org_uv).  rdmult is the value derive_ccso_filter receives (ccso_search first multiplies
+ * the lambda by clamp(base_q_idx, 1, 63), :788-793).  Writes the planes' entries of *out and blk_flags[p]
+ * (one byte per 256x256 luma / 128x128 chroma block, the reference's mbmi.ccso_blk_y/u/v).  Same result as the C code:
+ * the per-sample work (class histograms, trial filter + per-block SSE) runs on the GPU, the float LUT rounding and the
+ * double RD decisions on the host as written in the reference. */
+int svtf_ccso_derive_frame(svtf_ctx *ctx, int32_t rdmult, int32_t plane_start, int32_t plane_end, svtf_ccso_params *out,
+                           uint8_t *const blk_flags[3]);
+
 /* ---- CDEF strength search ------------------------------------------------------------------ */
 /* cdef_seg_search(pcs, scs, segment) over the whole frame (Encoder/Codec/EbCdefProcess.c:114).
  * Input = current picture (post-deblock) + uploaded source.  Outputs (host, caller-owned, may be

@@ -324,6 +324,59 @@ REF_API int ref_ccso_apply_frame(const svtf_geom *g, void *y, int sy, void *cb, 
     return 0;
 }
 
+/* CCSO derivation for one plane: derive_ccso_filter (Encoder/Codec/EbPickccso.c:464).  luma/rec/org are uint16 samples
+ * at stride g->width with g->height rows allocated (the reference keeps every plane at luma stride and copies
+ * pd[0].dst.height rows).  ccso_search (:785) itself only scales rdmult and sets up pd from the recon descriptor. */
+extern int ccso_stride, ccso_stride_ext;
+void       derive_ccso_filter(PictureControlSet *pcs, const int plane, MacroblockdPlane *pd, const uint16_t *org_uv, const uint16_t *ext_rec_y,
+                              const uint16_t *rec_uv, int rdmult);
+REF_API int ref_ccso_derive_plane(const svtf_geom *g, int plane, const uint16_t *luma, const uint16_t *rec, const uint16_t *org, int rdmult,
+                                  svtf_ccso_params *out, uint8_t *flags) {
+    harness    h;
+    const int  mi_stride = g->mi_cols;
+    ref_mi_soa soa       = {0};
+    soa.mi_stride        = mi_stride;
+    if (harness_init(&h, g, &soa, (void *)luma, g->width, (void *)luma, g->width, (void *)luma, g->width))
+        return -1;
+    h.scs->static_config.encoder_bit_depth = g->bit_depth;
+    struct MacroblockdPlane pd[3];
+    memset(pd, 0, sizeof(pd));
+    for (int p = 0; p < 3; p++) {
+        pd[p].subsampling_x = pd[p].subsampling_y = p ? 1 : 0;
+        pd[p].is_16bit                            = 1;
+        pd[p].dst.width                           = g->width >> (p ? 1 : 0);
+        pd[p].dst.height                          = g->height >> (p ? 1 : 0);
+    }
+    const int W = g->width, H = g->height, es = W + 10;
+    uint16_t *ext = calloc((size_t)es * (H + 10), sizeof(uint16_t));
+    for (int r = 0; r < H; r++) memcpy(ext + (size_t)(r + 5) * es + 5, luma + (size_t)r * W, sizeof(uint16_t) * W);
+    extend_ccso_border(ext, CCSO_PADDING_SIZE, pd);
+    ccso_stride     = W;
+    ccso_stride_ext = es;
+    derive_ccso_filter(h.pcs, plane, pd, org, ext, rec, rdmult);
+    const CcsoInfo *ci      = &h.ppcs->frm_hdr.ccso_info;
+    out->ccso_enable[plane] = ci->ccso_enable[plane];
+    const int pw = g->width >> (plane ? 1 : 0), ph = g->height >> (plane ? 1 : 0), bl = plane ? 7 : 8;
+    const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
+    memset(flags, 0, (size_t)nbx * nby);
+    if (ci->ccso_enable[plane]) {
+        out->ccso_bo_only[plane]       = ci->ccso_bo_only[plane];
+        out->quant_idx[plane]          = ci->quant_idx[plane];
+        out->ext_filter_support[plane] = ci->ext_filter_support[plane];
+        out->edge_clf[plane]           = ci->edge_clf[plane];
+        out->max_band_log2[plane]      = ci->max_band_log2[plane];
+        memcpy(out->filter_offset[plane], ci->filter_offset[plane], SVTF_CCSO_LUT_SIZE);
+        for (int by = 0; by < nby; by++)
+            for (int bx = 0; bx < nbx; bx++) {
+                const MbModeInfo *m  = &h.mi[64 * by * mi_stride + 64 * bx].mbmi;
+                flags[by * nbx + bx] = plane == 0 ? m->ccso_blk_y : (plane == 1 ? m->ccso_blk_u : m->ccso_blk_v);
+            }
+    }
+    free(ext);
+    harness_free(&h);
+    return 0;
+}
+
 /* =========================================================================================
  * leaf-level wrappers (the functions the reference's own unit tests exercise)
  * ======================================================================================= */

@@ -19,8 +19,52 @@ STUB(set_unscaled_input_16bit)
 STUB(svt_aom_ac_quant_qtx)
 STUB(svt_aom_assert_err)
 STUB(svt_aom_downscaled_source_buffer_desc_ctor)
-STUB(svt_aom_get_syntax_rate_from_cdf)
 STUB(svt_aom_resize_frame)
+/* referenced only by parts of EbMdRateEstimation.c the oracle never calls (it is compiled in for
+ * svt_aom_get_syntax_rate_from_cdf, used by derive_blk_md in EbPickccso.c) */
+STUB(av1_get_skip_context)
+STUB(av1_get_skip_mode_context)
+STUB(svt_aom_allow_intrabc)
+STUB(svt_aom_allow_palette)
+STUB(svt_aom_blk_geom_mds)
+STUB(svt_aom_filter_intra_allowed)
+STUB(svt_aom_filter_intra_allowed_bsize)
+STUB(svt_aom_get_comp_group_idx_context_enc)
+STUB(svt_aom_get_comp_index_context_enc)
+STUB(svt_aom_get_comp_reference_type_cdf)
+STUB(svt_aom_get_kf_y_mode_ctx)
+STUB(svt_aom_get_palette_bsize_ctx)
+STUB(svt_aom_get_palette_mode_ctx)
+STUB(svt_aom_get_pred_cdf_comp_bwdref_p)
+STUB(svt_aom_get_pred_cdf_comp_bwdref_p1)
+STUB(svt_aom_get_pred_cdf_comp_ref_p)
+STUB(svt_aom_get_pred_cdf_comp_ref_p1)
+STUB(svt_aom_get_pred_cdf_comp_ref_p2)
+STUB(svt_aom_get_pred_cdf_single_ref_p1)
+STUB(svt_aom_get_pred_cdf_single_ref_p2)
+STUB(svt_aom_get_pred_cdf_single_ref_p3)
+STUB(svt_aom_get_pred_cdf_single_ref_p4)
+STUB(svt_aom_get_pred_cdf_single_ref_p5)
+STUB(svt_aom_get_pred_cdf_single_ref_p6)
+STUB(svt_aom_get_pred_cdf_uni_comp_ref_p)
+STUB(svt_aom_get_pred_cdf_uni_comp_ref_p1)
+STUB(svt_aom_get_pred_cdf_uni_comp_ref_p2)
+STUB(svt_aom_get_pred_context_switchable_interp)
+STUB(svt_aom_get_reference_mode_cdf)
+STUB(svt_aom_get_wedge_params_bits)
+STUB(svt_aom_has_second_ref)
+STUB(svt_aom_has_uni_comp_refs)
+STUB(svt_aom_have_newmv_in_inter_mode)
+STUB(svt_aom_is_interintra_allowed)
+STUB(svt_aom_is_interintra_wedge_used)
+STUB(svt_aom_is_masked_compound_type)
+STUB(svt_aom_is_nontrans_global_motion_ec)
+STUB(svt_aom_mode_context_analyzer)
+STUB(svt_aom_motion_mode_allowed)
+STUB(svt_aom_partition_cdf_length)
+STUB(svt_av1_build_nmv_cost_table)
+STUB(svt_av1_get_intra_inter_context)
+STUB(svt_av1_get_mv_joint)
 STUB(svt_av1_loop_restoration_save_boundary_lines)
 STUB(svt_av1_superres_upscale_frame)
 STUB(svt_block_on_mutex)
@@ -37,9 +81,14 @@ STUB(svt_system_resource_get_producer_fifo)
 /* RTCD data pointers that are not on the exercised paths */
 void *svt_full_distortion_kernel16_bits  = 0;
 void *svt_spatial_full_distortion_kernel = 0;
-void *ccso_filter_block_hbd_with_buf     = 0;
-void *ccso_derive_src_block              = 0;
-void *compute_distortion_block           = 0;
+/* RTCD pointers used by derive_ccso_filter (Encoder/Codec/EbPickccso.c): the _c kernels, as common_dsp_rtcd.c:636-658
+ * sets them without SIMD.  (Declared without prototypes: this file includes no reference header.) */
+void     ccso_filter_block_hbd_with_buf_c();
+void     ccso_derive_src_block_c();
+uint64_t compute_distortion_block_c();
+void *ccso_filter_block_hbd_with_buf = (void *)ccso_filter_block_hbd_with_buf_c;
+void *ccso_derive_src_block          = (void *)ccso_derive_src_block_c;
+void *compute_distortion_block       = (void *)compute_distortion_block_c;
 
 static void     memcpy_c(void *d, const void *s, size_t n) { memcpy(d, s, n); }
 static uint32_t log2f_c(uint32_t x) {

@@ -5,6 +5,8 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cfloat>
+#include <cmath>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -15,6 +17,7 @@
 #include "svtf_search.cuh"
 #include "svtf_search2_kernel.cuh"
 #include "svtf_pick.cuh"
+#include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
 
 namespace svtf {
@@ -41,6 +44,8 @@ struct Surface {
 } // namespace svtf
 
 using namespace svtf;
+
+static void derive_scratch_free(void *p);
 
 struct svtf_ctx {
     int          device = 0;
@@ -91,6 +96,7 @@ struct svtf_ctx {
     uint8_t     *d_tab_skip = nullptr;
     int          pick_cap = 0, tab_cap = 0;
     int          sm_count = 0;
+    void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
     uint64_t     launches = 0;
     std::string  err;
 
@@ -208,6 +214,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
         if (sl.ev) cudaEventDestroy(sl.ev);
     }
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
+    derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
     if (c->own_stream)
         cudaStreamDestroy(c->own_stream);
@@ -878,4 +885,306 @@ extern "C" int svtf_cdef_pick_table(svtf_ctx *c, const svtf_cdef_search_cfg *cfg
     CUDA_TRY(c, cudaMemcpyAsync(c->d_tab_mse, mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaMemcpyAsync(c->d_tab_skip, skip, nfb, cudaMemcpyHostToDevice, c->stream));
     return pick_device(c, cfg, c->d_tab_mse, c->d_tab_skip, nfb, out_params, fb_strength_idx, "svtf_cdef_pick_table");
+}
+
+// ---- CCSO filter derivation ----------------------------------------------------------------------
+// ccso_search / derive_ccso_filter (Encoder/Codec/EbPickccso.c:464-782, :785-812).  Kernels: svtf_ccso_derive.cuh.
+// The host keeps the reference's sequential decisions verbatim (float LUT rounding :431-461, double RD cost
+// EbPickccso.h:9 + EbRestoration.h:346, per-block on/off :71-121 whose CDF rate never reaches the caller's cost,
+// LUT bit count :360-379).  The 4 (band-only: 8) band settings of one (bo, support, quantiser, classifier) group have
+// independent training loops, so they run in lock-step: one trial launch per round evaluates every LUT still training.
+namespace {
+
+const int     kCcsoOffset[8] = {-10, -7, -3, -1, 0, 1, 3, 7};
+const uint8_t kCcsoQuant[4]  = {16, 8, 32, 64};
+
+struct DeriveScratch { // device + pinned host buffers of one context, grown on demand
+    int                *d_herr = nullptr, *d_hcnt = nullptr, *h_herr = nullptr, *h_hcnt = nullptr;
+    unsigned long long *d_dist = nullptr, *h_dist = nullptr;
+    int8_t             *d_luts = nullptr, *h_luts = nullptr;
+    int                 nfb_cap = 0;
+};
+
+int ccso_lut_bits(const int8_t *lut, int band_log2, int intervals, int bo) {
+    static const int reordered[8] = {0, 1, -1, 3, -3, 7, -7, -10};
+    int              bits = 0, n = bo ? 1 : intervals;
+    for (int d0 = 0; d0 < n; d0++)
+        for (int d1 = 0; d1 < n; d1++)
+            for (int b = 0; b < (1 << band_log2); b++)
+                for (int i = 0; i < 7; i++) {
+                    bits++;
+                    if (reordered[i] == lut[(b << 4) + (d0 << 2) + d1])
+                        break;
+                }
+    return bits;
+}
+
+void ccso_lut_from_means(int8_t *lut, const int *err, const int *cnt, int band_log2, int intervals, int bo) {
+    const int n = bo ? 1 : intervals;
+    for (int d0 = 0; d0 < n; d0++)
+        for (int d1 = 0; d1 < n; d1++)
+            for (int b = 0; b < (1 << band_log2); b++) {
+                const int i = (b << 4) + (d0 << 2) + d1;
+                if (!cnt[i])
+                    continue;
+                const float t = (float)err[i] / cnt[i];
+                if (t < kCcsoOffset[0] || t >= kCcsoOffset[7]) {
+                    lut[i] = (int8_t)std::min(std::max((int)t, kCcsoOffset[0]), kCcsoOffset[7]);
+                } else {
+                    for (int k = 0; k < 7; k++)
+                        if (t >= kCcsoOffset[k] && t <= kCcsoOffset[k + 1]) {
+                            lut[i] = (int8_t)(fabs(t - kCcsoOffset[k]) > fabs(t - kCcsoOffset[k + 1]) ? kCcsoOffset[k + 1] : kCcsoOffset[k]);
+                            break;
+                        }
+                }
+            }
+}
+
+double ccso_rd_cost(int rdmult, int bits, uint64_t dist, int bd) {
+    return (((double)bits) * rdmult) / (double)(1 << 9) + ((double)(dist >> (2 * (bd - 8))) * (1 << 7));
+}
+
+struct BandState { // one band_log2 training loop
+    bool                 enable = true, keep = true;
+    double               prev_cost = DBL_MAX, best_cost = DBL_MAX;
+    int                  iter = 0;
+    int8_t               lut[2048], best_lut[2048];
+    std::vector<uint8_t> ctl, best_ctl;
+    std::vector<int>     herr, hcnt; // [nfb][entries] at this band count
+};
+
+} // namespace
+
+static void derive_scratch_free(void *p) {
+    DeriveScratch *s = static_cast<DeriveScratch *>(p);
+    if (!s)
+        return;
+    cudaFree(s->d_herr), cudaFree(s->d_hcnt), cudaFree(s->d_dist), cudaFree(s->d_luts);
+    cudaFreeHost(s->h_herr), cudaFreeHost(s->h_hcnt), cudaFreeHost(s->h_dist), cudaFreeHost(s->h_luts);
+    delete s;
+}
+
+static DeriveScratch *derive_scratch(svtf_ctx *c, int nfb) {
+    if (!c->derive_scratch)
+        c->derive_scratch = new DeriveScratch();
+    DeriveScratch *s = static_cast<DeriveScratch *>(c->derive_scratch);
+    if (nfb > s->nfb_cap) {
+        cudaFree(s->d_herr), cudaFree(s->d_hcnt), cudaFree(s->d_dist), cudaFree(s->d_luts);
+        cudaFreeHost(s->h_herr), cudaFreeHost(s->h_hcnt), cudaFreeHost(s->h_dist), cudaFreeHost(s->h_luts);
+        *s                 = DeriveScratch();
+        const size_t hb    = sizeof(int) * 2048 * (size_t)nfb, db = sizeof(unsigned long long) * CD_MAX_LUT * (size_t)nfb;
+        bool         ok    = cudaMalloc(&s->d_herr, hb) == cudaSuccess && cudaMalloc(&s->d_hcnt, hb) == cudaSuccess &&
+            cudaMalloc(&s->d_dist, db) == cudaSuccess && cudaMalloc(&s->d_luts, CD_MAX_LUT * 2048) == cudaSuccess &&
+            cudaHostAlloc(reinterpret_cast<void **>(&s->h_herr), hb, cudaHostAllocDefault) == cudaSuccess &&
+            cudaHostAlloc(reinterpret_cast<void **>(&s->h_hcnt), hb, cudaHostAllocDefault) == cudaSuccess &&
+            cudaHostAlloc(reinterpret_cast<void **>(&s->h_dist), db, cudaHostAllocDefault) == cudaSuccess &&
+            cudaHostAlloc(reinterpret_cast<void **>(&s->h_luts), CD_MAX_LUT * 2048, cudaHostAllocDefault) == cudaSuccess;
+        if (!ok)
+            return nullptr;
+        s->nfb_cap = nfb;
+    }
+    return s;
+}
+
+template <typename T>
+static void launch_hist(const CcsoDeriveArgs &a, dim3 grid, cudaStream_t s) { ccso_hist_kernel<T><<<grid, CD_THREADS, 0, s>>>(a); }
+template <typename T>
+static void launch_try(const CcsoDeriveArgs &a, dim3 grid, cudaStream_t s) { ccso_try_kernel<T><<<grid, CD_THREADS, 0, s>>>(a); }
+
+// derive_ccso_filter for one plane on the context's surfaces: classifier = pre-CDEF luma, rec = current picture,
+// org = uploaded source.
+static int ccso_derive_plane(svtf_ctx *c, int plane, int rdmult, svtf_ccso_params *out, uint8_t *flags) {
+    const svtf_geom &g  = c->geom;
+    const int        ss = plane ? 1 : 0, bd = g.bit_depth;
+    const int        pw = g.width >> ss, ph = g.height >> ss, bl = plane ? 7 : 8;
+    const int        nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl, nfb = nbx * nby;
+    DeriveScratch   *sc  = derive_scratch(c, nfb);
+    if (!sc)
+        return c->fail(SVTF_E_NOMEM, "svtf_ccso_derive_frame: scratch allocation failed");
+    const Surface &lum = c->surf[c->pre_cdef >= 0 ? c->pre_cdef : c->cur], &cur = c->surf[c->cur];
+    CcsoDeriveArgs a;
+    memset(&a, 0, sizeof(a));
+    a.luma = lum.base[0], a.luma_pitch = lum.pitch[0];
+    a.rec = cur.base[plane], a.rec_pitch = cur.pitch[plane];
+    a.org = c->source.base[plane], a.org_pitch = c->source.pitch[plane];
+    a.W = g.width, a.H = g.height, a.pw = pw, a.ph = ph, a.ss = ss, a.blk_log2 = bl, a.nbx = nbx, a.max_val = (1 << bd) - 1;
+    a.herr = sc->d_herr, a.hcnt = sc->d_hcnt, a.luts = sc->d_luts, a.dist = sc->d_dist;
+    const dim3 grid((pw + 63) / 64, (ph + 63) / 64);
+    const bool u8 = g.sample_bytes == 1;
+
+    // trial filter + per-block SSE for `nl` LUTs already in sc->h_luts; results in sc->h_dist[l*nfb + fb]
+    auto run_try = [&](int nl, const int *shifts) -> int {
+        a.nl = nl;
+        for (int l = 0; l < nl; l++) a.shift[l] = shifts[l];
+        CUDA_TRY(c, cudaMemcpyAsync(sc->d_luts, sc->h_luts, (size_t)nl * 2048, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(c, cudaMemsetAsync(sc->d_dist, 0, sizeof(unsigned long long) * (size_t)nl * nfb, c->stream));
+        if (u8)
+            launch_try<uint8_t>(a, grid, c->stream);
+        else
+            launch_try<uint16_t>(a, grid, c->stream);
+        CUDA_TRY(c, cudaGetLastError());
+        c->launches++;
+        CUDA_TRY(c, cudaMemcpyAsync(sc->h_dist, sc->d_dist, sizeof(unsigned long long) * (size_t)nl * nfb, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        return SVTF_OK;
+    };
+
+    // unfiltered distortion: the trial kernel with an all-zero LUT (band-only so no classes are evaluated)
+    std::vector<uint64_t> unf(nfb);
+    {
+        memset(sc->h_luts, 0, 2048);
+        a.bo = 1, a.dy = a.dx = 0, a.thr = 0, a.edge_clf = 0;
+        const int sh = bd;
+        if (int r = run_try(1, &sh))
+            return r;
+        for (int i = 0; i < nfb; i++) unf[i] = sc->h_dist[i];
+    }
+    uint64_t unf_total = 0;
+    for (int i = 0; i < nfb; i++) unf_total += unf[i];
+    const double unfiltered_cost = ccso_rd_cost(rdmult, 1, unf_total, bd);
+    double       final_cost      = DBL_MAX;
+    int8_t       final_lut[2048] = {0};
+    std::vector<uint8_t> final_ctl(nfb, 0);
+    int          final_clf = 0, final_q = 0, final_sup = 0, final_bo = 0, final_band = 0;
+    const int    frame_bits = 10, frame_bits_bo = 5; // EbPickccso.c:531-546 with CONFIG_CCSO_SIGFIX
+    static const int taps[6][2] = {{-1, 0}, {-1, -1}, {0, -1}, {1, -1}, {0, -3}, {0, -5}}; // derive_ccso_sample_pos
+
+    for (int bo = 0; bo < 2; bo++)
+        for (int sup = 0; sup < (bo ? 1 : 6); sup++)
+            for (int q = 0; q < (bo ? 1 : 4); q++)
+                for (int clf = 0; clf < (bo ? 1 : 2); clf++) {
+                    const int intervals = clf ? 2 : 3, nbands = bo ? 8 : 4, fine = nbands - 1; // finest band_log2 of the group
+                    a.bo = bo, a.dy = taps[sup][0], a.dx = taps[sup][1], a.thr = kCcsoQuant[q], a.edge_clf = clf;
+                    a.hist_shift = bd - fine, a.nidx = bo ? 2048 : 128;
+                    const size_t hbytes = sizeof(int) * (size_t)a.nidx * nfb;
+                    CUDA_TRY(c, cudaMemsetAsync(sc->d_herr, 0, hbytes, c->stream));
+                    CUDA_TRY(c, cudaMemsetAsync(sc->d_hcnt, 0, hbytes, c->stream));
+                    if (u8)
+                        launch_hist<uint8_t>(a, grid, c->stream);
+                    else
+                        launch_hist<uint16_t>(a, grid, c->stream);
+                    CUDA_TRY(c, cudaGetLastError());
+                    c->launches++;
+                    CUDA_TRY(c, cudaMemcpyAsync(sc->h_herr, sc->d_herr, hbytes, cudaMemcpyDeviceToHost, c->stream));
+                    CUDA_TRY(c, cudaMemcpyAsync(sc->h_hcnt, sc->d_hcnt, hbytes, cudaMemcpyDeviceToHost, c->stream));
+                    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+
+                    // per band count: histograms at that granularity (band = finest band >> (fine - log2))
+                    std::vector<BandState> st(nbands);
+                    for (int b = 0; b < nbands; b++) {
+                        BandState &s = st[b];
+                        s.ctl.assign(nfb, 1), s.best_ctl.assign(nfb, 0);
+                        memset(s.lut, 0, sizeof(s.lut)), memset(s.best_lut, 0, sizeof(s.best_lut));
+                        const int ne = 16 << b; // LUT indices < (1<<b) << 4
+                        s.herr.assign((size_t)nfb * ne, 0), s.hcnt.assign((size_t)nfb * ne, 0);
+                        for (int fb = 0; fb < nfb; fb++)
+                            for (int i = 0; i < (16 << fine); i++) {
+                                const int cn = sc->h_hcnt[(size_t)fb * a.nidx + i];
+                                if (!cn)
+                                    continue;
+                                const int j = (((i >> 4) >> (fine - b)) << 4) + (i & 15);
+                                s.herr[(size_t)fb * ne + j] += sc->h_herr[(size_t)fb * a.nidx + i];
+                                s.hcnt[(size_t)fb * ne + j] += cn;
+                            }
+                    }
+                    for (;;) { // lock-step rounds
+                        int active[CD_MAX_LUT], shifts[CD_MAX_LUT], na = 0;
+                        for (int b = 0; b < nbands; b++) {
+                            BandState &s = st[b];
+                            if (!s.keep)
+                                continue;
+                            if (s.enable) { // ccso_compute_class_err + derive_lut_offset
+                                const int ne = 16 << b;
+                                int       err[2048] = {0}, cnt[2048] = {0};
+                                memset(s.lut, 0, sizeof(s.lut));
+                                for (int fb = 0; fb < nfb; fb++) {
+                                    if (!s.ctl[fb])
+                                        continue;
+                                    const int n = bo ? 1 : intervals;
+                                    for (int d0 = 0; d0 < n; d0++)
+                                        for (int d1 = 0; d1 < n; d1++)
+                                            for (int bn = 0; bn < (1 << b); bn++) {
+                                                const int i = (bn << 4) + (d0 << 2) + d1;
+                                                err[i] += s.herr[(size_t)fb * ne + i], cnt[i] += s.hcnt[(size_t)fb * ne + i];
+                                            }
+                                }
+                                ccso_lut_from_means(s.lut, err, cnt, b, intervals, bo);
+                            }
+                            memcpy(sc->h_luts + (size_t)na * 2048, s.lut, 2048);
+                            shifts[na] = bd - b, active[na] = b, na++;
+                        }
+                        if (!na)
+                            break;
+                        if (int r = run_try(na, shifts))
+                            return r;
+                        for (int k = 0; k < na; k++) {
+                            BandState      &s   = st[active[k]];
+                            const uint64_t *trn = reinterpret_cast<const uint64_t *>(sc->h_dist) + (size_t)k * nfb;
+                            bool            improvement = false;
+                            uint64_t        cur_dist = 0;
+                            if (s.enable) { // derive_blk_md
+                                bool any = false;
+                                for (int fb = 0; fb < nfb; fb++) {
+                                    const bool on = trn[fb] < unf[fb];
+                                    s.ctl[fb]     = on;
+                                    cur_dist += on ? trn[fb] : unf[fb];
+                                    any |= on;
+                                }
+                                s.enable = any;
+                            }
+                            if (s.enable) {
+                                const int    bits = ccso_lut_bits(s.lut, active[k], intervals, bo) + (bo ? frame_bits_bo : frame_bits) + nfb;
+                                const double cost = ccso_rd_cost(rdmult, bits, cur_dist, bd);
+                                if (cost < s.prev_cost)
+                                    s.prev_cost = cost, improvement = true;
+                                if (cost < s.best_cost) {
+                                    s.best_cost = cost;
+                                    memcpy(s.best_lut, s.lut, sizeof(s.lut));
+                                    s.best_ctl = s.ctl;
+                                }
+                            }
+                            s.iter++;
+                            if (!improvement || s.iter > 15) // CCSO_MAX_ITERATIONS
+                                s.keep = false;
+                        }
+                    }
+                    for (int b = 0; b < nbands; b++) // in the reference's order: strict "<" keeps the earlier setting on ties
+                        if (st[b].best_cost < final_cost) {
+                            final_cost = st[b].best_cost;
+                            final_q = q, final_sup = sup, final_bo = bo, final_band = b, final_clf = clf;
+                            memcpy(final_lut, st[b].best_lut, sizeof(final_lut));
+                            final_ctl = st[b].best_ctl;
+                        }
+                }
+    const bool on = !(unfiltered_cost < final_cost);
+    out->ccso_enable[plane] = on;
+    memset(flags, 0, nfb);
+    if (on) {
+        memcpy(flags, final_ctl.data(), nfb);
+        memcpy(out->filter_offset[plane], final_lut, 2048);
+        out->quant_idx[plane] = (uint8_t)final_q, out->ext_filter_support[plane] = (uint8_t)final_sup;
+        out->ccso_bo_only[plane] = (uint8_t)final_bo, out->max_band_log2[plane] = (uint8_t)final_band;
+        out->edge_clf[plane] = (uint8_t)final_clf;
+    }
+    return SVTF_OK;
+}
+
+extern "C" int svtf_ccso_derive_frame(svtf_ctx *c, int32_t rdmult, int32_t plane_start, int32_t plane_end, svtf_ccso_params *out,
+                                      uint8_t *const blk_flags[3]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_ccso_derive_frame: NULL context");
+    if (!out || !blk_flags || plane_start < 0 || plane_end > 3 || plane_start > plane_end || rdmult < 0)
+        return c->fail(SVTF_E_ARG, "svtf_ccso_derive_frame: bad argument");
+    if (!c->have_frame || !c->have_source)
+        return c->fail(SVTF_E_STATE, "svtf_ccso_derive_frame: upload the picture and the source first");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_ccso_derive_frame: not available on a striped context");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    for (int p = plane_start; p < plane_end; p++) {
+        if (!blk_flags[p])
+            return c->fail(SVTF_E_ARG, "svtf_ccso_derive_frame: NULL flag array for a requested plane");
+        if (int r = ccso_derive_plane(c, p, rdmult, out, blk_flags[p]))
+            return r;
+    }
+    return SVTF_OK;
 }

@@ -311,6 +311,18 @@ class FilterContext:
         self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), _ptr(dirs), _ptr(var)))
         return mse, skip, dirs, var
 
+    def ccso_search(self, rdmult, plane_start=0, plane_end=3):
+        """svtf_ccso_derive_frame: derive the CCSO parameters and block flags of the current picture against the source."""
+        g = self.geom
+        out = L.CcsoParams()
+        flags = []
+        for p in range(3):
+            pw, ph, bl = g.width >> (1 if p else 0), g.height >> (1 if p else 0), 7 if p else 8
+            flags.append(np.zeros(((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl), dtype=np.uint8))
+        fl = (C.c_void_p * 3)(*[f.ctypes.data for f in flags])
+        self._chk(self._lib.svtf_ccso_derive_frame(self._h, rdmult, plane_start, plane_end, C.byref(out), fl))
+        return out, flags
+
     def pick_table(self, cfg, mse, skip):
         """svtf_cdef_pick_table: finish_cdef_search on the GPU from a host table mse[2][nfb][64], skip[nfb]."""
         mse = np.ascontiguousarray(mse, dtype=np.uint64)

@@ -173,6 +173,37 @@ def cdef_level1_lists():
     return first, second
 
 
+
+# ------------------------------------------------------------------------------------------------
+# CCSO derivation helpers (shared by Oracle and Ref): planes as uint16 at luma stride
+# ------------------------------------------------------------------------------------------------
+def ccso_nblocks(geom, plane):
+    pw, ph, bl = geom.width >> (1 if plane else 0), geom.height >> (1 if plane else 0), 7 if plane else 8
+    return ((pw + (1 << bl) - 1) >> bl) * ((ph + (1 << bl) - 1) >> bl)
+
+
+def _ccso_derive_call(fn, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
+    W, H = geom.width, geom.height
+    luma = np.ascontiguousarray(pre_luma[:H, :W], dtype=np.uint16)
+    ph, pw = H >> (1 if plane else 0), W >> (1 if plane else 0)
+    rec = np.zeros((H, W), dtype=np.uint16)
+    org = np.zeros((H, W), dtype=np.uint16)
+    rec[:ph, :pw] = rec_plane[:ph, :pw]
+    org[:ph, :pw] = org_plane[:ph, :pw]
+    out = L.CcsoParams()
+    flags = np.zeros(ccso_nblocks(geom, plane), dtype=np.uint8)
+    assert fn(C.byref(geom), C.c_int(plane), _p(luma), _p(rec), _p(org), C.c_int(rdmult), C.byref(out), _p(flags)) == 0
+    return out, flags
+
+
+def ccso_plane_sig(params, plane):
+    """Comparable summary of one plane's derived CCSO parameters."""
+    if not params.ccso_enable[plane]:
+        return (0,)
+    lut = bytes(bytearray(np.ctypeslib.as_array(params.filter_offset[plane]).view(np.uint8)))
+    return (1, params.ccso_bo_only[plane], params.quant_idx[plane], params.ext_filter_support[plane], params.edge_clf[plane],
+            params.max_band_log2[plane], lut)
+
 # ------------------------------------------------------------------------------------------------
 # the CPU restatement
 # ------------------------------------------------------------------------------------------------
@@ -205,6 +236,9 @@ class Oracle:
                                           C.byref(ccso), fl if flags is not None else None)
         assert r == 0
         return out
+
+    def ccso_derive_plane(self, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
+        return _ccso_derive_call(self.lib.orc_ccso_derive_plane, geom, plane, pre_luma, rec_plane, org_plane, rdmult)
 
     def cdef_search(self, geom, rec, src, mi, cfg):
         nv, nh = nfb_of(geom)
@@ -298,6 +332,9 @@ class Ref:
         assert self.lib.ref_ccso_apply_frame(C.byref(geom), *_planes(out), _p(pre_luma), C.c_int(pre_luma.strides[0] // pre_luma.itemsize),
                                              C.byref(ccso), fl if flags is not None else None) == 0
         return out
+
+    def ccso_derive_plane(self, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
+        return _ccso_derive_call(self.lib.ref_ccso_derive_plane, geom, plane, pre_luma, rec_plane, org_plane, rdmult)
 
     def cdef_search(self, geom, rec, src, soa, cfg):
         nv, nh = nfb_of(geom)
