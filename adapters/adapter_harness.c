@@ -15,6 +15,7 @@
 #include "EbDeblockingFilter.h"
 #include "EbDeblockingCommon.h"
 #include "EbCcso.h"
+#include "EbPickccso.h"
 #include "EbModeDecisionProcess.h"
 
 #include "../include/svtfilt_b200.h"
@@ -177,6 +178,50 @@ API int adapt_ccso_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb,
     struct MacroblockdPlane pd[3];
     memset(pd, 0, sizeof(pd));
     ccso_frame(h.recon, h.pcs, pd, ext);
+    free(ext);
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}
+
+/* ccso_search(pcs, pd, rdmult, ext_rec_y, rec_uv, org_uv) on uint16 planes at luma stride; returns the derived
+ * parameters and per-block flags as the reference leaves them in frm_hdr.ccso_info / mbmi.ccso_blk_*. */
+API int adapt_ccso_search(const svtf_geom *g, int base_q_idx, int rdmult, const uint16_t *luma, uint16_t *rec[3], uint16_t *org[3],
+                          svtf_ccso_params *out, uint8_t *const flags[3]) {
+    harness    h;
+    ref_mi_soa soa = {0};
+    soa.mi_stride  = g->mi_cols;
+    if (harness_init(&h, g, &soa, (void *)luma, g->width, (void *)luma, g->width, (void *)luma, g->width))
+        return -1;
+    h.ppcs->frm_hdr.quantization_params.base_q_idx = (uint8_t)base_q_idx;
+    const int W = g->width, H = g->height, es = W + 10;
+    uint16_t *ext = calloc((size_t)es * (H + 10), sizeof(uint16_t));
+    for (int r = 0; r < H + 10; r++)
+        for (int c = 0; c < W + 10; c++) {
+            const int rr = r - 5 < 0 ? 0 : (r - 5 >= H ? H - 1 : r - 5), cc = c - 5 < 0 ? 0 : (c - 5 >= W ? W - 1 : c - 5);
+            ext[r * es + c] = luma[rr * W + cc];
+        }
+    struct MacroblockdPlane pd[3];
+    memset(pd, 0, sizeof(pd));
+    ccso_search(h.pcs, pd, rdmult, ext, rec, org);
+    const CcsoInfo *ci = &h.ppcs->frm_hdr.ccso_info;
+    memset(out, 0, sizeof(*out));
+    for (int p = 0; p < 3; p++) {
+        out->ccso_enable[p] = ci->ccso_enable[p];
+        const int pw = W >> (p ? 1 : 0), ph = H >> (p ? 1 : 0), bl = p ? 7 : 8;
+        const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
+        memset(flags[p], 0, (size_t)nbx * nby);
+        if (!ci->ccso_enable[p])
+            continue;
+        out->ccso_bo_only[p] = ci->ccso_bo_only[p], out->quant_idx[p] = ci->quant_idx[p], out->ext_filter_support[p] = ci->ext_filter_support[p];
+        out->edge_clf[p] = ci->edge_clf[p], out->max_band_log2[p] = ci->max_band_log2[p];
+        memcpy(out->filter_offset[p], ci->filter_offset[p], SVTF_CCSO_LUT_SIZE);
+        for (int by = 0; by < nby; by++)
+            for (int bx = 0; bx < nbx; bx++) {
+                const MbModeInfo *m = &h.mi[64 * by * soa.mi_stride + 64 * bx].mbmi;
+                flags[p][by * nbx + bx] = p == 0 ? m->ccso_blk_y : (p == 1 ? m->ccso_blk_u : m->ccso_blk_v);
+            }
+    }
     free(ext);
     svtf_adapter_release(h.pcs);
     harness_free(&h);

@@ -30,6 +30,7 @@
 #include "EbDeblockingFilter.h"
 #include "EbDeblockingCommon.h"
 #include "EbCcso.h"
+#include "EbPickccso.h"
 
 #include "../include/svtfilt_b200.h"
 #include "../include/svtfilt_b200_adapters.h"
@@ -368,4 +369,87 @@ void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdP
     end_picture(s, frame);
     s->resident = 0;
     for (int pl = 0; pl < 3; pl++) free(flags[pl]);
+}
+
+/* ccso_search (Encoder/Codec/EbPickccso.c:785): ext_rec_y = pre-CDEF luma padded by 5, rec_uv / org_uv = the picture to
+ * correct and the source, uint16 samples at luma stride (Encoder/Codec/EbCdefProcess.c:524-661).  The three planes are
+ * staged on the picture's context (classifier luma as the "pre-CDEF" picture, rec as the current picture, org as the
+ * source), svtf_ccso_derive_frame runs the search, the result goes where the reference writes it. */
+void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const uint16_t *ext_rec_y, uint16_t *rec_uv[3], uint16_t *org_uv[3]) {
+    (void)pd;
+    FrameHeader  *fh     = &pcs->ppcs->frm_hdr;
+    int           weight = fh->quantization_params.base_q_idx;
+    weight               = weight < 1 ? 1 : (weight > 63 ? 63 : weight);
+    const int64_t rd     = (int64_t)rdmult * weight; /* :788-793 */
+    if (rd >= 2147483647)
+        return;
+    CtxSlot  *s  = slot_for(pcs);
+    const int W = s->geom.width, H = s->geom.height, cw = s->geom.mi_cols * 4, chh = s->geom.mi_rows * 4, es = W + 10;
+    const int sb = s->geom.sample_bytes;
+    /* planes in the context's sample type and coded size (replicated beyond the visible picture; those samples are
+     * never read by the derivation, which works on width x height) */
+    uint8_t *buf[3][3]; /* [kind: classifier, rec, org][plane] */
+    for (int k = 0; k < 3; k++)
+        for (int p = 0; p < 3; p++) {
+            const int pw = cw >> (p ? 1 : 0), ph = chh >> (p ? 1 : 0), vw = W >> (p ? 1 : 0), vh = H >> (p ? 1 : 0);
+            buf[k][p]    = (uint8_t *)calloc((size_t)pw * ph, sb);
+            for (int r = 0; r < ph; r++)
+                for (int c = 0; c < pw; c++) {
+                    const int rr = r < vh ? r : vh - 1, cc = c < vw ? c : vw - 1;
+                    uint16_t  v;
+                    if (k == 0)
+                        v = p == 0 ? ext_rec_y[(size_t)(5 + rr) * es + 5 + cc] : 0;
+                    else
+                        v = (k == 1 ? rec_uv[p] : org_uv[p])[(size_t)rr * W + cc];
+                    if (sb == 1)
+                        buf[k][p][(size_t)r * pw + c] = (uint8_t)v;
+                    else
+                        ((uint16_t *)buf[k][p])[(size_t)r * pw + c] = v;
+                }
+        }
+    CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+    CHECK(svtf_upload_frame(s->ctx, buf[0][0], cw, buf[0][1], cw / 2, buf[0][2], cw / 2), s->ctx);
+    send_mi(s, pcs);
+    svtf_cdef_params idp;
+    memset(&idp, 0, sizeof(idp));
+    const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
+    int8_t   *idx = (int8_t *)calloc(nfb, 1);
+    CHECK(svtf_cdef_apply_frame(s->ctx, &idp, idx), s->ctx); /* strengths 0: copies, marks the pre-CDEF surface */
+    CHECK(svtf_overwrite_current(s->ctx, buf[1][0], cw, buf[1][1], cw / 2, buf[1][2], cw / 2), s->ctx);
+    CHECK(svtf_upload_source(s->ctx, buf[2][0], cw, buf[2][1], cw / 2, buf[2][2], cw / 2), s->ctx);
+    svtf_ccso_params out;
+    memset(&out, 0, sizeof(out));
+    uint8_t *flags[3];
+    int      nbx[3], nby[3];
+    for (int p = 0; p < 3; p++) {
+        const int pw = W >> (p ? 1 : 0), ph = H >> (p ? 1 : 0), bl = p ? 7 : 8;
+        nbx[p] = (pw + (1 << bl) - 1) >> bl, nby[p] = (ph + (1 << bl) - 1) >> bl;
+        flags[p] = (uint8_t *)calloc((size_t)nbx[p] * nby[p], 1);
+    }
+    CHECK(svtf_ccso_derive_frame(s->ctx, (int)rd, 0, 3, &out, flags), s->ctx);
+    CcsoInfo *ci = &fh->ccso_info;
+    for (int p = 0; p < 3; p++) {
+        ci->ccso_enable[p] = out.ccso_enable[p];
+        if (!out.ccso_enable[p])
+            continue;
+        for (int by = 0; by < nby[p]; by++)
+            for (int bx = 0; bx < nbx[p]; bx++) { /* :731-751 */
+                MbModeInfo *m = &pcs->mi_grid_base[64 * by * pcs->mi_stride + 64 * bx]->mbmi;
+                const uint8_t f = flags[p][by * nbx[p] + bx];
+                if (p == 0) m->ccso_blk_y = f;
+                if (p == 1) m->ccso_blk_u = f;
+                if (p == 2) m->ccso_blk_v = f;
+            }
+        memcpy(ci->filter_offset[p], out.filter_offset[p], SVTF_CCSO_LUT_SIZE);
+        ci->quant_idx[p] = out.quant_idx[p], ci->ext_filter_support[p] = out.ext_filter_support[p];
+        ci->ccso_bo_only[p] = out.ccso_bo_only[p], ci->max_band_log2[p] = out.max_band_log2[p], ci->edge_clf[p] = out.edge_clf[p];
+    }
+#if CONFIG_D143_CCSO_FM_FLAG
+    ci->ccso_frame_flag = ci->ccso_enable[0] | ci->ccso_enable[1] | ci->ccso_enable[2];
+#endif
+    s->resident = 0;
+    free(idx);
+    for (int p = 0; p < 3; p++) free(flags[p]);
+    for (int k = 0; k < 3; k++)
+        for (int p = 0; p < 3; p++) free(buf[k][p]);
 }

@@ -135,6 +135,36 @@ def cpu_search_measure(H, band_h, threads):
             "sample": f"{threads} threads x one 3840x{band_h} 10-bit band, 64 strengths + pick, 1 step"}
 
 
+def ccso_derive_leg(H, S, geom, wl, ctx, np, with_cpu):
+    """CCSO derivation (ccso_search): whole 4K 10-bit picture on the GPU; the reference's C on a small picture."""
+    src = H.synth_source(geom, wl["rec"], 0xB200CC, amp=6)
+    ctx.begin(geom)
+    ctx.upload(wl["rec"])
+    ctx.upload_source(src)
+    ctx.set_mi(wl["mi"])
+    ctx.cdef_frame(wl["cdef"], wl["idx"])
+    ctx.sync()
+    l0 = ctx.launch_count
+    t0 = time.perf_counter()
+    out, _ = ctx.ccso_search(4000)
+    dt = time.perf_counter() - t0
+    res = {"metric": "CCSO derivation Mpixel/s (200 configurations x <=16 training iterations per plane, 3 planes)",
+           "value": round(geom.width * geom.height / dt / 1e6, 2), "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 1),
+           "gpu_launches": ctx.launch_count - l0, "enabled_planes": [int(out.ccso_enable[p]) for p in range(3)], "cpu_baseline": None}
+    if with_cpu and H.ref_available():
+        g2 = S.make_geom(480, 272, BD)
+        rec = H.synth_picture(g2, 0xCC1)
+        org = H.synth_source(g2, rec, 0xCC2, amp=6)
+        ref = H.Ref()
+        t0 = time.perf_counter()
+        for p in range(3):
+            ref.ccso_derive_plane(g2, p, rec[0], rec[p], org[p], 4000)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": round(480 * 272 / dt / 1e6, 4), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                               "sample": "one 480x272 10-bit picture, 3 planes, single thread (derive_ccso_filter is serial)"}
+    return res
+
+
 def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search.
     Several pictures are in flight, one context + stream + submitting host thread each — the reference's CDEF stage runs
@@ -476,6 +506,7 @@ def main():
     clocks = sampler.stop() if sampler else None
 
     search = gpu_search_leg(H, S, geom, wls[0], ctxs[:4], max(3, args.steps // 2), np) if rank == 0 else None
+    derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
@@ -494,7 +525,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:

@@ -90,3 +90,28 @@ def test_adapters_match_reference(H, orc, adapt, w, h, bd, sb):
     assert H.planes_equal(got, exp), "ccso vs oracle: " + H.first_diff(got, exp)
     if ref:
         assert H.planes_equal(got, ref.ccso_apply(g, post, dbk[0], ccso, flags))
+
+
+    # --- ccso_search(pcs, pd, rdmult, ext_rec_y, rec_uv, org_uv): uint16 planes at luma stride ---
+    W, Hh = g.width, g.height
+    luma16 = np.ascontiguousarray(dbk[0][:Hh, :W], dtype=np.uint16)
+    rec16, org16 = [], []
+    for p in range(3):
+        ph, pw = Hh >> (1 if p else 0), W >> (1 if p else 0)
+        r = np.zeros((Hh, W), np.uint16)
+        o = np.zeros((Hh, W), np.uint16)
+        r[:ph, :pw], o[:ph, :pw] = post[p][:ph, :pw], src[p][:ph, :pw]
+        rec16.append(r)
+        org16.append(o)
+    base_q, rdmult = 37, 9
+    dout = H.L.CcsoParams()
+    dflags = [np.zeros(H.ccso_nblocks(g, p), np.uint8) for p in range(3)]
+    vp3 = lambda arrs: (C.c_void_p * 3)(*[a.ctypes.data for a in arrs])  # noqa: E731
+    assert adapt.adapt_ccso_search(C.byref(g), base_q, rdmult, H._p(luma16), vp3(rec16), vp3(org16), C.byref(dout), vp3(dflags)) == 0
+    for p in range(3):
+        e, ef = orc.ccso_derive_plane(g, p, dbk[0], post[p], src[p], rdmult * base_q)
+        assert H.ccso_plane_sig(dout, p) == H.ccso_plane_sig(e, p), f"ccso_search plane {p}"
+        assert np.array_equal(dflags[p], ef)
+        if ref:
+            r, rf = ref.ccso_derive_plane(g, p, dbk[0], post[p], src[p], rdmult * base_q)
+            assert H.ccso_plane_sig(dout, p) == H.ccso_plane_sig(r, p) and np.array_equal(dflags[p], rf)
