@@ -226,6 +226,21 @@ int svtf_filter_chain(svtf_ctx *ctx, const svtf_lf_params *lf, const svtf_cdef_p
                       const int8_t *fb_strength_idx, const svtf_ccso_params *ccso,
                       const uint8_t *const blk_flags[3]);
 
+/* svt_av1_pick_filter_level(src, pcs, LPF_PICK_FROM_FULL_IMAGE) (Encoder/Codec/EbDeblockingFilter.c:1129-1252): searches
+ * the deblocking level of luma (one level for both directions), then U, then V, each with search_filter_level (:886-985)
+ * — trial deblock of that plane, SSE against the uploaded source, keep the unfiltered picture.  `start` carries the
+ * levels the search starts from (the reference's last_frame_filter_level = the frame header's levels on entry, after the
+ * optional reference-frame averaging) and every other loop-filter parameter; note the reference starts the luma search
+ * from last_frame_filter_level[2] (the U level) unless dlf_avg is set (:903-909, dir = 2) and so does this function.
+ * The picture on the context is left unfiltered.  out_levels = {luma, luma, u, v}. */
+typedef struct svtf_lf_search_cfg {
+    int32_t dlf_avg;                /* ppcs->dlf_ctrls.dlf_avg */
+    int32_t early_exit_convergence; /* ppcs->dlf_ctrls.early_exit_convergence (0 = never) */
+    int32_t only_4x4;               /* frm_hdr->tx_mode == ONLY_4X4 */
+    int32_t search_chroma;          /* 0: keep the start chroma levels (the dlf_avg_uv path, :1211-1219) */
+} svtf_lf_search_cfg;
+int svtf_lf_search_frame(svtf_ctx *ctx, const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]);
+
 /* ccso_search / derive_ccso_filter (Encoder/Codec/EbPickccso.c:785, :464) for planes [plane_start, plane_end) on the
  * context's surfaces: classifier = the luma before the last CDEF pass (ext_rec_y), rec = the current picture (rec_uv),
  * org = the uploaded source (org_uv).  rdmult is the value derive_ccso_filter receives (ccso_search first multiplies

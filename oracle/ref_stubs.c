@@ -79,8 +79,13 @@ STUB(svt_system_resource_get_consumer_fifo)
 STUB(svt_system_resource_get_producer_fifo)
 
 /* RTCD data pointers that are not on the exercised paths */
-void *svt_full_distortion_kernel16_bits  = 0;
-void *svt_spatial_full_distortion_kernel = 0;
+uint64_t svt_full_distortion_kernel16_bits_c();
+uint64_t svt_spatial_full_distortion_kernel_c();
+void    *svt_full_distortion_kernel16_bits  = (void *)svt_full_distortion_kernel16_bits_c;  /* picture_sse_calculations */
+void    *svt_spatial_full_distortion_kernel = (void *)svt_spatial_full_distortion_kernel_c;
+/* RTCD pointers referenced by parts of EbPictureOperators.c that are never called here */
+void *svt_aom_un_pack2d_16_bit_src_mul4 = 0, *svt_compressed_packmsb = 0, *svt_enc_msb_pack2_d = 0, *svt_enc_msb_un_pack2_d = 0;
+void *svt_full_distortion_kernel32_bits = 0, *svt_full_distortion_kernel_cbf_zero32_bits = 0, *svt_pack2d_16_bit_src_mul4 = 0;
 /* RTCD pointers used by derive_ccso_filter (Encoder/Codec/EbPickccso.c): the _c kernels, as common_dsp_rtcd.c:636-658
  * sets them without SIMD.  (Declared without prototypes: this file includes no reference header.) */
 void     ccso_filter_block_hbd_with_buf_c();

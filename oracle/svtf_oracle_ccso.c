@@ -244,3 +244,124 @@ ORC_API int orc_ccso_derive_plane(const svtf_geom *g, int plane, const uint16_t 
     free(unf), free(trn), free(ctl), free(best_ctl), free(final_ctl), free(tmp), free(herr), free(hcnt), free(cls);
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Deblocking level search — svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE), Encoder/Codec/EbDeblockingFilter.c:
+ *   search_filter_level :886-985, try_filter_frame :841-880, picture_sse_calculations :716-835.
+ * Pinned against the reference's own static search_filter_level (oracle/ref_shim_dlf.c includes the file).
+ * ------------------------------------------------------------------------------------------------------- */
+int orc_deblock_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const svtf_mi_t *mi, int mi_stride,
+                      const svtf_lf_params *lf, int plane_start, int plane_end);
+
+typedef struct {
+    const svtf_geom *g;
+    void            *rec[3];
+    const void      *src[3];
+    int              stride[3], sstride[3];
+    const svtf_mi_t *mi;
+    int              mi_stride;
+} LfS;
+
+static int64_t lfs_try(const LfS *s, const svtf_lf_params *lf, int plane) {
+    const svtf_geom *g  = s->g;
+    const int        sb = g->sample_bytes, ss = plane ? 1 : 0;
+    const int        ch = (g->mi_rows * 4) >> ss;
+    void            *tmp[3];
+    for (int p = 0; p < 3; p++) { /* trial on a copy: the picture itself stays unfiltered */
+        const size_t n = (size_t)s->stride[p] * ((g->mi_rows * 4) >> (p ? 1 : 0)) * sb;
+        tmp[p]         = malloc(n);
+        memcpy(tmp[p], s->rec[p], n);
+    }
+    orc_deblock_frame(g, tmp[0], s->stride[0], tmp[1], s->stride[1], tmp[2], s->stride[2], s->mi, s->mi_stride, lf, plane, plane + 1);
+    int w, h;
+    if (sb == 1)
+        w = (g->mi_cols * 4) >> ss, h = ch;
+    else
+        w = (g->width + ss) >> ss, h = (g->height + ss) >> ss;
+    int64_t e = 0;
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            const int64_t a = sb == 1 ? ((const uint8_t *)s->src[plane])[(size_t)y * s->sstride[plane] + x]
+                                      : ((const uint16_t *)s->src[plane])[(size_t)y * s->sstride[plane] + x];
+            const int64_t b = sb == 1 ? ((const uint8_t *)tmp[plane])[(size_t)y * s->stride[plane] + x]
+                                      : ((const uint16_t *)tmp[plane])[(size_t)y * s->stride[plane] + x];
+            e += (a - b) * (a - b);
+        }
+    for (int p = 0; p < 3; p++) free(tmp[p]);
+    return e;
+}
+
+static int lfs_plane(const LfS *s, svtf_lf_params *lf, const svtf_lf_search_cfg *cfg, const int32_t last[4], int plane) {
+    const int lvl      = plane == 0 ? (cfg->dlf_avg ? last[0] : last[2]) : last[plane + 1]; /* dir = 2 for luma, :903-909 */
+    int       filt_mid = clampi(lvl, 0, 63), step = filt_mid < 16 ? 4 : filt_mid / 4;
+    int64_t   ss_err[64];
+    for (int i = 0; i < 64; i++) ss_err[i] = -1;
+#define LFS_TRY(level, dst)                                           \
+    do {                                                              \
+        if (plane == 0)                                               \
+            lf->filter_level[0] = lf->filter_level[1] = (level);      \
+        else if (plane == 1)                                          \
+            lf->filter_level_u = (level);                             \
+        else                                                          \
+            lf->filter_level_v = (level);                             \
+        (dst) = lfs_try(s, lf, plane);                                \
+    } while (0)
+    int64_t best_err;
+    LFS_TRY(filt_mid, best_err);
+    int filt_best = filt_mid, direction = 0, convergence = 0;
+    ss_err[filt_mid] = best_err;
+    while (step > 0) {
+        const int filt_high = filt_mid + step < 63 ? filt_mid + step : 63, filt_low = filt_mid - step > 0 ? filt_mid - step : 0;
+        int64_t   bias      = (best_err >> (15 - (filt_mid / 8))) * step;
+        if (!cfg->only_4x4)
+            bias >>= 1;
+        if (direction <= 0 && filt_low != filt_mid) {
+            if (ss_err[filt_low] < 0)
+                LFS_TRY(filt_low, ss_err[filt_low]);
+            if (ss_err[filt_low] < best_err + bias) {
+                if (ss_err[filt_low] < best_err)
+                    best_err = ss_err[filt_low];
+                filt_best = filt_low;
+            }
+        }
+        if (direction >= 0 && filt_high != filt_mid) {
+            if (ss_err[filt_high] < 0)
+                LFS_TRY(filt_high, ss_err[filt_high]);
+            if (ss_err[filt_high] < best_err - bias) {
+                best_err  = ss_err[filt_high];
+                filt_best = filt_high;
+            }
+        }
+        if (filt_best == filt_mid) {
+            convergence++;
+            if (convergence == cfg->early_exit_convergence)
+                step = 0;
+            else
+                step /= 2;
+            direction = 0;
+        } else {
+            direction = filt_best < filt_mid ? -1 : 1;
+            filt_mid  = filt_best;
+        }
+    }
+#undef LFS_TRY
+    return filt_best;
+}
+
+ORC_API int orc_lf_search_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const void *src_y, int ssy,
+                                const void *src_cb, int sscb, const void *src_cr, int sscr, const svtf_mi_t *mi, int mi_stride,
+                                const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]) {
+    LfS s = {g, {y, cb, cr}, {src_y, src_cb, src_cr}, {sy, scb, scr}, {ssy, sscb, sscr}, mi, mi_stride};
+    svtf_lf_params lf = *start;
+    const int32_t  last[4] = {start->filter_level[0], start->filter_level[1], start->filter_level_u, start->filter_level_v};
+    int            u = last[2], v = last[3];
+    const int      yl = lfs_plane(&s, &lf, cfg, last, 0);
+    lf.filter_level[0] = lf.filter_level[1] = yl;
+    if (cfg->search_chroma) {
+        u                 = lfs_plane(&s, &lf, cfg, last, 1);
+        lf.filter_level_u = u;
+        v                 = lfs_plane(&s, &lf, cfg, last, 2);
+    }
+    out_levels[0] = out_levels[1] = yl, out_levels[2] = u, out_levels[3] = v;
+    return 0;
+}

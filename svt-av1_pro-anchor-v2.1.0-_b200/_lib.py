@@ -53,6 +53,10 @@ class CcsoParams(C.Structure):
                 ("filter_offset", (C.c_int8 * CCSO_LUT_SIZE) * 3)]
 
 
+class LfSearchCfg(C.Structure):
+    _fields_ = [("dlf_avg", C.c_int32), ("early_exit_convergence", C.c_int32), ("only_4x4", C.c_int32), ("search_chroma", C.c_int32)]
+
+
 class DevPlane(C.Structure):
     _fields_ = [("ptr", C.c_void_p), ("pitch", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
 
@@ -62,7 +66,7 @@ EXPORTS = [
     "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
-    "svtf_filter_chain", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
+    "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
     "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free",
 ]
 
@@ -101,6 +105,7 @@ def load():
     lib.svtf_ccso_apply_frame.argtypes = [vp, C.POINTER(CcsoParams), C.POINTER(vp)]
     lib.svtf_filter_chain.argtypes = [vp, C.POINTER(LfParams), C.POINTER(CdefParams), vp, C.POINTER(CcsoParams), C.POINTER(vp)]
     lib.svtf_cdef_search_frame.argtypes = [vp, C.POINTER(CdefSearchCfg), vp, vp, vp, vp]
+    lib.svtf_lf_search_frame.argtypes = [vp, C.POINTER(LfParams), C.POINTER(LfSearchCfg), vp]
     lib.svtf_ccso_derive_frame.argtypes = [vp, i32, i32, i32, C.POINTER(CcsoParams), vp]
     lib.svtf_cdef_pick.argtypes = [vp, C.POINTER(CdefSearchCfg), C.POINTER(CdefParams), vp]
     lib.svtf_cdef_pick_table.argtypes = [vp, C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]

@@ -439,9 +439,9 @@ static int need_frame_mi(svtf_ctx *c, const char *fn) {
     return SVTF_OK;
 }
 
-extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_deblock_frame: NULL context");
+// only_selected: launch no tiles for planes outside the mask (their samples in the output surface are then undefined;
+// used by the level search, which measures the filtered plane alone) instead of copying them through
+static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end, bool only_selected) {
     if (!lf || plane_start < 0 || plane_end > 3 || plane_start > plane_end)
         return c->fail(SVTF_E_ARG, "svtf_deblock_frame: bad arguments");
     if (int r = need_frame_mi(c, "svtf_deblock_frame"))
@@ -479,6 +479,8 @@ extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t
         a.tiles_x[p]   = (w + 8 + DBK_TILE - 1) / DBK_TILE;
         a.ty0[p]       = ((dlo >> ss) + 8) / DBK_TILE;
         a.tiles_y[p]   = ((dhi >> ss) - 1 + 8) / DBK_TILE + 1 - a.ty0[p];
+        if (only_selected && !((mask >> p) & 1))
+            a.tiles_y[p] = 0;
         a.tile_base[p] = total;
         total += a.tiles_x[p] * a.tiles_y[p];
     }
@@ -492,6 +494,12 @@ extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t
     c->launches++;
     c->cur = nxt;
     return SVTF_OK;
+}
+
+extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_deblock_frame: NULL context");
+    return deblock_impl(c, lf, plane_start, plane_end, false);
 }
 
 // ---- CCSO parameters -> device (LUT + block flags) --------------------------------------------------
@@ -1186,5 +1194,161 @@ extern "C" int svtf_ccso_derive_frame(svtf_ctx *c, int32_t rdmult, int32_t plane
         if (int r = ccso_derive_plane(c, p, rdmult, out, blk_flags[p]))
             return r;
     }
+    return SVTF_OK;
+}
+
+
+// ---- deblocking level search -------------------------------------------------------------------------
+// svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE) (Encoder/Codec/EbDeblockingFilter.c:1129-1252):
+// search_filter_level (:886-985) per plane with try_filter_frame (:841-880) = deblock one plane with a trial level,
+// picture_sse_calculations (:716-835) against the source, restore.  On the device a trial is one deblock launch of that
+// plane's tiles into a scratch surface plus one SSE reduction; nothing is restored because the unfiltered picture is
+// never overwritten.
+template <typename T>
+__global__ void __launch_bounds__(256) plane_sse_kernel(const T *a, const int pa, const T *b, const int pb, const int w, const int h,
+                                                        unsigned long long *out) {
+    unsigned long long acc = 0;
+    const int          n = w * h;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const int       y = i / w, x = i - y * w;
+        const long long d = (long long)a[(size_t)y * pa + x] - (long long)b[(size_t)y * pb + x];
+        acc += (unsigned long long)(d * d);
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, m);
+    __shared__ unsigned long long s[8];
+    if ((threadIdx.x & 31) == 0)
+        s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int i = 0; i < 8; i++) t += s[i];
+        atomicAdd(out, t);
+    }
+}
+
+// try_filter_frame: SSE of `plane` after deblocking it with lf (levels already set by the caller)
+static int lf_trial(svtf_ctx *c, const svtf_lf_params *lf, int plane, int64_t *err) {
+    const int saved = c->cur;
+    if (int r = deblock_impl(c, lf, plane, plane + 1, true))
+        return r;
+    const Surface  &s  = c->surf[c->cur];
+    const int       ss = plane ? 1 : 0;
+    // picture_sse_calculations: 8-bit pictures are measured over the aligned size, 16-bit ones over the visible size
+    int w, h;
+    if (c->geom.sample_bytes == 1)
+        w = (c->geom.mi_cols * 4) >> ss, h = (c->geom.mi_rows * 4) >> ss;
+    else
+        w = (c->geom.width + ss) >> ss, h = (c->geom.height + ss) >> ss;
+    unsigned long long *d_out = reinterpret_cast<unsigned long long *>(c->d_pick_tot); // 8 bytes of an idle scratch buffer
+    CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out), c->stream));
+    const int grid = std::min((w * h + 255) / 256, 8 * std::max(c->sm_count, 1));
+    if (c->geom.sample_bytes == 1)
+        plane_sse_kernel<uint8_t><<<grid, 256, 0, c->stream>>>(static_cast<const uint8_t *>(c->source.base[plane]), c->source.pitch[plane],
+                                                              static_cast<const uint8_t *>(s.base[plane]), s.pitch[plane], w, h, d_out);
+    else
+        plane_sse_kernel<uint16_t><<<grid, 256, 0, c->stream>>>(static_cast<const uint16_t *>(c->source.base[plane]), c->source.pitch[plane],
+                                                               static_cast<const uint16_t *>(s.base[plane]), s.pitch[plane], w, h, d_out);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    unsigned long long v = 0;
+    CUDA_TRY(c, cudaMemcpyAsync(&v, d_out, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out), c->stream)); // the pick expects a zeroed tot
+    *err   = (int64_t)v;
+    c->cur = saved;
+    return SVTF_OK;
+}
+
+// search_filter_level for one plane (dir 2 = both luma directions, as svt_av1_pick_filter_level calls it)
+static int lf_search_plane(svtf_ctx *c, svtf_lf_params *lf, const svtf_lf_search_cfg *cfg, const int32_t last[4], int plane, int32_t *best) {
+    const int min_level = 0, max_level = 63; // MAX_LOOP_FILTER
+    // luma is searched with dir = 2 and the start level is last_frame_filter_level[dir] unless dlf_avg: index 2 is the U
+    // level (:903-909) — kept as the reference has it
+    const int lvl       = plane == 0 ? (cfg->dlf_avg ? last[0] : last[2]) : last[plane + 1];
+    int       filt_mid  = std::min(std::max(lvl, min_level), max_level);
+    int       step      = filt_mid < 16 ? 4 : filt_mid / 4;
+    int64_t   ss_err[64];
+    for (int i = 0; i < 64; i++) ss_err[i] = -1;
+    auto try_level = [&](int level, int64_t *e) -> int {
+        if (plane == 0)
+            lf->filter_level[0] = lf->filter_level[1] = level;
+        else if (plane == 1)
+            lf->filter_level_u = level;
+        else
+            lf->filter_level_v = level;
+        return lf_trial(c, lf, plane, e);
+    };
+    int64_t best_err;
+    if (int r = try_level(filt_mid, &best_err))
+        return r;
+    int filt_best = filt_mid, direction = 0, convergence = 0;
+    ss_err[filt_mid] = best_err;
+    while (step > 0) {
+        const int filt_high = std::min(filt_mid + step, max_level), filt_low = std::max(filt_mid - step, min_level);
+        int64_t   bias      = (best_err >> (15 - (filt_mid / 8))) * step; // bias against raising the level
+        if (!cfg->only_4x4)
+            bias >>= 1;
+        if (direction <= 0 && filt_low != filt_mid) {
+            if (ss_err[filt_low] < 0)
+                if (int r = try_level(filt_low, &ss_err[filt_low]))
+                    return r;
+            if (ss_err[filt_low] < best_err + bias) {
+                if (ss_err[filt_low] < best_err)
+                    best_err = ss_err[filt_low];
+                filt_best = filt_low;
+            }
+        }
+        if (direction >= 0 && filt_high != filt_mid) {
+            if (ss_err[filt_high] < 0)
+                if (int r = try_level(filt_high, &ss_err[filt_high]))
+                    return r;
+            if (ss_err[filt_high] < best_err - bias) {
+                best_err  = ss_err[filt_high];
+                filt_best = filt_high;
+            }
+        }
+        if (filt_best == filt_mid) {
+            convergence++;
+            if (convergence == cfg->early_exit_convergence)
+                step = 0;
+            else
+                step /= 2;
+            direction = 0;
+        } else {
+            direction = filt_best < filt_mid ? -1 : 1;
+            filt_mid  = filt_best;
+        }
+    }
+    *best = filt_best;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_lf_search_frame(svtf_ctx *c, const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_lf_search_frame: NULL context");
+    if (!start || !cfg || !out_levels)
+        return c->fail(SVTF_E_ARG, "svtf_lf_search_frame: NULL argument");
+    if (int r = need_frame_mi(c, "svtf_lf_search_frame"))
+        return r;
+    if (!c->have_source)
+        return c->fail(SVTF_E_STATE, "svtf_lf_search_frame: upload the source picture first");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_lf_search_frame: not available on a striped context");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    svtf_lf_params lf      = *start;
+    const int32_t  last[4] = {start->filter_level[0], start->filter_level[1], start->filter_level_u, start->filter_level_v};
+    int32_t        y = 0, u = last[2], v = last[3];
+    if (int r = lf_search_plane(c, &lf, cfg, last, 0, &y))
+        return r;
+    lf.filter_level[0] = lf.filter_level[1] = y;
+    if (cfg->search_chroma) {
+        if (int r = lf_search_plane(c, &lf, cfg, last, 1, &u))
+            return r;
+        lf.filter_level_u = u;
+        if (int r = lf_search_plane(c, &lf, cfg, last, 2, &v))
+            return r;
+    }
+    out_levels[0] = out_levels[1] = y, out_levels[2] = u, out_levels[3] = v;
     return SVTF_OK;
 }

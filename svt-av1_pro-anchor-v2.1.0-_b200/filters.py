@@ -311,6 +311,13 @@ class FilterContext:
         self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), _ptr(dirs), _ptr(var)))
         return mse, skip, dirs, var
 
+    def pick_filter_level(self, start_lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
+        """svtf_lf_search_frame: svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE) on the uploaded picture + source."""
+        cfg = L.LfSearchCfg(dlf_avg, early_exit_convergence, only_4x4, search_chroma)
+        out = (C.c_int32 * 4)()
+        self._chk(self._lib.svtf_lf_search_frame(self._h, C.byref(start_lf), C.byref(cfg), out))
+        return list(out)
+
     def ccso_search(self, rdmult, plane_start=0, plane_end=3):
         """svtf_ccso_derive_frame: derive the CCSO parameters and block flags of the current picture against the source."""
         g = self.geom

@@ -240,6 +240,15 @@ class Oracle:
     def ccso_derive_plane(self, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
         return _ccso_derive_call(self.lib.orc_ccso_derive_plane, geom, plane, pre_luma, rec_plane, org_plane, rdmult)
 
+    def lf_search(self, geom, rec, src, mi, lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
+        rec = [p.copy() for p in rec]
+        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        cfg = L.LfSearchCfg(dlf_avg, early_exit_convergence, only_4x4, search_chroma)
+        out = (C.c_int32 * 4)()
+        assert self.lib.orc_lf_search_frame(C.byref(geom), *_planes(rec), *_planes(src), _p(mi), C.c_int(mi.shape[1]), C.byref(lf),
+                                            C.byref(cfg), out) == 0
+        return list(out)
+
     def cdef_search(self, geom, rec, src, mi, cfg):
         nv, nh = nfb_of(geom)
         nfb = nv * nh
@@ -335,6 +344,14 @@ class Ref:
 
     def ccso_derive_plane(self, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
         return _ccso_derive_call(self.lib.ref_ccso_derive_plane, geom, plane, pre_luma, rec_plane, org_plane, rdmult)
+
+    def lf_search(self, geom, rec, src, soa, lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
+        rec = [p.copy() for p in rec]
+        s, keep = self._soa(soa)
+        cfg = L.LfSearchCfg(dlf_avg, early_exit_convergence, only_4x4, search_chroma)
+        out = (C.c_int32 * 4)()
+        assert self.lib.ref_lf_search_frame(C.byref(geom), *_planes(rec), *_planes(src), C.byref(s), C.byref(lf), C.byref(cfg), out) == 0
+        return list(out)
 
     def cdef_search(self, geom, rec, src, soa, cfg):
         nv, nh = nfb_of(geom)
