@@ -142,6 +142,44 @@ API int adapt_cdef_search_pick(const svtf_geom *g, void *ry, int rsy, void *rcb,
     return 0;
 }
 
+/* The DLF kernel's sequence (Encoder/Codec/EbDlfProcess.c:101-106): pick the levels against the source, then filter. */
+void svt_av1_pick_filter_level_by_q(PictureControlSet *pcs, uint8_t qindex, int32_t *filter_level) {
+    (void)pcs, (void)qindex, (void)filter_level;
+    fprintf(stderr, "adapter_harness: svt_av1_pick_filter_level_by_q is the reference's own scalar formula; not part of this harness\n");
+    abort();
+}
+API int adapt_pick_and_deblock(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, void *oy, int osy, void *ocb,
+                               int oscb, void *ocr, int oscr, const ref_mi_soa *soa, const svtf_lf_params *lf,
+                               const svtf_lf_search_cfg *cfg, int resident, int32_t out_levels[4]) {
+    harness h;
+    if (harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    fill_lf(&h, lf);
+    EbPictureBufferDesc *s = h.source;
+    *s                     = *h.recon;
+    s->buffer_y = oy, s->buffer_cb = ocb, s->buffer_cr = ocr;
+    s->stride_y = (uint16_t)osy, s->stride_cb = (uint16_t)oscb, s->stride_cr = (uint16_t)oscr;
+    h.pcs->input_frame16bit                  = s;
+    h.ppcs->frm_hdr.tx_mode                  = cfg->only_4x4 ? ONLY_4X4 : TX_MODE_SELECT;
+    h.ppcs->dlf_ctrls.dlf_avg                = (uint8_t)cfg->dlf_avg;
+    h.ppcs->dlf_ctrls.early_exit_convergence = (uint8_t)cfg->early_exit_convergence;
+    h.ppcs->dlf_ctrls.dlf_avg_uv             = (uint8_t)!cfg->search_chroma;
+    h.pcs->temporal_layer_index              = 1;
+    h.ppcs->tot_ref_frame_types              = 0;
+    svtf_adapter_set_resident(resident);
+    svt_av1_pick_filter_level((EbPictureBufferDesc *)h.ppcs->enhanced_pic, h.pcs, LPF_PICK_FROM_FULL_IMAGE);
+    const struct LoopFilter *l = &h.ppcs->frm_hdr.loop_filter_params;
+    out_levels[0] = l->filter_level[0], out_levels[1] = l->filter_level[1], out_levels[2] = l->filter_level_u, out_levels[3] = l->filter_level_v;
+    svt_av1_loop_filter_frame(h.recon, h.pcs, 0, 3);
+    if (resident) { /* bring the picture back as the last stage of a resident chain would */
+        svtf_adapter_set_resident(0);
+        svtf_adapter_fetch(h.pcs, h.recon);
+    }
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}
+
 /* ccso_frame(frame, pcs, pd, ext_rec_y) with ext_rec_y built like Encoder/Codec/EbCdefProcess.c:480-502 */
 API int adapt_ccso_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const void *pre_y, int pre_sy,
                          const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {

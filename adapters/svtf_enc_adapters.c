@@ -7,6 +7,8 @@
  *   Encoder/Codec/EbEncCdef.c:728           finish_cdef_search
  *   Encoder/Codec/EbCdefProcess.c:114       cdef_seg_search      (static there -> svtf_cdef_search_picture here)
  *   Common/Codec/EbCcso.c:626               ccso_frame
+ *   Encoder/Codec/EbPickccso.c:785          ccso_search
+ *   Encoder/Codec/EbDeblockingFilter.c:1129 svt_av1_pick_filter_level
  * (see INTEGRATION.md for the three-line changes at the call sites).
  *
  * What an adapter does: (1) flatten pcs->mi_grid_base into the packed 4-byte mi words, (2) hand the recon
@@ -166,10 +168,17 @@ static void end_picture(CtxSlot *s, const EbPictureBufferDesc *pic) {
     CHECK(svtf_download_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
 }
 
+void svtf_adapter_fetch(const PictureControlSet *pcs, void *pic) {
+    CtxSlot *s = slot_for(pcs);
+    if (!s->resident) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: svtf_adapter_fetch: no resident picture for this pcs\n");
+        abort();
+    }
+    end_picture(s, (const EbPictureBufferDesc *)pic);
+}
+
 /* ---------------------------------------------------------------------------------------------------- */
-void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControlSet *pcs, int32_t plane_start,
-                               int32_t plane_end) {
-    CtxSlot                 *s  = slot_for(pcs);
+static void lf_of(const PictureControlSet *pcs, svtf_lf_params *out) {
     const FrameHeader       *fh = &pcs->ppcs->frm_hdr;
     const struct LoopFilter *l  = &fh->loop_filter_params;
     svtf_lf_params           lf;
@@ -189,10 +198,79 @@ void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControl
     lf.delta_lf_present = fh->delta_lf_params.delta_lf_present;
     lf.delta_lf_multi   = fh->delta_lf_params.delta_lf_multi;
     for (int i = 0; i < 4; i++) lf.curr_delta_lf[i] = pcs->ppcs->curr_delta_lf[i];
+    *out = lf;
+}
+
+void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControlSet *pcs, int32_t plane_start,
+                               int32_t plane_end) {
+    CtxSlot       *s = slot_for(pcs);
+    svtf_lf_params lf;
+    lf_of(pcs, &lf);
     begin_picture(s, pcs, frame_buffer);
     CHECK(svtf_deblock_frame(s->ctx, &lf, plane_start, plane_end), s->ctx);
     if (!g_resident)
         end_picture(s, frame_buffer), s->resident = 0;
+}
+
+/* svt_av1_pick_filter_level (Encoder/Codec/EbDeblockingFilter.c:1129).  LPF_PICK_MINIMAL_LPF and LPF_PICK_FROM_Q are
+ * the reference's scalar formulas (svt_av1_pick_filter_level_by_q stays where it is); the full-image search
+ * (:1147-1249: up to ~3 x 8 trial deblocks of a whole plane + SSE against the source) is svtf_lf_search_frame.  The
+ * reconstruction is uploaded once and stays on the device for the svt_av1_loop_filter_frame call that follows
+ * (EbDlfProcess.c:104-106) when svtf_adapter_set_resident(1) is on; the temp_lf_recon_pic allocation is not needed. */
+EbErrorType svt_av1_pick_filter_level(EbPictureBufferDesc *srcBuffer, PictureControlSet *pcs, LpfPickMethod method) {
+    SequenceControlSet *scs = pcs->scs;
+    FrameHeader        *fh  = &pcs->ppcs->frm_hdr;
+    struct LoopFilter  *l   = &fh->loop_filter_params;
+    l->sharpness_level      = 0;
+    if (method == LPF_PICK_MINIMAL_LPF) {
+        l->filter_level[0] = l->filter_level[1] = 0;
+        return EB_ErrorNone;
+    }
+    if (method >= LPF_PICK_FROM_Q) {
+        int32_t lvl[4];
+        svt_av1_pick_filter_level_by_q(pcs, fh->quantization_params.base_q_idx, lvl);
+        l->filter_level[0] = lvl[0], l->filter_level[1] = lvl[1], l->filter_level_u = lvl[2], l->filter_level_v = lvl[3];
+        return EB_ErrorNone;
+    }
+    if (pcs->ppcs->dlf_ctrls.dlf_avg && pcs->ppcs->tot_ref_frame_types > 0) { /* :1175-1205, start from the references' mean */
+        int32_t tot[4] = {0, 0, 0, 0}, refs = 0;
+        for (uint32_t it = 0; it < pcs->ppcs->tot_ref_frame_types; ++it) {
+            MvReferenceFrame rf[2];
+            av1_set_ref_frame(rf, pcs->ppcs->ref_frame_type_arr[it]);
+            if (rf[1] != NONE_FRAME)
+                continue;
+            const EbReferenceObject *ro = pcs->ref_pic_ptr_array[get_list_idx(rf[0])][get_ref_frame_idx(rf[0])]->object_ptr;
+            tot[0] += ro->filter_level[0], tot[1] += ro->filter_level[1], tot[2] += ro->filter_level_u, tot[3] += ro->filter_level_v;
+            refs++;
+        }
+        l->filter_level[0] = tot[0] / refs, l->filter_level[1] = tot[1] / refs;
+        l->filter_level_u = tot[2] / refs, l->filter_level_v = tot[3] / refs;
+    }
+    const Bool           is_16bit = scs->is_16bit_pipeline;
+    EbPictureBufferDesc *recon;
+    svt_aom_get_recon_pic(pcs, &recon, is_16bit);
+    /* the picture the error is measured against (picture_sse_calculations :736, :783) */
+    const EbPictureBufferDesc *src = is_16bit ? pcs->input_frame16bit : (EbPictureBufferDesc *)pcs->ppcs->enhanced_pic;
+    (void)srcBuffer;
+    CtxSlot       *s = slot_for(pcs);
+    svtf_lf_params lf;
+    lf_of(pcs, &lf);
+    begin_picture(s, pcs, recon);
+    void   *p[3];
+    int32_t st[3];
+    plane_ptrs(src, s->geom.sample_bytes, p, st);
+    CHECK(svtf_upload_source(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    svtf_lf_search_cfg cfg;
+    cfg.dlf_avg                = pcs->ppcs->dlf_ctrls.dlf_avg;
+    cfg.early_exit_convergence = pcs->ppcs->dlf_ctrls.early_exit_convergence;
+    cfg.only_4x4               = fh->tx_mode == ONLY_4X4;
+    cfg.search_chroma          = !(pcs->ppcs->dlf_ctrls.dlf_avg_uv && pcs->temporal_layer_index > 0); /* :1218 */
+    int32_t out[4];
+    CHECK(svtf_lf_search_frame(s->ctx, &lf, &cfg, out), s->ctx);
+    l->filter_level[0] = out[0], l->filter_level[1] = out[1], l->filter_level_u = out[2], l->filter_level_v = out[3];
+    if (!g_resident)
+        s->resident = 0; /* the picture on the device is unchanged; nothing to copy back */
+    return EB_ErrorNone;
 }
 
 static void fb_indices(const PictureControlSet *pcs, const svtf_geom *g, int8_t *idx) {

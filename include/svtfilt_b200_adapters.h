@@ -10,6 +10,10 @@
  *   void finish_cdef_search(PictureControlSet *pcs);                          Encoder/Codec/EbEncCdef.c:728
  *   void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdPlane *pd,
  *                   uint16_t *ext_rec_y);                                     Common/Codec/EbCcso.c:626
+ *   void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const uint16_t *ext_rec_y,
+ *                    uint16_t *rec_uv[3], uint16_t *org_uv[3]);               Encoder/Codec/EbPickccso.c:785
+ *   EbErrorType svt_av1_pick_filter_level(EbPictureBufferDesc *srcBuffer, PictureControlSet *pcs,
+ *                                         LpfPickMethod method);              Encoder/Codec/EbDeblockingFilter.c:1129
  */
 #ifndef SVTFILT_B200_ADAPTERS_H
 #define SVTFILT_B200_ADAPTERS_H
@@ -27,9 +31,12 @@ void svtf_cdef_search_picture(struct PictureControlSet *pcs, struct SequenceCont
 /* CUDA device used by contexts the adapters create (default 0). */
 void svtf_adapter_set_device(int device);
 /* 1: keep the picture resident on the GPU between DLF, CDEF search, CDEF apply and CCSO of one pcs (no
- * intermediate download/upload); ccso_frame (or svtf_adapter_download) brings it back.  0 (default): every entry
+ * intermediate download/upload); ccso_frame (or svtf_adapter_fetch) brings it back.  0 (default): every entry
  * point uploads and downloads, i.e. each is a stand-alone drop-in. */
 void svtf_adapter_set_resident(int on);
+/* Copy the resident picture of `pcs` back into `pic` (EbPictureBufferDesc *) — the end of a resident chain that does
+ * not finish with ccso_frame. */
+void svtf_adapter_fetch(const struct PictureControlSet *pcs, void *pic);
 /* Destroy the cached GPU context of a picture (call where the pipeline recycles the pcs). */
 void svtf_adapter_release(const struct PictureControlSet *pcs);
 

@@ -115,3 +115,31 @@ def test_adapters_match_reference(H, orc, adapt, w, h, bd, sb):
         if ref:
             r, rf = ref.ccso_derive_plane(g, p, dbk[0], post[p], src[p], rdmult * base_q)
             assert H.ccso_plane_sig(dout, p) == H.ccso_plane_sig(r, p) and np.array_equal(dflags[p], rf)
+
+
+@pytest.mark.parametrize("w,h,bd,sb,start,kw,resident", [
+    (200, 136, 8, 1, (12, 12, 8, 8), {}, 0),
+    (264, 200, 10, 2, (30, 30, 16, 20), {"early_exit_convergence": 2}, 1),
+    (136, 104, 10, 2, (8, 8, 40, 12), {"search_chroma": 0, "dlf_avg": 1}, 1),
+])
+def test_pick_filter_level_adapter_then_deblock(H, orc, adapt, w, h, bd, sb, start, kw, resident):
+    """svt_av1_pick_filter_level(enhanced_pic, pcs, LPF_PICK_FROM_FULL_IMAGE) followed by svt_av1_loop_filter_frame(recon,
+    pcs, 0, 3), as the DLF kernel calls them (Encoder/Codec/EbDlfProcess.c:101-106)."""
+    from test_lf_search_oracle import blocky_case
+
+    S = H.S
+    g, rec, src, soa = blocky_case(H, w, h, bd, sb, 7300 + w, 6)
+    mi = H.pack_mi(soa)
+    s, keep = _soa(H, soa)
+    lf = S.lf_params((start[0], start[1]), start[2], start[3], sharpness_level=3)
+    cfg = H.L.LfSearchCfg(kw.get("dlf_avg", 0), kw.get("early_exit_convergence", 0), kw.get("only_4x4", 0), kw.get("search_chroma", 1))
+    got = [p.copy() for p in rec]
+    lv = (C.c_int32 * 4)()
+    assert adapt.adapt_pick_and_deblock(C.byref(g), *H._planes(got), *H._planes(src), C.byref(s), C.byref(lf), C.byref(cfg), resident, lv) == 0
+    lf0 = S.lf_params((start[0], start[1]), start[2], start[3], sharpness_level=0)  # the pick resets sharpness (:1136)
+    exp_lv = orc.lf_search(g, rec, src, mi, lf0, **kw)
+    assert list(lv) == exp_lv
+    if H.ref_available():
+        assert list(lv) == H.Ref().lf_search(g, rec, src, soa, lf0, **kw)
+    exp = orc.deblock(g, rec, mi, S.lf_params((exp_lv[0], exp_lv[1]), exp_lv[2], exp_lv[3], sharpness_level=0))
+    assert H.planes_equal(got, exp), H.first_diff(got, exp)
