@@ -1,0 +1,82 @@
+/*
+ * adapter_harness_dec.c — drives the Tier-2 DECODER adapters (svtf_dec_adapters.c) on the same synthetic EbDecHandle the
+ * real decoder functions are driven with in oracle/ref_shim_dec.c (oracle/dec_harness.h); same exported signatures with
+ * the prefix adaptdec_.  TEST INFRASTRUCTURE ONLY.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "EbDecHandle.h"
+#include "EbDecUtils.h"
+#include "EbDecLF.h"
+#include "EbDecCdef.h"
+#include "EbDecCcso.h"
+#include "EbCcso.h"
+
+#include "../include/svtfilt_b200.h"
+#include "../include/svtfilt_b200_adapters.h"
+#include "../oracle/dec_harness.h"
+
+#define API __attribute__((visibility("default")))
+
+API int adaptdec_lf_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const dec_mi_soa *soa,
+                          const svtf_lf_params *lf, int plane_start, int plane_end) {
+    dec_harness h;
+    if (dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    dec_harness_fill_lf(&h, lf);
+    svt_aom_dec_av1_loop_filter_frame(h.dec, h.recon, &h.lf_ctxt, plane_start, plane_end, 0, 1);
+    svtf_dec_adapter_release(h.dec);
+    dec_harness_free(&h);
+    return 0;
+}
+
+API int adaptdec_cdef_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const dec_mi_soa *soa,
+                            const svtf_cdef_params *cdef, const int8_t *fb_idx) {
+    dec_harness h;
+    if (dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    dec_harness_fill_cdef(&h, g, soa, cdef, fb_idx);
+    svt_cdef_frame(h.dec, 1);
+    svtf_dec_adapter_release(h.dec);
+    dec_harness_free(&h);
+    return 0;
+}
+
+API int adaptdec_ccso_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const uint8_t *pre_y, int pre_sy,
+                            const dec_mi_soa *soa, const svtf_ccso_params *p, const uint8_t blk[3]) {
+    dec_harness h;
+    if (g->sample_bytes != 1 || dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    dec_harness_fill_ccso(&h, p, blk);
+    const int es  = g->width + 2 * CCSO_PADDING_SIZE;
+    uint16_t *ext = calloc((size_t)es * (g->height + 2 * CCSO_PADDING_SIZE), sizeof(uint16_t));
+    for (int r = 0; r < g->height; r++)
+        for (int c = 0; c < g->width; c++) ext[(r + CCSO_PADDING_SIZE) * es + c + CCSO_PADDING_SIZE] = pre_y[r * pre_sy + c];
+    /* (the border of ext_rec_y is not read by the adapter: the device clamps coordinates instead) */
+    dec_ccso_frame(h.recon, h.dec, ext);
+    free(ext);
+    svtf_dec_adapter_release(h.dec);
+    dec_harness_free(&h);
+    return 0;
+}
+
+/* The decoder's frame sequence with the frame kept on the device between the stages: LF -> CDEF, then fetch
+ * (Decoder/Codec/EbDecParseObu.c:2382-2428 without CCSO / LR). */
+API int adaptdec_lf_cdef_resident(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const dec_mi_soa *soa,
+                                  const svtf_lf_params *lf, const svtf_cdef_params *cdef, const int8_t *fb_idx) {
+    dec_harness h;
+    if (dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    dec_harness_fill_lf(&h, lf);
+    dec_harness_fill_cdef(&h, g, soa, cdef, fb_idx);
+    svtf_dec_adapter_set_resident(1);
+    svt_aom_dec_av1_loop_filter_frame(h.dec, h.recon, &h.lf_ctxt, 0, 3, 0, 1);
+    svt_cdef_frame(h.dec, 1);
+    svtf_dec_adapter_fetch(h.dec, h.recon);
+    svtf_dec_adapter_set_resident(0);
+    svtf_dec_adapter_release(h.dec);
+    dec_harness_free(&h);
+    return 0;
+}

@@ -1,0 +1,356 @@
+/*
+ * svtf_dec_adapters.c — Tier-2 of the drop-in boundary, decoder side: the reference decoder's frame-level post-recon
+ * filters (same names, same signatures) as thin marshalling over the Tier-1 C ABI (include/svtfilt_b200.h).  Compiled
+ * against the reference's decoder headers; linked INSTEAD of the bodies in
+ *   Decoder/Codec/EbDecLF.c:697    svt_aom_dec_av1_loop_filter_frame
+ *   Decoder/Codec/EbDecCdef.c:507  svt_cdef_frame
+ *   Decoder/Codec/EbDecCcso.c:384  dec_ccso_frame
+ * (decoder section).  The multi-threaded row variants (svt_aom_dec_loop_filter_row EbDecLF.c:650,
+ * svt_cdef_sb_row_mt EbDecCdef.c:385) exist to spread the CPU loops over worker threads with spin-wait row counters; with
+ * the filters on the GPU the frame-level call is made once, from the thread that finishes the frame's reconstruction.
+ *
+ * What an adapter does: (1) flatten the decoder's SB -> block -> transform-unit side info into one packed word per 4x4
+ * (svtf_pack_mi_dec: block size / skip / ref / mode / segment from the covering BlockModeInfo through FrameMiMap, the
+ * transform sizes from LfCtxt.tx_size_l / tx_size_uv, which the parser already keeps per 4x4), (2) upload the picture,
+ * (3) launch, (4) download into the same buffers.  Errors: the reference functions return void; a failing Tier-1 call
+ * logs and aborts — there is no CPU fallback.
+ */
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "EbDecHandle.h"
+#include "EbDecUtils.h"
+#include "EbDecLF.h"
+#include "EbDecCdef.h"
+#include "EbDecCcso.h"
+#include "EbCcso.h"
+
+#include "../include/svtfilt_b200.h"
+#include "../include/svtfilt_b200_adapters.h"
+
+/* 1: reproduce what dec_ccso_frame does today where that is well defined (see dec_ccso_frame below);
+ * 0: the encoder/common definition of CCSO (Common/Codec/EbCcso.c) on the decoder's data */
+#ifndef SVTF_DEC_CCSO_AS_REFERENCE
+#define SVTF_DEC_CCSO_AS_REFERENCE 1
+#endif
+
+#define SVTF_DEC_MAX_CACHED 16
+typedef struct {
+    const EbDecHandle *dec;
+    svtf_ctx          *ctx;
+    svtf_geom          geom;
+    int                resident;  /* the frame being decoded is on the device */
+    int                have_tx;   /* the mi words on the device carry the transform sizes (set by the LF call) */
+} DecSlot;
+static DecSlot         g_slots[SVTF_DEC_MAX_CACHED];
+static pthread_mutex_t g_lock     = PTHREAD_MUTEX_INITIALIZER;
+static int             g_device   = 0;
+static int             g_resident = 0;
+
+void svtf_dec_adapter_set_device(int device) { g_device = device; }
+void svtf_dec_adapter_set_resident(int on) { g_resident = on; }
+
+static void die(const char *where, svtf_ctx *ctx) {
+    fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: %s failed: %s (no CPU fallback on this path)\n", where,
+            svtf_last_error(ctx));
+    abort();
+}
+#define CHECK(call, ctx)       \
+    do {                       \
+        if ((call) != SVTF_OK) \
+            die(#call, ctx);   \
+    } while (0)
+
+static svtf_geom geom_of(const EbDecHandle *dec, const EbPictureBufferDesc *pic) {
+    const FrameHeader *fh = &dec->frame_header;
+    svtf_geom          g;
+    g.width        = fh->frame_size.frame_width; /* the deblock limit, EbDecLF.c:119-124 */
+    g.height       = fh->frame_size.frame_height;
+    g.mi_cols      = fh->mi_cols;
+    g.mi_rows      = fh->mi_rows;
+    g.bit_depth    = pic->bit_depth;
+    g.sample_bytes = (pic->bit_depth > EB_EIGHT_BIT || dec->is_16bit_pipeline) ? 2 : 1;
+    return g;
+}
+
+static DecSlot *slot_for(const EbDecHandle *dec, const EbPictureBufferDesc *pic) {
+    pthread_mutex_lock(&g_lock);
+    DecSlot        *free_slot = NULL, *s = NULL;
+    const svtf_geom g = geom_of(dec, pic);
+    for (int i = 0; i < SVTF_DEC_MAX_CACHED; i++) {
+        if (g_slots[i].dec == dec) {
+            s = &g_slots[i];
+            break;
+        }
+        if (!g_slots[i].dec && !free_slot)
+            free_slot = &g_slots[i];
+    }
+    if (s && memcmp(&s->geom, &g, sizeof(g))) { /* a new sequence / frame size on the same handle */
+        svtf_ctx_destroy(s->ctx);
+        memset(s, 0, sizeof(*s));
+        free_slot = s, s = NULL;
+    }
+    if (!s) {
+        if (!free_slot) {
+            fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: more than %d decoder handles\n", SVTF_DEC_MAX_CACHED);
+            abort();
+        }
+        s       = free_slot;
+        s->dec  = dec;
+        s->geom = g;
+        if (svtf_ctx_create(g_device, &s->geom, &s->ctx) != SVTF_OK)
+            die("svtf_ctx_create", NULL);
+    }
+    pthread_mutex_unlock(&g_lock);
+    return s;
+}
+
+void svtf_dec_adapter_release(const struct EbDecHandle *dec) {
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < SVTF_DEC_MAX_CACHED; i++)
+        if (g_slots[i].dec == dec) {
+            svtf_ctx_destroy(g_slots[i].ctx);
+            memset(&g_slots[i], 0, sizeof(g_slots[i]));
+        }
+    pthread_mutex_unlock(&g_lock);
+}
+
+/* the block covering a 4x4 (what svt_aom_get_cur_mode_info resolves, Decoder/Codec/EbDecNbr.c:39-48) */
+static const BlockModeInfo *mode_at(const EbDecHandle *dec, int mi_row, int mi_col) {
+    const FrameMiMap *m  = &dec->main_frame_buf.frame_mi_map;
+    const int         sh = m->sb_size_log2 - MI_SIZE_LOG2;
+    const SBInfo     *sb = m->pps_sb_info[(mi_row >> sh) * m->sb_cols + (mi_col >> sh)];
+    return &sb->sb_mode_info[m->p_mi_offset[mi_row * m->mi_cols_algnsb + mi_col]];
+}
+
+/* SB/block/TU side info -> packed words.  lf_ctxt == NULL (CDEF-only call): transform sizes are not needed. */
+static void send_mi(DecSlot *s, const EbDecHandle *dec, const LfCtxt *lf_ctxt) {
+    const int    rows = s->geom.mi_rows, cols = s->geom.mi_cols, st = dec->frame_header.mi_stride;
+    const size_t n    = (size_t)rows * cols;
+    uint8_t     *soa  = (uint8_t *)calloc(7, n);
+    svtf_mi_t   *mi   = (svtf_mi_t *)malloc(sizeof(svtf_mi_t) * n);
+    if (!soa || !mi)
+        die("malloc(mi)", s->ctx);
+    uint8_t *bsize = soa, *txy = soa + n, *txuv = soa + 2 * n, *skip = soa + 3 * n, *ref0 = soa + 4 * n, *mode = soa + 5 * n, *seg = soa + 6 * n;
+    for (int r = 0; r < rows; r++)
+        for (int c = 0; c < cols; c++) {
+            const BlockModeInfo *b = mode_at(dec, r, c);
+            const size_t         i = (size_t)r * cols + c;
+            bsize[i] = (uint8_t)b->bsize, skip[i] = (uint8_t)b->skip, ref0[i] = (uint8_t)b->ref_frame[0];
+            mode[i] = (uint8_t)b->mode, seg[i] = (uint8_t)b->segment_id;
+            if (lf_ctxt)
+                txy[i] = (uint8_t)lf_ctxt->tx_size_l[r * st + c], txuv[i] = (uint8_t)lf_ctxt->tx_size_uv[r * st + c];
+        }
+    CHECK(svtf_pack_mi_dec(n, bsize, txy, txuv, skip, ref0, mode, seg, mi), s->ctx);
+    CHECK(svtf_set_mi(s->ctx, mi, cols), s->ctx);
+    CHECK(svtf_sync(s->ctx), s->ctx);
+    s->have_tx = lf_ctxt != NULL;
+    free(soa);
+    free(mi);
+}
+
+static void plane_ptrs(const EbPictureBufferDesc *pic, int sb, void *p[3], int32_t st[3]) {
+    /* visible origin as svt_aom_derive_blk_pointers computes it (Decoder/Codec/EbDecUtils.c:42-78), 4:2:0 */
+    p[0]  = pic->buffer_y + ((size_t)(pic->org_x + pic->org_y * pic->stride_y) * sb);
+    p[1]  = pic->buffer_cb + ((size_t)((pic->org_x >> 1) + (pic->org_y >> 1) * pic->stride_cb) * sb);
+    p[2]  = pic->buffer_cr + ((size_t)((pic->org_x >> 1) + (pic->org_y >> 1) * pic->stride_cr) * sb);
+    st[0] = pic->stride_y, st[1] = pic->stride_cb, st[2] = pic->stride_cr;
+}
+
+static void begin_frame(DecSlot *s, const EbDecHandle *dec, const EbPictureBufferDesc *pic, const LfCtxt *lf_ctxt) {
+    if (g_resident && s->resident) {
+        if (lf_ctxt && !s->have_tx)
+            send_mi(s, dec, lf_ctxt);
+        return;
+    }
+    void   *p[3];
+    int32_t st[3];
+    plane_ptrs(pic, s->geom.sample_bytes, p, st);
+    CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+    CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    send_mi(s, dec, lf_ctxt);
+    s->resident = 1;
+}
+
+static void end_frame(DecSlot *s, const EbPictureBufferDesc *pic) {
+    void   *p[3];
+    int32_t st[3];
+    plane_ptrs(pic, s->geom.sample_bytes, p, st);
+    CHECK(svtf_download_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+}
+
+/* Copy the resident frame back into `pic` (the end of a resident chain). */
+void svtf_dec_adapter_fetch(const struct EbDecHandle *dec, void *pic) {
+    DecSlot *s = slot_for(dec, (const EbPictureBufferDesc *)pic);
+    if (!s->resident) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: svtf_dec_adapter_fetch: no resident frame for this handle\n");
+        abort();
+    }
+    end_frame(s, (const EbPictureBufferDesc *)pic);
+    s->resident = 0;
+}
+
+static void lf_of(const EbDecHandle *dec, svtf_lf_params *out) {
+    const FrameHeader       *fh = &dec->frame_header;
+    const struct LoopFilter *l  = &fh->loop_filter_params;
+    svtf_lf_params           lf;
+    memset(&lf, 0, sizeof(lf));
+    lf.filter_level[0] = l->filter_level[0], lf.filter_level[1] = l->filter_level[1];
+    lf.filter_level_u = l->filter_level_u, lf.filter_level_v = l->filter_level_v;
+    lf.sharpness_level        = l->sharpness_level;
+    lf.mode_ref_delta_enabled = l->mode_ref_delta_enabled;
+    memcpy(lf.ref_deltas, l->ref_deltas, sizeof(lf.ref_deltas));
+    memcpy(lf.mode_deltas, l->mode_deltas, sizeof(lf.mode_deltas));
+    lf.segmentation_enabled = fh->segmentation_params.segmentation_enabled;
+    for (int i = 0; i < 8; i++)
+        for (int f = 0; f < 8; f++) {
+            lf.seg_feature_enabled[i][f] = fh->segmentation_params.feature_enabled[i][f];
+            lf.seg_feature_data[i][f]    = fh->segmentation_params.feature_data[i][f];
+        }
+    lf.delta_lf_present = fh->delta_lf_params.delta_lf_present;
+    lf.delta_lf_multi   = fh->delta_lf_params.delta_lf_multi;
+    *out                = lf;
+}
+
+/* ---------------------------------------------------------------------------------------------------- */
+void svt_aom_dec_av1_loop_filter_frame(EbDecHandle *dec_handle_ptr, EbPictureBufferDesc *recon_picture_buf, LfCtxt *lf_ctxt,
+                                       int32_t plane_start, int32_t plane_end, int32_t is_mt, int enable_flag) {
+    (void)is_mt;
+    if (!enable_flag)
+        return;
+    DecSlot       *s = slot_for(dec_handle_ptr, recon_picture_buf);
+    svtf_lf_params lf;
+    lf_of(dec_handle_ptr, &lf);
+    begin_frame(s, dec_handle_ptr, recon_picture_buf, lf_ctxt);
+    /* the reference filters planes 0 .. plane_end - plane_start - 1 (dec_loop_filter_sb :612, plane loop :296): the
+     * decoder only ever calls it with plane_start = 0 (EbDecParseObu.c:2385-2396) */
+    const int32_t num_planes = plane_end - plane_start;
+    if (lf.delta_lf_present) { /* per-superblock deltas, SBInfo.sb_delta_lf */
+        const MainFrameBuf *mf  = &dec_handle_ptr->main_frame_buf;
+        const int           nsb = mf->sb_cols * mf->sb_rows;
+        int32_t            *d   = (int32_t *)malloc(sizeof(int32_t) * 4 * (size_t)nsb);
+        if (!d)
+            die("malloc(sb_delta_lf)", s->ctx);
+        for (int sb = 0; sb < nsb; sb++)
+            for (int i = 0; i < FRAME_LF_COUNT; i++) d[sb * 4 + i] = mf->cur_frame_bufs[0].sb_info[sb].sb_delta_lf[i];
+        CHECK(svtf_deblock_frame_sb_delta(s->ctx, &lf, 0, num_planes, d, mf->sb_cols, dec_handle_ptr->seq_header.sb_size_log2), s->ctx);
+        free(d);
+    } else
+        CHECK(svtf_deblock_frame(s->ctx, &lf, 0, num_planes), s->ctx);
+    if (!g_resident)
+        end_frame(s, recon_picture_buf), s->resident = 0;
+}
+
+/* ---------------------------------------------------------------------------------------------------- */
+void svt_cdef_frame(EbDecHandle *dec_handle, int enable_flag) {
+    if (!enable_flag)
+        return;
+    EbPictureBufferDesc *recon = dec_handle->cur_pic_buf[0]->ps_pic_buf;
+    DecSlot             *s     = slot_for(dec_handle, recon);
+    const FrameHeader   *fh    = &dec_handle->frame_header;
+    begin_frame(s, dec_handle, recon, NULL);
+    svtf_cdef_params p;
+    memset(&p, 0, sizeof(p));
+    p.cdef_damping = fh->cdef_params.cdef_damping;
+    p.cdef_bits    = fh->cdef_params.cdef_bits;
+    for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++) {
+        p.cdef_y_strength[i]  = (uint8_t)fh->cdef_params.cdef_y_strength[i];
+        p.cdef_uv_strength[i] = (uint8_t)fh->cdef_params.cdef_uv_strength[i];
+    }
+    /* per-64x64 strength index: SBInfo.sb_cdef_strength[quadrant] (svt_cdef_block, EbDecCdef.c:94-116); -1 = not coded */
+    const int           nvfb = (s->geom.mi_rows + 15) / 16, nhfb = (s->geom.mi_cols + 15) / 16;
+    const MainFrameBuf *mf   = &dec_handle->main_frame_buf;
+    const int           b128 = dec_handle->seq_header.sb_size == BLOCK_128X128;
+    int8_t             *idx  = (int8_t *)malloc((size_t)nvfb * nhfb);
+    if (!idx)
+        die("malloc(fb_idx)", s->ctx);
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++) {
+            const SBInfo *sb = b128 ? mf->cur_frame_bufs[0].sb_info + (fbr >> 1) * mf->sb_cols + (fbc >> 1)
+                                    : mf->cur_frame_bufs[0].sb_info + fbr * mf->sb_cols + fbc;
+            idx[fbr * nhfb + fbc] = sb->sb_cdef_strength[b128 ? (fbc & 1) + 2 * (fbr & 1) : 0];
+        }
+    CHECK(svtf_cdef_apply_frame(s->ctx, &p, idx), s->ctx);
+    free(idx);
+    if (!g_resident)
+        end_frame(s, recon), s->resident = 0;
+}
+
+/* ----------------------------------------------------------------------------------------------------
+ * dec_ccso_frame (Decoder/Codec/EbDecCcso.c:384).  The decoder's CCSO is reachable only when a stream signals it (the
+ * encoder's call sites are commented out) and its apply loop differs from the common definition (Common/Codec/EbCcso.c:
+ * 297-622) in ways that look unintended:
+ *   (1) band index: shift_bits = bit_depth in every variant (:51,136,222,310), i.e. band 0 regardless of max_band_log2;
+ *   (2) block flags: the luma variants read sb_ccso_blk_v (:66,152) — `plane == 1 ? _u : _v`;
+ *   (3) block flags are looked up at frame_buf->sb_info + <mi-grid offset of the block> (:63-65), which is inside the SBInfo
+ *       array only for the block at (0,0): defined behaviour exists for pictures of one filter block per plane only
+ *       (<= 256x256 luma);
+ *   (4) samples are addressed from buffer_y/cb/cr without the picture origin (:396-404), i.e. the padding is filtered
+ *       when org_x/org_y are not 0; 8-bit pictures only.
+ * With SVTF_DEC_CCSO_AS_REFERENCE (default) this adapter reproduces (1) and (2) so that its output equals the reference's
+ * wherever the reference is defined (pinned on single-block pictures with a zero origin, tests/test_gpu_dec_adapters.py);
+ * for (3) it takes block (by, bx)'s flag from the superblock that contains the block's top-left sample — where the parser
+ * stores it (EbDecParseBlock.c:357-377) — and for (4) it honours the origin.  Built with SVTF_DEC_CCSO_AS_REFERENCE=0 it
+ * applies the common definition.
+ */
+void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle *dec_handle, uint16_t *ext_rec_y) {
+    DecSlot           *s  = slot_for(dec_handle, frame);
+    const FrameHeader *fh = &dec_handle->frame_header;
+    const CcsoInfo    *ci = &fh->ccso_info;
+    if (s->geom.sample_bytes != 1) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: dec_ccso_frame is defined for 8-bit pictures only (EbDecCcso.c:396)\n");
+        abort();
+    }
+    svtf_ccso_params p;
+    memset(&p, 0, sizeof(p));
+    uint8_t            *flags[3];
+    const MainFrameBuf *mf    = &dec_handle->main_frame_buf;
+    const int           sb_l2 = dec_handle->seq_header.sb_size_log2;
+    const int           W = frame->width, H = frame->height;
+    for (int pl = 0; pl < 3; pl++) {
+        p.ccso_enable[pl] = ci->ccso_enable[pl], p.ccso_bo_only[pl] = ci->ccso_bo_only[pl], p.quant_idx[pl] = ci->quant_idx[pl];
+        p.ext_filter_support[pl] = ci->ext_filter_support[pl], p.edge_clf[pl] = ci->edge_clf[pl];
+        p.max_band_log2[pl] = SVTF_DEC_CCSO_AS_REFERENCE ? 0 : (uint8_t)ci->max_band_log2[pl];
+        memcpy(p.filter_offset[pl], ci->filter_offset[pl], SVTF_CCSO_LUT_SIZE);
+        const int pw = W >> (pl ? 1 : 0), ph = H >> (pl ? 1 : 0), bl = pl ? 7 : 8;
+        const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
+        flags[pl] = (uint8_t *)malloc((size_t)nbx * nby);
+        for (int by = 0; by < nby; by++)
+            for (int bx = 0; bx < nbx; bx++) {
+                const SBInfo *sb = mf->cur_frame_bufs[0].sb_info + ((by << 8) >> sb_l2) * mf->sb_cols + ((bx << 8) >> sb_l2);
+                const int     fp = SVTF_DEC_CCSO_AS_REFERENCE ? (pl == 1 ? 1 : 2) : pl;
+                flags[pl][by * nbx + bx] = fp == 0 ? sb->sb_ccso_blk_y[0] : (fp == 1 ? sb->sb_ccso_blk_u[0] : sb->sb_ccso_blk_v[0]);
+            }
+    }
+    if (!(g_resident && s->resident)) {
+        /* stand-alone call: the classifier input is the caller's ext_rec_y (luma before CDEF, padded by CCSO_PADDING_SIZE,
+         * EbDecParseObu.c:2399-2419): stage it as the pre-CDEF picture with an identity CDEF pass, then put the picture
+         * to correct on top */
+        const int cw = s->geom.mi_cols * 4, chh = s->geom.mi_rows * 4, es = W + 2 * CCSO_PADDING_SIZE;
+        void     *pp[3];
+        int32_t   st[3];
+        plane_ptrs(frame, 1, pp, st);
+        uint8_t *ly = (uint8_t *)malloc((size_t)cw * chh);
+        for (int r = 0; r < chh; r++)
+            for (int c = 0; c < cw; c++)
+                ly[(size_t)r * cw + c] = (uint8_t)ext_rec_y[(size_t)(CCSO_PADDING_SIZE + (r < H ? r : H - 1)) * es + CCSO_PADDING_SIZE + (c < W ? c : W - 1)];
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, ly, cw, pp[1], st[1], pp[2], st[2]), s->ctx);
+        send_mi(s, dec_handle, NULL);
+        svtf_cdef_params idp;
+        memset(&idp, 0, sizeof(idp));
+        const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
+        int8_t   *idx = (int8_t *)calloc(nfb, 1);
+        CHECK(svtf_cdef_apply_frame(s->ctx, &idp, idx), s->ctx);
+        CHECK(svtf_sync(s->ctx), s->ctx);
+        free(idx), free(ly);
+        CHECK(svtf_overwrite_current(s->ctx, pp[0], st[0], pp[1], st[1], pp[2], st[2]), s->ctx);
+    }
+    const uint8_t *cf[3] = {flags[0], flags[1], flags[2]};
+    CHECK(svtf_ccso_apply_frame(s->ctx, &p, cf), s->ctx);
+    end_frame(s, frame);
+    s->resident = 0;
+    for (int pl = 0; pl < 3; pl++) free(flags[pl]);
+}

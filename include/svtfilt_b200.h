@@ -207,6 +207,12 @@ int svtf_rewind(svtf_ctx *ctx);
  * (Encoder/Codec/EbDeblockingFilter.c:624) == svt_aom_dec_av1_loop_filter_frame
  * (Decoder/Codec/EbDecLF.c:697) on the same side info. */
 int svtf_deblock_frame(svtf_ctx *ctx, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end);
+/* The same with per-superblock loop-filter deltas, as the DECODER keeps them (SBInfo.sb_delta_lf, read by
+ * dec_set_lpf_parameters through svt_aom_get_filter_level_delta_lf, Decoder/Codec/EbDecLF.c:159-193,357,548):
+ * sb_delta_lf[sb_rows*sb_cols][4] (FRAME_LF_COUNT entries per superblock, raster order) replaces lf->curr_delta_lf for
+ * the 4x4 units of each superblock when lf->delta_lf_present; sb_size_log2 is 6 or 7. */
+int svtf_deblock_frame_sb_delta(svtf_ctx *ctx, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end,
+                                const int32_t *sb_delta_lf, int32_t sb_cols, int32_t sb_size_log2);
 
 /* svt_av1_cdef_frame(scs, pcs) (Encoder/Codec/EbEncCdef.c:284) == svt_cdef_frame
  * (Decoder/Codec/EbDecCdef.c:507).  fb_strength_idx: one int8 per 64x64 filter block

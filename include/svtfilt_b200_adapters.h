@@ -40,6 +40,20 @@ void svtf_adapter_fetch(const struct PictureControlSet *pcs, void *pic);
 /* Destroy the cached GPU context of a picture (call where the pipeline recycles the pcs). */
 void svtf_adapter_release(const struct PictureControlSet *pcs);
 
+/* ---- decoder side (adapters/svtf_dec_adapters.c; include after EbDecHandle.h) ----
+ *   void svt_aom_dec_av1_loop_filter_frame(EbDecHandle*, EbPictureBufferDesc *recon, LfCtxt*, int32_t plane_start,
+ *                                          int32_t plane_end, int32_t is_mt, int enable_flag);   Decoder/Codec/EbDecLF.c:697
+ *   void svt_cdef_frame(EbDecHandle*, int enable_flag);                                          Decoder/Codec/EbDecCdef.c:507
+ *   void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle*, uint16_t *ext_rec_y);          Decoder/Codec/EbDecCcso.c:384
+ */
+struct EbDecHandle;
+void svtf_dec_adapter_set_device(int device);
+/* 1: the frame stays on the GPU between the LF, CDEF and CCSO calls of one decoder handle; dec_ccso_frame (or
+ * svtf_dec_adapter_fetch) brings it back.  0 (default): every entry point uploads and downloads. */
+void svtf_dec_adapter_set_resident(int on);
+void svtf_dec_adapter_fetch(const struct EbDecHandle *dec, void *pic);
+void svtf_dec_adapter_release(const struct EbDecHandle *dec);
+
 #ifdef __cplusplus
 }
 #endif

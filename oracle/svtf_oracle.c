@@ -235,8 +235,18 @@ ORC_API void orc_lf_build_tables(const svtf_lf_params *lf, lf_tables *t) {
 /* set_lpf_parameters — Encoder/Codec/EbDeblockingFilter.c:162-285.
  * Returns the filter length (0 = none) and the level for the unit at plane position (x,y);
  * *tx_dim_log2 receives log2 of the current unit's transform size along the walk direction. */
-static int lpf_params(const svtf_geom *g, const svtf_mi_t *mi, int mi_stride, const lf_tables *t, int plane, int dir,
-                      int x, int y, int *level, int *tx_dim_log2) {
+/* per-superblock level tables (decoder: SBInfo.sb_delta_lf, Decoder/Codec/EbDecLF.c:159-193; the table of the superblock
+ * containing a unit serves both as "current" and as "left/above" level, :357,548); NULL = one table for the frame */
+typedef struct {
+    const lf_tables *t;
+    int              sb_cols, sb_shift;
+} sb_tables;
+static const lf_tables *lvl_tab(const lf_tables *t, const sb_tables *sbt, int mi_row, int mi_col) {
+    return sbt ? &sbt->t[(mi_row >> sbt->sb_shift) * sbt->sb_cols + (mi_col >> sbt->sb_shift)] : t;
+}
+
+static int lpf_params(const svtf_geom *g, const svtf_mi_t *mi, int mi_stride, const lf_tables *t, const sb_tables *sbt, int plane,
+                      int dir, int x, int y, int *level, int *tx_dim_log2) {
     const int ss = plane ? 1 : 0;
     const int pw = g->width >> ss, ph = g->height >> ss;
     *tx_dim_log2 = 2;
@@ -250,12 +260,13 @@ static int lpf_params(const svtf_geom *g, const svtf_mi_t *mi, int mi_stride, co
     const int coord        = dir == 0 ? x : y;
     if (coord & ((4 << ts) - 1))
         return 0;
-    const int curr_level = t->lvl[plane][MI_SEG(cur)][dir][MI_REF0(cur)][MI_MODE_LF(cur)];
+    const int curr_level = lvl_tab(t, sbt, mi_row, mi_col)->lvl[plane][MI_SEG(cur)][dir][MI_REF0(cur)][MI_MODE_LF(cur)];
     if (!coord)
         return 0;
     const svtf_mi_t prv    = dir == 0 ? mi[mi_row * mi_stride + mi_col - (1 << ss)] : mi[(mi_row - (1 << ss)) * mi_stride + mi_col];
     const int       pv_ts  = dir == 0 ? (plane ? MI_TXW_UV(prv) : MI_TXW_Y(prv)) : (plane ? MI_TXH_UV(prv) : MI_TXH_Y(prv));
-    const int       pv_lvl = t->lvl[plane][MI_SEG(prv)][dir][MI_REF0(prv)][MI_MODE_LF(prv)];
+    const lf_tables *pt    = dir == 0 ? lvl_tab(t, sbt, mi_row, mi_col - (1 << ss)) : lvl_tab(t, sbt, mi_row - (1 << ss), mi_col);
+    const int       pv_lvl = pt->lvl[plane][MI_SEG(prv)][dir][MI_REF0(prv)][MI_MODE_LF(prv)];
     /* plane block size along the direction: get_plane_block_size (Common/Codec/EbUtility.h:86-115);
      * for 4:2:0 every entry of ss_size_lookup[.][1][1] is max(4, dim/2) */
     int bdim = 4 << (dir == 0 ? MI_BW(cur) : MI_BH(cur));
@@ -277,9 +288,8 @@ static int lpf_params(const svtf_geom *g, const svtf_mi_t *mi, int mi_stride, co
  * per superblock (vertical edges of SB x, then horizontal edges of SB x-1); because edges of one
  * pass never overlap this equals "all vertical edges, then all horizontal edges",
  * which is the order used here (and on the GPU).  Checked against the real function. */
-ORC_API int orc_deblock_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr,
-                              const svtf_mi_t *mi, int mi_stride, const svtf_lf_params *lf, int plane_start,
-                              int plane_end) {
+static int deblock_frame_impl(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const svtf_mi_t *mi,
+                              int mi_stride, const svtf_lf_params *lf, int plane_start, int plane_end, const sb_tables *sbt) {
     lf_tables t;
     orc_lf_build_tables(lf, &t);
     plane_t pl[3] = {{y, sy, g->sample_bytes}, {cb, scb, g->sample_bytes}, {cr, scr, g->sample_bytes}};
@@ -298,7 +308,7 @@ ORC_API int orc_deblock_frame(const svtf_geom *g, void *y, int sy, void *cb, int
                 for (int b = 0; b < (dir == 0 ? cw : chh);) {         /* walk along the direction   */
                     const int x = dir == 0 ? b : a, yy = dir == 0 ? a : b;
                     int       level = 0, tlog2 = 2;
-                    const int len = lpf_params(g, mi, mi_stride, &t, plane, dir, x, yy, &level, &tlog2);
+                    const int len = lpf_params(g, mi, mi_stride, &t, sbt, plane, dir, x, yy, &level, &tlog2);
                     if (len) {
                         for (int l = 0; l < 4; l++) {
                             int px[14];
@@ -321,6 +331,34 @@ ORC_API int orc_deblock_frame(const svtf_geom *g, void *y, int sy, void *cb, int
         }
     }
     return 0;
+}
+
+ORC_API int orc_deblock_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr,
+                              const svtf_mi_t *mi, int mi_stride, const svtf_lf_params *lf, int plane_start,
+                              int plane_end) {
+    return deblock_frame_impl(g, y, sy, cb, scb, cr, scr, mi, mi_stride, lf, plane_start, plane_end, NULL);
+}
+
+/* svt_aom_dec_av1_loop_filter_frame with delta_lf_present — Decoder/Codec/EbDecLF.c:697: every superblock carries its
+ * own deltas (sb_delta_lf[sb][FRAME_LF_COUNT]); checked against the real decoder function (tests/test_dec_oracle.py). */
+ORC_API int orc_deblock_frame_sb_delta(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const svtf_mi_t *mi,
+                                       int mi_stride, const svtf_lf_params *lf, int plane_start, int plane_end,
+                                       const int32_t *sb_delta_lf, int sb_cols, int sb_size_log2) {
+    if (!lf->delta_lf_present)
+        return deblock_frame_impl(g, y, sy, cb, scb, cr, scr, mi, mi_stride, lf, plane_start, plane_end, NULL);
+    const int  sb_mi = 1 << (sb_size_log2 - 2), rows = (g->mi_rows + sb_mi - 1) / sb_mi;
+    lf_tables *tabs  = malloc(sizeof(lf_tables) * rows * sb_cols);
+    if (!tabs)
+        return -1;
+    svtf_lf_params l = *lf;
+    for (int sb = 0; sb < rows * sb_cols; sb++) {
+        for (int i = 0; i < 4; i++) l.curr_delta_lf[i] = sb_delta_lf[sb * 4 + i];
+        orc_lf_build_tables(&l, &tabs[sb]);
+    }
+    const sb_tables sbt = {tabs, sb_cols, sb_size_log2 - 2};
+    const int       r   = deblock_frame_impl(g, y, sy, cb, scb, cr, scr, mi, mi_stride, lf, plane_start, plane_end, &sbt);
+    free(tabs);
+    return r;
 }
 
 /* ==========================================================================================

@@ -96,6 +96,8 @@ struct svtf_ctx {
     uint8_t     *d_tab_skip = nullptr;
     int          pick_cap = 0, tab_cap = 0;
     int          sm_count = 0;
+    uint8_t     *d_sb_lvl = nullptr;     // per-superblock deblock level tables (svtf_deblock_frame_sb_delta)
+    size_t       sb_lvl_cap = 0;
     void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
     uint64_t     launches = 0;
     std::string  err;
@@ -216,6 +218,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
+    cudaFree(c->d_sb_lvl);
     if (c->own_stream)
         cudaStreamDestroy(c->own_stream);
     delete c;
@@ -441,7 +444,8 @@ static int need_frame_mi(svtf_ctx *c, const char *fn) {
 
 // only_selected: launch no tiles for planes outside the mask (their samples in the output surface are then undefined;
 // used by the level search, which measures the filtered plane alone) instead of copying them through
-static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end, bool only_selected) {
+static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end, bool only_selected,
+                        const uint8_t *d_sb_lvl = nullptr, int sb_cols = 0, int sb_shift = 0) {
     if (!lf || plane_start < 0 || plane_end > 3 || plane_start > plane_end)
         return c->fail(SVTF_E_ARG, "svtf_deblock_frame: bad arguments");
     if (int r = need_frame_mi(c, "svtf_deblock_frame"))
@@ -485,6 +489,7 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
         total += a.tiles_x[p] * a.tiles_y[p];
     }
     a.plane_mask = mask;
+    a.sb_lvl = d_sb_lvl, a.sb_cols = sb_cols, a.sb_shift = sb_shift;
     build_lf_tables(*lf, a.t);
     if (c->geom.sample_bytes == 1)
         deblock_kernel<uint8_t><<<total, DBK_THREADS, 0, c->stream>>>(a);
@@ -500,6 +505,45 @@ extern "C" int svtf_deblock_frame(svtf_ctx *c, const svtf_lf_params *lf, int32_t
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_deblock_frame: NULL context");
     return deblock_impl(c, lf, plane_start, plane_end, false);
+}
+
+// Deblock with per-superblock loop-filter deltas (the decoder's SBInfo.sb_delta_lf, Decoder/Codec/EbDecLF.c:159-193): one
+// level table per superblock, built on the host exactly like the frame table with that superblock's deltas in place of
+// curr_delta_lf, looked up by the superblock containing each 4x4.
+extern "C" int svtf_deblock_frame_sb_delta(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end,
+                                           const int32_t *sb_delta_lf, int32_t sb_cols, int32_t sb_size_log2) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_deblock_frame_sb_delta: NULL context");
+    if (!lf || !sb_delta_lf || (sb_size_log2 != 6 && sb_size_log2 != 7))
+        return c->fail(SVTF_E_ARG, "svtf_deblock_frame_sb_delta: bad arguments");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_deblock_frame_sb_delta: not available on a striped context");
+    if (!lf->delta_lf_present)
+        return deblock_impl(c, lf, plane_start, plane_end, false);
+    const int sb_mi = 1 << (sb_size_log2 - 2);
+    const int cols = (c->geom.mi_cols + sb_mi - 1) / sb_mi, rows = (c->geom.mi_rows + sb_mi - 1) / sb_mi;
+    if (sb_cols != cols)
+        return c->fail(SVTF_E_ARG, "svtf_deblock_frame_sb_delta: sb_cols does not match the frame");
+    const size_t bytes = (size_t)rows * cols * 768;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->sb_lvl_cap < bytes) {
+        if (c->d_sb_lvl)
+            cudaFree(c->d_sb_lvl);
+        c->d_sb_lvl = nullptr, c->sb_lvl_cap = 0;
+        CUDA_TRY(c, cudaMalloc(&c->d_sb_lvl, bytes));
+        c->sb_lvl_cap = bytes;
+    }
+    std::vector<uint8_t> host(bytes);
+    svtf_lf_params       t = *lf;
+    uint8_t              lim[64], mblim[64], hev[64];
+    for (int sb = 0; sb < rows * cols; sb++) {
+        for (int i = 0; i < 4; i++) t.curr_delta_lf[i] = sb_delta_lf[sb * 4 + i];
+        if (int r = svtf_lf_build_tables(&t, &host[(size_t)sb * 768], lim, mblim, hev))
+            return c->fail(r, "svtf_deblock_frame_sb_delta: bad loop-filter parameters");
+    }
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_sb_lvl, host.data(), bytes, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream)); // `host` goes out of scope
+    return deblock_impl(c, lf, plane_start, plane_end, false, c->d_sb_lvl, cols, sb_size_log2 - 2);
 }
 
 // ---- CCSO parameters -> device (LUT + block flags) --------------------------------------------------

@@ -109,6 +109,9 @@ struct DeblockArgs {
     int              ty0[3];                               // first tile row of the launch (stripe window)
     unsigned         plane_mask;                           // bit p: plane p is filtered (else copied)
     LfTables         t;
+    // per-superblock level tables [sb][plane][256] (delta_lf_present with the decoder's per-SB deltas) or nullptr
+    const uint8_t *sb_lvl;
+    int            sb_cols, sb_shift; // superblocks per row; log2(4x4 units per superblock side)
 };
 
 // One line across an edge; s[k*st], k=-7..6 = p6..p0,q0..q6 (16-bit samples in shared memory).
@@ -190,7 +193,8 @@ __device__ __forceinline__ void lpf_line(uint16_t *s, const int st, const int le
 __device__ __forceinline__ unsigned dbk_edge_params(const svtf_mi_t *__restrict__ mi, const int mi_stride,
                                                     const uint8_t *lvl /* [seg][dir][ref][mlf] of this plane */,
                                                     const int plane, const int dir, const int x, const int y, const int pw,
-                                                    const int ph) {
+                                                    const int ph, const uint8_t *__restrict__ sb_lvl = nullptr, const int sb_cols = 0,
+                                                    const int sb_shift = 0) {
     if (x < 0 || y < 0 || x >= pw || y >= ph)
         return 0;
     const int coord = dir == 0 ? x : y;
@@ -205,11 +209,16 @@ __device__ __forceinline__ unsigned dbk_edge_params(const svtf_mi_t *__restrict_
     const svtf_mi_t prv = dir == 0 ? __ldg(mi + mi_row * mi_stride + mi_col - (1 << ss))
                                    : __ldg(mi + (mi_row - (1 << ss)) * mi_stride + mi_col);
     // lvl index: ((seg*2+dir)*8+ref)*2+mlf ; key = ref | mlf<<3 | seg<<4
-    auto level_of = [&](svtf_mi_t m) {
-        const int key = mi_lvl_key(m);
-        return (int)lvl[(((key >> 4) * 2 + dir) * 8 + (key & 7)) * 2 + ((key >> 3) & 1)];
+    // with per-superblock deltas the table of the superblock that CONTAINS the unit is used, for the current unit and
+    // for its left/top neighbour alike (sb_delta_lf / sb_delta_lf_left / _above, Decoder/Codec/EbDecLF.c:357,548)
+    auto level_of = [&](svtf_mi_t m, int r, int c) {
+        const int key = mi_lvl_key(m), idx = (((key >> 4) * 2 + dir) * 8 + (key & 7)) * 2 + ((key >> 3) & 1);
+        if (sb_lvl)
+            return (int)__ldg(sb_lvl + ((size_t)((r >> sb_shift) * sb_cols + (c >> sb_shift)) * 3 + plane) * 256 + idx);
+        return (int)lvl[idx];
     };
-    const int cur_lvl = level_of(cur), pv_lvl = level_of(prv);
+    const int cur_lvl = level_of(cur, mi_row, mi_col);
+    const int pv_lvl  = dir == 0 ? level_of(prv, mi_row, mi_col - (1 << ss)) : level_of(prv, mi_row - (1 << ss), mi_col);
     int       bdim    = 4 << mi_bdim(cur, dir);
     if (ss)
         bdim = max(4, bdim >> 1);
@@ -268,11 +277,13 @@ __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_const
         for (int i = tid; i < DBK_VUNITS * DBK_EDGES + DBK_EDGES * 16; i += DBK_THREADS) {
             if (i < DBK_VUNITS * DBK_EDGES) {
                 const int u = i / DBK_EDGES, k = i - u * DBK_EDGES;
-                vpar[i] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph);
+                vpar[i] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph, a.sb_lvl, a.sb_cols,
+                                                   a.sb_shift);
             } else {
                 const int j = i - DBK_VUNITS * DBK_EDGES;
                 const int k = j >> 4, u = j & 15;
-                hpar[j] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph);
+                hpar[j] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph, a.sb_lvl, a.sb_cols,
+                                                   a.sb_shift);
             }
         }
         __syncthreads();

@@ -269,8 +269,14 @@ class FilterContext:
         return [(arr[i].ptr, arr[i].pitch, arr[i].width, arr[i].height) for i in range(3)]
 
     # ---- filters (reference entry-point names) ----
-    def loop_filter_frame(self, lf, plane_start=0, plane_end=3):
-        self._chk(self._lib.svtf_deblock_frame(self._h, C.byref(lf), plane_start, plane_end))
+    def loop_filter_frame(self, lf, plane_start=0, plane_end=3, sb_delta_lf=None, sb_size_log2=6):
+        """svt_av1_loop_filter_frame; with sb_delta_lf ([sb_rows, sb_cols, 4] int32) the decoder's per-superblock
+        loop-filter deltas replace lf.curr_delta_lf (svtf_deblock_frame_sb_delta)."""
+        if sb_delta_lf is None:
+            self._chk(self._lib.svtf_deblock_frame(self._h, C.byref(lf), plane_start, plane_end))
+            return
+        d = np.ascontiguousarray(sb_delta_lf, dtype=np.int32)
+        self._chk(self._lib.svtf_deblock_frame_sb_delta(self._h, C.byref(lf), plane_start, plane_end, _ptr(d), d.shape[1], sb_size_log2))
 
     def cdef_frame(self, cdef, fb_strength_idx):
         idx = np.ascontiguousarray(fb_strength_idx, dtype=np.int8)

@@ -134,6 +134,74 @@ def synth_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=
     return soa
 
 
+# TxSize enum (Common/Codec/EbDefinitions.h:852-880) by (width, height)
+TX_DIMS = [(4, 4), (8, 8), (16, 16), (32, 32), (64, 64), (4, 8), (8, 4), (8, 16), (16, 8), (16, 32), (32, 16), (32, 64), (64, 32),
+           (4, 16), (16, 4), (8, 32), (32, 8), (16, 64), (64, 16)]
+TX_OF = {d: i for i, d in enumerate(TX_DIMS)}
+
+
+def _sub_tx(w, h):
+    """sub_tx_size_map: squares halve both sides, 2:1 and 4:1 rectangles halve the long side"""
+    if w == h:
+        return (max(w // 2, 4), max(h // 2, 4))
+    return (w // 2, h) if w > h else (w, h // 2)
+
+
+def synth_dec_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=False, var_tx=True):
+    """The decoder's view of a frame: the blocks of synth_mode_info with explicit per-4x4 transform sizes (TxSize enums) —
+    luma: the largest transform of the block split 0..2 times, per transform unit when var_tx (inter blocks in AV1 carry a
+    transform partition tree); chroma: av1_get_max_uv_txsize of the block that carries the chroma (the one at the odd
+    row/column of an 8x8).  Keys: bsize, tx_size_y, tx_size_uv, skip, ref_frame0, mode, segment_id."""
+    soa = synth_mode_info(geom, seed, p_split, p_skip, p_inter, segments)
+    rng = np.random.default_rng(seed + 77)
+    R, Cc = geom.mi_rows, geom.mi_cols
+    txy = np.zeros((R, Cc), np.uint8)
+
+    def fill(r, c, w, h, depth):
+        if r >= R or c >= Cc:
+            return
+        if depth < 2 and (w, h) != (4, 4) and rng.random() < 0.45:
+            sw, sh = _sub_tx(w, h)
+            for rr in range(r, r + h // 4, sh // 4):
+                for cc in range(c, c + w // 4, sw // 4):
+                    fill(rr, cc, sw, sh, depth + 1)
+        else:
+            txy[r:min(R, r + h // 4), c:min(Cc, c + w // 4)] = TX_OF[(w, h)]
+
+    seen = np.zeros((R, Cc), bool)
+    for r in range(R):
+        for c in range(Cc):
+            if seen[r, c]:
+                continue
+            w, h = BLOCK_DIMS[soa["bsize"][r, c]]
+            seen[r:r + h // 4, c:c + w // 4] = True
+            tw, th = min(w, 64), min(h, 64)
+            inter = soa["ref_frame0"][r, c] > 0
+            if var_tx and inter and not soa["skip"][r, c]:
+                for rr in range(r, r + h // 4, th // 4):
+                    for cc in range(c, c + w // 4, tw // 4):
+                        fill(rr, cc, tw, th, 0)
+            else:
+                d = 0 if (inter and soa["skip"][r, c]) else int(rng.integers(0, 3))
+                for _ in range(d):
+                    tw, th = _sub_tx(tw, th)
+                for rr in range(r, min(R, r + h // 4), th // 4):
+                    for cc in range(c, min(Cc, c + w // 4), tw // 4):
+                        txy[rr:min(R, rr + th // 4), cc:min(Cc, cc + tw // 4)] = TX_OF[(tw, th)]
+    uv_of_bsize = np.zeros(len(BLOCK_DIMS), np.uint8)
+    for i, (w, h) in enumerate(BLOCK_DIMS):
+        uv_of_bsize[i] = TX_OF[(min(max(w // 2, 4), 32), min(max(h // 2, 4), 32))]
+    rr, cc = np.meshgrid(np.arange(R) | 1, np.arange(Cc) | 1, indexing="ij")
+    out = {k: soa[k] for k in ("bsize", "skip", "ref_frame0", "mode", "segment_id")}
+    out["tx_size_y"] = txy
+    out["tx_size_uv"] = uv_of_bsize[soa["bsize"][np.minimum(rr, R - 1), np.minimum(cc, Cc - 1)]]
+    return out
+
+
+def pack_mi_dec(soa):
+    return S.pack_mi_dec(soa["bsize"], soa["tx_size_y"], soa["tx_size_uv"], soa["skip"], soa["ref_frame0"], soa["mode"], soa["segment_id"])
+
+
 def pack_mi(soa):
     return S.pack_mi_enc(soa["bsize"], soa["tx_depth"], soa["skip"], soa["ref_frame0"], soa["mode"], soa["segment_id"])
 
@@ -214,10 +282,15 @@ class Oracle:
         self.lib = C.CDLL(ORC_PATH)
         self.lib.orc_cdef_dist.restype = C.c_uint64
 
-    def deblock(self, geom, planes, mi, lf, plane_start=0, plane_end=3):
+    def deblock(self, geom, planes, mi, lf, plane_start=0, plane_end=3, sb_delta_lf=None, sb_size_log2=6):
         out = [p.copy() for p in planes]
         mi = np.ascontiguousarray(mi, dtype=np.uint32)
-        r = self.lib.orc_deblock_frame(C.byref(geom), *_planes(out), _p(mi), C.c_int(mi.shape[1]), C.byref(lf), plane_start, plane_end)
+        if sb_delta_lf is None:
+            r = self.lib.orc_deblock_frame(C.byref(geom), *_planes(out), _p(mi), C.c_int(mi.shape[1]), C.byref(lf), plane_start, plane_end)
+        else:
+            d = np.ascontiguousarray(sb_delta_lf, dtype=np.int32)
+            r = self.lib.orc_deblock_frame_sb_delta(C.byref(geom), *_planes(out), _p(mi), C.c_int(mi.shape[1]), C.byref(lf), plane_start,
+                                                    plane_end, _p(d), C.c_int(d.shape[1]), C.c_int(sb_size_log2))
         assert r == 0
         return out
 
@@ -417,6 +490,61 @@ class Ref:
         w, h = C.c_int(), C.c_int()
         self.lib.ref_tx_size_dims(tx, C.byref(w), C.byref(h))
         return w.value, h.value
+
+
+REFDEC_PATH = os.path.join(ROOT, "oracle", "_ref", "libsvtrefdec.so")
+
+
+class DecMiSoa(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("bsize", "tx_size_y", "tx_size_uv", "skip", "ref_frame0", "mode", "segment_id")] + [
+        ("mi_stride", C.c_int32), ("sb128", C.c_int32), ("sb_delta_lf", C.c_void_p)]
+
+
+def dec_soa_struct(soa, sb_delta_lf=None):
+    keep = {k: np.ascontiguousarray(soa[k], dtype=np.uint8) for k in ("bsize", "tx_size_y", "tx_size_uv", "skip", "ref_frame0", "mode", "segment_id")}
+    s = DecMiSoa(*[keep[k].ctypes.data for k in ("bsize", "tx_size_y", "tx_size_uv", "skip", "ref_frame0", "mode", "segment_id")],
+                 keep["bsize"].shape[1], 0, None)
+    if sb_delta_lf is not None:
+        keep["d"] = np.ascontiguousarray(sb_delta_lf, dtype=np.int32)
+        s.sb_delta_lf = keep["d"].ctypes.data
+    return s, keep
+
+
+class DecDriver:
+    """The three decoder frame functions behind a library that exports <prefix>_lf_frame / _cdef_frame / _ccso_frame:
+    oracle/_ref/libsvtrefdec.so (prefix refdec: the REAL decoder code) or the adapter test library (prefix adaptdec)."""
+
+    def __init__(self, path=REFDEC_PATH, prefix="refdec"):
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+
+    def _fn(self, name):
+        return getattr(self.lib, f"{self.prefix}_{name}")
+
+    def deblock(self, geom, planes, soa, lf, plane_start=0, plane_end=3, sb_delta_lf=None):
+        out = [p.copy() for p in planes]
+        s, keep = dec_soa_struct(soa, sb_delta_lf)
+        assert self._fn("lf_frame")(C.byref(geom), *_planes(out), C.byref(s), C.byref(lf), plane_start, plane_end) == 0
+        return out
+
+    def cdef_apply(self, geom, planes, soa, cdef, fb_idx):
+        out = [p.copy() for p in planes]
+        s, keep = dec_soa_struct(soa)
+        idx = np.ascontiguousarray(fb_idx, dtype=np.int8)
+        assert self._fn("cdef_frame")(C.byref(geom), *_planes(out), C.byref(s), C.byref(cdef), _p(idx)) == 0
+        return out
+
+    def ccso_apply(self, geom, planes, pre_luma, soa, ccso, blk):
+        out = [p.copy() for p in planes]
+        s, keep = dec_soa_struct(soa)
+        pre = np.ascontiguousarray(pre_luma, dtype=np.uint8)
+        b = (C.c_uint8 * 3)(*blk)
+        assert self._fn("ccso_frame")(C.byref(geom), *_planes(out), _p(pre), C.c_int(pre.shape[1]), C.byref(s), C.byref(ccso), b) == 0
+        return out
+
+
+def refdec_available():
+    return os.path.exists(REFDEC_PATH)
 
 
 def planes_equal(a, b):
