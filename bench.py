@@ -165,6 +165,39 @@ def ccso_derive_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
+def lf_search_leg(H, S, geom, wl, ctx, np, with_cpu):
+    """Deblocking level search (svt_av1_pick_filter_level, LPF_PICK_FROM_FULL_IMAGE): luma + both chroma planes, each a
+    bisection of whole-plane trial deblocks + SSE against the source; the reference's C on a smaller picture."""
+    src = H.synth_source(geom, wl["rec"], 0xB200D1, amp=6)
+    lf = S.lf_params((24, 24), 16, 16)
+    ctx.begin(geom)
+    ctx.upload(wl["rec"])
+    ctx.upload_source(src)
+    ctx.set_mi(wl["mi"])
+    ctx.pick_filter_level(lf)  # warm-up
+    l0 = ctx.launch_count
+    n = 5
+    t0 = time.perf_counter()
+    for _ in range(n):
+        lv = ctx.pick_filter_level(lf)
+    dt = (time.perf_counter() - t0) / n
+    res = {"metric": "deblock level search Mpixel/s (Y, U, V searched; picture resident)", "value": round(geom.width * geom.height / dt / 1e6, 1),
+           "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 3), "gpu_launches_per_picture": (ctx.launch_count - l0) // n,
+           "picked_levels": lv, "cpu_baseline": None}
+    if with_cpu and H.ref_available():
+        g2 = S.make_geom(960, 544, BD)
+        rec = H.synth_picture(g2, 0xD11)
+        org = H.synth_source(g2, rec, 0xD12, amp=6)
+        soa = H.synth_mode_info(g2, 0xD13)
+        ref = H.Ref()
+        t0 = time.perf_counter()
+        ref.lf_search(g2, rec, org, soa, lf)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": round(960 * 544 / dt / 1e6, 2), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                               "sample": "one 960x544 10-bit picture, single thread (the reference's search is serial per picture)"}
+    return res
+
+
 def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search.
     Several pictures are in flight, one context + stream + submitting host thread each — the reference's CDEF stage runs
@@ -320,6 +353,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=12, help="distinct 4K pictures resident per GPU (12 x 24.9 MB x 3 surfaces > L2)")
     ap.add_argument("--e2e-inflight", type=int, default=4)
+    ap.add_argument("--search-inflight", type=int, default=4, help="pictures in flight in the CDEF-search leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -505,8 +539,9 @@ def main():
     e2e_ok = all(np.array_equal(chk[p], pins_out[0].planes[p]) for p in range(3))
     clocks = sampler.stop() if sampler else None
 
-    search = gpu_search_leg(H, S, geom, wls[0], ctxs[:4], max(3, args.steps // 2), np) if rank == 0 else None
+    search = gpu_search_leg(H, S, geom, wls[0], ctxs[:args.search_inflight], max(3, args.steps // 2), np) if rank == 0 else None
     derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
+    lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
@@ -525,7 +560,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:

@@ -26,6 +26,7 @@ struct PickState {
     int      best_bits;
     int      out0[8], out1[8]; // lists of the best cdef_bits so far
     unsigned ticket;           // CTAs of the running accumulate launch that have finished
+    int      wide;             // some table entry is >= 2^31: accumulate with 64-bit sums (else 32-bit, same totals)
 };
 
 struct PickArgs {
@@ -42,59 +43,79 @@ __device__ __forceinline__ uint64_t pick_load(const PickArgs &a, int pl, int fb,
     return (a.bias && i == 0) ? ((uint64_t)(uint16_t)a.bias * v) >> 6 : v;
 }
 
+// State reset (CTA 0), count of searched filter blocks and the width test of the table.  The state is zeroed by a memset
+// ahead of this launch; the fields below are written by disjoint threads / atomics.
 __global__ void __launch_bounds__(PICK_THREADS) pick_init_kernel(const PickArgs a) {
-    __shared__ int s_cnt;
-    if (threadIdx.x == 0)
-        s_cnt = 0;
-    __syncthreads();
-    int c = 0;
-    for (int i = threadIdx.x; i < a.nfb; i += PICK_THREADS) c += a.skip[i] == 0;
-    atomicAdd(&s_cnt, c);
-    for (int i = threadIdx.x; i < 64 * 64; i += PICK_THREADS) a.tot[i] = 0;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        PickState &s = *a.st;
-        for (int i = 0; i < 8; i++) s.lev0[i] = s.lev1[i] = s.out0[i] = s.out1[i] = 0;
-        s.tot_mse = PICK_INF, s.count = s_cnt, s.best_cost = PICK_INF, s.best_bits = 0, s.ticket = 0;
+    int      c = 0;
+    unsigned w = 0;
+    for (int fb = blockIdx.x; fb < a.nfb; fb += gridDim.x) {
+        if (a.skip[fb])
+            continue;
+        c += threadIdx.x == 0;
+        if (threadIdx.x < 128) {
+            const int pl = threadIdx.x >> 6, i = threadIdx.x & 63;
+            if (i < a.end_gi)
+                w |= pick_load(a, pl, fb, i) >> 31 ? 1u : 0u;
+        }
+    }
+    if (__syncthreads_or((int)w) && threadIdx.x == 0)
+        atomicOr(&a.st->wide, 1);
+    if (threadIdx.x == 0 && c)
+        atomicAdd(&a.st->count, c);
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < 64 * 64; i += PICK_THREADS) a.tot[i] = 0;
+        if (threadIdx.x == 0) {
+            PickState &s = *a.st;
+            s.tot_mse = PICK_INF, s.best_cost = PICK_INF;
+        }
     }
 }
 
 // svt_search_one_dual_c, argmin part (first (j,k) in raster order wins ties) + list update + re-zeroing of tot.
 // pos: list slot that receives the pick; rot: rotate the list first; bits >= 0: this was the last call for that
-// cdef_bits -> RD cost and best-so-far update (EbEncCdef.c:845-876).
+// cdef_bits -> RD cost and best-so-far update (EbEncCdef.c:845-876).  Runs in the last CTA of an accumulate launch.
+constexpr int PT_THREADS = 128; // 8 groups of 4 rows x 16 groups of 4 columns: a 32 x 64 slab of tot per CTA
+constexpr int PT_CHUNK   = 32;  // filter blocks per CTA
+
 __device__ __forceinline__ void pick_argmin_body(const PickArgs &a, const int pos, const int rot, const int bits, const int64_t lambda,
                                                  uint64_t *s_v, int *s_i) {
-    const int tid = threadIdx.x;
-    uint64_t  bv = ~(uint64_t)0;
-    int       bi = 1 << 30;
-    uint64_t tv[64 * 64 / PICK_THREADS];
+    const int     tid = threadIdx.x;
+    uint64_t      bv  = ~(uint64_t)0;
+    int           bi  = 1 << 30;
+    constexpr int PER = 64 * 64 / PT_THREADS;
 #pragma unroll
-    for (int n = 0; n < 64 * 64 / PICK_THREADS; n++) tv[n] = __ldcg(&a.tot[tid + n * PICK_THREADS]); // other CTAs' atomics: read at L2
+    for (int h = 0; h < 2; h++) { // two batches of 16 loads in flight (other CTAs' atomics: read at L2)
+        uint64_t tv[PER / 2];
 #pragma unroll
-    for (int n = 0; n < 64 * 64 / PICK_THREADS; n++) {
-        const int i = tid + n * PICK_THREADS, j = i >> 6, k = i & 63;
-        a.tot[i] = 0;
-        if (j < a.end_gi && k < a.end_gi && (tv[n] < bv || (tv[n] == bv && i < bi)))
-            bv = tv[n], bi = i;
-    }
-    s_v[tid] = bv, s_i[tid] = bi;
-    __syncthreads();
-    for (int s = PICK_THREADS / 2; s > 0; s >>= 1) {
-        if (tid < s) {
-            const uint64_t v = s_v[tid + s];
-            const int      i = s_i[tid + s];
-            if (v < s_v[tid] || (v == s_v[tid] && i < s_i[tid]))
-                s_v[tid] = v, s_i[tid] = i;
+        for (int n = 0; n < PER / 2; n++) tv[n] = __ldcg(&a.tot[tid + (h * (PER / 2) + n) * PT_THREADS]);
+#pragma unroll
+        for (int n = 0; n < PER / 2; n++) {
+            const int i = tid + (h * (PER / 2) + n) * PT_THREADS, j = i >> 6, k = i & 63;
+            a.tot[i] = 0;
+            if (j < a.end_gi && k < a.end_gi && (tv[n] < bv || (tv[n] == bv && i < bi)))
+                bv = tv[n], bi = i;
         }
-        __syncthreads();
     }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+        const uint64_t v = __shfl_xor_sync(0xffffffffu, bv, m);
+        const int      i = __shfl_xor_sync(0xffffffffu, bi, m);
+        if (v < bv || (v == bv && i < bi))
+            bv = v, bi = i;
+    }
+    if ((tid & 31) == 0)
+        s_v[tid >> 5] = bv, s_i[tid >> 5] = bi;
+    __syncthreads();
     if (tid == 0) {
+        for (int w = 1; w < PT_THREADS / 32; w++)
+            if (s_v[w] < bv || (s_v[w] == bv && s_i[w] < bi))
+                bv = s_v[w], bi = s_i[w];
         PickState &s = *a.st;
         // the scan in the C code starts from best = 1<<63 with a strict "<": totals >= 1<<63 never win and (0,0) stays
         int      b0 = 0, b1 = 0;
         uint64_t best = PICK_INF;
-        if (s_v[0] < PICK_INF)
-            best = s_v[0], b0 = s_i[0] >> 6, b1 = s_i[0] & 63;
+        if (bv < PICK_INF)
+            best = bv, b0 = bi >> 6, b1 = bi & 63;
         if (rot)
             for (int j = 0; j < pos; j++) s.lev0[j] = s.lev0[j + 1], s.lev1[j] = s.lev1[j + 1];
         s.lev0[pos] = b0, s.lev1[pos] = b1;
@@ -114,56 +135,102 @@ __device__ __forceinline__ void pick_argmin_body(const PickArgs &a, const int po
     }
 }
 
-// svt_search_one_dual_c, accumulation part.  nb entries of the list are fixed; `rot` = 1 reads them one position
-// further (the refinement step drops entry 0, EbEncCdef.c:717-722).  CTA (tile, chunk): a 16x16 tile of tot over a
-// chunk of 64 filter blocks; thread (tj, tk) owns one entry.  One u64 atomic per entry and CTA.
-constexpr int PICK_CHUNK = 64;
+// svt_search_one_dual_c, accumulation part: tot[j][k] += min(best_so_far(fb), mse0[fb][j] + mse1[fb][k]) over the
+// searched filter blocks.  nb entries of the list are fixed; `rot` = 1 reads them one position further (the refinement
+// step drops entry 0, EbEncCdef.c:717-722).  CTA (half, chunk): rows [32*half, 32*half+32) of tot over PT_CHUNK filter
+// blocks; a thread keeps a 4 x 4 register tile of tot, so one filter block costs it 5 shared loads and 16 min-adds.
+//
+// The 75 calls of a picture are a dependent chain, so the latency of one call is what counts:
+//  * the table rows of the chunk do not depend on the previous call: they are staged (16-byte loads, all in flight) BEFORE
+//    cudaGridDependencySynchronize(), and every launch carries the programmatic-stream-serialization attribute, so launch
+//    latency and staging overlap the previous call's atomics / argmin tail;
+//  * after the dependency only the 16 list entries are read from global memory; best_so_far comes from shared memory.
+// narrow (every table entry below 2^31, PickState.wide == 0): the sum fits 32 bits and min(a + b, best) is one VIADDMNMX;
+// the totals are u64 either way, so both variants give the C code's numbers.
+template <bool NARROW>
+__device__ __forceinline__ void pick_tot_loop(const uint64_t (*srow)[128], const uint64_t *sbest, const int jt, uint64_t (&acc)[4][4]) {
+    const int tid = threadIdx.x, tj = tid >> 4, tk = tid & 15;
+#pragma unroll 2
+    for (int f = 0; f < PT_CHUNK; f++) {
+        uint64_t av[4], bv[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) av[r] = srow[f][jt + tj * 4 + r], bv[r] = srow[f][64 + tk * 4 + r];
+        const uint64_t bst = sbest[f];
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                if (NARROW)
+                    acc[r][c] += __viaddmin_u32((unsigned)av[r], (unsigned)bv[c], (unsigned)bst);
+                else
+                    acc[r][c] += min(bst, av[r] + bv[c]);
+            }
+    }
+}
+
 // The CTA that finishes last (ticket counter, no waiting) runs the argmin + list update of the same call.
-__global__ void __launch_bounds__(PICK_THREADS) pick_tot_kernel(const PickArgs a, const int nb, const int rot, const int pos, const int bits,
-                                                                const int64_t lambda) {
-    __shared__ uint64_t sa[PICK_CHUNK][16], sb[PICK_CHUNK][16], sbest[PICK_CHUNK];
-    __shared__ uint8_t  svalid[PICK_CHUNK];
-    __shared__ int      s_last;
-    const int tid = threadIdx.x;
-    const int jt = (blockIdx.x >> 2) * 16, kt = (blockIdx.x & 3) * 16, fb0 = blockIdx.y * PICK_CHUNK;
-    if (jt < a.end_gi && kt < a.end_gi) {
-    for (int i = tid; i < PICK_CHUNK * 32; i += PICK_THREADS) {
-        const int f = i >> 5, e = i & 31, fb = fb0 + f;
-        if (fb < a.nfb && !a.skip[fb]) {
-            if (e < 16)
-                sa[f][e] = pick_load(a, 0, fb, jt + e);
-            else
-                sb[f][e - 16] = pick_load(a, 1, fb, kt + e - 16);
+__global__ void __launch_bounds__(PT_THREADS) pick_tot_kernel(const PickArgs a, const int nb, const int rot, const int pos, const int bits,
+                                                              const int64_t lambda) {
+    __shared__ __align__(16) uint64_t srow[PT_CHUNK][128]; // [fb][plane 0: 64 strengths | plane 1: 64 strengths]
+    __shared__ uint64_t               sbest[PT_CHUNK];
+    __shared__ int                    s_last;
+    const int  tid = threadIdx.x, jt = blockIdx.x * 32, fb0 = blockIdx.y * PT_CHUNK;
+    const bool active = jt < a.end_gi;
+    if (active) {
+        // rows of the chunk, skipped or not (a skipped block gets best = 0 below and then adds min(0, .) = 0)
+        constexpr int VPT = PT_CHUNK * 64 / PT_THREADS; // 16-byte vectors per thread
+        ulonglong2    v[VPT];
+#pragma unroll
+        for (int n = 0; n < VPT; n++) {
+            const int i = tid + n * PT_THREADS, f = i >> 6, e = i & 63, fb = min(fb0 + f, a.nfb - 1);
+            v[n] = __ldg(reinterpret_cast<const ulonglong2 *>(a.mse + ((size_t)(e >> 5) * a.nfb + fb) * 64) + (e & 31));
+        }
+#pragma unroll
+        for (int n = 0; n < VPT; n++) {
+            const int i = tid + n * PT_THREADS, f = i >> 6, e = i & 63;
+            if (a.bias && (e & 31) == 0)
+                v[n].x = ((uint64_t)(uint16_t)a.bias * v[n].x) >> 6; // entry 0 of a row, EbEncCdef.c:776-789
+            *reinterpret_cast<ulonglong2 *>(&srow[f][2 * e]) = v[n];
         }
     }
-    if (tid < PICK_CHUNK) {
-        const int  fb = fb0 + tid;
-        const bool ok = fb < a.nfb && !a.skip[fb];
-        // all list entries first, then all table loads: two dependent memory round trips instead of 2*nb
-        int l0[8], l1[8];
+    uint8_t skp = 1;
+    if (tid < PT_CHUNK && fb0 + tid < a.nfb)
+        skp = a.skip[fb0 + tid];
+    cudaGridDependencySynchronize(); // the previous call's list update and the re-zeroed tot are visible from here on
+    if (active) {
+        __syncthreads();
+        const bool narrow = !a.st->wide;
+        if (tid < PT_CHUNK) {
+            uint64_t best = 0;
+            if (!skp) {
+                best = narrow ? 0xffffffffull : PICK_INF;
 #pragma unroll
-        for (int g = 0; g < 8; g++) l0[g] = a.st->lev0[min(g + rot, 7)], l1[g] = a.st->lev1[min(g + rot, 7)];
-        uint64_t va[8], vb[8];
-#pragma unroll
-        for (int g = 0; g < 8; g++) {
-            const bool use = ok && g < nb;
-            va[g] = use ? pick_load(a, 0, fb, l0[g]) : PICK_INF, vb[g] = use ? pick_load(a, 1, fb, l1[g]) : 0;
+                for (int g = 0; g < 8; g++)
+                    if (g < nb)
+                        best = min(best, srow[tid][a.st->lev0[min(g + rot, 7)]] + srow[tid][64 + a.st->lev1[min(g + rot, 7)]]);
+            }
+            sbest[tid] = best;
         }
-        uint64_t best = PICK_INF;
+        __syncthreads();
+        uint64_t acc[4][4];
 #pragma unroll
-        for (int g = 0; g < 8; g++) best = min(best, va[g] + vb[g]);
-        sbest[tid]  = best;
-        svalid[tid] = ok;
-    }
-    __syncthreads();
-    const int tj = tid >> 4, tk = tid & 15;
-    uint64_t  acc = 0;
-#pragma unroll 4
-    for (int f = 0; f < PICK_CHUNK; f++)
-        if (svalid[f])
-            acc += min(sbest[f], sa[f][tj] + sb[f][tk]);
-    if (jt + tj < a.end_gi && kt + tk < a.end_gi && acc)
-        atomicAdd(reinterpret_cast<unsigned long long *>(&a.tot[(jt + tj) * 64 + kt + tk]), (unsigned long long)acc);
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[r][c] = 0;
+        if (narrow)
+            pick_tot_loop<true>(srow, sbest, jt, acc);
+        else
+            pick_tot_loop<false>(srow, sbest, jt, acc);
+        cudaTriggerProgrammaticLaunchCompletion(); // the next call may launch and stage its rows now
+        const int tj = tid >> 4, tk = tid & 15;
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int j = jt + tj * 4 + r, k = tk * 4 + c;
+                if (j < a.end_gi && k < a.end_gi && acc[r][c])
+                    atomicAdd(reinterpret_cast<unsigned long long *>(&a.tot[j * 64 + k]), (unsigned long long)acc[r][c]);
+            }
     }
     __threadfence();
     __syncthreads();
@@ -172,7 +239,7 @@ __global__ void __launch_bounds__(PICK_THREADS) pick_tot_kernel(const PickArgs a
     __syncthreads();
     if (s_last) {
         __threadfence();
-        pick_argmin_body(a, pos, rot, bits, lambda, &sa[0][0], reinterpret_cast<int *>(&sb[0][0]));
+        pick_argmin_body(a, pos, rot, bits, lambda, &srow[0][0], reinterpret_cast<int *>(&srow[1][0]));
     }
 }
 
@@ -199,21 +266,34 @@ __global__ void __launch_bounds__(PICK_THREADS) pick_assign_kernel(const PickArg
 
 // Enqueues the whole schedule of finish_cdef_search on `stream` (77 small launches, no host synchronisation).
 inline cudaError_t pick_enqueue(const PickArgs &a, int8_t *d_fb_idx, int64_t lambda, int sm_count, cudaStream_t stream, uint64_t *launches) {
-    (void)sm_count;
-    const dim3 grid(16, (a.nfb + PICK_CHUNK - 1) / PICK_CHUNK);
-    pick_init_kernel<<<1, PICK_THREADS, 0, stream>>>(a);
-    uint64_t n = 1;
-    for (int bits = 0; bits <= 3; bits++) {
+    cudaError_t e = cudaMemsetAsync(a.st, 0, sizeof(PickState), stream);
+    if (e != cudaSuccess)
+        return e;
+    pick_init_kernel<<<max(1, min(a.nfb, 2 * max(sm_count, 1))), PICK_THREADS, 0, stream>>>(a);
+    uint64_t           n = 1;
+    cudaLaunchAttribute attr[1];
+    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(2, (a.nfb + PT_CHUNK - 1) / PT_CHUNK);
+    cfg.blockDim           = dim3(PT_THREADS);
+    cfg.dynamicSmemBytes   = 0;
+    cfg.stream             = stream;
+    cfg.attrs              = attr;
+    cfg.numAttrs           = 1;
+    for (int bits = 0; bits <= 3 && e == cudaSuccess; bits++) {
         const int nb = 1 << bits;
-        for (int k = 0; k < nb; k++) { // joint_strength_search_dual: greedy fill
-            pick_tot_kernel<<<grid, PICK_THREADS, 0, stream>>>(a, k, 0, k, -1, lambda);
+        for (int k = 0; k < nb && e == cudaSuccess; k++) { // joint_strength_search_dual: greedy fill
+            e = cudaLaunchKernelEx(&cfg, pick_tot_kernel, a, k, 0, k, -1, lambda);
             n += 1;
         }
-        for (int k = 0; k < 4 * nb; k++) { // refinement: drop the oldest entry, re-pick the last
-            pick_tot_kernel<<<grid, PICK_THREADS, 0, stream>>>(a, nb - 1, 1, nb - 1, k == 4 * nb - 1 ? bits : -1, lambda);
+        for (int k = 0; k < 4 * nb && e == cudaSuccess; k++) { // refinement: drop the oldest entry, re-pick the last
+            e = cudaLaunchKernelEx(&cfg, pick_tot_kernel, a, nb - 1, 1, nb - 1, k == 4 * nb - 1 ? bits : -1, lambda);
             n += 1;
         }
     }
+    if (e != cudaSuccess)
+        return e;
     pick_assign_kernel<<<(a.nfb + PICK_THREADS - 1) / PICK_THREADS, PICK_THREADS, 0, stream>>>(a, d_fb_idx);
     if (launches)
         *launches += n + 1;
