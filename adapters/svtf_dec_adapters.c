@@ -10,7 +10,7 @@
  * the filters on the GPU the frame-level call is made once, from the thread that finishes the frame's reconstruction.
  *
  * What an adapter does: (1) flatten the decoder's SB -> block -> transform-unit side info into one packed word per 4x4
- * (svtf_pack_mi_dec: block size / skip / ref / mode / segment from the covering BlockModeInfo through FrameMiMap, the
+ * (svtf_set_mi_soa_dec: block size / skip / ref / mode / segment from the covering BlockModeInfo through FrameMiMap, the
  * transform sizes from LfCtxt.tx_size_l / tx_size_uv, which the parser already keeps per 4x4), (2) upload the picture,
  * (3) launch, (4) download into the same buffers.  Errors: the reference functions return void; a failing Tier-1 call
  * logs and aborts — there is no CPU fallback.
@@ -130,8 +130,7 @@ static void send_mi(DecSlot *s, const EbDecHandle *dec, const LfCtxt *lf_ctxt) {
     const int    rows = s->geom.mi_rows, cols = s->geom.mi_cols, st = dec->frame_header.mi_stride;
     const size_t n    = (size_t)rows * cols;
     uint8_t     *soa  = (uint8_t *)calloc(7, n);
-    svtf_mi_t   *mi   = (svtf_mi_t *)malloc(sizeof(svtf_mi_t) * n);
-    if (!soa || !mi)
+    if (!soa)
         die("malloc(mi)", s->ctx);
     uint8_t *bsize = soa, *txy = soa + n, *txuv = soa + 2 * n, *skip = soa + 3 * n, *ref0 = soa + 4 * n, *mode = soa + 5 * n, *seg = soa + 6 * n;
     for (int r = 0; r < rows; r++)
@@ -143,12 +142,10 @@ static void send_mi(DecSlot *s, const EbDecHandle *dec, const LfCtxt *lf_ctxt) {
             if (lf_ctxt)
                 txy[i] = (uint8_t)lf_ctxt->tx_size_l[r * st + c], txuv[i] = (uint8_t)lf_ctxt->tx_size_uv[r * st + c];
         }
-    CHECK(svtf_pack_mi_dec(n, bsize, txy, txuv, skip, ref0, mode, seg, mi), s->ctx);
-    CHECK(svtf_set_mi(s->ctx, mi, cols), s->ctx);
+    CHECK(svtf_set_mi_soa_dec(s->ctx, bsize, txy, txuv, skip, ref0, mode, seg, cols), s->ctx); /* packed on the device */
     CHECK(svtf_sync(s->ctx), s->ctx);
     s->have_tx = lf_ctxt != NULL;
     free(soa);
-    free(mi);
 }
 
 static void plane_ptrs(const EbPictureBufferDesc *pic, int sb, void *p[3], int32_t st[3]) {

@@ -120,11 +120,10 @@ void svtf_adapter_release(const PictureControlSet *pcs) {
 /* mi_grid_base -> packed words (the fields set_lpf_parameters and svt_sb_compute_cdef_list read:
  * EbDeblockingFilter.c:187-260, EbEncCdef.c:267-270). */
 static void send_mi(CtxSlot *s, const PictureControlSet *pcs) {
-    const int  rows = s->geom.mi_rows, cols = s->geom.mi_cols;
-    const size_t n  = (size_t)rows * cols;
-    uint8_t   *soa  = (uint8_t *)malloc(6 * n);
-    svtf_mi_t *mi   = (svtf_mi_t *)malloc(sizeof(svtf_mi_t) * n);
-    if (!soa || !mi)
+    const int    rows = s->geom.mi_rows, cols = s->geom.mi_cols;
+    const size_t n    = (size_t)rows * cols;
+    uint8_t     *soa  = (uint8_t *)malloc(6 * n);
+    if (!soa)
         die("malloc(mi)", s->ctx);
     uint8_t *bsize = soa, *txd = soa + n, *skip = soa + 2 * n, *ref0 = soa + 3 * n, *mode = soa + 4 * n, *seg = soa + 5 * n;
     for (int r = 0; r < rows; r++)
@@ -134,11 +133,11 @@ static void send_mi(CtxSlot *s, const PictureControlSet *pcs) {
             bsize[i] = (uint8_t)b->bsize, txd[i] = b->tx_depth, skip[i] = b->skip;
             ref0[i] = (uint8_t)b->ref_frame[0], mode[i] = (uint8_t)b->mode, seg[i] = (uint8_t)b->segment_id;
         }
-    CHECK(svtf_pack_mi_enc(n, bsize, txd, skip, ref0, mode, seg, mi), s->ctx);
-    CHECK(svtf_set_mi(s->ctx, mi, cols), s->ctx);
-    CHECK(svtf_sync(s->ctx), s->ctx); /* mi/soa are freed below */
+    /* byte planes up, packed on the device (an encoder that keeps these six planes next to mi_grid_base — written where
+     * EncDec updates the mode info of a block — passes them here directly and this loop disappears) */
+    CHECK(svtf_set_mi_soa_enc(s->ctx, bsize, txd, skip, ref0, mode, seg, cols), s->ctx);
+    CHECK(svtf_sync(s->ctx), s->ctx); /* soa is freed below */
     free(soa);
-    free(mi);
 }
 
 static void plane_ptrs(const EbPictureBufferDesc *pic, int sb, void *p[3], int32_t st[3]) {

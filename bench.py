@@ -198,6 +198,44 @@ def lf_search_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
+def side_info_leg(H, S, geom, ctx, np):
+    """Side info to the device: host packer + 4 B per 4x4 over PCIe (svtf_pack_mi_enc + svtf_set_mi) against byte planes
+    + packing on the device (svtf_set_mi_soa_enc, 1.5 B per 4x4)."""
+    soa = H.synth_mode_info(geom, 0xB200E1)
+    keys = ("bsize", "tx_depth", "skip", "ref_frame0", "mode", "segment_id")
+    pins = {k: S.PinnedArray(soa[k].shape, np.uint8) for k in keys}
+    for k in keys:
+        pins[k].array[...] = soa[k]
+    psoa = {k: pins[k].array for k in keys}
+    pin_mi = S.PinnedArray(soa["bsize"].shape, np.uint32)
+    ctx.begin(geom)
+    n = 10
+
+    def timed(fn):
+        fn()
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fn()
+        ctx.sync()
+        return (time.perf_counter() - t0) / n * 1e3
+
+    def host_path():
+        pin_mi.array[...] = H.pack_mi(psoa)
+        ctx.set_mi(pin_mi.array)
+
+    t_host = timed(host_path)
+    t_up = timed(lambda: ctx.set_mi(pin_mi.array))
+    t_soa = timed(lambda: ctx.set_mi_soa(psoa))
+    same = bool(np.array_equal(ctx.get_mi(), H.pack_mi(soa)))
+    for k in keys:
+        pins[k].close()
+    pin_mi.close()
+    return {"metric": "side info of one 4K picture to the device, ms", "host_pack_plus_upload_ms": round(t_host, 3), "packed_upload_only_ms": round(t_up, 3),
+            "byte_planes_plus_device_pack_ms": round(t_soa, 3), "device_words_equal_host_words": same,
+            "bytes_per_4x4": {"packed": 4, "byte_planes": 6}}
+
+
 def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search.
     Several pictures are in flight, one context + stream + submitting host thread each — the reference's CDEF stage runs
@@ -541,6 +579,7 @@ def main():
 
     search = gpu_search_leg(H, S, geom, wls[0], ctxs[:args.search_inflight], max(3, args.steps // 2), np) if rank == 0 else None
     derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
+    side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
     lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -560,7 +599,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:

@@ -63,7 +63,7 @@ class DevPlane(C.Structure):
 
 # every symbol include/svtfilt_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
-    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
+    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_set_mi_soa_enc", "svtf_set_mi_soa_dec", "svtf_get_mi", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
@@ -100,6 +100,9 @@ def load():
         f.argtypes = [vp, vp, i32, vp, i32, vp, i32]
     lib.svtf_set_mi.argtypes = [vp, vp, i32]
     lib.svtf_rewind.argtypes = [vp]
+    lib.svtf_set_mi_soa_enc.argtypes = [vp] + [vp] * 6 + [i32]
+    lib.svtf_set_mi_soa_dec.argtypes = [vp] + [vp] * 7 + [i32]
+    lib.svtf_get_mi.argtypes = [vp, vp, i32]
     lib.svtf_deblock_frame.argtypes = [vp, C.POINTER(LfParams), i32, i32]
     lib.svtf_deblock_frame_sb_delta.argtypes = [vp, C.POINTER(LfParams), i32, i32, vp, i32, i32]
     lib.svtf_cdef_apply_frame.argtypes = [vp, C.POINTER(CdefParams), vp]

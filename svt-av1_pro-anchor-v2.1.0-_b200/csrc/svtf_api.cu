@@ -19,6 +19,7 @@
 #include "svtf_pick.cuh"
 #include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
+#include "svtf_mi_pack.cuh"
 
 namespace svtf {
 
@@ -96,6 +97,9 @@ struct svtf_ctx {
     uint8_t     *d_tab_skip = nullptr;
     int          pick_cap = 0, tab_cap = 0;
     int          sm_count = 0;
+    int         *h_mi_bad = nullptr;     // pinned: "invalid enum" flag of the last svtf_set_mi_soa_*
+    uint8_t     *d_mi_soa = nullptr;     // byte planes of svtf_set_mi_soa_* (7 x mi_rows x mi_stride) + 4 bytes error flag
+    size_t       mi_soa_cap = 0;
     uint8_t     *d_sb_lvl = nullptr;     // per-superblock deblock level tables (svtf_deblock_frame_sb_delta)
     size_t       sb_lvl_cap = 0;
     void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
@@ -218,17 +222,21 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
-    cudaFree(c->d_sb_lvl);
+    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa);
+    if (c->h_mi_bad)
+        cudaFreeHost(c->h_mi_bad);
     if (c->own_stream)
         cudaStreamDestroy(c->own_stream);
     delete c;
 }
 
+static int mi_soa_check(svtf_ctx *c);
+
 extern "C" int svtf_sync(svtf_ctx *c) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_sync: NULL context");
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    return SVTF_OK;
+    return mi_soa_check(c);
 }
 
 extern "C" int svtf_ctx_set_stream(svtf_ctx *c, void *cuda_stream) {
@@ -395,6 +403,132 @@ extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) 
     return SVTF_OK;
 }
 
+// ---- side info as byte planes, packed on the device (svtf_mi_pack.cuh) --------------------------------------
+static const MiPackTables &mi_pack_tables() {
+    static MiPackTables   t;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        // every geometry combination through the host packers: the device words are the host words by construction
+        for (int si = 0; si < 2; si++)
+            for (int td = 0; td < 3; td++)
+                for (int bs = 0; bs < 22; bs++) {
+                    const uint8_t b = (uint8_t)bs, d = (uint8_t)td, sk = (uint8_t)si, rf = (uint8_t)si;
+                    svtf_mi_t     w = 0;
+                    svtf_pack_mi_enc(1, &b, &d, &sk, &rf, nullptr, nullptr, &w);
+                    t.enc_geom[si][td][bs] = w & 0x3ffffu;
+                }
+        for (int bs = 0; bs < 22; bs++) {
+            const uint8_t b = (uint8_t)bs, z = 0;
+            svtf_mi_t     w = 0;
+            svtf_pack_mi_dec(1, &b, &z, &z, nullptr, nullptr, nullptr, nullptr, &w);
+            t.blk_geom[bs] = w & (0x3fu << 12);
+        }
+        for (int tx = 0; tx < 19; tx++) {
+            const uint8_t b = 0, x = (uint8_t)tx, z = 0;
+            svtf_mi_t     w = 0;
+            svtf_pack_mi_dec(1, &b, &x, &z, nullptr, nullptr, nullptr, nullptr, &w);
+            t.tx_y[tx] = w & 0x3fu;
+            svtf_pack_mi_dec(1, &b, &z, &x, nullptr, nullptr, nullptr, nullptr, &w);
+            t.tx_uv[tx] = w & (0x3fu << 6);
+        }
+        t.mode_lf = 0;
+        for (int m = 0; m < 32; m++) {
+            const uint8_t b = 0, z = 0, md = (uint8_t)m;
+            svtf_mi_t     w = 0;
+            svtf_pack_mi_dec(1, &b, &z, &z, nullptr, nullptr, &md, nullptr, &w);
+            t.mode_lf |= ((w >> 23) & 1u) << m;
+        }
+    });
+    return t;
+}
+
+static int set_mi_soa(svtf_ctx *c, const uint8_t *const planes[7], int nplanes, int32_t stride, bool dec, const char *who) {
+    if (!c->have_geom)
+        return c->fail(SVTF_E_STATE, std::string(who) + ": call svtf_frame_begin first");
+    for (int p = 0; p < nplanes; p++)
+        if (!planes[p])
+            return c->fail(SVTF_E_ARG, std::string(who) + ": NULL plane");
+    if (stride < c->geom.mi_cols)
+        return c->fail(SVTF_E_ARG, std::string(who) + ": stride smaller than mi_cols");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    const int    rows = c->geom.mi_rows, cols = c->geom.mi_cols;
+    const size_t plane_bytes = (size_t)rows * cols, need = 7 * plane_bytes + 16;
+    if (c->mi_soa_cap < need) {
+        if (c->d_mi_soa)
+            cudaFree(c->d_mi_soa);
+        c->d_mi_soa = nullptr, c->mi_soa_cap = 0;
+        CUDA_TRY(c, cudaMalloc(&c->d_mi_soa, need));
+        c->mi_soa_cap = need;
+    }
+    int *d_bad = reinterpret_cast<int *>(c->d_mi_soa + ((7 * plane_bytes + 3) & ~(size_t)3));
+    CUDA_TRY(c, cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
+    for (int p = 0; p < nplanes; p++) {
+        const uint8_t *src = planes[p] + (size_t)(c->glob_row0 / 4) * stride; // whole-picture planes -> this context's rows
+        if (stride == cols)
+            CUDA_TRY(c, cudaMemcpyAsync(c->d_mi_soa + p * plane_bytes, src, plane_bytes, cudaMemcpyHostToDevice, c->stream));
+        else
+            CUDA_TRY(c, cudaMemcpy2DAsync(c->d_mi_soa + p * plane_bytes, cols, src, stride, cols, rows, cudaMemcpyHostToDevice, c->stream));
+    }
+    MiPackArgs a;
+    const uint8_t *d = c->d_mi_soa;
+    a.bsize = d;
+    if (dec)
+        a.tx0 = d + plane_bytes, a.tx1 = d + 2 * plane_bytes, a.skip = d + 3 * plane_bytes, a.ref0 = d + 4 * plane_bytes,
+        a.mode = d + 5 * plane_bytes, a.seg = d + 6 * plane_bytes;
+    else
+        a.tx0 = d + plane_bytes, a.tx1 = nullptr, a.skip = d + 2 * plane_bytes, a.ref0 = d + 3 * plane_bytes, a.mode = d + 4 * plane_bytes,
+        a.seg = d + 5 * plane_bytes;
+    a.in_pitch = cols, a.rows = rows, a.cols = cols, a.out = c->d_mi, a.out_pitch = c->mi_stride, a.dec = dec, a.bad = d_bad;
+    a.t = mi_pack_tables();
+    mi_pack_kernel<<<dim3((cols + MP_THREADS - 1) / MP_THREADS, rows), MP_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    // no host synchronisation here: the flag lands in pinned memory and is looked at by the next svtf_sync / download
+    if (!c->h_mi_bad)
+        CUDA_TRY(c, cudaMallocHost(&c->h_mi_bad, sizeof(int)));
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_mi_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    c->have_mi = true;
+    return SVTF_OK;
+}
+
+static int mi_soa_check(svtf_ctx *c) { // after a stream synchronisation
+    if (c->h_mi_bad && *c->h_mi_bad) {
+        *c->h_mi_bad = 0;
+        c->have_mi   = false;
+        return c->fail(SVTF_E_ARG, "svtf_set_mi_soa: invalid enum value in the side info (the picture was filtered with undefined side info)");
+    }
+    return SVTF_OK;
+}
+
+extern "C" int svtf_set_mi_soa_enc(svtf_ctx *c, const uint8_t *bsize, const uint8_t *tx_depth, const uint8_t *skip, const uint8_t *ref_frame0,
+                                   const uint8_t *mode, const uint8_t *segment_id, int32_t stride) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_set_mi_soa_enc: NULL context");
+    const uint8_t *pl[7] = {bsize, tx_depth, skip, ref_frame0, mode, segment_id, nullptr};
+    return set_mi_soa(c, pl, 6, stride, false, "svtf_set_mi_soa_enc");
+}
+
+extern "C" int svtf_set_mi_soa_dec(svtf_ctx *c, const uint8_t *bsize, const uint8_t *tx_size_y, const uint8_t *tx_size_uv, const uint8_t *skip,
+                                   const uint8_t *ref_frame0, const uint8_t *mode, const uint8_t *segment_id, int32_t stride) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_set_mi_soa_dec: NULL context");
+    const uint8_t *pl[7] = {bsize, tx_size_y, tx_size_uv, skip, ref_frame0, mode, segment_id};
+    return set_mi_soa(c, pl, 7, stride, true, "svtf_set_mi_soa_dec");
+}
+
+// The packed words as the device holds them (tests; [mi_rows][stride] words)
+extern "C" int svtf_get_mi(svtf_ctx *c, svtf_mi_t *out, int32_t stride) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_get_mi: NULL context");
+    if (!c->have_mi || !out || stride < c->geom.mi_cols)
+        return c->fail(SVTF_E_STATE, "svtf_get_mi: no side info set, NULL output or stride smaller than mi_cols");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaMemcpy2DAsync(out, sizeof(svtf_mi_t) * stride, c->d_mi, sizeof(svtf_mi_t) * c->mi_stride, sizeof(svtf_mi_t) * c->geom.mi_cols,
+                                  c->geom.mi_rows, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return SVTF_OK;
+}
+
 extern "C" int svtf_download_frame_async(svtf_ctx *c, void *y, int32_t sy, void *cb, int32_t scb, void *cr, int32_t scr) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_download_frame: NULL context");
@@ -410,7 +544,7 @@ extern "C" int svtf_download_frame(svtf_ctx *c, void *y, int32_t sy, void *cb, i
     if (r != SVTF_OK)
         return r;
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    return SVTF_OK;
+    return mi_soa_check(c);
 }
 
 extern "C" int svtf_rewind(svtf_ctx *c) {

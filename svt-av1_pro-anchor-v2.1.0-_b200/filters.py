@@ -237,6 +237,23 @@ class FilterContext:
         self._mi_keep = mi
         self._chk(self._lib.svtf_set_mi(self._h, _ptr(mi), mi.shape[1]))
 
+    def set_mi_soa(self, soa):
+        """Side info as byte planes, packed on the device.  soa: dict with bsize, skip, ref_frame0, mode, segment_id and either
+        tx_depth (encoder, svtf_set_mi_soa_enc) or tx_size_y + tx_size_uv (decoder, svtf_set_mi_soa_dec)."""
+        dec = "tx_size_y" in soa
+        keys = ("bsize", "tx_size_y", "tx_size_uv", "skip", "ref_frame0", "mode", "segment_id") if dec else \
+            ("bsize", "tx_depth", "skip", "ref_frame0", "mode", "segment_id")
+        arrs = [soa[k] if (isinstance(soa[k], np.ndarray) and soa[k].dtype == np.uint8 and soa[k].flags.c_contiguous)
+                else np.ascontiguousarray(soa[k], dtype=np.uint8) for k in keys]
+        self._mi_keep = arrs
+        fn = self._lib.svtf_set_mi_soa_dec if dec else self._lib.svtf_set_mi_soa_enc
+        self._chk(fn(self._h, *[_ptr(a) for a in arrs], arrs[0].shape[1]))
+
+    def get_mi(self):
+        out = np.zeros((self.geom.mi_rows, self.geom.mi_cols), dtype=np.uint32)
+        self._chk(self._lib.svtf_get_mi(self._h, _ptr(out), out.shape[1]))
+        return out
+
     def download(self, out=None):
         g = self.geom
         if out is None:
