@@ -245,6 +245,31 @@ int svtf_filter_chain(svtf_ctx *ctx, const svtf_lf_params *lf, const svtf_cdef_p
                       const int8_t *fb_strength_idx, const svtf_ccso_params *ccso,
                       const uint8_t *const blk_flags[3]);
 
+/* ---- loop restoration (the stage after CDEF/CCSO on the same surfaces) ----------------------------------
+ * svt_av1_loop_restoration_filter_frame (Common/Codec/EbRestoration.c:1179) with the stripe boundaries of
+ * svt_av1_loop_restoration_save_boundary_lines (:1682): Wiener (7-tap separable, svt_av1_[highbd_]wiener_convolve_add_src_c,
+ * Common/Codec/convolve.c:100/194) and self-guided (svt_apply_selfguided_restoration_c :957) restoration per unit.
+ * RestorationUnitInfo (EbRestoration.h:184-188) / RestorationInfo (:225-242) as plain data: */
+#define SVTF_RESTORE_NONE 0
+#define SVTF_RESTORE_WIENER 1
+#define SVTF_RESTORE_SGRPROJ 2
+typedef struct svtf_lr_unit {
+    int32_t restoration_type;                     /* SVTF_RESTORE_*                                        */
+    int16_t wiener_vfilter[8], wiener_hfilter[8]; /* WienerInfo.vfilter / hfilter (InterpKernel, tap 7 = 0) */
+    int32_t sgr_ep, sgr_xqd[2];                   /* SgrprojInfo                                           */
+} svtf_lr_unit;
+typedef struct svtf_lr_params {
+    int32_t frame_restoration_type[3]; /* SVTF_RESTORE_NONE: the plane is left as it is; anything else: per-unit types apply */
+    int32_t restoration_unit_size[3];  /* in samples of the plane (64, 128 or 256; chroma may be 32)                         */
+    int32_t optimized_lr;              /* rsi->optimized_lr: stripe borders from the picture itself (:350-377)               */
+} svtf_lr_params;
+/* Units per row / column of a plane (count_units_in_tile, EbRestoration.c:124: round to nearest, at least 1). */
+int svtf_lr_units(const svtf_geom *geom, int32_t plane, int32_t unit_size, int32_t *horz_units, int32_t *vert_units);
+/* Filters the current picture.  units[p]: vert_units x horz_units entries, raster order.  The rows above/below each
+ * 64-row stripe come from the DEBLOCKED picture (the surface CDEF read), as the reference saves them before CDEF; on a
+ * context where no CDEF ran they come from the current picture. */
+int svtf_lr_apply_frame(svtf_ctx *ctx, const svtf_lr_params *lr, const svtf_lr_unit *const units[3]);
+
 /* svt_av1_pick_filter_level(src, pcs, LPF_PICK_FROM_FULL_IMAGE) (Encoder/Codec/EbDeblockingFilter.c:1129-1252): searches
  * the deblocking level of luma (one level for both directions), then U, then V, each with search_filter_level (:886-985)
  * — trial deblock of that plane, SSE against the uploaded source, keep the unfiltered picture.  `start` carries the

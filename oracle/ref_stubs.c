@@ -65,14 +65,12 @@ STUB(svt_aom_partition_cdf_length)
 STUB(svt_av1_build_nmv_cost_table)
 STUB(svt_av1_get_intra_inter_context)
 STUB(svt_av1_get_mv_joint)
-STUB(svt_av1_loop_restoration_save_boundary_lines)
 STUB(svt_av1_superres_upscale_frame)
 STUB(svt_block_on_mutex)
 STUB(svt_get_empty_object)
 STUB(svt_get_full_object)
 STUB(svt_post_full_object)
 STUB(svt_print_alloc_fail_impl)
-STUB(svt_recon_picture_buffer_desc_ctor)
 STUB(svt_release_mutex)
 STUB(svt_release_object)
 STUB(svt_system_resource_get_consumer_fifo)
@@ -103,3 +101,13 @@ static uint32_t log2f_c(uint32_t x) {
 }
 void (*svt_memcpy)(void *, const void *, size_t) = memcpy_c;
 uint32_t (*svt_log2f)(uint32_t)                  = log2f_c;
+
+/* loop restoration (Common/Codec/EbRestoration.c, convolve.c): RTCD pointers -> the _c kernels; super-resolution is off */
+STUB(svt_av1_upscale_normative_rows)
+void svt_apply_selfguided_restoration_c();
+void svt_av1_wiener_convolve_add_src_c();
+void svt_av1_highbd_wiener_convolve_add_src_c();
+void *svt_apply_selfguided_restoration       = (void *)svt_apply_selfguided_restoration_c;
+void *svt_av1_wiener_convolve_add_src        = (void *)svt_av1_wiener_convolve_add_src_c;
+void *svt_av1_highbd_wiener_convolve_add_src = (void *)svt_av1_highbd_wiener_convolve_add_src_c;
+void  svt_log(int level, const char *tag, const char *fmt, ...) { (void)level, (void)tag, (void)fmt; }

@@ -53,6 +53,17 @@ class CcsoParams(C.Structure):
                 ("filter_offset", (C.c_int8 * CCSO_LUT_SIZE) * 3)]
 
 
+class LrUnit(C.Structure):
+    """svtf_lr_unit (RestorationUnitInfo, Common/Codec/EbRestoration.h:184-188)"""
+    _fields_ = [("restoration_type", C.c_int32), ("wiener_vfilter", C.c_int16 * 8), ("wiener_hfilter", C.c_int16 * 8), ("sgr_ep", C.c_int32),
+                ("sgr_xqd", C.c_int32 * 2)]
+
+
+class LrParams(C.Structure):
+    """svtf_lr_params"""
+    _fields_ = [("frame_restoration_type", C.c_int32 * 3), ("restoration_unit_size", C.c_int32 * 3), ("optimized_lr", C.c_int32)]
+
+
 class LfSearchCfg(C.Structure):
     _fields_ = [("dlf_avg", C.c_int32), ("early_exit_convergence", C.c_int32), ("only_4x4", C.c_int32), ("search_chroma", C.c_int32)]
 
@@ -63,7 +74,7 @@ class DevPlane(C.Structure):
 
 # every symbol include/svtfilt_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
-    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_set_mi_soa_enc", "svtf_set_mi_soa_dec", "svtf_get_mi", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
+    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_set_mi_soa_enc", "svtf_set_mi_soa_dec", "svtf_get_mi", "svtf_lr_units", "svtf_lr_apply_frame", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
@@ -103,6 +114,8 @@ def load():
     lib.svtf_set_mi_soa_enc.argtypes = [vp] + [vp] * 6 + [i32]
     lib.svtf_set_mi_soa_dec.argtypes = [vp] + [vp] * 7 + [i32]
     lib.svtf_get_mi.argtypes = [vp, vp, i32]
+    lib.svtf_lr_units.argtypes = [C.POINTER(Geom), i32, i32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.svtf_lr_apply_frame.argtypes = [vp, C.POINTER(LrParams), C.POINTER(C.c_void_p)]
     lib.svtf_deblock_frame.argtypes = [vp, C.POINTER(LfParams), i32, i32]
     lib.svtf_deblock_frame_sb_delta.argtypes = [vp, C.POINTER(LfParams), i32, i32, vp, i32, i32]
     lib.svtf_cdef_apply_frame.argtypes = [vp, C.POINTER(CdefParams), vp]

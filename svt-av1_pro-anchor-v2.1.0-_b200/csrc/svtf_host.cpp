@@ -109,6 +109,16 @@ extern "C" int svtf_pack_mi_dec(size_t n, const uint8_t *bsize, const uint8_t *t
     return SVTF_OK;
 }
 
+// count_units_in_tile (Common/Codec/EbRestoration.c:124) over the whole-frame rectangle (svt_aom_whole_frame_rect :104)
+extern "C" int svtf_lr_units(const svtf_geom *geom, int32_t plane, int32_t unit_size, int32_t *horz_units, int32_t *vert_units) {
+    if (!geom || !horz_units || !vert_units || unit_size <= 0 || plane < 0 || plane > 2)
+        return svtf::set_global_error(SVTF_E_ARG, "svtf_lr_units: bad argument");
+    const int ss = plane ? 1 : 0, pw = (geom->width + ss) >> ss, ph = (geom->height + ss) >> ss;
+    *horz_units  = std::max((pw + (unit_size >> 1)) / unit_size, 1);
+    *vert_units  = std::max((ph + (unit_size >> 1)) / unit_size, 1);
+    return SVTF_OK;
+}
+
 namespace svtf {
 
 // Per-frame deblock tables.  Level table: svt_av1_loop_filter_frame_init

@@ -334,6 +334,12 @@ class FilterContext:
         self._chk(self._lib.svtf_cdef_search_frame(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), _ptr(dirs), _ptr(var)))
         return mse, skip, dirs, var
 
+    def loop_restoration_filter_frame(self, lr, units):
+        """svt_av1_loop_restoration_filter_frame on the current picture (svtf_lr_apply_frame).  lr: LrParams; units: three
+        ctypes arrays of LrUnit (vert_units x horz_units, raster order; None for a plane without restoration)."""
+        up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) if u is not None else None for u in units])
+        self._chk(self._lib.svtf_lr_apply_frame(self._h, C.byref(lr), up))
+
     def pick_filter_level(self, start_lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
         """svtf_lf_search_frame: svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE) on the uploaded picture + source."""
         cfg = L.LfSearchCfg(dlf_avg, early_exit_convergence, only_4x4, search_chroma)

@@ -233,6 +233,50 @@ def synth_ccso(geom, seed, quant_idx=(0, 0, 0), support=(0, 1, 2), edge_clf=(0, 
     return S.ccso_params(enable, bo_only, quant_idx, support, edge_clf, band_log2, lut), flags
 
 
+def lr_units_of(geom, plane, unit_size):
+    ss = 1 if plane else 0
+    pw, ph = (geom.width + ss) >> ss, (geom.height + ss) >> ss
+    return max((pw + unit_size // 2) // unit_size, 1), max((ph + unit_size // 2) // unit_size, 1)
+
+
+def synth_lr(geom, seed, unit_size=(64, 32, 32), frame_type=(3, 3, 3), optimized_lr=0, p_none=0.15, p_wiener=0.45):
+    """Restoration parameters for a frame: per-unit RESTORE_NONE / WIENER (symmetric 7-tap, 5-tap for chroma, within the
+    coded ranges of Common/Codec/EbRestoration.h:118-160) / SGRPROJ (ep 0..15, xqd within SGRPROJ_PRJ_MIN/MAX).
+    Returns (LrParams, [unit arrays])."""
+    rng = np.random.default_rng(seed ^ 0x1235)
+    lr = L.LrParams()
+    units = []
+    for p in range(3):
+        lr.frame_restoration_type[p] = frame_type[p]
+        lr.restoration_unit_size[p] = unit_size[p]
+        hu, vu = lr_units_of(geom, p, unit_size[p])
+        arr = (L.LrUnit * (hu * vu))()
+        for u in arr:
+            t = rng.random()
+            u.restoration_type = 0 if t < p_none else (1 if t < p_none + p_wiener else 2)
+            if frame_type[p] == 1 and u.restoration_type == 2:
+                u.restoration_type = 1
+            if frame_type[p] == 2 and u.restoration_type == 1:
+                u.restoration_type = 2
+            for f in (u.wiener_vfilter, u.wiener_hfilter):
+                t0 = 0 if p else int(rng.integers(-5, 11))
+                t1, t2 = int(rng.integers(-23, 9)), int(rng.integers(-17, 47))
+                f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7] = t0, t1, t2, -2 * (t0 + t1 + t2), t2, t1, t0, 0
+            u.sgr_ep = int(rng.integers(0, 16))
+            u.sgr_xqd[0], u.sgr_xqd[1] = int(rng.integers(-96, 32)), int(rng.integers(-32, 96))
+        units.append(arr)
+    lr.optimized_lr = optimized_lr
+    return lr, units
+
+
+def _lr_call(fn, geom, cur, dbk, lr, units):
+    out = [p.copy() for p in cur]
+    dbk = [np.ascontiguousarray(p) for p in dbk]
+    up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
+    assert fn(C.byref(geom), *_planes(out), *_planes(dbk), C.byref(lr), up) == 0
+    return out
+
+
 def cdef_level1_lists():
     """cdef_level 1 (exhaustive, presets <= M0): 16 primary {0,4,..,60} then 48 secondary pri+{1,2,3}
     (Encoder/Codec/EncModeConfig.c:871-910)."""
@@ -312,6 +356,9 @@ class Oracle:
 
     def ccso_derive_plane(self, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
         return _ccso_derive_call(self.lib.orc_ccso_derive_plane, geom, plane, pre_luma, rec_plane, org_plane, rdmult)
+
+    def lr_apply(self, geom, cur, dbk, lr, units):
+        return _lr_call(self.lib.orc_lr_frame, geom, cur, dbk, lr, units)
 
     def lf_search(self, geom, rec, src, mi, lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
         rec = [p.copy() for p in rec]
@@ -417,6 +464,9 @@ class Ref:
 
     def ccso_derive_plane(self, geom, plane, pre_luma, rec_plane, org_plane, rdmult):
         return _ccso_derive_call(self.lib.ref_ccso_derive_plane, geom, plane, pre_luma, rec_plane, org_plane, rdmult)
+
+    def lr_apply(self, geom, cur, dbk, lr, units):
+        return _lr_call(self.lib.ref_lr_frame, geom, cur, dbk, lr, units)
 
     def lf_search(self, geom, rec, src, soa, lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
         rec = [p.copy() for p in rec]
