@@ -265,3 +265,132 @@ API int adapt_ccso_search(const svtf_geom *g, int base_q_idx, int rdmult, const 
     harness_free(&h);
     return 0;
 }
+
+/* ---- loop restoration -------------------------------------------------------------------------------------
+ * RestorationInfo of the three planes from plain data; the stripe boundaries (what
+ * svt_av1_loop_restoration_save_boundary_lines keeps of the deblocked picture, Common/Codec/EbRestoration.c:1522-1574:
+ * rows y0-2, y0-1 above and y1, y1+1 below every stripe, the last one repeated at the crop border) are written here from
+ * the deblocked picture the test passes. */
+#include "EbRestoration.h"
+static void lr_fill(harness *h, Av1Common *cm, const svtf_geom *g, const svtf_lr_params *lr, const svtf_lr_unit *const units[3],
+                    void *const dbk[3], const int dst[3]) {
+    memset(cm, 0, sizeof(*cm));
+    cm->child_pcs = h->pcs;
+    cm->mi_rows = g->mi_rows, cm->mi_cols = g->mi_cols;
+    cm->frm_size.frame_width = (uint16_t)g->width, cm->frm_size.frame_height = (uint16_t)g->height;
+    cm->frm_size.superres_upscaled_width = (uint16_t)g->width, cm->frm_size.superres_upscaled_height = (uint16_t)g->height;
+    cm->frm_size.superres_denominator    = SCALE_NUMERATOR;
+    cm->subsampling_x = cm->subsampling_y = 1;
+    cm->bit_depth = g->bit_depth, cm->use_highbitdepth = g->sample_bytes == 2;
+    const int sb = g->sample_bytes;
+    for (int p = 0; p < 3; p++) {
+        RestorationInfo *rsi = &h->pcs->rst_info[p];
+        const int        ss = p ? 1 : 0, pw = (g->width + ss) >> ss, ph = (g->height + ss) >> ss, sh = 64 >> ss, off = 8 >> ss;
+        int32_t          hu = 1, vu = 1;
+        rsi->frame_restoration_type = (RestorationType)lr->frame_restoration_type[p];
+        rsi->restoration_unit_size  = lr->restoration_unit_size[p];
+        svtf_lr_units(g, p, lr->restoration_unit_size[p], &hu, &vu);
+        rsi->horz_units_per_tile = hu, rsi->vert_units_per_tile = vu, rsi->units_per_tile = hu * vu;
+        rsi->unit_info = calloc(hu * vu, sizeof(RestorationUnitInfo));
+        for (int u = 0; u < hu * vu && units[p]; u++) {
+            RestorationUnitInfo *ri = &rsi->unit_info[u];
+            ri->restoration_type    = (RestorationType)units[p][u].restoration_type;
+            memcpy(ri->wiener_info.vfilter, units[p][u].wiener_vfilter, sizeof(ri->wiener_info.vfilter));
+            memcpy(ri->wiener_info.hfilter, units[p][u].wiener_hfilter, sizeof(ri->wiener_info.hfilter));
+            ri->sgrproj_info.ep = units[p][u].sgr_ep, ri->sgrproj_info.xqd[0] = units[p][u].sgr_xqd[0], ri->sgrproj_info.xqd[1] = units[p][u].sgr_xqd[1];
+        }
+        RestorationStripeBoundaries *b = &rsi->boundaries;
+        const int nstripes = (ph + off + sh - 1) / sh, stride = (pw + 2 * RESTORATION_EXTRA_HORZ + 31) & ~31;
+        b->stripe_boundary_stride = stride;
+        b->stripe_boundary_above  = calloc((size_t)nstripes * RESTORATION_CTX_VERT * stride, sb);
+        b->stripe_boundary_below  = calloc((size_t)nstripes * RESTORATION_CTX_VERT * stride, sb);
+        if (!dbk)
+            continue;
+        for (int k = 0; k < nstripes; k++) {
+            const int y0 = k * sh - off > 0 ? k * sh - off : 0, y1 = (k + 1) * sh - off < ph ? (k + 1) * sh - off : ph;
+            for (int i = 0; i < RESTORATION_CTX_VERT; i++) {
+                const size_t row = ((size_t)(RESTORATION_CTX_VERT * k + i) * stride + RESTORATION_EXTRA_HORZ) * sb;
+                if (k > 0)
+                    memcpy(b->stripe_boundary_above + row, (uint8_t *)dbk[p] + (size_t)(y0 - 2 + i) * dst[p] * sb, (size_t)pw * sb);
+                if (y1 < ph)
+                    memcpy(b->stripe_boundary_below + row, (uint8_t *)dbk[p] + (size_t)(y1 + i < ph ? y1 + i : ph - 1) * dst[p] * sb, (size_t)pw * sb);
+            }
+        }
+    }
+}
+static void lr_free(harness *h) {
+    for (int p = 0; p < 3; p++) {
+        free(h->pcs->rst_info[p].unit_info);
+        free(h->pcs->rst_info[p].boundaries.stripe_boundary_above), free(h->pcs->rst_info[p].boundaries.stripe_boundary_below);
+    }
+}
+static void lr_yv12(Yv12BufferConfig *f, const svtf_geom *g, void *const pl[3], const int st[3]) {
+    memset(f, 0, sizeof(*f));
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        f->buffers[p]      = g->sample_bytes == 2 ? CONVERT_TO_BYTEPTR(pl[p]) : (uint8_t *)pl[p];
+        f->strides[ss]     = st[p];
+        f->crop_widths[ss] = (g->width + ss) >> ss, f->crop_heights[ss] = (g->height + ss) >> ss;
+    }
+}
+
+/* stand-alone: `cur` (after CDEF) is restored in place, the stripe borders come from `dbk` through rst_info[].boundaries */
+API int adapt_lr_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, void *dy, int dsy, void *dcb, int dscb,
+                       void *dcr, int dscr, const svtf_lr_params *lr, const svtf_lr_unit *const units[3]) {
+    static const uint8_t zero = 0;
+    harness              h;
+    ref_mi_soa           soa = {NULL, NULL, NULL, NULL, NULL, NULL, g->mi_cols};
+    (void)zero;
+    if (harness_init(&h, g, &soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    Av1Common   cm;
+    void *const dbk[3] = {dy, dcb, dcr}, *const cur[3] = {y, cb, cr};
+    const int   dst[3] = {dsy, dscb, dscr}, cst[3] = {sy, scb, scr};
+    lr_fill(&h, &cm, g, lr, units, dbk, dst);
+    Yv12BufferConfig f;
+    lr_yv12(&f, g, cur, cst);
+    svtf_adapter_set_resident(0);
+    svt_av1_loop_restoration_filter_frame(NULL, &f, &cm, lr->optimized_lr);
+    svtf_adapter_release(h.pcs);
+    lr_free(&h);
+    harness_free(&h);
+    return 0;
+}
+
+/* resident chain through the adapters: svt_av1_loop_filter_frame -> svt_av1_cdef_frame -> svt_av1_loop_restoration_filter_frame */
+API int adapt_chain_lr(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const ref_mi_soa *soa,
+                       const svtf_lf_params *lf, const svtf_cdef_params *cp, const int8_t *fb_strength_idx, const svtf_lr_params *lr,
+                       const svtf_lr_unit *const units[3]) {
+    harness h;
+    if (harness_init(&h, g, soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    fill_lf(&h, lf);
+    FrameHeader *fh              = &h.ppcs->frm_hdr;
+    fh->cdef_params.cdef_damping = (uint8_t)cp->cdef_damping;
+    fh->cdef_params.cdef_bits    = (uint8_t)cp->cdef_bits;
+    for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++) {
+        fh->cdef_params.cdef_y_strength[i]  = cp->cdef_y_strength[i];
+        fh->cdef_params.cdef_uv_strength[i] = cp->cdef_uv_strength[i];
+    }
+    const int nvfb = (g->mi_rows + 15) / 16, nhfb = (g->mi_cols + 15) / 16;
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++) {
+            int8_t idx = fb_strength_idx[fbr * nhfb + fbc];
+            h.mi[16 * fbr * soa->mi_stride + 16 * fbc].mbmi.cdef_strength = idx < 0 ? 0 : idx;
+        }
+    Av1Common cm;
+    lr_fill(&h, &cm, g, lr, units, NULL, NULL);
+    void *const      cur[3] = {y, cb, cr};
+    const int        cst[3] = {sy, scb, scr};
+    Yv12BufferConfig f;
+    lr_yv12(&f, g, cur, cst);
+    svtf_adapter_set_resident(1);
+    svt_av1_loop_filter_frame(h.recon, h.pcs, 0, 3);
+    svt_av1_cdef_frame(h.scs, h.pcs);
+    svt_av1_loop_restoration_filter_frame(NULL, &f, &cm, lr->optimized_lr);
+    svtf_adapter_set_resident(0);
+    svtf_adapter_release(h.pcs);
+    lr_free(&h);
+    harness_free(&h);
+    return 0;
+}

@@ -33,6 +33,7 @@
 #include "EbDeblockingCommon.h"
 #include "EbCcso.h"
 #include "EbPickccso.h"
+#include "EbRestoration.h"
 
 #include "../include/svtfilt_b200.h"
 #include "../include/svtfilt_b200_adapters.h"
@@ -529,4 +530,80 @@ void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const
     for (int p = 0; p < 3; p++) free(flags[p]);
     for (int k = 0; k < 3; k++)
         for (int p = 0; p < 3; p++) free(buf[k][p]);
+}
+
+/* ----------------------------------------------------------------------------------------------------
+ * svt_av1_loop_restoration_filter_frame (Common/Codec/EbRestoration.c:1179), called by the restoration kernel
+ * (Encoder/Codec/EbRestProcess.c) on cm->frame_to_show after the filters were picked.
+ * Resident chain (svtf_adapter_set_resident(1), the picture went DLF -> CDEF on this pcs's context): the stripe borders
+ * come from the deblocked surface still on the device, svt_av1_loop_restoration_save_boundary_lines has nothing to do,
+ * and this call ends the chain (download).  Stand-alone: `frame` is uploaded and the deblocked rows the reference saved
+ * in rst_info[p].boundaries (two above and two below every 64-row stripe, :1522-1574) are written into an otherwise
+ * empty picture that is uploaded as the pre-CDEF picture — only those rows are ever read. */
+void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig *frame, Av1Common *cm, int32_t optimized_lr) {
+    (void)rst_tmpbuf;
+    PictureControlSet *pcs = cm->child_pcs;
+    CtxSlot           *s   = slot_for(pcs);
+    const int          sb  = s->geom.sample_bytes;
+    svtf_lr_params     lr;
+    svtf_lr_unit      *units[3] = {NULL, NULL, NULL};
+    memset(&lr, 0, sizeof(lr));
+    lr.optimized_lr = optimized_lr;
+    for (int p = 0; p < 3; p++) {
+        const RestorationInfo *rsi = &pcs->rst_info[p];
+        lr.frame_restoration_type[p] = rsi->frame_restoration_type == RESTORE_NONE ? SVTF_RESTORE_NONE : (int32_t)rsi->frame_restoration_type;
+        lr.restoration_unit_size[p]  = rsi->restoration_unit_size;
+        if (rsi->frame_restoration_type == RESTORE_NONE)
+            continue;
+        units[p] = (svtf_lr_unit *)calloc(rsi->units_per_tile, sizeof(svtf_lr_unit));
+        for (int u = 0; u < rsi->units_per_tile; u++) {
+            const RestorationUnitInfo *ri = &rsi->unit_info[u];
+            units[p][u].restoration_type  = ri->restoration_type == RESTORE_WIENER ? SVTF_RESTORE_WIENER
+                 : ri->restoration_type == RESTORE_SGRPROJ                          ? SVTF_RESTORE_SGRPROJ
+                                                                                    : SVTF_RESTORE_NONE;
+            memcpy(units[p][u].wiener_vfilter, ri->wiener_info.vfilter, sizeof(units[p][u].wiener_vfilter));
+            memcpy(units[p][u].wiener_hfilter, ri->wiener_info.hfilter, sizeof(units[p][u].wiener_hfilter));
+            units[p][u].sgr_ep = ri->sgrproj_info.ep, units[p][u].sgr_xqd[0] = ri->sgrproj_info.xqd[0], units[p][u].sgr_xqd[1] = ri->sgrproj_info.xqd[1];
+        }
+    }
+    void   *fp[3];
+    int32_t fst[3];
+    for (int p = 0; p < 3; p++) {
+        fp[p]  = cm->use_highbitdepth ? (void *)CONVERT_TO_SHORTPTR(frame->buffers[p]) : (void *)frame->buffers[p];
+        fst[p] = frame->strides[p > 0];
+    }
+    if (!(g_resident && s->resident)) {
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, fp[0], fst[0], fp[1], fst[1], fp[2], fst[2]), s->ctx);
+        if (!optimized_lr) {
+            uint8_t *dbk[3];
+            int32_t  dst[3];
+            for (int p = 0; p < 3; p++) {
+                const int ss = p ? 1 : 0, cw = (s->geom.mi_cols * 4) >> ss, chh = (s->geom.mi_rows * 4) >> ss;
+                const int pw = (s->geom.width + ss) >> ss, ph = (s->geom.height + ss) >> ss, sh = 64 >> ss, off = 8 >> ss;
+                const RestorationStripeBoundaries *b = &pcs->rst_info[p].boundaries;
+                dbk[p] = (uint8_t *)calloc((size_t)cw * chh, sb), dst[p] = cw;
+                for (int k = 0;; k++) {
+                    const int y0 = k * sh - off > 0 ? k * sh - off : 0, y1 = (k + 1) * sh - off < ph ? (k + 1) * sh - off : ph;
+                    if (y0 >= ph)
+                        break;
+                    for (int i = 0; i < RESTORATION_CTX_VERT; i++) {
+                        const size_t row = (size_t)(RESTORATION_CTX_VERT * k + i) * b->stripe_boundary_stride + RESTORATION_EXTRA_HORZ;
+                        if (k > 0)
+                            memcpy(dbk[p] + (size_t)(y0 - 2 + i) * cw * sb, b->stripe_boundary_above + row * sb, (size_t)pw * sb);
+                        if (y1 < ph && y1 + i < chh)
+                            memcpy(dbk[p] + (size_t)(y1 + i) * cw * sb, b->stripe_boundary_below + row * sb, (size_t)pw * sb);
+                    }
+                }
+            }
+            CHECK(svtf_upload_pre_cdef(s->ctx, dbk[0], dst[0], dbk[1], dst[1], dbk[2], dst[2]), s->ctx);
+            CHECK(svtf_sync(s->ctx), s->ctx);
+            for (int p = 0; p < 3; p++) free(dbk[p]);
+        }
+    }
+    const svtf_lr_unit *cu[3] = {units[0], units[1], units[2]};
+    CHECK(svtf_lr_apply_frame(s->ctx, &lr, cu), s->ctx);
+    CHECK(svtf_download_frame(s->ctx, fp[0], fst[0], fp[1], fst[1], fp[2], fst[2]), s->ctx);
+    s->resident = 0;
+    for (int p = 0; p < 3; p++) free(units[p]);
 }

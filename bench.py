@@ -236,6 +236,50 @@ def side_info_leg(H, S, geom, ctx, np):
             "bytes_per_4x4": {"packed": 4, "byte_planes": 6}}
 
 
+def lr_leg(H, S, geom, wl, ctx, np, with_cpu):
+    """Loop restoration (Wiener / self-guided, 64x64 luma units, mixed types) after deblock + CDEF on the resident picture."""
+    lr, units = H.synth_lr(geom, 0xB200F1)
+    lf = S.lf_params((24, 24), 16, 16)
+    ctx.begin(geom)
+    ctx.upload(wl["rec"])
+    ctx.set_mi(wl["mi"])
+    n = 10
+
+    def run(with_lr):
+        ctx.rewind()
+        ctx.loop_filter_frame(lf)
+        ctx.cdef_frame(wl["cdef"], wl["idx"])
+        if with_lr:
+            ctx.loop_restoration_filter_frame(lr, units)
+
+    def timed(with_lr):
+        run(with_lr)
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            run(with_lr)
+        ctx.sync()
+        return (time.perf_counter() - t0) / n
+
+    base, full = timed(False), timed(True)
+    dt = max(full - base, 1e-9)
+    res = {"metric": "loop restoration Mpixel/s (after deblock + CDEF, picture resident; includes the upload of the unit parameters)",
+           "value": round(geom.width * geom.height / dt / 1e6, 1), "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 3),
+           "chain_with_lr_ms": round(full * 1e3, 3), "cpu_baseline": None}
+    if with_cpu and H.ref_available():
+        g2 = S.make_geom(960, 544, BD)
+        dbk = H.synth_picture(g2, 0xF11)
+        cur = H.synth_source(g2, dbk, 0xF12, amp=5)
+        lr2, u2 = H.synth_lr(g2, 0xF13)
+        ref = H.Ref()
+        t0 = time.perf_counter()
+        ref.lr_apply(g2, cur, dbk, lr2, u2)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": round(960 * 544 / dt / 1e6, 2), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                               "sample": "one 960x544 10-bit picture incl. save_boundary_lines, single thread"}
+    return res
+
+
 def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search.
     Several pictures are in flight, one context + stream + submitting host thread each — the reference's CDEF stage runs
@@ -579,6 +623,7 @@ def main():
 
     search = gpu_search_leg(H, S, geom, wls[0], ctxs[:args.search_inflight], max(3, args.steps // 2), np) if rank == 0 else None
     derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
+    lrl = lr_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
     lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     cpu = search_cpu = None
@@ -599,7 +644,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side, "loop_restoration": lrl,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:

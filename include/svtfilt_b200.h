@@ -187,6 +187,11 @@ int svtf_upload_frame(svtf_ctx *ctx, const void *y, int32_t stride_y, const void
  * the pre-CDEF luma (ccso_frame's ext_rec_y argument) is the one uploaded before. */
 int svtf_overwrite_current(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
                            const void *cr, int32_t stride_cr);
+/* The picture as it was BEFORE CDEF, for a caller that ran deblock / CDEF elsewhere and hands over only the later
+ * stages: ccso_frame classifies on its luma (ext_rec_y), loop restoration takes its stripe borders from it
+ * (RestorationStripeBoundaries, Common/Codec/EbRestoration.c:1522-1574).  The current picture is not touched. */
+int svtf_upload_pre_cdef(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
+                         const void *cr, int32_t stride_cr);
 /* Source picture (pcs->cdef_input_source / input_frame16bit) for the strength search. */
 int svtf_upload_source(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb,
                        const void *cr, int32_t stride_cr);

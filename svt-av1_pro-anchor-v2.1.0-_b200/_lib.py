@@ -74,7 +74,7 @@ class DevPlane(C.Structure):
 
 # every symbol include/svtfilt_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
-    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_set_mi_soa_enc", "svtf_set_mi_soa_dec", "svtf_get_mi", "svtf_lr_units", "svtf_lr_apply_frame", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
+    "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_set_mi_soa_enc", "svtf_set_mi_soa_dec", "svtf_get_mi", "svtf_upload_pre_cdef", "svtf_lr_units", "svtf_lr_apply_frame", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
@@ -107,7 +107,7 @@ def load():
     lib.svtf_launch_count.restype = C.c_uint64
     lib.svtf_frame_begin.argtypes = [vp, C.POINTER(Geom)]
     lib.svtf_stripe_begin.argtypes = [vp, C.POINTER(Geom), C.c_int32, C.c_int32]
-    for f in (lib.svtf_upload_frame, lib.svtf_upload_source, lib.svtf_overwrite_current, lib.svtf_download_frame, lib.svtf_download_frame_async):
+    for f in (lib.svtf_upload_frame, lib.svtf_upload_source, lib.svtf_upload_pre_cdef, lib.svtf_overwrite_current, lib.svtf_download_frame, lib.svtf_download_frame_async):
         f.argtypes = [vp, vp, i32, vp, i32, vp, i32]
     lib.svtf_set_mi.argtypes = [vp, vp, i32]
     lib.svtf_rewind.argtypes = [vp]

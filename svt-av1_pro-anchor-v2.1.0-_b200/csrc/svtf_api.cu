@@ -375,6 +375,24 @@ extern "C" int svtf_overwrite_current(svtf_ctx *c, const void *y, int32_t sy, co
     return copy_planes(c, c->surf[c->cur], src, st, true, in_lo(c), in_hi(c));
 }
 
+// The picture as it was before CDEF, for a caller that ran deblock / CDEF elsewhere: CCSO classifies on its luma, loop
+// restoration takes its stripe borders from it.  Goes to a surface of its own; the current picture is not touched.
+extern "C" int svtf_upload_pre_cdef(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_upload_pre_cdef: NULL context");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_upload_pre_cdef: upload the current picture first");
+    if (c->cur == 3)
+        return c->fail(SVTF_E_STATE, "svtf_upload_pre_cdef: the current picture is a restoration output");
+    const void   *src[3] = {y, cb, cr};
+    const int32_t st[3]  = {sy, scb, scr};
+    const int     slot   = c->cur == 1 ? 2 : 1;
+    int           r      = copy_planes(c, c->surf[slot], src, st, true, in_lo(c), in_hi(c));
+    if (r == SVTF_OK)
+        c->pre_cdef = slot;
+    return r;
+}
+
 extern "C" int svtf_upload_source(svtf_ctx *c, const void *y, int32_t sy, const void *cb, int32_t scb, const void *cr, int32_t scr) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_upload_source: NULL context");

@@ -228,6 +228,9 @@ class FilterContext:
     def upload(self, planes):
         self._chk(self._lib.svtf_upload_frame(self._h, *self._planes_args(planes)))
 
+    def upload_pre_cdef(self, planes):
+        self._chk(self._lib.svtf_upload_pre_cdef(self._h, *self._planes_args(planes)))
+
     def upload_source(self, planes):
         self._chk(self._lib.svtf_upload_source(self._h, *self._planes_args(planes)))
 

@@ -143,3 +143,36 @@ def test_pick_filter_level_adapter_then_deblock(H, orc, adapt, w, h, bd, sb, sta
         assert list(lv) == H.Ref().lf_search(g, rec, src, soa, lf0, **kw)
     exp = orc.deblock(g, rec, mi, S.lf_params((exp_lv[0], exp_lv[1]), exp_lv[2], exp_lv[3], sharpness_level=0))
     assert H.planes_equal(got, exp), H.first_diff(got, exp)
+
+
+@pytest.mark.parametrize("w,h,bd,sb,seed,kw", [(200, 136, 8, 1, 1, {}), (264, 200, 10, 2, 2, {"unit_size": (128, 64, 64)}),
+                                               (134, 70, 10, 2, 3, {}), (200, 136, 10, 2, 4, {"optimized_lr": 1})])
+def test_loop_restoration_adapter(H, orc, adapt, w, h, bd, sb, seed, kw):
+    """svt_av1_loop_restoration_filter_frame(rst_tmpbuf, frame, cm, optimized_lr): stand-alone (stripe borders from
+    rst_info[].boundaries) and at the end of a resident DLF -> CDEF -> LR chain, against the oracle and the reference."""
+    from test_lr_oracle import vis
+
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    rec = H.synth_picture(g, 14000 + seed, noise=10)
+    soa = H.synth_mode_info(g, 14100 + seed, p_skip=0.3)
+    mi = H.pack_mi(soa)
+    lf = S.lf_params((20, 20), 12, 12)
+    cdef, idx = H.synth_cdef(g, 14200 + seed)
+    lr, units = H.synth_lr(g, 14300 + seed, **kw)
+    up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
+    dbk = orc.deblock(g, rec, mi, lf)
+    post = orc.cdef_apply(g, dbk, mi, cdef, idx)
+    exp = orc.lr_apply(g, post, dbk, lr, units)
+    # stand-alone
+    got = [p.copy() for p in post]
+    assert adapt.adapt_lr_frame(C.byref(g), *H._planes(got), *H._planes(dbk), C.byref(lr), up) == 0
+    assert H.planes_equal(vis(H, g, got), vis(H, g, exp)), H.first_diff(vis(H, g, got), vis(H, g, exp))
+    if H.ref_available():
+        assert H.planes_equal(vis(H, g, got), vis(H, g, H.Ref().lr_apply(g, post, dbk, lr, units)))
+    # resident chain
+    s, keep = _soa(H, soa)
+    got2 = [p.copy() for p in rec]
+    idx8 = np.ascontiguousarray(idx, dtype=np.int8)
+    assert adapt.adapt_chain_lr(C.byref(g), *H._planes(got2), C.byref(s), C.byref(lf), C.byref(cdef), H._p(idx8), C.byref(lr), up) == 0
+    assert H.planes_equal(vis(H, g, got2), vis(H, g, exp)), H.first_diff(vis(H, g, got2), vis(H, g, exp))
