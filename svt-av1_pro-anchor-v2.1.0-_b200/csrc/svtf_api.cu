@@ -646,7 +646,12 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
     a.plane_mask = mask;
     a.sb_lvl = d_sb_lvl, a.sb_cols = sb_cols, a.sb_shift = sb_shift;
     build_lf_tables(*lf, a.t);
-    if (c->geom.sample_bytes == 1)
+    if (d_sb_lvl) {
+        if (c->geom.sample_bytes == 1)
+            deblock_kernel<uint8_t, true><<<total, DBK_THREADS, 0, c->stream>>>(a);
+        else
+            deblock_kernel<uint16_t, true><<<total, DBK_THREADS, 0, c->stream>>>(a);
+    } else if (c->geom.sample_bytes == 1)
         deblock_kernel<uint8_t><<<total, DBK_THREADS, 0, c->stream>>>(a);
     else
         deblock_kernel<uint16_t><<<total, DBK_THREADS, 0, c->stream>>>(a);

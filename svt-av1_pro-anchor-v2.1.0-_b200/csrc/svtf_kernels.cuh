@@ -232,7 +232,7 @@ __device__ __forceinline__ unsigned dbk_edge_params(const svtf_mi_t *__restrict_
     return 0;
 }
 
-template <typename T>
+template <typename T, bool SBLVL = false> // SBLVL: per-superblock level tables (decoder delta_lf), a separate instantiation
 __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_constant__ DeblockArgs a) {
     __shared__ __align__(16) uint16_t tile[DBK_LOAD * DBK_PITCH];
     __shared__ uint8_t                vpar[DBK_VUNITS * DBK_EDGES]; // [row unit][edge]
@@ -277,13 +277,13 @@ __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_const
         for (int i = tid; i < DBK_VUNITS * DBK_EDGES + DBK_EDGES * 16; i += DBK_THREADS) {
             if (i < DBK_VUNITS * DBK_EDGES) {
                 const int u = i / DBK_EDGES, k = i - u * DBK_EDGES;
-                vpar[i] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph, a.sb_lvl, a.sb_cols,
-                                                   a.sb_shift);
+                vpar[i] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph, SBLVL ? a.sb_lvl : nullptr,
+                                                   a.sb_cols, a.sb_shift);
             } else {
                 const int j = i - DBK_VUNITS * DBK_EDGES;
                 const int k = j >> 4, u = j & 15;
-                hpar[j] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph, a.sb_lvl, a.sb_cols,
-                                                   a.sb_shift);
+                hpar[j] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph, SBLVL ? a.sb_lvl : nullptr,
+                                                   a.sb_cols, a.sb_shift);
             }
         }
         __syncthreads();

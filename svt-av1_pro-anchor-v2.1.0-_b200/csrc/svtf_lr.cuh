@@ -57,7 +57,8 @@ __device__ __forceinline__ int lr_x_by_xplus1(unsigned z) {
 
 // A and B of the self-guided filter from the box sums around (r, c) of the staged input
 template <int R>
-__device__ __forceinline__ void lr_sgr_ab(const uint16_t *in, const int r, const int c, const int bd, const unsigned s, uint16_t &A, uint32_t &B) {
+__device__ __forceinline__ void lr_sgr_ab(const uint16_t *in, const uint16_t *xb, const int r, const int c, const int bd, const unsigned s,
+                                          uint16_t &A, uint32_t &B) {
     uint32_t sum = 0, sq = 0;
 #pragma unroll
     for (int dy = -R; dy <= R; dy++)
@@ -70,7 +71,7 @@ __device__ __forceinline__ void lr_sgr_ab(const uint16_t *in, const int r, const
     const uint32_t     a = (uint32_t)lr_rnd((int)sq, 2 * (bd - 8)), b = (uint32_t)lr_rnd((int)sum, bd - 8);
     const uint32_t     p = (a * n < b * b) ? 0 : a * n - b * b;
     const uint32_t     z = (p * s + (1u << 19)) >> 20;
-    const int          Av = lr_x_by_xplus1(min(z, 255u));
+    const int          Av = xb[min(z, 255u)];
     A                     = (uint16_t)Av;
     B                     = ((uint32_t)(256 - Av) * sum * one_by + (1u << 11)) >> 12;
 }
@@ -80,6 +81,7 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     __shared__ uint16_t s_in[LR_IN_ROWS * LR_IN_P];
     __shared__ __align__(16) unsigned char s_buf[66 * 66 * 6]; // Wiener: horizontal pass (u16 [70][64]); SGR: A (u16) and B (u32)
     __shared__ LrUnitDev s_unit;
+    __shared__ uint16_t  s_xb[256];
     const int tid = threadIdx.x;
     int       plane = 0;
     if ((int)blockIdx.x >= a.base[2])
@@ -87,7 +89,7 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     else if ((int)blockIdx.x >= a.base[1])
         plane = 1;
     const int lin = blockIdx.x - a.base[plane], k = lin / a.chunks[plane], ch = lin - k * a.chunks[plane];
-    const int ss = plane ? 1 : 0, TW = LR_MAXW >> ss, SH = 64 >> ss, off = 8 >> ss;
+    const int ss = plane ? 1 : 0, TW = LR_MAXW >> ss, tws = 6 - ss, SH = 64 >> ss, off = 8 >> ss;
     const int pw = a.pw[plane], ph = a.ph[plane], cw = a.cw[plane], chh = a.chh[plane];
     // the last "stripe" of the grid is the tail: coded rows below the visible picture, copied
     const bool beyond = k == a.stripes[plane] - 1;
@@ -108,36 +110,36 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
         type = s_unit.type;
     }
     if (type == SVTF_RESTORE_NONE) { // copy (also: planes without restoration, coded samples outside the visible picture)
-        for (int i = tid; i < h * w; i += LR_THREADS) {
-            const int r = i / w, c = i - r * w;
-            out[(size_t)(y0 + r) * op + x0 + c] = cur[(size_t)(y0 + r) * cp + x0 + c];
-        }
+        for (int r = tid >> 5; r < h; r += LR_THREADS / 32)
+            for (int c = tid & 31; c < w; c += 32) out[(size_t)(y0 + r) * op + x0 + c] = cur[(size_t)(y0 + r) * cp + x0 + c];
         return;
     }
     // ---- stage the stripe input: rows y0-3 .. y1+2, columns x0-3 .. x0+w+2 (setup_processing_stripe_boundary :288) ----
     const bool above = k > 0, below = y1 < ph;
     const int  wv = min(w, pw - x0); // visible columns of this chunk
-    for (int i = tid; i < (h + 6) * (TW + 6); i += LR_THREADS) {
-        const int rr = i / (TW + 6), cc = i - rr * (TW + 6);
-        const int r = y0 - 3 + rr, xc = min(max(x0 - 3 + cc, 0), pw - 1);
-        int       v;
+    const int lane = tid & 31, wrp = tid >> 5;
+    if (tid < 256) // svt_aom_eb_x_by_xplus1 as a table: one entry per thread
+        s_xb[tid] = (uint16_t)lr_x_by_xplus1((unsigned)tid);
+    for (int rr = wrp; rr < h + 6; rr += LR_THREADS / 32) { // one source row per warp pass: the row decision is made once
+        const int r = y0 - 3 + rr;
+        const T  *src;
         if (r < y0) {
             if (!above)
-                v = cur[(size_t)max(r, 0) * cp + xc];
+                src = cur + (size_t)max(r, 0) * cp;
             else if (a.opt)
-                v = cur[(size_t)(r == y0 - 3 ? y0 - 2 : r) * cp + xc];
+                src = cur + (size_t)(r == y0 - 3 ? y0 - 2 : r) * cp;
             else
-                v = dbk[(size_t)max(r, y0 - 2) * dp + xc];
+                src = dbk + (size_t)max(r, y0 - 2) * dp;
         } else if (r >= y1) {
             if (!below)
-                v = cur[(size_t)min(r, ph - 1) * cp + xc];
+                src = cur + (size_t)min(r, ph - 1) * cp;
             else if (a.opt)
-                v = cur[(size_t)min(r == y1 + 2 ? y1 + 1 : r, ph - 1) * cp + xc];
+                src = cur + (size_t)min(r == y1 + 2 ? y1 + 1 : r, ph - 1) * cp;
             else
-                v = dbk[(size_t)min(min(r, y1 + 1), ph - 1) * dp + xc];
+                src = dbk + (size_t)min(min(r, y1 + 1), ph - 1) * dp;
         } else
-            v = cur[(size_t)r * cp + xc];
-        s_in[rr * LR_IN_P + cc] = (uint16_t)v;
+            src = cur + (size_t)r * cp;
+        for (int cc = lane; cc < TW + 6; cc += 32) s_in[rr * LR_IN_P + cc] = (uint16_t)src[min(max(x0 - 3 + cc, 0), pw - 1)];
     }
     __syncthreads();
     const int bd = a.bd, maxv = (1 << bd) - 1;
@@ -145,24 +147,27 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
         // svt_av1_[highbd_]wiener_convolve_add_src_c: horizontal pass into 16 bits, then vertical
         uint16_t *tmp = reinterpret_cast<uint16_t *>(s_buf); // [h + 6][TW]
         const int r0 = bd == 12 ? 5 : 3, r1 = 14 - r0, lim = (1 << (bd + 1 + 7 - r0)) - 1;
+        int       hf[7], vf[7];
+#pragma unroll
+        for (int t = 0; t < 7; t++) hf[t] = s_unit.hf[t], vf[t] = s_unit.vf[t];
         for (int i = tid; i < (h + 6) * TW; i += LR_THREADS) {
-            const int       rr = i / TW, c = i - rr * TW;
+            const int       rr = i >> tws, c = i & (TW - 1);
             const uint16_t *p = &s_in[rr * LR_IN_P + c];
             int             sum = ((int)p[3] << 7) + (1 << (bd + 6));
 #pragma unroll
-            for (int t = 0; t < 7; t++) sum += (int)p[t] * s_unit.hf[t];
+            for (int t = 0; t < 7; t++) sum += (int)p[t] * hf[t];
             tmp[rr * TW + c] = (uint16_t)min(max(lr_rnd(sum, r0), 0), lim);
         }
         __syncthreads();
         for (int i = tid; i < h * TW; i += LR_THREADS) {
-            const int r = i / TW, c = i - r * TW;
+            const int r = i >> tws, c = i & (TW - 1);
             if (c >= w)
                 continue;
             int v;
             if (c < wv) {
                 int sum = ((int)tmp[(r + 3) * TW + c] << 7) - (1 << (bd + r1 - 1));
 #pragma unroll
-                for (int t = 0; t < 7; t++) sum += (int)tmp[(r + t) * TW + c] * s_unit.vf[t];
+                for (int t = 0; t < 7; t++) sum += (int)tmp[(r + t) * TW + c] * vf[t];
                 v = min(max(lr_rnd(sum, r1), 0), maxv);
             } else
                 v = cur[(size_t)(y0 + r) * cp + x0 + c];
@@ -189,14 +194,13 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     if (rad0 > 0) { // selfguided_restoration_fast_internal :669 — A/B on the rows -1, 1, 3, .. of the stripe
         const unsigned sv   = (unsigned)c_sgr_s[ep][0];
         const int      rows = (h + 1) / 2 + 1; // i = -1, 1, .., <= h
-        for (int i = tid; i < rows * (TW + 2); i += LR_THREADS) {
-            const int ri = i / (TW + 2), c = i - ri * (TW + 2);
-            lr_sgr_ab<2>(s_in, 3 + (2 * ri - 1), 3 + (c - 1), bd, sv, sA[ri * AP + c], sB[ri * AP + c]);
-        }
+        for (int ri = wrp; ri < rows; ri += LR_THREADS / 32)
+            for (int c = lane; c < TW + 2; c += 32)
+                lr_sgr_ab<2>(s_in, s_xb, 3 + (2 * ri - 1), 3 + (c - 1), bd, sv, sA[ri * AP + c], sB[ri * AP + c]);
         __syncthreads();
 #pragma unroll
         for (int n = 0; n < PER; n++) {
-            const int i = tid + n * LR_THREADS, r = i / TW, c = i - r * TW;
+            const int i = tid + n * LR_THREADS, r = i >> tws, c = i & (TW - 1);
             if (i >= h * TW)
                 continue;
             const int dg = s_in[(r + 3) * LR_IN_P + c + 3], cc = c + 1;
@@ -218,14 +222,13 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     }
     if (rad1 > 0) { // selfguided_restoration_internal :803 — A/B on rows -1 .. h
         const unsigned sv = (unsigned)c_sgr_s[ep][1];
-        for (int i = tid; i < (h + 2) * (TW + 2); i += LR_THREADS) {
-            const int ri = i / (TW + 2), c = i - ri * (TW + 2);
-            lr_sgr_ab<1>(s_in, 3 + (ri - 1), 3 + (c - 1), bd, sv, sA[ri * AP + c], sB[ri * AP + c]);
-        }
+        for (int ri = wrp; ri < h + 2; ri += LR_THREADS / 32)
+            for (int c = lane; c < TW + 2; c += 32)
+                lr_sgr_ab<1>(s_in, s_xb, 3 + (ri - 1), 3 + (c - 1), bd, sv, sA[ri * AP + c], sB[ri * AP + c]);
         __syncthreads();
 #pragma unroll
         for (int n = 0; n < PER; n++) {
-            const int i = tid + n * LR_THREADS, r = i / TW, c = i - r * TW;
+            const int i = tid + n * LR_THREADS, r = i >> tws, c = i & (TW - 1);
             if (i >= h * TW)
                 continue;
             const int dg = s_in[(r + 3) * LR_IN_P + c + 3], q = (r + 1) * AP + c + 1;
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     }
 #pragma unroll
     for (int n = 0; n < PER; n++) {
-        const int i = tid + n * LR_THREADS, r = i / TW, c = i - r * TW;
+        const int i = tid + n * LR_THREADS, r = i >> tws, c = i & (TW - 1);
         if (i >= h * TW || c >= w)
             continue;
         int v;

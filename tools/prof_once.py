@@ -30,4 +30,13 @@ with S.FilterContext(g) as c:
     c.cdef_seg_search(cfg, want_outputs=False)
     p = c.finish_cdef_search(cfg)
     c.sync()
+    # loop restoration after deblock + CDEF, and the side-info packer
+    lr, units = H.synth_lr(g, 0xB200F1)
+    for _ in range(2):
+        c.rewind()
+        c.loop_filter_frame(lf)
+        c.cdef_frame(cdef, idx)
+        c.loop_restoration_filter_frame(lr, units)
+    c.set_mi_soa(H.synth_mode_info(g, 0xB200C2 + 1, p_split=0.5, p_skip=0.3, p_inter=0.7))
+    c.sync()
 print("ok", p[0].cdef_bits)
