@@ -13,9 +13,13 @@
 #include "EbDecCdef.h"
 #include "EbDecCcso.h"
 #include "EbCcso.h"
+#include "EbDecProcessFrame.h"
+#include "EbDecRestoration.h"
+#include "EbRestoration.h"
 
 #include "../include/svtfilt_b200.h"
 #include "../include/svtfilt_b200_adapters.h"
+#define DEC_HARNESS_LR
 #include "../oracle/dec_harness.h"
 
 #define API __attribute__((visibility("default")))
@@ -77,6 +81,54 @@ API int adaptdec_lf_cdef_resident(const svtf_geom *g, void *y, int sy, void *cb,
     svtf_dec_adapter_fetch(h.dec, h.recon);
     svtf_dec_adapter_set_resident(0);
     svtf_dec_adapter_release(h.dec);
+    dec_harness_free(&h);
+    return 0;
+}
+
+/* Loop restoration, stand-alone calls in the decoder's order (EbDecParseObu.c:2421-2455): save(0) sees the deblocked
+ * picture, save(1) and the filter the picture to restore. */
+API int adaptdec_lr_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, void *dy, int dsy, void *dcb, int dscb,
+                          void *dcr, int dscr, const dec_mi_soa *soa, const svtf_lr_params *lr, const svtf_lr_unit *const units[3]) {
+    dec_harness    h, hd;
+    dec_harness_lr l, ld;
+    if (dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr) || dec_harness_fill_lr(&h, &l, g, lr, units))
+        return -1;
+    if (dec_harness_init(&hd, g, soa, dy, dsy, dcb, dscb, dcr, dscr) || dec_harness_fill_lr(&hd, &ld, g, lr, units))
+        return -1;
+    EbPictureBufferDesc *cur = h.pic_buf->ps_pic_buf;
+    h.pic_buf->ps_pic_buf    = hd.recon;
+    svt_aom_dec_av1_loop_restoration_save_boundary_lines(h.dec, 0);
+    h.pic_buf->ps_pic_buf = cur;
+    svt_aom_dec_av1_loop_restoration_save_boundary_lines(h.dec, 1);
+    svt_aom_dec_av1_loop_restoration_filter_frame(h.dec, 0, 1);
+    dec_harness_lr_store(&h, &l, g);
+    svtf_dec_adapter_release(h.dec);
+    dec_harness_lr_free(&l), dec_harness_lr_free(&ld);
+    dec_harness_free(&h), dec_harness_free(&hd);
+    return 0;
+}
+
+/* The decoder's whole post-recon sequence with the frame kept on the device: LF -> save(0) -> CDEF -> save(1) -> LR -> fetch */
+API int adaptdec_chain_lr_resident(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const dec_mi_soa *soa,
+                                   const svtf_lf_params *lf, const svtf_cdef_params *cdef, const int8_t *fb_idx, const svtf_lr_params *lr,
+                                   const svtf_lr_unit *const units[3]) {
+    dec_harness    h;
+    dec_harness_lr l;
+    if (dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr) || dec_harness_fill_lr(&h, &l, g, lr, units))
+        return -1;
+    dec_harness_fill_lf(&h, lf);
+    dec_harness_fill_cdef(&h, g, soa, cdef, fb_idx);
+    svtf_dec_adapter_set_resident(1);
+    svt_aom_dec_av1_loop_filter_frame(h.dec, h.recon, &h.lf_ctxt, 0, 3, 0, 1);
+    svt_aom_dec_av1_loop_restoration_save_boundary_lines(h.dec, 0);
+    svt_cdef_frame(h.dec, 1);
+    svt_aom_dec_av1_loop_restoration_save_boundary_lines(h.dec, 1);
+    svt_aom_dec_av1_loop_restoration_filter_frame(h.dec, 0, 1);
+    svtf_dec_adapter_fetch(h.dec, h.recon);
+    svtf_dec_adapter_set_resident(0);
+    dec_harness_lr_store(&h, &l, g);
+    svtf_dec_adapter_release(h.dec);
+    dec_harness_lr_free(&l);
     dec_harness_free(&h);
     return 0;
 }

@@ -5,6 +5,7 @@
  *   Decoder/Codec/EbDecLF.c:697    svt_aom_dec_av1_loop_filter_frame
  *   Decoder/Codec/EbDecCdef.c:507  svt_cdef_frame
  *   Decoder/Codec/EbDecCcso.c:384  dec_ccso_frame
+ *   Decoder/Codec/EbDecRestoration.c:429 / :473  svt_aom_dec_av1_loop_restoration_filter_frame / _save_boundary_lines
  * (decoder section).  The multi-threaded row variants (svt_aom_dec_loop_filter_row EbDecLF.c:650,
  * svt_cdef_sb_row_mt EbDecCdef.c:385) exist to spread the CPU loops over worker threads with spin-wait row counters; with
  * the filters on the GPU the frame-level call is made once, from the thread that finishes the frame's reconstruction.
@@ -26,6 +27,9 @@
 #include "EbDecCdef.h"
 #include "EbDecCcso.h"
 #include "EbCcso.h"
+#include "EbDecProcessFrame.h"
+#include "EbDecRestoration.h"
+#include "EbRestoration.h"
 
 #include "../include/svtfilt_b200.h"
 #include "../include/svtfilt_b200_adapters.h"
@@ -43,6 +47,8 @@ typedef struct {
     svtf_geom          geom;
     int                resident;  /* the frame being decoded is on the device */
     int                have_tx;   /* the mi words on the device carry the transform sizes (set by the LF call) */
+    uint8_t           *dbk[3];    /* stand-alone loop restoration: the deblocked rows around the stripe boundaries */
+    int                have_dbk;
 } DecSlot;
 static DecSlot         g_slots[SVTF_DEC_MAX_CACHED];
 static pthread_mutex_t g_lock     = PTHREAD_MUTEX_INITIALIZER;
@@ -89,6 +95,7 @@ static DecSlot *slot_for(const EbDecHandle *dec, const EbPictureBufferDesc *pic)
     }
     if (s && memcmp(&s->geom, &g, sizeof(g))) { /* a new sequence / frame size on the same handle */
         svtf_ctx_destroy(s->ctx);
+        for (int p = 0; p < 3; p++) free(s->dbk[p]);
         memset(s, 0, sizeof(*s));
         free_slot = s, s = NULL;
     }
@@ -112,6 +119,7 @@ void svtf_dec_adapter_release(const struct EbDecHandle *dec) {
     for (int i = 0; i < SVTF_DEC_MAX_CACHED; i++)
         if (g_slots[i].dec == dec) {
             svtf_ctx_destroy(g_slots[i].ctx);
+            for (int p = 0; p < 3; p++) free(g_slots[i].dbk[p]);
             memset(&g_slots[i], 0, sizeof(g_slots[i]));
         }
     pthread_mutex_unlock(&g_lock);
@@ -347,7 +355,122 @@ void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle *dec_handle, uint16_
     }
     const uint8_t *cf[3] = {flags[0], flags[1], flags[2]};
     CHECK(svtf_ccso_apply_frame(s->ctx, &p, cf), s->ctx);
-    end_frame(s, frame);
-    s->resident = 0;
+    if (g_resident)
+        s->resident = 1; /* loop restoration or svtf_dec_adapter_fetch follows */
+    else
+        end_frame(s, frame), s->resident = 0;
     for (int pl = 0; pl < 3; pl++) free(flags[pl]);
+}
+
+/* ----------------------------------------------------------------------------------------------------
+ * Loop restoration (Decoder/Codec/EbDecRestoration.c).  The decoder calls, single-threaded (EbDecParseObu.c:2421-2455):
+ *   svt_aom_dec_av1_loop_restoration_save_boundary_lines(dec, 0)   after the loop filter: keep two deblocked rows above and
+ *                                                                  below every 64-row stripe
+ *   svt_cdef_frame / dec_ccso_frame / superres
+ *   svt_aom_dec_av1_loop_restoration_save_boundary_lines(dec, 1)   the picture's own edge rows for the frame top / bottom
+ *   svt_aom_dec_av1_loop_restoration_filter_frame(dec, 0, do_lr)   lr_pad_pic + SB rows x 64-column blocks with column
+ *                                                                  save / restore around every block
+ * On the device the deblocked picture is still resident when the frame went LF -> CDEF here (resident mode), so both
+ * saves are no-ops and the filter is one launch (svtf_lr_apply_frame).  Stand-alone, save(0) keeps the boundary rows in
+ * an adapter-owned sparse picture which the filter call uploads as the pre-CDEF picture — only those rows are read;
+ * save(1) has nothing to keep (the device repeats the picture's edge rows itself, as lr_pad_pic does).
+ * Restoration units: LrCtxt.lr_unit[plane][unit_row * lr_stride + unit_col] (:341; written by the parser,
+ * EbDecParseBlock.c:2692) -> the dense [vert][horz] array of svtf_lr_apply_frame; the decoder's "use the previous unit when
+ * less than half a unit remains" (:333-338) is the same count as svtf_lr_units.
+ * Superres is not supported (the reference upscales between CDEF and the second save; that stage is not on the device).
+ */
+static void lr_stripe_rows(DecSlot *s, const EbPictureBufferDesc *pic) {
+    const int sb = s->geom.sample_bytes;
+    void     *pp[3];
+    int32_t   st[3];
+    plane_ptrs(pic, sb, pp, st);
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0, cw = (s->geom.mi_cols * 4) >> ss, chh = (s->geom.mi_rows * 4) >> ss;
+        const int pw = (s->geom.width + ss) >> ss, ph = (s->geom.height + ss) >> ss, sh = 64 >> ss, off = 8 >> ss;
+        if (!s->dbk[p] && !(s->dbk[p] = (uint8_t *)calloc((size_t)cw * chh, sb)))
+            die("malloc(deblocked rows)", s->ctx);
+        for (int k = 0;; k++) {
+            const int y0 = k * sh - off > 0 ? k * sh - off : 0, y1 = (k + 1) * sh - off < ph ? (k + 1) * sh - off : ph;
+            if (y0 >= ph)
+                break;
+            for (int i = 0; i < RESTORATION_CTX_VERT; i++) {
+                if (k > 0)
+                    memcpy(s->dbk[p] + (size_t)(y0 - 2 + i) * cw * sb, (uint8_t *)pp[p] + (size_t)(y0 - 2 + i) * st[p] * sb, (size_t)pw * sb);
+                if (y1 + i < ph)
+                    memcpy(s->dbk[p] + (size_t)(y1 + i) * cw * sb, (uint8_t *)pp[p] + (size_t)(y1 + i) * st[p] * sb, (size_t)pw * sb);
+            }
+        }
+    }
+    s->have_dbk = 1;
+}
+
+void svt_aom_dec_av1_loop_restoration_save_boundary_lines(EbDecHandle *dec_handle, int after_cdef) {
+    EbPictureBufferDesc *pic = dec_handle->cur_pic_buf[0]->ps_pic_buf;
+    DecSlot             *s   = slot_for(dec_handle, pic);
+    if (after_cdef || (g_resident && s->resident))
+        return;
+    lr_stripe_rows(s, pic);
+}
+
+void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int optimized_lr, int enable_flag) {
+    if (!enable_flag)
+        return;
+    EbPictureBufferDesc *pic = dec_handle->cur_pic_buf[0]->ps_pic_buf;
+    DecSlot             *s   = slot_for(dec_handle, pic);
+    const LrCtxt        *lc  = (const LrCtxt *)dec_handle->pv_lr_ctxt;
+    const FrameHeader   *fh  = &dec_handle->frame_header;
+    if (fh->frame_size.superres_upscaled_width != fh->frame_size.frame_width) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: loop restoration with superres is not supported\n");
+        abort();
+    }
+    svtf_lr_params lr;
+    svtf_lr_unit  *units[3] = {NULL, NULL, NULL};
+    memset(&lr, 0, sizeof(lr));
+    lr.optimized_lr = optimized_lr;
+    for (int p = 0; p < 3; p++) {
+        const LrParams *fp = &fh->lr_params[p];
+        lr.frame_restoration_type[p] = fp->frame_restoration_type == RESTORE_NONE ? SVTF_RESTORE_NONE : (int32_t)fp->frame_restoration_type;
+        lr.restoration_unit_size[p]  = fp->loop_restoration_size;
+        if (fp->frame_restoration_type == RESTORE_NONE)
+            continue;
+        int32_t hu, vu;
+        CHECK(svtf_lr_units(&s->geom, p, fp->loop_restoration_size, &hu, &vu), s->ctx);
+        if (!(units[p] = (svtf_lr_unit *)calloc((size_t)hu * vu, sizeof(svtf_lr_unit))))
+            die("malloc(units)", s->ctx);
+        for (int v = 0; v < vu; v++)
+            for (int u = 0; u < hu; u++) {
+                const RestorationUnitInfo *ri = lc->lr_unit[p] + v * lc->lr_stride[p] + u;
+                svtf_lr_unit              *o  = &units[p][v * hu + u];
+                o->restoration_type = ri->restoration_type == RESTORE_WIENER ? SVTF_RESTORE_WIENER
+                    : ri->restoration_type == RESTORE_SGRPROJ                 ? SVTF_RESTORE_SGRPROJ
+                                                                              : SVTF_RESTORE_NONE;
+                memcpy(o->wiener_vfilter, ri->wiener_info.vfilter, sizeof(o->wiener_vfilter));
+                memcpy(o->wiener_hfilter, ri->wiener_info.hfilter, sizeof(o->wiener_hfilter));
+                o->sgr_ep = ri->sgrproj_info.ep, o->sgr_xqd[0] = ri->sgrproj_info.xqd[0], o->sgr_xqd[1] = ri->sgrproj_info.xqd[1];
+            }
+    }
+    if (!(g_resident && s->resident)) {
+        void   *pp[3];
+        int32_t st[3];
+        plane_ptrs(pic, s->geom.sample_bytes, pp, st);
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, pp[0], st[0], pp[1], st[1], pp[2], st[2]), s->ctx);
+        if (!optimized_lr) {
+            if (!s->have_dbk) {
+                fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: loop restoration without the deblocked boundary rows "
+                                "(svt_aom_dec_av1_loop_restoration_save_boundary_lines(dec, 0) was not called for this frame)\n");
+                abort();
+            }
+            const int cw = s->geom.mi_cols * 4;
+            CHECK(svtf_upload_pre_cdef(s->ctx, s->dbk[0], cw, s->dbk[1], cw >> 1, s->dbk[2], cw >> 1), s->ctx);
+            CHECK(svtf_sync(s->ctx), s->ctx);
+        }
+        s->resident = 1;
+    }
+    s->have_dbk = 0;
+    const svtf_lr_unit *cu[3] = {units[0], units[1], units[2]};
+    CHECK(svtf_lr_apply_frame(s->ctx, &lr, cu), s->ctx);
+    if (!g_resident)
+        end_frame(s, pic), s->resident = 0;
+    for (int p = 0; p < 3; p++) free(units[p]);
 }

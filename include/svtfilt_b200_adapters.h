@@ -45,11 +45,14 @@ void svtf_adapter_release(const struct PictureControlSet *pcs);
  *                                          int32_t plane_end, int32_t is_mt, int enable_flag);   Decoder/Codec/EbDecLF.c:697
  *   void svt_cdef_frame(EbDecHandle*, int enable_flag);                                          Decoder/Codec/EbDecCdef.c:507
  *   void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle*, uint16_t *ext_rec_y);          Decoder/Codec/EbDecCcso.c:384
+ *   void svt_aom_dec_av1_loop_restoration_save_boundary_lines(EbDecHandle*, int after_cdef);     Decoder/Codec/EbDecRestoration.c:473
+ *   void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle*, int optimized_lr, int enable_flag);           :429
  */
 struct EbDecHandle;
 void svtf_dec_adapter_set_device(int device);
-/* 1: the frame stays on the GPU between the LF, CDEF and CCSO calls of one decoder handle; dec_ccso_frame (or
- * svtf_dec_adapter_fetch) brings it back.  0 (default): every entry point uploads and downloads. */
+/* 1: the frame stays on the GPU between the LF, CDEF, CCSO and loop-restoration calls of one decoder handle (the two
+ * save_boundary_lines calls become no-ops: the deblocked picture is still on the device); svtf_dec_adapter_fetch after the
+ * last enabled stage brings it back.  0 (default): every entry point uploads and downloads. */
 void svtf_dec_adapter_set_resident(int on);
 void svtf_dec_adapter_fetch(const struct EbDecHandle *dec, void *pic);
 void svtf_dec_adapter_release(const struct EbDecHandle *dec);

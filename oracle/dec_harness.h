@@ -249,4 +249,120 @@ static void dec_harness_fill_ccso(dec_harness *h, const svtf_ccso_params *p, con
     }
     h->sb_info[0].sb_ccso_blk_y[0] = blk[0], h->sb_info[0].sb_ccso_blk_u[0] = blk[1], h->sb_info[0].sb_ccso_blk_v[0] = blk[2];
 }
+
+/* ---- loop restoration (needs EbDecProcessFrame.h + EbRestoration.h; define DEC_HARNESS_LR before including) ----
+ * LrCtxt as init_lr_ctxt builds it for one thread (Decoder/Codec/EbDecMemInit.c:430-503): one RestorationLineBuffers and
+ * one scratch per plane, the deblocked-line store per plane, the [SB x 64] output scratch; lr_unit[plane] indexed
+ * [unit_row * sb_cols + unit_col] (EbDecMemInit.c:292-303, EbDecRestoration.c:341).  The picture gets a border: lr_pad_pic
+ * (EbDecRestoration.c:105) writes 6 samples around it and the Wiener kernels read a little further. */
+#ifdef DEC_HARNESS_LR
+#define DECH_BORDER 64
+typedef struct {
+    LrCtxt                  ctx;
+    RestorationLineBuffers *rlb[3], **rlbs0, ***rlbs;
+    int32_t                *tmp, **tmps;
+    void                   *padded[3], *orig[3];
+    int                     orig_st[3];
+} dec_harness_lr;
+
+static void dec_harness_lr_free(dec_harness_lr *l) {
+    for (int p = 0; p < 3; p++) {
+        free(l->ctx.lr_unit[p]), free(l->rlb[p]), free(l->padded[p]);
+        free(l->ctx.boundaries[p].stripe_boundary_above), free(l->ctx.boundaries[p].stripe_boundary_below);
+    }
+    free(l->rlbs0), free(l->rlbs), free(l->tmp), free(l->tmps), free(l->ctx.dst);
+}
+
+/* units[p]: svtf layout [vert][horz] (svtf_lr_units); pictures: moved into bordered buffers (dec_harness_lr_store copies back) */
+static int dec_harness_fill_lr(dec_harness *h, dec_harness_lr *l, const svtf_geom *g, const svtf_lr_params *lr,
+                               const svtf_lr_unit *const units[3]) {
+    memset(l, 0, sizeof(*l));
+    EbDecHandle *d   = h->dec;
+    const int    sb  = g->sample_bytes, nsb = h->sb_cols * h->sb_rows;
+    d->pv_lr_ctxt    = &l->ctx;
+    d->dec_config.threads = 1;
+    d->seq_header.max_frame_width = (uint16_t)g->width, d->seq_header.max_frame_height = (uint16_t)g->height;
+    Av1Common *cm = &d->cm;
+    cm->mi_rows = g->mi_rows, cm->mi_cols = g->mi_cols;
+    cm->frm_size.frame_width = (uint16_t)g->width, cm->frm_size.frame_height = (uint16_t)g->height;
+    cm->frm_size.superres_upscaled_width = (uint16_t)g->width, cm->frm_size.superres_upscaled_height = (uint16_t)g->height;
+    cm->frm_size.superres_denominator = SCALE_NUMERATOR;
+    d->frame_header.frame_size.superres_denominator = SCALE_NUMERATOR;
+    cm->subsampling_x = cm->subsampling_y = 1;
+    cm->bit_depth = g->bit_depth, cm->use_highbitdepth = sb == 2;
+    l->ctx.dec_handle_ptr = d;
+    l->ctx.is_thread_min  = TRUE;
+    l->rlbs = calloc(1, sizeof(*l->rlbs)), l->rlbs0 = calloc(3, sizeof(*l->rlbs0));
+    l->tmps = calloc(1, sizeof(*l->tmps)), l->tmp = malloc(RESTORATION_TMPBUF_SIZE);
+    l->ctx.dst = calloc((size_t)(MAX_SB_SIZE + 8) * RESTORATION_PROC_UNIT_SIZE, sb);
+    if (!l->rlbs || !l->rlbs0 || !l->tmps || !l->tmp || !l->ctx.dst)
+        return -1;
+    l->rlbs[0] = l->rlbs0, l->tmps[0] = l->tmp;
+    l->ctx.rlbs = l->rlbs, l->ctx.rst_tmpbuf = l->tmps;
+    const int num_stripes = (RESTORATION_UNIT_OFFSET + g->height + 63) / 64;
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        LrParams *fp = &d->frame_header.lr_params[p];
+        fp->frame_restoration_type = (RestorationType)lr->frame_restoration_type[p];
+        fp->loop_restoration_size  = (uint16_t)lr->restoration_unit_size[p];
+        fp->lr_size_log2           = 0;
+        while ((1 << fp->lr_size_log2) < lr->restoration_unit_size[p]) fp->lr_size_log2++;
+        l->rlb[p] = l->rlbs0[p] = calloc(1, sizeof(RestorationLineBuffers));
+        l->ctx.lr_unit[p]   = calloc(nsb, sizeof(RestorationUnitInfo));
+        l->ctx.lr_stride[p] = h->sb_cols;
+        const int plane_w = ((g->width + ss) >> ss) + 2 * RESTORATION_EXTRA_HORZ, stride = (plane_w + 31) & ~31;
+        const int size    = num_stripes * stride * RESTORATION_CTX_VERT * sb;
+        RestorationStripeBoundaries *b = &l->ctx.boundaries[p];
+        b->stripe_boundary_above = calloc(size, 1), b->stripe_boundary_below = calloc(size, 1);
+        b->stripe_boundary_size = size, b->stripe_boundary_stride = stride;
+        if (!l->rlb[p] || !l->ctx.lr_unit[p] || !b->stripe_boundary_above || !b->stripe_boundary_below)
+            return -1;
+        if (lr->frame_restoration_type[p] != SVTF_RESTORE_NONE) {
+            /* svt_av1_lr_count_units_in_tile (Common/Codec/EbRestoration.c:1318): max((size + unit / 2) / unit, 1) */
+            const int U = lr->restoration_unit_size[p], pw = (g->width + ss) >> ss, ph = (g->height + ss) >> ss;
+            const int hu = (pw + U / 2) / U > 1 ? (pw + U / 2) / U : 1, vu = (ph + U / 2) / U > 1 ? (ph + U / 2) / U : 1;
+            if (hu > h->sb_cols || vu * h->sb_cols > nsb)
+                return -1;
+            for (int v = 0; v < vu; v++)
+                for (int u = 0; u < hu; u++) {
+                    RestorationUnitInfo *ri = &l->ctx.lr_unit[p][v * h->sb_cols + u];
+                    const svtf_lr_unit  *su = &units[p][v * hu + u];
+                    ri->restoration_type = (RestorationType)su->restoration_type;
+                    memcpy(ri->wiener_info.vfilter, su->wiener_vfilter, sizeof(ri->wiener_info.vfilter));
+                    memcpy(ri->wiener_info.hfilter, su->wiener_hfilter, sizeof(ri->wiener_info.hfilter));
+                    ri->sgrproj_info.ep = su->sgr_ep, ri->sgrproj_info.xqd[0] = su->sgr_xqd[0], ri->sgrproj_info.xqd[1] = su->sgr_xqd[1];
+                }
+        }
+    }
+    /* bordered picture */
+    EbPictureBufferDesc *r = h->recon;
+    uint8_t **bufs[3] = {&r->buffer_y, &r->buffer_cb, &r->buffer_cr};
+    uint16_t *sts[3]  = {&r->stride_y, &r->stride_cb, &r->stride_cr};
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0, cw = (g->mi_cols * 4) >> ss, chh = (g->mi_rows * 4) >> ss, bd = DECH_BORDER >> ss;
+        const int stride = (cw + 2 * bd + 31) & ~31;
+        l->orig[p] = *bufs[p], l->orig_st[p] = *sts[p];
+        uint8_t *buf = l->padded[p] = calloc((size_t)stride * (chh + 2 * bd), sb);
+        if (!buf)
+            return -1;
+        for (int y = 0; y < chh; y++)
+            memcpy(buf + ((size_t)(y + bd) * stride + bd) * sb, (uint8_t *)l->orig[p] + (size_t)y * l->orig_st[p] * sb, (size_t)cw * sb);
+        *bufs[p] = buf, *sts[p] = (uint16_t)stride;
+    }
+    r->org_x = r->org_y = DECH_BORDER;
+    return 0;
+}
+
+/* bordered picture -> the caller's planes (visible size: lr_pad_pic overwrites coded rows below the picture) */
+static void dec_harness_lr_store(dec_harness *h, dec_harness_lr *l, const svtf_geom *g) {
+    EbPictureBufferDesc *r = h->recon;
+    const uint8_t *bufs[3] = {r->buffer_y, r->buffer_cb, r->buffer_cr};
+    const int      sts[3]  = {r->stride_y, r->stride_cb, r->stride_cr}, sb = g->sample_bytes;
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0, w = (g->width + ss) >> ss, hh = (g->height + ss) >> ss, bd = DECH_BORDER >> ss;
+        for (int y = 0; y < hh; y++)
+            memcpy((uint8_t *)l->orig[p] + (size_t)y * l->orig_st[p] * sb, bufs[p] + ((size_t)(y + bd) * sts[p] + bd) * sb, (size_t)w * sb);
+    }
+}
+#endif /* DEC_HARNESS_LR */
 #endif /* DEC_HARNESS_H */

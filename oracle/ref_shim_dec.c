@@ -5,6 +5,7 @@
  *   svt_cdef_frame                     Decoder/Codec/EbDecCdef.c:507
  *   dec_ccso_frame                     Decoder/Codec/EbDecCcso.c:384  (+ the ext_rec_y preparation of
  *                                      Decoder/Codec/EbDecParseObu.c:2399-2419)
+ *   svt_aom_dec_av1_loop_restoration_filter_frame / _save_boundary_lines   Decoder/Codec/EbDecRestoration.c:429 / :473
  * are compiled from the reference tree into oracle/_ref/libsvtrefdec.so (oracle/Makefile) and called on an EbDecHandle
  * built by dec_harness.h.  The decoder walks blocks -> transform units instead of the 4x4 grid, so these entry points
  * pin that the packed-mi formulation (svtf_pack_mi_dec) describes the same edges.
@@ -19,7 +20,11 @@
 #include "EbDecCdef.h"
 #include "EbDecCcso.h"
 #include "EbCcso.h"
+#include "EbDecProcessFrame.h"
+#include "EbDecRestoration.h"
+#include "EbRestoration.h"
 
+#define DEC_HARNESS_LR
 #include "dec_harness.h"
 
 #define REF_API __attribute__((visibility("default")))
@@ -61,5 +66,29 @@ REF_API int refdec_ccso_frame(const svtf_geom *g, void *y, int sy, void *cb, int
     dec_ccso_frame(h.recon, h.dec, ext);
     free(ext);
     dec_harness_free(&h);
+    return 0;
+}
+
+/* Loop restoration as the decoder runs it (Decoder/Codec/EbDecParseObu.c:2421-2455, single thread): the boundary lines of
+ * the DEBLOCKED picture (after_cdef = 0), of the picture to restore (after_cdef = 1), then the frame filter with
+ * optimized_lr = 0.  cur: in/out; dbk: the deblocked picture. */
+REF_API int refdec_lr_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, void *dy, int dsy, void *dcb, int dscb,
+                            void *dcr, int dscr, const dec_mi_soa *soa, const svtf_lr_params *lr, const svtf_lr_unit *const units[3]) {
+    dec_harness    h, hd;
+    dec_harness_lr l, ld;
+    if (dec_harness_init(&h, g, soa, y, sy, cb, scb, cr, scr) || dec_harness_fill_lr(&h, &l, g, lr, units))
+        return -1;
+    /* the deblocked picture goes through the same handle: swap it in for the first save */
+    if (dec_harness_init(&hd, g, soa, dy, dsy, dcb, dscb, dcr, dscr) || dec_harness_fill_lr(&hd, &ld, g, lr, units))
+        return -1;
+    EbPictureBufferDesc *cur = h.pic_buf->ps_pic_buf;
+    h.pic_buf->ps_pic_buf    = hd.recon;
+    svt_aom_dec_av1_loop_restoration_save_boundary_lines(h.dec, 0);
+    h.pic_buf->ps_pic_buf = cur;
+    svt_aom_dec_av1_loop_restoration_save_boundary_lines(h.dec, 1);
+    svt_aom_dec_av1_loop_restoration_filter_frame(h.dec, 0, 1);
+    dec_harness_lr_store(&h, &l, g);
+    dec_harness_lr_free(&l), dec_harness_lr_free(&ld);
+    dec_harness_free(&h), dec_harness_free(&hd);
     return 0;
 }

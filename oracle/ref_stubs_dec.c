@@ -20,6 +20,12 @@ STUB(generate_padding_l_hbd)
 STUB(generate_padding_r)
 STUB(generate_padding_r_hbd)
 STUB(generate_padding_t)
+STUB(svt_aom_realloc_frame_buffer)
+STUB(svt_aom_yv12_copy_y_c)
+STUB(svt_aom_yv12_copy_u_c)
+STUB(svt_aom_yv12_copy_v_c)
+STUB(svt_av1_upscale_normative_rows)
+STUB(svt_print_alloc_fail_impl)
 
 #define RTCD(name)   \
     void name##_c(); \
@@ -45,6 +51,10 @@ RTCD(svt_aom_cdef_find_dir_dual)
 RTCD(svt_cdef_filter_block)
 RTCD(svt_aom_copy_rect8_8bit_to_16bit)
 RTCD(ccso_filter_block_hbd_wo_buf)
+RTCD(svt_apply_selfguided_restoration)
+RTCD(svt_av1_wiener_convolve_add_src)
+RTCD(svt_av1_highbd_wiener_convolve_add_src)
+void svt_log(int level, const char *tag, const char *fmt, ...) { (void)level, (void)tag, (void)fmt; }
 
 static void memcpy_c(void *d, const void *s, size_t n) { memcpy(d, s, n); }
 void (*svt_memcpy)(void *, const void *, size_t) = memcpy_c;

@@ -593,6 +593,17 @@ class DecDriver:
         return out
 
 
+    def lr_apply(self, geom, cur, dbk, soa, lr, units):
+        """svt_aom_dec_av1_loop_restoration_save_boundary_lines(0 / 1) + _filter_frame on the decoder handle; units in
+        the svtf layout ([vert][horz] per plane)."""
+        out = [p.copy() for p in cur]
+        dbk = [np.ascontiguousarray(p) for p in dbk]
+        s, keep = dec_soa_struct(soa)
+        up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
+        assert self._fn("lr_frame")(C.byref(geom), *_planes(out), *_planes(dbk), C.byref(s), C.byref(lr), up) == 0
+        return out
+
+
 def refdec_available():
     return os.path.exists(REFDEC_PATH)
 

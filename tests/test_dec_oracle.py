@@ -96,3 +96,33 @@ def test_decoder_ccso_where_defined(H, orc, refdec, w, h, seed, blk, bo, band, c
     vis = lambda pl: [a[:h >> s, :w >> s] for a, s in zip(pl, (0, 1, 1))]
     assert H.planes_equal(vis(got), vis(exp)), H.first_diff(vis(got), vis(exp))
     assert not H.planes_equal(vis(got), vis(rec))
+
+
+# ---- loop restoration as the decoder runs it (Decoder/Codec/EbDecRestoration.c) ----
+def _vis(g, planes):
+    return [p[: (g.height + s) >> s, : (g.width + s) >> s] for p, s in zip(planes, (0, 1, 1))]
+
+
+@pytest.mark.parametrize("w,h,bd,sb,seed,kw", [
+    (136, 72, 8, 1, 1, {}),
+    (200, 136, 10, 2, 2, {}),
+    (264, 200, 10, 2, 3, {"unit_size": (128, 64, 64)}),
+    (72, 136, 12, 2, 4, {}),
+    (328, 200, 8, 2, 5, {"unit_size": (256, 128, 128), "p_none": 0.0}),
+    (136, 200, 8, 1, 6, {"frame_type": (1, 0, 2)}),
+    (200, 120, 8, 1, 7, {}),          # the last stripe ends on the crop border
+    (136, 264, 10, 2, 8, {"unit_size": (64, 64, 64)}),
+])
+def test_decoder_lr_matches_oracle(H, orc, refdec, w, h, bd, sb, seed, kw):
+    """svt_aom_dec_av1_loop_restoration_filter_frame walks SB rows x 64-column blocks with column save/restore; the oracle
+    evaluates every sample from its stripe input — same pixels."""
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    dbk = H.synth_picture(g, 8700 + seed, noise=10)
+    cur = H.synth_source(g, dbk, 8750 + seed, amp=6)
+    soa = H.synth_dec_mode_info(g, 8800 + seed)
+    lr, units = H.synth_lr(g, 8850 + seed, **kw)
+    exp = orc.lr_apply(g, cur, dbk, lr, units)
+    got = refdec.lr_apply(g, cur, dbk, soa, lr, units)
+    assert H.planes_equal(_vis(g, got), _vis(g, exp)), H.first_diff(_vis(g, got), _vis(g, exp))
+    assert not H.planes_equal(_vis(g, got), _vis(g, cur))

@@ -119,3 +119,57 @@ def test_dec_ccso_adapter_single_block(H, orc, adaptdec, refdec, w, h, seed, blk
     flags = [np.array([blk[2]], np.uint8), np.array([blk[1]], np.uint8), np.array([blk[2]], np.uint8)]
     exp2 = orc.ccso_apply(g, rec, pre[0], c0, flags)
     assert H.planes_equal(got, exp2), H.first_diff(got, exp2)
+
+
+def _vis(g, planes):
+    return [p[: (g.height + s) >> s, : (g.width + s) >> s] for p, s in zip(planes, (0, 1, 1))]
+
+
+@pytest.mark.parametrize("w,h,bd,sb,seed,kw", [
+    (136, 72, 8, 1, 1, {}),
+    (200, 136, 10, 2, 2, {}),
+    (264, 200, 10, 2, 3, {"unit_size": (128, 64, 64)}),
+    (72, 136, 12, 2, 4, {}),
+    (328, 200, 8, 2, 5, {"unit_size": (256, 128, 128), "p_none": 0.0}),
+    (136, 200, 8, 1, 6, {"frame_type": (1, 0, 2)}),
+    (200, 120, 8, 1, 7, {}),
+])
+def test_dec_loop_restoration_adapter(H, orc, adaptdec, refdec, w, h, bd, sb, seed, kw):
+    """save_boundary_lines(0) / (1) + svt_aom_dec_av1_loop_restoration_filter_frame, stand-alone, on a bordered picture."""
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    dbk = H.synth_picture(g, 10500 + seed, noise=10)
+    cur = H.synth_source(g, dbk, 10550 + seed, amp=6)
+    soa = H.synth_dec_mode_info(g, 10600 + seed)
+    lr, units = H.synth_lr(g, 10650 + seed, **kw)
+    got = adaptdec.lr_apply(g, cur, dbk, soa, lr, units)
+    exp = orc.lr_apply(g, cur, dbk, lr, units)
+    assert H.planes_equal(_vis(g, got), _vis(g, exp)), H.first_diff(_vis(g, got), _vis(g, exp))
+    if refdec:
+        ref = refdec.lr_apply(g, cur, dbk, soa, lr, units)
+        assert H.planes_equal(_vis(g, got), _vis(g, ref))
+
+
+@pytest.mark.parametrize("w,h,bd,sb,seed", [(264, 200, 10, 2, 1), (200, 136, 8, 1, 2)])
+def test_dec_chain_lf_cdef_lr_resident(H, orc, adaptdec, w, h, bd, sb, seed):
+    """The decoder's order LF -> save(0) -> CDEF -> save(1) -> LR with the frame on the device throughout."""
+    import ctypes as C
+
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    rec = H.synth_picture(g, 10700 + seed, noise=8)
+    soa = H.synth_dec_mode_info(g, 10710 + seed, p_skip=0.4)
+    lf = S.lf_params((22, 20), 15, 13)
+    cdef, idx = H.synth_cdef(g, 10720 + seed)
+    lr, units = H.synth_lr(g, 10730 + seed)
+    out = [p.copy() for p in rec]
+    s, keep = H.dec_soa_struct(soa)
+    idx8 = np.ascontiguousarray(idx, dtype=np.int8)
+    up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
+    assert adaptdec.lib.adaptdec_chain_lr_resident(C.byref(g), *H._planes(out), C.byref(s), C.byref(lf), C.byref(cdef), H._p(idx8),
+                                                   C.byref(lr), up) == 0
+    mi = H.pack_mi_dec(soa)
+    d = orc.deblock(g, rec, mi, lf)
+    c = orc.cdef_apply(g, d, mi, cdef, idx)
+    exp = orc.lr_apply(g, c, d, lr, units)
+    assert H.planes_equal(_vis(g, out), _vis(g, exp)), H.first_diff(_vis(g, out), _vis(g, exp))
