@@ -19,6 +19,7 @@
 #include "svtf_pick.cuh"
 #include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
+#include "svtf_cdef3.cuh"
 #include "svtf_mi_pack.cuh"
 #include "svtf_lr.cuh"
 
@@ -107,6 +108,7 @@ struct svtf_ctx {
     size_t       sb_lvl_cap = 0;
     void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
     uint64_t     launches = 0;
+    bool         cdef3_ready = false;      // dynamic shared-memory opt-in of cdef3_kernel done on this device
     std::string  err;
 
     int fail(int code, const std::string &m) {
@@ -824,10 +826,36 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
         memset(&b.ccso, 0, sizeof(b.ccso));
         if (cc)
             ccso_fill(c, cc, blk_flags, b.ccso);
-        if (c->geom.sample_bytes == 1)
-            cdef2_kernel<uint8_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
-        else
-            cdef2_kernel<uint16_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
+        // A/B switches: SVTF_CDEF_V2 = the round-1b kernel, SVTF_CDEF_INT = cdef3 with packed-integer taps at every bit depth
+        static const bool use_v2 = getenv("SVTF_CDEF_V2") != nullptr, force_int = getenv("SVTF_CDEF_INT") != nullptr;
+        if (use_v2) {
+            if (c->geom.sample_bytes == 1)
+                cdef2_kernel<uint8_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
+            else
+                cdef2_kernel<uint16_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
+        } else {
+            constexpr int smem_i = C3_SMEM_WORDS_I * 4, smem_f = C3_SMEM_WORDS_F * 4;
+            if (!c->cdef3_ready) {
+                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
+                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
+                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
+                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
+                c->cdef3_ready = true;
+            }
+            // fp16 taps are exact for samples < 1024 and luma damping + (bit_depth - 8) <= 9 (svtf_cdef3.cuh)
+            const bool fp = !force_int && c->geom.bit_depth <= 10 && cp->cdef_damping + (c->geom.bit_depth - 8) <= 9;
+            if (c->geom.sample_bytes == 1) {
+                if (fp)
+                    cdef3_kernel<uint8_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
+                else
+                    cdef3_kernel<uint8_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
+            } else {
+                if (fp)
+                    cdef3_kernel<uint16_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
+                else
+                    cdef3_kernel<uint16_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
+            }
+        }
     }
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
