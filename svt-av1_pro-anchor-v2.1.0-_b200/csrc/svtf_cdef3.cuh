@@ -41,52 +41,50 @@ __device__ __forceinline__ __half2  u2h(const uint32_t u) { return *reinterpret_
 __device__ __forceinline__ uint32_t pk_i2h(const uint32_t w) { return h2u(__hsub2(u2h(w | 0x64006400u), u2h(0x64006400u))); }
 __device__ __forceinline__ uint32_t pk_h2i(const uint32_t f) { return h2u(__hadd2(u2h(f), u2h(0x64006400u))) & 0x03FF03FFu; }
 
-// Stage rows x (8*chunks) samples as A (even pair alignment) and B (odd: word i = samples 2i+1, 2i+2); tile origin =
-// (x0-8, y0-2); outside the coded plane -> sentinel.  FP: A/B hold fp16 values and I (if given) the integer pairs.
-template <typename T, bool FP>
-__device__ __forceinline__ void cdef3_stage(uint32_t *A, uint32_t *B, uint32_t *I, const int pw, const int rows, const int chunks,
-                                            const T *in, const int ipitch, const int x0, const int y0, const int cw, const int ch,
-                                            const int tid) {
-    const uint32_t S = FP ? C3_SENT_F : C3_SENT_I;
-    for (int i = tid; i < rows * chunks; i += C2_THREADS) {
-        const int r = i / chunks, c = (i - r * chunks) * 8;
-        const int gy = y0 - 2 + r, gx = x0 - 8 + c;
-        uint32_t  w0 = S, w1 = S, w2 = S, w3 = S, wn = S; // wn.lo = first sample of the next chunk
-        uint32_t  i0 = 0, i1 = 0, i2 = 0, i3 = 0;
-        if (gy >= 0 && gy < ch) {
-            const T *row = in + (size_t)gy * ipitch;
-            if (gx >= 0 && gx < cw) { // cw is a multiple of 8 (luma) / 4 (chroma)
-                if (gx + 8 <= cw) {
-                    const uint4 v = ld8<T>(row + gx);
-                    i0 = v.x, i1 = v.y, i2 = v.z, i3 = v.w;
-                    if (FP)
-                        w0 = pk_i2h(i0), w1 = pk_i2h(i1), w2 = pk_i2h(i2), w3 = pk_i2h(i3);
-                    else
-                        w0 = i0, w1 = i1, w2 = i2, w3 = i3;
-                } else { // chroma planes whose width is 4 mod 8: last half chunk
-                    const uint2 h = ld4<T>(row + gx);
-                    i0 = h.x, i1 = h.y;
-                    if (FP)
-                        w0 = pk_i2h(i0), w1 = pk_i2h(i1);
-                    else
-                        w0 = i0, w1 = i1;
-                }
-            }
-            const int gn = gx + 8;
-            if (gn >= 0 && gn < cw) {
-                const uint32_t n = (uint32_t)__ldg(row + gn);
-                wn               = FP ? pk_i2h(n) : n;
+// Staging is split in two so that every global load of a thread (tile chunks, CCSO LUT, side info) is in flight before
+// the first one is consumed: c3_load fetches one 8-sample chunk + the sample that follows it into registers, c3_store
+// writes it as A (even pair alignment), B (odd: word i = samples 2i+1, 2i+2) and, FP only, I (the integer pairs; A/B
+// then hold fp16 values).  Tile origin = (x0-8, y0-2); outside the coded plane -> sentinel.
+struct C3Chunk {
+    uint32_t w0, w1, w2, w3, wn; // raw integer pairs; wn.lo = first sample of the next chunk
+    int      m;                  // bit 0: w0,w1 valid; bit 1: w2,w3 valid; bit 2: wn valid
+};
+template <typename T>
+__device__ __forceinline__ C3Chunk c3_load(const T *in, const int ipitch, const int gx, const int gy, const int cw, const int ch,
+                                           const bool item) {
+    C3Chunk k;
+    k.w0 = k.w1 = k.w2 = k.w3 = k.wn = 0, k.m = 0;
+    if (item && gy >= 0 && gy < ch) {
+        const T *row = in + (size_t)gy * ipitch;
+        if (gx >= 0 && gx < cw) { // cw is a multiple of 8 (luma) / 4 (chroma)
+            if (gx + 8 <= cw) {
+                const uint4 v = ld8<T>(row + gx);
+                k.w0 = v.x, k.w1 = v.y, k.w2 = v.z, k.w3 = v.w, k.m = 3;
+            } else { // chroma planes whose width is 4 mod 8: last half chunk
+                const uint2 h = ld4<T>(row + gx);
+                k.w0 = h.x, k.w1 = h.y, k.m = 1;
             }
         }
-        const int o = r * pw + (c >> 1);
-        A[o] = w0, A[o + 1] = w1, A[o + 2] = w2, A[o + 3] = w3;
-        B[o]     = __byte_perm(w0, w1, 0x5432);
-        B[o + 1] = __byte_perm(w1, w2, 0x5432);
-        B[o + 2] = __byte_perm(w2, w3, 0x5432);
-        B[o + 3] = __byte_perm(w3, wn, 0x5432);
-        if (FP && I)
-            I[o] = i0, I[o + 1] = i1, I[o + 2] = i2, I[o + 3] = i3;
+        const int gn = gx + 8;
+        if (gn >= 0 && gn < cw)
+            k.wn = (uint32_t)__ldg(row + gn), k.m |= 4;
     }
+    return k;
+}
+template <bool FP>
+__device__ __forceinline__ void c3_store(uint32_t *A, uint32_t *B, uint32_t *I, const int o, const C3Chunk &k) {
+    const uint32_t S  = FP ? C3_SENT_F : C3_SENT_I;
+    const bool     v0 = k.m & 1, v1 = k.m & 2, vn = k.m & 4;
+    const uint32_t w0 = v0 ? (FP ? pk_i2h(k.w0) : k.w0) : S, w1 = v0 ? (FP ? pk_i2h(k.w1) : k.w1) : S;
+    const uint32_t w2 = v1 ? (FP ? pk_i2h(k.w2) : k.w2) : S, w3 = v1 ? (FP ? pk_i2h(k.w3) : k.w3) : S;
+    const uint32_t wn = vn ? (FP ? pk_i2h(k.wn) : k.wn) : S;
+    A[o] = w0, A[o + 1] = w1, A[o + 2] = w2, A[o + 3] = w3;
+    B[o]     = __byte_perm(w0, w1, 0x5432);
+    B[o + 1] = __byte_perm(w1, w2, 0x5432);
+    B[o + 2] = __byte_perm(w2, w3, 0x5432);
+    B[o + 3] = __byte_perm(w3, wn, 0x5432);
+    if (FP && I)
+        I[o] = k.w0, I[o + 1] = k.w1, I[o + 2] = k.w2, I[o + 3] = k.w3;
 }
 
 // Per-thread strength constants of one tap class (primary or secondary).
@@ -232,7 +230,7 @@ __global__ void __launch_bounds__(C2_THREADS, 3) cdef3_kernel(const __grid_const
     __shared__ uint8_t s_dir[64];
     __shared__ int     s_var[64];
     __shared__ uint8_t s_active[64];
-    __shared__ __align__(4) uint8_t s_lut[3][SVTF_CCSO_LUT_SIZE]; // CCSO offsets + 128
+    __shared__ __align__(16) uint8_t s_lut[3][SVTF_CCSO_LUT_SIZE]; // CCSO offsets + 128
 
     const int tid = threadIdx.x;
     const int fbc = blockIdx.x, fbr = blockIdx.y + a.fbr0;
@@ -241,20 +239,65 @@ __global__ void __launch_bounds__(C2_THREADS, 3) cdef3_kernel(const __grid_const
     const int x0 = fbc * 64, y0 = fbr * 64;
     const int cs = a.d.bit_depth - 8;
 
-    const int idx = a.fb_idx[fbr * nhfb + fbc];
-    int       ylev = 0, ysec = 0, uvlev = 0, uvsec = 0;
+    const T *iny  = static_cast<const T *>(a.in.p[0]);
+    T       *outy = static_cast<T *>(a.out.p[0]);
+    const int W = a.d.width, H = a.d.height;
+
+    // ---- every global load of this thread, issued before the first use ----
+    const int idx = __ldg(a.fb_idx + fbr * nhfb + fbc);
+    int       flg = 0; // bit p: CCSO block flag of plane p (one flag per 256x256 luma samples, row = ceil(plane width / block))
+    if (a.ccso.on) {
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+            bool on = a.ccso.enable[p];
+            if (on && a.ccso.blk_flags[p]) {
+                const int pwid = W >> (p ? 1 : 0), bl = p ? 7 : 8;
+                const int nbx  = (pwid + (1 << bl) - 1) >> bl;
+                on             = (x0 >> 8) < nbx && __ldg(a.ccso.blk_flags[p] + ((y0 + a.ccso.y_glob) >> 8) * nbx + (x0 >> 8)) != 0;
+            }
+            flg |= (int)on << p;
+        }
+    }
+    svtf_mi_t m4[4] = {~0u, ~0u, ~0u, ~0u};
+    bool      mi_in = false;
+    if (tid < 64) { // svt_sb_compute_cdef_list — Encoder/Codec/EbEncCdef.c:238-281
+        const int r = (tid >> 3) * 2, c = (tid & 7) * 2;
+        mi_in = fbr * 16 + r < a.d.mi_rows && fbc * 16 + c < a.d.mi_cols;
+        if (mi_in) {
+            const svtf_mi_t *m = a.mi + (fbr * 16 + r) * a.mi_stride + fbc * 16 + c;
+            m4[0] = __ldg(m), m4[1] = __ldg(m + 1), m4[2] = __ldg(m + a.mi_stride), m4[3] = __ldg(m + a.mi_stride + 1);
+        }
+    }
+    C3Chunk ky[3], kc[2];
+    int     ry[3], cy[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) { // luma: 68 rows x 10 chunks
+        const int i = tid + k * C2_THREADS;
+        ry[k] = i / 10, cy[k] = (i - ry[k] * 10) * 8;
+        ky[k] = c3_load<T>(iny, a.in.pitch[0], x0 - 8 + cy[k], y0 - 2 + ry[k], cw, ch, i < C2_YROWS * 10);
+    }
+    const int rc = tid / 6, cc = (tid - rc * 6) * 8; // chroma: 36 rows x 6 chunks per plane
+#pragma unroll
+    for (int p = 0; p < 2; p++)
+        kc[p] = c3_load<T>(static_cast<const T *>(a.in.p[1 + p]), a.in.pitch[1 + p], x0 / 2 - 8 + cc, y0 / 2 - 2 + rc, cw / 2, ch / 2,
+                           tid < C2_CROWS * 6);
+    // CCSO LUTs (3 x 2048 bytes = 384 x 16 bytes) of the planes that can run
+    uint4      l0 = make_uint4(0, 0, 0, 0), l1 = l0;
+    const bool lut0 = a.ccso.on && a.ccso.enable[tid >> 7], lut1 = a.ccso.on && a.ccso.enable[2] && tid < 128;
+    if (lut0)
+        l0 = __ldg(reinterpret_cast<const uint4 *>(a.ccso.lut) + tid);
+    if (lut1)
+        l1 = __ldg(reinterpret_cast<const uint4 *>(a.ccso.lut) + C2_THREADS + tid);
+
+    int ylev = 0, ysec = 0, uvlev = 0, uvsec = 0;
     if (idx >= 0) {
         const int ys = a.y_strength[idx], us = a.uv_strength[idx];
         ylev = ys >> 2, ysec = ys & 3, ysec += ysec == 3;
         uvlev = us >> 2, uvsec = us & 3, uvsec += uvsec == 3;
     }
     int act = 0;
-    if (tid < 64) { // svt_sb_compute_cdef_list — Encoder/Codec/EbEncCdef.c:238-281
-        const int r = (tid >> 3) * 2, c = (tid & 7) * 2;
-        if (fbr * 16 + r < a.d.mi_rows && fbc * 16 + c < a.d.mi_cols) {
-            const svtf_mi_t *m = a.mi + (fbr * 16 + r) * a.mi_stride + fbc * 16 + c;
-            act = !(mi_skip(__ldg(m)) & mi_skip(__ldg(m + 1)) & mi_skip(__ldg(m + a.mi_stride)) & mi_skip(__ldg(m + a.mi_stride + 1)));
-        }
+    if (tid < 64) {
+        act           = mi_in && !(mi_skip(m4[0]) & mi_skip(m4[1]) & mi_skip(m4[2]) & mi_skip(m4[3]));
         s_active[tid] = (uint8_t)act;
     } else if (tid < 96) {
         // Cdef_Directions (Common/Codec/EbCdef.c:99-122) as nibble tables (value + 2) indexed by direction:
@@ -267,48 +310,38 @@ __global__ void __launch_bounds__(C2_THREADS, 3) cdef3_kernel(const __grid_const
     }
     const int  any_active = __syncthreads_or(act);
     const bool process    = (ylev | ysec | uvlev | uvsec) && any_active;
+    const int  q_on       = flg; // bit p: CCSO (ccso_frame, Common/Codec/EbCcso.c:626) runs on plane p of this tile
 
-    // ---- fused CCSO (ccso_frame, Common/Codec/EbCcso.c:626): per-plane state of this 64x64 luma tile ----
-    const int W = a.d.width, H = a.d.height;
-    int       q_on = 0; // bit p: CCSO runs on plane p of this tile
-    if (a.ccso.on) {
+    if (!process && !q_on) { // untouched filter block: carry the interior chunks over to the output surface
 #pragma unroll
-        for (int p = 0; p < 3; p++) {
-            bool on = a.ccso.enable[p];
-            if (on && a.ccso.blk_flags[p]) { // one flag per 256x256 luma samples, row length = ceil(plane width / block)
-                const int pwid = W >> (p ? 1 : 0), bl = p ? 7 : 8;
-                const int nbx  = (pwid + (1 << bl) - 1) >> bl;
-                on             = (x0 >> 8) < nbx && a.ccso.blk_flags[p][((y0 + a.ccso.y_glob) >> 8) * nbx + (x0 >> 8)] != 0;
+        for (int k = 0; k < 3; k++)
+            if (ry[k] >= 2 && ry[k] < 66 && cy[k] >= 8 && cy[k] < 72 && (ky[k].m & 3) == 3)
+                st8<T>(outy + (size_t)(y0 - 2 + ry[k]) * a.out.pitch[0] + x0 - 8 + cy[k], make_uint4(ky[k].w0, ky[k].w1, ky[k].w2, ky[k].w3));
+#pragma unroll
+        for (int p = 0; p < 2; p++)
+            if (rc >= 2 && rc < 34 && cc >= 8 && cc < 40 && (kc[p].m & 1)) {
+                T *o = static_cast<T *>(a.out.p[1 + p]) + (size_t)(y0 / 2 - 2 + rc) * a.out.pitch[1 + p] + x0 / 2 - 8 + cc;
+                if ((kc[p].m & 3) == 3)
+                    st8<T>(o, make_uint4(kc[p].w0, kc[p].w1, kc[p].w2, kc[p].w3));
+                else
+                    st4<T>(o, make_uint2(kc[p].w0, kc[p].w1));
             }
-            q_on |= (int)on << p;
-        }
-    }
-    const T *iny  = static_cast<const T *>(a.in.p[0]);
-    T       *outy = static_cast<T *>(a.out.p[0]);
-    if (!process && !q_on) { // untouched filter block: carry the samples over to the output surface
-        for (int i = tid; i < 64 * 8; i += C2_THREADS) {
-            const int r = i >> 3, c = (i & 7) * 8;
-            if (y0 + r < ch && x0 + c < cw)
-                st8<T>(outy + (size_t)(y0 + r) * a.out.pitch[0] + x0 + c, ld8<T>(iny + (size_t)(y0 + r) * a.in.pitch[0] + x0 + c));
-        }
-        for (int i = tid; i < 2 * 32 * 8; i += C2_THREADS) {
-            const int p = 1 + (i >> 8), r = (i >> 3) & 31, c = (i & 7) * 4;
-            if (y0 / 2 + r < ch / 2 && x0 / 2 + c < cw / 2)
-                st4<T>(static_cast<T *>(a.out.p[p]) + (size_t)(y0 / 2 + r) * a.out.pitch[p] + x0 / 2 + c,
-                       ld4<T>(static_cast<const T *>(a.in.p[p]) + (size_t)(y0 / 2 + r) * a.in.pitch[p] + x0 / 2 + c));
-        }
         return;
     }
 
-    if (q_on) // LUTs of the planes that run, biased by +128
-        for (int i = tid; i < 3 * SVTF_CCSO_LUT_SIZE / 4; i += C2_THREADS)
-            if ((q_on >> (i / (SVTF_CCSO_LUT_SIZE / 4))) & 1)
-                reinterpret_cast<uint32_t *>(&s_lut[0][0])[i] = __ldg(reinterpret_cast<const uint32_t *>(a.ccso.lut) + i) ^ 0x80808080u;
-    cdef3_stage<T, FP>(yA, yA + C3_YSZ, FP ? yI : nullptr, C2_YPW, C2_YROWS, 10, iny, a.in.pitch[0], x0, y0, cw, ch, tid);
-    cdef3_stage<T, FP>(cA0, cA0 + C3_CSZ, nullptr, C2_CPW, C2_CROWS, 6, static_cast<const T *>(a.in.p[1]), a.in.pitch[1], x0 / 2, y0 / 2,
-                       cw / 2, ch / 2, tid);
-    cdef3_stage<T, FP>(cA0 + 2 * C3_CSZ, cA0 + 3 * C3_CSZ, nullptr, C2_CPW, C2_CROWS, 6, static_cast<const T *>(a.in.p[2]), a.in.pitch[2],
-                       x0 / 2, y0 / 2, cw / 2, ch / 2, tid);
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+        if (tid + k * C2_THREADS < C2_YROWS * 10)
+            c3_store<FP>(yA, yA + C3_YSZ, FP ? yI : nullptr, ry[k] * C2_YPW + (cy[k] >> 1), ky[k]);
+    if (tid < C2_CROWS * 6) {
+        c3_store<FP>(cA0, cA0 + C3_CSZ, nullptr, rc * C2_CPW + (cc >> 1), kc[0]);
+        c3_store<FP>(cA0 + 2 * C3_CSZ, cA0 + 3 * C3_CSZ, nullptr, rc * C2_CPW + (cc >> 1), kc[1]);
+    }
+    if (lut0) // biased by +128
+        reinterpret_cast<uint4 *>(&s_lut[0][0])[tid] = make_uint4(l0.x ^ 0x80808080u, l0.y ^ 0x80808080u, l0.z ^ 0x80808080u, l0.w ^ 0x80808080u);
+    if (lut1)
+        reinterpret_cast<uint4 *>(&s_lut[0][0])[C2_THREADS + tid] =
+            make_uint4(l1.x ^ 0x80808080u, l1.y ^ 0x80808080u, l1.z ^ 0x80808080u, l1.w ^ 0x80808080u);
     __syncthreads();
     // ---- direction search: thread = (block, half of the directions) ----
     if (tid < 128 && process) {
