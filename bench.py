@@ -436,7 +436,7 @@ def main():
     ap.add_argument("--batch", type=int, default=12, help="distinct 4K pictures resident per GPU (12 x 24.9 MB x 3 surfaces > L2)")
     ap.add_argument("--streams", type=int, default=4, help="CUDA streams the resident pictures are spread over (independent pictures)")
     ap.add_argument("--e2e-inflight", type=int, default=4)
-    ap.add_argument("--search-inflight", type=int, default=4, help="pictures in flight in the CDEF-search leg")
+    ap.add_argument("--search-inflight", type=int, default=8, help="pictures in flight in the CDEF-search leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

@@ -256,3 +256,49 @@ def test_device_pick_after_search(H, orc):
     b = orc.cdef_pick(cfg, mse, skip)
     assert _params_sig(a[0]) == _params_sig(b[0])
     assert np.array_equal(a[1], b[1])
+
+
+@pytest.mark.parametrize("bd,sb", [(8, 1), (10, 2), (8, 2)])
+def test_cdef_fp16_taps_exact_on_extreme_content(H, orc, bd, sb):
+    """cdef3_kernel runs the taps of 8/10-bit pictures in packed fp16 (svtf_cdef3.cuh).  Full-range white noise, 0/max
+    checkerboards and steep ramps make every |p - x| / strength / shift combination occur; every one of the 64 luma and
+    chroma strengths and dampings 3..9 (9 and, at 10 bits, 8 fall back to the packed-integer taps) must stay bit-exact."""
+    S = H.S
+    g = S.make_geom(512, 256, bd, sb)
+    rng = np.random.default_rng(0xF16 + bd)
+    mx = (1 << bd) - 1
+    dt = np.uint8 if sb == 1 else np.uint16
+    pics = []
+    for kind in range(3):
+        pl = []
+        for p in range(3):
+            s = 1 if p else 0
+            w, h = (g.mi_cols * 4) >> s, (g.mi_rows * 4) >> s
+            if kind == 0:
+                v = rng.integers(0, mx + 1, size=(h, w))
+            elif kind == 1:
+                yy, xx = np.mgrid[0:h, 0:w]
+                v = (((xx // 3 + yy // 2) & 1) * mx) ^ (rng.integers(0, 4, size=(h, w)) == 0) * rng.integers(0, mx + 1, size=(h, w))
+            else:
+                yy, xx = np.mgrid[0:h, 0:w]
+                v = np.clip((xx * 37 + yy * 91) % (2 * mx + 2) - (mx // 2) + rng.integers(-3, 4, size=(h, w)), 0, mx)
+            pl.append(np.ascontiguousarray(v.astype(dt)))
+        pics.append(pl)
+    soa = H.synth_mode_info(g, 0xF17, p_skip=0.2)
+    mi = H.pack_mi(soa)
+    nv, nh = H.nfb_of(g)
+    with S.FilterContext(g) as ctx:
+        for damping in (3, 4, 5, 6, 7, 8, 9):
+            for rot in range(8):
+                ys = [(8 * rot + k) % 64 for k in range(8)]
+                us = [(8 * rot + 5 * k + 3) % 64 for k in range(8)]
+                cdef = S.cdef_params(damping, ys, us)
+                idx = ((np.arange(nv * nh) + rot) % 8).astype(np.int8)
+                rec = pics[(rot + damping) % 3]
+                ctx.begin(g)
+                ctx.upload(rec)
+                ctx.set_mi(mi)
+                ctx.cdef_frame(cdef, idx)
+                got = ctx.download()
+                exp = orc.cdef_apply(g, rec, mi, cdef, idx)
+                assert H.planes_equal(got, exp), f"damping {damping} strengths {ys} {us}: " + H.first_diff(got, exp)
