@@ -20,6 +20,7 @@
 #include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
 #include "svtf_cdef3.cuh"
+#include "svtf_search3.cuh"
 #include "svtf_mi_pack.cuh"
 #include "svtf_lr.cuh"
 
@@ -108,6 +109,7 @@ struct svtf_ctx {
     size_t       sb_lvl_cap = 0;
     void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
     uint64_t     launches = 0;
+    bool         search3_ready = false;    // same for cdef_search3_kernel
     bool         cdef3_ready = false;      // dynamic shared-memory opt-in of cdef3_kernel done on this device
     std::string  err;
 
@@ -1037,10 +1039,24 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
             if (a.fs_uv[gi] != -1)
                 b.present_uv |= 1ull << (a.fs[gi] & 63);
         }
-        if (c->geom.sample_bytes == 1)
-            cdef_search2_kernel<uint8_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
-        else
-            cdef_search2_kernel<uint16_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
+        static const bool use_v2 = getenv("SVTF_SEARCH_V2") != nullptr; // A/B switch: packed-integer taps (svtf_search2.cuh)
+        if (use_v2) {
+            if (c->geom.sample_bytes == 1)
+                cdef_search2_kernel<uint8_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
+            else
+                cdef_search2_kernel<uint16_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
+        } else { // fp16 taps (svtf_search3.cuh); search damping = 3 + (base_q_idx >> 6) <= 6, inside the exactness bound
+            constexpr int smem = S3_SMEM_WORDS * 4;
+            if (!c->search3_ready) {
+                CUDA_TRY(c, cudaFuncSetAttribute(cdef_search3_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                CUDA_TRY(c, cudaFuncSetAttribute(cdef_search3_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                c->search3_ready = true;
+            }
+            if (c->geom.sample_bytes == 1)
+                cdef_search3_kernel<uint8_t><<<grid, S2_THREADS, smem, c->stream>>>(b);
+            else
+                cdef_search3_kernel<uint16_t><<<grid, S2_THREADS, smem, c->stream>>>(b);
+        }
     }
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;

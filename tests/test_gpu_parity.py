@@ -258,6 +258,29 @@ def test_device_pick_after_search(H, orc):
     assert np.array_equal(a[1], b[1])
 
 
+def _extreme_pictures(g, seed):
+    """Full-range white noise, a 0/max checkerboard with random outliers, a steep wrapping ramp."""
+    rng = np.random.default_rng(seed)
+    mx = (1 << g.bit_depth) - 1
+    dt = np.uint8 if g.sample_bytes == 1 else np.uint16
+    pics = []
+    for kind in range(3):
+        pl = []
+        for p in range(3):
+            s = 1 if p else 0
+            w, h = (g.mi_cols * 4) >> s, (g.mi_rows * 4) >> s
+            yy, xx = np.mgrid[0:h, 0:w]
+            if kind == 0:
+                v = rng.integers(0, mx + 1, size=(h, w))
+            elif kind == 1:
+                v = (((xx // 3 + yy // 2) & 1) * mx) ^ (rng.integers(0, 4, size=(h, w)) == 0) * rng.integers(0, mx + 1, size=(h, w))
+            else:
+                v = np.clip((xx * 37 + yy * 91) % (2 * mx + 2) - (mx // 2) + rng.integers(-3, 4, size=(h, w)), 0, mx)
+            pl.append(np.ascontiguousarray(v.astype(dt)))
+        pics.append(pl)
+    return pics
+
+
 @pytest.mark.parametrize("bd,sb", [(8, 1), (10, 2), (8, 2)])
 def test_cdef_fp16_taps_exact_on_extreme_content(H, orc, bd, sb):
     """cdef3_kernel runs the taps of 8/10-bit pictures in packed fp16 (svtf_cdef3.cuh).  Full-range white noise, 0/max
@@ -265,25 +288,7 @@ def test_cdef_fp16_taps_exact_on_extreme_content(H, orc, bd, sb):
     chroma strengths and dampings 3..9 (9 and, at 10 bits, 8 fall back to the packed-integer taps) must stay bit-exact."""
     S = H.S
     g = S.make_geom(512, 256, bd, sb)
-    rng = np.random.default_rng(0xF16 + bd)
-    mx = (1 << bd) - 1
-    dt = np.uint8 if sb == 1 else np.uint16
-    pics = []
-    for kind in range(3):
-        pl = []
-        for p in range(3):
-            s = 1 if p else 0
-            w, h = (g.mi_cols * 4) >> s, (g.mi_rows * 4) >> s
-            if kind == 0:
-                v = rng.integers(0, mx + 1, size=(h, w))
-            elif kind == 1:
-                yy, xx = np.mgrid[0:h, 0:w]
-                v = (((xx // 3 + yy // 2) & 1) * mx) ^ (rng.integers(0, 4, size=(h, w)) == 0) * rng.integers(0, mx + 1, size=(h, w))
-            else:
-                yy, xx = np.mgrid[0:h, 0:w]
-                v = np.clip((xx * 37 + yy * 91) % (2 * mx + 2) - (mx // 2) + rng.integers(-3, 4, size=(h, w)), 0, mx)
-            pl.append(np.ascontiguousarray(v.astype(dt)))
-        pics.append(pl)
+    pics = _extreme_pictures(g, 0xF16 + bd)
     soa = H.synth_mode_info(g, 0xF17, p_skip=0.2)
     mi = H.pack_mi(soa)
     nv, nh = H.nfb_of(g)
@@ -302,3 +307,27 @@ def test_cdef_fp16_taps_exact_on_extreme_content(H, orc, bd, sb):
                 got = ctx.download()
                 exp = orc.cdef_apply(g, rec, mi, cdef, idx)
                 assert H.planes_equal(got, exp), f"damping {damping} strengths {ys} {us}: " + H.first_diff(got, exp)
+
+
+@pytest.mark.parametrize("bd,sb,qidx", [(8, 1, 10), (10, 2, 120), (10, 2, 255), (8, 2, 200)])
+def test_cdef_search_fp16_exact_on_extreme_content(H, orc, bd, sb, qidx):
+    """cdef_search3_kernel (fp16 taps, rounding and clamp; integer moments) on white noise / checkerboard / ramp
+    reconstructions, all 64 strengths, search damping 3..6 (= 3 + base_q_idx / 64): the u64 mse table is bit-exact."""
+    S = H.S
+    g = S.make_geom(256, 128, bd, sb)
+    pics = _extreme_pictures(g, 0x5EA + bd + qidx)
+    mi = H.pack_mi(H.synth_mode_info(g, 0x5EB, p_skip=0.2))
+    first, second = H.cdef_level1_lists()
+    cfg = S.cdef_search_cfg(first, second, base_q_idx=qidx, lambda_=4000)
+    with S.FilterContext(g) as ctx:
+        for k in range(3):
+            rec, src = pics[k], pics[(k + 1) % 3]
+            ctx.begin(g)
+            ctx.upload(rec)
+            ctx.upload_source(src)
+            ctx.set_mi(mi)
+            mse, skip, dirs, var = ctx.cdef_seg_search(cfg)
+            e_mse, e_skip, e_dirs, e_var = orc.cdef_search(g, rec, src, mi, cfg)
+            assert np.array_equal(skip, e_skip) and np.array_equal(dirs, e_dirs) and np.array_equal(var, e_var)
+            bad = np.argwhere(mse != e_mse)
+            assert len(bad) == 0, f"picture {k}: {len(bad)} mse entries differ, first {bad[0]}: {mse[tuple(bad[0])]} vs {e_mse[tuple(bad[0])]}"
