@@ -280,6 +280,45 @@ def lr_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
+def handoff_leg(H, S, geom, wl, ctx, np, with_cpu):
+    """Recon hand-off: the filtered picture leaves the device as the padded reference picture
+    (pad_ref_and_set_flags: borders of 160 luma samples, 8-bit + 2-bit split) into pinned host memory."""
+    ox = oy = 160
+    W, Hh = geom.width, geom.height
+    ctx.begin(geom)
+    ctx.upload(wl["rec"])
+    shp = ctx.ref_padded_shapes(W, Hh, ox, oy)
+    pins = [[S.PinnedArray(sh, dt) for sh in shp] for dt in (np.uint16, np.uint8, np.uint8)]
+    out = tuple([p.array for p in grp] for grp in pins)
+    n = 8
+
+    def timed(split):
+        o = out if split else (out[0], None, None)
+        ctx.download_ref_padded(W, Hh, ox, oy, 0, 0, split, split, out=o)
+        t0 = time.perf_counter()
+        for _ in range(n):
+            ctx.download_ref_padded(W, Hh, ox, oy, 0, 0, split, split, out=o)
+        return (time.perf_counter() - t0) / n
+
+    plain, full = timed(False), timed(True)
+    samples = sum(a * b for a, b in shp)
+    res = {"metric": "recon hand-off ms per 4K 10-bit picture (padded reference picture to pinned host memory, synchronous)",
+           "padded_only_ms": round(plain * 1e3, 3), "padded_plus_8bit_2bit_split_ms": round(full * 1e3, 3),
+           "d2h_bytes": {"padded_only": samples * 2, "with_split": samples * 4},
+           "value": round(W * Hh / full / 1e6, 1), "unit": "Mpixel/s", "cpu_baseline": None}
+    if with_cpu and H.ref_available():
+        ref = H.Ref()
+        t0 = time.perf_counter()
+        H.handoff_cpu(ref.lib, "ref_", geom, wl["rec"], W, Hh, ox, oy, 0, 0, True, True)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": round(W * Hh / dt / 1e6, 1), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                               "sample": "one 4K 10-bit picture: copy into the padded buffer + generate_padding16_bit + un_pack2d, single thread"}
+    for grp in pins:
+        for p in grp:
+            p.close()
+    return res
+
+
 def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search.
     Several pictures are in flight, one context + stream + submitting host thread each — the reference's CDEF stage runs
@@ -646,6 +685,7 @@ def main():
     derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lrl = lr_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
+    hand = handoff_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -666,7 +706,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side, "loop_restoration": lrl,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side, "loop_restoration": lrl, "handoff": hand,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:

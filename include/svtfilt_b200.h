@@ -210,6 +210,28 @@ int svtf_set_mi_soa_dec(svtf_ctx *ctx, const uint8_t *bsize, const uint8_t *tx_s
                         const uint8_t *ref_frame0, const uint8_t *mode, const uint8_t *segment_id, int32_t stride);
 /* The packed words as the device holds them ([mi_rows][stride]); for tests and debugging. */
 int svtf_get_mi(svtf_ctx *ctx, svtf_mi_t *out, int32_t stride);
+/* ---- recon hand-off -----------------------------------------------------------------------------------
+ * svtf_download_ref_padded: the current end of the chain leaves the device as the PADDED reference picture that
+ * pad_ref_and_set_flags (Encoder/Codec/EbEncDecProcess.c:1589-1760) builds on the host: the last valid column/row is
+ * replicated into pad_right/pad_bottom (svt_aom_pad_input_picture_16bit, Common/Codec/EbMcp.c:296), then the borders
+ * org_x/org_y are replicated (svt_aom_generate_padding / _16_bit, Common/Codec/EbMcp.c:95/201); optionally the padded
+ * picture is also split into the 8-bit + 2-bit planes (svt_aom_un_pack2d, Common/Codec/EbPictureOperators.c:235) or, for
+ * 8-bit content held in 16-bit samples, narrowed (svt_convert_16bit_to_8bit_c, Common/C_DEFAULT/EbPackUnPack_C.c:277).
+ * dst[p] points at the FIRST sample of the padded allocation of plane p (EbPictureBufferDesc.buffer_y/cb/cr), strides in
+ * samples; the written rectangle is (width + 2*org_x) x (height + 2*org_y) (chroma: every term halved, rounding up).
+ * dst8 / dstn may be NULL (no split); they require 16-bit samples, dstn additionally bit_depth 10.  Synchronises. */
+typedef struct svtf_ref_layout {
+    int32_t width, height;         /* EbPictureBufferDesc.width / height of the destination (luma samples) */
+    int32_t org_x, org_y;          /* its border (luma samples) */
+    int32_t pad_right, pad_bottom; /* scs->pad_right / pad_bottom: trailing columns / rows of width / height that replicate the last valid one */
+} svtf_ref_layout;
+int svtf_download_ref_padded(svtf_ctx *ctx, const svtf_ref_layout *layout, void *const dst[3], const int32_t dst_stride[3],
+                             uint8_t *const dst8[3], const int32_t stride8[3], uint8_t *const dstn[3], const int32_t striden[3]);
+/* svt_convert_pic_8bit_to_16bit (Encoder/Codec/EbRestProcess.c:235; call site Encoder/Codec/EbDlfProcess.c:81-95): a context with
+ * 16-bit samples takes the picture as 8-bit planes (half the bytes over PCIe) and widens it on the device.  Otherwise as
+ * svtf_upload_frame. */
+int svtf_upload_frame_8as16(svtf_ctx *ctx, const uint8_t *y, int32_t stride_y, const uint8_t *cb, int32_t stride_cb, const uint8_t *cr,
+                            int32_t stride_cr);
 /* Device -> host copy of the current end of the filter chain; synchronises. */
 int svtf_download_frame(svtf_ctx *ctx, void *y, int32_t stride_y, void *cb, int32_t stride_cb, void *cr,
                         int32_t stride_cr);

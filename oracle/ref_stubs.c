@@ -82,7 +82,9 @@ uint64_t svt_spatial_full_distortion_kernel_c();
 void    *svt_full_distortion_kernel16_bits  = (void *)svt_full_distortion_kernel16_bits_c;  /* picture_sse_calculations */
 void    *svt_spatial_full_distortion_kernel = (void *)svt_spatial_full_distortion_kernel_c;
 /* RTCD pointers referenced by parts of EbPictureOperators.c that are never called here */
-void *svt_aom_un_pack2d_16_bit_src_mul4 = 0, *svt_compressed_packmsb = 0, *svt_enc_msb_pack2_d = 0, *svt_enc_msb_un_pack2_d = 0;
+void svt_enc_msb_un_pack2_d(); /* Common/C_DEFAULT/EbPackUnPack_C.c, compiled in for the hand-off pin */
+void *svt_aom_un_pack2d_16_bit_src_mul4 = (void *)svt_enc_msb_un_pack2_d; /* common_dsp_rtcd.c:883 (C only) */
+void *svt_compressed_packmsb = 0;
 void *svt_full_distortion_kernel32_bits = 0, *svt_full_distortion_kernel_cbf_zero32_bits = 0, *svt_pack2d_16_bit_src_mul4 = 0;
 /* RTCD pointers used by derive_ccso_filter (Encoder/Codec/EbPickccso.c): the _c kernels, as common_dsp_rtcd.c:636-658
  * sets them without SIMD.  (Declared without prototypes: this file includes no reference header.) */

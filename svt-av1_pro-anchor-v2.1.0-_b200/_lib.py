@@ -68,6 +68,12 @@ class LfSearchCfg(C.Structure):
     _fields_ = [("dlf_avg", C.c_int32), ("early_exit_convergence", C.c_int32), ("only_4x4", C.c_int32), ("search_chroma", C.c_int32)]
 
 
+class RefLayout(C.Structure):
+    """svtf_ref_layout"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("org_x", C.c_int32), ("org_y", C.c_int32), ("pad_right", C.c_int32),
+                ("pad_bottom", C.c_int32)]
+
+
 class DevPlane(C.Structure):
     _fields_ = [("ptr", C.c_void_p), ("pitch", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
 
@@ -78,7 +84,7 @@ EXPORTS = [
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
-    "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free",
+    "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
 ]
 
 _lib = None
@@ -109,6 +115,9 @@ def load():
     lib.svtf_stripe_begin.argtypes = [vp, C.POINTER(Geom), C.c_int32, C.c_int32]
     for f in (lib.svtf_upload_frame, lib.svtf_upload_source, lib.svtf_upload_pre_cdef, lib.svtf_overwrite_current, lib.svtf_download_frame, lib.svtf_download_frame_async):
         f.argtypes = [vp, vp, i32, vp, i32, vp, i32]
+    lib.svtf_upload_frame_8as16.argtypes = [vp, vp, i32, vp, i32, vp, i32]
+    lib.svtf_download_ref_padded.argtypes = [vp, C.POINTER(RefLayout), C.POINTER(vp), C.POINTER(i32), C.POINTER(vp), C.POINTER(i32), C.POINTER(vp),
+                                             C.POINTER(i32)]
     lib.svtf_set_mi.argtypes = [vp, vp, i32]
     lib.svtf_rewind.argtypes = [vp]
     lib.svtf_set_mi_soa_enc.argtypes = [vp] + [vp] * 6 + [i32]

@@ -23,6 +23,7 @@
 #include "svtf_search3.cuh"
 #include "svtf_mi_pack.cuh"
 #include "svtf_lr.cuh"
+#include "svtf_handoff.cuh"
 
 namespace svtf {
 
@@ -109,6 +110,8 @@ struct svtf_ctx {
     size_t       sb_lvl_cap = 0;
     void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
     uint64_t     launches = 0;
+    uint8_t     *d_handoff = nullptr;      // staging of svtf_download_ref_padded / svtf_upload_frame_8as16, allocated on first use
+    size_t       handoff_cap = 0;
     bool         search3_ready = false;    // same for cdef_search3_kernel
     bool         cdef3_ready = false;      // dynamic shared-memory opt-in of cdef3_kernel done on this device
     std::string  err;
@@ -229,7 +232,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
-    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units);
+    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff);
     if (c->h_mi_bad)
         cudaFreeHost(c->h_mi_bad);
     if (c->own_stream)
@@ -570,6 +573,135 @@ extern "C" int svtf_download_frame(svtf_ctx *c, void *y, int32_t sy, void *cb, i
         return r;
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return mi_soa_check(c);
+}
+
+// ---- recon hand-off (svtf_handoff.cuh) ---------------------------------------------------------------------------
+static int handoff_reserve(svtf_ctx *c, size_t bytes) {
+    if (bytes <= c->handoff_cap)
+        return SVTF_OK;
+    if (c->d_handoff) {
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        CUDA_TRY(c, cudaFree(c->d_handoff));
+        c->d_handoff = nullptr, c->handoff_cap = 0;
+    }
+    CUDA_TRY(c, cudaMalloc(&c->d_handoff, bytes));
+    c->handoff_cap = bytes;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_download_ref_padded(svtf_ctx *c, const svtf_ref_layout *lay, void *const dst[3], const int32_t dst_stride[3],
+                                        uint8_t *const dst8[3], const int32_t stride8[3], uint8_t *const dstn[3], const int32_t striden[3]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_download_ref_padded: NULL context");
+    if (!lay || !dst || !dst_stride)
+        return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: NULL argument");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_download_ref_padded: no picture uploaded");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_download_ref_padded: not available on a striped context");
+    const svtf_geom &g = c->geom;
+    const int vw = lay->width - lay->pad_right, vh = lay->height - lay->pad_bottom;
+    if (lay->org_x < 0 || lay->org_y < 0 || lay->pad_right < 0 || lay->pad_bottom < 0 || vw <= 0 || vh <= 0 || vw > g.mi_cols * 4 ||
+        vh > g.mi_rows * 4)
+        return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: layout does not fit the picture");
+    const bool want8 = dst8 != nullptr, wantn = dstn != nullptr;
+    if ((want8 || wantn) && g.sample_bytes != 2)
+        return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: the 8-bit / 2-bit split needs 16-bit samples");
+    if (wantn && g.bit_depth != 10)
+        return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: the 2-bit plane exists for 10-bit pictures only");
+    if ((want8 && !stride8) || (wantn && !striden))
+        return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: missing strides");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    HandoffArgs  a;
+    const size_t sb = g.sample_bytes;
+    size_t       off = 0, o16[3], o8[3], on[3];
+    int          items = 0;
+    for (int p = 0; p < 3; p++) {
+        const int     ss = p ? 1 : 0;
+        HandoffPlane &q  = a.p[p];
+        q.valid_w = (vw + ss) >> ss, q.valid_h = (vh + ss) >> ss;
+        q.org_x = (lay->org_x + ss) >> ss, q.org_y = (lay->org_y + ss) >> ss;
+        q.out_w = ((lay->width + ss) >> ss) + 2 * q.org_x, q.out_h = ((lay->height + ss) >> ss) + 2 * q.org_y;
+        q.dpitch = (q.out_w + 7) & ~7, q.chunks = q.dpitch / 8;
+        q.first_item = items;
+        items += q.chunks * q.out_h;
+        if (!dst[p] || dst_stride[p] < q.out_w || (want8 && (!dst8[p] || stride8[p] < q.out_w)) || (wantn && (!dstn[p] || striden[p] < q.out_w)))
+            return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: plane pointer NULL or stride smaller than the padded width");
+        const size_t n = (size_t)q.dpitch * q.out_h;
+        o16[p] = off, off += (n * sb + 255) & ~(size_t)255;
+        o8[p] = off, off += want8 ? (n + 255) & ~(size_t)255 : 0;
+        on[p] = off, off += wantn ? (n + 255) & ~(size_t)255 : 0;
+    }
+    if (int r = handoff_reserve(c, off))
+        return r;
+    const Planes cur = c->surf[c->cur].planes();
+    for (int p = 0; p < 3; p++) {
+        a.p[p].src = cur.p[p], a.p[p].src_pitch = cur.pitch[p];
+        a.p[p].dst  = c->d_handoff + o16[p];
+        a.p[p].dst8 = want8 ? c->d_handoff + o8[p] : nullptr;
+        a.p[p].dstn = wantn ? c->d_handoff + on[p] : nullptr;
+    }
+    a.total  = items;
+    a.shift8 = g.bit_depth == 10 ? 2 : 0;
+    const int blocks = std::min((items + 255) / 256, std::max(1, c->sm_count) * 8);
+    if (sb == 1)
+        handoff_kernel<uint8_t><<<blocks, 256, 0, c->stream>>>(a);
+    else
+        handoff_kernel<uint16_t><<<blocks, 256, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    for (int p = 0; p < 3; p++) {
+        const HandoffPlane &q = a.p[p];
+        CUDA_TRY(c, cudaMemcpy2DAsync(dst[p], (size_t)dst_stride[p] * sb, q.dst, (size_t)q.dpitch * sb, (size_t)q.out_w * sb, q.out_h,
+                                      cudaMemcpyDeviceToHost, c->stream));
+        if (want8)
+            CUDA_TRY(c, cudaMemcpy2DAsync(dst8[p], stride8[p], q.dst8, q.dpitch, q.out_w, q.out_h, cudaMemcpyDeviceToHost, c->stream));
+        if (wantn)
+            CUDA_TRY(c, cudaMemcpy2DAsync(dstn[p], striden[p], q.dstn, q.dpitch, q.out_w, q.out_h, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return mi_soa_check(c);
+}
+
+extern "C" int svtf_upload_frame_8as16(svtf_ctx *c, const uint8_t *y, int32_t sy, const uint8_t *cb, int32_t scb, const uint8_t *cr, int32_t scr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_upload_frame_8as16: NULL context");
+    if (!c->have_geom)
+        return c->fail(SVTF_E_STATE, "svtf_upload_frame_8as16: call svtf_frame_begin first");
+    if (c->geom.sample_bytes != 2 || c->geom.bit_depth != 8)
+        return c->fail(SVTF_E_ARG, "svtf_upload_frame_8as16: needs a context with 8-bit content in 16-bit samples");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_upload_frame_8as16: not available on a striped context");
+    const uint8_t *src[3] = {y, cb, cr};
+    const int32_t  st[3]  = {sy, scb, scr};
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    WidenArgs a;
+    size_t    off = 0, o[3];
+    int       items = 0;
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        a.w[p] = (c->geom.mi_cols * 4) >> ss, a.h[p] = (c->geom.mi_rows * 4) >> ss;
+        if (!src[p] || st[p] < a.w[p])
+            return c->fail(SVTF_E_ARG, "plane pointer NULL or stride smaller than the coded width");
+        a.spitch[p] = (a.w[p] + 7) & ~7, a.chunks[p] = a.spitch[p] / 8;
+        a.first_item[p] = items;
+        items += a.chunks[p] * a.h[p];
+        o[p] = off, off += ((size_t)a.spitch[p] * a.h[p] + 255) & ~(size_t)255;
+    }
+    if (int r = handoff_reserve(c, off))
+        return r;
+    Planes d = c->surf[0].planes();
+    for (int p = 0; p < 3; p++) {
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->d_handoff + o[p], a.spitch[p], src[p], st[p], a.w[p], a.h[p], cudaMemcpyHostToDevice, c->stream));
+        a.src[p] = c->d_handoff + o[p], a.dst[p] = static_cast<uint16_t *>(d.p[p]), a.dpitch[p] = d.pitch[p];
+    }
+    a.total = items;
+    widen_kernel<<<std::min((items + 255) / 256, std::max(1, c->sm_count) * 8), 256, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    c->cur = 0, c->pre_cdef = -1;
+    c->have_frame = true;
+    return SVTF_OK;
 }
 
 extern "C" int svtf_rewind(svtf_ctx *c) {

@@ -265,6 +265,41 @@ class FilterContext:
         self._chk(self._lib.svtf_download_frame(self._h, *self._planes_args(out)))
         return out
 
+    def upload_8as16(self, planes8):
+        """svt_convert_pic_8bit_to_16bit on the way in: uint8 planes into a context with 16-bit samples."""
+        assert all(p.dtype == np.uint8 and p.flags.c_contiguous for p in planes8)
+        args = []
+        for a in planes8:
+            args += [_ptr(a), a.strides[0]]
+        self._chk(self._lib.svtf_upload_frame_8as16(self._h, *args))
+
+    def ref_padded_shapes(self, width, height, org_x, org_y):
+        return [((((height + s) >> s) + 2 * ((org_y + s) >> s)), (((width + s) >> s) + 2 * ((org_x + s) >> s))) for s in (0, 1, 1)]
+
+    def download_ref_padded(self, width, height, org_x, org_y, pad_right=0, pad_bottom=0, split=False, two_bit=False, out=None):
+        """pad_ref_and_set_flags: the current picture as padded reference planes; with `split` also the 8-bit planes and, with
+        `two_bit`, the 2-bit planes of svt_aom_un_pack2d.  Returns (planes, planes8 or None, planesn or None).
+        out: optional (planes, planes8, planesn) of preallocated (e.g. pinned) arrays."""
+        g = self.geom
+        lay = L.RefLayout(width, height, org_x, org_y, pad_right, pad_bottom)
+        dt = np.uint8 if g.sample_bytes == 1 else np.uint16
+        shp = self.ref_padded_shapes(width, height, org_x, org_y)
+
+        def arr(lst):
+            return (C.c_void_p * 3)(*[a.ctypes.data for a in lst]), (C.c_int32 * 3)(*[a.strides[0] // a.itemsize for a in lst])
+
+        if out is not None:
+            out, o8, on = out
+        else:
+            out = [np.zeros(sh, dtype=dt) for sh in shp]
+            o8 = [np.zeros(sh, dtype=np.uint8) for sh in shp] if split else None
+            on = [np.zeros(sh, dtype=np.uint8) for sh in shp] if two_bit else None
+        p, st = arr(out)
+        p8, st8 = arr(o8) if split else (None, None)
+        pn, stn = arr(on) if two_bit else (None, None)
+        self._chk(self._lib.svtf_download_ref_padded(self._h, C.byref(lay), p, st, p8, st8, pn, stn))
+        return out, o8, on
+
     def rewind(self):
         self._chk(self._lib.svtf_rewind(self._h))
 

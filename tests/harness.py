@@ -619,3 +619,43 @@ def first_diff(a, b):
             r, c = d[0]
             return f"plane {p}: {len(d)} diffs, first at (y={r}, x={c}): {x[r, c]} vs {y[r, c]}"
     return "equal"
+
+
+# ---- recon hand-off (oracle/svtf_oracle_handoff.c, oracle/ref_shim_handoff.c) ----------------------------------
+def handoff_cpu(lib, prefix, geom, planes, width, height, org_x, org_y, pad_right=0, pad_bottom=0, split=False, two_bit=False):
+    """pad_ref_and_set_flags on the host with `lib` (the oracle: prefix 'svtf_orc_', the reference: 'ref_'): places the valid
+    part of every plane at (org_x, org_y) of a padded allocation, pads it, optionally splits it.  Same returns as
+    FilterContext.download_ref_padded."""
+    vp = C.c_void_p
+    out, o8, on = [], [] if split else None, [] if two_bit else None
+    for p, s in zip(planes, (0, 1, 1)):
+        w, h = (width + s) >> s, (height + s) >> s
+        ox, oy = (org_x + s) >> s, (org_y + s) >> s
+        pr, pb = pad_right >> s, pad_bottom >> s
+        vw, vh = ((width - pad_right) + s) >> s, ((height - pad_bottom) + s) >> s
+        pr, pb = w - vw, h - vh
+        buf = np.zeros((h + 2 * oy, w + 2 * ox), dtype=p.dtype)
+        buf[oy:oy + vh, ox:ox + vw] = p[:vh, :vw]
+        getattr(lib, prefix + "pad_plane")(vp(buf.ctypes.data), buf.shape[1], p.dtype.itemsize, w, h, ox, oy, pr, pb)
+        out.append(buf)
+        if split:
+            b8 = np.zeros(buf.shape, np.uint8)
+            bn = np.zeros(buf.shape, np.uint8) if two_bit else None
+            if geom.bit_depth == 10:
+                getattr(lib, prefix + "unpack2d")(vp(buf.ctypes.data), buf.shape[1], vp(b8.ctypes.data), b8.shape[1],
+                                                  vp(bn.ctypes.data) if two_bit else None, buf.shape[1], buf.shape[1], buf.shape[0])
+            else:
+                getattr(lib, prefix + "convert_16_to_8")(vp(buf.ctypes.data), buf.shape[1], vp(b8.ctypes.data), b8.shape[1], buf.shape[1], buf.shape[0])
+            o8.append(b8)
+            if two_bit:
+                on.append(bn)
+    return out, o8, on
+
+
+def widen_cpu(lib, prefix, planes8):
+    out = []
+    for p in planes8:
+        d = np.zeros(p.shape, np.uint16)
+        getattr(lib, prefix + "convert_8_to_16")(C.c_void_p(p.ctypes.data), p.shape[1], C.c_void_p(d.ctypes.data), d.shape[1], p.shape[1], p.shape[0])
+        out.append(d)
+    return out
