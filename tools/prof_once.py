@@ -40,3 +40,10 @@ with S.FilterContext(g) as c:
     c.set_mi_soa(H.synth_mode_info(g, 0xB200C2 + 1, p_split=0.5, p_skip=0.3, p_inter=0.7))
     c.sync()
 print("ok", p[0].cdef_bits)
+# recon hand-off: padded reference picture with the 8-bit / 2-bit split (svtf_download_ref_padded)
+with S.FilterContext(g) as c:
+    c.begin(g)
+    c.upload(rec)
+    for _ in range(2):
+        c.download_ref_padded(3840, 2160, 160, 160, 0, 0, True, True)
+print("handoff ok")
