@@ -54,6 +54,31 @@ def workload(H, geom, seed):
 # ------------------------------------------------------------------------------------------------
 # CPU legs
 # ------------------------------------------------------------------------------------------------
+def bind_to_gpu_cpus(torch, local):
+    """Run this rank's host threads (and first-touch its pinned buffers) on the CPUs local to its GPU
+    (/sys/bus/pci/devices/<bdf>/local_cpulist): with several ranks per box the end-to-end path is bound by host memory and
+    PCIe, and a rank on the wrong socket pays the inter-socket link twice per picture.  Best effort; returns a note."""
+    try:
+        p = torch.cuda.get_device_properties(local)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/local_cpulist") as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"{bdf}: {len(cpus)} local CPUs"
+    except Exception as e:  # noqa: BLE001 - purely advisory
+        return f"not bound ({type(e).__name__})"
+    return "not bound"
+
+
 def cpu_chain_runner(H):
     """Returns (kind, fn(geom, wl) -> None) running deblock->CDEF->CCSO on the CPU."""
     if H.ref_available():
@@ -499,6 +524,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_cpus(torch, local)
 
     geom = S.make_geom(W4K, H4K, BD)
     npx = W4K * H4K
@@ -701,7 +727,7 @@ def main():
             "dtype": "u16", "data": "synthetic",
             "config": {"workload": "decoder post-recon filter chain, 4K (3840x2160) 10-bit 4:2:0, deblock+CDEF+CCSO",
                        "pictures_per_gpu_per_step": B, "l2": f"inputs larger than L2: {B} pictures x 3 surfaces x {frame_bytes / 1e6:.1f} MB resident",
-                       "streams_per_gpu": NS,
+                       "streams_per_gpu": NS, "host_affinity": numa,
                        "sharding": f"{world} rank(s), pictures sharded by stream, no collective"},
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
