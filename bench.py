@@ -524,7 +524,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    numa = bind_to_gpu_cpus(torch, local)
+    # (a single rank keeps every host core: its cpu_baseline leg times the reference on all of them)
+    numa = bind_to_gpu_cpus(torch, local) if world > 1 else "all host CPUs (single rank)"
 
     geom = S.make_geom(W4K, H4K, BD)
     npx = W4K * H4K
