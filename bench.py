@@ -327,9 +327,29 @@ def handoff_leg(H, S, geom, wl, ctx, np, with_cpu):
 
     plain, full = timed(False), timed(True)
     samples = sum(a * b for a, b in shp)
+    # the kernel alone (padded planes + split stay on the device), CUDA events on the context's stream; the 12 resident
+    # pictures of the main leg were written since, so the source surface is not in L2
+    import torch
+
+    st = torch.cuda.Stream()
+    ctx.set_stream(st.cuda_stream)
+    evs = []
+    for _ in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        ctx.ref_padded_resident(W, Hh, ox, oy, True, True)
+        e1.record(st)
+        evs.append((e0, e1))
+    st.synchronize()
+    ctx.set_stream(None)
+    k_ms = statistics.median(a.elapsed_time(b) for a, b in evs[1:])
+    src_samples = sum(((geom.mi_cols * 4) >> s) * ((geom.mi_rows * 4) >> s) for s in (0, 1, 1))
+    alg = src_samples * 2 + samples * 4  # read every source sample once; write 16-bit + 8-bit + 2-bit planes of the padded picture
     res = {"metric": "recon hand-off ms per 4K 10-bit picture (padded reference picture to pinned host memory, synchronous)",
            "padded_only_ms": round(plain * 1e3, 3), "padded_plus_8bit_2bit_split_ms": round(full * 1e3, 3),
            "d2h_bytes": {"padded_only": samples * 2, "with_split": samples * 4},
+           "kernel": {"name": "handoff_kernel", "ms": round(k_ms, 4), "alg_bytes": alg, "alg_GBps": round(alg / (k_ms * 1e-3) / 1e9, 1),
+                      "note": "bandwidth-bound stage: read b, write b+1+1 bytes per padded sample; back-to-back launches on one 4K picture (source 25 MB may sit in L2)"},
            "value": round(W * Hh / full / 1e6, 1), "unit": "Mpixel/s", "cpu_baseline": None}
     if with_cpu and H.ref_available():
         ref = H.Ref()

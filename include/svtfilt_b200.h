@@ -219,7 +219,9 @@ int svtf_get_mi(svtf_ctx *ctx, svtf_mi_t *out, int32_t stride);
  * 8-bit content held in 16-bit samples, narrowed (svt_convert_16bit_to_8bit_c, Common/C_DEFAULT/EbPackUnPack_C.c:277).
  * dst[p] points at the FIRST sample of the padded allocation of plane p (EbPictureBufferDesc.buffer_y/cb/cr), strides in
  * samples; the written rectangle is (width + 2*org_x) x (height + 2*org_y) (chroma: every term halved, rounding up).
- * dst8 / dstn may be NULL (no split); they require 16-bit samples, dstn additionally bit_depth 10.  Synchronises. */
+ * dst8 / dstn may be NULL (no split); they require 16-bit samples, dstn additionally bit_depth 10.  Synchronises.
+ * dst == NULL: the kernel only — the padded planes stay in the context's device staging block (non-NULL dst8 / dstn then
+ * only say which planes to produce), stream-ordered, not synchronised; used to time the kernel apart from the DMA. */
 typedef struct svtf_ref_layout {
     int32_t width, height;         /* EbPictureBufferDesc.width / height of the destination (luma samples) */
     int32_t org_x, org_y;          /* its border (luma samples) */

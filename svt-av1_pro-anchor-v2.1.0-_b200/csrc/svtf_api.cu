@@ -593,7 +593,8 @@ extern "C" int svtf_download_ref_padded(svtf_ctx *c, const svtf_ref_layout *lay,
                                         uint8_t *const dst8[3], const int32_t stride8[3], uint8_t *const dstn[3], const int32_t striden[3]) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_download_ref_padded: NULL context");
-    if (!lay || !dst || !dst_stride)
+    const bool resident = dst == nullptr; // kernel only: the padded planes stay in the context's staging block
+    if (!lay || (!resident && !dst_stride))
         return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: NULL argument");
     if (!c->have_frame)
         return c->fail(SVTF_E_STATE, "svtf_download_ref_padded: no picture uploaded");
@@ -609,7 +610,7 @@ extern "C" int svtf_download_ref_padded(svtf_ctx *c, const svtf_ref_layout *lay,
         return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: the 8-bit / 2-bit split needs 16-bit samples");
     if (wantn && g.bit_depth != 10)
         return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: the 2-bit plane exists for 10-bit pictures only");
-    if ((want8 && !stride8) || (wantn && !striden))
+    if (!resident && ((want8 && !stride8) || (wantn && !striden)))
         return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: missing strides");
     CUDA_TRY(c, cudaSetDevice(c->device));
     HandoffArgs  a;
@@ -625,7 +626,8 @@ extern "C" int svtf_download_ref_padded(svtf_ctx *c, const svtf_ref_layout *lay,
         q.dpitch = (q.out_w + 7) & ~7, q.chunks = q.dpitch / 8;
         q.first_item = items;
         items += q.chunks * q.out_h;
-        if (!dst[p] || dst_stride[p] < q.out_w || (want8 && (!dst8[p] || stride8[p] < q.out_w)) || (wantn && (!dstn[p] || striden[p] < q.out_w)))
+        if (!resident &&
+            (!dst[p] || dst_stride[p] < q.out_w || (want8 && (!dst8[p] || stride8[p] < q.out_w)) || (wantn && (!dstn[p] || striden[p] < q.out_w))))
             return c->fail(SVTF_E_ARG, "svtf_download_ref_padded: plane pointer NULL or stride smaller than the padded width");
         const size_t n = (size_t)q.dpitch * q.out_h;
         o16[p] = off, off += (n * sb + 255) & ~(size_t)255;
@@ -650,6 +652,8 @@ extern "C" int svtf_download_ref_padded(svtf_ctx *c, const svtf_ref_layout *lay,
         handoff_kernel<uint16_t><<<blocks, 256, 0, c->stream>>>(a);
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
+    if (resident)
+        return SVTF_OK;
     for (int p = 0; p < 3; p++) {
         const HandoffPlane &q = a.p[p];
         CUDA_TRY(c, cudaMemcpy2DAsync(dst[p], (size_t)dst_stride[p] * sb, q.dst, (size_t)q.dpitch * sb, (size_t)q.out_w * sb, q.out_h,

@@ -300,6 +300,12 @@ class FilterContext:
         self._chk(self._lib.svtf_download_ref_padded(self._h, C.byref(lay), p, st, p8, st8, pn, stn))
         return out, o8, on
 
+    def ref_padded_resident(self, width, height, org_x, org_y, split=True, two_bit=True):
+        """The hand-off kernel alone (dst == NULL): padded planes into the device staging block, stream-ordered, no DMA."""
+        lay = L.RefLayout(width, height, org_x, org_y, 0, 0)
+        one = (C.c_void_p * 3)(1, 1, 1)  # non-NULL markers: which planes to produce
+        self._chk(self._lib.svtf_download_ref_padded(self._h, C.byref(lay), None, None, one if split else None, None, one if two_bit else None, None))
+
     def rewind(self):
         self._chk(self._lib.svtf_rewind(self._h))
 
