@@ -18,7 +18,8 @@ namespace svtf {
 
 constexpr int LR_THREADS = 256;
 constexpr int LR_MAXW    = 64;               // processing-unit width (RESTORATION_PROC_UNIT_SIZE), 32 for 4:2:0 chroma
-constexpr int LR_IN_P    = LR_MAXW + 6 + 2;  // shared input pitch
+constexpr int LR_C0      = 8;                // shared-input column of plane column x0 (column 0 <-> x0 - 8: 8-sample vectors line up)
+constexpr int LR_IN_P    = LR_MAXW + 16 + 2; // shared input pitch in samples: 41 words, odd -> row and column walks are conflict-free
 constexpr int LR_IN_ROWS = 64 + 6;
 
 struct LrUnitDev { // svtf_lr_unit, device copy
@@ -55,31 +56,47 @@ __device__ __forceinline__ int lr_x_by_xplus1(unsigned z) {
     return (int)((256u * z + (z + 1) / 2) / (z + 1));
 }
 
-// A and B of the self-guided filter from the box sums around (r, c) of the staged input
+// A and B of the self-guided filter (selfguided_restoration_[fast_]internal, EbRestoration.c:669/803) for LR_SEG consecutive
+// positions of one row: the (2R+1)-row column sums of the LR_SEG + 2R columns are formed once in registers and the box
+// sums slide over them — (2R+1)(LR_SEG+2R)/LR_SEG shared loads per position instead of (2R+1)^2.  All sums are exact
+// 32-bit integers, so the order of the additions is free.  `in` points at the centre sample of the first position.
+constexpr int LR_SEG = 6;
 template <int R>
-__device__ __forceinline__ void lr_sgr_ab(const uint16_t *in, const uint16_t *xb, const int r, const int c, const int bd, const unsigned s,
-                                          uint16_t &A, uint32_t &B) {
-    uint32_t sum = 0, sq = 0;
+__device__ __forceinline__ void lr_sgr_ab_seg(const uint16_t *in, const uint16_t *xb, const int bd, const unsigned s, const int npos, uint16_t *A,
+                                              uint32_t *B) {
+    constexpr int NC = LR_SEG + 2 * R;
+    uint32_t      cs[NC], cq[NC];
 #pragma unroll
-    for (int dy = -R; dy <= R; dy++)
+    for (int j = 0; j < NC; j++) {
+        uint32_t a = 0, q = 0;
 #pragma unroll
-        for (int dx = -R; dx <= R; dx++) {
-            const uint32_t v = in[(r + dy) * LR_IN_P + c + dx];
-            sum += v, sq += v * v;
+        for (int dy = -R; dy <= R; dy++) {
+            const uint32_t v = in[dy * LR_IN_P + j - R];
+            a += v, q += v * v;
         }
+        cs[j] = a, cq[j] = q;
+    }
     constexpr uint32_t n = (2 * R + 1) * (2 * R + 1), one_by = R == 2 ? 164 : 455; // svt_aom_eb_one_by_x[n - 1]
-    const uint32_t     a = (uint32_t)lr_rnd((int)sq, 2 * (bd - 8)), b = (uint32_t)lr_rnd((int)sum, bd - 8);
-    const uint32_t     p = (a * n < b * b) ? 0 : a * n - b * b;
-    const uint32_t     z = (p * s + (1u << 19)) >> 20;
-    const int          Av = xb[min(z, 255u)];
-    A                     = (uint16_t)Av;
-    B                     = ((uint32_t)(256 - Av) * sum * one_by + (1u << 11)) >> 12;
+#pragma unroll
+    for (int j = 0; j < LR_SEG; j++) {
+        if (j >= npos)
+            break;
+        uint32_t sum = 0, sq = 0;
+#pragma unroll
+        for (int d = 0; d <= 2 * R; d++) sum += cs[j + d], sq += cq[j + d];
+        const uint32_t a = (uint32_t)lr_rnd((int)sq, 2 * (bd - 8)), b = (uint32_t)lr_rnd((int)sum, bd - 8);
+        const uint32_t p = (a * n < b * b) ? 0 : a * n - b * b;
+        const uint32_t z = (p * s + (1u << 19)) >> 20;
+        const int      Av = xb[min(z, 255u)];
+        A[j]              = (uint16_t)Av;
+        B[j]              = ((uint32_t)(256 - Av) * sum * one_by + (1u << 11)) >> 12;
+    }
 }
 
 template <typename T>
 __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ LrArgs a) {
-    __shared__ uint16_t s_in[LR_IN_ROWS * LR_IN_P];
-    __shared__ __align__(16) unsigned char s_buf[66 * 66 * 6]; // Wiener: horizontal pass (u16 [70][64]); SGR: A (u16) and B (u32)
+    __shared__ __align__(16) uint16_t s_in[LR_IN_ROWS * LR_IN_P];
+    __shared__ __align__(16) unsigned char s_buf[66 * 66 * 6]; // Wiener: horizontal pass (u16 [70][TW]); SGR: A (u16) and B (u32)
     __shared__ LrUnitDev s_unit;
     __shared__ uint16_t  s_xb[256];
     const int tid = threadIdx.x;
@@ -89,7 +106,8 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     else if ((int)blockIdx.x >= a.base[1])
         plane = 1;
     const int lin = blockIdx.x - a.base[plane], k = lin / a.chunks[plane], ch = lin - k * a.chunks[plane];
-    const int ss = plane ? 1 : 0, TW = LR_MAXW >> ss, tws = 6 - ss, SH = 64 >> ss, off = 8 >> ss;
+    const int ss = plane ? 1 : 0, TW = LR_MAXW >> ss, SH = 64 >> ss, off = 8 >> ss;
+    const int sgs = 3 - ss;    // log2(8-column segments per row)
     const int pw = a.pw[plane], ph = a.ph[plane], cw = a.cw[plane], chh = a.chh[plane];
     // the last "stripe" of the grid is the tail: coded rows below the visible picture, copied
     const bool beyond = k == a.stripes[plane] - 1;
@@ -110,68 +128,105 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
         type = s_unit.type;
     }
     if (type == SVTF_RESTORE_NONE) { // copy (also: planes without restoration, coded samples outside the visible picture)
-        for (int r = tid >> 5; r < h; r += LR_THREADS / 32)
-            for (int c = tid & 31; c < w; c += 32) out[(size_t)(y0 + r) * op + x0 + c] = cur[(size_t)(y0 + r) * cp + x0 + c];
+        // coded widths are multiples of 4 (chroma) / 8 (luma) and x0 of 32: 4-sample vectors
+        for (int i = tid; i < h * (TW / 4); i += LR_THREADS) {
+            const int r = i / (TW / 4), c = (i - r * (TW / 4)) * 4;
+            if (c < w)
+                st4<T>(out + (size_t)(y0 + r) * op + x0 + c, ld4<T>(cur + (size_t)(y0 + r) * cp + x0 + c));
+        }
         return;
     }
-    // ---- stage the stripe input: rows y0-3 .. y1+2, columns x0-3 .. x0+w+2 (setup_processing_stripe_boundary :288) ----
+    // ---- stage the stripe input: rows y0-3 .. y1+2, columns x0-8 .. x0+TW+7 (setup_processing_stripe_boundary :288) ----
     const bool above = k > 0, below = y1 < ph;
     const int  wv = min(w, pw - x0); // visible columns of this chunk
-    const int lane = tid & 31, wrp = tid >> 5;
-    if (tid < 256) // svt_aom_eb_x_by_xplus1 as a table: one entry per thread
-        s_xb[tid] = (uint16_t)lr_x_by_xplus1((unsigned)tid);
-    for (int rr = wrp; rr < h + 6; rr += LR_THREADS / 32) { // one source row per warp pass: the row decision is made once
-        const int r = y0 - 3 + rr;
-        const T  *src;
-        if (r < y0) {
-            if (!above)
-                src = cur + (size_t)max(r, 0) * cp;
-            else if (a.opt)
-                src = cur + (size_t)(r == y0 - 3 ? y0 - 2 : r) * cp;
-            else
-                src = dbk + (size_t)max(r, y0 - 2) * dp;
-        } else if (r >= y1) {
-            if (!below)
-                src = cur + (size_t)min(r, ph - 1) * cp;
-            else if (a.opt)
-                src = cur + (size_t)min(r == y1 + 2 ? y1 + 1 : r, ph - 1) * cp;
-            else
-                src = dbk + (size_t)min(min(r, y1 + 1), ph - 1) * dp;
-        } else
-            src = cur + (size_t)r * cp;
-        for (int cc = lane; cc < TW + 6; cc += 32) s_in[rr * LR_IN_P + cc] = (uint16_t)src[min(max(x0 - 3 + cc, 0), pw - 1)];
+    s_xb[tid] = (uint16_t)lr_x_by_xplus1((unsigned)tid); // svt_aom_eb_x_by_xplus1 as a table: one entry per thread
+    {
+        const int nch = TW / 8 + 2;
+        for (int i = tid; i < (h + 6) * nch; i += LR_THREADS) {
+            const int rr = ss ? i / 6 : i / 10, j = i - rr * nch;
+            const int r  = y0 - 3 + rr;
+            const T  *src;
+            if (r < y0) {
+                if (!above)
+                    src = cur + (size_t)max(r, 0) * cp;
+                else if (a.opt)
+                    src = cur + (size_t)(r == y0 - 3 ? y0 - 2 : r) * cp;
+                else
+                    src = dbk + (size_t)max(r, y0 - 2) * dp;
+            } else if (r >= y1) {
+                if (!below)
+                    src = cur + (size_t)min(r, ph - 1) * cp;
+                else if (a.opt)
+                    src = cur + (size_t)min(r == y1 + 2 ? y1 + 1 : r, ph - 1) * cp;
+                else
+                    src = dbk + (size_t)min(min(r, y1 + 1), ph - 1) * dp;
+            } else
+                src = cur + (size_t)r * cp;
+            const int gx = x0 - 8 + 8 * j;
+            uint4     v;
+            if (gx >= 0 && gx + 8 <= pw)
+                v = ld8<T>(src + gx);
+            else { // columns outside the plane repeat the edge column
+                uint32_t e[8];
+#pragma unroll
+                for (int t = 0; t < 8; t++) e[t] = src[min(max(gx + t, 0), pw - 1)];
+                v = make_uint4(e[0] | (e[1] << 16), e[2] | (e[3] << 16), e[4] | (e[5] << 16), e[6] | (e[7] << 16));
+            }
+            uint32_t *d = reinterpret_cast<uint32_t *>(s_in + rr * LR_IN_P + 8 * j);
+            d[0] = v.x, d[1] = v.y, d[2] = v.z, d[3] = v.w;
+        }
     }
     __syncthreads();
     const int bd = a.bd, maxv = (1 << bd) - 1;
     if (type == SVTF_RESTORE_WIENER) {
-        // svt_av1_[highbd_]wiener_convolve_add_src_c: horizontal pass into 16 bits, then vertical
+        // svt_av1_[highbd_]wiener_convolve_add_src_c: horizontal pass into 16 bits, then vertical.  A thread produces 8
+        // consecutive outputs of a row (horizontal) / of a column (vertical) from 14 inputs held in registers.
         uint16_t *tmp = reinterpret_cast<uint16_t *>(s_buf); // [h + 6][TW]
         const int r0 = bd == 12 ? 5 : 3, r1 = 14 - r0, lim = (1 << (bd + 1 + 7 - r0)) - 1;
         int       hf[7], vf[7];
 #pragma unroll
         for (int t = 0; t < 7; t++) hf[t] = s_unit.hf[t], vf[t] = s_unit.vf[t];
-        for (int i = tid; i < (h + 6) * TW; i += LR_THREADS) {
-            const int       rr = i >> tws, c = i & (TW - 1);
-            const uint16_t *p = &s_in[rr * LR_IN_P + c];
-            int             sum = ((int)p[3] << 7) + (1 << (bd + 6));
+        for (int i = tid; i < ((h + 6) << sgs); i += LR_THREADS) {
+            const int       rr = i >> sgs, c = (i & ((1 << sgs) - 1)) * 8;
+            const uint16_t *p = &s_in[rr * LR_IN_P + LR_C0 + c - 3];
+            int             x[14];
 #pragma unroll
-            for (int t = 0; t < 7; t++) sum += (int)p[t] * hf[t];
-            tmp[rr * TW + c] = (uint16_t)min(max(lr_rnd(sum, r0), 0), lim);
+            for (int t = 0; t < 14; t++) x[t] = p[t];
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                int sum = (x[j + 3] << 7) + (1 << (bd + 6));
+#pragma unroll
+                for (int t = 0; t < 7; t++) sum += x[j + t] * hf[t];
+                const uint32_t v = (uint32_t)min(max(lr_rnd(sum, r0), 0), lim);
+                o[j >> 1]        = (j & 1) ? (o[j >> 1] | (v << 16)) : v;
+            }
+            uint32_t *d = reinterpret_cast<uint32_t *>(tmp + rr * TW + c);
+            d[0] = o[0], d[1] = o[1], d[2] = o[2], d[3] = o[3];
         }
         __syncthreads();
-        for (int i = tid; i < h * TW; i += LR_THREADS) {
-            const int r = i >> tws, c = i & (TW - 1);
+        const int nseg = (h + 7) >> 3;
+        for (int i = tid; i < nseg * TW; i += LR_THREADS) {
+            const int sg = i / TW, c = i - sg * TW, rb = sg * 8;
             if (c >= w)
                 continue;
-            int v;
+            T *o = out + (size_t)(y0 + rb) * op + x0 + c;
             if (c < wv) {
-                int sum = ((int)tmp[(r + 3) * TW + c] << 7) - (1 << (bd + r1 - 1));
+                int x[14];
 #pragma unroll
-                for (int t = 0; t < 7; t++) sum += (int)tmp[(r + t) * TW + c] * vf[t];
-                v = min(max(lr_rnd(sum, r1), 0), maxv);
-            } else
-                v = cur[(size_t)(y0 + r) * cp + x0 + c];
-            out[(size_t)(y0 + r) * op + x0 + c] = (T)v;
+                for (int t = 0; t < 14; t++) x[t] = rb + t < h + 6 ? tmp[(rb + t) * TW + c] : 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (rb + j >= h)
+                        break;
+                    int sum = (x[j + 3] << 7) - (1 << (bd + r1 - 1));
+#pragma unroll
+                    for (int t = 0; t < 7; t++) sum += x[j + t] * vf[t];
+                    o[(size_t)j * op] = (T)min(max(lr_rnd(sum, r1), 0), maxv);
+                }
+            } else {
+                for (int j = 0; j < 8 && rb + j < h; j++) o[(size_t)j * op] = cur[(size_t)(y0 + rb + j) * cp + x0 + c];
+            }
         }
         return;
     }
@@ -184,74 +239,108 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
         xq0 = s_unit.xqd[0], xq1 = 0;
     else
         xq0 = s_unit.xqd[0], xq1 = 128 - xq0 - s_unit.xqd[1];
-    constexpr int PER = 64 * 64 / LR_THREADS;
-    int           acc[PER];
+    // a thread owns two work items of 8 consecutive samples of a row (item i = tid + n*256: row i >> sgs, segment i & ..)
+    int acc[2][8];
 #pragma unroll
-    for (int n = 0; n < PER; n++) acc[n] = 0;
+    for (int n = 0; n < 2; n++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[n][j] = 0;
     constexpr int AP = LR_MAXW + 2; // pitch of A / B: columns -1 .. TW
     uint16_t     *sA = reinterpret_cast<uint16_t *>(s_buf);
     uint32_t     *sB = reinterpret_cast<uint32_t *>(s_buf + 66 * 66 * 2);
+    const int     nsg = (TW + 2 + LR_SEG - 1) / LR_SEG; // segments of LR_SEG positions per A/B row
     if (rad0 > 0) { // selfguided_restoration_fast_internal :669 — A/B on the rows -1, 1, 3, .. of the stripe
         const unsigned sv   = (unsigned)c_sgr_s[ep][0];
         const int      rows = (h + 1) / 2 + 1; // i = -1, 1, .., <= h
-        for (int ri = wrp; ri < rows; ri += LR_THREADS / 32)
-            for (int c = lane; c < TW + 2; c += 32)
-                lr_sgr_ab<2>(s_in, s_xb, 3 + (2 * ri - 1), 3 + (c - 1), bd, sv, sA[ri * AP + c], sB[ri * AP + c]);
+        for (int i = tid; i < rows * nsg; i += LR_THREADS) {
+            const int ri = i / nsg, c = (i - ri * nsg) * LR_SEG; // positions c .. c+5 <-> stripe columns c-1 ..
+            lr_sgr_ab_seg<2>(s_in + (3 + 2 * ri - 1) * LR_IN_P + LR_C0 + c - 1, s_xb, bd, sv, TW + 2 - c, sA + ri * AP + c, sB + ri * AP + c);
+        }
         __syncthreads();
 #pragma unroll
-        for (int n = 0; n < PER; n++) {
-            const int i = tid + n * LR_THREADS, r = i >> tws, c = i & (TW - 1);
-            if (i >= h * TW)
+        for (int n = 0; n < 2; n++) {
+            const int i = tid + n * LR_THREADS, r = i >> sgs, c = (i & ((1 << sgs) - 1)) * 8;
+            if (r >= h)
                 continue;
-            const int dg = s_in[(r + 3) * LR_IN_P + c + 3], cc = c + 1;
-            int       av, bv, sh;
+            const uint16_t *dgp = s_in + (r + 3) * LR_IN_P + LR_C0 + c;
             if (!(r & 1)) { // even row: rows r-1 and r+1 -> A rows r/2 and r/2+1
-                const int q0 = (r >> 1) * AP, q1 = q0 + AP;
-                av = (sA[q0 + cc] + sA[q1 + cc]) * 6 + (sA[q0 + cc - 1] + sA[q1 + cc - 1] + sA[q0 + cc + 1] + sA[q1 + cc + 1]) * 5;
-                bv = (int)((sB[q0 + cc] + sB[q1 + cc]) * 6 + (sB[q0 + cc - 1] + sB[q1 + cc - 1] + sB[q0 + cc + 1] + sB[q1 + cc + 1]) * 5);
-                sh = 9;
+                const int q0 = (r >> 1) * AP + c, q1 = q0 + AP;
+                int       as[10], bs[10]; // column sums of the two rows at positions c .. c+9
+#pragma unroll
+                for (int t = 0; t < 10; t++) as[t] = sA[q0 + t] + sA[q1 + t], bs[t] = (int)(sB[q0 + t] + sB[q1 + t]);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int dg = dgp[j];
+                    const int av = as[j + 1] * 6 + (as[j] + as[j + 2]) * 5, bv = bs[j + 1] * 6 + (bs[j] + bs[j + 2]) * 5;
+                    acc[n][j] += xq0 * (lr_rnd(av * dg + bv, 9) - (dg << 4));
+                }
             } else { // odd row r -> A row (r+1)/2
-                const int q = ((r + 1) >> 1) * AP;
-                av = sA[q + cc] * 6 + (sA[q + cc - 1] + sA[q + cc + 1]) * 5;
-                bv = (int)(sB[q + cc] * 6 + (sB[q + cc - 1] + sB[q + cc + 1]) * 5);
-                sh = 8;
+                const int q = ((r + 1) >> 1) * AP + c;
+                int       as[10], bs[10];
+#pragma unroll
+                for (int t = 0; t < 10; t++) as[t] = sA[q + t], bs[t] = (int)sB[q + t];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int dg = dgp[j];
+                    const int av = as[j + 1] * 6 + (as[j] + as[j + 2]) * 5, bv = bs[j + 1] * 6 + (bs[j] + bs[j + 2]) * 5;
+                    acc[n][j] += xq0 * (lr_rnd(av * dg + bv, 8) - (dg << 4));
+                }
             }
-            acc[n] += xq0 * (lr_rnd(av * dg + bv, sh) - (dg << 4));
         }
         __syncthreads();
     }
     if (rad1 > 0) { // selfguided_restoration_internal :803 — A/B on rows -1 .. h
         const unsigned sv = (unsigned)c_sgr_s[ep][1];
-        for (int ri = wrp; ri < h + 2; ri += LR_THREADS / 32)
-            for (int c = lane; c < TW + 2; c += 32)
-                lr_sgr_ab<1>(s_in, s_xb, 3 + (ri - 1), 3 + (c - 1), bd, sv, sA[ri * AP + c], sB[ri * AP + c]);
+        for (int i = tid; i < (h + 2) * nsg; i += LR_THREADS) {
+            const int ri = i / nsg, c = (i - ri * nsg) * LR_SEG;
+            lr_sgr_ab_seg<1>(s_in + (3 + ri - 1) * LR_IN_P + LR_C0 + c - 1, s_xb, bd, sv, TW + 2 - c, sA + ri * AP + c, sB + ri * AP + c);
+        }
         __syncthreads();
 #pragma unroll
-        for (int n = 0; n < PER; n++) {
-            const int i = tid + n * LR_THREADS, r = i >> tws, c = i & (TW - 1);
-            if (i >= h * TW)
+        for (int n = 0; n < 2; n++) {
+            const int i = tid + n * LR_THREADS, r = i >> sgs, c = (i & ((1 << sgs) - 1)) * 8;
+            if (r >= h)
                 continue;
-            const int dg = s_in[(r + 3) * LR_IN_P + c + 3], q = (r + 1) * AP + c + 1;
-            const int av = (sA[q] + sA[q - 1] + sA[q + 1] + sA[q - AP] + sA[q + AP]) * 4 +
-                           (sA[q - 1 - AP] + sA[q - 1 + AP] + sA[q + 1 - AP] + sA[q + 1 + AP]) * 3;
-            const int bv = (int)((sB[q] + sB[q - 1] + sB[q + 1] + sB[q - AP] + sB[q + AP]) * 4 +
-                                 (sB[q - 1 - AP] + sB[q - 1 + AP] + sB[q + 1 - AP] + sB[q + 1 + AP]) * 3);
-            acc[n] += xq1 * (lr_rnd(av * dg + bv, 9) - (dg << 4));
+            const uint16_t *dgp = s_in + (r + 3) * LR_IN_P + LR_C0 + c;
+            const int       q   = (r + 1) * AP + c; // position c <-> stripe column c-1
+            int             a4[10], a3[10], b4[10], b3[10]; // per column: centre row (weight 4 / 3 pattern) and the rows above + below
+#pragma unroll
+            for (int t = 0; t < 10; t++) {
+                const int am = sA[q + t], ao = sA[q - AP + t] + sA[q + AP + t];
+                const int bm = (int)sB[q + t], bo = (int)(sB[q - AP + t] + sB[q + AP + t]);
+                a4[t] = am, a3[t] = ao, b4[t] = bm, b3[t] = bo;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int dg = dgp[j];
+                // (centre + left + right + up + down) * 4 + (four diagonals) * 3
+                const int av = (a4[j + 1] + a4[j] + a4[j + 2] + a3[j + 1]) * 4 + (a3[j] + a3[j + 2]) * 3;
+                const int bv = (b4[j + 1] + b4[j] + b4[j + 2] + b3[j + 1]) * 4 + (b3[j] + b3[j + 2]) * 3;
+                acc[n][j] += xq1 * (lr_rnd(av * dg + bv, 9) - (dg << 4));
+            }
         }
     }
 #pragma unroll
-    for (int n = 0; n < PER; n++) {
-        const int i = tid + n * LR_THREADS, r = i >> tws, c = i & (TW - 1);
-        if (i >= h * TW || c >= w)
+    for (int n = 0; n < 2; n++) {
+        const int i = tid + n * LR_THREADS, r = i >> sgs, c = (i & ((1 << sgs) - 1)) * 8;
+        if (r >= h || c >= w)
             continue;
-        int v;
-        if (c < wv) {
-            const int dg = s_in[(r + 3) * LR_IN_P + c + 3];
-            const int wv16 = (int)(short)lr_rnd((dg << 11) + acc[n], 11);
-            v              = min(max(wv16, 0), maxv);
-        } else
-            v = cur[(size_t)(y0 + r) * cp + x0 + c];
-        out[(size_t)(y0 + r) * op + x0 + c] = (T)v;
+        const uint16_t *dgp = s_in + (r + 3) * LR_IN_P + LR_C0 + c;
+        uint32_t        o[4];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int      dg   = dgp[j];
+            const int      wv16 = (int)(short)lr_rnd((dg << 11) + acc[n][j], 11);
+            const uint32_t v    = (uint32_t)min(max(wv16, 0), maxv);
+            o[j >> 1]           = (j & 1) ? (o[j >> 1] | (v << 16)) : v;
+        }
+        T *op8 = out + (size_t)(y0 + r) * op + x0 + c;
+        if (c + 8 <= wv)
+            st8<T>(op8, make_uint4(o[0], o[1], o[2], o[3]));
+        else {
+            for (int j = 0; j < 8 && c + j < w; j++)
+                op8[j] = c + j < wv ? (T)((o[j >> 1] >> (16 * (j & 1))) & 0xffff) : cur[(size_t)(y0 + r) * cp + x0 + c + j];
+        }
     }
 }
 
