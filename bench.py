@@ -364,6 +364,60 @@ def handoff_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
+def streams_1080p_leg(H, S, torch, dist, dev, local, rank, world, steps):
+    """BASELINE configs[4] (and [0]'s picture format): independent 1080p 8-bit streams sharded over the GPUs by stream — 64 streams on
+    8 GPUs = 8 per GPU, so every rank runs 8 contexts, one picture of each stream per step, each on its own CUDA stream; no collective.
+    Device-resident (the pictures are rewound, not re-uploaded); 8 pictures x 3 surfaces x 3.1 MB fit in L2, so the kernels of this
+    leg read from L2 — it measures launch / tail behaviour at the small picture size, not HBM."""
+    g = S.make_geom(1920, 1080, 8, 1)
+    per_gpu = 8
+    wls = [workload(H, g, 0xC5 + 31 * rank + 5 * i) for i in range(2)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(per_gpu)]
+    ctxs = []
+    for i in range(per_gpu):
+        c = S.FilterContext(g, device=local)
+        c.begin(g)
+        c.upload(wls[i % 2]["rec"])
+        c.set_mi(wls[i % 2]["mi"])
+        c.sync()
+        c.set_stream(streams[i].cuda_stream)
+        ctxs.append(c)
+
+    def step():
+        for i, c in enumerate(ctxs):
+            wl = wls[i % 2]
+            c.rewind()
+            c.filter_chain(wl["lf"], wl["cdef"], wl["idx"], wl["ccso"], wl["flags"])
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(streams[0])
+    for st in streams[1:]:
+        st.wait_event(ev0)
+    for _ in range(steps):
+        step()
+    for st in streams[1:]:
+        e = torch.cuda.Event()
+        e.record(st)
+        streams[0].wait_event(e)
+    ev1.record(streams[0])
+    torch.cuda.synchronize(dev)
+    tt = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms = float(tt.item())
+    for c in ctxs:
+        c.close()
+    return {"metric": "filtered Mpixel/s (deblock+CDEF+CCSO), independent 1080p 8-bit streams sharded by stream",
+            "value": round(world * per_gpu * 1920 * 1080 * steps / (ms * 1e-3) / 1e6, 1), "unit": "Mpixel/s",
+            "streams_per_gpu": per_gpu, "streams_total": world * per_gpu, "pictures_per_s": round(world * per_gpu * steps / (ms * 1e-3), 1),
+            "ms_per_step": round(ms / steps, 4), "note": "device-resident, L2-resident working set (24 x 3.1 MB per GPU)"}
+
+
 def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     """Metric (ii): filter blocks per second through cdef_seg_search (64 strengths, all planes) + finish_cdef_search.
     Several pictures are in flight, one context + stream + submitting host thread each — the reference's CDEF stage runs
@@ -728,6 +782,7 @@ def main():
     e2e_ok = all(np.array_equal(chk[p], pins_out[0].planes[p]) for p in range(3))
     clocks = sampler.stop() if sampler else None
 
+    c5 = streams_1080p_leg(H, S, torch, dist, dev, local, rank, world, max(5, args.steps))
     search = gpu_search_leg(H, S, geom, wls[0], ctxs[:args.search_inflight], max(3, args.steps // 2), np) if rank == 0 else None
     derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lrl = lr_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
@@ -753,7 +808,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side, "loop_restoration": lrl, "handoff": hand,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:
