@@ -739,8 +739,10 @@ static int need_frame_mi(svtf_ctx *c, const char *fn) {
 
 // only_selected: launch no tiles for planes outside the mask (their samples in the output surface are then undefined;
 // used by the level search, which measures the filtered plane alone) instead of copying them through
+// sse_out: level-search trial — ONE plane (plane_start) is filtered (or, at level 0, left alone) and measured against the source
+// into *sse_out instead of being written; the chain position does not move.
 static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end, bool only_selected,
-                        const uint8_t *d_sb_lvl = nullptr, int sb_cols = 0, int sb_shift = 0) {
+                        const uint8_t *d_sb_lvl = nullptr, int sb_cols = 0, int sb_shift = 0, unsigned long long *sse_out = nullptr) {
     if (!lf || plane_start < 0 || plane_end > 3 || plane_start > plane_end)
         return c->fail(SVTF_E_ARG, "svtf_deblock_frame: bad arguments");
     if (int r = need_frame_mi(c, "svtf_deblock_frame"))
@@ -757,10 +759,11 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
             continue;
         mask |= 1u << p;
     }
-    if (!mask)
+    if (!mask && !sse_out)
         return SVTF_OK; // nothing to filter: the picture stays where it is
     CUDA_TRY(c, cudaSetDevice(c->device));
     DeblockArgs a;
+    a.sse_src = nullptr, a.sse_pitch = a.sse_w = a.sse_h = 0, a.sse_out = sse_out;
     const int   nxt = next_surface(c);
     a.in        = c->surf[c->cur].planes();
     a.out       = c->surf[nxt].planes();
@@ -778,7 +781,7 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
         a.tiles_x[p]   = (w + 8 + DBK_TILE - 1) / DBK_TILE;
         a.ty0[p]       = ((dlo >> ss) + 8) / DBK_TILE;
         a.tiles_y[p]   = ((dhi >> ss) - 1 + 8) / DBK_TILE + 1 - a.ty0[p];
-        if (only_selected && !((mask >> p) & 1))
+        if (only_selected && !((mask >> p) & 1) && !(sse_out && p == plane_start))
             a.tiles_y[p] = 0;
         a.tile_base[p] = total;
         total += a.tiles_x[p] * a.tiles_y[p];
@@ -786,6 +789,23 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
     a.plane_mask = mask;
     a.sb_lvl = d_sb_lvl, a.sb_cols = sb_cols, a.sb_shift = sb_shift;
     build_lf_tables(*lf, a.t);
+    if (sse_out) {
+        const int p = plane_start, ss = p ? 1 : 0;
+        a.sse_src = c->source.base[p], a.sse_pitch = c->source.pitch[p];
+        // picture_sse_calculations (Encoder/Codec/EbDeblockingFilter.c:716-835): 8-bit pictures are measured over the aligned
+        // size, 16-bit ones over the visible size
+        if (c->geom.sample_bytes == 1)
+            a.sse_w = (c->geom.mi_cols * 4) >> ss, a.sse_h = (c->geom.mi_rows * 4) >> ss;
+        else
+            a.sse_w = (c->geom.width + ss) >> ss, a.sse_h = (c->geom.height + ss) >> ss;
+        if (c->geom.sample_bytes == 1)
+            deblock_kernel<uint8_t, false, true><<<total, DBK_THREADS, 0, c->stream>>>(a);
+        else
+            deblock_kernel<uint16_t, false, true><<<total, DBK_THREADS, 0, c->stream>>>(a);
+        CUDA_TRY(c, cudaGetLastError());
+        c->launches++;
+        return SVTF_OK;
+    }
     if (d_sb_lvl) {
         if (c->geom.sample_bytes == 1)
             deblock_kernel<uint8_t, true><<<total, DBK_THREADS, 0, c->stream>>>(a);
@@ -1670,98 +1690,52 @@ extern "C" int svtf_lr_apply_frame(svtf_ctx *c, const svtf_lr_params *lr, const 
 
 // svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE) (Encoder/Codec/EbDeblockingFilter.c:1129-1252):
 // search_filter_level (:886-985) per plane with try_filter_frame (:841-880) = deblock one plane with a trial level,
-// picture_sse_calculations (:716-835) against the source, restore.  On the device a trial is one deblock launch of that
-// plane's tiles into a scratch surface plus one SSE reduction; nothing is restored because the unfiltered picture is
-// never overwritten.
-template <typename T>
-__global__ void __launch_bounds__(256) plane_sse_kernel(const T *a, const int pa, const T *b, const int pb, const int w, const int h,
-                                                        unsigned long long *out) {
-    unsigned long long acc = 0;
-    const int          n = w * h;
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
-        const int       y = i / w, x = i - y * w;
-        const long long d = (long long)a[(size_t)y * pa + x] - (long long)b[(size_t)y * pb + x];
-        acc += (unsigned long long)(d * d);
+// picture_sse_calculations (:716-835) against the source, restore.  On the device a trial is ONE launch: the deblock kernel's
+// SSE instantiation filters that plane's tiles in shared memory and measures them against the source instead of writing
+// them; nothing is restored because the unfiltered picture is never overwritten.
+// search_filter_level (Encoder/Codec/EbDeblockingFilter.c:886-985) for one plane as a state machine (dir 2 = both luma
+// directions, as svt_av1_pick_filter_level calls it): `wanted()` names the levels the next step of the reference's loop
+// would try (filt_low and filt_high are tried independently of each other's result), `advance()` is the loop body once
+// their errors are known.  The three planes' searches are independent of one another (a plane's trial filters that plane
+// alone, with that plane's level), so svtf_lf_search_frame runs them in lock-step: one batch of trials = up to six
+// deblock+SSE launches and ONE host round trip, instead of one round trip per trial.
+struct LfPlaneSearch {
+    int     plane, filt_mid, step, filt_best, direction = 0, convergence = 0;
+    int64_t best_err = 0, ss_err[64];
+    bool    started = false;
+    void init(int p, int lvl) {
+        plane    = p;
+        filt_mid = std::min(std::max(lvl, 0), 63); // MAX_LOOP_FILTER
+        step     = filt_mid < 16 ? 4 : filt_mid / 4;
+        for (int i = 0; i < 64; i++) ss_err[i] = -1;
+        filt_best = filt_mid;
     }
-#pragma unroll
-    for (int m = 16; m > 0; m >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, m);
-    __shared__ unsigned long long s[8];
-    if ((threadIdx.x & 31) == 0)
-        s[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned long long t = 0;
-        for (int i = 0; i < 8; i++) t += s[i];
-        atomicAdd(out, t);
+    bool done() const { return started && step <= 0; }
+    int  low() const { return std::max(filt_mid - step, 0); }
+    int  high() const { return std::min(filt_mid + step, 63); }
+    int  wanted(int lv[2]) const {
+        int n = 0;
+        if (!started) {
+            lv[n++] = filt_mid;
+            return n;
+        }
+        if (direction <= 0 && low() != filt_mid && ss_err[low()] < 0)
+            lv[n++] = low();
+        if (direction >= 0 && high() != filt_mid && ss_err[high()] < 0 && !(n && lv[0] == high()))
+            lv[n++] = high();
+        return n;
     }
-}
-
-// try_filter_frame: SSE of `plane` after deblocking it with lf (levels already set by the caller)
-static int lf_trial(svtf_ctx *c, const svtf_lf_params *lf, int plane, int64_t *err) {
-    const int saved = c->cur;
-    if (int r = deblock_impl(c, lf, plane, plane + 1, true))
-        return r;
-    const Surface  &s  = c->surf[c->cur];
-    const int       ss = plane ? 1 : 0;
-    // picture_sse_calculations: 8-bit pictures are measured over the aligned size, 16-bit ones over the visible size
-    int w, h;
-    if (c->geom.sample_bytes == 1)
-        w = (c->geom.mi_cols * 4) >> ss, h = (c->geom.mi_rows * 4) >> ss;
-    else
-        w = (c->geom.width + ss) >> ss, h = (c->geom.height + ss) >> ss;
-    unsigned long long *d_out = reinterpret_cast<unsigned long long *>(c->d_pick_tot); // 8 bytes of an idle scratch buffer
-    CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out), c->stream));
-    const int grid = std::min((w * h + 255) / 256, 8 * std::max(c->sm_count, 1));
-    if (c->geom.sample_bytes == 1)
-        plane_sse_kernel<uint8_t><<<grid, 256, 0, c->stream>>>(static_cast<const uint8_t *>(c->source.base[plane]), c->source.pitch[plane],
-                                                              static_cast<const uint8_t *>(s.base[plane]), s.pitch[plane], w, h, d_out);
-    else
-        plane_sse_kernel<uint16_t><<<grid, 256, 0, c->stream>>>(static_cast<const uint16_t *>(c->source.base[plane]), c->source.pitch[plane],
-                                                               static_cast<const uint16_t *>(s.base[plane]), s.pitch[plane], w, h, d_out);
-    CUDA_TRY(c, cudaGetLastError());
-    c->launches++;
-    unsigned long long v = 0;
-    CUDA_TRY(c, cudaMemcpyAsync(&v, d_out, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out), c->stream)); // the pick expects a zeroed tot
-    *err   = (int64_t)v;
-    c->cur = saved;
-    return SVTF_OK;
-}
-
-// search_filter_level for one plane (dir 2 = both luma directions, as svt_av1_pick_filter_level calls it)
-static int lf_search_plane(svtf_ctx *c, svtf_lf_params *lf, const svtf_lf_search_cfg *cfg, const int32_t last[4], int plane, int32_t *best) {
-    const int min_level = 0, max_level = 63; // MAX_LOOP_FILTER
-    // luma is searched with dir = 2 and the start level is last_frame_filter_level[dir] unless dlf_avg: index 2 is the U
-    // level (:903-909) — kept as the reference has it
-    const int lvl       = plane == 0 ? (cfg->dlf_avg ? last[0] : last[2]) : last[plane + 1];
-    int       filt_mid  = std::min(std::max(lvl, min_level), max_level);
-    int       step      = filt_mid < 16 ? 4 : filt_mid / 4;
-    int64_t   ss_err[64];
-    for (int i = 0; i < 64; i++) ss_err[i] = -1;
-    auto try_level = [&](int level, int64_t *e) -> int {
-        if (plane == 0)
-            lf->filter_level[0] = lf->filter_level[1] = level;
-        else if (plane == 1)
-            lf->filter_level_u = level;
-        else
-            lf->filter_level_v = level;
-        return lf_trial(c, lf, plane, e);
-    };
-    int64_t best_err;
-    if (int r = try_level(filt_mid, &best_err))
-        return r;
-    int filt_best = filt_mid, direction = 0, convergence = 0;
-    ss_err[filt_mid] = best_err;
-    while (step > 0) {
-        const int filt_high = std::min(filt_mid + step, max_level), filt_low = std::max(filt_mid - step, min_level);
+    void advance(const svtf_lf_search_cfg *cfg) {
+        if (!started) {
+            started  = true;
+            best_err = ss_err[filt_mid];
+            return;
+        }
+        const int filt_high = high(), filt_low = low();
         int64_t   bias      = (best_err >> (15 - (filt_mid / 8))) * step; // bias against raising the level
         if (!cfg->only_4x4)
             bias >>= 1;
         if (direction <= 0 && filt_low != filt_mid) {
-            if (ss_err[filt_low] < 0)
-                if (int r = try_level(filt_low, &ss_err[filt_low]))
-                    return r;
             if (ss_err[filt_low] < best_err + bias) {
                 if (ss_err[filt_low] < best_err)
                     best_err = ss_err[filt_low];
@@ -1769,9 +1743,6 @@ static int lf_search_plane(svtf_ctx *c, svtf_lf_params *lf, const svtf_lf_search
             }
         }
         if (direction >= 0 && filt_high != filt_mid) {
-            if (ss_err[filt_high] < 0)
-                if (int r = try_level(filt_high, &ss_err[filt_high]))
-                    return r;
             if (ss_err[filt_high] < best_err - bias) {
                 best_err  = ss_err[filt_high];
                 filt_best = filt_high;
@@ -1789,9 +1760,7 @@ static int lf_search_plane(svtf_ctx *c, svtf_lf_params *lf, const svtf_lf_search
             filt_mid  = filt_best;
         }
     }
-    *best = filt_best;
-    return SVTF_OK;
-}
+};
 
 extern "C" int svtf_lf_search_frame(svtf_ctx *c, const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]) {
     if (!c)
@@ -1805,19 +1774,56 @@ extern "C" int svtf_lf_search_frame(svtf_ctx *c, const svtf_lf_params *start, co
     if (c->striped)
         return c->fail(SVTF_E_STATE, "svtf_lf_search_frame: not available on a striped context");
     CUDA_TRY(c, cudaSetDevice(c->device));
-    svtf_lf_params lf      = *start;
-    const int32_t  last[4] = {start->filter_level[0], start->filter_level[1], start->filter_level_u, start->filter_level_v};
-    int32_t        y = 0, u = last[2], v = last[3];
-    if (int r = lf_search_plane(c, &lf, cfg, last, 0, &y))
-        return r;
-    lf.filter_level[0] = lf.filter_level[1] = y;
-    if (cfg->search_chroma) {
-        if (int r = lf_search_plane(c, &lf, cfg, last, 1, &u))
-            return r;
-        lf.filter_level_u = u;
-        if (int r = lf_search_plane(c, &lf, cfg, last, 2, &v))
-            return r;
+    const int32_t last[4] = {start->filter_level[0], start->filter_level[1], start->filter_level_u, start->filter_level_v};
+    int32_t       y = 0, u = last[2], v = last[3];
+    LfPlaneSearch ps[3];
+    // luma is searched with dir = 2 and the start level is last_frame_filter_level[dir] unless dlf_avg: index 2 is the U
+    // level (:903-909) — kept as the reference has it
+    ps[0].init(0, cfg->dlf_avg ? last[0] : last[2]);
+    ps[1].init(1, last[2]);
+    ps[2].init(2, last[3]);
+    const int           nplanes = cfg->search_chroma ? 3 : 1;
+    unsigned long long *d_out   = reinterpret_cast<unsigned long long *>(c->d_pick_tot); // 48 bytes of an idle scratch buffer
+    for (;;) {
+        int trial_plane[6], trial_level[6], nt = 0;
+        for (int p = 0; p < nplanes; p++) {
+            if (ps[p].done())
+                continue;
+            int       lv[2];
+            const int n = ps[p].wanted(lv);
+            for (int k = 0; k < n; k++) trial_plane[nt] = p, trial_level[nt] = lv[k], nt++;
+        }
+        if (nt) {
+            CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out) * 6, c->stream));
+            for (int t = 0; t < nt; t++) { // try_filter_frame (:841-880): this plane, this level
+                svtf_lf_params lf = *start;
+                if (trial_plane[t] == 0)
+                    lf.filter_level[0] = lf.filter_level[1] = trial_level[t];
+                else if (trial_plane[t] == 1)
+                    lf.filter_level_u = trial_level[t];
+                else
+                    lf.filter_level_v = trial_level[t];
+                if (int r = deblock_impl(c, &lf, trial_plane[t], trial_plane[t] + 1, true, nullptr, 0, 0, d_out + t))
+                    return r;
+            }
+            unsigned long long res[6] = {0, 0, 0, 0, 0, 0};
+            CUDA_TRY(c, cudaMemcpyAsync(res, d_out, sizeof(*d_out) * 6, cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            for (int t = 0; t < nt; t++) ps[trial_plane[t]].ss_err[trial_level[t]] = (int64_t)res[t];
+        }
+        bool all_done = true;
+        for (int p = 0; p < nplanes; p++)
+            if (!ps[p].done()) {
+                ps[p].advance(cfg);
+                all_done = all_done && ps[p].done();
+            }
+        if (all_done)
+            break;
     }
+    CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out) * 6, c->stream)); // the pick expects a zeroed tot
+    y = ps[0].filt_best;
+    if (cfg->search_chroma)
+        u = ps[1].filt_best, v = ps[2].filt_best;
     out_levels[0] = out_levels[1] = y, out_levels[2] = u, out_levels[3] = v;
     return SVTF_OK;
 }

@@ -112,6 +112,11 @@ struct DeblockArgs {
     // per-superblock level tables [sb][plane][256] (delta_lf_present with the decoder's per-SB deltas) or nullptr
     const uint8_t *sb_lvl;
     int            sb_cols, sb_shift; // superblocks per row; log2(4x4 units per superblock side)
+    // SSE instantiation (deblock level search, try_filter_frame + picture_sse_calculations): the filtered tile is not written but
+    // measured against the source plane over [0, sse_w) x [0, sse_h); one launch covers ONE plane
+    const void         *sse_src;
+    int                 sse_pitch, sse_w, sse_h;
+    unsigned long long *sse_out;
 };
 
 // One line across an edge; s[k*st], k=-7..6 = p6..p0,q0..q6 (16-bit samples in shared memory).
@@ -232,7 +237,9 @@ __device__ __forceinline__ unsigned dbk_edge_params(const svtf_mi_t *__restrict_
     return 0;
 }
 
-template <typename T, bool SBLVL = false> // SBLVL: per-superblock level tables (decoder delta_lf), a separate instantiation
+// SBLVL: per-superblock level tables (decoder delta_lf); SSE: measure against the source instead of writing (level search).
+// Both are separate instantiations so the common path keeps its 32 registers.
+template <typename T, bool SBLVL = false, bool SSE = false>
 __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_constant__ DeblockArgs a) {
     __shared__ __align__(16) uint16_t tile[DBK_LOAD * DBK_PITCH];
     __shared__ uint8_t                vpar[DBK_VUNITS * DBK_EDGES]; // [row unit][edge]
@@ -311,6 +318,46 @@ __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_const
         }
     }
     __syncthreads();
+    if (SSE) { // ---- squared error of the tile against the source (svt_spatial_full_distortion_kernel / _16bits) ----
+        const T           *src = static_cast<const T *>(a.sse_src);
+        unsigned long long acc = 0;
+        for (int i = tid; i < DBK_TILE * (DBK_TILE / 8); i += DBK_THREADS) {
+            const int r = i >> 3, c = (i & 7) * 8;
+            const int gy = Y0 + 8 + r, gx = X0 + 8 + c;
+            if (gy < 0 || gy >= a.sse_h || gx < 0 || gx >= a.sse_w)
+                continue;
+            const uint16_t *s = tile + (r + 8) * DBK_PITCH + 8 + c;
+            unsigned        e = 0;
+            if (gx + 8 <= a.sse_w) {
+                const uint4    v    = ld8<T>(src + (size_t)gy * a.sse_pitch + gx);
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int d0 = (int)s[2 * k] - (int)(w[k] & 0xffff), d1 = (int)s[2 * k + 1] - (int)(w[k] >> 16);
+                    e += (unsigned)(d0 * d0) + (unsigned)(d1 * d1);
+                }
+            } else {
+                for (int k = 0; gx + k < a.sse_w; k++) {
+                    const int d = (int)s[k] - (int)src[(size_t)gy * a.sse_pitch + gx + k];
+                    e += (unsigned)(d * d);
+                }
+            }
+            acc += e;
+        }
+#pragma unroll
+        for (int m = 16; m > 0; m >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, m);
+        __shared__ unsigned long long s_sse[DBK_THREADS / 32];
+        if ((tid & 31) == 0)
+            s_sse[tid >> 5] = acc;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long t = 0;
+            for (int i = 0; i < DBK_THREADS / 32; i++) t += s_sse[i];
+            if (t)
+                atomicAdd(a.sse_out, t);
+        }
+        return;
+    }
     // ---- write the 64x64 tile (staged rows/cols 8..71) ----
     for (int i = tid; i < DBK_TILE * (DBK_TILE / 8); i += DBK_THREADS) {
         const int r = i >> 3, c = (i & 7) * 8;
