@@ -394,3 +394,38 @@ API int adapt_chain_lr(const svtf_geom *g, void *y, int sy, void *cb, int scb, v
     harness_free(&h);
     return 0;
 }
+
+/* svtf_pad_ref_pictures on padded reference buffers: `pad16` / `pad8` / `padn` point at the first sample of the padded
+ * allocations (strides in samples), whose picture part at (org_x, org_y) already holds the filtered picture.  resident:
+ * deblock the picture on the GPU first (svt_av1_loop_filter_frame) and pad from the device copy. */
+API int adapt_pad_ref(const svtf_geom *g, void *pad[3], const int pst[3], uint8_t *pad8[3], const int st8[3], uint8_t *padn[3], const int stn[3],
+                      int org_x, int org_y, int pad_right, int pad_bottom, const ref_mi_soa *soa, const svtf_lf_params *lf, int resident) {
+    harness h;
+    const int sb = g->sample_bytes;
+    /* the recon descriptor points into the padded allocation */
+    if (harness_init(&h, g, soa, pad[0], pst[0], pad[1], pst[1], pad[2], pst[2]))
+        return -1;
+    EbPictureBufferDesc *r = h.recon;
+    r->org_x = (uint16_t)org_x, r->org_y = (uint16_t)org_y;
+    r->width = (uint16_t)(g->width + pad_right), r->height = (uint16_t)(g->height + pad_bottom);
+    h.scs->pad_right = pad_right, h.scs->pad_bottom = pad_bottom;
+    EbPictureBufferDesc r8 = *r; /* the 8-bit reference picture of a 16-bit pipeline */
+    if (sb == 2) {
+        r8.buffer_y = pad8[0], r8.buffer_cb = pad8[1], r8.buffer_cr = pad8[2];
+        r8.stride_y = (uint16_t)st8[0], r8.stride_cb = (uint16_t)st8[1], r8.stride_cr = (uint16_t)st8[2];
+        r8.buffer_bit_inc_y = padn ? padn[0] : NULL, r8.buffer_bit_inc_cb = padn ? padn[1] : NULL, r8.buffer_bit_inc_cr = padn ? padn[2] : NULL;
+        if (padn)
+            r8.stride_bit_inc_y = (uint16_t)stn[0], r8.stride_bit_inc_cb = (uint16_t)stn[1], r8.stride_bit_inc_cr = (uint16_t)stn[2];
+        h.eds->recon_pic = &r8;
+    }
+    if (resident) {
+        fill_lf(&h, lf);
+        svtf_adapter_set_resident(1);
+        svt_av1_loop_filter_frame(h.recon, h.pcs, 0, 3);
+    }
+    svtf_pad_ref_pictures(h.pcs, h.scs);
+    svtf_adapter_set_resident(0);
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}

@@ -607,3 +607,49 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
     s->resident = 0;
     for (int p = 0; p < 3; p++) free(units[p]);
 }
+
+/* ----------------------------------------------------------------------------------------------------
+ * Recon hand-off: the pixel work of pad_ref_and_set_flags (Encoder/Codec/EbEncDecProcess.c:1589-1744) —
+ * right/bottom replication, border padding and the 8-bit / 2-bit split (or narrowing) of the reference picture — from the
+ * picture on the GPU.  pad_ref_and_set_flags keeps its bookkeeping (ref_poc, qp, slice_type, ...) and calls this in place of
+ * lines 1604-1744.  With a resident chain the picture never was on the host; otherwise it is uploaded from the recon buffer
+ * first.  (is_16bit_pipeline with 8-bit content and max_input_pad_right/bottom != 0: the reference narrows the full
+ * allocation width including columns its padding did not write; this function writes the padded rectangle only.)
+ * ---------------------------------------------------------------------------------------------------- */
+void svtf_pad_ref_pictures(PictureControlSet *pcs, SequenceControlSet *scs) {
+    EbPictureBufferDesc *ref8, *ref16;
+    svt_aom_get_recon_pic(pcs, &ref8, 0);
+    svt_aom_get_recon_pic(pcs, &ref16, 1);
+    const Bool is_16bit = scs->static_config.encoder_bit_depth > EB_EIGHT_BIT;
+    const Bool pipe16   = scs->is_16bit_pipeline;
+    CtxSlot   *s        = slot_for(pcs);
+    if (!(g_resident && s->resident)) { /* stand-alone: the filtered picture is in the recon buffer */
+        const EbPictureBufferDesc *pic = (is_16bit || pipe16) ? ref16 : ref8;
+        void                      *p[3];
+        int32_t                    st[3];
+        plane_ptrs(pic, s->geom.sample_bytes, p, st);
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    }
+    const EbPictureBufferDesc *d = (is_16bit || pipe16) ? ref16 : ref8;
+    svtf_ref_layout            lay;
+    lay.org_x = d->org_x, lay.org_y = d->org_y;
+    if (pipe16 && !is_16bit) { /* :1687-1710: borders around the unpadded input size, no right/bottom replication */
+        lay.width = d->width - scs->max_input_pad_right, lay.height = d->height - scs->max_input_pad_bottom;
+        lay.pad_right = lay.pad_bottom = 0;
+    } else {
+        lay.width = d->width, lay.height = d->height;
+        lay.pad_right = (int32_t)scs->pad_right, lay.pad_bottom = (int32_t)scs->pad_bottom;
+    }
+    void         *dst[3]  = {d->buffer_y, d->buffer_cb, d->buffer_cr};
+    const int32_t dstr[3] = {d->stride_y, d->stride_cb, d->stride_cr};
+    if (is_16bit || pipe16) {
+        uint8_t      *d8[3]  = {ref8->buffer_y, ref8->buffer_cb, ref8->buffer_cr};
+        const int32_t s8[3]  = {ref8->stride_y, ref8->stride_cb, ref8->stride_cr};
+        uint8_t      *dn[3]  = {ref8->buffer_bit_inc_y, ref8->buffer_bit_inc_cb, ref8->buffer_bit_inc_cr};
+        const int32_t sn[3]  = {ref8->stride_bit_inc_y, ref8->stride_bit_inc_cb, ref8->stride_bit_inc_cr};
+        const int     two    = is_16bit && scs->static_config.encoder_bit_depth == EB_TEN_BIT && dn[0] && dn[1] && dn[2];
+        CHECK(svtf_download_ref_padded(s->ctx, &lay, dst, dstr, d8, s8, two ? dn : NULL, two ? sn : NULL), s->ctx);
+    } else
+        CHECK(svtf_download_ref_padded(s->ctx, &lay, dst, dstr, NULL, NULL, NULL, NULL), s->ctx);
+}

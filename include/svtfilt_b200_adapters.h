@@ -28,6 +28,11 @@ struct SequenceControlSet;
  * pcs->mse_seg, pcs->skip_cdef_seg and pcs->cdef_dir_data.  The first CDEF segment to arrive calls it. */
 void svtf_cdef_search_picture(struct PictureControlSet *pcs, struct SequenceControlSet *scs);
 
+/* The pixel work of pad_ref_and_set_flags (Encoder/Codec/EbEncDecProcess.c:1589-1744): right/bottom replication, border
+ * padding and the 8-bit / 2-bit split (or narrowing) of the reference picture, produced on the GPU (resident picture, or the
+ * recon buffer uploaded first).  pad_ref_and_set_flags calls it in place of its lines 1604-1744 and keeps its bookkeeping. */
+void svtf_pad_ref_pictures(struct PictureControlSet *pcs, struct SequenceControlSet *scs);
+
 /* CUDA device used by contexts the adapters create (default 0). */
 void svtf_adapter_set_device(int device);
 /* 1: keep the picture resident on the GPU between DLF, CDEF search, CDEF apply and CCSO of one pcs (no

@@ -176,3 +176,46 @@ def test_loop_restoration_adapter(H, orc, adapt, w, h, bd, sb, seed, kw):
     idx8 = np.ascontiguousarray(idx, dtype=np.int8)
     assert adapt.adapt_chain_lr(C.byref(g), *H._planes(got2), C.byref(s), C.byref(lf), C.byref(cdef), H._p(idx8), C.byref(lr), up) == 0
     assert H.planes_equal(vis(H, g, got2), vis(H, g, exp)), H.first_diff(vis(H, g, got2), vis(H, g, exp))
+
+
+@pytest.mark.parametrize("w,h,bd,sb,resident", [(200, 136, 8, 1, 0), (328, 200, 10, 2, 0), (328, 200, 10, 2, 1), (200, 136, 8, 2, 1),
+                                                (322, 198, 10, 2, 0)])
+def test_pad_ref_pictures_adapter(H, orc, adapt, w, h, bd, sb, resident):
+    """svtf_pad_ref_pictures = the pixel work of pad_ref_and_set_flags, through the reference's own structures: padded reference
+    picture (+ 8-bit / 2-bit planes in the 16-bit pipeline) from the recon buffer, or from the picture left on the GPU by
+    svt_av1_loop_filter_frame (resident)."""
+    S = H.S
+    pr, pb = (-w) % 8, (-h) % 8  # picture padded to a multiple of 8 by replication
+    g = S.make_geom(w, h, bd, sb)
+    pic = H.synth_picture(g, 2500 + w + bd)
+    soa = H.synth_mode_info(g, 2501)
+    mi = H.pack_mi(soa)
+    s, keep = _soa(H, soa)
+    lf = S.lf_params((26, 20), 11, 13)
+    ox, oy = 48, 32
+    filt = orc.deblock(g, pic, mi, lf) if resident else pic
+    split, two = sb == 2, sb == 2 and bd == 10
+    exp = H.handoff_cpu(orc.lib, "svtf_orc_", g, filt, w + pr, h + pb, ox, oy, pr, pb, split, two)
+    if H.ref_available():
+        ref = H.handoff_cpu(H.Ref().lib, "ref_", g, filt, w + pr, h + pb, ox, oy, pr, pb, split, two)
+        assert H.planes_equal(exp[0], ref[0])
+    # padded allocations with the picture placed at (org_x, org_y)
+    bufs = [np.zeros_like(p) for p in exp[0]]
+    for b, p, sft in zip(bufs, pic, (0, 1, 1)):
+        vw, vh = (w + sft) >> sft, (h + sft) >> sft
+        b[(oy + sft) >> sft:((oy + sft) >> sft) + vh, (ox + sft) >> sft:((ox + sft) >> sft) + vw] = p[:vh, :vw]
+    b8 = [np.zeros(p.shape, np.uint8) for p in bufs]
+    bn = [np.zeros(p.shape, np.uint8) for p in bufs]
+
+    def arr(lst):
+        return (C.c_void_p * 3)(*[a.ctypes.data for a in lst]), (C.c_int * 3)(*[a.strides[0] // a.itemsize for a in lst])
+
+    p16, s16 = arr(bufs)
+    p8, s8 = arr(b8)
+    pn, sn = arr(bn)
+    assert adapt.adapt_pad_ref(C.byref(g), p16, s16, p8, s8, pn if two else None, sn, ox, oy, pr, pb, C.byref(s), C.byref(lf), resident) == 0
+    assert H.planes_equal(bufs, exp[0]), "padded: " + H.first_diff(bufs, exp[0])
+    if split:
+        assert H.planes_equal(b8, exp[1]), "8-bit: " + H.first_diff(b8, exp[1])
+    if two:
+        assert H.planes_equal(bn, exp[2]), "2-bit: " + H.first_diff(bn, exp[2])
