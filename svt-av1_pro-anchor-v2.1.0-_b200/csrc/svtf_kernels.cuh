@@ -240,12 +240,14 @@ __device__ __forceinline__ unsigned dbk_edge_params(const svtf_mi_t *__restrict_
 // SBLVL: per-superblock level tables (decoder delta_lf); SSE: measure against the source instead of writing (level search).
 // Both are separate instantiations so the common path keeps its 32 registers.
 template <typename T, bool SBLVL = false, bool SSE = false>
-__global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_constant__ DeblockArgs a) {
+__global__ void __launch_bounds__(DBK_THREADS, 8) deblock_kernel(const __grid_constant__ DeblockArgs a) {
     __shared__ __align__(16) uint16_t tile[DBK_LOAD * DBK_PITCH];
-    __shared__ uint8_t                vpar[DBK_VUNITS * DBK_EDGES]; // [row unit][edge]
-    __shared__ uint8_t                hpar[DBK_EDGES * 16];         // [edge][col unit]
-    __shared__ uint8_t                s_lvl[256];
-    __shared__ uint8_t                s_thr[3][64]; // lim, mblim, hev
+    // work lists of the two passes, one per filter code (1 = 4-tap, 2 = 8/6-tap, 3 = 14-tap): entry = level << 10 | unit << 5 | edge.
+    // Lanes then work on edges that exist, four lines of a 4-sample unit next to each other, one filter length per list.
+    __shared__ uint16_t s_list[2][3][DBK_VUNITS * DBK_EDGES + 2];
+    __shared__ int      s_cnt[2][3];
+    __shared__ uint8_t  s_lvl[256];
+    __shared__ uint8_t  s_thr[3][64]; // lim, mblim, hev
 
     const int tid   = threadIdx.x;
     const int bid   = blockIdx.x;
@@ -279,40 +281,50 @@ __global__ void __launch_bounds__(DBK_THREADS) deblock_kernel(const __grid_const
             s_thr[1][tid] = a.t.mblim[tid];
             s_thr[2][tid] = a.t.hev[tid];
         }
+        if (tid < 6)
+            (&s_cnt[0][0])[tid] = 0;
         __syncthreads();
-        // ---- edge parameters: vertical edges per (4-row unit, edge), horizontal per (edge, 4-col unit) ----
+        // ---- edge parameters: vertical edges per (4-row unit, edge), horizontal per (edge, 4-col unit) -> work lists ----
         for (int i = tid; i < DBK_VUNITS * DBK_EDGES + DBK_EDGES * 16; i += DBK_THREADS) {
+            unsigned pr;
+            int      pass, u, k;
             if (i < DBK_VUNITS * DBK_EDGES) {
-                const int u = i / DBK_EDGES, k = i - u * DBK_EDGES;
-                vpar[i] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph, SBLVL ? a.sb_lvl : nullptr,
-                                                   a.sb_cols, a.sb_shift);
+                pass = 0, u = i / DBK_EDGES, k = i - u * DBK_EDGES;
+                pr = dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph, SBLVL ? a.sb_lvl : nullptr,
+                                     a.sb_cols, a.sb_shift);
             } else {
                 const int j = i - DBK_VUNITS * DBK_EDGES;
-                const int k = j >> 4, u = j & 15;
-                hpar[j] = (uint8_t)dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph, SBLVL ? a.sb_lvl : nullptr,
-                                                   a.sb_cols, a.sb_shift);
+                pass = 1, k = j >> 4, u = j & 15;
+                pr = dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph, SBLVL ? a.sb_lvl : nullptr,
+                                     a.sb_cols, a.sb_shift);
+            }
+            if (pr & 3) {
+                const int code = (pr & 3) - 1;
+                s_list[pass][code][atomicAdd(&s_cnt[pass][code], 1)] = (uint16_t)(((pr >> 2) << 10) | (u << 5) | k);
             }
         }
         __syncthreads();
         const int sh = a.d.bit_depth - 8;
-        // ---- column pass: vertical edges; lane -> consecutive rows (pitch is odd in words) ----
-        for (int i = tid; i < 72 * DBK_EDGES; i += DBK_THREADS) {
-            const int      k = i / 72, r = i - k * 72;
-            const unsigned pr = vpar[(r >> 2) * DBK_EDGES + k];
-            if (pr & 3) {
-                const int code = pr & 3, lv = pr >> 2;
-                const int len  = code == 1 ? 4 : (code == 3 ? 14 : (plane ? 6 : 8));
+        // ---- column pass: vertical edges; thread = one line (row) of a listed unit ----
+#pragma unroll
+        for (int code = 0; code < 3; code++) {
+            const int n   = s_cnt[0][code] * 4;
+            const int len = code == 0 ? 4 : (code == 2 ? 14 : (plane ? 6 : 8));
+            for (int i = tid; i < n; i += DBK_THREADS) {
+                const unsigned e  = s_list[0][code][i >> 2];
+                const int      lv = e >> 10, r = ((e >> 5) & 31) * 4 + (i & 3), k = e & 31;
                 lpf_line(tile + (r + 4) * DBK_PITCH + 8 + 4 * k, 1, len, sh, s_thr[1][lv], s_thr[0][lv], s_thr[2][lv]);
             }
         }
         __syncthreads();
-        // ---- row pass: horizontal edges; lane -> consecutive columns ----
-        for (int i = tid; i < 64 * DBK_EDGES; i += DBK_THREADS) {
-            const int      k = i >> 6, c = i & 63;
-            const unsigned pr = hpar[k * 16 + (c >> 2)];
-            if (pr & 3) {
-                const int code = pr & 3, lv = pr >> 2;
-                const int len  = code == 1 ? 4 : (code == 3 ? 14 : (plane ? 6 : 8));
+        // ---- row pass: horizontal edges; thread = one line (column) of a listed unit ----
+#pragma unroll
+        for (int code = 0; code < 3; code++) {
+            const int n   = s_cnt[1][code] * 4;
+            const int len = code == 0 ? 4 : (code == 2 ? 14 : (plane ? 6 : 8));
+            for (int i = tid; i < n; i += DBK_THREADS) {
+                const unsigned e  = s_list[1][code][i >> 2];
+                const int      lv = e >> 10, c = ((e >> 5) & 31) * 4 + (i & 3), k = e & 31;
                 lpf_line(tile + (8 + 4 * k) * DBK_PITCH + 8 + c, DBK_PITCH, len, sh, s_thr[1][lv], s_thr[0][lv], s_thr[2][lv]);
             }
         }
