@@ -193,26 +193,14 @@ __device__ __forceinline__ void lpf_line(uint16_t *s, const int st, const int le
 }
 
 // set_lpf_parameters — Encoder/Codec/EbDeblockingFilter.c:162-285, evaluated independently per 4-sample
-// unit (the reference walks by transform size; skipped units are never on a transform edge).
-// Returns (level << 2) | code, code 0 = no filter, 1 = 4-tap, 2 = 8-tap (luma) / 6-tap (chroma), 3 = 14-tap.
-__device__ __forceinline__ unsigned dbk_edge_params(const svtf_mi_t *__restrict__ mi, const int mi_stride,
-                                                    const uint8_t *lvl /* [seg][dir][ref][mlf] of this plane */,
-                                                    const int plane, const int dir, const int x, const int y, const int pw,
-                                                    const int ph, const uint8_t *__restrict__ sb_lvl = nullptr, const int sb_cols = 0,
-                                                    const int sb_shift = 0) {
-    if (x < 0 || y < 0 || x >= pw || y >= ph)
-        return 0;
-    const int coord = dir == 0 ? x : y;
-    if (coord == 0)
-        return 0;
-    const int       ss     = plane ? 1 : 0;
-    const int       mi_row = ss | ((y << ss) >> 2), mi_col = ss | ((x << ss) >> 2);
-    const svtf_mi_t cur    = __ldg(mi + mi_row * mi_stride + mi_col);
-    const int       ts     = mi_tx(cur, plane, dir);
-    if (coord & ((4 << ts) - 1))
-        return 0;
-    const svtf_mi_t prv = dir == 0 ? __ldg(mi + mi_row * mi_stride + mi_col - (1 << ss))
-                                   : __ldg(mi + (mi_row - (1 << ss)) * mi_stride + mi_col);
+// unit (the reference walks by transform size; skipped units are never on a transform edge).  `cur` is the unit's mode
+// info, already known to lie on a transform edge in direction `dir` (coord = x or y of the edge, != 0); `prv` its left /
+// top neighbour.  Returns (level << 2) | code, code 0 = no filter, 1 = 4-tap, 2 = 8-tap (luma) / 6-tap (chroma), 3 = 14-tap.
+__device__ __forceinline__ unsigned dbk_edge_decide(const svtf_mi_t cur, const svtf_mi_t prv, const int ts,
+                                                    const uint8_t *lvl /* [seg][dir][ref][mlf] of this plane */, const int plane,
+                                                    const int dir, const int coord, const int mi_row, const int mi_col,
+                                                    const uint8_t *__restrict__ sb_lvl, const int sb_cols, const int sb_shift) {
+    const int ss = plane ? 1 : 0;
     // lvl index: ((seg*2+dir)*8+ref)*2+mlf ; key = ref | mlf<<3 | seg<<4
     // with per-superblock deltas the table of the superblock that CONTAINS the unit is used, for the current unit and
     // for its left/top neighbour alike (sb_delta_lf / sb_delta_lf_left / _above, Decoder/Codec/EbDecLF.c:357,548)
@@ -284,23 +272,34 @@ __global__ void __launch_bounds__(DBK_THREADS, 8) deblock_kernel(const __grid_co
         if (tid < 6)
             (&s_cnt[0][0])[tid] = 0;
         __syncthreads();
-        // ---- edge parameters: vertical edges per (4-row unit, edge), horizontal per (edge, 4-col unit) -> work lists ----
-        for (int i = tid; i < DBK_VUNITS * DBK_EDGES + DBK_EDGES * 16; i += DBK_THREADS) {
-            unsigned pr;
-            int      pass, u, k;
-            if (i < DBK_VUNITS * DBK_EDGES) {
-                pass = 0, u = i / DBK_EDGES, k = i - u * DBK_EDGES;
-                pr = dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 0, X0 + 8 + 4 * k, Y0 + 4 + 4 * u, pw, ph, SBLVL ? a.sb_lvl : nullptr,
-                                     a.sb_cols, a.sb_shift);
-            } else {
-                const int j = i - DBK_VUNITS * DBK_EDGES;
-                pass = 1, k = j >> 4, u = j & 15;
-                pr = dbk_edge_params(a.mi, a.mi_stride, s_lvl, plane, 1, X0 + 8 + 4 * u, Y0 + 8 + 4 * k, pw, ph, SBLVL ? a.sb_lvl : nullptr,
-                                     a.sb_cols, a.sb_shift);
+        // ---- edge parameters -> work lists.  One thread per 4x4 unit of the tile decides its left (vertical) and its top
+        //      (horizontal) edge from one read of the unit's mode info: units (ur, uc) = plane position (Y0 + 4ur, X0 + 4uc),
+        //      ur 1..18, uc 2..18; vertical edges: row unit ur-1, edge uc-2; horizontal: edge ur-2 (ur >= 2), col unit uc-2 (<= 15)
+        constexpr int NUC = DBK_EDGES;
+        for (int i = tid; i < DBK_VUNITS * NUC; i += DBK_THREADS) {
+            const int ur = 1 + i / NUC, uc = 2 + (i - (i / NUC) * NUC);
+            const int x = X0 + 4 * uc, y = Y0 + 4 * ur;
+            if (x < 0 || y < 0 || x >= pw || y >= ph)
+                continue;
+            const int       mi_row = ss | ((y << ss) >> 2), mi_col = ss | ((x << ss) >> 2);
+            const svtf_mi_t *mp    = a.mi + mi_row * a.mi_stride + mi_col;
+            const svtf_mi_t  cur   = __ldg(mp);
+            const int        tsv = mi_tx(cur, plane, 0), tsh = mi_tx(cur, plane, 1);
+            if (x != 0 && !(x & ((4 << tsv) - 1))) {
+                const unsigned pr = dbk_edge_decide(cur, __ldg(mp - (1 << ss)), tsv, s_lvl, plane, 0, x, mi_row, mi_col, SBLVL ? a.sb_lvl : nullptr,
+                                                    a.sb_cols, a.sb_shift);
+                if (pr & 3) {
+                    const int code = (pr & 3) - 1;
+                    s_list[0][code][atomicAdd(&s_cnt[0][code], 1)] = (uint16_t)(((pr >> 2) << 10) | ((ur - 1) << 5) | (uc - 2));
+                }
             }
-            if (pr & 3) {
-                const int code = (pr & 3) - 1;
-                s_list[pass][code][atomicAdd(&s_cnt[pass][code], 1)] = (uint16_t)(((pr >> 2) << 10) | (u << 5) | k);
+            if (ur >= 2 && uc <= 17 && y != 0 && !(y & ((4 << tsh) - 1))) {
+                const unsigned pr = dbk_edge_decide(cur, __ldg(mp - (1 << ss) * a.mi_stride), tsh, s_lvl, plane, 1, y, mi_row, mi_col,
+                                                    SBLVL ? a.sb_lvl : nullptr, a.sb_cols, a.sb_shift);
+                if (pr & 3) {
+                    const int code = (pr & 3) - 1;
+                    s_list[1][code][atomicAdd(&s_cnt[1][code], 1)] = (uint16_t)(((pr >> 2) << 10) | ((uc - 2) << 5) | (ur - 2));
+                }
             }
         }
         __syncthreads();
