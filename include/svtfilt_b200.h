@@ -314,6 +314,46 @@ typedef struct svtf_lf_search_cfg {
 } svtf_lf_search_cfg;
 int svtf_lf_search_frame(svtf_ctx *ctx, const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]);
 
+/* ---- loop-restoration filter search (the caller of the restoration filters) ----------------------
+ * restoration_seg_search + rest_finish_search (Encoder/Codec/EbRestorationPick.c:1471/1555) with the Wiener tools:
+ *   search_norestore_seg :1432 (SSE of the unfiltered unit), search_wiener_seg :1296 (svt_av1_compute_stats[_highbd]_c
+ *   :671/:708 -> wiener_decompose_sep_sym :906 / linsolve_wiener :766 -> finalize_sym_filter :977 -> compute_score :937 ->
+ *   finer_tile_search_wiener_seg :1042, every trial = try_restoration_unit_seg :129 = filter the unit + SSE), then
+ *   search_wiener_finish :1380 (count_wiener_bits :1008, RDCOST_DBL) and the per-plane frame decision (:1596-1624).
+ * The picture searched is the context's current picture (after CDEF / CCSO), the source the uploaded source picture.
+ * The search filters WITHOUT stripe boundaries (scs->use_boundaries_in_rest_search = 0, EbEncHandle.c:4162: rows
+ * above / below a stripe are the picture's own rows; the frame edge is replicated, svt_extend_frame).
+ * Not covered (returns SVTF_E_ARG when asked): the self-guided search (sg_enabled), use_prev_frame_coeffs. */
+typedef struct svtf_lr_search_cfg {
+    int32_t restoration_unit_size[3];   /* rst_info[p].restoration_unit_size                                      */
+    int32_t wn_enabled;                 /* cm->wn_filter_ctrls.enabled (Common/Codec/Av1Common.h:32-45)           */
+    int32_t wn_filter_tap_lvl;          /* 1: Y 7-tap, UV 5-tap; 2: 5 / 5; 3: 3 / 3                               */
+    int32_t wn_use_refinement;          /* refinement search around the solved taps                               */
+    int32_t wn_max_one_refinement_step; /* only the step of 4                                                     */
+    int32_t wn_use_chroma;              /* search U and V as well                                                 */
+    int32_t sg_enabled;                 /* must be 0 (self-guided search: not covered)                            */
+    int32_t rdmult;                     /* x->rdmult                                                              */
+    int32_t wiener_restore_cost[2];     /* x->wiener_restore_cost (bits << AV1_PROB_COST_SHIFT)                   */
+} svtf_lr_search_cfg;
+/* Per restoration unit, RestUnitSearchInfo (Common/Codec/EbRestoration.h:349): sse[0] = RESTORE_NONE, sse[1] = RESTORE_WIENER
+ * (INT64_MAX: no usable filter), the refined taps, and best_rtype[RESTORE_WIENER - 1]. */
+typedef struct svtf_lr_unit_search {
+    int64_t sse[2];
+    int16_t wiener_vfilter[8], wiener_hfilter[8];
+    int32_t best_rtype;
+} svtf_lr_unit_search;
+/* out_frame_type[p] = rst_info[p].frame_restoration_type; out_units[p] (vert_units x horz_units of svtf_lr_units) = the
+ * unit_info the reference leaves in rst_info[p] (ready for svtf_lr_apply_frame); out_search[p] may be NULL. */
+int svtf_lr_search_frame(svtf_ctx *ctx, const svtf_lr_search_cfg *cfg, int32_t out_frame_type[3], svtf_lr_unit *const out_units[3],
+                         svtf_lr_unit_search *const out_search[3]);
+/* svt_av1_compute_stats_c / _highbd_c (:671/:708) of every restoration unit of one plane of the current picture against
+ * the source: M[unit][win*win], H[unit][win*win][win*win] (int64, as the reference leaves them, bit-depth scaling and
+ * symmetric fill included).  wiener_win = 7, 5 or 3. */
+int svtf_lr_wiener_stats(svtf_ctx *ctx, int32_t plane, int32_t unit_size, int32_t wiener_win, int64_t *M, int64_t *H);
+/* The host half of search_wiener_seg for one unit, from its statistics: taps (InterpKernel layout, tap 7 = 0) or
+ * return 0 when the reference rejects the filter (decomposition failure or compute_score > 0); 1 = usable. */
+int svtf_lr_wiener_from_stats(int32_t wiener_win, const int64_t *M, const int64_t *H, int16_t vfilter[8], int16_t hfilter[8]);
+
 /* ccso_search / derive_ccso_filter (Encoder/Codec/EbPickccso.c:785, :464) for planes [plane_start, plane_end) on the
  * context's surfaces: classifier = the luma before the last CDEF pass (ext_rec_y), rec = the current picture (rec_uv),
  * org = the uploaded source (org_uv).  rdmult is the value derive_ccso_filter receives (ccso_search first multiplies

@@ -10,8 +10,8 @@
 #include <stdlib.h>
 #include <string.h>
 
-#define STUB(name)                                                   \
-    void name(void) {                                                \
+#define STUB(name) /* weak: a reference object that defines the symbol wins */ \
+    __attribute__((weak)) void name(void) {                                                \
         fprintf(stderr, "ref_stubs: unexpected call to " #name "\n"); \
         abort();                                                     \
     }
@@ -66,12 +66,10 @@ STUB(svt_av1_build_nmv_cost_table)
 STUB(svt_av1_get_intra_inter_context)
 STUB(svt_av1_get_mv_joint)
 STUB(svt_av1_superres_upscale_frame)
-STUB(svt_block_on_mutex)
 STUB(svt_get_empty_object)
 STUB(svt_get_full_object)
 STUB(svt_post_full_object)
 STUB(svt_print_alloc_fail_impl)
-STUB(svt_release_mutex)
 STUB(svt_release_object)
 STUB(svt_system_resource_get_consumer_fifo)
 STUB(svt_system_resource_get_producer_fifo)
@@ -113,3 +111,45 @@ void *svt_apply_selfguided_restoration       = (void *)svt_apply_selfguided_rest
 void *svt_av1_wiener_convolve_add_src        = (void *)svt_av1_wiener_convolve_add_src_c;
 void *svt_av1_highbd_wiener_convolve_add_src = (void *)svt_av1_highbd_wiener_convolve_add_src_c;
 void  svt_log(int level, const char *tag, const char *fmt, ...) { (void)level, (void)tag, (void)fmt; }
+
+/* loop-restoration search (Encoder/Codec/EbRestorationPick.c is part of ref_shim_lrs.c; EbEntropyCoding.c is compiled in
+ * for svt_aom_count_primitive_refsubexpfin, EbPsnr.c + C_DEFAULT/variance.c for the SSE of a unit) */
+void svt_block_on_mutex(void *m) { (void)m; } /* single-threaded harness */
+void svt_release_mutex(void *m) { (void)m; }
+void svt_av1_compute_stats_c();
+void svt_av1_compute_stats_highbd_c();
+void svt_av1_highbd_pixel_proj_error_c();
+void svt_av1_lowbd_pixel_proj_error_c();
+void svt_av1_selfguided_restoration_c();
+void svt_get_proj_subspace_c();
+void svt_aom_highbd_8_mse16x16_c();
+void svt_aom_mse16x16_c();
+void *svt_av1_compute_stats          = (void *)svt_av1_compute_stats_c;
+void *svt_av1_compute_stats_highbd   = (void *)svt_av1_compute_stats_highbd_c;
+void *svt_av1_highbd_pixel_proj_error = (void *)svt_av1_highbd_pixel_proj_error_c;
+void *svt_av1_lowbd_pixel_proj_error = (void *)svt_av1_lowbd_pixel_proj_error_c;
+void *svt_av1_selfguided_restoration = (void *)svt_av1_selfguided_restoration_c;
+void *svt_get_proj_subspace          = (void *)svt_get_proj_subspace_c;
+void *svt_aom_highbd_8_mse16x16      = (void *)svt_aom_highbd_8_mse16x16_c;
+void *svt_aom_mse16x16               = (void *)svt_aom_mse16x16_c;
+STUB(get_mbmi)
+STUB(svt_aom_daala_stop_encode)
+STUB(svt_aom_film_grain_params_equal)
+STUB(svt_aom_get_block_dimensions)
+STUB(svt_aom_get_relative_dist_enc)
+STUB(svt_aom_init_mode_probs)
+STUB(svt_aom_neighbor_array_unit_mode_write)
+STUB(svt_aom_output_bitstream_reset)
+STUB(svt_aom_output_bitstream_unit_ctor)
+STUB(svt_aom_segmentation_feature_bits)
+STUB(svt_aom_segmentation_feature_signed)
+STUB(svt_av1_allow_palette)
+STUB(svt_av1_default_coef_probs)
+STUB(svt_av1_get_nz_map_contexts)
+STUB(svt_av1_index_color_cache)
+STUB(svt_av1_tokenize_color_map)
+STUB(svt_av1_txb_init_levels)
+STUB(svt_get_palette_cache_y)
+STUB(svt_od_ec_encode_bool_q15)
+STUB(svt_od_ec_encode_cdf_q15)
+STUB(svt_realloc_output_bitstream_unit)

@@ -62,6 +62,8 @@ static int px(const void *p, int st, int sb, int x, int y) {
 /* stripe input at (x, r), r in [y0 - 3, y1 + 3) */
 static int stripe_px(const stripe_in *s, int x, int r) {
     const int xc = IMIN(IMAX(x, 0), s->pw - 1);
+    if (s->opt == 2) /* the encoder's search: no stripe boundaries (need_bounadaries = 0, EbRestoration.c:1112) */
+        return px(s->cur, s->cur_st, s->sb, xc, IMIN(IMAX(r, 0), s->ph - 1));
     if (r < s->y0) {
         if (!s->above)
             return px(s->cur, s->cur_st, s->sb, xc, IMAX(r, 0));
@@ -200,6 +202,32 @@ ORC_API int orc_lr_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb,
         free(out);
     }
     return 0;
+}
+
+/* try_restoration_unit_seg (Encoder/Codec/EbRestorationPick.c:129): the unit [h0, h1) x [v0, v1) of one plane filtered with
+ * *u WITHOUT stripe boundaries, squared error against the source (sse_restoration_unit :56).  Used by svtf_oracle_lrs.c. */
+int64_t orc_lr_try_unit(const void *cur, int cst, const void *src, int sst, int sb, int bd, int ss, int pw, int ph, int h0, int h1, int v0,
+                        int v1, const svtf_lr_unit *u) {
+    const int sh = 64 >> ss, off = 8 >> ss;
+    int64_t   sse = 0;
+    for (int k = 0;; k++) {
+        stripe_in s = {cur, cur, cst, cst, sb, pw, ph, IMAX(0, k * sh - off), IMIN((k + 1) * sh - off, ph), k > 0, 0, 2};
+        if (s.y0 >= ph)
+            break;
+        for (int yy = IMAX(s.y0, v0); yy < IMIN(s.y1, v1); yy++)
+            for (int xx = h0; xx < h1; xx++) {
+                int v;
+                if (u->restoration_type == SVTF_RESTORE_WIENER)
+                    v = wiener_px(&s, u, bd, xx, yy);
+                else if (u->restoration_type == SVTF_RESTORE_SGRPROJ)
+                    v = sgr_px(&s, u, bd, xx, yy);
+                else
+                    v = px(cur, cst, sb, xx, yy);
+                const int64_t d = v - px(src, sst, sb, xx, yy);
+                sse += d * d;
+            }
+    }
+    return sse;
 }
 
 /* the table value, for the test that compares it with the reference's svt_aom_eb_x_by_xplus1 */

@@ -64,6 +64,18 @@ class LrParams(C.Structure):
     _fields_ = [("frame_restoration_type", C.c_int32 * 3), ("restoration_unit_size", C.c_int32 * 3), ("optimized_lr", C.c_int32)]
 
 
+class LrSearchCfg(C.Structure):
+    """svtf_lr_search_cfg (WnFilterCtrls, Common/Codec/Av1Common.h:32-45; Macroblock.rdmult / wiener_restore_cost)"""
+    _fields_ = [("restoration_unit_size", C.c_int32 * 3), ("wn_enabled", C.c_int32), ("wn_filter_tap_lvl", C.c_int32),
+                ("wn_use_refinement", C.c_int32), ("wn_max_one_refinement_step", C.c_int32), ("wn_use_chroma", C.c_int32),
+                ("sg_enabled", C.c_int32), ("rdmult", C.c_int32), ("wiener_restore_cost", C.c_int32 * 2)]
+
+
+class LrUnitSearch(C.Structure):
+    """svtf_lr_unit_search (RestUnitSearchInfo, Common/Codec/EbRestoration.h:349)"""
+    _fields_ = [("sse", C.c_int64 * 2), ("wiener_vfilter", C.c_int16 * 8), ("wiener_hfilter", C.c_int16 * 8), ("best_rtype", C.c_int32)]
+
+
 class LfSearchCfg(C.Structure):
     _fields_ = [("dlf_avg", C.c_int32), ("early_exit_convergence", C.c_int32), ("only_4x4", C.c_int32), ("search_chroma", C.c_int32)]
 

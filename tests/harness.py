@@ -277,6 +277,69 @@ def _lr_call(fn, geom, cur, dbk, lr, units):
     return out
 
 
+def lr_search_cfg(unit_size=(64, 32, 32), tap_lvl=1, refinement=1, one_step=0, chroma=1, rdmult=9000, cost=(120, 900)):
+    """WnFilterCtrls of a Wiener-only search (Encoder/Codec/EncModeConfig.c set_wn_filter_ctrls) + the rate inputs."""
+    c = L.LrSearchCfg()
+    for p in range(3):
+        c.restoration_unit_size[p] = unit_size[p]
+    c.wn_enabled, c.wn_filter_tap_lvl, c.wn_use_refinement, c.wn_max_one_refinement_step, c.wn_use_chroma = 1, tap_lvl, refinement, one_step, chroma
+    c.sg_enabled, c.rdmult = 0, rdmult
+    c.wiener_restore_cost[0], c.wiener_restore_cost[1] = cost
+    return c
+
+
+def lr_search_sig(geom, cfg, ftype, units, search):
+    """Comparable form of a search result: frame types, per-unit (type, taps), per-unit (sse none, sse wiener, refined taps)."""
+    sig = []
+    for p in range(3):
+        hu, vu = lr_units_of(geom, p, cfg.restoration_unit_size[p])
+        us = [(u.restoration_type, tuple(u.wiener_vfilter), tuple(u.wiener_hfilter)) for u in units[p][: hu * vu]]
+        ss = [(s.sse[0], s.sse[1], tuple(s.wiener_vfilter), tuple(s.wiener_hfilter)) for s in search[p][: hu * vu]]
+        sig.append((ftype[p], us, ss))
+    return sig
+
+
+def _lr_search_call(fn, geom, cur, src, cfg):
+    cur = [np.ascontiguousarray(p) for p in cur]
+    src = [np.ascontiguousarray(p) for p in src]
+    ftype = (C.c_int32 * 3)()
+    units, search = [], []
+    for p in range(3):
+        hu, vu = lr_units_of(geom, p, cfg.restoration_unit_size[p])
+        units.append((L.LrUnit * (hu * vu))())
+        search.append((L.LrUnitSearch * (hu * vu))())
+    up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
+    sp = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in search])
+    assert fn(C.byref(geom), *_planes(cur), *_planes(src), C.byref(cfg), ftype, up, sp) == 0
+    return lr_search_sig(geom, cfg, ftype, units, search)
+
+
+def lr_unit_limits(geom, plane, unit_size):
+    """[h0, h1, v0, v1] of every restoration unit of a plane, raster order (foreach_rest_unit_in_tile, EbRestoration.c:1250)."""
+    ss = 1 if plane else 0
+    pw, ph, off = (geom.width + ss) >> ss, (geom.height + ss) >> ss, 8 >> ss
+    hu, vu = lr_units_of(geom, plane, unit_size)
+    return [(uc * unit_size, pw if uc == hu - 1 else (uc + 1) * unit_size, max(0, ur * unit_size - off),
+             ph if ur == vu - 1 else (ur + 1) * unit_size - off) for ur in range(vu) for uc in range(hu)]
+
+
+def _wiener_stats_call(fn, geom, plane, dgd, src, lim, win):
+    ss = 1 if plane else 0
+    pw, ph = (geom.width + ss) >> ss, (geom.height + ss) >> ss
+    M, Hm = np.zeros(win * win, np.int64), np.zeros((win * win, win * win), np.int64)
+    dgd, src = np.ascontiguousarray(dgd), np.ascontiguousarray(src)
+    fn(_p(dgd), dgd.strides[0] // dgd.itemsize, _p(src), src.strides[0] // src.itemsize, geom.sample_bytes, geom.bit_depth, pw, ph,
+       *[int(v) for v in lim], win, _p(M), _p(Hm))
+    return M, Hm
+
+
+def _wiener_from_stats_call(fn, win, M, Hm):
+    vf, hf = (C.c_int16 * 8)(), (C.c_int16 * 8)()
+    M, Hm = np.ascontiguousarray(M), np.ascontiguousarray(Hm)
+    ok = fn(win, _p(M), _p(Hm), vf, hf)
+    return ok, tuple(vf), tuple(hf)
+
+
 def cdef_level1_lists():
     """cdef_level 1 (exhaustive, presets <= M0): 16 primary {0,4,..,60} then 48 secondary pri+{1,2,3}
     (Encoder/Codec/EncModeConfig.c:871-910)."""
@@ -359,6 +422,16 @@ class Oracle:
 
     def lr_apply(self, geom, cur, dbk, lr, units):
         return _lr_call(self.lib.orc_lr_frame, geom, cur, dbk, lr, units)
+
+    def lr_search(self, geom, cur, src, cfg):
+        return _lr_search_call(self.lib.orc_lr_search_frame, geom, cur, src, cfg)
+
+    def wiener_stats(self, geom, plane, dgd, src, lim, win):
+        self.lib.orc_lr_wiener_stats.restype = None
+        return _wiener_stats_call(self.lib.orc_lr_wiener_stats, geom, plane, dgd, src, lim, win)
+
+    def wiener_from_stats(self, win, M, Hm):
+        return _wiener_from_stats_call(self.lib.orc_lr_wiener_from_stats, win, M, Hm)
 
     def lf_search(self, geom, rec, src, mi, lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
         rec = [p.copy() for p in rec]
@@ -467,6 +540,15 @@ class Ref:
 
     def lr_apply(self, geom, cur, dbk, lr, units):
         return _lr_call(self.lib.ref_lr_frame, geom, cur, dbk, lr, units)
+
+    def lr_search(self, geom, cur, src, cfg):
+        return _lr_search_call(self.lib.ref_lr_search, geom, cur, src, cfg)
+
+    def wiener_stats(self, geom, plane, dgd, src, lim, win):
+        return _wiener_stats_call(self.lib.ref_lr_wiener_stats, geom, plane, dgd, src, lim, win)
+
+    def wiener_from_stats(self, win, M, Hm):
+        return _wiener_from_stats_call(self.lib.ref_lr_wiener_from_stats, win, M, Hm)
 
     def lf_search(self, geom, rec, src, soa, lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
         rec = [p.copy() for p in rec]
