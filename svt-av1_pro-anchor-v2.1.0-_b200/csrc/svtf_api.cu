@@ -23,6 +23,7 @@
 #include "svtf_search3.cuh"
 #include "svtf_mi_pack.cuh"
 #include "svtf_lr.cuh"
+#include "svtf_lrs.cuh"
 #include "svtf_handoff.cuh"
 
 namespace svtf {
@@ -110,6 +111,8 @@ struct svtf_ctx {
     size_t       sb_lvl_cap = 0;
     void        *derive_scratch = nullptr; // CCSO derivation buffers (DeriveScratch), created on first use
     uint64_t     launches = 0;
+    uint8_t     *d_lrs = nullptr;          // scratch of the loop-restoration filter search (svtf_lr_search_frame), allocated on first use
+    size_t       lrs_cap = 0;
     uint8_t     *d_handoff = nullptr;      // staging of svtf_download_ref_padded / svtf_upload_frame_8as16, allocated on first use
     size_t       handoff_cap = 0;
     bool         search3_ready = false;    // same for cdef_search3_kernel
@@ -232,7 +235,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
-    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff);
+    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff), cudaFree(c->d_lrs);
     if (c->h_mi_bad)
         cudaFreeHost(c->h_mi_bad);
     if (c->own_stream)
@@ -1685,6 +1688,309 @@ extern "C" int svtf_lr_apply_frame(svtf_ctx *c, const svtf_lr_params *lr, const 
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
     c->cur = 3;
+    return SVTF_OK;
+}
+
+// ---- loop-restoration filter search, Wiener tools (svtf_lrs.cuh, svtf_lrs_host.cpp) -----------------------------------
+namespace {
+struct LrsPlane { // one searched plane
+    int plane, win, unit, hu, vu, first; // first: index of its unit 0 in the per-call unit arrays
+};
+struct LrsPlan {
+    std::vector<LrsPlane>           planes;
+    std::vector<LrsTile>            tiles;
+    std::vector<int>                count;   // samples per unit
+    std::vector<unsigned long long> acc_off; // offset of each unit's statistics accumulators
+    size_t                          acc_total = 0;
+    int                             units = 0;
+    // device carve-up
+    size_t o_tiles = 0, o_sum = 0, o_sse = 0, o_count = 0, o_off = 0, o_acc = 0, o_trial = 0, o_units = 0, bytes = 0;
+};
+
+// Units of a plane (foreach_rest_unit_in_tile, Common/Codec/EbRestoration.c:1250): raster order, the last one of a row /
+// column takes the remainder, rows shifted up by 8 luma samples.
+void lrs_unit_rect(const svtf_geom &g, const LrsPlane &pl, int u, int lim[4]) {
+    const int ss = pl.plane ? 1 : 0, pw = (g.width + ss) >> ss, ph = (g.height + ss) >> ss, off = 8 >> ss;
+    const int ur = u / pl.hu, uc = u - ur * pl.hu;
+    lim[0] = uc * pl.unit, lim[1] = uc == pl.hu - 1 ? pw : (uc + 1) * pl.unit;
+    lim[2] = std::max(0, ur * pl.unit - off), lim[3] = ur == pl.vu - 1 ? ph : (ur + 1) * pl.unit - off;
+}
+
+void lrs_add_plane(const svtf_geom &g, LrsPlan &plan, int plane, int unit_size, int win) {
+    LrsPlane pl{plane, win, unit_size, 0, 0, plan.units};
+    svtf_lr_units(&g, plane, unit_size, &pl.hu, &pl.vu);
+    for (int u = 0; u < pl.hu * pl.vu; u++) {
+        int lim[4];
+        lrs_unit_rect(g, pl, u, lim);
+        plan.count.push_back((lim[1] - lim[0]) * (lim[3] - lim[2]));
+        plan.acc_off.push_back(plan.acc_total);
+        plan.acc_total += (size_t)win * win * win * win + win * win;
+        for (int y = lim[2]; y < lim[3]; y += LRS_T)
+            for (int x = lim[0]; x < lim[1]; x += LRS_T)
+                plan.tiles.push_back(LrsTile{(int16_t)x, (int16_t)y, (int16_t)std::min(LRS_T, lim[1] - x), (int16_t)std::min(LRS_T, lim[3] - y),
+                                             plan.units + u, plane});
+    }
+    plan.units += pl.hu * pl.vu;
+    plan.planes.push_back(pl);
+}
+
+int lrs_reserve(svtf_ctx *c, LrsPlan &plan) {
+    auto carve = [&](size_t &o, size_t n) { o = plan.bytes, plan.bytes += (n + 255) & ~size_t(255); };
+    carve(plan.o_tiles, sizeof(LrsTile) * plan.tiles.size());
+    carve(plan.o_sum, 8 * (size_t)plan.units), carve(plan.o_sse, 8 * (size_t)plan.units), carve(plan.o_trial, 8 * (size_t)plan.units);
+    carve(plan.o_count, 4 * (size_t)plan.units), carve(plan.o_off, 8 * (size_t)plan.units);
+    carve(plan.o_units, sizeof(LrUnitDev) * (size_t)plan.units);
+    carve(plan.o_acc, 8 * plan.acc_total);
+    if (plan.bytes > c->lrs_cap) {
+        if (c->d_lrs) {
+            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            CUDA_TRY(c, cudaFree(c->d_lrs));
+            c->d_lrs = nullptr, c->lrs_cap = 0;
+        }
+        CUDA_TRY(c, cudaMalloc(&c->d_lrs, plan.bytes));
+        c->lrs_cap = plan.bytes;
+    }
+    return SVTF_OK;
+}
+
+// Uploads the plan, runs the per-unit sums (and, with stats, the Wiener statistics) and brings the results to the host.
+int lrs_measure(svtf_ctx *c, LrsPlan &plan, bool stats, std::vector<unsigned long long> &sse_none, std::vector<long long> &acc) {
+    if (int r = lrs_reserve(c, plan))
+        return r;
+    uint8_t *d = c->d_lrs;
+    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_tiles, plan.tiles.data(), sizeof(LrsTile) * plan.tiles.size(), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_count, plan.count.data(), 4 * (size_t)plan.units, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_off, plan.acc_off.data(), 8 * (size_t)plan.units, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemsetAsync(d + plan.o_sum, 0, plan.o_count - plan.o_sum, c->stream)); // sum, sse, trial
+    LrsArgs a;
+    a.cur = c->surf[c->cur].planes(), a.src = c->source.planes();
+    for (int p = 0; p < 3; p++) a.pw[p] = (c->geom.width + (p ? 1 : 0)) >> (p ? 1 : 0), a.ph[p] = (c->geom.height + (p ? 1 : 0)) >> (p ? 1 : 0);
+    a.tiles      = reinterpret_cast<const LrsTile *>(d + plan.o_tiles);
+    a.unit_sum   = reinterpret_cast<unsigned long long *>(d + plan.o_sum);
+    a.unit_sse   = reinterpret_cast<unsigned long long *>(d + plan.o_sse);
+    a.unit_count = reinterpret_cast<const int *>(d + plan.o_count);
+    a.acc        = reinterpret_cast<long long *>(d + plan.o_acc);
+    a.acc_off    = reinterpret_cast<const unsigned long long *>(d + plan.o_off);
+    a.bd         = c->geom.bit_depth;
+    const int  nt = (int)plan.tiles.size();
+    const bool b8 = c->geom.sample_bytes == 1;
+    if (b8)
+        lrs_sums_kernel<uint8_t><<<nt, LRS_THREADS, 0, c->stream>>>(a);
+    else
+        lrs_sums_kernel<uint16_t><<<nt, LRS_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    if (stats) {
+        CUDA_TRY(c, cudaMemsetAsync(d + plan.o_acc, 0, 8 * plan.acc_total, c->stream));
+        // tiles are grouped by plane: one launch per plane with that plane's window
+        int t0 = 0;
+        for (const LrsPlane &pl : plan.planes) {
+            int t1 = t0;
+            while (t1 < nt && plan.tiles[t1].plane == pl.plane) t1++;
+            LrsArgs b = a;
+            b.tiles   = a.tiles + t0;
+            const int n = t1 - t0;
+#define LRS_LAUNCH(T, W) lrs_stats_kernel<T, W><<<n, LRS_THREADS, 0, c->stream>>>(b)
+            if (pl.win == 7)
+                b8 ? LRS_LAUNCH(uint8_t, 7) : LRS_LAUNCH(uint16_t, 7);
+            else if (pl.win == 5)
+                b8 ? LRS_LAUNCH(uint8_t, 5) : LRS_LAUNCH(uint16_t, 5);
+            else
+                b8 ? LRS_LAUNCH(uint8_t, 3) : LRS_LAUNCH(uint16_t, 3);
+#undef LRS_LAUNCH
+            CUDA_TRY(c, cudaGetLastError());
+            c->launches++;
+            t0 = t1;
+        }
+        acc.resize(plan.acc_total);
+        CUDA_TRY(c, cudaMemcpyAsync(acc.data(), d + plan.o_acc, 8 * plan.acc_total, cudaMemcpyDeviceToHost, c->stream));
+    }
+    sse_none.resize(plan.units);
+    CUDA_TRY(c, cudaMemcpyAsync(sse_none.data(), d + plan.o_sse, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return SVTF_OK;
+}
+
+// The reference's M / H of one unit from the raw accumulators: bit-depth divider (high-bitdepth path only), H mirrored.
+void lrs_finish_stats(const svtf_geom &g, int win, const long long *raw, int64_t *M, int64_t *H) {
+    const int win2 = win * win, div = g.sample_bytes == 1 ? 1 : (g.bit_depth == 12 ? 16 : (g.bit_depth == 10 ? 4 : 1));
+    for (int k = 0; k < win2; k++) {
+        M[k] = raw[win2 * win2 + k] / div;
+        for (int l = k; l < win2; l++) H[k * win2 + l] = H[l * win2 + k] = raw[k * win2 + l] / div;
+    }
+}
+
+int lrs_check(svtf_ctx *c, const char *fn) {
+    if (!c->have_frame || !c->have_source)
+        return c->fail(SVTF_E_STATE, std::string(fn) + ": upload a picture and a source first");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, std::string(fn) + ": not available on a striped context");
+    return SVTF_OK;
+}
+bool lrs_unit_size_ok(int plane, int us) { return (us == 64 || us == 128 || us == 256 || (plane && us == 32)); }
+} // namespace
+
+extern "C" int svtf_lr_wiener_stats(svtf_ctx *c, int32_t plane, int32_t unit_size, int32_t wiener_win, int64_t *M, int64_t *H) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_lr_wiener_stats: NULL context");
+    if (plane < 0 || plane > 2 || !lrs_unit_size_ok(plane, unit_size) || (wiener_win != 7 && wiener_win != 5 && wiener_win != 3) || !M || !H)
+        return c->fail(SVTF_E_ARG, "svtf_lr_wiener_stats: bad argument");
+    if (int r = lrs_check(c, "svtf_lr_wiener_stats"))
+        return r;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    LrsPlan plan;
+    lrs_add_plane(c->geom, plan, plane, unit_size, wiener_win);
+    std::vector<unsigned long long> sse;
+    std::vector<long long>          acc;
+    if (int r = lrs_measure(c, plan, true, sse, acc))
+        return r;
+    const int win2 = wiener_win * wiener_win;
+    for (int u = 0; u < plan.units; u++) lrs_finish_stats(c->geom, wiener_win, acc.data() + plan.acc_off[u], M + (size_t)u * win2, H + (size_t)u * win2 * win2);
+    return SVTF_OK;
+}
+
+extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, int32_t out_frame_type[3], svtf_lr_unit *const out_units[3],
+                                    svtf_lr_unit_search *const out_search[3]) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_lr_search_frame: NULL context");
+    if (!cfg || !out_frame_type || !out_units)
+        return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: NULL argument");
+    if (cfg->sg_enabled)
+        return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: the self-guided search is not covered");
+    if (cfg->wn_enabled && (cfg->wn_filter_tap_lvl < 1 || cfg->wn_filter_tap_lvl > 3))
+        return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: wn_filter_tap_lvl must be 1..3");
+    if (int r = lrs_check(c, "svtf_lr_search_frame"))
+        return r;
+    const int nplanes = cfg->wn_enabled && cfg->wn_use_chroma ? 3 : 1;
+    const int wn_luma = cfg->wn_filter_tap_lvl == 1 ? 7 : (cfg->wn_filter_tap_lvl == 2 ? 5 : 3);
+    for (int p = 0; p < 3; p++) {
+        if (!lrs_unit_size_ok(p, cfg->restoration_unit_size[p]) || !out_units[p])
+            return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: bad restoration unit size or NULL unit array");
+        int hu, vu;
+        svtf_lr_units(&c->geom, p, cfg->restoration_unit_size[p], &hu, &vu);
+        out_frame_type[p] = SVTF_RESTORE_NONE;
+        std::memset(out_units[p], 0, sizeof(svtf_lr_unit) * hu * vu);
+    }
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    LrsPlan plan;
+    for (int p = 0; p < nplanes; p++) lrs_add_plane(c->geom, plan, p, cfg->restoration_unit_size[p], p ? std::min(wn_luma, 5) : wn_luma);
+    std::vector<unsigned long long> sse_none;
+    std::vector<long long>          acc;
+    if (int r = lrs_measure(c, plan, cfg->wn_enabled != 0, sse_none, acc))
+        return r;
+    std::vector<svtf_lr_unit_search> us(plan.units);
+    std::vector<LrsRefine>           ref(plan.units);
+    for (const LrsPlane &pl : plan.planes)
+        for (int u = 0; u < pl.hu * pl.vu; u++) {
+            svtf_lr_unit_search &s = us[pl.first + u];
+            std::memset(&s, 0, sizeof(s));
+            s.sse[0] = (int64_t)sse_none[pl.first + u], s.sse[1] = INT64_MAX;
+            if (!cfg->wn_enabled)
+                continue;
+            int64_t M[49], H[49 * 49];
+            lrs_finish_stats(c->geom, pl.win, acc.data() + plan.acc_off[pl.first + u], M, H);
+            int16_t vf[8], hf[8];
+            if (svtf_lr_wiener_from_stats(pl.win, M, H, vf, hf) == 1)
+                ref[pl.first + u].start(pl.win, cfg->wn_use_refinement != 0, cfg->wn_max_one_refinement_step != 0, vf, hf);
+        }
+    // ---- refinement in lock-step: one launch filters every unit that has a trial pending and measures it ----
+    if (cfg->wn_enabled) {
+        uint8_t *d = c->d_lrs;
+        LrArgs   a;
+        a.cur = a.dbk = c->surf[c->cur].planes();
+        a.out = a.cur; // never written by the SSE instantiation
+        a.src = c->source.planes();
+        int grid = 0;
+        for (int p = 0; p < 3; p++) {
+            const int ss = p ? 1 : 0;
+            a.pw[p] = (c->geom.width + ss) >> ss, a.ph[p] = (c->geom.height + ss) >> ss;
+            a.cw[p] = a.pw[p], a.chh[p] = a.ph[p]; // only the visible picture is measured
+            a.unit[p] = 0, a.hu[p] = a.vu[p] = 0, a.units[p] = nullptr, a.sse[p] = nullptr;
+            a.frame_type[p] = SVTF_RESTORE_NONE, a.chunks[p] = a.stripes[p] = 0, a.base[p] = grid;
+        }
+        for (const LrsPlane &pl : plan.planes) {
+            const int p = pl.plane, ss = p ? 1 : 0, sh = 64 >> ss, off = 8 >> ss;
+            a.unit[p] = pl.unit, a.hu[p] = pl.hu, a.vu[p] = pl.vu;
+            a.units[p]      = reinterpret_cast<const LrUnitDev *>(d + plan.o_units) + pl.first;
+            a.sse[p]        = reinterpret_cast<unsigned long long *>(d + plan.o_trial) + pl.first;
+            a.frame_type[p] = SVTF_RESTORE_WIENER;
+            a.chunks[p]     = (a.cw[p] + (LR_MAXW >> ss) - 1) / (LR_MAXW >> ss);
+            a.stripes[p]    = (a.ph[p] + off + sh - 1) / sh + 1;
+        }
+        for (int p = 0; p < 3; p++) a.base[p] = grid, grid += a.chunks[p] * a.stripes[p];
+        a.opt = 2, a.bd = c->geom.bit_depth;
+        std::vector<LrUnitDev>          host(plan.units);
+        std::vector<unsigned long long> trial(plan.units);
+        for (;;) {
+            int pending = 0;
+            for (int u = 0; u < plan.units; u++) {
+                LrUnitDev &h = host[u];
+                std::memset(&h, 0, sizeof(h));
+                if (!ref[u].pending())
+                    continue;
+                pending++;
+                h.type = SVTF_RESTORE_WIENER;
+                for (int t = 0; t < 8; t++) h.vf[t] = ref[u].vf[t], h.hf[t] = ref[u].hf[t];
+            }
+            if (!pending)
+                break;
+            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host.data(), sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
+            CUDA_TRY(c, cudaMemsetAsync(d + plan.o_trial, 0, 8 * (size_t)plan.units, c->stream));
+            if (c->geom.sample_bytes == 1)
+                lr_kernel<uint8_t, true><<<grid, LR_THREADS, 0, c->stream>>>(a);
+            else
+                lr_kernel<uint16_t, true><<<grid, LR_THREADS, 0, c->stream>>>(a);
+            CUDA_TRY(c, cudaGetLastError());
+            c->launches++;
+            CUDA_TRY(c, cudaMemcpyAsync(trial.data(), d + plan.o_trial, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            for (int u = 0; u < plan.units; u++)
+                if (ref[u].pending())
+                    ref[u].feed((int64_t)trial[u]);
+        }
+    }
+    // ---- search_wiener_finish :1380 per unit in raster order, then the frame decision (rest_finish_search :1596-1624) ----
+    for (const LrsPlane &pl : plan.planes) {
+        const int n = pl.hu * pl.vu;
+        int64_t   sse_n = 0, sse_w = 0, bits_w = 0;
+        int16_t   rvf[8] = {3, -7, 15, -22, 15, -7, 3, 0}, rhf[8] = {3, -7, 15, -22, 15, -7, 3, 0}; // set_default_wiener
+        for (int u = 0; u < n; u++) sse_n += us[pl.first + u].sse[0];
+        if (cfg->wn_enabled) {
+            for (int u = 0; u < n; u++) {
+                svtf_lr_unit_search &s = us[pl.first + u];
+                const LrsRefine     &r = ref[pl.first + u];
+                const int64_t bits_none = cfg->wiener_restore_cost[0];
+                s.best_rtype            = SVTF_RESTORE_NONE;
+                if (!r.started) { // no usable filter: the unit stays unrestored under RESTORE_WIENER
+                    bits_w += bits_none, sse_w += s.sse[0];
+                    continue;
+                }
+                s.sse[1] = r.err;
+                std::memcpy(s.wiener_vfilter, r.vf, 16), std::memcpy(s.wiener_hfilter, r.hf, 16);
+                const int64_t bits_wn = cfg->wiener_restore_cost[1] + ((int64_t)lrs_wiener_bits(pl.win, r.vf, r.hf, rvf, rhf) << 9);
+                const double  cn = lrs_rdcost(cfg->rdmult, bits_none >> 4, s.sse[0]), cw = lrs_rdcost(cfg->rdmult, bits_wn >> 4, s.sse[1]);
+                if (cw < cn) {
+                    s.best_rtype = SVTF_RESTORE_WIENER;
+                    sse_w += s.sse[1], bits_w += bits_wn;
+                    std::memcpy(rvf, r.vf, 16), std::memcpy(rhf, r.hf, 16);
+                } else
+                    sse_w += s.sse[0], bits_w += bits_none;
+            }
+            if (lrs_rdcost(cfg->rdmult, bits_w >> 4, sse_w) < lrs_rdcost(cfg->rdmult, 0, sse_n)) {
+                out_frame_type[pl.plane] = SVTF_RESTORE_WIENER;
+                for (int u = 0; u < n; u++) { // copy_unit_info :1202
+                    const svtf_lr_unit_search &s = us[pl.first + u];
+                    out_units[pl.plane][u].restoration_type = s.best_rtype;
+                    if (s.best_rtype == SVTF_RESTORE_WIENER) {
+                        std::memcpy(out_units[pl.plane][u].wiener_vfilter, s.wiener_vfilter, 16);
+                        std::memcpy(out_units[pl.plane][u].wiener_hfilter, s.wiener_hfilter, 16);
+                    }
+                }
+            }
+        }
+        if (out_search && out_search[pl.plane])
+            std::memcpy(out_search[pl.plane], us.data() + pl.first, sizeof(svtf_lr_unit_search) * n);
+    }
     return SVTF_OK;
 }
 

@@ -13,6 +13,27 @@ struct LfTables {
 
 void build_lf_tables(const svtf_lf_params &lf, LfTables &t);
 
+// ---- loop-restoration filter search, host half (svtf_lrs_host.cpp) ----
+// finer_tile_search_wiener_seg (Encoder/Codec/EbRestorationPick.c:1042) as a resumable state machine: while pending(), filter
+// the unit with vf / hf, measure the squared error and feed() it; afterwards vf / hf / err hold the refined result.
+struct LrsRefine {
+    int16_t vf[8], hf[8];
+    int64_t err = 0;
+    bool    started = false;
+    void    start(int win, bool use_refinement, bool one_step, const int16_t *v, const int16_t *h);
+    void    feed(int64_t e);
+    bool    pending() const { return waiting; }
+
+  private:
+    int  win = 7, phase = 2, step = 4, dir = 0, tap = 0, sign = -1;
+    bool refine = false, one_step = false, moved_down = false, waiting = false;
+    bool propose();
+    void next_slot(bool went_down);
+    void advance();
+};
+int    lrs_wiener_bits(int win, const int16_t *vf, const int16_t *hf, const int16_t *ref_vf, const int16_t *ref_hf); // count_wiener_bits :1008
+double lrs_rdcost(int rdmult, int64_t rate, int64_t dist);                                                          // RDCOST_DBL
+
 // Records the message for svtf_last_error(NULL) and returns `code`.
 int set_global_error(int code, const char *msg);
 

@@ -35,8 +35,12 @@ struct LrArgs {
     int              unit[3], hu[3], vu[3];
     const LrUnitDev *units[3];
     int              frame_type[3];
-    int              opt, bd;
+    int              opt, bd;                        // opt 2: no stripe boundaries (the encoder's filter search)
     int              chunks[3], stripes[3], base[3]; // linearised (plane, stripe, chunk) grid
+    // SSE instantiation (try_restoration_unit_seg, Encoder/Codec/EbRestorationPick.c:129): nothing is written; the squared
+    // error of the filtered samples against `src` is added to sse[plane][unit].  Units of type NONE are skipped.
+    Planes              src;
+    unsigned long long *sse[3];
 };
 
 // svt_aom_eb_sgr_params (EbRestoration.c:85-103)
@@ -93,7 +97,7 @@ __device__ __forceinline__ void lr_sgr_ab_seg(const uint16_t *in, const uint16_t
     }
 }
 
-template <typename T>
+template <typename T, bool SSE = false>
 __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ LrArgs a) {
     __shared__ __align__(16) uint16_t s_in[LR_IN_ROWS * LR_IN_P];
     __shared__ __align__(16) unsigned char s_buf[66 * 66 * 6]; // Wiener: horizontal pass (u16 [70][TW]); SGR: A (u16) and B (u32)
@@ -119,14 +123,21 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     if (h <= 0 || w <= 0)
         return;
     const bool filt = !beyond && a.frame_type[plane] != SVTF_RESTORE_NONE && x0 < pw;
-    int        type = SVTF_RESTORE_NONE;
+    int        type = SVTF_RESTORE_NONE, unit_idx = 0;
+    __shared__ unsigned long long s_sse;
     if (filt) {
         const int U = a.unit[plane];
+        unit_idx    = min((y0 + off) / U, a.vu[plane] - 1) * a.hu[plane] + min(x0 / U, a.hu[plane] - 1);
         if (tid == 0)
-            s_unit = a.units[plane][min((y0 + off) / U, a.vu[plane] - 1) * a.hu[plane] + min(x0 / U, a.hu[plane] - 1)];
+            s_unit = a.units[plane][unit_idx], s_sse = 0;
         __syncthreads();
         type = s_unit.type;
     }
+    if (SSE && type == SVTF_RESTORE_NONE)
+        return;
+    const T  *srcp = SSE ? static_cast<const T *>(a.src.p[plane]) : nullptr;
+    const int sp   = SSE ? a.src.pitch[plane] : 0;
+    unsigned long long my_sse = 0;
     if (type == SVTF_RESTORE_NONE) { // copy (also: planes without restoration, coded samples outside the visible picture)
         // coded widths are multiples of 4 (chroma) / 8 (luma) and x0 of 32: 4-sample vectors
         for (int i = tid; i < h * (TW / 4); i += LR_THREADS) {
@@ -146,7 +157,9 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
             const int rr = ss ? i / 6 : i / 10, j = i - rr * nch;
             const int r  = y0 - 3 + rr;
             const T  *src;
-            if (r < y0) {
+            if (a.opt == 2)
+                src = cur + (size_t)min(max(r, 0), ph - 1) * cp;
+            else if (r < y0) {
                 if (!above)
                     src = cur + (size_t)max(r, 0) * cp;
                 else if (a.opt)
@@ -222,11 +235,25 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
                     int sum = (x[j + 3] << 7) - (1 << (bd + r1 - 1));
 #pragma unroll
                     for (int t = 0; t < 7; t++) sum += x[j + t] * vf[t];
-                    o[(size_t)j * op] = (T)min(max(lr_rnd(sum, r1), 0), maxv);
+                    const int v = min(max(lr_rnd(sum, r1), 0), maxv);
+                    if (SSE) {
+                        const int d = v - (int)srcp[(size_t)(y0 + rb + j) * sp + x0 + c];
+                        my_sse += (unsigned)(d * d);
+                    } else
+                        o[(size_t)j * op] = (T)v;
                 }
-            } else {
+            } else if (!SSE) {
                 for (int j = 0; j < 8 && rb + j < h; j++) o[(size_t)j * op] = cur[(size_t)(y0 + rb + j) * cp + x0 + c];
             }
+        }
+        if (SSE) {
+#pragma unroll
+            for (int m = 16; m; m >>= 1) my_sse += __shfl_xor_sync(0xffffffffu, my_sse, m);
+            if (!(tid & 31))
+                atomicAdd(&s_sse, my_sse);
+            __syncthreads();
+            if (tid == 0)
+                atomicAdd(a.sse[plane] + unit_idx, s_sse);
         }
         return;
     }
@@ -333,7 +360,13 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
             const int      wv16 = (int)(short)lr_rnd((dg << 11) + acc[n][j], 11);
             const uint32_t v    = (uint32_t)min(max(wv16, 0), maxv);
             o[j >> 1]           = (j & 1) ? (o[j >> 1] | (v << 16)) : v;
+            if (SSE && c + j < wv) {
+                const int d = (int)v - (int)srcp[(size_t)(y0 + r) * sp + x0 + c + j];
+                my_sse += (unsigned)(d * d);
+            }
         }
+        if (SSE)
+            continue;
         T *op8 = out + (size_t)(y0 + r) * op + x0 + c;
         if (c + 8 <= wv)
             st8<T>(op8, make_uint4(o[0], o[1], o[2], o[3]));
@@ -341,6 +374,15 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
             for (int j = 0; j < 8 && c + j < w; j++)
                 op8[j] = c + j < wv ? (T)((o[j >> 1] >> (16 * (j & 1))) & 0xffff) : cur[(size_t)(y0 + r) * cp + x0 + c + j];
         }
+    }
+    if (SSE) {
+#pragma unroll
+        for (int m = 16; m; m >>= 1) my_sse += __shfl_xor_sync(0xffffffffu, my_sse, m);
+        if (!(tid & 31))
+            atomicAdd(&s_sse, my_sse);
+        __syncthreads();
+        if (tid == 0)
+            atomicAdd(a.sse[plane] + unit_idx, s_sse);
     }
 }
 

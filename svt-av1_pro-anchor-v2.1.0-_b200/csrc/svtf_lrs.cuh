@@ -1,0 +1,150 @@
+// svtf_lrs.cuh — device half of the loop-restoration filter search (Wiener tools): per-unit sums and the Wiener statistics.
+//
+// Reference: svt_av1_compute_stats_c / _highbd_c (Encoder/Codec/EbRestorationPick.c:671 / :708), find_average[_highbd]
+// (EbRestorationPick.h:24-43), search_norestore_seg :1432 (sse_restoration_unit :56).  The trial filtering + SSE of
+// finer_tile_search_wiener_seg is lr_kernel<T, true> (svtf_lr.cuh).
+//
+// Statistics of one restoration unit: with y = the win x win window of (picture - avg) around a sample (index = column offset
+// * win + row offset) and x = source - avg,  M[k] = sum y[k] x,  H[k][l] = sum y[k] y[l] over the unit's samples; window
+// samples outside the picture repeat its edge (svt_extend_frame), samples outside the unit are the picture's own.
+//
+// The reference runs win^2 (win^2 + 1) / 2 + win^2 multiply-adds per sample out of a 49-entry array.  Here H is cut into
+// win x win blocks (kb, lb) = (column offset of y[k], column offset of y[l]); a lane owns one block of the upper triangle
+// (28 / 15 / 6 blocks for win 7 / 5 / 3 -> 1 / 2 / 5 lane groups per warp) and walks 8 samples DOWN a column: the two
+// vertical strips of 8 + win - 1 picture samples it needs (columns c + kb and c + lb) are read once into registers, and the
+// 8 x win x win products accumulate in 32-bit registers (flushed to 64-bit shared accumulators before they can overflow).
+// Lanes of a diagonal block also accumulate M for their column.  One CTA = one 64 x 64 tile of one unit; its totals are
+// added to the unit's 64-bit accumulators in global memory (the host divides by the bit-depth divider and mirrors H).
+#pragma once
+#include "svtf_kernels.cuh"
+
+namespace svtf {
+
+struct LrsTile { // a tile of at most 64 x 64 samples inside one restoration unit (plane coordinates)
+    int16_t x0, y0, w, h;
+    int32_t unit; // index into the per-call unit arrays (all searched planes concatenated)
+    int32_t plane;
+};
+
+constexpr int LRS_THREADS = 256;
+constexpr int LRS_T       = 64;
+
+struct LrsArgs {
+    Planes                    cur, src;
+    int                       pw[3], ph[3];
+    const LrsTile            *tiles;
+    unsigned long long       *unit_sum; // sum of the picture's samples per unit (find_average)
+    unsigned long long       *unit_sse; // squared error picture - source per unit (RESTORE_NONE)
+    const int                *unit_count; // samples per unit
+    long long                *acc;        // statistics kernel: per unit win^4 (H, upper triangle) + win^2 (M) accumulators
+    const unsigned long long *acc_off;    // offset of each unit's accumulators in `acc`
+    int                       bd;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(LRS_THREADS) lrs_sums_kernel(const __grid_constant__ LrsArgs a) {
+    const LrsTile t   = a.tiles[blockIdx.x];
+    const T      *cur = static_cast<const T *>(a.cur.p[t.plane]), *src = static_cast<const T *>(a.src.p[t.plane]);
+    const int     cp = a.cur.pitch[t.plane], sp = a.src.pitch[t.plane];
+    unsigned long long sum = 0, sse = 0;
+    for (int i = threadIdx.x; i < t.w * t.h; i += LRS_THREADS) {
+        const int r = i / t.w, c = i - r * t.w;
+        const int v = cur[(size_t)(t.y0 + r) * cp + t.x0 + c], d = v - (int)src[(size_t)(t.y0 + r) * sp + t.x0 + c];
+        sum += (unsigned)v, sse += (unsigned)(d * d);
+    }
+#pragma unroll
+    for (int m = 16; m; m >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, m), sse += __shfl_xor_sync(0xffffffffu, sse, m);
+    if (!(threadIdx.x & 31)) {
+        atomicAdd(a.unit_sum + t.unit, sum);
+        atomicAdd(a.unit_sse + t.unit, sse);
+    }
+}
+
+template <typename T, int WIN>
+__global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_constant__ LrsArgs a) {
+    constexpr int WIN2 = WIN * WIN, HW = WIN / 2, NB = WIN * (WIN + 1) / 2, G = 32 / NB, NACC = WIN2 * WIN2 + WIN2;
+    constexpr int DP = LRS_T + 2 * HW + 2; // pitch of the staged picture window (int16)
+    __shared__ int16_t   s_d[(LRS_T + 2 * HW) * DP];
+    __shared__ int16_t   s_x[LRS_T * LRS_T];
+    __shared__ long long s_acc[NACC];
+    const LrsTile t   = a.tiles[blockIdx.x];
+    const int     tid = threadIdx.x, plane = t.plane, pw = a.pw[plane], ph = a.ph[plane];
+    const T      *cur = static_cast<const T *>(a.cur.p[plane]), *src = static_cast<const T *>(a.src.p[plane]);
+    const int     cp = a.cur.pitch[plane], sp = a.src.pitch[plane];
+    const int     avg = (int)(a.unit_sum[t.unit] / (unsigned long long)a.unit_count[t.unit]);
+    for (int i = tid; i < NACC; i += LRS_THREADS) s_acc[i] = 0;
+    for (int i = tid; i < (t.h + 2 * HW) * (t.w + 2 * HW); i += LRS_THREADS) {
+        const int r = i / (t.w + 2 * HW), c = i - r * (t.w + 2 * HW);
+        const int y = min(max(t.y0 + r - HW, 0), ph - 1), x = min(max(t.x0 + c - HW, 0), pw - 1);
+        s_d[r * DP + c] = (int16_t)((int)cur[(size_t)y * cp + x] - avg);
+    }
+    for (int i = tid; i < t.h * t.w; i += LRS_THREADS) {
+        const int r = i / t.w, c = i - r * t.w;
+        s_x[r * LRS_T + c] = (int16_t)((int)src[(size_t)(t.y0 + r) * sp + t.x0 + c] - avg);
+    }
+    __syncthreads();
+    const int lane = tid & 31, warp = tid >> 5, g = lane / NB, blk = lane - g * NB;
+    if (g < G) {
+        int kb = 0, lb = blk; // block (kb, lb), kb <= lb: row kb of the upper triangle holds WIN - kb blocks
+        while (lb >= WIN - kb) lb -= WIN - kb, kb++;
+        lb += kb;
+        const bool diag = kb == lb;
+        int        acc[WIN][WIN], accm[WIN];
+#pragma unroll
+        for (int r1 = 0; r1 < WIN; r1++) {
+            accm[r1] = 0;
+#pragma unroll
+            for (int r2 = 0; r2 < WIN; r2++) acc[r1][r2] = 0;
+        }
+        auto flush = [&]() {
+#pragma unroll
+            for (int r1 = 0; r1 < WIN; r1++) {
+#pragma unroll
+                for (int r2 = 0; r2 < WIN; r2++) {
+                    if ((!diag || r1 <= r2) && acc[r1][r2])
+                        atomicAdd(reinterpret_cast<unsigned long long *>(&s_acc[(kb * WIN + r1) * WIN2 + lb * WIN + r2]),
+                                  (unsigned long long)(long long)acc[r1][r2]);
+                    acc[r1][r2] = 0;
+                }
+                if (diag && accm[r1])
+                    atomicAdd(reinterpret_cast<unsigned long long *>(&s_acc[WIN2 * WIN2 + kb * WIN + r1]), (unsigned long long)(long long)accm[r1]);
+                accm[r1] = 0;
+            }
+        };
+        // 32-bit partial sums: |y| < 2^bd, so 2^(31 - 2 bd) products fit; a column segment adds 8
+        const int flush_every = a.bd > 10 ? 8 : (a.bd > 8 ? 128 : 2048);
+        const int nbands = (t.h + 7) >> 3, nitems = nbands * t.w;
+        int       since = 0;
+        for (int it = warp * G + g; it < nitems; it += (LRS_THREADS / 32) * G) {
+            const int band = it / t.w, c = it - band * t.w, r0 = band * 8;
+            int       ya[8 + WIN - 1], yb[8 + WIN - 1];
+#pragma unroll
+            for (int k = 0; k < 8 + WIN - 1; k++) {
+                const int rr = min(r0 + k, t.h + 2 * HW - 1);
+                ya[k] = s_d[rr * DP + c + kb], yb[k] = s_d[rr * DP + c + lb];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (r0 + j < t.h) {
+                    const int x = s_x[(r0 + j) * LRS_T + c];
+#pragma unroll
+                    for (int r1 = 0; r1 < WIN; r1++) {
+#pragma unroll
+                        for (int r2 = 0; r2 < WIN; r2++) acc[r1][r2] += ya[j + r1] * yb[j + r2];
+                        accm[r1] += ya[j + r1] * x;
+                    }
+                }
+            }
+            if (++since >= flush_every)
+                flush(), since = 0;
+        }
+        flush();
+    }
+    __syncthreads();
+    long long *out = a.acc + a.acc_off[t.unit];
+    for (int i = tid; i < NACC; i += LRS_THREADS)
+        if (s_acc[i])
+            atomicAdd(reinterpret_cast<unsigned long long *>(out + i), (unsigned long long)s_acc[i]);
+}
+
+} // namespace svtf

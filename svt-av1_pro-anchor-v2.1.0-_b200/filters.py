@@ -137,6 +137,18 @@ def cdef_pick_host(cfg, mse, skip):
     return out, idx
 
 
+def wiener_from_stats(win, M, H):
+    """svtf_lr_wiener_from_stats: the host half of search_wiener_seg (Encoder/Codec/EbRestorationPick.c:1296) for one unit.
+    Returns (usable, vfilter, hfilter)."""
+    lib = L.load()
+    M, H = np.ascontiguousarray(M, dtype=np.int64), np.ascontiguousarray(H, dtype=np.int64)
+    vf, hf = (C.c_int16 * 8)(), (C.c_int16 * 8)()
+    r = lib.svtf_lr_wiener_from_stats(win, _ptr(M), _ptr(H), vf, hf)
+    if r < 0:
+        raise SvtfError(r, lib.svtf_last_error(None).decode())
+    return r, tuple(vf), tuple(hf)
+
+
 class PinnedPicture:
     """Three planes in page-locked host memory (svtf_host_alloc), exposed as numpy arrays."""
 
@@ -383,6 +395,35 @@ class FilterContext:
         ctypes arrays of LrUnit (vert_units x horz_units, raster order; None for a plane without restoration)."""
         up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) if u is not None else None for u in units])
         self._chk(self._lib.svtf_lr_apply_frame(self._h, C.byref(lr), up))
+
+    def restoration_search(self, cfg):
+        """restoration_seg_search + rest_finish_search (Encoder/Codec/EbRestorationPick.c:1471/1555, Wiener tools) on the
+        current picture against the uploaded source (svtf_lr_search_frame).  cfg: LrSearchCfg.  Returns (frame types,
+        [LrUnit arrays], [LrUnitSearch arrays]) — the unit arrays are ready for loop_restoration_filter_frame."""
+        ftype = (C.c_int32 * 3)()
+        units, search = [], []
+        for p in range(3):
+            hu, vu = self.lr_units(p, cfg.restoration_unit_size[p])
+            units.append((L.LrUnit * (hu * vu))())
+            search.append((L.LrUnitSearch * (hu * vu))())
+        up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
+        sp = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in search])
+        self._chk(self._lib.svtf_lr_search_frame(self._h, C.byref(cfg), ftype, up, sp))
+        return list(ftype), units, search
+
+    def lr_units(self, plane, unit_size):
+        hu, vu = C.c_int32(), C.c_int32()
+        self._lib.svtf_lr_units(C.byref(self.geom), plane, unit_size, C.byref(hu), C.byref(vu))
+        return hu.value, vu.value
+
+    def compute_stats(self, plane, unit_size, wiener_win):
+        """svt_av1_compute_stats[_highbd] of every restoration unit of a plane (svtf_lr_wiener_stats): M [units][win^2],
+        H [units][win^2][win^2], int64."""
+        hu, vu = self.lr_units(plane, unit_size)
+        n = wiener_win * wiener_win
+        M, Hm = np.zeros((hu * vu, n), np.int64), np.zeros((hu * vu, n, n), np.int64)
+        self._chk(self._lib.svtf_lr_wiener_stats(self._h, plane, unit_size, wiener_win, _ptr(M), _ptr(Hm)))
+        return M, Hm
 
     def pick_filter_level(self, start_lf, dlf_avg=0, early_exit_convergence=0, only_4x4=0, search_chroma=1):
         """svtf_lf_search_frame: svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE) on the uploaded picture + source."""

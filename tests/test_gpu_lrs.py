@@ -1,0 +1,104 @@
+"""Loop-restoration filter search on the GPU (svtf_lr_wiener_stats, svtf_lr_search_frame) against the oracle
+(oracle/svtf_oracle_lrs.c, pinned against the reference's EbRestorationPick.c in tests/test_lrs_oracle.py)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def search_case(H, w, h, bd, sb, seed, noise=10, amp=6):
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    src = H.synth_picture(g, 13000 + seed, noise=noise)
+    cur = H.synth_source(g, src, 13100 + seed, amp=amp)
+    return g, cur, src
+
+
+def vis(g, planes):
+    return [np.ascontiguousarray(p[: (g.height + s) >> s, : (g.width + s) >> s]) for p, s in zip(planes, (0, 1, 1))]
+
+
+def ctx_with(H, g, cur, src):
+    ctx = H.S.FilterContext(g)
+    ctx.begin(g)
+    ctx.upload(cur)
+    ctx.upload_source(src)
+    return ctx
+
+
+@pytest.mark.parametrize("w,h,bd,sb,win,plane,unit,seed", [
+    (136, 72, 8, 1, 7, 0, 64, 1), (200, 136, 10, 2, 7, 0, 64, 2), (200, 136, 10, 2, 5, 1, 32, 3), (72, 136, 12, 2, 7, 0, 64, 4),
+    (134, 70, 8, 2, 3, 2, 32, 5), (328, 200, 10, 2, 5, 0, 128, 6), (520, 300, 12, 2, 7, 0, 256, 7),
+])
+def test_wiener_stats_match_oracle(H, orc, w, h, bd, sb, win, plane, unit, seed):
+    g, cur, src = search_case(H, w, h, bd, sb, seed)
+    ctx = ctx_with(H, g, cur, src)
+    M, Hm = ctx.compute_stats(plane, unit, win)
+    c, s = vis(g, cur), vis(g, src)
+    for u, lim in enumerate(H.lr_unit_limits(g, plane, unit)):
+        a = orc.wiener_stats(g, plane, c[plane], s[plane], lim, win)
+        assert np.array_equal(a[0], M[u]), (u, lim)
+        assert np.array_equal(a[1], Hm[u]), (u, lim)
+
+
+def test_wiener_stats_extreme_content(H, orc):
+    """Largest products: a 12-bit checkerboard of 0 / 4095 (32-bit partial sums must be flushed in time)."""
+    S = H.S
+    g = S.make_geom(200, 136, 12, 2)
+    cur = [np.zeros(((g.mi_rows * 4) >> s, (g.mi_cols * 4) >> s), np.uint16) for s in (0, 1, 1)]
+    for p in cur:
+        yy, xx = np.indices(p.shape)
+        p[:] = np.where(((yy // 3) + (xx // 5)) & 1, 4095, 0)
+    src = [4095 - p for p in cur]
+    ctx = ctx_with(H, g, cur, src)
+    M, Hm = ctx.compute_stats(0, 128, 7)
+    c, s = vis(g, cur), vis(g, src)
+    for u, lim in enumerate(H.lr_unit_limits(g, 0, 128)):
+        a = orc.wiener_stats(g, 0, c[0], s[0], lim, 7)
+        assert np.array_equal(a[0], M[u]) and np.array_equal(a[1], Hm[u]), u
+
+
+@pytest.mark.parametrize("w,h,bd,sb,seed,kw", [
+    (136, 72, 8, 1, 1, {}),
+    (200, 136, 10, 2, 2, {}),
+    (136, 104, 10, 2, 3, {"tap_lvl": 2}),
+    (104, 72, 12, 2, 4, {"tap_lvl": 3, "one_step": 1}),
+    (200, 72, 8, 2, 5, {"unit_size": (128, 64, 64), "refinement": 0}),
+    (134, 70, 10, 2, 6, {"chroma": 0, "rdmult": 300000}),
+    (136, 72, 8, 1, 7, {"rdmult": 40, "cost": (10, 60)}),
+    (328, 200, 10, 2, 8, {"unit_size": (256, 128, 128)}),
+])
+def test_lr_search_matches_oracle(H, orc, w, h, bd, sb, seed, kw):
+    g, cur, src = search_case(H, w, h, bd, sb, seed)
+    cfg = H.lr_search_cfg(**kw)
+    ctx = ctx_with(H, g, cur, src)
+    ftype, units, search = ctx.restoration_search(cfg)
+    a = H.lr_search_sig(g, cfg, ftype, units, search)
+    b = orc.lr_search(g, vis(g, cur), vis(g, src), cfg)
+    for p in range(3):
+        assert a[p][0] == b[p][0], ("frame type", p)
+        assert a[p][2] == b[p][2], ("unit search", p)
+        assert a[p][1] == b[p][1], ("unit info", p)
+    assert any(t != 0 for t in ftype)
+
+
+def test_lr_search_then_apply_lowers_error(H):
+    """Property at a larger size: applying what the search returns must not raise the squared error of any searched plane
+    (without stripe boundaries the search's own SSE is what the frame filter would give; with them it stays close)."""
+    S = H.S
+    g, cur, src = search_case(H, 1920, 1080, 10, 2, 31)
+    ctx = ctx_with(H, g, cur, src)
+    cfg = H.lr_search_cfg(unit_size=(256, 128, 128))
+    ftype, units, search = ctx.restoration_search(cfg)
+    assert ftype == [1, 1, 1]
+    lr = S._lib.LrParams()
+    for p in range(3):
+        lr.frame_restoration_type[p], lr.restoration_unit_size[p] = ftype[p], cfg.restoration_unit_size[p]
+    lr.optimized_lr = 0
+    ctx.loop_restoration_filter_frame(lr, units)
+    out = ctx.download()
+    c, s, o = vis(g, cur), vis(g, src), vis(g, out)
+    for p in range(3):
+        before = int(((c[p].astype(np.int64) - s[p]) ** 2).sum())
+        after = int(((o[p].astype(np.int64) - s[p]) ** 2).sum())
+        assert after < before, (p, before, after)

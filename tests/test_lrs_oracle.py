@@ -63,3 +63,22 @@ def test_oracle_lr_search_matches_reference(H, orc, ref, w, h, bd, sb, seed, kw)
         assert a[p][0] == b[p][0], ("frame type", p)
         assert a[p][2] == b[p][2], ("unit search", p)
         assert a[p][1] == b[p][1], ("unit info", p)
+
+
+def test_product_host_solve_matches_oracle(H, orc):
+    """svtf_lr_wiener_from_stats (the product's host code, no GPU needed) against the oracle on real and on degenerate statistics."""
+    S = H.S
+    g, cur, src = search_case(H, 136, 104, 10, 2, 21)
+    cur, src = vis(g, cur), vis(g, src)
+    for plane, win in ((0, 7), (0, 5), (1, 5), (2, 3)):
+        for lim in H.lr_unit_limits(g, plane, 64 if plane == 0 else 32):
+            M, Hm = orc.wiener_stats(g, plane, cur[plane], src[plane], lim, win)
+            assert S.wiener_from_stats(win, M, Hm) == orc.wiener_from_stats(win, M, Hm)
+    rng = np.random.default_rng(78)
+    for win in (7, 5, 3):
+        n = win * win
+        for k in range(12):
+            a = rng.integers(-(1 << (8 + k)), 1 << (8 + k), size=(n, n)).astype(np.int64)
+            Hm = (a @ a.T if k % 2 else a + a.T) if k else np.zeros((n, n), np.int64)
+            M = rng.integers(-(1 << (12 + 2 * k)), 1 << (12 + 2 * k), size=n).astype(np.int64) if k else np.zeros(n, np.int64)
+            assert S.wiener_from_stats(win, M, Hm) == orc.wiener_from_stats(win, M, Hm), (win, k)
