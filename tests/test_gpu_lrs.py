@@ -79,7 +79,8 @@ def test_lr_search_matches_oracle(H, orc, w, h, bd, sb, seed, kw):
         assert a[p][0] == b[p][0], ("frame type", p)
         assert a[p][2] == b[p][2], ("unit search", p)
         assert a[p][1] == b[p][1], ("unit info", p)
-    assert any(t != 0 for t in ftype)
+    if kw.get("tap_lvl", 1) != 3:  # the 3-tap search legitimately keeps RESTORE_NONE on this content (as the oracle does)
+        assert any(t != 0 for t in ftype)
 
 
 def test_lr_search_then_apply_lowers_error(H):
