@@ -223,6 +223,43 @@ def lf_search_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
+def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
+    """Loop-restoration filter search, Wiener tools (restoration_seg_search + rest_finish_search): statistics of every unit,
+    host solve, refinement trials of all units in lock-step; the reference's C on a smaller picture."""
+    src = H.synth_source(geom, wl["rec"], 0xB200F1, amp=6)
+    cfg = H.lr_search_cfg(unit_size=(256, 128, 128))
+    ctx.begin(geom)
+    ctx.upload(src)          # the picture searched: "reconstruction" = source + coding noise
+    ctx.upload_source(wl["rec"])
+    ctx.restoration_search(cfg)  # warm-up
+    l0 = ctx.launch_count
+    n = 3
+    t0 = time.perf_counter()
+    for _ in range(n):
+        ftype, units, search = ctx.restoration_search(cfg)
+    dt = (time.perf_counter() - t0) / n
+    t0 = time.perf_counter()
+    for _ in range(n):
+        ctx.compute_stats(0, 256, 7)
+    dts = (time.perf_counter() - t0) / n
+    res = {"metric": "loop-restoration search Mpixel/s (Wiener 7-tap luma + 5-tap chroma, refinement on; picture resident)",
+           "value": round(geom.width * geom.height / dt / 1e6, 1), "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 3),
+           "gpu_launches_per_picture": (ctx.launch_count - l0 - n * 2) // n, "luma_stats_ms_incl_download": round(dts * 1e3, 3),
+           "frame_types": ftype, "cpu_baseline": None}
+    if with_cpu and H.ref_available():
+        g2 = S.make_geom(960, 544, BD)
+        rec = H.synth_picture(g2, 0xF11)
+        org = H.synth_source(g2, rec, 0xF12, amp=6)
+        vis = lambda pl: [np.ascontiguousarray(p[: (g2.height + s) >> s, : (g2.width + s) >> s]) for p, s in zip(pl, (0, 1, 1))]
+        ref = H.Ref()
+        t0 = time.perf_counter()
+        ref.lr_search(g2, vis(org), vis(rec), cfg)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": round(960 * 544 / dt / 1e6, 3), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                               "sample": "one 960x544 10-bit picture, one segment, single thread"}
+    return res
+
+
 def side_info_leg(H, S, geom, ctx, np):
     """Side info to the device: host packer + 4 B per 4x4 over PCIe (svtf_pack_mi_enc + svtf_set_mi) against byte planes
     + packing on the device (svtf_set_mi_soa_enc, 1.5 B per 4x4)."""
@@ -789,6 +826,7 @@ def main():
     side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
     hand = handoff_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
+    lrs = lr_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
@@ -808,7 +846,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "lr_search": lrs, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:

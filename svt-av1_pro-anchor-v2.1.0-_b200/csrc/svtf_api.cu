@@ -11,6 +11,9 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <atomic>
+#include <chrono>
+#include <thread>
 #include <vector>
 
 #include "svtf_kernels.cuh"
@@ -113,6 +116,8 @@ struct svtf_ctx {
     uint64_t     launches = 0;
     uint8_t     *d_lrs = nullptr;          // scratch of the loop-restoration filter search (svtf_lr_search_frame), allocated on first use
     size_t       lrs_cap = 0;
+    uint8_t     *h_lrs = nullptr;          // pinned mirror of the parts of d_lrs that cross PCIe every refinement round
+    size_t       h_lrs_cap = 0;
     uint8_t     *d_handoff = nullptr;      // staging of svtf_download_ref_padded / svtf_upload_frame_8as16, allocated on first use
     size_t       handoff_cap = 0;
     bool         search3_ready = false;    // same for cdef_search3_kernel
@@ -236,6 +241,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
     cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff), cudaFree(c->d_lrs);
+    if (c->h_lrs) cudaFreeHost(c->h_lrs);
     if (c->h_mi_bad)
         cudaFreeHost(c->h_mi_bad);
     if (c->own_stream)
@@ -1750,17 +1756,29 @@ int lrs_reserve(svtf_ctx *c, LrsPlan &plan) {
         CUDA_TRY(c, cudaMalloc(&c->d_lrs, plan.bytes));
         c->lrs_cap = plan.bytes;
     }
+    if (plan.bytes > c->h_lrs_cap) { // same carve-up on the host side, pinned
+        if (c->h_lrs) {
+            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            CUDA_TRY(c, cudaFreeHost(c->h_lrs));
+            c->h_lrs = nullptr, c->h_lrs_cap = 0;
+        }
+        CUDA_TRY(c, cudaMallocHost(&c->h_lrs, plan.bytes));
+        c->h_lrs_cap = plan.bytes;
+    }
     return SVTF_OK;
 }
 
 // Uploads the plan, runs the per-unit sums (and, with stats, the Wiener statistics) and brings the results to the host.
-int lrs_measure(svtf_ctx *c, LrsPlan &plan, bool stats, std::vector<unsigned long long> &sse_none, std::vector<long long> &acc) {
+int lrs_measure(svtf_ctx *c, LrsPlan &plan, bool stats, const unsigned long long *&sse_none, const long long *&acc) {
     if (int r = lrs_reserve(c, plan))
         return r;
-    uint8_t *d = c->d_lrs;
-    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_tiles, plan.tiles.data(), sizeof(LrsTile) * plan.tiles.size(), cudaMemcpyHostToDevice, c->stream));
-    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_count, plan.count.data(), 4 * (size_t)plan.units, cudaMemcpyHostToDevice, c->stream));
-    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_off, plan.acc_off.data(), 8 * (size_t)plan.units, cudaMemcpyHostToDevice, c->stream));
+    uint8_t *d = c->d_lrs, *h = c->h_lrs;
+    std::memcpy(h + plan.o_tiles, plan.tiles.data(), sizeof(LrsTile) * plan.tiles.size());
+    std::memcpy(h + plan.o_count, plan.count.data(), 4 * (size_t)plan.units);
+    std::memcpy(h + plan.o_off, plan.acc_off.data(), 8 * (size_t)plan.units);
+    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_tiles, h + plan.o_tiles, sizeof(LrsTile) * plan.tiles.size(), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_count, h + plan.o_count, 4 * (size_t)plan.units, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_off, h + plan.o_off, 8 * (size_t)plan.units, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaMemsetAsync(d + plan.o_sum, 0, plan.o_count - plan.o_sum, c->stream)); // sum, sse, trial
     LrsArgs a;
     a.cur = c->surf[c->cur].planes(), a.src = c->source.planes();
@@ -1802,12 +1820,12 @@ int lrs_measure(svtf_ctx *c, LrsPlan &plan, bool stats, std::vector<unsigned lon
             c->launches++;
             t0 = t1;
         }
-        acc.resize(plan.acc_total);
-        CUDA_TRY(c, cudaMemcpyAsync(acc.data(), d + plan.o_acc, 8 * plan.acc_total, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaMemcpyAsync(h + plan.o_acc, d + plan.o_acc, 8 * plan.acc_total, cudaMemcpyDeviceToHost, c->stream));
     }
-    sse_none.resize(plan.units);
-    CUDA_TRY(c, cudaMemcpyAsync(sse_none.data(), d + plan.o_sse, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(h + plan.o_sse, d + plan.o_sse, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    sse_none = reinterpret_cast<const unsigned long long *>(h + plan.o_sse);
+    acc      = reinterpret_cast<const long long *>(h + plan.o_acc);
     return SVTF_OK;
 }
 
@@ -1827,6 +1845,18 @@ int lrs_check(svtf_ctx *c, const char *fn) {
         return c->fail(SVTF_E_STATE, std::string(fn) + ": not available on a striped context");
     return SVTF_OK;
 }
+template <class F>
+void host_parallel_for(int n, F fn) {
+    const int nt = std::max(1, std::min({(int)std::thread::hardware_concurrency(), 8, n / 8}));
+    std::atomic<int> next{0};
+    auto             worker = [&] {
+        for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) fn(i);
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; t++) th.emplace_back(worker);
+    worker();
+    for (auto &t : th) t.join();
+}
 bool lrs_unit_size_ok(int plane, int us) { return (us == 64 || us == 128 || us == 256 || (plane && us == 32)); }
 } // namespace
 
@@ -1840,12 +1870,12 @@ extern "C" int svtf_lr_wiener_stats(svtf_ctx *c, int32_t plane, int32_t unit_siz
     CUDA_TRY(c, cudaSetDevice(c->device));
     LrsPlan plan;
     lrs_add_plane(c->geom, plan, plane, unit_size, wiener_win);
-    std::vector<unsigned long long> sse;
-    std::vector<long long>          acc;
+    const unsigned long long *sse;
+    const long long          *acc;
     if (int r = lrs_measure(c, plan, true, sse, acc))
         return r;
     const int win2 = wiener_win * wiener_win;
-    for (int u = 0; u < plan.units; u++) lrs_finish_stats(c->geom, wiener_win, acc.data() + plan.acc_off[u], M + (size_t)u * win2, H + (size_t)u * win2 * win2);
+    for (int u = 0; u < plan.units; u++) lrs_finish_stats(c->geom, wiener_win, acc + plan.acc_off[u], M + (size_t)u * win2, H + (size_t)u * win2 * win2);
     return SVTF_OK;
 }
 
@@ -1872,27 +1902,40 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
         std::memset(out_units[p], 0, sizeof(svtf_lr_unit) * hu * vu);
     }
     CUDA_TRY(c, cudaSetDevice(c->device));
+    const bool timing = std::getenv("SVTF_LRS_TIMING") != nullptr;
+    auto       now    = [] { return std::chrono::steady_clock::now(); };
+    auto       ms     = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    const auto t_start = now();
     LrsPlan plan;
     for (int p = 0; p < nplanes; p++) lrs_add_plane(c->geom, plan, p, cfg->restoration_unit_size[p], p ? std::min(wn_luma, 5) : wn_luma);
-    std::vector<unsigned long long> sse_none;
-    std::vector<long long>          acc;
+    const unsigned long long *sse_none;
+    const long long          *acc;
     if (int r = lrs_measure(c, plan, cfg->wn_enabled != 0, sse_none, acc))
         return r;
+    const auto t_measured = now();
     std::vector<svtf_lr_unit_search> us(plan.units);
     std::vector<LrsRefine>           ref(plan.units);
+    // the solve of a unit (integer alternating least squares, ~20k multiply-divides for a 7x7 window) is independent of every
+    // other unit: a few host threads share them (the reference spreads units over its restoration segments the same way)
+    std::vector<int> win_of(plan.units);
     for (const LrsPlane &pl : plan.planes)
-        for (int u = 0; u < pl.hu * pl.vu; u++) {
-            svtf_lr_unit_search &s = us[pl.first + u];
-            std::memset(&s, 0, sizeof(s));
-            s.sse[0] = (int64_t)sse_none[pl.first + u], s.sse[1] = INT64_MAX;
-            if (!cfg->wn_enabled)
-                continue;
-            int64_t M[49], H[49 * 49];
-            lrs_finish_stats(c->geom, pl.win, acc.data() + plan.acc_off[pl.first + u], M, H);
-            int16_t vf[8], hf[8];
-            if (svtf_lr_wiener_from_stats(pl.win, M, H, vf, hf) == 1)
-                ref[pl.first + u].start(pl.win, cfg->wn_use_refinement != 0, cfg->wn_max_one_refinement_step != 0, vf, hf);
-        }
+        for (int u = 0; u < pl.hu * pl.vu; u++) win_of[pl.first + u] = pl.win;
+    host_parallel_for(plan.units, [&](int u) {
+        svtf_lr_unit_search &s = us[u];
+        std::memset(&s, 0, sizeof(s));
+        s.sse[0] = (int64_t)sse_none[u], s.sse[1] = INT64_MAX;
+        if (!cfg->wn_enabled)
+            return;
+        int64_t M[49], H[49 * 49];
+        lrs_finish_stats(c->geom, win_of[u], acc + plan.acc_off[u], M, H);
+        int16_t vf[8], hf[8];
+        if (svtf_lr_wiener_from_stats(win_of[u], M, H, vf, hf) == 1)
+            ref[u].start(win_of[u], cfg->wn_use_refinement != 0, cfg->wn_max_one_refinement_step != 0, vf, hf);
+    });
+    const auto t_solved = now();
+    int        rounds   = 0;
     // ---- refinement in lock-step: one launch filters every unit that has a trial pending and measures it ----
     if (cfg->wn_enabled) {
         uint8_t *d = c->d_lrs;
@@ -1919,8 +1962,8 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
         }
         for (int p = 0; p < 3; p++) a.base[p] = grid, grid += a.chunks[p] * a.stripes[p];
         a.opt = 2, a.bd = c->geom.bit_depth;
-        std::vector<LrUnitDev>          host(plan.units);
-        std::vector<unsigned long long> trial(plan.units);
+        LrUnitDev                *host  = reinterpret_cast<LrUnitDev *>(c->h_lrs + plan.o_units);
+        const unsigned long long *trial = reinterpret_cast<const unsigned long long *>(c->h_lrs + plan.o_trial);
         for (;;) {
             int pending = 0;
             for (int u = 0; u < plan.units; u++) {
@@ -1934,7 +1977,8 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
             }
             if (!pending)
                 break;
-            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host.data(), sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
+            rounds++;
+            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host, sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
             CUDA_TRY(c, cudaMemsetAsync(d + plan.o_trial, 0, 8 * (size_t)plan.units, c->stream));
             if (c->geom.sample_bytes == 1)
                 lr_kernel<uint8_t, true><<<grid, LR_THREADS, 0, c->stream>>>(a);
@@ -1942,13 +1986,16 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
                 lr_kernel<uint16_t, true><<<grid, LR_THREADS, 0, c->stream>>>(a);
             CUDA_TRY(c, cudaGetLastError());
             c->launches++;
-            CUDA_TRY(c, cudaMemcpyAsync(trial.data(), d + plan.o_trial, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_trial, d + plan.o_trial, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
             CUDA_TRY(c, cudaStreamSynchronize(c->stream));
             for (int u = 0; u < plan.units; u++)
                 if (ref[u].pending())
                     ref[u].feed((int64_t)trial[u]);
         }
     }
+    if (timing)
+        std::fprintf(stderr, "svtf_lr_search_frame: plan+stats %.3f ms, host solve %.3f ms, %d refinement rounds %.3f ms\n", ms(t_start, t_measured),
+                     ms(t_measured, t_solved), rounds, ms(t_solved, now()));
     // ---- search_wiener_finish :1380 per unit in raster order, then the frame decision (rest_finish_search :1596-1624) ----
     for (const LrsPlane &pl : plan.planes) {
         const int n = pl.hu * pl.vu;
