@@ -357,6 +357,77 @@ API int adapt_lr_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, v
     return 0;
 }
 
+/* restoration_seg_search (segment 0) + rest_finish_search on the reference's own structures */
+void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, const Yv12BufferConfig *src, Yv12BufferConfig *trial_frame_rst,
+                            PictureControlSet *pcs, uint32_t segment_index);
+void rest_finish_search(PictureControlSet *pcs);
+API int adapt_lr_search(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, void *oy, int osy, void *ocb, int oscb, void *ocr,
+                        int oscr, const svtf_lr_search_cfg *cfg, int32_t out_type[3], svtf_lr_unit *const out_units[3],
+                        svtf_lr_unit_search *const out_search[3]) {
+    harness    h;
+    ref_mi_soa soa = {NULL, NULL, NULL, NULL, NULL, NULL, g->mi_cols};
+    if (harness_init(&h, g, &soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    Av1Common      cm;
+    Macroblock    *x = calloc(1, sizeof(*x));
+    svtf_lr_params lr;
+    memset(&lr, 0, sizeof(lr));
+    for (int p = 0; p < 3; p++) lr.restoration_unit_size[p] = cfg->restoration_unit_size[p];
+    const svtf_lr_unit *none[3] = {NULL, NULL, NULL};
+    lr_fill(&h, &cm, g, &lr, none, NULL, NULL);
+    h.ppcs->av1_cm = &cm, h.ppcs->av1x = x;
+    cm.wn_filter_ctrls.enabled                 = (Bool)cfg->wn_enabled;
+    cm.wn_filter_ctrls.filter_tap_lvl          = (uint8_t)cfg->wn_filter_tap_lvl;
+    cm.wn_filter_ctrls.use_refinement          = (Bool)cfg->wn_use_refinement;
+    cm.wn_filter_ctrls.max_one_refinement_step = (Bool)cfg->wn_max_one_refinement_step;
+    cm.wn_filter_ctrls.use_chroma              = (Bool)cfg->wn_use_chroma;
+    x->rdmult                                  = cfg->rdmult;
+    x->wiener_restore_cost[0] = cfg->wiener_restore_cost[0], x->wiener_restore_cost[1] = cfg->wiener_restore_cost[1];
+    for (int p = 0; p < 3; p++) h.pcs->rusi_picture[p] = calloc(h.pcs->rst_info[p].units_per_tile, sizeof(RestUnitSearchInfo));
+    void *const      cur[3] = {y, cb, cr}, *const org[3] = {oy, ocb, ocr};
+    const int        cst[3] = {sy, scb, scr}, ost[3] = {osy, oscb, oscr};
+    Yv12BufferConfig f, s;
+    lr_yv12(&f, g, cur, cst), lr_yv12(&s, g, org, ost);
+    svtf_adapter_set_resident(0);
+    restoration_seg_search(NULL, &f, &s, NULL, h.pcs, 1); /* a later segment: nothing to do */
+    restoration_seg_search(NULL, &f, &s, NULL, h.pcs, 0);
+    for (int p = 0; p < 3; p++)
+        for (int u = 0; u < h.pcs->rst_info[p].units_per_tile && out_search && out_search[p]; u++) {
+            const RestUnitSearchInfo *ri = &h.pcs->rusi_picture[p][u];
+            svtf_lr_unit_search      *os = &out_search[p][u];
+            memset(os, 0, sizeof(*os));
+            if (p && !cfg->wn_use_chroma)
+                continue;
+            os->sse[0] = ri->sse[RESTORE_NONE], os->sse[1] = ri->sse[RESTORE_WIENER];
+            if (os->sse[1] != INT64_MAX) {
+                memcpy(os->wiener_vfilter, ri->wiener.vfilter, 16);
+                memcpy(os->wiener_hfilter, ri->wiener.hfilter, 16);
+            }
+        }
+    rest_finish_search(h.pcs);
+    for (int p = 0; p < 3; p++) {
+        const RestorationInfo *rsi = &h.pcs->rst_info[p];
+        out_type[p]                = (int32_t)rsi->frame_restoration_type;
+        for (int u = 0; u < rsi->units_per_tile; u++) {
+            svtf_lr_unit *o = &out_units[p][u];
+            memset(o, 0, sizeof(*o));
+            if (rsi->frame_restoration_type == RESTORE_NONE)
+                continue;
+            o->restoration_type = (int32_t)rsi->unit_info[u].restoration_type;
+            if (o->restoration_type == SVTF_RESTORE_WIENER) {
+                memcpy(o->wiener_vfilter, rsi->unit_info[u].wiener_info.vfilter, 16);
+                memcpy(o->wiener_hfilter, rsi->unit_info[u].wiener_info.hfilter, 16);
+            }
+        }
+        free(h.pcs->rusi_picture[p]);
+    }
+    svtf_adapter_release(h.pcs);
+    lr_free(&h);
+    free(x);
+    harness_free(&h);
+    return 0;
+}
+
 /* resident chain through the adapters: svt_av1_loop_filter_frame -> svt_av1_cdef_frame -> svt_av1_loop_restoration_filter_frame */
 API int adapt_chain_lr(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, const ref_mi_soa *soa,
                        const svtf_lf_params *lf, const svtf_cdef_params *cp, const int8_t *fb_strength_idx, const svtf_lr_params *lr,

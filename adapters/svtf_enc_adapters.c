@@ -609,6 +609,125 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
 }
 
 /* ----------------------------------------------------------------------------------------------------
+ * restoration_seg_search + rest_finish_search (Encoder/Codec/EbRestorationPick.c:1471 / :1555), called by the restoration
+ * kernel (Encoder/Codec/EbRestProcess.c:599-610) once per restoration segment and once per picture.  The GPU searches the
+ * whole picture in one call, so the segment that carries segment_index 0 does the work and the others return; the results
+ * land where the reference leaves them: pcs->rusi_picture[plane][unit] (sse[RESTORE_NONE], sse[RESTORE_WIENER], wiener) after
+ * the segment call, rst_info[plane].frame_restoration_type / unit_info[] after rest_finish_search.
+ * Covered: the Wiener tools without stripe boundaries (scs->use_boundaries_in_rest_search = 0, the reference's setting,
+ * Encoder/Globals/EbEncHandle.c:4162) and without use_prev_frame_coeffs.  With cm->sg_filter_ctrls.enabled the search must
+ * stay on the host: the adapter aborts rather than return a different decision.
+ * org_fts is the picture after CDEF (uploaded unless the chain is resident), src the source picture.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct {
+    const PictureControlSet *pcs;
+    int32_t                  frame_type[3];
+    svtf_lr_unit            *units[3];
+} LrSearchResult;
+static LrSearchResult g_lr_res[SVTF_MAX_CACHED];
+
+static LrSearchResult *lr_result_for(const PictureControlSet *pcs, int create) {
+    LrSearchResult *r = NULL;
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < SVTF_MAX_CACHED && !r; i++)
+        if (g_lr_res[i].pcs == pcs)
+            r = &g_lr_res[i];
+    for (int i = 0; i < SVTF_MAX_CACHED && !r && create; i++)
+        if (!g_lr_res[i].pcs) {
+            r      = &g_lr_res[i];
+            r->pcs = pcs;
+        }
+    pthread_mutex_unlock(&g_lock);
+    return r;
+}
+
+void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, const Yv12BufferConfig *src, Yv12BufferConfig *trial_frame_rst,
+                            PictureControlSet *pcs, uint32_t segment_index) {
+    (void)rst_tmpbuf, (void)trial_frame_rst;
+    if (segment_index != 0)
+        return;
+    Av1Common        *cm = pcs->ppcs->av1_cm;
+    const Macroblock *x  = pcs->ppcs->av1x;
+    CtxSlot          *s  = slot_for(pcs);
+    if (cm->sg_filter_ctrls.enabled || cm->use_boundaries_in_rest_search || cm->wn_filter_ctrls.use_prev_frame_coeffs) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: restoration_seg_search covers the Wiener tools only "
+                        "(sg_filter_ctrls.enabled, use_boundaries_in_rest_search and use_prev_frame_coeffs must be 0)\n");
+        abort();
+    }
+    svtf_lr_search_cfg cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    for (int p = 0; p < 3; p++) cfg.restoration_unit_size[p] = pcs->rst_info[p].restoration_unit_size;
+    cfg.wn_enabled                 = cm->wn_filter_ctrls.enabled;
+    cfg.wn_filter_tap_lvl          = cm->wn_filter_ctrls.filter_tap_lvl;
+    cfg.wn_use_refinement          = cm->wn_filter_ctrls.use_refinement;
+    cfg.wn_max_one_refinement_step = cm->wn_filter_ctrls.max_one_refinement_step;
+    cfg.wn_use_chroma              = cm->wn_filter_ctrls.use_chroma;
+    cfg.rdmult                     = x->rdmult;
+    cfg.wiener_restore_cost[0] = x->wiener_restore_cost[0], cfg.wiener_restore_cost[1] = x->wiener_restore_cost[1];
+    void   *fp[3], *sp[3];
+    int32_t fst[3], sst[3];
+    for (int p = 0; p < 3; p++) {
+        fp[p]  = cm->use_highbitdepth ? (void *)CONVERT_TO_SHORTPTR(org_fts->buffers[p]) : (void *)org_fts->buffers[p];
+        sp[p]  = cm->use_highbitdepth ? (void *)CONVERT_TO_SHORTPTR(src->buffers[p]) : (void *)src->buffers[p];
+        fst[p] = org_fts->strides[p > 0], sst[p] = src->strides[p > 0];
+    }
+    if (!(g_resident && s->resident)) {
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, fp[0], fst[0], fp[1], fst[1], fp[2], fst[2]), s->ctx);
+    }
+    CHECK(svtf_upload_source(s->ctx, sp[0], sst[0], sp[1], sst[1], sp[2], sst[2]), s->ctx);
+    LrSearchResult      *r = lr_result_for(pcs, 1);
+    svtf_lr_unit_search *us[3];
+    if (!r) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: more than %d restoration searches in flight\n", SVTF_MAX_CACHED);
+        abort();
+    }
+    for (int p = 0; p < 3; p++) {
+        free(r->units[p]);
+        r->units[p] = (svtf_lr_unit *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit));
+        us[p]       = (svtf_lr_unit_search *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit_search));
+    }
+    CHECK(svtf_lr_search_frame(s->ctx, &cfg, r->frame_type, r->units, us), s->ctx);
+    const int planes = cm->wn_filter_ctrls.enabled && cm->wn_filter_ctrls.use_chroma ? 3 : 1;
+    for (int p = 0; p < planes; p++)
+        for (int u = 0; u < pcs->rst_info[p].units_per_tile; u++) {
+            RestUnitSearchInfo *ri    = &pcs->rusi_picture[p][u];
+            ri->sse[RESTORE_NONE]     = us[p][u].sse[0];
+            ri->sse[RESTORE_WIENER]   = us[p][u].sse[1];
+            if (us[p][u].sse[1] != INT64_MAX) {
+                memcpy(ri->wiener.vfilter, us[p][u].wiener_vfilter, sizeof(ri->wiener.vfilter));
+                memcpy(ri->wiener.hfilter, us[p][u].wiener_hfilter, sizeof(ri->wiener.hfilter));
+            } else
+                ri->best_rtype[RESTORE_WIENER - 1] = RESTORE_NONE;
+        }
+    for (int p = 0; p < 3; p++) free(us[p]);
+}
+
+void rest_finish_search(PictureControlSet *pcs) {
+    LrSearchResult *r = lr_result_for(pcs, 0);
+    if (!r) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: rest_finish_search without restoration_seg_search\n");
+        abort();
+    }
+    for (int p = 0; p < 3; p++) {
+        RestorationInfo *rsi        = &pcs->rst_info[p];
+        rsi->frame_restoration_type = (RestorationType)r->frame_type[p];
+        if (r->frame_type[p] != SVTF_RESTORE_NONE)
+            for (int u = 0; u < rsi->units_per_tile; u++) { /* copy_unit_info :1202 */
+                rsi->unit_info[u].restoration_type = (RestorationType)r->units[p][u].restoration_type;
+                if (r->units[p][u].restoration_type == SVTF_RESTORE_WIENER) {
+                    memcpy(rsi->unit_info[u].wiener_info.vfilter, r->units[p][u].wiener_vfilter, sizeof(rsi->unit_info[u].wiener_info.vfilter));
+                    memcpy(rsi->unit_info[u].wiener_info.hfilter, r->units[p][u].wiener_hfilter, sizeof(rsi->unit_info[u].wiener_info.hfilter));
+                }
+            }
+        free(r->units[p]);
+    }
+    pthread_mutex_lock(&g_lock);
+    memset(r, 0, sizeof(*r));
+    pthread_mutex_unlock(&g_lock);
+}
+
+/* ----------------------------------------------------------------------------------------------------
  * Recon hand-off: the pixel work of pad_ref_and_set_flags (Encoder/Codec/EbEncDecProcess.c:1589-1744) —
  * right/bottom replication, border padding and the 8-bit / 2-bit split (or narrowing) of the reference picture — from the
  * picture on the GPU.  pad_ref_and_set_flags keeps its bookkeeping (ref_poc, qp, slice_type, ...) and calls this in place of

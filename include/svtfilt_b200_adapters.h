@@ -33,6 +33,12 @@ void svtf_cdef_search_picture(struct PictureControlSet *pcs, struct SequenceCont
  * recon buffer uploaded first).  pad_ref_and_set_flags calls it in place of its lines 1604-1744 and keeps its bookkeeping. */
 void svtf_pad_ref_pictures(struct PictureControlSet *pcs, struct SequenceControlSet *scs);
 
+/* Also provided with the reference's own names and signatures (Encoder/Codec/EbRestorationPick.c:1471 / :1555):
+ *   void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, const Yv12BufferConfig *src,
+ *                               Yv12BufferConfig *trial_frame_rst, PictureControlSet *pcs, uint32_t segment_index);
+ *   void rest_finish_search(PictureControlSet *pcs);
+ * (Wiener tools; segment 0 searches the whole picture on the GPU, the other segments return.) */
+
 /* CUDA device used by contexts the adapters create (default 0). */
 void svtf_adapter_set_device(int device);
 /* 1: keep the picture resident on the GPU between DLF, CDEF search, CDEF apply and CCSO of one pcs (no

@@ -219,3 +219,22 @@ def test_pad_ref_pictures_adapter(H, orc, adapt, w, h, bd, sb, resident):
         assert H.planes_equal(b8, exp[1]), "8-bit: " + H.first_diff(b8, exp[1])
     if two:
         assert H.planes_equal(bn, exp[2]), "2-bit: " + H.first_diff(bn, exp[2])
+
+
+@pytest.mark.parametrize("w,h,bd,sb,kw", [(200, 136, 10, 2, {}), (136, 72, 8, 1, {"tap_lvl": 2, "one_step": 1}), (264, 136, 8, 2, {"chroma": 0})])
+def test_restoration_search_adapter(H, orc, adapt, w, h, bd, sb, kw):
+    """restoration_seg_search(.., segment 0) + rest_finish_search on real PictureControlSet / Av1Common / Macroblock structures:
+    rusi_picture[] and rst_info[] end up as the oracle's (pinned to the reference's own search) say.  The planes handed over
+    are the visible picture with arbitrary strides, as the reference's Yv12BufferConfig describes it."""
+    S = H.S
+    g = S.make_geom(w, h, bd, sb)
+    src = H.synth_picture(g, 14000 + w, noise=10)
+    cur = H.synth_source(g, src, 14001, amp=6)
+    cfg = H.lr_search_cfg(**kw)
+    got = H._lr_search_call(adapt.adapt_lr_search, g, cur, src, cfg)
+    vis = lambda pl: [np.ascontiguousarray(p[: (g.height + s) >> s, : (g.width + s) >> s]) for p, s in zip(pl, (0, 1, 1))]
+    exp = orc.lr_search(g, vis(cur), vis(src), cfg)
+    for p in range(3):
+        assert got[p][0] == exp[p][0], ("frame type", p)
+        assert got[p][2] == exp[p][2], ("unit search", p)
+        assert got[p][1] == exp[p][1], ("unit info", p)
