@@ -363,7 +363,7 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
 void rest_finish_search(PictureControlSet *pcs);
 API int adapt_lr_search(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, void *oy, int osy, void *ocb, int oscb, void *ocr,
                         int oscr, const svtf_lr_search_cfg *cfg, int32_t out_type[3], svtf_lr_unit *const out_units[3],
-                        svtf_lr_unit_search *const out_search[3]) {
+                        svtf_lr_unit_search *const out_search[3], int32_t sg_frame_ep_cnt[16]) {
     harness    h;
     ref_mi_soa soa = {NULL, NULL, NULL, NULL, NULL, NULL, g->mi_cols};
     if (harness_init(&h, g, &soa, y, sy, cb, scb, cr, scr))
@@ -383,6 +383,15 @@ API int adapt_lr_search(const svtf_geom *g, void *y, int sy, void *cb, int scb, 
     cm.wn_filter_ctrls.use_chroma              = (Bool)cfg->wn_use_chroma;
     x->rdmult                                  = cfg->rdmult;
     x->wiener_restore_cost[0] = cfg->wiener_restore_cost[0], x->wiener_restore_cost[1] = cfg->wiener_restore_cost[1];
+    x->sgrproj_restore_cost[0] = cfg->sgrproj_restore_cost[0], x->sgrproj_restore_cost[1] = cfg->sgrproj_restore_cost[1];
+    for (int t = 0; t < 3; t++) x->switchable_restore_cost[t] = cfg->switchable_restore_cost[t];
+    cm.sg_filter_ctrls.enabled = (Bool)cfg->sg_enabled, cm.sg_filter_ctrls.use_chroma = (Bool)cfg->sg_use_chroma;
+    cm.sg_filter_ctrls.step_range = 16;
+    for (int t = 0; t < 2; t++) {
+        cm.sg_filter_ctrls.start_ep[t] = (int8_t)cfg->sg_start_ep[t], cm.sg_filter_ctrls.end_ep[t] = (int8_t)cfg->sg_end_ep[t];
+        cm.sg_filter_ctrls.ep_inc[t] = (int8_t)cfg->sg_ep_inc[t], cm.sg_filter_ctrls.refine[t] = (int8_t)cfg->sg_refine[t];
+    }
+    cm.sg_ref_frame_ep[0] = cm.sg_ref_frame_ep[1] = -1;
     for (int p = 0; p < 3; p++) h.pcs->rusi_picture[p] = calloc(h.pcs->rst_info[p].units_per_tile, sizeof(RestUnitSearchInfo));
     void *const      cur[3] = {y, cb, cr}, *const org[3] = {oy, ocb, ocr};
     const int        cst[3] = {sy, scb, scr}, ost[3] = {osy, oscb, oscr};
@@ -396,15 +405,22 @@ API int adapt_lr_search(const svtf_geom *g, void *y, int sy, void *cb, int scb, 
             const RestUnitSearchInfo *ri = &h.pcs->rusi_picture[p][u];
             svtf_lr_unit_search      *os = &out_search[p][u];
             memset(os, 0, sizeof(*os));
-            if (p && !cfg->wn_use_chroma)
+            if (p && !(cfg->wn_enabled && cfg->wn_use_chroma) && !(cfg->sg_enabled && cfg->sg_use_chroma))
                 continue;
-            os->sse[0] = ri->sse[RESTORE_NONE], os->sse[1] = ri->sse[RESTORE_WIENER];
+            os->sse[0] = ri->sse[RESTORE_NONE];
+            os->sse[1] = cfg->wn_enabled && (!p || cfg->wn_use_chroma) ? ri->sse[RESTORE_WIENER] : INT64_MAX;
             if (os->sse[1] != INT64_MAX) {
                 memcpy(os->wiener_vfilter, ri->wiener.vfilter, 16);
                 memcpy(os->wiener_hfilter, ri->wiener.hfilter, 16);
             }
+            if (cfg->sg_enabled && (!p || cfg->sg_use_chroma)) {
+                os->sse[2] = ri->sse[RESTORE_SGRPROJ];
+                os->sgr_ep = ri->sgrproj.ep, os->sgr_xqd[0] = ri->sgrproj.xqd[0], os->sgr_xqd[1] = ri->sgrproj.xqd[1];
+            }
         }
     rest_finish_search(h.pcs);
+    if (sg_frame_ep_cnt)
+        for (int i = 0; i < 16; i++) sg_frame_ep_cnt[i] = cm.sg_frame_ep_cnt[i];
     for (int p = 0; p < 3; p++) {
         const RestorationInfo *rsi = &h.pcs->rst_info[p];
         out_type[p]                = (int32_t)rsi->frame_restoration_type;
@@ -417,6 +433,9 @@ API int adapt_lr_search(const svtf_geom *g, void *y, int sy, void *cb, int scb, 
             if (o->restoration_type == SVTF_RESTORE_WIENER) {
                 memcpy(o->wiener_vfilter, rsi->unit_info[u].wiener_info.vfilter, 16);
                 memcpy(o->wiener_hfilter, rsi->unit_info[u].wiener_info.hfilter, 16);
+            } else if (o->restoration_type == SVTF_RESTORE_SGRPROJ) {
+                o->sgr_ep = rsi->unit_info[u].sgrproj_info.ep;
+                o->sgr_xqd[0] = rsi->unit_info[u].sgrproj_info.xqd[0], o->sgr_xqd[1] = rsi->unit_info[u].sgrproj_info.xqd[1];
             }
         }
         free(h.pcs->rusi_picture[p]);

@@ -614,9 +614,9 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
  * whole picture in one call, so the segment that carries segment_index 0 does the work and the others return; the results
  * land where the reference leaves them: pcs->rusi_picture[plane][unit] (sse[RESTORE_NONE], sse[RESTORE_WIENER], wiener) after
  * the segment call, rst_info[plane].frame_restoration_type / unit_info[] after rest_finish_search.
- * Covered: the Wiener tools without stripe boundaries (scs->use_boundaries_in_rest_search = 0, the reference's setting,
- * Encoder/Globals/EbEncHandle.c:4162) and without use_prev_frame_coeffs.  With cm->sg_filter_ctrls.enabled the search must
- * stay on the host: the adapter aborts rather than return a different decision.
+ * Covered: the Wiener and the self-guided tools (and RESTORE_SWITCHABLE between them) without stripe boundaries
+ * (scs->use_boundaries_in_rest_search = 0, the reference's setting, Encoder/Globals/EbEncHandle.c:4162).  Not covered:
+ * wn_filter_ctrls.use_prev_frame_coeffs — the adapter aborts rather than return a different decision.
  * org_fts is the picture after CDEF (uploaded unless the chain is resident), src the source picture.
  * ---------------------------------------------------------------------------------------------------- */
 typedef struct {
@@ -649,9 +649,9 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     Av1Common        *cm = pcs->ppcs->av1_cm;
     const Macroblock *x  = pcs->ppcs->av1x;
     CtxSlot          *s  = slot_for(pcs);
-    if (cm->sg_filter_ctrls.enabled || cm->use_boundaries_in_rest_search || cm->wn_filter_ctrls.use_prev_frame_coeffs) {
-        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: restoration_seg_search covers the Wiener tools only "
-                        "(sg_filter_ctrls.enabled, use_boundaries_in_rest_search and use_prev_frame_coeffs must be 0)\n");
+    if (cm->use_boundaries_in_rest_search || (cm->wn_filter_ctrls.enabled && cm->wn_filter_ctrls.use_prev_frame_coeffs)) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: restoration_seg_search needs use_boundaries_in_rest_search = 0 and "
+                        "wn_filter_ctrls.use_prev_frame_coeffs = 0\n");
         abort();
     }
     svtf_lr_search_cfg cfg;
@@ -664,6 +664,22 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     cfg.wn_use_chroma              = cm->wn_filter_ctrls.use_chroma;
     cfg.rdmult                     = x->rdmult;
     cfg.wiener_restore_cost[0] = x->wiener_restore_cost[0], cfg.wiener_restore_cost[1] = x->wiener_restore_cost[1];
+    cfg.sgrproj_restore_cost[0] = x->sgrproj_restore_cost[0], cfg.sgrproj_restore_cost[1] = x->sgrproj_restore_cost[1];
+    for (int t = 0; t < 3; t++) cfg.switchable_restore_cost[t] = x->switchable_restore_cost[t];
+    cfg.sg_enabled    = cm->sg_filter_ctrls.enabled;
+    cfg.sg_use_chroma = cm->sg_filter_ctrls.use_chroma;
+    for (int t = 0; t < 2; t++) { /* the ep range of search_selfguided_restoration (:567-589) */
+        const int8_t step = cm->sg_filter_ctrls.step_range, e0 = cm->sg_ref_frame_ep[0], e1 = cm->sg_ref_frame_ep[1];
+        if (step < 16) {
+            const int mid        = e0 < 0 && e1 < 0 ? 0 : (e1 < 0 ? e0 : (e0 < 0 ? e1 : (e0 + e1) / 2));
+            cfg.sg_start_ep[t]   = e0 < 0 && e1 < 0 ? 0 : (mid - step > 0 ? mid - step : 0);
+            cfg.sg_end_ep[t]     = e0 < 0 && e1 < 0 ? SGRPROJ_PARAMS : (mid + step < SGRPROJ_PARAMS ? mid + step : SGRPROJ_PARAMS);
+            cfg.sg_ep_inc[t] = 1, cfg.sg_refine[t] = 1;
+        } else {
+            cfg.sg_start_ep[t] = cm->sg_filter_ctrls.start_ep[t], cfg.sg_end_ep[t] = cm->sg_filter_ctrls.end_ep[t];
+            cfg.sg_ep_inc[t] = cm->sg_filter_ctrls.ep_inc[t], cfg.sg_refine[t] = cm->sg_filter_ctrls.refine[t];
+        }
+    }
     void   *fp[3], *sp[3];
     int32_t fst[3], sst[3];
     for (int p = 0; p < 3; p++) {
@@ -687,18 +703,28 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
         r->units[p] = (svtf_lr_unit *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit));
         us[p]       = (svtf_lr_unit_search *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit_search));
     }
-    CHECK(svtf_lr_search_frame(s->ctx, &cfg, r->frame_type, r->units, us), s->ctx);
-    const int planes = cm->wn_filter_ctrls.enabled && cm->wn_filter_ctrls.use_chroma ? 3 : 1;
+    int32_t ep_cnt[16];
+    CHECK(svtf_lr_search_frame(s->ctx, &cfg, r->frame_type, r->units, us, ep_cnt), s->ctx);
+    for (int i = 0; i < 16; i++) cm->sg_frame_ep_cnt[i] += ep_cnt[i]; /* :1250 */
+    const int wn = cm->wn_filter_ctrls.enabled, sg = cm->sg_filter_ctrls.enabled;
+    const int planes = (wn && cm->wn_filter_ctrls.use_chroma) || (sg && cm->sg_filter_ctrls.use_chroma) ? 3 : 1;
     for (int p = 0; p < planes; p++)
         for (int u = 0; u < pcs->rst_info[p].units_per_tile; u++) {
-            RestUnitSearchInfo *ri    = &pcs->rusi_picture[p][u];
-            ri->sse[RESTORE_NONE]     = us[p][u].sse[0];
-            ri->sse[RESTORE_WIENER]   = us[p][u].sse[1];
-            if (us[p][u].sse[1] != INT64_MAX) {
-                memcpy(ri->wiener.vfilter, us[p][u].wiener_vfilter, sizeof(ri->wiener.vfilter));
-                memcpy(ri->wiener.hfilter, us[p][u].wiener_hfilter, sizeof(ri->wiener.hfilter));
-            } else
-                ri->best_rtype[RESTORE_WIENER - 1] = RESTORE_NONE;
+            RestUnitSearchInfo *ri = &pcs->rusi_picture[p][u];
+            ri->sse[RESTORE_NONE]  = us[p][u].sse[0];
+            if (wn && (!p || cm->wn_filter_ctrls.use_chroma)) {
+                ri->sse[RESTORE_WIENER] = us[p][u].sse[1];
+                if (us[p][u].sse[1] != INT64_MAX) {
+                    memcpy(ri->wiener.vfilter, us[p][u].wiener_vfilter, sizeof(ri->wiener.vfilter));
+                    memcpy(ri->wiener.hfilter, us[p][u].wiener_hfilter, sizeof(ri->wiener.hfilter));
+                } else
+                    ri->best_rtype[RESTORE_WIENER - 1] = RESTORE_NONE;
+            }
+            if (sg && (!p || cm->sg_filter_ctrls.use_chroma)) {
+                ri->sse[RESTORE_SGRPROJ] = us[p][u].sse[2];
+                ri->sgrproj.ep           = us[p][u].sgr_ep;
+                ri->sgrproj.xqd[0] = us[p][u].sgr_xqd[0], ri->sgrproj.xqd[1] = us[p][u].sgr_xqd[1];
+            }
         }
     for (int p = 0; p < 3; p++) free(us[p]);
 }
@@ -718,6 +744,10 @@ void rest_finish_search(PictureControlSet *pcs) {
                 if (r->units[p][u].restoration_type == SVTF_RESTORE_WIENER) {
                     memcpy(rsi->unit_info[u].wiener_info.vfilter, r->units[p][u].wiener_vfilter, sizeof(rsi->unit_info[u].wiener_info.vfilter));
                     memcpy(rsi->unit_info[u].wiener_info.hfilter, r->units[p][u].wiener_hfilter, sizeof(rsi->unit_info[u].wiener_info.hfilter));
+                } else if (r->units[p][u].restoration_type == SVTF_RESTORE_SGRPROJ) {
+                    rsi->unit_info[u].sgrproj_info.ep     = r->units[p][u].sgr_ep;
+                    rsi->unit_info[u].sgrproj_info.xqd[0] = r->units[p][u].sgr_xqd[0];
+                    rsi->unit_info[u].sgrproj_info.xqd[1] = r->units[p][u].sgr_xqd[1];
                 }
             }
         free(r->units[p]);

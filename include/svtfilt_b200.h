@@ -315,15 +315,18 @@ typedef struct svtf_lf_search_cfg {
 int svtf_lf_search_frame(svtf_ctx *ctx, const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]);
 
 /* ---- loop-restoration filter search (the caller of the restoration filters) ----------------------
- * restoration_seg_search + rest_finish_search (Encoder/Codec/EbRestorationPick.c:1471/1555) with the Wiener tools:
+ * restoration_seg_search + rest_finish_search (Encoder/Codec/EbRestorationPick.c:1471/1555):
  *   search_norestore_seg :1432 (SSE of the unfiltered unit), search_wiener_seg :1296 (svt_av1_compute_stats[_highbd]_c
  *   :671/:708 -> wiener_decompose_sep_sym :906 / linsolve_wiener :766 -> finalize_sym_filter :977 -> compute_score :937 ->
- *   finer_tile_search_wiener_seg :1042, every trial = try_restoration_unit_seg :129 = filter the unit + SSE), then
- *   search_wiener_finish :1380 (count_wiener_bits :1008, RDCOST_DBL) and the per-plane frame decision (:1596-1624).
+ *   finer_tile_search_wiener_seg :1042, every trial = try_restoration_unit_seg :129 = filter the unit + SSE),
+ *   search_sgrproj_seg :1220 (search_selfguided_restoration :550: per parameter set ep the two guided filters of the unit,
+ *   svt_get_proj_subspace_c :417, encode_xq :508, finer_search_pixel_proj_error :320; then the unit filtered for real), then
+ *   search_wiener_finish :1380 / search_sgrproj_finish :1267 / search_switchable :1148 (count_wiener_bits :1008,
+ *   count_sgrproj_bits :655, RDCOST_DBL) and the per-plane frame decision (:1596-1624).
  * The picture searched is the context's current picture (after CDEF / CCSO), the source the uploaded source picture.
  * The search filters WITHOUT stripe boundaries (scs->use_boundaries_in_rest_search = 0, EbEncHandle.c:4162: rows
  * above / below a stripe are the picture's own rows; the frame edge is replicated, svt_extend_frame).
- * Not covered (returns SVTF_E_ARG when asked): the self-guided search (sg_enabled), use_prev_frame_coeffs. */
+ * Not covered: use_prev_frame_coeffs (Wiener taps carried over from the previous frame). */
 typedef struct svtf_lr_search_cfg {
     int32_t restoration_unit_size[3];   /* rst_info[p].restoration_unit_size                                      */
     int32_t wn_enabled;                 /* cm->wn_filter_ctrls.enabled (Common/Codec/Av1Common.h:32-45)           */
@@ -331,21 +334,31 @@ typedef struct svtf_lr_search_cfg {
     int32_t wn_use_refinement;          /* refinement search around the solved taps                               */
     int32_t wn_max_one_refinement_step; /* only the step of 4                                                     */
     int32_t wn_use_chroma;              /* search U and V as well                                                 */
-    int32_t sg_enabled;                 /* must be 0 (self-guided search: not covered)                            */
+    int32_t sg_enabled;                 /* cm->sg_filter_ctrls.enabled (Av1Common.h:47-60)                        */
+    int32_t sg_use_chroma;
+    /* the ep range search_selfguided_restoration ends up with, per plane type [luma, chroma] (:567-589): either
+     * ctrls->start_ep / end_ep / ep_inc / refine (step_range 16) or the range around the reference frames' ep with
+     * ep_inc 1 and refine 1 (step_range < 16) */
+    int32_t sg_start_ep[2], sg_end_ep[2], sg_ep_inc[2], sg_refine[2];
     int32_t rdmult;                     /* x->rdmult                                                              */
     int32_t wiener_restore_cost[2];     /* x->wiener_restore_cost (bits << AV1_PROB_COST_SHIFT)                   */
+    int32_t sgrproj_restore_cost[2];    /* x->sgrproj_restore_cost                                                */
+    int32_t switchable_restore_cost[3]; /* x->switchable_restore_cost                                             */
 } svtf_lr_search_cfg;
-/* Per restoration unit, RestUnitSearchInfo (Common/Codec/EbRestoration.h:349): sse[0] = RESTORE_NONE, sse[1] = RESTORE_WIENER
- * (INT64_MAX: no usable filter), the refined taps, and best_rtype[RESTORE_WIENER - 1]. */
+/* Per restoration unit, what restoration_seg_search leaves in RestUnitSearchInfo (Common/Codec/EbRestoration.h:349): sse of
+ * RESTORE_NONE / RESTORE_WIENER (INT64_MAX: no usable filter) / RESTORE_SGRPROJ, the refined Wiener taps, the self-guided
+ * parameters. */
 typedef struct svtf_lr_unit_search {
-    int64_t sse[2];
+    int64_t sse[3];
     int16_t wiener_vfilter[8], wiener_hfilter[8];
-    int32_t best_rtype;
+    int32_t sgr_ep, sgr_xqd[2];
+    int32_t reserved;
 } svtf_lr_unit_search;
 /* out_frame_type[p] = rst_info[p].frame_restoration_type; out_units[p] (vert_units x horz_units of svtf_lr_units) = the
- * unit_info the reference leaves in rst_info[p] (ready for svtf_lr_apply_frame); out_search[p] may be NULL. */
+ * unit_info the reference leaves in rst_info[p] (ready for svtf_lr_apply_frame); out_search[p] may be NULL;
+ * sg_frame_ep_cnt (may be NULL): the 16 counters the search adds to cm->sg_frame_ep_cnt (:1250). */
 int svtf_lr_search_frame(svtf_ctx *ctx, const svtf_lr_search_cfg *cfg, int32_t out_frame_type[3], svtf_lr_unit *const out_units[3],
-                         svtf_lr_unit_search *const out_search[3]);
+                         svtf_lr_unit_search *const out_search[3], int32_t sg_frame_ep_cnt[16]);
 /* svt_av1_compute_stats_c / _highbd_c (:671/:708) of every restoration unit of one plane of the current picture against
  * the source: M[unit][win*win], H[unit][win*win][win*win] (int64, as the reference leaves them, bit-depth scaling and
  * symmetric fill included).  wiener_win = 7, 5 or 3. */

@@ -53,7 +53,7 @@ static void lrs_frame_free(lrs_frame *fr) {
 
 REF_API int ref_lr_search(const svtf_geom *g, const void *y, int sy, const void *cb, int scb, const void *cr, int scr, const void *oy, int osy,
                           const void *ocb, int oscb, const void *ocr, int oscr, const svtf_lr_search_cfg *cfg, int32_t out_type[3],
-                          svtf_lr_unit *const out_units[3], svtf_lr_unit_search *const out_search[3]) {
+                          svtf_lr_unit *const out_units[3], svtf_lr_unit_search *const out_search[3], int32_t sg_frame_ep_cnt[16]) {
     PictureControlSet       *pcs  = calloc(1, sizeof(*pcs));
     PictureParentControlSet *ppcs = calloc(1, sizeof(*ppcs));
     Av1Common               *cm   = calloc(1, sizeof(*cm));
@@ -76,7 +76,16 @@ REF_API int ref_lr_search(const svtf_geom *g, const void *y, int sy, const void 
     cm->wn_filter_ctrls.max_one_refinement_step = (Bool)cfg->wn_max_one_refinement_step;
     cm->wn_filter_ctrls.use_prev_frame_coeffs   = 0;
     cm->wn_filter_ctrls.use_chroma              = (Bool)cfg->wn_use_chroma;
-    cm->sg_filter_ctrls.enabled                 = 0;
+    cm->sg_filter_ctrls.enabled                 = (Bool)cfg->sg_enabled;
+    cm->sg_filter_ctrls.use_chroma              = (Bool)cfg->sg_use_chroma;
+    cm->sg_filter_ctrls.step_range              = 16; /* the explicit ep range */
+    for (int t = 0; t < 2; t++) {
+        cm->sg_filter_ctrls.start_ep[t] = (int8_t)cfg->sg_start_ep[t], cm->sg_filter_ctrls.end_ep[t] = (int8_t)cfg->sg_end_ep[t];
+        cm->sg_filter_ctrls.ep_inc[t] = (int8_t)cfg->sg_ep_inc[t], cm->sg_filter_ctrls.refine[t] = (int8_t)cfg->sg_refine[t];
+    }
+    cm->sg_ref_frame_ep[0] = cm->sg_ref_frame_ep[1] = -1;
+    x->sgrproj_restore_cost[0] = cfg->sgrproj_restore_cost[0], x->sgrproj_restore_cost[1] = cfg->sgrproj_restore_cost[1];
+    for (int t = 0; t < 3; t++) x->switchable_restore_cost[t] = cfg->switchable_restore_cost[t];
     ppcs->frm_hdr.frame_type                    = KEY_FRAME;
     x->rdmult                                   = cfg->rdmult;
     x->wiener_restore_cost[0] = cfg->wiener_restore_cost[0], x->wiener_restore_cost[1] = cfg->wiener_restore_cost[1];
@@ -108,20 +117,33 @@ REF_API int ref_lr_search(const svtf_geom *g, const void *y, int sy, const void 
                 if (o->restoration_type == SVTF_RESTORE_WIENER) {
                     memcpy(o->wiener_vfilter, rsi->unit_info[u].wiener_info.vfilter, 16);
                     memcpy(o->wiener_hfilter, rsi->unit_info[u].wiener_info.hfilter, 16);
+                } else if (o->restoration_type == SVTF_RESTORE_SGRPROJ) {
+                    o->sgr_ep = rsi->unit_info[u].sgrproj_info.ep;
+                    o->sgr_xqd[0] = rsi->unit_info[u].sgrproj_info.xqd[0], o->sgr_xqd[1] = rsi->unit_info[u].sgrproj_info.xqd[1];
                 }
             }
             if (out_search && out_search[p]) {
                 const RestUnitSearchInfo *ri = &pcs->rusi_picture[p][u];
                 svtf_lr_unit_search      *os = &out_search[p][u];
                 memset(os, 0, sizeof(*os));
-                os->sse[0] = ri->sse[RESTORE_NONE], os->sse[1] = ri->sse[RESTORE_WIENER];
+                const int searched = !p || (cfg->wn_enabled && cfg->wn_use_chroma) || (cfg->sg_enabled && cfg->sg_use_chroma);
+                if (!searched)
+                    continue;
+                os->sse[0] = ri->sse[RESTORE_NONE];
+                os->sse[1] = cfg->wn_enabled && (!p || cfg->wn_use_chroma) ? ri->sse[RESTORE_WIENER] : INT64_MAX;
                 if (os->sse[1] != INT64_MAX) {
                     memcpy(os->wiener_vfilter, ri->wiener.vfilter, 16);
                     memcpy(os->wiener_hfilter, ri->wiener.hfilter, 16);
                 }
+                if (cfg->sg_enabled && (!p || cfg->sg_use_chroma)) {
+                    os->sse[2] = ri->sse[RESTORE_SGRPROJ];
+                    os->sgr_ep = ri->sgrproj.ep, os->sgr_xqd[0] = ri->sgrproj.xqd[0], os->sgr_xqd[1] = ri->sgrproj.xqd[1];
+                }
             }
         }
     }
+    if (sg_frame_ep_cnt)
+        for (int i = 0; i < 16; i++) sg_frame_ep_cnt[i] = cm->sg_frame_ep_cnt[i];
     for (int p = 0; p < 3; p++) {
         free(pcs->rusi_picture[p]);
         free(pcs->rst_info[p].unit_info), free(pcs->rst_info[p].boundaries.stripe_boundary_above), free(pcs->rst_info[p].boundaries.stripe_boundary_below);

@@ -112,17 +112,11 @@ static void sgr_ab(const stripe_in *s, int bd, int r, int sv, int x, int y, int 
     *B               = (int32_t)(((uint32_t)(256 - *A) * (uint32_t)sum * (uint32_t)(n == 25 ? one_by_25 : one_by_9) + (1u << 11)) >> 12);
 }
 
-static int sgr_px(const stripe_in *s, const svtf_lr_unit *u, int bd, int x, int y) {
-    const int ep = u->sgr_ep, r0 = sgr_r[ep][0], r1 = sgr_r[ep][1];
-    const int dg = stripe_px(s, x, y), uu = dg << 4;
-    int       xq[2]; /* svt_decode_xq */
-    if (r0 == 0)
-        xq[0] = 0, xq[1] = 128 - u->sgr_xqd[1];
-    else if (r1 == 0)
-        xq[0] = u->sgr_xqd[0], xq[1] = 0;
-    else
-        xq[0] = u->sgr_xqd[0], xq[1] = 128 - xq[0] - u->sgr_xqd[1];
-    int v = uu << 7;
+/* flt0 / flt1 of svt_av1_selfguided_restoration_c (:905) at (x, y): the two guided filters' outputs, 4 fractional bits */
+static void sgr_flt(const stripe_in *s, int ep, int bd, int x, int y, int *f0, int *f1) {
+    const int r0 = sgr_r[ep][0], r1 = sgr_r[ep][1];
+    const int dg = stripe_px(s, x, y);
+    *f0 = *f1 = 0;
     if (r0 > 0) { /* fast: A/B exist on the rows y0 - 1, y0 + 1, ... of the stripe only */
         int a = 0, b = 0, A, B, sh;
         if (!((y - s->y0) & 1)) {
@@ -139,7 +133,7 @@ static int sgr_px(const stripe_in *s, const svtf_lr_unit *u, int bd, int x, int 
             }
             sh = 8 + 4 - 4;
         }
-        v += xq[0] * (RND(a * dg + b, sh) - uu);
+        *f0 = RND(a * dg + b, sh);
     }
     if (r1 > 0) {
         int a = 0, b = 0, A, B;
@@ -148,10 +142,43 @@ static int sgr_px(const stripe_in *s, const svtf_lr_unit *u, int bd, int x, int 
                 sgr_ab(s, bd, r1, sgr_s[ep][1], x + dx, y + dy, &A, &B);
                 a += A * ((dx && dy) ? 3 : 4), b += B * ((dx && dy) ? 3 : 4);
             }
-        v += xq[1] * (RND(a * dg + b, 8 + 5 - 4) - uu);
+        *f1 = RND(a * dg + b, 8 + 5 - 4);
     }
+}
+
+static int sgr_px(const stripe_in *s, const svtf_lr_unit *u, int bd, int x, int y) {
+    const int ep = u->sgr_ep, r0 = sgr_r[ep][0], r1 = sgr_r[ep][1];
+    const int dg = stripe_px(s, x, y), uu = dg << 4;
+    int       xq[2], f0, f1; /* svt_decode_xq */
+    if (r0 == 0)
+        xq[0] = 0, xq[1] = 128 - u->sgr_xqd[1];
+    else if (r1 == 0)
+        xq[0] = u->sgr_xqd[0], xq[1] = 0;
+    else
+        xq[0] = u->sgr_xqd[0], xq[1] = 128 - xq[0] - u->sgr_xqd[1];
+    sgr_flt(s, ep, bd, x, y, &f0, &f1);
+    int v = uu << 7;
+    if (r0 > 0)
+        v += xq[0] * (f0 - uu);
+    if (r1 > 0)
+        v += xq[1] * (f1 - uu);
     const int w = (int16_t)RND(v, 7 + 4);
     return IMIN(IMAX(w, 0), (1 << bd) - 1);
+}
+
+/* apply_sgr (Encoder/Codec/EbRestorationPick.c:522) for the unit [h0, h1) x [v0, v1): flt0 / flt1 (row pitch h1 - h0) of
+ * parameter set ep, no stripe boundaries.  The reference filters 64-row blocks counted from the unit's first row; the only
+ * thing that depends on the block is the row parity of the radius-2 filter, and units, blocks and stripes all start on
+ * even rows.  Used by svtf_oracle_lrs.c. */
+void orc_lr_sgr_unit_flt(const void *cur, int cst, int sb, int bd, int ss, int pw, int ph, int h0, int h1, int v0, int v1, int ep, int32_t *flt0,
+                         int32_t *flt1) {
+    stripe_in s = {cur, cur, cst, cst, sb, pw, ph, v0, v1, 0, 0, 2};
+    for (int yy = v0; yy < v1; yy++)
+        for (int xx = h0; xx < h1; xx++) {
+            int f0, f1;
+            sgr_flt(&s, ep, bd, xx, yy, &f0, &f1);
+            flt0[(size_t)(yy - v0) * (h1 - h0) + xx - h0] = f0, flt1[(size_t)(yy - v0) * (h1 - h0) + xx - h0] = f1;
+        }
 }
 
 ORC_API int orc_lr_units(const svtf_geom *g, int plane, int unit_size, int *horz, int *vert) {

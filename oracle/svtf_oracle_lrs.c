@@ -14,6 +14,7 @@
  * takes the remainder (up to 1.5 units), rows shifted up by 8 luma samples.
  * Pinned against the reference's own code through oracle/ref_shim_lrs.c (tests/test_lrs_oracle.py).
  */
+#include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -278,15 +279,154 @@ static int64_t refine(const plane_ctx *c, const int lim[4], int win, const svtf_
     return err;
 }
 
+/* ---- self-guided tools ---- */
+void orc_lr_sgr_unit_flt(const void *cur, int cst, int sb, int bd, int ss, int pw, int ph, int h0, int h1, int v0, int v1, int ep, int32_t *flt0,
+                         int32_t *flt1);
+/* svt_aom_eb_sgr_params radii (Common/Codec/EbRestoration.c:85-103) */
+static const int sg_r[16][2] = {{2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {0, 1}, {0, 1}, {0, 1}, {0, 1}, {2, 0}, {2, 0}};
+static const int sg_min[2] = {-96, -32}, sg_max[2] = {31, 95}; /* SGRPROJ_PRJ_MIN0/1, MAX0/1 */
+
+static int iclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+/* get_pixel_proj_error :305 (svt_decode_xq + svt_av1_[lowbd|highbd]_pixel_proj_error_c :167/:233) */
+static int64_t proj_error(const plane_ctx *c, const int lim[4], const int32_t *f0, const int32_t *f1, const int *xqd, int ep) {
+    const int r0 = sg_r[ep][0], r1 = sg_r[ep][1], w = lim[1] - lim[0];
+    int       xq[2];
+    if (r0 == 0)
+        xq[0] = 0, xq[1] = 128 - xqd[1];
+    else if (r1 == 0)
+        xq[0] = xqd[0], xq[1] = 0;
+    else
+        xq[0] = xqd[0], xq[1] = 128 - xq[0] - xqd[1];
+    int64_t err = 0;
+    for (int y = lim[2]; y < lim[3]; y++)
+        for (int x = lim[0]; x < lim[1]; x++) {
+            const size_t i = (size_t)(y - lim[2]) * w + x - lim[0];
+            const int    u = px(c->cur, c->cst, c->sb, x, y) << 4;
+            int          v = u << 7;
+            if (r0 > 0)
+                v += xq[0] * (f0[i] - u);
+            if (r1 > 0)
+                v += xq[1] * (f1[i] - u);
+            const int e = ((v + (1 << 10)) >> 11) - px(c->src, c->sst, c->sb, x, y);
+            err += (int64_t)e * e;
+        }
+    return err;
+}
+
+/* search_selfguided_restoration :550 for one unit: best (ep, xqd) */
+static void search_sgr_unit(const plane_ctx *c, const int lim[4], int start_ep, int end_ep, int ep_inc, int do_refine, int *best_ep, int best_xqd[2]) {
+    const int    w = lim[1] - lim[0], h = lim[3] - lim[2], size = w * h;
+    int32_t     *f0 = malloc(sizeof(int32_t) * size), *f1 = malloc(sizeof(int32_t) * size);
+    int64_t      best_err = -1;
+    *best_ep = 0, best_xqd[0] = best_xqd[1] = 0;
+    for (int ep = start_ep; ep < end_ep; ep += ep_inc) {
+        const int r0 = sg_r[ep][0], r1 = sg_r[ep][1];
+        orc_lr_sgr_unit_flt(c->cur, c->cst, c->sb, c->bd, c->ss, c->pw, c->ph, lim[0], lim[1], lim[2], lim[3], ep, f0, f1);
+        /* svt_get_proj_subspace_c :417: least squares in double */
+        double H[2][2] = {{0, 0}, {0, 0}}, C[2] = {0, 0};
+        for (int y = lim[2]; y < lim[3]; y++)
+            for (int x = lim[0]; x < lim[1]; x++) {
+                const size_t i  = (size_t)(y - lim[2]) * w + x - lim[0];
+                const double u  = (double)(px(c->cur, c->cst, c->sb, x, y) << 4);
+                const double sv = (double)(px(c->src, c->sst, c->sb, x, y) << 4) - u;
+                const double a  = r0 > 0 ? (double)f0[i] - u : 0, b = r1 > 0 ? (double)f1[i] - u : 0;
+                H[0][0] += a * a, H[1][1] += b * b, H[0][1] += a * b, C[0] += a * sv, C[1] += b * sv;
+            }
+        H[0][0] /= size, H[0][1] /= size, H[1][1] /= size, H[1][0] = H[0][1], C[0] /= size, C[1] /= size;
+        int xq[2] = {0, 0};
+        if (r0 == 0) {
+            if (!(H[1][1] < 1e-8))
+                xq[1] = (int)rint(C[1] / H[1][1] * 128);
+        } else if (r1 == 0) {
+            if (!(H[0][0] < 1e-8))
+                xq[0] = (int)rint(C[0] / H[0][0] * 128);
+        } else {
+            const double det = H[0][0] * H[1][1] - H[0][1] * H[1][0];
+            if (!(det < 1e-8)) {
+                const double x0 = (H[1][1] * C[0] - H[0][1] * C[1]) / det, x1 = (H[0][0] * C[1] - H[1][0] * C[0]) / det;
+                xq[0] = (int)rint(x0 * 128), xq[1] = (int)rint(x1 * 128);
+            }
+        }
+        int xqd[2]; /* encode_xq :508 */
+        if (r0 == 0)
+            xqd[0] = 0, xqd[1] = iclamp(128 - xq[1], sg_min[1], sg_max[1]);
+        else if (r1 == 0)
+            xqd[0] = iclamp(xq[0], sg_min[0], sg_max[0]), xqd[1] = iclamp(128 - xqd[0], sg_min[1], sg_max[1]);
+        else
+            xqd[0] = iclamp(xq[0], sg_min[0], sg_max[0]), xqd[1] = iclamp(128 - xqd[0] - xq[1], sg_min[1], sg_max[1]);
+        /* finer_search_pixel_proj_error :320, start_step 2 */
+        int64_t err = proj_error(c, lim, f0, f1, xqd, ep);
+        if (do_refine)
+            for (int st = 2; st >= 1; st >>= 1)
+                for (int p = 0; p < 2; p++) {
+                    if ((r0 == 0 && p == 0) || (r1 == 0 && p == 1))
+                        continue;
+                    int moved_down = 0;
+                    for (int sign = -1; sign <= 1; sign += 2) {
+                        for (;;) {
+                            if (sign < 0 ? xqd[p] - st < sg_min[p] : xqd[p] + st > sg_max[p])
+                                break;
+                            xqd[p] += sign * st;
+                            const int64_t e2 = proj_error(c, lim, f0, f1, xqd, ep);
+                            if (e2 > err) {
+                                xqd[p] -= sign * st;
+                                break;
+                            }
+                            err = e2;
+                            if (sign < 0)
+                                moved_down = 1;
+                            if (st != 2)
+                                break;
+                        }
+                        if (moved_down)
+                            break;
+                    }
+                    if (moved_down)
+                        break;
+                }
+        if (best_err == -1 || err < best_err)
+            *best_ep = ep, best_err = err, best_xqd[0] = xqd[0], best_xqd[1] = xqd[1];
+    }
+    free(f0), free(f1);
+}
+
+static int sgr_bits(const int *ep_xqd /* ep, xqd0, xqd1 */, const int *ref_xqd) { /* count_sgrproj_bits :655 */
+    int bits = 4;
+    if (sg_r[ep_xqd[0]][0] > 0)
+        bits += count_refsubexpfin(sg_max[0] - sg_min[0] + 1, 4, ref_xqd[0] - sg_min[0], ep_xqd[1] - sg_min[0]);
+    if (sg_r[ep_xqd[0]][1] > 0)
+        bits += count_refsubexpfin(sg_max[1] - sg_min[1] + 1, 4, ref_xqd[1] - sg_min[1], ep_xqd[2] - sg_min[1]);
+    return bits;
+}
+
+/* what rest_finish_search keeps per unit across the planes (its `rusi` array is allocated and zeroed ONCE, before the
+ * plane loop :1570-1577, so entries a plane does not refresh still hold the previous plane's values) */
+typedef struct {
+    int64_t sse[3];
+    int16_t vf[8], hf[8];
+    int     sgr[3]; /* ep, xqd0, xqd1 */
+    int     best[3]; /* best_rtype[WIENER - 1], [SGRPROJ - 1], [SWITCHABLE - 1] */
+} finish_unit;
+
 ORC_API int orc_lr_search_frame(const svtf_geom *g, const void *y, int sy, const void *cb, int scb, const void *cr, int scr, const void *oy,
                                 int osy, const void *ocb, int oscb, const void *ocr, int oscr, const svtf_lr_search_cfg *cfg,
-                                int32_t out_type[3], svtf_lr_unit *const out_units[3], svtf_lr_unit_search *const out_search[3]) {
+                                int32_t out_type[3], svtf_lr_unit *const out_units[3], svtf_lr_unit_search *const out_search[3],
+                                int32_t sg_frame_ep_cnt[16]) {
     const void *const cur[3] = {y, cb, cr}, *const src[3] = {oy, ocb, ocr};
     const int         cst[3] = {sy, scb, scr}, sst[3] = {osy, oscb, oscr};
-    if (cfg->sg_enabled)
-        return -1;
-    const int planes = cfg->wn_enabled && cfg->wn_use_chroma ? 3 : 1;
+    const int wn = cfg->wn_enabled != 0, sg = cfg->sg_enabled != 0;
+    const int planes  = (wn && cfg->wn_use_chroma) || (sg && cfg->sg_use_chroma) ? 3 : 1;
     const int wn_luma = cfg->wn_filter_tap_lvl == 1 ? 7 : (cfg->wn_filter_tap_lvl == 2 ? 5 : 3);
+    int       n0;
+    {
+        int hu, vu;
+        orc_lr_units(g, 0, cfg->restoration_unit_size[0], &hu, &vu);
+        n0 = hu * vu;
+    }
+    finish_unit *fu = calloc(n0, sizeof(*fu));
+    if (sg_frame_ep_cnt)
+        memset(sg_frame_ep_cnt, 0, sizeof(int32_t) * 16);
     for (int p = 0; p < 3; p++) {
         out_type[p] = SVTF_RESTORE_NONE;
         int hu, vu;
@@ -295,67 +435,123 @@ ORC_API int orc_lr_search_frame(const svtf_geom *g, const void *y, int sy, const
     }
     for (int p = 0; p < planes; p++) {
         const int ss = p ? 1 : 0, U = cfg->restoration_unit_size[p], off = 8 >> ss, win = p ? IMIN(wn_luma, 5) : wn_luma;
+        const int do_wn = wn && (!p || cfg->wn_use_chroma), do_sg = sg && (!p || cfg->sg_use_chroma);
         plane_ctx c = {cur[p], src[p], cst[p], sst[p], g->sample_bytes, g->bit_depth, ss, (g->width + ss) >> ss, (g->height + ss) >> ss};
         int       hu, vu;
         orc_lr_units(g, p, U, &hu, &vu);
-        svtf_lr_unit_search *us = calloc((size_t)hu * vu, sizeof(*us));
+        const int            n  = hu * vu;
+        svtf_lr_unit_search *us = calloc((size_t)n, sizeof(*us));
         int64_t             *M = malloc(sizeof(int64_t) * WIN2), *H = malloc(sizeof(int64_t) * WIN2 * WIN2);
         if (!us || !M || !H)
             return -1;
-        /* ---- per unit: SSE unfiltered, Wiener taps + refined SSE ---- */
-        for (int u = 0; u < hu * vu; u++) {
+        /* ---- restoration_seg_search: per unit ---- */
+        for (int u = 0; u < n; u++) {
             const int ur = u / hu, uc = u % hu;
             const int lim[4] = {uc * U, uc == hu - 1 ? c.pw : (uc + 1) * U, IMAX(0, ur * U - off), ur == vu - 1 ? c.ph : (ur + 1) * U - off};
             svtf_lr_unit none;
             memset(&none, 0, sizeof(none));
             us[u].sse[0] = orc_lr_try_unit(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, ss, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], &none);
             us[u].sse[1] = INT64_MAX;
-            if (!cfg->wn_enabled)
-                continue;
-            orc_lr_wiener_stats(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], win, M, H);
-            int16_t vf[8], hf[8];
-            if (!orc_lr_wiener_from_stats(win, M, H, vf, hf))
-                continue;
-            us[u].sse[1] = refine(&c, lim, win, cfg, vf, hf);
-            memcpy(us[u].wiener_vfilter, vf, 16), memcpy(us[u].wiener_hfilter, hf, 16);
-        }
-        /* ---- frame decision: RESTORE_NONE against RESTORE_WIENER with per-unit on/off (search_wiener_finish) ---- */
-        int64_t sse_none = 0, sse_w = 0, bits_w = 0;
-        int16_t rvf[8] = {3, -7, 15, -22, 15, -7, 3, 0}, rhf[8] = {3, -7, 15, -22, 15, -7, 3, 0}; /* set_default_wiener */
-        for (int u = 0; u < hu * vu; u++) sse_none += us[u].sse[0];
-        if (cfg->wn_enabled) {
-            for (int u = 0; u < hu * vu; u++) {
-                const int64_t bits_none = cfg->wiener_restore_cost[0];
-                us[u].best_rtype        = SVTF_RESTORE_NONE;
-                if (us[u].sse[1] == INT64_MAX) {
-                    bits_w += bits_none, sse_w += us[u].sse[0];
-                    continue;
+            if (do_wn) {
+                orc_lr_wiener_stats(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], win, M, H);
+                int16_t vf[8], hf[8];
+                if (orc_lr_wiener_from_stats(win, M, H, vf, hf)) {
+                    us[u].sse[1] = refine(&c, lim, win, cfg, vf, hf);
+                    memcpy(us[u].wiener_vfilter, vf, 16), memcpy(us[u].wiener_hfilter, hf, 16);
                 }
-                const int64_t bits_wn = cfg->wiener_restore_cost[1] +
-                    ((int64_t)wiener_bits(win, us[u].wiener_vfilter, us[u].wiener_hfilter, rvf, rhf) << 9);
-                const double cn = rdcost(cfg->rdmult, bits_none >> 4, us[u].sse[0]), cw = rdcost(cfg->rdmult, bits_wn >> 4, us[u].sse[1]);
-                if (cw < cn) {
-                    us[u].best_rtype = SVTF_RESTORE_WIENER;
-                    sse_w += us[u].sse[1], bits_w += bits_wn;
-                    memcpy(rvf, us[u].wiener_vfilter, 16), memcpy(rhf, us[u].wiener_hfilter, 16);
-                } else
-                    sse_w += us[u].sse[0], bits_w += bits_none;
             }
-            const double cost_none = rdcost(cfg->rdmult, 0, sse_none), cost_w = rdcost(cfg->rdmult, bits_w >> 4, sse_w);
-            if (cost_w < cost_none) {
-                out_type[p] = SVTF_RESTORE_WIENER;
-                for (int u = 0; u < hu * vu; u++) { /* copy_unit_info :1202 */
-                    out_units[p][u].restoration_type = us[u].best_rtype;
-                    if (us[u].best_rtype == SVTF_RESTORE_WIENER) {
-                        memcpy(out_units[p][u].wiener_vfilter, us[u].wiener_vfilter, 16);
-                        memcpy(out_units[p][u].wiener_hfilter, us[u].wiener_hfilter, 16);
+            if (do_sg) {
+                int ep, xqd[2];
+                search_sgr_unit(&c, lim, cfg->sg_start_ep[p > 0], cfg->sg_end_ep[p > 0], cfg->sg_ep_inc[p > 0], cfg->sg_refine[p > 0], &ep, xqd);
+                us[u].sgr_ep = ep, us[u].sgr_xqd[0] = xqd[0], us[u].sgr_xqd[1] = xqd[1];
+                if (sg_frame_ep_cnt)
+                    sg_frame_ep_cnt[ep]++;
+                svtf_lr_unit t;
+                memset(&t, 0, sizeof(t));
+                t.restoration_type = SVTF_RESTORE_SGRPROJ, t.sgr_ep = ep, t.sgr_xqd[0] = xqd[0], t.sgr_xqd[1] = xqd[1];
+                us[u].sse[2] = orc_lr_try_unit(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, ss, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], &t);
+            }
+        }
+        /* ---- rest_finish_search: cost of every frame type that applies, per-unit decisions in raster order ---- */
+        const int force = wn ? (sg ? 4 : 1) : (sg ? 2 : 0); /* RESTORE_TYPES = 4: all */
+        double    best_cost = 0;
+        int       best_type = 0;
+        for (int r = 0; r < (n > 1 ? 4 : 3); r++) {
+            if (force != 4 && r != 0 && r != force)
+                continue;
+            if (p && ((r == 1 && !cfg->wn_use_chroma) || (r == 2 && !cfg->sg_use_chroma)))
+                continue;
+            int64_t sse = 0, bits = 0;
+            int16_t rvf[8] = {3, -7, 15, -22, 15, -7, 3, 0}, rhf[8] = {3, -7, 15, -22, 15, -7, 3, 0}; /* set_default_wiener */
+            int     rsg[2] = {-32, 31};                                                              /* set_default_sgrproj */
+            for (int u = 0; u < n; u++) {
+                finish_unit *f = &fu[u];
+                if (r == 0) {
+                    f->sse[0] = us[u].sse[0];
+                    sse += f->sse[0];
+                } else if (r == 1) { /* search_wiener_finish */
+                    const int64_t bits_none = cfg->wiener_restore_cost[0];
+                    f->sse[1] = us[u].sse[1];
+                    if (f->sse[1] == INT64_MAX) {
+                        bits += bits_none, sse += f->sse[0], f->best[0] = 0;
+                        continue;
                     }
+                    memcpy(f->vf, us[u].wiener_vfilter, 16), memcpy(f->hf, us[u].wiener_hfilter, 16);
+                    const int64_t bw = cfg->wiener_restore_cost[1] + ((int64_t)wiener_bits(win, f->vf, f->hf, rvf, rhf) << 9);
+                    const double  cn = rdcost(cfg->rdmult, bits_none >> 4, f->sse[0]), cw = rdcost(cfg->rdmult, bw >> 4, f->sse[1]);
+                    f->best[0] = cw < cn ? 1 : 0;
+                    sse += f->sse[f->best[0]], bits += cw < cn ? bw : bits_none;
+                    if (cw < cn)
+                        memcpy(rvf, f->vf, 16), memcpy(rhf, f->hf, 16);
+                } else if (r == 2) { /* search_sgrproj_finish */
+                    f->sse[2] = us[u].sse[2];
+                    f->sgr[0] = us[u].sgr_ep, f->sgr[1] = us[u].sgr_xqd[0], f->sgr[2] = us[u].sgr_xqd[1];
+                    const int64_t bits_none = cfg->sgrproj_restore_cost[0];
+                    const int64_t bs = cfg->sgrproj_restore_cost[1] + ((int64_t)sgr_bits(f->sgr, rsg) << 9);
+                    const double  cn = rdcost(cfg->rdmult, bits_none >> 4, f->sse[0]), cs = rdcost(cfg->rdmult, bs >> 4, f->sse[2]);
+                    f->best[1] = cs < cn ? 2 : 0;
+                    sse += f->sse[f->best[1]], bits += cs < cn ? bs : bits_none;
+                    if (cs < cn)
+                        rsg[0] = f->sgr[1], rsg[1] = f->sgr[2];
+                } else { /* search_switchable */
+                    double  bc = 0;
+                    int64_t bb = 0;
+                    int     bt = 0;
+                    for (int t = 0; t < 3; t++) {
+                        if (t > 0 && f->best[t - 1] == 0)
+                            continue;
+                        const int64_t coeff = t == 1 ? wiener_bits(p ? 5 : 7, f->vf, f->hf, rvf, rhf) : (t == 2 ? sgr_bits(f->sgr, rsg) : 0);
+                        const int64_t b     = cfg->switchable_restore_cost[t] + (coeff << 9);
+                        const double  cost  = rdcost(cfg->rdmult, b >> 4, f->sse[t]);
+                        if (t == 0 || cost < bc)
+                            bc = cost, bb = b, bt = t;
+                    }
+                    f->best[2] = bt;
+                    sse += f->sse[bt], bits += bb;
+                    if (bt == 1)
+                        memcpy(rvf, f->vf, 16), memcpy(rhf, f->hf, 16);
+                    if (bt == 2)
+                        rsg[0] = f->sgr[1], rsg[1] = f->sgr[2];
                 }
             }
+            const double cost = rdcost(cfg->rdmult, bits >> 4, sse);
+            if (r == 0 || cost < best_cost)
+                best_cost = cost, best_type = r;
         }
+        out_type[p] = best_type;
+        if (best_type != 0)
+            for (int u = 0; u < n; u++) { /* copy_unit_info :1202 */
+                svtf_lr_unit *o = &out_units[p][u];
+                o->restoration_type = fu[u].best[best_type - 1];
+                if (o->restoration_type == SVTF_RESTORE_WIENER)
+                    memcpy(o->wiener_vfilter, fu[u].vf, 16), memcpy(o->wiener_hfilter, fu[u].hf, 16);
+                else if (o->restoration_type == SVTF_RESTORE_SGRPROJ)
+                    o->sgr_ep = fu[u].sgr[0], o->sgr_xqd[0] = fu[u].sgr[1], o->sgr_xqd[1] = fu[u].sgr[2];
+            }
         if (out_search && out_search[p])
-            memcpy(out_search[p], us, sizeof(*us) * hu * vu);
+            memcpy(out_search[p], us, sizeof(*us) * n);
         free(us), free(M), free(H);
     }
+    free(fu);
     return 0;
 }

@@ -65,15 +65,18 @@ class LrParams(C.Structure):
 
 
 class LrSearchCfg(C.Structure):
-    """svtf_lr_search_cfg (WnFilterCtrls, Common/Codec/Av1Common.h:32-45; Macroblock.rdmult / wiener_restore_cost)"""
+    """svtf_lr_search_cfg (WnFilterCtrls / SgFilterCtrls, Common/Codec/Av1Common.h:32-60; Macroblock.rdmult / *_restore_cost)"""
     _fields_ = [("restoration_unit_size", C.c_int32 * 3), ("wn_enabled", C.c_int32), ("wn_filter_tap_lvl", C.c_int32),
                 ("wn_use_refinement", C.c_int32), ("wn_max_one_refinement_step", C.c_int32), ("wn_use_chroma", C.c_int32),
-                ("sg_enabled", C.c_int32), ("rdmult", C.c_int32), ("wiener_restore_cost", C.c_int32 * 2)]
+                ("sg_enabled", C.c_int32), ("sg_use_chroma", C.c_int32), ("sg_start_ep", C.c_int32 * 2), ("sg_end_ep", C.c_int32 * 2),
+                ("sg_ep_inc", C.c_int32 * 2), ("sg_refine", C.c_int32 * 2), ("rdmult", C.c_int32), ("wiener_restore_cost", C.c_int32 * 2),
+                ("sgrproj_restore_cost", C.c_int32 * 2), ("switchable_restore_cost", C.c_int32 * 3)]
 
 
 class LrUnitSearch(C.Structure):
     """svtf_lr_unit_search (RestUnitSearchInfo, Common/Codec/EbRestoration.h:349)"""
-    _fields_ = [("sse", C.c_int64 * 2), ("wiener_vfilter", C.c_int16 * 8), ("wiener_hfilter", C.c_int16 * 8), ("best_rtype", C.c_int32)]
+    _fields_ = [("sse", C.c_int64 * 3), ("wiener_vfilter", C.c_int16 * 8), ("wiener_hfilter", C.c_int16 * 8), ("sgr_ep", C.c_int32),
+                ("sgr_xqd", C.c_int32 * 2), ("reserved", C.c_int32)]
 
 
 class LfSearchCfg(C.Structure):
@@ -138,7 +141,8 @@ def load():
     lib.svtf_get_mi.argtypes = [vp, vp, i32]
     lib.svtf_lr_units.argtypes = [C.POINTER(Geom), i32, i32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.svtf_lr_apply_frame.argtypes = [vp, C.POINTER(LrParams), C.POINTER(C.c_void_p)]
-    lib.svtf_lr_search_frame.argtypes = [vp, C.POINTER(LrSearchCfg), C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+    lib.svtf_lr_search_frame.argtypes = [vp, C.POINTER(LrSearchCfg), C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                         C.POINTER(C.c_int32)]
     lib.svtf_lr_wiener_stats.argtypes = [vp, i32, i32, i32, vp, vp]
     lib.svtf_lr_wiener_from_stats.argtypes = [i32, vp, vp, C.POINTER(C.c_int16), C.POINTER(C.c_int16)]
     lib.svtf_deblock_frame.argtypes = [vp, C.POINTER(LfParams), i32, i32]

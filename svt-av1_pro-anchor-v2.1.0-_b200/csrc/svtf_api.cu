@@ -118,6 +118,8 @@ struct svtf_ctx {
     size_t       lrs_cap = 0;
     uint8_t     *h_lrs = nullptr;          // pinned mirror of the parts of d_lrs that cross PCIe every refinement round
     size_t       h_lrs_cap = 0;
+    int32_t     *d_lrs_flt = nullptr;      // filter outputs of the self-guided search's current ep (two int32 planes per plane)
+    size_t       lrs_flt_cap = 0;
     uint8_t     *d_handoff = nullptr;      // staging of svtf_download_ref_padded / svtf_upload_frame_8as16, allocated on first use
     size_t       handoff_cap = 0;
     bool         search3_ready = false;    // same for cdef_search3_kernel
@@ -240,7 +242,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
-    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff), cudaFree(c->d_lrs);
+    cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff), cudaFree(c->d_lrs), cudaFree(c->d_lrs_flt);
     if (c->h_lrs) cudaFreeHost(c->h_lrs);
     if (c->h_mi_bad)
         cudaFreeHost(c->h_mi_bad);
@@ -1710,7 +1712,7 @@ struct LrsPlan {
     size_t                          acc_total = 0;
     int                             units = 0;
     // device carve-up
-    size_t o_tiles = 0, o_sum = 0, o_sse = 0, o_count = 0, o_off = 0, o_acc = 0, o_trial = 0, o_units = 0, bytes = 0;
+    size_t o_tiles = 0, o_sum = 0, o_sse = 0, o_count = 0, o_off = 0, o_acc = 0, o_trial = 0, o_units = 0, o_proj = 0, bytes = 0;
 };
 
 // Units of a plane (foreach_rest_unit_in_tile, Common/Codec/EbRestoration.c:1250): raster order, the last one of a row /
@@ -1746,6 +1748,7 @@ int lrs_reserve(svtf_ctx *c, LrsPlan &plan) {
     carve(plan.o_sum, 8 * (size_t)plan.units), carve(plan.o_sse, 8 * (size_t)plan.units), carve(plan.o_trial, 8 * (size_t)plan.units);
     carve(plan.o_count, 4 * (size_t)plan.units), carve(plan.o_off, 8 * (size_t)plan.units);
     carve(plan.o_units, sizeof(LrUnitDev) * (size_t)plan.units);
+    carve(plan.o_proj, 40 * (size_t)plan.units);
     carve(plan.o_acc, 8 * plan.acc_total);
     if (plan.bytes > c->lrs_cap) {
         if (c->d_lrs) {
@@ -1769,7 +1772,8 @@ int lrs_reserve(svtf_ctx *c, LrsPlan &plan) {
 }
 
 // Uploads the plan, runs the per-unit sums (and, with stats, the Wiener statistics) and brings the results to the host.
-int lrs_measure(svtf_ctx *c, LrsPlan &plan, bool stats, const unsigned long long *&sse_none, const long long *&acc) {
+int lrs_measure(svtf_ctx *c, LrsPlan &plan, const bool stats_of[3], const unsigned long long *&sse_none, const long long *&acc) {
+    const bool stats = stats_of[0] || stats_of[1] || stats_of[2];
     if (int r = lrs_reserve(c, plan))
         return r;
     uint8_t *d = c->d_lrs, *h = c->h_lrs;
@@ -1805,6 +1809,10 @@ int lrs_measure(svtf_ctx *c, LrsPlan &plan, bool stats, const unsigned long long
         for (const LrsPlane &pl : plan.planes) {
             int t1 = t0;
             while (t1 < nt && plan.tiles[t1].plane == pl.plane) t1++;
+            if (!stats_of[pl.plane]) {
+                t0 = t1;
+                continue;
+            }
             LrsArgs b = a;
             b.tiles   = a.tiles + t0;
             const int n = t1 - t0;
@@ -1872,26 +1880,76 @@ extern "C" int svtf_lr_wiener_stats(svtf_ctx *c, int32_t plane, int32_t unit_siz
     lrs_add_plane(c->geom, plan, plane, unit_size, wiener_win);
     const unsigned long long *sse;
     const long long          *acc;
-    if (int r = lrs_measure(c, plan, true, sse, acc))
+    const bool all[3] = {true, true, true};
+    if (int r = lrs_measure(c, plan, all, sse, acc))
         return r;
     const int win2 = wiener_win * wiener_win;
     for (int u = 0; u < plan.units; u++) lrs_finish_stats(c->geom, wiener_win, acc + plan.acc_off[u], M + (size_t)u * win2, H + (size_t)u * win2 * win2);
     return SVTF_OK;
 }
 
+namespace {
+// LrArgs of a measuring launch (LR_SSE / LR_FLT) over the planes whose `active` flag is set; returns the grid size
+int lrs_trial_args(svtf_ctx *c, const LrsPlan &plan, const bool active[3], int frame_type, LrArgs &a) {
+    uint8_t *d = c->d_lrs;
+    a.cur = a.dbk = c->surf[c->cur].planes();
+    a.out = a.cur; // never written by the measuring instantiations
+    a.src = c->source.planes();
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        a.pw[p] = (c->geom.width + ss) >> ss, a.ph[p] = (c->geom.height + ss) >> ss;
+        a.cw[p] = a.pw[p], a.chh[p] = a.ph[p]; // only the visible picture is measured
+        a.unit[p] = 0, a.hu[p] = a.vu[p] = 0, a.units[p] = nullptr, a.sse[p] = nullptr, a.proj[p] = nullptr;
+        a.frame_type[p] = SVTF_RESTORE_NONE, a.chunks[p] = a.stripes[p] = 0;
+    }
+    for (const LrsPlane &pl : plan.planes) {
+        const int p = pl.plane, ss = p ? 1 : 0, sh = 64 >> ss, off = 8 >> ss;
+        if (!active[p])
+            continue;
+        a.unit[p] = pl.unit, a.hu[p] = pl.hu, a.vu[p] = pl.vu;
+        a.units[p]      = reinterpret_cast<const LrUnitDev *>(d + plan.o_units) + pl.first;
+        a.sse[p]        = reinterpret_cast<unsigned long long *>(d + plan.o_trial) + pl.first;
+        a.proj[p]       = reinterpret_cast<long long *>(d + plan.o_proj) + 5 * (size_t)pl.first;
+        a.frame_type[p] = frame_type;
+        a.chunks[p]     = (a.cw[p] + (LR_MAXW >> ss) - 1) / (LR_MAXW >> ss);
+        a.stripes[p]    = (a.ph[p] + off + sh - 1) / sh + 1;
+    }
+    int grid = 0;
+    for (int p = 0; p < 3; p++) a.base[p] = grid, grid += a.chunks[p] * a.stripes[p];
+    a.opt = 2, a.bd = c->geom.bit_depth;
+    return grid;
+}
+
+template <int MODE>
+int lrs_launch_lr(svtf_ctx *c, const LrArgs &a, int grid) {
+    if (grid <= 0)
+        return SVTF_OK;
+    if (c->geom.sample_bytes == 1)
+        lr_kernel<uint8_t, MODE><<<grid, LR_THREADS, 0, c->stream>>>(a);
+    else
+        lr_kernel<uint16_t, MODE><<<grid, LR_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    return SVTF_OK;
+}
+} // namespace
+
 extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, int32_t out_frame_type[3], svtf_lr_unit *const out_units[3],
-                                    svtf_lr_unit_search *const out_search[3]) {
+                                    svtf_lr_unit_search *const out_search[3], int32_t sg_frame_ep_cnt[16]) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_lr_search_frame: NULL context");
     if (!cfg || !out_frame_type || !out_units)
         return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: NULL argument");
-    if (cfg->sg_enabled)
-        return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: the self-guided search is not covered");
-    if (cfg->wn_enabled && (cfg->wn_filter_tap_lvl < 1 || cfg->wn_filter_tap_lvl > 3))
+    const bool wn = cfg->wn_enabled != 0, sg = cfg->sg_enabled != 0;
+    if (wn && (cfg->wn_filter_tap_lvl < 1 || cfg->wn_filter_tap_lvl > 3))
         return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: wn_filter_tap_lvl must be 1..3");
+    if (sg)
+        for (int t = 0; t < 2; t++)
+            if (cfg->sg_start_ep[t] < 0 || cfg->sg_end_ep[t] > 16 || cfg->sg_ep_inc[t] < 1)
+                return c->fail(SVTF_E_ARG, "svtf_lr_search_frame: self-guided ep range must lie in [0, 16) with a positive increment");
     if (int r = lrs_check(c, "svtf_lr_search_frame"))
         return r;
-    const int nplanes = cfg->wn_enabled && cfg->wn_use_chroma ? 3 : 1;
+    const int nplanes = (wn && cfg->wn_use_chroma) || (sg && cfg->sg_use_chroma) ? 3 : 1;
     const int wn_luma = cfg->wn_filter_tap_lvl == 1 ? 7 : (cfg->wn_filter_tap_lvl == 2 ? 5 : 3);
     for (int p = 0; p < 3; p++) {
         if (!lrs_unit_size_ok(p, cfg->restoration_unit_size[p]) || !out_units[p])
@@ -1901,6 +1959,8 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
         out_frame_type[p] = SVTF_RESTORE_NONE;
         std::memset(out_units[p], 0, sizeof(svtf_lr_unit) * hu * vu);
     }
+    if (sg_frame_ep_cnt)
+        std::memset(sg_frame_ep_cnt, 0, sizeof(int32_t) * 16);
     CUDA_TRY(c, cudaSetDevice(c->device));
     const bool timing = std::getenv("SVTF_LRS_TIMING") != nullptr;
     auto       now    = [] { return std::chrono::steady_clock::now(); };
@@ -1908,25 +1968,29 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
         return std::chrono::duration<double, std::milli>(b - a).count();
     };
     const auto t_start = now();
-    LrsPlan plan;
-    for (int p = 0; p < nplanes; p++) lrs_add_plane(c->geom, plan, p, cfg->restoration_unit_size[p], p ? std::min(wn_luma, 5) : wn_luma);
+    LrsPlan    plan;
+    bool       do_wn[3] = {false, false, false}, do_sg[3] = {false, false, false};
+    for (int p = 0; p < nplanes; p++) {
+        do_wn[p] = wn && (!p || cfg->wn_use_chroma), do_sg[p] = sg && (!p || cfg->sg_use_chroma);
+        lrs_add_plane(c->geom, plan, p, cfg->restoration_unit_size[p], p ? std::min(wn_luma, 5) : wn_luma);
+    }
     const unsigned long long *sse_none;
     const long long          *acc;
-    if (int r = lrs_measure(c, plan, cfg->wn_enabled != 0, sse_none, acc))
+    if (int r = lrs_measure(c, plan, do_wn, sse_none, acc))
         return r;
-    const auto t_measured = now();
+    const auto                       t_measured = now();
     std::vector<svtf_lr_unit_search> us(plan.units);
     std::vector<LrsRefine>           ref(plan.units);
     // the solve of a unit (integer alternating least squares, ~20k multiply-divides for a 7x7 window) is independent of every
     // other unit: a few host threads share them (the reference spreads units over its restoration segments the same way)
-    std::vector<int> win_of(plan.units);
+    std::vector<int> win_of(plan.units), plane_of(plan.units);
     for (const LrsPlane &pl : plan.planes)
-        for (int u = 0; u < pl.hu * pl.vu; u++) win_of[pl.first + u] = pl.win;
+        for (int u = 0; u < pl.hu * pl.vu; u++) win_of[pl.first + u] = pl.win, plane_of[pl.first + u] = pl.plane;
     host_parallel_for(plan.units, [&](int u) {
         svtf_lr_unit_search &s = us[u];
         std::memset(&s, 0, sizeof(s));
         s.sse[0] = (int64_t)sse_none[u], s.sse[1] = INT64_MAX;
-        if (!cfg->wn_enabled)
+        if (!do_wn[plane_of[u]])
             return;
         int64_t M[49], H[49 * 49];
         lrs_finish_stats(c->geom, win_of[u], acc + plan.acc_off[u], M, H);
@@ -1935,35 +1999,24 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
             ref[u].start(win_of[u], cfg->wn_use_refinement != 0, cfg->wn_max_one_refinement_step != 0, vf, hf);
     });
     const auto t_solved = now();
-    int        rounds   = 0;
-    // ---- refinement in lock-step: one launch filters every unit that has a trial pending and measures it ----
-    if (cfg->wn_enabled) {
-        uint8_t *d = c->d_lrs;
-        LrArgs   a;
-        a.cur = a.dbk = c->surf[c->cur].planes();
-        a.out = a.cur; // never written by the SSE instantiation
-        a.src = c->source.planes();
-        int grid = 0;
-        for (int p = 0; p < 3; p++) {
-            const int ss = p ? 1 : 0;
-            a.pw[p] = (c->geom.width + ss) >> ss, a.ph[p] = (c->geom.height + ss) >> ss;
-            a.cw[p] = a.pw[p], a.chh[p] = a.ph[p]; // only the visible picture is measured
-            a.unit[p] = 0, a.hu[p] = a.vu[p] = 0, a.units[p] = nullptr, a.sse[p] = nullptr;
-            a.frame_type[p] = SVTF_RESTORE_NONE, a.chunks[p] = a.stripes[p] = 0, a.base[p] = grid;
-        }
-        for (const LrsPlane &pl : plan.planes) {
-            const int p = pl.plane, ss = p ? 1 : 0, sh = 64 >> ss, off = 8 >> ss;
-            a.unit[p] = pl.unit, a.hu[p] = pl.hu, a.vu[p] = pl.vu;
-            a.units[p]      = reinterpret_cast<const LrUnitDev *>(d + plan.o_units) + pl.first;
-            a.sse[p]        = reinterpret_cast<unsigned long long *>(d + plan.o_trial) + pl.first;
-            a.frame_type[p] = SVTF_RESTORE_WIENER;
-            a.chunks[p]     = (a.cw[p] + (LR_MAXW >> ss) - 1) / (LR_MAXW >> ss);
-            a.stripes[p]    = (a.ph[p] + off + sh - 1) / sh + 1;
-        }
-        for (int p = 0; p < 3; p++) a.base[p] = grid, grid += a.chunks[p] * a.stripes[p];
-        a.opt = 2, a.bd = c->geom.bit_depth;
-        LrUnitDev                *host  = reinterpret_cast<LrUnitDev *>(c->h_lrs + plan.o_units);
-        const unsigned long long *trial = reinterpret_cast<const unsigned long long *>(c->h_lrs + plan.o_trial);
+    int        rounds = 0, sg_rounds = 0;
+    uint8_t   *d = c->d_lrs;
+    LrUnitDev *host = reinterpret_cast<LrUnitDev *>(c->h_lrs + plan.o_units);
+    const unsigned long long *trial = reinterpret_cast<const unsigned long long *>(c->h_lrs + plan.o_trial);
+    // one measuring round: upload the candidates in `host`, zero the counters, run `launch`, fetch the counters
+    auto round_trip = [&](auto launch) -> int {
+        CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host, sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(c, cudaMemsetAsync(d + plan.o_trial, 0, 8 * (size_t)plan.units, c->stream));
+        if (int r = launch())
+            return r;
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_trial, d + plan.o_trial, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        return SVTF_OK;
+    };
+    // ---- Wiener refinement in lock-step: one launch filters every unit that has a trial pending and measures it ----
+    if (wn) {
+        LrArgs    a;
+        const int grid = lrs_trial_args(c, plan, do_wn, SVTF_RESTORE_WIENER, a);
         for (;;) {
             int pending = 0;
             for (int u = 0; u < plan.units; u++) {
@@ -1978,65 +2031,225 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
             if (!pending)
                 break;
             rounds++;
-            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host, sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
-            CUDA_TRY(c, cudaMemsetAsync(d + plan.o_trial, 0, 8 * (size_t)plan.units, c->stream));
-            if (c->geom.sample_bytes == 1)
-                lr_kernel<uint8_t, true><<<grid, LR_THREADS, 0, c->stream>>>(a);
-            else
-                lr_kernel<uint16_t, true><<<grid, LR_THREADS, 0, c->stream>>>(a);
-            CUDA_TRY(c, cudaGetLastError());
-            c->launches++;
-            CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_trial, d + plan.o_trial, 8 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
-            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            if (int r = round_trip([&] { return lrs_launch_lr<LR_SSE>(c, a, grid); }))
+                return r;
             for (int u = 0; u < plan.units; u++)
                 if (ref[u].pending())
                     ref[u].feed((int64_t)trial[u]);
         }
+        for (int u = 0; u < plan.units; u++)
+            if (ref[u].started) {
+                us[u].sse[1] = ref[u].err;
+                std::memcpy(us[u].wiener_vfilter, ref[u].vf, 16), std::memcpy(us[u].wiener_hfilter, ref[u].hf, 16);
+            }
+    }
+    const auto t_wiener = now();
+    // ---- self-guided search (search_selfguided_restoration :550): the ep candidates one after the other, all units in lock-step ----
+    if (sg) {
+        // filter outputs of the candidate ep: two int32 planes per searched plane
+        size_t need = 0, off_p[3] = {0, 0, 0}, half[3] = {0, 0, 0};
+        const Planes cur = c->surf[c->cur].planes();
+        for (int p = 0; p < 3; p++)
+            if (do_sg[p]) {
+                const int ss = p ? 1 : 0;
+                half[p]  = (size_t)cur.pitch[p] * (((c->geom.height + ss) >> ss) + 1);
+                off_p[p] = need, need += 2 * half[p];
+            }
+        if (need * 4 > c->lrs_flt_cap) {
+            if (c->d_lrs_flt) {
+                CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+                CUDA_TRY(c, cudaFree(c->d_lrs_flt));
+                c->d_lrs_flt = nullptr, c->lrs_flt_cap = 0;
+            }
+            CUDA_TRY(c, cudaMalloc(&c->d_lrs_flt, need * 4));
+            c->lrs_flt_cap = need * 4;
+        }
+        LrArgs fa;
+        LrsProjArgs pa;
+        pa.cur = cur, pa.src = c->source.planes();
+        pa.tiles = reinterpret_cast<const LrsTile *>(d + plan.o_tiles);
+        pa.units = reinterpret_cast<const LrUnitDev *>(d + plan.o_units);
+        pa.err   = reinterpret_cast<unsigned long long *>(d + plan.o_trial);
+        for (int p = 0; p < 3; p++) pa.flt[p] = c->d_lrs_flt + off_p[p], pa.flt_half[p] = half[p];
+        std::vector<LrsSgRefine> sref(plan.units);
+        std::vector<int64_t>     best_err(plan.units, -1);
+        const long long         *proj = reinterpret_cast<const long long *>(c->h_lrs + plan.o_proj);
+        for (int k = 0;; k++) {
+            bool act[3] = {false, false, false};
+            int  ep_of[3] = {0, 0, 0}, any = 0;
+            for (int p = 0; p < 3; p++) {
+                ep_of[p] = cfg->sg_start_ep[p > 0] + k * cfg->sg_ep_inc[p > 0];
+                act[p]   = do_sg[p] && ep_of[p] < cfg->sg_end_ep[p > 0];
+                any += act[p];
+            }
+            if (!any)
+                break;
+            // the two guided filters of every unit for this ep + the sums of the projection
+            const int grid = lrs_trial_args(c, plan, act, 3 /* any restoring frame type */, fa);
+            for (int p = 0; p < 3; p++) fa.flt[p] = c->d_lrs_flt + off_p[p], fa.flt_half[p] = half[p];
+            for (int u = 0; u < plan.units; u++) {
+                std::memset(&host[u], 0, sizeof(LrUnitDev));
+                if (act[plane_of[u]])
+                    host[u].type = SVTF_RESTORE_SGRPROJ, host[u].ep = ep_of[plane_of[u]];
+            }
+            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host, sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
+            CUDA_TRY(c, cudaMemsetAsync(d + plan.o_proj, 0, 40 * (size_t)plan.units, c->stream));
+            if (int r = lrs_launch_lr<LR_FLT>(c, fa, grid))
+                return r;
+            CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_proj, d + plan.o_proj, 40 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            for (int u = 0; u < plan.units; u++)
+                if (act[plane_of[u]]) {
+                    int xqd[2];
+                    lrs_sg_initial_xqd(ep_of[plane_of[u]], proj + 5 * (size_t)u, plan.count[u], xqd);
+                    sref[u].start(ep_of[plane_of[u]], cfg->sg_refine[plane_of[u] > 0] != 0, xqd);
+                }
+            // the projection error of every pending candidate, in lock-step
+            const int nt = (int)plan.tiles.size();
+            for (;;) {
+                int pending = 0;
+                for (int u = 0; u < plan.units; u++) {
+                    std::memset(&host[u], 0, sizeof(LrUnitDev));
+                    if (!act[plane_of[u]] || !sref[u].pending())
+                        continue;
+                    pending++;
+                    host[u].type = SVTF_RESTORE_SGRPROJ, host[u].ep = ep_of[plane_of[u]];
+                    host[u].xqd[0] = sref[u].xqd[0], host[u].xqd[1] = sref[u].xqd[1];
+                }
+                if (!pending)
+                    break;
+                sg_rounds++;
+                if (int r = round_trip([&]() -> int {
+                        if (c->geom.sample_bytes == 1)
+                            lrs_proj_err_kernel<uint8_t><<<nt, LRS_THREADS, 0, c->stream>>>(pa);
+                        else
+                            lrs_proj_err_kernel<uint16_t><<<nt, LRS_THREADS, 0, c->stream>>>(pa);
+                        CUDA_TRY(c, cudaGetLastError());
+                        c->launches++;
+                        return SVTF_OK;
+                    }))
+                    return r;
+                for (int u = 0; u < plan.units; u++)
+                    if (act[plane_of[u]] && sref[u].pending())
+                        sref[u].feed((int64_t)trial[u]);
+            }
+            for (int u = 0; u < plan.units; u++)
+                if (act[plane_of[u]] && (best_err[u] == -1 || sref[u].err < best_err[u])) {
+                    best_err[u]  = sref[u].err;
+                    us[u].sgr_ep = ep_of[plane_of[u]], us[u].sgr_xqd[0] = sref[u].xqd[0], us[u].sgr_xqd[1] = sref[u].xqd[1];
+                }
+        }
+        // the unit filtered for real with the parameters found (clipping included): sse[RESTORE_SGRPROJ]
+        LrArgs    a;
+        const int grid = lrs_trial_args(c, plan, do_sg, SVTF_RESTORE_SGRPROJ, a);
+        for (int u = 0; u < plan.units; u++) {
+            std::memset(&host[u], 0, sizeof(LrUnitDev));
+            if (!do_sg[plane_of[u]])
+                continue;
+            host[u].type = SVTF_RESTORE_SGRPROJ, host[u].ep = us[u].sgr_ep, host[u].xqd[0] = us[u].sgr_xqd[0], host[u].xqd[1] = us[u].sgr_xqd[1];
+            if (sg_frame_ep_cnt)
+                sg_frame_ep_cnt[us[u].sgr_ep]++;
+        }
+        if (int r = round_trip([&] { return lrs_launch_lr<LR_SSE>(c, a, grid); }))
+            return r;
+        for (int u = 0; u < plan.units; u++)
+            if (do_sg[plane_of[u]])
+                us[u].sse[2] = (int64_t)trial[u];
     }
     if (timing)
-        std::fprintf(stderr, "svtf_lr_search_frame: plan+stats %.3f ms, host solve %.3f ms, %d refinement rounds %.3f ms\n", ms(t_start, t_measured),
-                     ms(t_measured, t_solved), rounds, ms(t_solved, now()));
-    // ---- search_wiener_finish :1380 per unit in raster order, then the frame decision (rest_finish_search :1596-1624) ----
+        std::fprintf(stderr, "svtf_lr_search_frame: plan+stats %.3f ms, host solve %.3f ms, %d Wiener rounds %.3f ms, self-guided (%d rounds) %.3f ms\n",
+                     ms(t_start, t_measured), ms(t_measured, t_solved), rounds, ms(t_solved, t_wiener), sg_rounds, ms(t_wiener, now()));
+    // ---- rest_finish_search :1555: the cost of every frame type that applies; per-unit decisions in raster order.  The
+    //      reference's per-unit array is allocated and zeroed once BEFORE the plane loop (:1570-1577), so what a plane does not
+    //      refresh (e.g. the Wiener entries of a chroma plane searched with the self-guided tools only) still holds the previous
+    //      plane's values when search_switchable reads it — kept as is. ----
+    struct FinishUnit {
+        int64_t sse[3];
+        int16_t vf[8], hf[8];
+        int     sgr_ep, sgr_xqd[2];
+        int     best[3]; // best_rtype[WIENER - 1], [SGRPROJ - 1], [SWITCHABLE - 1]
+    };
+    std::vector<FinishUnit> fu(plan.planes[0].hu * plan.planes[0].vu);
+    std::memset(fu.data(), 0, sizeof(FinishUnit) * fu.size());
+    const int force = wn ? (sg ? 4 : 1) : (sg ? 2 : 0); // force_restore_type_d; 4 = RESTORE_TYPES: all
     for (const LrsPlane &pl : plan.planes) {
-        const int n = pl.hu * pl.vu;
-        int64_t   sse_n = 0, sse_w = 0, bits_w = 0;
-        int16_t   rvf[8] = {3, -7, 15, -22, 15, -7, 3, 0}, rhf[8] = {3, -7, 15, -22, 15, -7, 3, 0}; // set_default_wiener
-        for (int u = 0; u < n; u++) sse_n += us[pl.first + u].sse[0];
-        if (cfg->wn_enabled) {
+        const int p = pl.plane, n = pl.hu * pl.vu;
+        double    best_cost = 0;
+        int       best_type = SVTF_RESTORE_NONE;
+        for (int r = 0; r < (n > 1 ? 4 : 3); r++) {
+            if (force != 4 && r != 0 && r != force)
+                continue;
+            if (p && ((r == 1 && !cfg->wn_use_chroma) || (r == 2 && !cfg->sg_use_chroma)))
+                continue;
+            int64_t sse = 0, bits = 0;
+            int16_t rvf[8] = {3, -7, 15, -22, 15, -7, 3, 0}, rhf[8] = {3, -7, 15, -22, 15, -7, 3, 0}; // set_default_wiener
+            int     rsg[2] = {-32, 31};                                                              // set_default_sgrproj
             for (int u = 0; u < n; u++) {
-                svtf_lr_unit_search &s = us[pl.first + u];
-                const LrsRefine     &r = ref[pl.first + u];
-                const int64_t bits_none = cfg->wiener_restore_cost[0];
-                s.best_rtype            = SVTF_RESTORE_NONE;
-                if (!r.started) { // no usable filter: the unit stays unrestored under RESTORE_WIENER
-                    bits_w += bits_none, sse_w += s.sse[0];
-                    continue;
-                }
-                s.sse[1] = r.err;
-                std::memcpy(s.wiener_vfilter, r.vf, 16), std::memcpy(s.wiener_hfilter, r.hf, 16);
-                const int64_t bits_wn = cfg->wiener_restore_cost[1] + ((int64_t)lrs_wiener_bits(pl.win, r.vf, r.hf, rvf, rhf) << 9);
-                const double  cn = lrs_rdcost(cfg->rdmult, bits_none >> 4, s.sse[0]), cw = lrs_rdcost(cfg->rdmult, bits_wn >> 4, s.sse[1]);
-                if (cw < cn) {
-                    s.best_rtype = SVTF_RESTORE_WIENER;
-                    sse_w += s.sse[1], bits_w += bits_wn;
-                    std::memcpy(rvf, r.vf, 16), std::memcpy(rhf, r.hf, 16);
-                } else
-                    sse_w += s.sse[0], bits_w += bits_none;
-            }
-            if (lrs_rdcost(cfg->rdmult, bits_w >> 4, sse_w) < lrs_rdcost(cfg->rdmult, 0, sse_n)) {
-                out_frame_type[pl.plane] = SVTF_RESTORE_WIENER;
-                for (int u = 0; u < n; u++) { // copy_unit_info :1202
-                    const svtf_lr_unit_search &s = us[pl.first + u];
-                    out_units[pl.plane][u].restoration_type = s.best_rtype;
-                    if (s.best_rtype == SVTF_RESTORE_WIENER) {
-                        std::memcpy(out_units[pl.plane][u].wiener_vfilter, s.wiener_vfilter, 16);
-                        std::memcpy(out_units[pl.plane][u].wiener_hfilter, s.wiener_hfilter, 16);
+                FinishUnit                &f = fu[u];
+                const svtf_lr_unit_search &s = us[pl.first + u];
+                if (r == 0) { // search_norestore_finish
+                    f.sse[0] = s.sse[0];
+                    sse += f.sse[0];
+                } else if (r == 1) { // search_wiener_finish :1380
+                    const int64_t bits_none = cfg->wiener_restore_cost[0];
+                    f.sse[1]                = s.sse[1];
+                    if (f.sse[1] == INT64_MAX) {
+                        bits += bits_none, sse += f.sse[0], f.best[0] = SVTF_RESTORE_NONE;
+                        continue;
                     }
+                    std::memcpy(f.vf, s.wiener_vfilter, 16), std::memcpy(f.hf, s.wiener_hfilter, 16);
+                    const int64_t bw = cfg->wiener_restore_cost[1] + ((int64_t)lrs_wiener_bits(pl.win, f.vf, f.hf, rvf, rhf) << 9);
+                    const double  cn = lrs_rdcost(cfg->rdmult, bits_none >> 4, f.sse[0]), cw = lrs_rdcost(cfg->rdmult, bw >> 4, f.sse[1]);
+                    f.best[0]        = cw < cn ? SVTF_RESTORE_WIENER : SVTF_RESTORE_NONE;
+                    sse += f.sse[f.best[0]], bits += cw < cn ? bw : bits_none;
+                    if (cw < cn)
+                        std::memcpy(rvf, f.vf, 16), std::memcpy(rhf, f.hf, 16);
+                } else if (r == 2) { // search_sgrproj_finish :1267
+                    f.sse[2] = s.sse[2], f.sgr_ep = s.sgr_ep, f.sgr_xqd[0] = s.sgr_xqd[0], f.sgr_xqd[1] = s.sgr_xqd[1];
+                    const int64_t bits_none = cfg->sgrproj_restore_cost[0];
+                    const int64_t bs = cfg->sgrproj_restore_cost[1] + ((int64_t)lrs_sgr_bits(f.sgr_ep, f.sgr_xqd, rsg) << 9);
+                    const double  cn = lrs_rdcost(cfg->rdmult, bits_none >> 4, f.sse[0]), cs = lrs_rdcost(cfg->rdmult, bs >> 4, f.sse[2]);
+                    f.best[1]        = cs < cn ? SVTF_RESTORE_SGRPROJ : SVTF_RESTORE_NONE;
+                    sse += f.sse[f.best[1]], bits += cs < cn ? bs : bits_none;
+                    if (cs < cn)
+                        rsg[0] = f.sgr_xqd[0], rsg[1] = f.sgr_xqd[1];
+                } else { // search_switchable :1148 (it counts Wiener bits with the full window of the plane type)
+                    double  bc = 0;
+                    int64_t bb = 0;
+                    int     bt = 0;
+                    for (int t = 0; t < 3; t++) {
+                        if (t > 0 && f.best[t - 1] == SVTF_RESTORE_NONE)
+                            continue;
+                        const int64_t coeff = t == 1 ? lrs_wiener_bits(p ? 5 : 7, f.vf, f.hf, rvf, rhf) : (t == 2 ? lrs_sgr_bits(f.sgr_ep, f.sgr_xqd, rsg) : 0);
+                        const int64_t b     = cfg->switchable_restore_cost[t] + (coeff << 9);
+                        const double  cost  = lrs_rdcost(cfg->rdmult, b >> 4, f.sse[t]);
+                        if (t == 0 || cost < bc)
+                            bc = cost, bb = b, bt = t;
+                    }
+                    f.best[2] = bt;
+                    sse += f.sse[bt], bits += bb;
+                    if (bt == 1)
+                        std::memcpy(rvf, f.vf, 16), std::memcpy(rhf, f.hf, 16);
+                    if (bt == 2)
+                        rsg[0] = f.sgr_xqd[0], rsg[1] = f.sgr_xqd[1];
                 }
             }
+            const double cost = lrs_rdcost(cfg->rdmult, bits >> 4, sse);
+            if (r == 0 || cost < best_cost)
+                best_cost = cost, best_type = r;
         }
-        if (out_search && out_search[pl.plane])
-            std::memcpy(out_search[pl.plane], us.data() + pl.first, sizeof(svtf_lr_unit_search) * n);
+        out_frame_type[p] = best_type;
+        if (best_type != SVTF_RESTORE_NONE)
+            for (int u = 0; u < n; u++) { // copy_unit_info :1202
+                svtf_lr_unit &o    = out_units[p][u];
+                o.restoration_type = fu[u].best[best_type - 1];
+                if (o.restoration_type == SVTF_RESTORE_WIENER)
+                    std::memcpy(o.wiener_vfilter, fu[u].vf, 16), std::memcpy(o.wiener_hfilter, fu[u].hf, 16);
+                else if (o.restoration_type == SVTF_RESTORE_SGRPROJ)
+                    o.sgr_ep = fu[u].sgr_ep, o.sgr_xqd[0] = fu[u].sgr_xqd[0], o.sgr_xqd[1] = fu[u].sgr_xqd[1];
+            }
+        if (out_search && out_search[p])
+            std::memcpy(out_search[p], us.data() + pl.first, sizeof(svtf_lr_unit_search) * n);
     }
     return SVTF_OK;
 }

@@ -31,6 +31,25 @@ struct LrsRefine {
     void next_slot(bool went_down);
     void advance();
 };
+// finer_search_pixel_proj_error (:320) as a state machine over the two projection coefficients of one (unit, ep): while
+// pending(), measure get_pixel_proj_error with xqd and feed() it.
+struct LrsSgRefine {
+    int     xqd[2] = {0, 0};
+    int64_t err    = 0;
+    void    start(int ep, bool do_refine, const int init_xqd[2]);
+    void    feed(int64_t e);
+    bool    pending() const { return waiting; }
+
+  private:
+    int  r[2] = {0, 0}, phase = 2, step = 2, p = 0, sign = -1;
+    bool refine = false, moved_down = false, waiting = false;
+    bool propose();
+    void next_slot(bool went_down);
+    void advance();
+};
+// svt_get_proj_subspace_c (:417) + encode_xq (:508) from the exact integer sums {f0 f0, f1 f1, f0 f1, f0 s, f1 s} of a unit
+void lrs_sg_initial_xqd(int ep, const long long sums[5], int size, int xqd[2]);
+int  lrs_sgr_bits(int ep, const int xqd[2], const int ref_xqd[2]); // count_sgrproj_bits :655
 int    lrs_wiener_bits(int win, const int16_t *vf, const int16_t *hf, const int16_t *ref_vf, const int16_t *ref_hf); // count_wiener_bits :1008
 double lrs_rdcost(int rdmult, int64_t rate, int64_t dist);                                                          // RDCOST_DBL
 

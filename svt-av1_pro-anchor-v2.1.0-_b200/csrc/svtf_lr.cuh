@@ -41,7 +41,15 @@ struct LrArgs {
     // error of the filtered samples against `src` is added to sse[plane][unit].  Units of type NONE are skipped.
     Planes              src;
     unsigned long long *sse[3];
+    // FLT instantiation (apply_sgr + the sums of svt_get_proj_subspace_c, EbRestorationPick.c:522/:417): for units of type
+    // SGRPROJ the two guided filters' outputs minus the sample (flt0 - u, flt1 - u, 4 fractional bits) are stored as int32 at
+    // flt[plane][y * cur.pitch + x] and flt[plane][flt_half[plane] + ...], and sum f0^2, f1^2, f0 f1, f0 s, f1 s (s = source
+    // - sample, same scale) are added to proj[plane][5 * unit + ...].
+    int32_t   *flt[3];
+    size_t     flt_half[3];
+    long long *proj[3];
 };
+enum { LR_APPLY = 0, LR_SSE = 1, LR_FLT = 2 };
 
 // svt_aom_eb_sgr_params (EbRestoration.c:85-103)
 __constant__ int c_sgr_r[16][2] = {{2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1},
@@ -97,12 +105,13 @@ __device__ __forceinline__ void lr_sgr_ab_seg(const uint16_t *in, const uint16_t
     }
 }
 
-template <typename T, bool SSE = false>
+template <typename T, int MODE = LR_APPLY>
 __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ LrArgs a) {
     __shared__ __align__(16) uint16_t s_in[LR_IN_ROWS * LR_IN_P];
     __shared__ __align__(16) unsigned char s_buf[66 * 66 * 6]; // Wiener: horizontal pass (u16 [70][TW]); SGR: A (u16) and B (u32)
     __shared__ LrUnitDev s_unit;
     __shared__ uint16_t  s_xb[256];
+    constexpr bool SSE = MODE == LR_SSE, FLT = MODE == LR_FLT;
     const int tid = threadIdx.x;
     int       plane = 0;
     if ((int)blockIdx.x >= a.base[2])
@@ -133,10 +142,12 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
         __syncthreads();
         type = s_unit.type;
     }
-    if (SSE && type == SVTF_RESTORE_NONE)
+    if (MODE != LR_APPLY && type == SVTF_RESTORE_NONE)
         return;
-    const T  *srcp = SSE ? static_cast<const T *>(a.src.p[plane]) : nullptr;
-    const int sp   = SSE ? a.src.pitch[plane] : 0;
+    if (FLT && type != SVTF_RESTORE_SGRPROJ)
+        return;
+    const T  *srcp = MODE != LR_APPLY ? static_cast<const T *>(a.src.p[plane]) : nullptr;
+    const int sp   = MODE != LR_APPLY ? a.src.pitch[plane] : 0;
     unsigned long long my_sse = 0;
     if (type == SVTF_RESTORE_NONE) { // copy (also: planes without restoration, coded samples outside the visible picture)
         // coded widths are multiples of 4 (chroma) / 8 (luma) and x0 of 32: 4-sample vectors
@@ -260,18 +271,21 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
     // ---- self-guided (svt_apply_selfguided_restoration_c :957) ----
     const int ep = s_unit.ep, rad0 = c_sgr_r[ep][0], rad1 = c_sgr_r[ep][1];
     int       xq0, xq1; // svt_decode_xq :634
-    if (rad0 == 0)
+    if (FLT)
+        xq0 = xq1 = 1;
+    else if (rad0 == 0)
         xq0 = 0, xq1 = 128 - s_unit.xqd[1];
     else if (rad1 == 0)
         xq0 = s_unit.xqd[0], xq1 = 0;
     else
         xq0 = s_unit.xqd[0], xq1 = 128 - xq0 - s_unit.xqd[1];
     // a thread owns two work items of 8 consecutive samples of a row (item i = tid + n*256: row i >> sgs, segment i & ..)
-    int acc[2][8];
+    int acc[2][8], acc_b[2][8]; // FLT keeps the two filters apart (acc: radius 2, acc_b: radius 1)
 #pragma unroll
     for (int n = 0; n < 2; n++)
 #pragma unroll
-        for (int j = 0; j < 8; j++) acc[n][j] = 0;
+        for (int j = 0; j < 8; j++) acc[n][j] = acc_b[n][j] = 0;
+    int(&acc1)[2][8] = FLT ? acc_b : acc;
     constexpr int AP = LR_MAXW + 2; // pitch of A / B: columns -1 .. TW
     uint16_t     *sA = reinterpret_cast<uint16_t *>(s_buf);
     uint32_t     *sB = reinterpret_cast<uint32_t *>(s_buf + 66 * 66 * 2);
@@ -343,9 +357,46 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
                 // (centre + left + right + up + down) * 4 + (four diagonals) * 3
                 const int av = (a4[j + 1] + a4[j] + a4[j + 2] + a3[j + 1]) * 4 + (a3[j] + a3[j + 2]) * 3;
                 const int bv = (b4[j + 1] + b4[j] + b4[j + 2] + b3[j + 1]) * 4 + (b3[j] + b3[j + 2]) * 3;
-                acc[n][j] += xq1 * (lr_rnd(av * dg + bv, 9) - (dg << 4));
+                acc1[n][j] += xq1 * (lr_rnd(av * dg + bv, 9) - (dg << 4));
             }
         }
+    }
+    if (FLT) {
+        long long  sum[5] = {0, 0, 0, 0, 0};
+        int32_t   *f0 = a.flt[plane], *f1 = a.flt[plane] + a.flt_half[plane];
+#pragma unroll
+        for (int n = 0; n < 2; n++) {
+            const int i = tid + n * LR_THREADS, r = i >> sgs, c = (i & ((1 << sgs) - 1)) * 8;
+            if (r >= h || c >= wv)
+                continue;
+            const uint16_t *dgp = s_in + (r + 3) * LR_IN_P + LR_C0 + c;
+            const size_t    row = (size_t)(y0 + r) * cp + x0 + c;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (c + j < wv) {
+                    const int       d0 = acc[n][j], d1 = acc_b[n][j];
+                    const long long sv = ((int)srcp[(size_t)(y0 + r) * sp + x0 + c + j] - (int)dgp[j]) << 4;
+                    f0[row + j] = d0, f1[row + j] = d1;
+                    sum[0] += (long long)d0 * d0, sum[1] += (long long)d1 * d1, sum[2] += (long long)d0 * d1;
+                    sum[3] += d0 * sv, sum[4] += d1 * sv;
+                }
+            }
+        }
+        __shared__ unsigned long long s_proj[5];
+        if (tid < 5)
+            s_proj[tid] = 0;
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 5; q++) {
+#pragma unroll
+            for (int m = 16; m; m >>= 1) sum[q] += __shfl_xor_sync(0xffffffffu, sum[q], m);
+            if (!(tid & 31))
+                atomicAdd(&s_proj[q], (unsigned long long)sum[q]);
+        }
+        __syncthreads();
+        if (tid < 5)
+            atomicAdd(reinterpret_cast<unsigned long long *>(a.proj[plane] + 5 * unit_idx + tid), s_proj[tid]);
+        return;
     }
 #pragma unroll
     for (int n = 0; n < 2; n++) {

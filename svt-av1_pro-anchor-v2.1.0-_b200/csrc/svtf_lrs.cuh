@@ -17,6 +17,7 @@
 // added to the unit's 64-bit accumulators in global memory (the host divides by the bit-depth divider and mirrors H).
 #pragma once
 #include "svtf_kernels.cuh"
+#include "svtf_lr.cuh"
 
 namespace svtf {
 
@@ -145,6 +146,51 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_con
     for (int i = tid; i < NACC; i += LRS_THREADS)
         if (s_acc[i])
             atomicAdd(reinterpret_cast<unsigned long long *>(out + i), (unsigned long long)s_acc[i]);
+}
+
+// get_pixel_proj_error (Encoder/Codec/EbRestorationPick.c:305; svt_av1_[lowbd|highbd]_pixel_proj_error_c :167/:233) for every
+// unit that has a candidate pending (units[].type == SGRPROJ: ep and xqd of the candidate): from the stored filter outputs
+// (lr_kernel<T, LR_FLT>), v = (u << 7) + xq0 (flt0 - u) + xq1 (flt1 - u), e = round(v, 11) - source (no clipping, as the
+// reference), sum e^2 per unit.  One CTA per 64 x 64 tile; 12 B read per sample.
+struct LrsProjArgs {
+    Planes             cur, src;
+    const LrsTile     *tiles;
+    const LrUnitDev   *units; // all searched planes concatenated, indexed by LrsTile::unit
+    const int32_t     *flt[3];
+    size_t             flt_half[3];
+    unsigned long long *err;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(LRS_THREADS) lrs_proj_err_kernel(const __grid_constant__ LrsProjArgs a) {
+    const LrsTile   t = a.tiles[blockIdx.x];
+    const LrUnitDev u = a.units[t.unit];
+    if (u.type != SVTF_RESTORE_SGRPROJ)
+        return;
+    const int r0 = c_sgr_r[u.ep][0], r1 = c_sgr_r[u.ep][1];
+    int       xq0, xq1; // svt_decode_xq
+    if (r0 == 0)
+        xq0 = 0, xq1 = 128 - u.xqd[1];
+    else if (r1 == 0)
+        xq0 = u.xqd[0], xq1 = 0;
+    else
+        xq0 = u.xqd[0], xq1 = 128 - xq0 - u.xqd[1];
+    const T       *cur = static_cast<const T *>(a.cur.p[t.plane]), *src = static_cast<const T *>(a.src.p[t.plane]);
+    const int      cp = a.cur.pitch[t.plane], sp = a.src.pitch[t.plane];
+    const int32_t *f0 = a.flt[t.plane], *f1 = f0 + a.flt_half[t.plane];
+    unsigned long long err = 0;
+    for (int i = threadIdx.x; i < t.w * t.h; i += LRS_THREADS) {
+        const int    r = i / t.w, c = i - r * t.w;
+        const size_t o = (size_t)(t.y0 + r) * cp + t.x0 + c;
+        const int    uu = (int)cur[o] << 4;
+        const int    v = (uu << 7) + xq0 * f0[o] + xq1 * f1[o];
+        const int    e = ((v + (1 << 10)) >> 11) - (int)src[(size_t)(t.y0 + r) * sp + t.x0 + c];
+        err += (unsigned long long)((long long)e * e);
+    }
+#pragma unroll
+    for (int m = 16; m; m >>= 1) err += __shfl_xor_sync(0xffffffffu, err, m);
+    if (!(threadIdx.x & 31) && err)
+        atomicAdd(a.err + t.unit, err);
 }
 
 } // namespace svtf

@@ -10,6 +10,7 @@
 // comparisons are IEEE double (RDCOST_DBL, Common/Codec/EbRestoration.h:346).
 #include <algorithm>
 #include <climits>
+#include <cmath>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -241,6 +242,120 @@ void LrsRefine::feed(int64_t e) {
         if (sign < 0)
             moved_down = true;
         if (!(step == 4 && !one_step)) { // only the largest step keeps moving in the same direction
+            next_slot(moved_down);
+            moved_down = false;
+        }
+    }
+    advance();
+}
+
+// ---- self-guided tools ------------------------------------------------------------------------------------------------
+namespace {
+const int kSgR[16][2] = {{2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {2, 1}, {0, 1}, {0, 1}, {0, 1}, {0, 1}, {2, 0}, {2, 0}};
+const int kSgMin[2] = {-96, -32}, kSgMax[2] = {31, 95}; // SGRPROJ_PRJ_MIN0/1, MAX0/1 (Common/Codec/EbRestoration.h:101-104)
+inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+} // namespace
+
+// The reference accumulates the five sums in double; every term is an integer below 2^34 and the totals stay below 2^53,
+// so its sums are exact and equal the integer sums converted once.  Everything after that is the reference's double
+// arithmetic, operation by operation.
+void lrs_sg_initial_xqd(int ep, const long long sums[5], int size, int xqd[2]) {
+    const int r0 = kSgR[ep][0], r1 = kSgR[ep][1];
+    double    h00 = (double)sums[0], h11 = (double)sums[1], h01 = (double)sums[2], c0 = (double)sums[3], c1 = (double)sums[4];
+    h00 /= size, h01 /= size, h11 /= size, c0 /= size, c1 /= size;
+    const double h10 = h01;
+    int          xq[2] = {0, 0};
+    if (r0 == 0) {
+        if (!(h11 < 1e-8))
+            xq[1] = (int)std::rint(c1 / h11 * 128);
+    } else if (r1 == 0) {
+        if (!(h00 < 1e-8))
+            xq[0] = (int)std::rint(c0 / h00 * 128);
+    } else {
+        const double det = h00 * h11 - h01 * h10;
+        if (!(det < 1e-8)) {
+            const double x0 = (h11 * c0 - h01 * c1) / det, x1 = (h00 * c1 - h10 * c0) / det;
+            xq[0] = (int)std::rint(x0 * 128), xq[1] = (int)std::rint(x1 * 128);
+        }
+    }
+    if (r0 == 0)
+        xqd[0] = 0, xqd[1] = clampi(128 - xq[1], kSgMin[1], kSgMax[1]);
+    else if (r1 == 0)
+        xqd[0] = clampi(xq[0], kSgMin[0], kSgMax[0]), xqd[1] = clampi(128 - xqd[0], kSgMin[1], kSgMax[1]);
+    else
+        xqd[0] = clampi(xq[0], kSgMin[0], kSgMax[0]), xqd[1] = clampi(128 - xqd[0] - xq[1], kSgMin[1], kSgMax[1]);
+}
+
+int lrs_sgr_bits(int ep, const int xqd[2], const int ref_xqd[2]) {
+    int bits = 4; // SGRPROJ_PARAMS_BITS
+    for (int p = 0; p < 2; p++)
+        if (kSgR[ep][p] > 0)
+            bits += subexp_bits(kSgMax[p] - kSgMin[p] + 1, 4 /* SGRPROJ_PRJ_SUBEXP_K */, ref_xqd[p] - kSgMin[p], xqd[p] - kSgMin[p]);
+    return bits;
+}
+
+void LrsSgRefine::start(int ep, bool do_refine, const int init_xqd[2]) {
+    r[0] = kSgR[ep][0], r[1] = kSgR[ep][1];
+    refine = do_refine, xqd[0] = init_xqd[0], xqd[1] = init_xqd[1];
+    phase = 0, waiting = true;
+}
+bool LrsSgRefine::propose() {
+    if (sign < 0 ? xqd[p] - step < kSgMin[p] : xqd[p] + step > kSgMax[p])
+        return false;
+    xqd[p] += sign * step;
+    return true;
+}
+void LrsSgRefine::next_slot(bool went_down) {
+    if (sign < 0 && !went_down) {
+        sign = 1;
+        return;
+    }
+    sign = -1;
+    if (!went_down) // next coefficient that has a filter behind it
+        for (int q = p + 1; q < 2; q++)
+            if (r[q] > 0) {
+                p = q;
+                return;
+            }
+    step >>= 1;
+    if (step < 1) {
+        phase = 2;
+        return;
+    }
+    p = r[0] > 0 ? 0 : 1;
+}
+void LrsSgRefine::advance() {
+    while (phase == 1) {
+        if (propose()) {
+            waiting = true;
+            return;
+        }
+        next_slot(moved_down);
+        moved_down = false;
+    }
+    waiting = false;
+}
+void LrsSgRefine::feed(int64_t e) {
+    waiting = false;
+    if (phase == 0) {
+        err = e;
+        if (!refine) {
+            phase = 2;
+            return;
+        }
+        phase = 1, step = 2, p = r[0] > 0 ? 0 : 1, sign = -1, moved_down = false;
+        advance();
+        return;
+    }
+    if (e > err) {
+        xqd[p] -= sign * step;
+        next_slot(moved_down);
+        moved_down = false;
+    } else {
+        err = e;
+        if (sign < 0)
+            moved_down = true;
+        if (step != 2) { // only the first step size keeps moving in the same direction
             next_slot(moved_down);
             moved_down = false;
         }

@@ -408,7 +408,8 @@ class FilterContext:
             search.append((L.LrUnitSearch * (hu * vu))())
         up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
         sp = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in search])
-        self._chk(self._lib.svtf_lr_search_frame(self._h, C.byref(cfg), ftype, up, sp))
+        self.sg_frame_ep_cnt = (C.c_int32 * 16)()
+        self._chk(self._lib.svtf_lr_search_frame(self._h, C.byref(cfg), ftype, up, sp, self.sg_frame_ep_cnt))
         return list(ftype), units, search
 
     def lr_units(self, plane, unit_size):

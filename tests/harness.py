@@ -277,25 +277,32 @@ def _lr_call(fn, geom, cur, dbk, lr, units):
     return out
 
 
-def lr_search_cfg(unit_size=(64, 32, 32), tap_lvl=1, refinement=1, one_step=0, chroma=1, rdmult=9000, cost=(120, 900)):
-    """WnFilterCtrls of a Wiener-only search (Encoder/Codec/EncModeConfig.c set_wn_filter_ctrls) + the rate inputs."""
+def lr_search_cfg(unit_size=(64, 32, 32), tap_lvl=1, refinement=1, one_step=0, chroma=1, rdmult=9000, cost=(120, 900), wn=1, sg=0, sg_chroma=1,
+                  sg_ep=((0, 16, 1, 1), (0, 16, 1, 1)), sg_cost=(130, 950), sw_cost=(150, 1000, 1100)):
+    """WnFilterCtrls / SgFilterCtrls of a search (Encoder/Codec/EncModeConfig.c set_wn_filter_ctrls / set_sg_filter_ctrls) + the rate
+    inputs.  sg_ep: (start_ep, end_ep, ep_inc, refine) for luma and chroma."""
     c = L.LrSearchCfg()
     for p in range(3):
         c.restoration_unit_size[p] = unit_size[p]
-    c.wn_enabled, c.wn_filter_tap_lvl, c.wn_use_refinement, c.wn_max_one_refinement_step, c.wn_use_chroma = 1, tap_lvl, refinement, one_step, chroma
-    c.sg_enabled, c.rdmult = 0, rdmult
-    c.wiener_restore_cost[0], c.wiener_restore_cost[1] = cost
+    c.wn_enabled, c.wn_filter_tap_lvl, c.wn_use_refinement, c.wn_max_one_refinement_step, c.wn_use_chroma = wn, tap_lvl, refinement, one_step, chroma
+    c.sg_enabled, c.sg_use_chroma, c.rdmult = sg, sg_chroma, rdmult
+    for t in range(2):
+        c.sg_start_ep[t], c.sg_end_ep[t], c.sg_ep_inc[t], c.sg_refine[t] = sg_ep[t]
+        c.wiener_restore_cost[t], c.sgrproj_restore_cost[t] = cost[t], sg_cost[t]
+    for t in range(3):
+        c.switchable_restore_cost[t] = sw_cost[t]
     return c
 
 
-def lr_search_sig(geom, cfg, ftype, units, search):
-    """Comparable form of a search result: frame types, per-unit (type, taps), per-unit (sse none, sse wiener, refined taps)."""
+def lr_search_sig(geom, cfg, ftype, units, search, ep_cnt):
+    """Comparable form of a search result: frame types, per-unit (type, taps, sgr), per-unit search info, ep counters."""
     sig = []
     for p in range(3):
         hu, vu = lr_units_of(geom, p, cfg.restoration_unit_size[p])
-        us = [(u.restoration_type, tuple(u.wiener_vfilter), tuple(u.wiener_hfilter)) for u in units[p][: hu * vu]]
-        ss = [(s.sse[0], s.sse[1], tuple(s.wiener_vfilter), tuple(s.wiener_hfilter)) for s in search[p][: hu * vu]]
+        us = [(u.restoration_type, tuple(u.wiener_vfilter), tuple(u.wiener_hfilter), u.sgr_ep, tuple(u.sgr_xqd)) for u in units[p][: hu * vu]]
+        ss = [(tuple(s.sse), tuple(s.wiener_vfilter), tuple(s.wiener_hfilter), s.sgr_ep, tuple(s.sgr_xqd)) for s in search[p][: hu * vu]]
         sig.append((ftype[p], us, ss))
+    sig.append(list(ep_cnt))
     return sig
 
 
@@ -303,6 +310,7 @@ def _lr_search_call(fn, geom, cur, src, cfg):
     cur = [np.ascontiguousarray(p) for p in cur]
     src = [np.ascontiguousarray(p) for p in src]
     ftype = (C.c_int32 * 3)()
+    cnt = (C.c_int32 * 16)()
     units, search = [], []
     for p in range(3):
         hu, vu = lr_units_of(geom, p, cfg.restoration_unit_size[p])
@@ -310,8 +318,8 @@ def _lr_search_call(fn, geom, cur, src, cfg):
         search.append((L.LrUnitSearch * (hu * vu))())
     up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in units])
     sp = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) for u in search])
-    assert fn(C.byref(geom), *_planes(cur), *_planes(src), C.byref(cfg), ftype, up, sp) == 0
-    return lr_search_sig(geom, cfg, ftype, units, search)
+    assert fn(C.byref(geom), *_planes(cur), *_planes(src), C.byref(cfg), ftype, up, sp, cnt) == 0
+    return lr_search_sig(geom, cfg, ftype, units, search, cnt)
 
 
 def lr_unit_limits(geom, plane, unit_size):

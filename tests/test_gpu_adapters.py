@@ -221,7 +221,8 @@ def test_pad_ref_pictures_adapter(H, orc, adapt, w, h, bd, sb, resident):
         assert H.planes_equal(bn, exp[2]), "2-bit: " + H.first_diff(bn, exp[2])
 
 
-@pytest.mark.parametrize("w,h,bd,sb,kw", [(200, 136, 10, 2, {}), (136, 72, 8, 1, {"tap_lvl": 2, "one_step": 1}), (264, 136, 8, 2, {"chroma": 0})])
+@pytest.mark.parametrize("w,h,bd,sb,kw", [(200, 136, 10, 2, {}), (136, 72, 8, 1, {"tap_lvl": 2, "one_step": 1}), (264, 136, 8, 2, {"chroma": 0}),
+                                          (136, 104, 10, 2, {"sg": 1}), (136, 72, 8, 1, {"wn": 0, "sg": 1, "sg_ep": ((0, 16, 3, 1), (8, 16, 1, 0))})])
 def test_restoration_search_adapter(H, orc, adapt, w, h, bd, sb, kw):
     """restoration_seg_search(.., segment 0) + rest_finish_search on real PictureControlSet / Av1Common / Macroblock structures:
     rusi_picture[] and rst_info[] end up as the oracle's (pinned to the reference's own search) say.  The planes handed over
@@ -238,3 +239,4 @@ def test_restoration_search_adapter(H, orc, adapt, w, h, bd, sb, kw):
         assert got[p][0] == exp[p][0], ("frame type", p)
         assert got[p][2] == exp[p][2], ("unit search", p)
         assert got[p][1] == exp[p][1], ("unit info", p)
+    assert got[3] == exp[3], "sg_frame_ep_cnt"

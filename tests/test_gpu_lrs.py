@@ -67,18 +67,27 @@ def test_wiener_stats_extreme_content(H, orc):
     (134, 70, 10, 2, 6, {"chroma": 0, "rdmult": 300000}),
     (136, 72, 8, 1, 7, {"rdmult": 40, "cost": (10, 60)}),
     (328, 200, 10, 2, 8, {"unit_size": (256, 128, 128)}),
+    # self-guided tools, alone and with Wiener (-> RESTORE_SWITCHABLE)
+    (136, 72, 8, 1, 9, {"wn": 0, "sg": 1}),
+    (136, 104, 10, 2, 10, {"sg": 1}),
+    (104, 72, 12, 2, 11, {"sg": 1, "sg_ep": ((0, 16, 4, 0), (10, 16, 1, 1))}),
+    (200, 72, 8, 2, 12, {"sg": 1, "chroma": 0, "sg_ep": ((2, 12, 3, 1), (8, 16, 2, 1))}),
+    (134, 70, 10, 2, 13, {"sg": 1, "sg_chroma": 0, "rdmult": 60000}),
+    (136, 72, 10, 2, 14, {"sg": 1, "rdmult": 300, "sw_cost": (20, 40, 30), "sg_cost": (15, 50)}),
+    (328, 200, 10, 2, 15, {"sg": 1, "unit_size": (256, 128, 128)}),
 ])
 def test_lr_search_matches_oracle(H, orc, w, h, bd, sb, seed, kw):
     g, cur, src = search_case(H, w, h, bd, sb, seed)
     cfg = H.lr_search_cfg(**kw)
     ctx = ctx_with(H, g, cur, src)
     ftype, units, search = ctx.restoration_search(cfg)
-    a = H.lr_search_sig(g, cfg, ftype, units, search)
+    a = H.lr_search_sig(g, cfg, ftype, units, search, ctx.sg_frame_ep_cnt)
     b = orc.lr_search(g, vis(g, cur), vis(g, src), cfg)
     for p in range(3):
         assert a[p][0] == b[p][0], ("frame type", p)
         assert a[p][2] == b[p][2], ("unit search", p)
         assert a[p][1] == b[p][1], ("unit info", p)
+    assert a[3] == b[3], "sg_frame_ep_cnt"
     if kw.get("tap_lvl", 1) != 3:  # the 3-tap search legitimately keeps RESTORE_NONE on this content (as the oracle does)
         assert any(t != 0 for t in ftype)
 

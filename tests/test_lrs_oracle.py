@@ -53,6 +53,13 @@ def test_oracle_wiener_solve_on_degenerate_stats(H, orc, ref):
     (200, 72, 8, 2, 5, {"unit_size": (128, 64, 64), "refinement": 0}),
     (134, 70, 10, 2, 6, {"chroma": 0, "rdmult": 300000}),
     (136, 72, 8, 1, 7, {"rdmult": 40, "cost": (10, 60)}),
+    # self-guided tools, alone and with Wiener (-> RESTORE_SWITCHABLE)
+    (136, 72, 8, 1, 8, {"wn": 0, "sg": 1}),
+    (136, 104, 10, 2, 9, {"sg": 1}),
+    (104, 72, 12, 2, 10, {"sg": 1, "sg_ep": ((0, 16, 4, 0), (10, 16, 1, 1))}),
+    (200, 72, 8, 2, 11, {"sg": 1, "chroma": 0, "sg_ep": ((2, 12, 3, 1), (8, 16, 2, 1))}),
+    (134, 70, 10, 2, 12, {"sg": 1, "sg_chroma": 0, "rdmult": 60000}),
+    (136, 72, 10, 2, 13, {"sg": 1, "rdmult": 300, "sw_cost": (20, 40, 30), "sg_cost": (15, 50)}),
 ])
 def test_oracle_lr_search_matches_reference(H, orc, ref, w, h, bd, sb, seed, kw):
     g, cur, src = search_case(H, w, h, bd, sb, seed)
@@ -63,6 +70,7 @@ def test_oracle_lr_search_matches_reference(H, orc, ref, w, h, bd, sb, seed, kw)
         assert a[p][0] == b[p][0], ("frame type", p)
         assert a[p][2] == b[p][2], ("unit search", p)
         assert a[p][1] == b[p][1], ("unit info", p)
+    assert a[3] == b[3], "sg_frame_ep_cnt"
 
 
 def test_product_host_solve_matches_oracle(H, orc):
