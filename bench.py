@@ -242,10 +242,20 @@ def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
     for _ in range(n):
         ctx.compute_stats(0, 256, 7)
     dts = (time.perf_counter() - t0) / n
+    cfg2 = H.lr_search_cfg(unit_size=(256, 128, 128), sg=1)
+    ctx.restoration_search(cfg2)
+    l1 = ctx.launch_count
+    t0 = time.perf_counter()
+    for _ in range(n):
+        ftype2, _, _ = ctx.restoration_search(cfg2)
+    dt2 = (time.perf_counter() - t0) / n
+    both = {"metric": "same with the self-guided tools too (16 parameter sets, coefficient refinement, RESTORE_SWITCHABLE)",
+            "value": round(geom.width * geom.height / dt2 / 1e6, 1), "unit": "Mpixel/s", "ms_per_picture": round(dt2 * 1e3, 3),
+            "gpu_launches_per_picture": (ctx.launch_count - l1) // n, "frame_types": ftype2}
     res = {"metric": "loop-restoration search Mpixel/s (Wiener 7-tap luma + 5-tap chroma, refinement on; picture resident)",
            "value": round(geom.width * geom.height / dt / 1e6, 1), "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 3),
            "gpu_launches_per_picture": (ctx.launch_count - l0 - n * 2) // n, "luma_stats_ms_incl_download": round(dts * 1e3, 3),
-           "frame_types": ftype, "cpu_baseline": None}
+           "frame_types": ftype, "wiener_and_self_guided": both, "cpu_baseline": None}
     if with_cpu and H.ref_available():
         g2 = S.make_geom(960, 544, BD)
         rec = H.synth_picture(g2, 0xF11)
@@ -257,6 +267,15 @@ def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
         dt = time.perf_counter() - t0
         res["cpu_baseline"] = {"value": round(960 * 544 / dt / 1e6, 3), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
                                "sample": "one 960x544 10-bit picture, one segment, single thread"}
+        g3 = S.make_geom(480, 272, BD)
+        rec = H.synth_picture(g3, 0xF13)
+        org = H.synth_source(g3, rec, 0xF14, amp=6)
+        vis3 = lambda pl: [np.ascontiguousarray(p[: (g3.height + s) >> s, : (g3.width + s) >> s]) for p, s in zip(pl, (0, 1, 1))]
+        t0 = time.perf_counter()
+        ref.lr_search(g3, vis3(org), vis3(rec), cfg2)
+        dt = time.perf_counter() - t0
+        both["cpu_baseline"] = {"value": round(480 * 272 / dt / 1e6, 3), "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                                "sample": "one 480x272 10-bit picture, one segment, single thread"}
     return res
 
 

@@ -1710,9 +1710,9 @@ struct LrsPlan {
     std::vector<int>                count;   // samples per unit
     std::vector<unsigned long long> acc_off; // offset of each unit's statistics accumulators
     size_t                          acc_total = 0;
-    int                             units = 0;
+    int                             units = 0, nslots = 1; // nslots: parameter sets the self-guided search measures at once
     // device carve-up
-    size_t o_tiles = 0, o_sum = 0, o_sse = 0, o_count = 0, o_off = 0, o_acc = 0, o_trial = 0, o_units = 0, o_proj = 0, bytes = 0;
+    size_t o_tiles = 0, o_sum = 0, o_sse = 0, o_count = 0, o_off = 0, o_acc = 0, o_trial = 0, o_units = 0, o_proj = 0, o_cand = 0, o_errk = 0, bytes = 0;
 };
 
 // Units of a plane (foreach_rest_unit_in_tile, Common/Codec/EbRestoration.c:1250): raster order, the last one of a row /
@@ -1748,7 +1748,9 @@ int lrs_reserve(svtf_ctx *c, LrsPlan &plan) {
     carve(plan.o_sum, 8 * (size_t)plan.units), carve(plan.o_sse, 8 * (size_t)plan.units), carve(plan.o_trial, 8 * (size_t)plan.units);
     carve(plan.o_count, 4 * (size_t)plan.units), carve(plan.o_off, 8 * (size_t)plan.units);
     carve(plan.o_units, sizeof(LrUnitDev) * (size_t)plan.units);
-    carve(plan.o_proj, 40 * (size_t)plan.units);
+    carve(plan.o_proj, 40 * (size_t)plan.units * plan.nslots);
+    carve(plan.o_cand, sizeof(LrsCand) * (size_t)plan.units * plan.nslots);
+    carve(plan.o_errk, 8 * (size_t)LRS_CAND * plan.units * plan.nslots);
     carve(plan.o_acc, 8 * plan.acc_total);
     if (plan.bytes > c->lrs_cap) {
         if (c->d_lrs) {
@@ -1900,7 +1902,7 @@ int lrs_trial_args(svtf_ctx *c, const LrsPlan &plan, const bool active[3], int f
         a.pw[p] = (c->geom.width + ss) >> ss, a.ph[p] = (c->geom.height + ss) >> ss;
         a.cw[p] = a.pw[p], a.chh[p] = a.ph[p]; // only the visible picture is measured
         a.unit[p] = 0, a.hu[p] = a.vu[p] = 0, a.units[p] = nullptr, a.sse[p] = nullptr, a.proj[p] = nullptr;
-        a.frame_type[p] = SVTF_RESTORE_NONE, a.chunks[p] = a.stripes[p] = 0;
+        a.frame_type[p] = SVTF_RESTORE_NONE, a.chunks[p] = a.stripes[p] = 0, a.force_ep[p] = -1, a.flt[p] = nullptr, a.flt_half[p] = 0;
     }
     for (const LrsPlane &pl : plan.planes) {
         const int p = pl.plane, ss = p ? 1 : 0, sh = 64 >> ss, off = 8 >> ss;
@@ -1974,6 +1976,9 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
         do_wn[p] = wn && (!p || cfg->wn_use_chroma), do_sg[p] = sg && (!p || cfg->sg_use_chroma);
         lrs_add_plane(c->geom, plan, p, cfg->restoration_unit_size[p], p ? std::min(wn_luma, 5) : wn_luma);
     }
+    for (int p = 0; p < nplanes; p++)
+        if (do_sg[p])
+            plan.nslots = std::max(plan.nslots, (cfg->sg_end_ep[p > 0] - cfg->sg_start_ep[p > 0] + cfg->sg_ep_inc[p > 0] - 1) / cfg->sg_ep_inc[p > 0]);
     const unsigned long long *sse_none;
     const long long          *acc;
     if (int r = lrs_measure(c, plan, do_wn, sse_none, acc))
@@ -2046,98 +2051,117 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
     const auto t_wiener = now();
     // ---- self-guided search (search_selfguided_restoration :550): the ep candidates one after the other, all units in lock-step ----
     if (sg) {
-        // filter outputs of the candidate ep: two int32 planes per searched plane
-        size_t need = 0, off_p[3] = {0, 0, 0}, half[3] = {0, 0, 0};
+        // All parameter sets (ep) at once: slot k of a plane = its k-th candidate ep.  Filter outputs: two int32 planes per
+        // searched plane and slot.
+        const int    nslots = plan.nslots;
+        size_t       slot_elems = 0, off_p[3] = {0, 0, 0}, half[3] = {0, 0, 0};
         const Planes cur = c->surf[c->cur].planes();
         for (int p = 0; p < 3; p++)
             if (do_sg[p]) {
                 const int ss = p ? 1 : 0;
                 half[p]  = (size_t)cur.pitch[p] * (((c->geom.height + ss) >> ss) + 1);
-                off_p[p] = need, need += 2 * half[p];
+                off_p[p] = slot_elems, slot_elems += 2 * half[p];
             }
-        if (need * 4 > c->lrs_flt_cap) {
+        const size_t need = slot_elems * nslots * 4;
+        if (need > c->lrs_flt_cap) {
             if (c->d_lrs_flt) {
                 CUDA_TRY(c, cudaStreamSynchronize(c->stream));
                 CUDA_TRY(c, cudaFree(c->d_lrs_flt));
                 c->d_lrs_flt = nullptr, c->lrs_flt_cap = 0;
             }
-            CUDA_TRY(c, cudaMalloc(&c->d_lrs_flt, need * 4));
-            c->lrs_flt_cap = need * 4;
+            CUDA_TRY(c, cudaMalloc(&c->d_lrs_flt, need));
+            c->lrs_flt_cap = need;
         }
-        LrArgs fa;
+        auto ep_at = [&](int p, int k) { return cfg->sg_start_ep[p > 0] + k * cfg->sg_ep_inc[p > 0]; };
+        auto act_at = [&](int p, int k) { return do_sg[p] && ep_at(p, k) < cfg->sg_end_ep[p > 0]; };
+        // the two guided filters of every unit for every ep + the sums of the projection: one launch per slot, no sync between
+        for (int u = 0; u < plan.units; u++) {
+            std::memset(&host[u], 0, sizeof(LrUnitDev));
+            if (do_sg[plane_of[u]])
+                host[u].type = SVTF_RESTORE_SGRPROJ;
+        }
+        CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host, sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(c, cudaMemsetAsync(d + plan.o_proj, 0, 40 * (size_t)plan.units * nslots, c->stream));
+        for (int k = 0; k < nslots; k++) {
+            bool act[3];
+            for (int p = 0; p < 3; p++) act[p] = act_at(p, k);
+            LrArgs    fa;
+            const int grid = lrs_trial_args(c, plan, act, 3 /* any restoring frame type */, fa);
+            for (int p = 0; p < 3; p++) {
+                fa.flt[p] = c->d_lrs_flt + k * slot_elems + off_p[p], fa.flt_half[p] = half[p], fa.force_ep[p] = ep_at(p, k);
+                if (fa.proj[p])
+                    fa.proj[p] += 5 * (size_t)plan.units * k;
+            }
+            if (int r = lrs_launch_lr<LR_FLT>(c, fa, grid))
+                return r;
+        }
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_proj, d + plan.o_proj, 40 * (size_t)plan.units * nslots, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        const long long         *proj = reinterpret_cast<const long long *>(c->h_lrs + plan.o_proj);
+        std::vector<LrsSgRefine> sref((size_t)plan.units * nslots);
+        for (int k = 0; k < nslots; k++)
+            for (int u = 0; u < plan.units; u++)
+                if (act_at(plane_of[u], k)) {
+                    int       xqd[2];
+                    const int ep = ep_at(plane_of[u], k);
+                    lrs_sg_initial_xqd(ep, proj + 5 * ((size_t)k * plan.units + u), plan.count[u], xqd);
+                    sref[(size_t)k * plan.units + u].start(ep, cfg->sg_refine[plane_of[u] > 0] != 0, xqd);
+                }
+        // The projection error of the pending candidates, every (unit, ep) in lock-step.  A (unit, ep) brings the candidates its
+        // line search asks for next IF each one lowers the error (a copy of its state machine fed with "no worse"); the real
+        // errors are then fed in order for as long as the machine asks for exactly the candidate that was measured.
         LrsProjArgs pa;
         pa.cur = cur, pa.src = c->source.planes();
         pa.tiles = reinterpret_cast<const LrsTile *>(d + plan.o_tiles);
-        pa.units = reinterpret_cast<const LrUnitDev *>(d + plan.o_units);
-        pa.err   = reinterpret_cast<unsigned long long *>(d + plan.o_trial);
+        pa.cand  = reinterpret_cast<const LrsCand *>(d + plan.o_cand);
+        pa.err   = reinterpret_cast<unsigned long long *>(d + plan.o_errk);
+        pa.units = plan.units, pa.slot_elems = slot_elems;
         for (int p = 0; p < 3; p++) pa.flt[p] = c->d_lrs_flt + off_p[p], pa.flt_half[p] = half[p];
-        std::vector<LrsSgRefine> sref(plan.units);
-        std::vector<int64_t>     best_err(plan.units, -1);
-        const long long         *proj = reinterpret_cast<const long long *>(c->h_lrs + plan.o_proj);
-        for (int k = 0;; k++) {
-            bool act[3] = {false, false, false};
-            int  ep_of[3] = {0, 0, 0}, any = 0;
-            for (int p = 0; p < 3; p++) {
-                ep_of[p] = cfg->sg_start_ep[p > 0] + k * cfg->sg_ep_inc[p > 0];
-                act[p]   = do_sg[p] && ep_of[p] < cfg->sg_end_ep[p > 0];
-                any += act[p];
+        LrsCand                  *cand = reinterpret_cast<LrsCand *>(c->h_lrs + plan.o_cand);
+        const unsigned long long *errk = reinterpret_cast<const unsigned long long *>(c->h_lrs + plan.o_errk);
+        const int    nt = (int)plan.tiles.size();
+        const size_t nu = (size_t)plan.units * nslots;
+        for (;;) {
+            int pending = 0;
+            for (size_t i = 0; i < nu; i++) {
+                LrsCand &cd = cand[i];
+                cd.n = 0, cd.ep = 0;
+                if (!sref[i].pending())
+                    continue;
+                pending++;
+                cd.ep = ep_at(plane_of[i % plan.units], (int)(i / plan.units));
+                LrsSgRefine sim = sref[i];
+                while (sim.pending() && cd.n < LRS_CAND) {
+                    cd.xqd[cd.n][0] = sim.xqd[0], cd.xqd[cd.n][1] = sim.xqd[1];
+                    cd.n++;
+                    sim.feed(sim.started_err() ? sim.err : 0);
+                }
             }
-            if (!any)
+            if (!pending)
                 break;
-            // the two guided filters of every unit for this ep + the sums of the projection
-            const int grid = lrs_trial_args(c, plan, act, 3 /* any restoring frame type */, fa);
-            for (int p = 0; p < 3; p++) fa.flt[p] = c->d_lrs_flt + off_p[p], fa.flt_half[p] = half[p];
-            for (int u = 0; u < plan.units; u++) {
-                std::memset(&host[u], 0, sizeof(LrUnitDev));
-                if (act[plane_of[u]])
-                    host[u].type = SVTF_RESTORE_SGRPROJ, host[u].ep = ep_of[plane_of[u]];
-            }
-            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_units, host, sizeof(LrUnitDev) * plan.units, cudaMemcpyHostToDevice, c->stream));
-            CUDA_TRY(c, cudaMemsetAsync(d + plan.o_proj, 0, 40 * (size_t)plan.units, c->stream));
-            if (int r = lrs_launch_lr<LR_FLT>(c, fa, grid))
-                return r;
-            CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_proj, d + plan.o_proj, 40 * (size_t)plan.units, cudaMemcpyDeviceToHost, c->stream));
+            sg_rounds++;
+            CUDA_TRY(c, cudaMemcpyAsync(d + plan.o_cand, cand, sizeof(LrsCand) * nu, cudaMemcpyHostToDevice, c->stream));
+            CUDA_TRY(c, cudaMemsetAsync(d + plan.o_errk, 0, 8 * (size_t)LRS_CAND * nu, c->stream));
+            if (c->geom.sample_bytes == 1)
+                lrs_proj_err_kernel<uint8_t><<<dim3(nt, nslots), LRS_THREADS, 0, c->stream>>>(pa);
+            else
+                lrs_proj_err_kernel<uint16_t><<<dim3(nt, nslots), LRS_THREADS, 0, c->stream>>>(pa);
+            CUDA_TRY(c, cudaGetLastError());
+            c->launches++;
+            CUDA_TRY(c, cudaMemcpyAsync(c->h_lrs + plan.o_errk, d + plan.o_errk, 8 * (size_t)LRS_CAND * nu, cudaMemcpyDeviceToHost, c->stream));
             CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-            for (int u = 0; u < plan.units; u++)
-                if (act[plane_of[u]]) {
-                    int xqd[2];
-                    lrs_sg_initial_xqd(ep_of[plane_of[u]], proj + 5 * (size_t)u, plan.count[u], xqd);
-                    sref[u].start(ep_of[plane_of[u]], cfg->sg_refine[plane_of[u] > 0] != 0, xqd);
-                }
-            // the projection error of every pending candidate, in lock-step
-            const int nt = (int)plan.tiles.size();
-            for (;;) {
-                int pending = 0;
-                for (int u = 0; u < plan.units; u++) {
-                    std::memset(&host[u], 0, sizeof(LrUnitDev));
-                    if (!act[plane_of[u]] || !sref[u].pending())
-                        continue;
-                    pending++;
-                    host[u].type = SVTF_RESTORE_SGRPROJ, host[u].ep = ep_of[plane_of[u]];
-                    host[u].xqd[0] = sref[u].xqd[0], host[u].xqd[1] = sref[u].xqd[1];
-                }
-                if (!pending)
-                    break;
-                sg_rounds++;
-                if (int r = round_trip([&]() -> int {
-                        if (c->geom.sample_bytes == 1)
-                            lrs_proj_err_kernel<uint8_t><<<nt, LRS_THREADS, 0, c->stream>>>(pa);
-                        else
-                            lrs_proj_err_kernel<uint16_t><<<nt, LRS_THREADS, 0, c->stream>>>(pa);
-                        CUDA_TRY(c, cudaGetLastError());
-                        c->launches++;
-                        return SVTF_OK;
-                    }))
-                    return r;
-                for (int u = 0; u < plan.units; u++)
-                    if (act[plane_of[u]] && sref[u].pending())
-                        sref[u].feed((int64_t)trial[u]);
+            for (size_t i = 0; i < nu; i++)
+                for (int j = 0; j < cand[i].n && sref[i].pending() && sref[i].xqd[0] == cand[i].xqd[j][0] && sref[i].xqd[1] == cand[i].xqd[j][1]; j++)
+                    sref[i].feed((int64_t)errk[i * LRS_CAND + j]);
+        }
+        // the best ep of every unit: first lowest error in ep order (:637-642)
+        for (int u = 0; u < plan.units; u++) {
+            int64_t best = -1;
+            for (int k = 0; k < nslots; k++) {
+                const LrsSgRefine &r = sref[(size_t)k * plan.units + u];
+                if (act_at(plane_of[u], k) && (best == -1 || r.err < best))
+                    best = r.err, us[u].sgr_ep = ep_at(plane_of[u], k), us[u].sgr_xqd[0] = r.xqd[0], us[u].sgr_xqd[1] = r.xqd[1];
             }
-            for (int u = 0; u < plan.units; u++)
-                if (act[plane_of[u]] && (best_err[u] == -1 || sref[u].err < best_err[u])) {
-                    best_err[u]  = sref[u].err;
-                    us[u].sgr_ep = ep_of[plane_of[u]], us[u].sgr_xqd[0] = sref[u].xqd[0], us[u].sgr_xqd[1] = sref[u].xqd[1];
-                }
         }
         // the unit filtered for real with the parameters found (clipping included): sse[RESTORE_SGRPROJ]
         LrArgs    a;

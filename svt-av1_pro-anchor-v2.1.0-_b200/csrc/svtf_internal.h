@@ -39,6 +39,7 @@ struct LrsSgRefine {
     void    start(int ep, bool do_refine, const int init_xqd[2]);
     void    feed(int64_t e);
     bool    pending() const { return waiting; }
+    bool    started_err() const { return phase != 0; } // err holds a measured value (the first trial has been fed)
 
   private:
     int  r[2] = {0, 0}, phase = 2, step = 2, p = 0, sign = -1;

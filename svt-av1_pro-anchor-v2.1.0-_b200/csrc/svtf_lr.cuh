@@ -48,6 +48,7 @@ struct LrArgs {
     int32_t   *flt[3];
     size_t     flt_half[3];
     long long *proj[3];
+    int        force_ep[3]; // >= 0: the parameter set of every unit of the plane (one launch per candidate ep)
 };
 enum { LR_APPLY = 0, LR_SSE = 1, LR_FLT = 2 };
 
@@ -269,7 +270,7 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
         return;
     }
     // ---- self-guided (svt_apply_selfguided_restoration_c :957) ----
-    const int ep = s_unit.ep, rad0 = c_sgr_r[ep][0], rad1 = c_sgr_r[ep][1];
+    const int ep = FLT && a.force_ep[plane] >= 0 ? a.force_ep[plane] : s_unit.ep, rad0 = c_sgr_r[ep][0], rad1 = c_sgr_r[ep][1];
     int       xq0, xq1; // svt_decode_xq :634
     if (FLT)
         xq0 = xq1 = 1;

@@ -149,48 +149,75 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_con
 }
 
 // get_pixel_proj_error (Encoder/Codec/EbRestorationPick.c:305; svt_av1_[lowbd|highbd]_pixel_proj_error_c :167/:233) for every
-// unit that has a candidate pending (units[].type == SGRPROJ: ep and xqd of the candidate): from the stored filter outputs
-// (lr_kernel<T, LR_FLT>), v = (u << 7) + xq0 (flt0 - u) + xq1 (flt1 - u), e = round(v, 11) - source (no clipping, as the
-// reference), sum e^2 per unit.  One CTA per 64 x 64 tile; 12 B read per sample.
+// unit that has candidates pending: from the stored filter outputs (lr_kernel<T, LR_FLT>),
+// v = (u << 7) + xq0 (flt0 - u) + xq1 (flt1 - u), e = round(v, 11) - source (no clipping, as the reference), sum e^2 per unit.
+// A unit brings up to LRS_CAND candidate coefficient pairs per launch (the host speculates along the reference's line
+// search: the candidates it will ask for if each one lowers the error); they share the 12 B read per sample.
+// One CTA per 64 x 64 tile.
+constexpr int LRS_CAND = 8;
+struct LrsCand { // per unit
+    int32_t n, ep;
+    int32_t xqd[LRS_CAND][2];
+};
 struct LrsProjArgs {
-    Planes             cur, src;
-    const LrsTile     *tiles;
-    const LrUnitDev   *units; // all searched planes concatenated, indexed by LrsTile::unit
-    const int32_t     *flt[3];
-    size_t             flt_half[3];
-    unsigned long long *err;
+    Planes              cur, src;
+    const LrsTile      *tiles;
+    const LrsCand      *cand; // [slot][unit]: all searched planes concatenated, indexed by LrsTile::unit
+    const int32_t      *flt[3]; // slot 0; slot k at + k * slot_elems
+    size_t              flt_half[3], slot_elems;
+    int                 units;
+    unsigned long long *err; // [slot][unit][LRS_CAND]
 };
 
 template <typename T>
 __global__ void __launch_bounds__(LRS_THREADS) lrs_proj_err_kernel(const __grid_constant__ LrsProjArgs a) {
-    const LrsTile   t = a.tiles[blockIdx.x];
-    const LrUnitDev u = a.units[t.unit];
-    if (u.type != SVTF_RESTORE_SGRPROJ)
+    const LrsTile  t = a.tiles[blockIdx.x];
+    const size_t   ci = (size_t)blockIdx.y * a.units + t.unit; // (slot = one candidate ep, unit)
+    const LrsCand &cd = a.cand[ci];
+    const int      n = cd.n;
+    if (n <= 0)
         return;
-    const int r0 = c_sgr_r[u.ep][0], r1 = c_sgr_r[u.ep][1];
-    int       xq0, xq1; // svt_decode_xq
-    if (r0 == 0)
-        xq0 = 0, xq1 = 128 - u.xqd[1];
-    else if (r1 == 0)
-        xq0 = u.xqd[0], xq1 = 0;
-    else
-        xq0 = u.xqd[0], xq1 = 128 - xq0 - u.xqd[1];
+    const int ep = cd.ep, r0 = c_sgr_r[ep][0], r1 = c_sgr_r[ep][1];
+    int       xq0[LRS_CAND], xq1[LRS_CAND]; // svt_decode_xq
+#pragma unroll
+    for (int j = 0; j < LRS_CAND; j++) {
+        const int q0 = cd.xqd[j][0], q1 = cd.xqd[j][1];
+        if (r0 == 0)
+            xq0[j] = 0, xq1[j] = 128 - q1;
+        else if (r1 == 0)
+            xq0[j] = q0, xq1[j] = 0;
+        else
+            xq0[j] = q0, xq1[j] = 128 - q0 - q1;
+    }
     const T       *cur = static_cast<const T *>(a.cur.p[t.plane]), *src = static_cast<const T *>(a.src.p[t.plane]);
     const int      cp = a.cur.pitch[t.plane], sp = a.src.pitch[t.plane];
-    const int32_t *f0 = a.flt[t.plane], *f1 = f0 + a.flt_half[t.plane];
-    unsigned long long err = 0;
+    const int32_t *f0 = a.flt[t.plane] + blockIdx.y * a.slot_elems, *f1 = f0 + a.flt_half[t.plane];
+    // a thread sees at most 64 * 64 / 256 = 16 samples and |e| < 2^13 (unclipped 12-bit): 32-bit partial sums
+    unsigned err32[LRS_CAND];
+#pragma unroll
+    for (int j = 0; j < LRS_CAND; j++) err32[j] = 0;
     for (int i = threadIdx.x; i < t.w * t.h; i += LRS_THREADS) {
         const int    r = i / t.w, c = i - r * t.w;
         const size_t o = (size_t)(t.y0 + r) * cp + t.x0 + c;
-        const int    uu = (int)cur[o] << 4;
-        const int    v = (uu << 7) + xq0 * f0[o] + xq1 * f1[o];
-        const int    e = ((v + (1 << 10)) >> 11) - (int)src[(size_t)(t.y0 + r) * sp + t.x0 + c];
-        err += (unsigned long long)((long long)e * e);
-    }
+        const int    uu = (int)cur[o] << 4, d0 = f0[o], d1 = f1[o], sv = (int)src[(size_t)(t.y0 + r) * sp + t.x0 + c];
 #pragma unroll
-    for (int m = 16; m; m >>= 1) err += __shfl_xor_sync(0xffffffffu, err, m);
-    if (!(threadIdx.x & 31) && err)
-        atomicAdd(a.err + t.unit, err);
+        for (int j = 0; j < LRS_CAND; j++) {
+            if (j < n) { // uniform over the CTA
+                const int v = (uu << 7) + xq0[j] * d0 + xq1[j] * d1;
+                const int e = ((v + (1 << 10)) >> 11) - sv;
+                err32[j] += (unsigned)(e * e);
+            }
+        }
+    }
+    unsigned long long err[LRS_CAND];
+#pragma unroll
+    for (int j = 0; j < LRS_CAND; j++) {
+        err[j] = err32[j];
+#pragma unroll
+        for (int m = 16; m; m >>= 1) err[j] += __shfl_xor_sync(0xffffffffu, err[j], m);
+        if (!(threadIdx.x & 31) && j < n)
+            atomicAdd(a.err + ci * LRS_CAND + j, err[j]);
+    }
 }
 
 } // namespace svtf

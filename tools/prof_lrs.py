@@ -24,3 +24,8 @@ with S.FilterContext(g) as c:
     t0 = time.perf_counter()
     c.compute_stats(0, 256, 7)
     print("luma stats ms", round((time.perf_counter() - t0) * 1e3, 3))
+    cfg2 = H.lr_search_cfg(unit_size=(256, 128, 128), sg=1)
+    for i in range(int(os.environ.get("N", "2"))):
+        t0 = time.perf_counter()
+        ft, units, search = c.restoration_search(cfg2)
+        print("search (Wiener + self-guided) ms", round((time.perf_counter() - t0) * 1e3, 3), ft, list(c.sg_frame_ep_cnt))
