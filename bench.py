@@ -238,6 +238,7 @@ def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
     for _ in range(n):
         ftype, units, search = ctx.restoration_search(cfg)
     dt = (time.perf_counter() - t0) / n
+    wn_launches = (ctx.launch_count - l0) // n
     t0 = time.perf_counter()
     for _ in range(n):
         ctx.compute_stats(0, 256, 7)
@@ -254,7 +255,7 @@ def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
             "gpu_launches_per_picture": (ctx.launch_count - l1) // n, "frame_types": ftype2}
     res = {"metric": "loop-restoration search Mpixel/s (Wiener 7-tap luma + 5-tap chroma, refinement on; picture resident)",
            "value": round(geom.width * geom.height / dt / 1e6, 1), "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 3),
-           "gpu_launches_per_picture": (ctx.launch_count - l0 - n * 2) // n, "luma_stats_ms_incl_download": round(dts * 1e3, 3),
+           "gpu_launches_per_picture": wn_launches, "luma_stats_ms_incl_download": round(dts * 1e3, 3),
            "frame_types": ftype, "wiener_and_self_guided": both, "cpu_baseline": None}
     if with_cpu and H.ref_available():
         g2 = S.make_geom(960, 544, BD)
