@@ -148,6 +148,108 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_con
             atomicAdd(reinterpret_cast<unsigned long long *>(out + i), (unsigned long long)s_acc[i]);
 }
 
+// ---- statistics, second form: one product image per window-offset DIFFERENCE --------------------------------------------
+// H[(c1,r1),(c2,r2)] = sum over the tile of d(p + o1) d(p + o2) depends on o1 and on delta = o2 - o1 only: with
+// P_delta(q) = d(q) d(q + delta) it is the sum of P_delta over the tile shifted by o1.  The upper triangle needs the
+// (WIN - 1)(2 WIN - 1) + WIN differences with dc > 0, or dc = 0 and dr >= 0 (85 for a 7x7 window), each with (WIN - |dr|)(WIN - dc)
+// shifts: 1 225 entries from 85 x 70 x 70 products per 64 x 64 tile instead of 4 096 x 1 225.
+//   stage 1, item = (delta, row qy of the extended tile): the row's products once, R(qy, c1) = sum over the w columns starting
+//            at c1, slid over c1 (one product in, one out); 32-bit, to shared memory (a batch of LRS_DB differences at a time);
+//   stage 2, item = (delta, c1): T(r1, c1) = sum of R over the h rows starting at r1, slid over r1, added to the unit's
+//            64-bit accumulator of entry ((c1, r1), (c1 + dc, r1 + dr)).
+// M (49 products per sample) is accumulated directly.  Same exact integers as lrs_stats_kernel (kept for reference and
+// selectable with SVTF_LRS_STATS_V1=1).
+constexpr int LRS_DB = 11;
+template <typename T, int WIN>
+__global__ void __launch_bounds__(LRS_THREADS) lrs_stats2_kernel(const __grid_constant__ LrsArgs a) {
+    constexpr int WIN2 = WIN * WIN, HW = WIN / 2, ND = (WIN - 1) * (2 * WIN - 1) + WIN, ER = LRS_T + 2 * HW;
+    constexpr int DP = ((ER / 2) & 1) ? ER : ER + 2; // odd pitch in 32-bit words
+    __shared__ int16_t   s_d[ER * DP];
+    __shared__ int16_t   s_x[LRS_T * LRS_T];
+    __shared__ int       s_R[LRS_DB * ER * WIN];
+    __shared__ long long s_M[WIN2];
+    const LrsTile t   = a.tiles[blockIdx.x];
+    const int     tid = threadIdx.x, plane = t.plane, pw = a.pw[plane], ph = a.ph[plane], w = t.w, h = t.h, eh = h + 2 * HW, ew = w + 2 * HW;
+    const T      *cur = static_cast<const T *>(a.cur.p[plane]), *src = static_cast<const T *>(a.src.p[plane]);
+    const int     cp = a.cur.pitch[plane], sp = a.src.pitch[plane];
+    const int     avg = (int)(a.unit_sum[t.unit] / (unsigned long long)a.unit_count[t.unit]);
+    long long    *out = a.acc + a.acc_off[t.unit];
+    if (tid < WIN2)
+        s_M[tid] = 0;
+    for (int i = tid; i < eh * ew; i += LRS_THREADS) {
+        const int r = i / ew, c = i - r * ew;
+        const int y = min(max(t.y0 + r - HW, 0), ph - 1), x = min(max(t.x0 + c - HW, 0), pw - 1);
+        s_d[r * DP + c] = (int16_t)((int)cur[(size_t)y * cp + x] - avg);
+    }
+    for (int i = tid; i < h * w; i += LRS_THREADS) {
+        const int r = i / w, c = i - r * w;
+        s_x[r * LRS_T + c] = (int16_t)((int)src[(size_t)(t.y0 + r) * sp + t.x0 + c] - avg);
+    }
+    __syncthreads();
+    { // M[c * WIN + r] = sum d(py + r, px + c) x(py, px): at most 16 samples per thread, |product| < 2^24
+        int m[WIN2];
+#pragma unroll
+        for (int k = 0; k < WIN2; k++) m[k] = 0;
+        for (int i = tid; i < h * w; i += LRS_THREADS) {
+            const int py = i / w, px = i - py * w, x = s_x[py * LRS_T + px];
+#pragma unroll
+            for (int cc = 0; cc < WIN; cc++)
+#pragma unroll
+                for (int rr = 0; rr < WIN; rr++) m[cc * WIN + rr] += (int)s_d[(py + rr) * DP + px + cc] * x;
+        }
+#pragma unroll
+        for (int k = 0; k < WIN2; k++) {
+            long long v = m[k];
+#pragma unroll
+            for (int q = 16; q; q >>= 1) v += __shfl_xor_sync(0xffffffffu, v, q);
+            if (!(tid & 31) && v)
+                atomicAdd(reinterpret_cast<unsigned long long *>(&s_M[k]), (unsigned long long)v);
+        }
+    }
+    for (int d0 = 0; d0 < ND; d0 += LRS_DB) {
+        const int nd = min(LRS_DB, ND - d0);
+        __syncthreads(); // s_R of the previous batch consumed (first pass: s_M zeroed, tiles staged)
+        for (int it = tid; it < nd * eh; it += LRS_THREADS) {
+            const int qy = it / nd, dl = it - qy * nd, di = d0 + dl;
+            const int dc = di < WIN ? 0 : 1 + (di - WIN) / (2 * WIN - 1), dr = di < WIN ? di : (di - WIN) % (2 * WIN - 1) - (WIN - 1);
+            int      *R = s_R + (dl * ER + qy) * WIN;
+            if (qy + dr < 0 || qy + dr >= eh) {
+#pragma unroll
+                for (int c1 = 0; c1 < WIN; c1++) R[c1] = 0;
+                continue;
+            }
+            const int16_t *pa = s_d + qy * DP, *pb = s_d + (qy + dr) * DP + dc;
+            int            sum = 0;
+            for (int qx = 0; qx < w; qx++) sum += (int)pa[qx] * pb[qx];
+            R[0] = sum;
+            for (int c1 = 1; c1 < WIN - dc; c1++) {
+                sum += (int)pa[c1 + w - 1] * pb[c1 + w - 1] - (int)pa[c1 - 1] * pb[c1 - 1];
+                R[c1] = sum;
+            }
+        }
+        __syncthreads();
+        for (int it = tid; it < nd * WIN; it += LRS_THREADS) {
+            const int dl = it / WIN, c1 = it - dl * WIN, di = d0 + dl;
+            const int dc = di < WIN ? 0 : 1 + (di - WIN) / (2 * WIN - 1), dr = di < WIN ? di : (di - WIN) % (2 * WIN - 1) - (WIN - 1);
+            if (c1 >= WIN - dc)
+                continue;
+            const int  lo = max(0, -dr), hi = min(WIN - 1, WIN - 1 - dr);
+            const int *R = s_R + dl * ER * WIN + c1;
+            long long  sum = 0;
+            for (int qy = lo; qy < lo + h; qy++) sum += R[qy * WIN];
+            for (int r1 = lo; r1 <= hi; r1++) {
+                if (sum)
+                    atomicAdd(reinterpret_cast<unsigned long long *>(out + (c1 * WIN + r1) * WIN2 + (c1 + dc) * WIN + r1 + dr), (unsigned long long)sum);
+                if (r1 < hi)
+                    sum += R[(r1 + h) * WIN] - R[r1 * WIN];
+            }
+        }
+    }
+    __syncthreads();
+    if (tid < WIN2 && s_M[tid])
+        atomicAdd(reinterpret_cast<unsigned long long *>(out + WIN2 * WIN2 + tid), (unsigned long long)s_M[tid]);
+}
+
 // get_pixel_proj_error (Encoder/Codec/EbRestorationPick.c:305; svt_av1_[lowbd|highbd]_pixel_proj_error_c :167/:233) for every
 // unit that has candidates pending: from the stored filter outputs (lr_kernel<T, LR_FLT>),
 // v = (u << 7) + xq0 (flt0 - u) + xq1 (flt1 - u), e = round(v, 11) - source (no clipping, as the reference), sum e^2 per unit.
