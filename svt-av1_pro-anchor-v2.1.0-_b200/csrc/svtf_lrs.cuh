@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_con
 // selectable with SVTF_LRS_STATS_V1=1).
 constexpr int LRS_DB = 11;
 template <typename T, int WIN>
-__global__ void __launch_bounds__(LRS_THREADS) lrs_stats2_kernel(const __grid_constant__ LrsArgs a) {
+__global__ void __launch_bounds__(LRS_THREADS, 4) lrs_stats2_kernel(const __grid_constant__ LrsArgs a) {
     constexpr int WIN2 = WIN * WIN, HW = WIN / 2, ND = (WIN - 1) * (2 * WIN - 1) + WIN, ER = LRS_T + 2 * HW;
     constexpr int DP = ((ER / 2) & 1) ? ER : ER + 2; // odd pitch in 32-bit words
     __shared__ int16_t   s_d[ER * DP];
@@ -187,23 +187,25 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats2_kernel(const __grid_co
     }
     __syncthreads();
     { // M[c * WIN + r] = sum d(py + r, px + c) x(py, px): at most 16 samples per thread, |product| < 2^24
-        int m[WIN2];
+        // one window column at a time: WIN accumulators live, so the kernel stays at 4+ CTAs per SM
+        for (int cc = 0; cc < WIN; cc++) {
+            int m[WIN];
 #pragma unroll
-        for (int k = 0; k < WIN2; k++) m[k] = 0;
-        for (int i = tid; i < h * w; i += LRS_THREADS) {
-            const int py = i / w, px = i - py * w, x = s_x[py * LRS_T + px];
+            for (int rr = 0; rr < WIN; rr++) m[rr] = 0;
+            for (int i = tid; i < h * w; i += LRS_THREADS) {
+                const int py = i / w, px = i - py * w, x = s_x[py * LRS_T + px];
 #pragma unroll
-            for (int cc = 0; cc < WIN; cc++)
+                for (int rr = 0; rr < WIN; rr++) m[rr] += (int)s_d[(py + rr) * DP + px + cc] * x;
+            }
 #pragma unroll
-                for (int rr = 0; rr < WIN; rr++) m[cc * WIN + rr] += (int)s_d[(py + rr) * DP + px + cc] * x;
-        }
+            for (int rr = 0; rr < WIN; rr++) {
+                int v = m[rr]; // a warp's total: 32 * 16 products < 2^24 * 2^9 overflows 32 bits at 12-bit -> reduce in 64
+                long long v64 = v;
 #pragma unroll
-        for (int k = 0; k < WIN2; k++) {
-            long long v = m[k];
-#pragma unroll
-            for (int q = 16; q; q >>= 1) v += __shfl_xor_sync(0xffffffffu, v, q);
-            if (!(tid & 31) && v)
-                atomicAdd(reinterpret_cast<unsigned long long *>(&s_M[k]), (unsigned long long)v);
+                for (int q = 16; q; q >>= 1) v64 += __shfl_xor_sync(0xffffffffu, v64, q);
+                if (!(tid & 31) && v64)
+                    atomicAdd(reinterpret_cast<unsigned long long *>(&s_M[cc * WIN + rr]), (unsigned long long)v64);
+            }
         }
     }
     for (int d0 = 0; d0 < ND; d0 += LRS_DB) {
@@ -220,6 +222,7 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats2_kernel(const __grid_co
             }
             const int16_t *pa = s_d + qy * DP, *pb = s_d + (qy + dr) * DP + dc;
             int            sum = 0;
+#pragma unroll 8
             for (int qx = 0; qx < w; qx++) sum += (int)pa[qx] * pb[qx];
             R[0] = sum;
             for (int c1 = 1; c1 < WIN - dc; c1++) {
@@ -236,6 +239,7 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats2_kernel(const __grid_co
             const int  lo = max(0, -dr), hi = min(WIN - 1, WIN - 1 - dr);
             const int *R = s_R + dl * ER * WIN + c1;
             long long  sum = 0;
+#pragma unroll 8
             for (int qy = lo; qy < lo + h; qy++) sum += R[qy * WIN];
             for (int r1 = lo; r1 <= hi; r1++) {
                 if (sum)
