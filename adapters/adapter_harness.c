@@ -392,6 +392,14 @@ API int adapt_lr_search(const svtf_geom *g, void *y, int sy, void *cb, int scb, 
         cm.sg_filter_ctrls.ep_inc[t] = (int8_t)cfg->sg_ep_inc[t], cm.sg_filter_ctrls.refine[t] = (int8_t)cfg->sg_refine[t];
     }
     cm.sg_ref_frame_ep[0] = cm.sg_ref_frame_ep[1] = -1;
+    cm.wn_filter_ctrls.use_prev_frame_coeffs = cfg->prev_units[0] || cfg->prev_units[1] || cfg->prev_units[2];
+    h.ppcs->frm_hdr.frame_type               = cm.wn_filter_ctrls.use_prev_frame_coeffs ? INTER_FRAME : KEY_FRAME;
+    for (int p = 0; p < 3; p++)
+        for (int u = 0; u < h.pcs->rst_info[p].units_per_tile && cfg->prev_units[p]; u++) {
+            h.pcs->rst_info[p].unit_info[u].restoration_type = (RestorationType)cfg->prev_units[p][u].restoration_type;
+            memcpy(h.pcs->rst_info[p].unit_info[u].wiener_info.vfilter, cfg->prev_units[p][u].wiener_vfilter, 16);
+            memcpy(h.pcs->rst_info[p].unit_info[u].wiener_info.hfilter, cfg->prev_units[p][u].wiener_hfilter, 16);
+        }
     for (int p = 0; p < 3; p++) h.pcs->rusi_picture[p] = calloc(h.pcs->rst_info[p].units_per_tile, sizeof(RestUnitSearchInfo));
     void *const      cur[3] = {y, cb, cr}, *const org[3] = {oy, ocb, ocr};
     const int        cst[3] = {sy, scb, scr}, ost[3] = {osy, oscb, oscr};

@@ -615,8 +615,8 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
  * land where the reference leaves them: pcs->rusi_picture[plane][unit] (sse[RESTORE_NONE], sse[RESTORE_WIENER], wiener) after
  * the segment call, rst_info[plane].frame_restoration_type / unit_info[] after rest_finish_search.
  * Covered: the Wiener and the self-guided tools (and RESTORE_SWITCHABLE between them) without stripe boundaries
- * (scs->use_boundaries_in_rest_search = 0, the reference's setting, Encoder/Globals/EbEncHandle.c:4162).  Not covered:
- * wn_filter_ctrls.use_prev_frame_coeffs — the adapter aborts rather than return a different decision.
+ * (scs->use_boundaries_in_rest_search = 0, the reference's setting, Encoder/Globals/EbEncHandle.c:4162; with 1 the adapter
+ * aborts rather than return a different decision), wn_filter_ctrls.use_prev_frame_coeffs included.
  * org_fts is the picture after CDEF (uploaded unless the chain is resident), src the source picture.
  * ---------------------------------------------------------------------------------------------------- */
 typedef struct {
@@ -649,9 +649,8 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     Av1Common        *cm = pcs->ppcs->av1_cm;
     const Macroblock *x  = pcs->ppcs->av1x;
     CtxSlot          *s  = slot_for(pcs);
-    if (cm->use_boundaries_in_rest_search || (cm->wn_filter_ctrls.enabled && cm->wn_filter_ctrls.use_prev_frame_coeffs)) {
-        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: restoration_seg_search needs use_boundaries_in_rest_search = 0 and "
-                        "wn_filter_ctrls.use_prev_frame_coeffs = 0\n");
+    if (cm->use_boundaries_in_rest_search) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: restoration_seg_search needs use_boundaries_in_rest_search = 0\n");
         abort();
     }
     svtf_lr_search_cfg cfg;
@@ -692,6 +691,20 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
         CHECK(svtf_upload_frame(s->ctx, fp[0], fst[0], fp[1], fst[1], fp[2], fst[2]), s->ctx);
     }
     CHECK(svtf_upload_source(s->ctx, sp[0], sst[0], sp[1], sst[1], sp[2], sst[2]), s->ctx);
+    /* use_prev_frame_coeffs (:1313-1319): the taps EbRestProcess.c:586-597 left in rst_info[].unit_info[] */
+    svtf_lr_unit *prev[3] = {NULL, NULL, NULL};
+    if (cm->wn_filter_ctrls.enabled && cm->wn_filter_ctrls.use_prev_frame_coeffs && pcs->ppcs->frm_hdr.frame_type != KEY_FRAME &&
+        pcs->ppcs->frm_hdr.frame_type != INTRA_ONLY_FRAME)
+        for (int p = 0; p < 3; p++) {
+            prev[p] = (svtf_lr_unit *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit));
+            for (int u = 0; u < pcs->rst_info[p].units_per_tile; u++) {
+                const RestorationUnitInfo *ri = &pcs->rst_info[p].unit_info[u];
+                prev[p][u].restoration_type   = ri->restoration_type == RESTORE_WIENER ? SVTF_RESTORE_WIENER : SVTF_RESTORE_NONE;
+                memcpy(prev[p][u].wiener_vfilter, ri->wiener_info.vfilter, sizeof(prev[p][u].wiener_vfilter));
+                memcpy(prev[p][u].wiener_hfilter, ri->wiener_info.hfilter, sizeof(prev[p][u].wiener_hfilter));
+            }
+            cfg.prev_units[p] = prev[p];
+        }
     LrSearchResult      *r = lr_result_for(pcs, 1);
     svtf_lr_unit_search *us[3];
     if (!r) {
@@ -726,7 +739,7 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
                 ri->sgrproj.xqd[0] = us[p][u].sgr_xqd[0], ri->sgrproj.xqd[1] = us[p][u].sgr_xqd[1];
             }
         }
-    for (int p = 0; p < 3; p++) free(us[p]);
+    for (int p = 0; p < 3; p++) free(us[p]), free(prev[p]);
 }
 
 void rest_finish_search(PictureControlSet *pcs) {

@@ -326,7 +326,7 @@ int svtf_lf_search_frame(svtf_ctx *ctx, const svtf_lf_params *start, const svtf_
  * The picture searched is the context's current picture (after CDEF / CCSO), the source the uploaded source picture.
  * The search filters WITHOUT stripe boundaries (scs->use_boundaries_in_rest_search = 0, EbEncHandle.c:4162: rows
  * above / below a stripe are the picture's own rows; the frame edge is replicated, svt_extend_frame).
- * Not covered: use_prev_frame_coeffs (Wiener taps carried over from the previous frame). */
+ * use_prev_frame_coeffs: see svtf_lr_search_cfg.prev_units. */
 typedef struct svtf_lr_search_cfg {
     int32_t restoration_unit_size[3];   /* rst_info[p].restoration_unit_size                                      */
     int32_t wn_enabled;                 /* cm->wn_filter_ctrls.enabled (Common/Codec/Av1Common.h:32-45)           */
@@ -344,6 +344,11 @@ typedef struct svtf_lr_search_cfg {
     int32_t wiener_restore_cost[2];     /* x->wiener_restore_cost (bits << AV1_PROB_COST_SHIFT)                   */
     int32_t sgrproj_restore_cost[2];    /* x->sgrproj_restore_cost                                                */
     int32_t switchable_restore_cost[3]; /* x->switchable_restore_cost                                             */
+    /* wn_filter_ctrls.use_prev_frame_coeffs on a frame that is neither KEY nor INTRA_ONLY (:1313-1319): units whose entry here
+     * has restoration_type SVTF_RESTORE_WIENER start the refinement from these taps (what the reference finds in
+     * pcs->rst_info[p].unit_info[], copied from the first list-0 reference picture, EbRestProcess.c:586-597) instead of
+     * solving for new ones.  NULL pointers: every unit is solved. */
+    const svtf_lr_unit *prev_units[3];
 } svtf_lr_search_cfg;
 /* Per restoration unit, what restoration_seg_search leaves in RestUnitSearchInfo (Common/Codec/EbRestoration.h:349): sse of
  * RESTORE_NONE / RESTORE_WIENER (INT64_MAX: no usable filter) / RESTORE_SGRPROJ, the refined Wiener taps, the self-guided

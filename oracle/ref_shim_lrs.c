@@ -74,7 +74,7 @@ REF_API int ref_lr_search(const svtf_geom *g, const void *y, int sy, const void 
     cm->wn_filter_ctrls.filter_tap_lvl          = (uint8_t)cfg->wn_filter_tap_lvl;
     cm->wn_filter_ctrls.use_refinement          = (Bool)cfg->wn_use_refinement;
     cm->wn_filter_ctrls.max_one_refinement_step = (Bool)cfg->wn_max_one_refinement_step;
-    cm->wn_filter_ctrls.use_prev_frame_coeffs   = 0;
+    cm->wn_filter_ctrls.use_prev_frame_coeffs   = cfg->prev_units[0] || cfg->prev_units[1] || cfg->prev_units[2];
     cm->wn_filter_ctrls.use_chroma              = (Bool)cfg->wn_use_chroma;
     cm->sg_filter_ctrls.enabled                 = (Bool)cfg->sg_enabled;
     cm->sg_filter_ctrls.use_chroma              = (Bool)cfg->sg_use_chroma;
@@ -86,7 +86,7 @@ REF_API int ref_lr_search(const svtf_geom *g, const void *y, int sy, const void 
     cm->sg_ref_frame_ep[0] = cm->sg_ref_frame_ep[1] = -1;
     x->sgrproj_restore_cost[0] = cfg->sgrproj_restore_cost[0], x->sgrproj_restore_cost[1] = cfg->sgrproj_restore_cost[1];
     for (int t = 0; t < 3; t++) x->switchable_restore_cost[t] = cfg->switchable_restore_cost[t];
-    ppcs->frm_hdr.frame_type                    = KEY_FRAME;
+    ppcs->frm_hdr.frame_type                    = cm->wn_filter_ctrls.use_prev_frame_coeffs ? INTER_FRAME : KEY_FRAME;
     x->rdmult                                   = cfg->rdmult;
     x->wiener_restore_cost[0] = cfg->wiener_restore_cost[0], x->wiener_restore_cost[1] = cfg->wiener_restore_cost[1];
     for (int p = 0; p < 3; p++) {
@@ -96,6 +96,12 @@ REF_API int ref_lr_search(const svtf_geom *g, const void *y, int sy, const void 
     if (svt_av1_alloc_restoration_buffers(pcs, cm) != EB_ErrorNone)
         return -1;
     for (int p = 0; p < 3; p++) pcs->rusi_picture[p] = calloc(pcs->rst_info[p].units_per_tile, sizeof(RestUnitSearchInfo));
+    for (int p = 0; p < 3; p++) /* what EbRestProcess.c:586-597 copies from the reference picture */
+        for (int u = 0; u < pcs->rst_info[p].units_per_tile && cfg->prev_units[p]; u++) {
+            pcs->rst_info[p].unit_info[u].restoration_type = (RestorationType)cfg->prev_units[p][u].restoration_type;
+            memcpy(pcs->rst_info[p].unit_info[u].wiener_info.vfilter, cfg->prev_units[p][u].wiener_vfilter, 16);
+            memcpy(pcs->rst_info[p].unit_info[u].wiener_info.hfilter, cfg->prev_units[p][u].wiener_hfilter, 16);
+        }
     pcs->rest_segments_column_count = pcs->rest_segments_row_count = 1;
     const void *const cur[3] = {y, cb, cr}, *const src[3] = {oy, ocb, ocr};
     const int         cst[3] = {sy, scb, scr}, sst[3] = {osy, oscb, oscr};

@@ -453,9 +453,16 @@ ORC_API int orc_lr_search_frame(const svtf_geom *g, const void *y, int sy, const
             us[u].sse[0] = orc_lr_try_unit(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, ss, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], &none);
             us[u].sse[1] = INT64_MAX;
             if (do_wn) {
-                orc_lr_wiener_stats(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], win, M, H);
                 int16_t vf[8], hf[8];
-                if (orc_lr_wiener_from_stats(win, M, H, vf, hf)) {
+                int     ok;
+                if (cfg->prev_units[p] && cfg->prev_units[p][u].restoration_type == SVTF_RESTORE_WIENER) { /* :1313-1319 */
+                    memcpy(vf, cfg->prev_units[p][u].wiener_vfilter, 16), memcpy(hf, cfg->prev_units[p][u].wiener_hfilter, 16);
+                    ok = 1;
+                } else {
+                    orc_lr_wiener_stats(c.cur, c.cst, c.src, c.sst, c.sb, c.bd, c.pw, c.ph, lim[0], lim[1], lim[2], lim[3], win, M, H);
+                    ok = orc_lr_wiener_from_stats(win, M, H, vf, hf);
+                }
+                if (ok) {
                     us[u].sse[1] = refine(&c, lim, win, cfg, vf, hf);
                     memcpy(us[u].wiener_vfilter, vf, 16), memcpy(us[u].wiener_hfilter, hf, 16);
                 }

@@ -70,7 +70,7 @@ class LrSearchCfg(C.Structure):
                 ("wn_use_refinement", C.c_int32), ("wn_max_one_refinement_step", C.c_int32), ("wn_use_chroma", C.c_int32),
                 ("sg_enabled", C.c_int32), ("sg_use_chroma", C.c_int32), ("sg_start_ep", C.c_int32 * 2), ("sg_end_ep", C.c_int32 * 2),
                 ("sg_ep_inc", C.c_int32 * 2), ("sg_refine", C.c_int32 * 2), ("rdmult", C.c_int32), ("wiener_restore_cost", C.c_int32 * 2),
-                ("sgrproj_restore_cost", C.c_int32 * 2), ("switchable_restore_cost", C.c_int32 * 3)]
+                ("sgrproj_restore_cost", C.c_int32 * 2), ("switchable_restore_cost", C.c_int32 * 3), ("prev_units", C.c_void_p * 3)]
 
 
 class LrUnitSearch(C.Structure):

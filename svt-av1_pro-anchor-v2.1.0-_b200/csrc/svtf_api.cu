@@ -1989,15 +1989,20 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
     std::vector<LrsRefine>           ref(plan.units);
     // the solve of a unit (integer alternating least squares, ~20k multiply-divides for a 7x7 window) is independent of every
     // other unit: a few host threads share them (the reference spreads units over its restoration segments the same way)
-    std::vector<int> win_of(plan.units), plane_of(plan.units);
+    std::vector<int> win_of(plan.units), plane_of(plan.units), first_of(plan.units);
     for (const LrsPlane &pl : plan.planes)
-        for (int u = 0; u < pl.hu * pl.vu; u++) win_of[pl.first + u] = pl.win, plane_of[pl.first + u] = pl.plane;
+        for (int u = 0; u < pl.hu * pl.vu; u++) win_of[pl.first + u] = pl.win, plane_of[pl.first + u] = pl.plane, first_of[pl.first + u] = pl.first;
     host_parallel_for(plan.units, [&](int u) {
         svtf_lr_unit_search &s = us[u];
         std::memset(&s, 0, sizeof(s));
         s.sse[0] = (int64_t)sse_none[u], s.sse[1] = INT64_MAX;
         if (!do_wn[plane_of[u]])
             return;
+        const svtf_lr_unit *prev = cfg->prev_units[plane_of[u]] ? cfg->prev_units[plane_of[u]] + (u - first_of[u]) : nullptr;
+        if (prev && prev->restoration_type == SVTF_RESTORE_WIENER) { // use_prev_frame_coeffs :1313-1319: no solve, no score check
+            ref[u].start(win_of[u], cfg->wn_use_refinement != 0, cfg->wn_max_one_refinement_step != 0, prev->wiener_vfilter, prev->wiener_hfilter);
+            return;
+        }
         int64_t M[49], H[49 * 49];
         lrs_finish_stats(c->geom, win_of[u], acc + plan.acc_off[u], M, H);
         int16_t vf[8], hf[8];

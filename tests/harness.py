@@ -278,7 +278,7 @@ def _lr_call(fn, geom, cur, dbk, lr, units):
 
 
 def lr_search_cfg(unit_size=(64, 32, 32), tap_lvl=1, refinement=1, one_step=0, chroma=1, rdmult=9000, cost=(120, 900), wn=1, sg=0, sg_chroma=1,
-                  sg_ep=((0, 16, 1, 1), (0, 16, 1, 1)), sg_cost=(130, 950), sw_cost=(150, 1000, 1100)):
+                  sg_ep=((0, 16, 1, 1), (0, 16, 1, 1)), sg_cost=(130, 950), sw_cost=(150, 1000, 1100), prev_units=None):
     """WnFilterCtrls / SgFilterCtrls of a search (Encoder/Codec/EncModeConfig.c set_wn_filter_ctrls / set_sg_filter_ctrls) + the rate
     inputs.  sg_ep: (start_ep, end_ep, ep_inc, refine) for luma and chroma."""
     c = L.LrSearchCfg()
@@ -291,6 +291,10 @@ def lr_search_cfg(unit_size=(64, 32, 32), tap_lvl=1, refinement=1, one_step=0, c
         c.wiener_restore_cost[t], c.sgrproj_restore_cost[t] = cost[t], sg_cost[t]
     for t in range(3):
         c.switchable_restore_cost[t] = sw_cost[t]
+    if prev_units is not None:  # use_prev_frame_coeffs: LrUnit arrays (kept alive on the struct)
+        c._keep = prev_units
+        for p in range(3):
+            c.prev_units[p] = C.cast(prev_units[p], C.c_void_p) if prev_units[p] is not None else None
     return c
 
 

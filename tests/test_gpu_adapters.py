@@ -222,7 +222,8 @@ def test_pad_ref_pictures_adapter(H, orc, adapt, w, h, bd, sb, resident):
 
 
 @pytest.mark.parametrize("w,h,bd,sb,kw", [(200, 136, 10, 2, {}), (136, 72, 8, 1, {"tap_lvl": 2, "one_step": 1}), (264, 136, 8, 2, {"chroma": 0}),
-                                          (136, 104, 10, 2, {"sg": 1}), (136, 72, 8, 1, {"wn": 0, "sg": 1, "sg_ep": ((0, 16, 3, 1), (8, 16, 1, 0))})])
+                                          (136, 104, 10, 2, {"sg": 1}), (136, 72, 8, 1, {"wn": 0, "sg": 1, "sg_ep": ((0, 16, 3, 1), (8, 16, 1, 0))}),
+                                          (200, 136, 10, 2, {"prev": 1})])
 def test_restoration_search_adapter(H, orc, adapt, w, h, bd, sb, kw):
     """restoration_seg_search(.., segment 0) + rest_finish_search on real PictureControlSet / Av1Common / Macroblock structures:
     rusi_picture[] and rst_info[] end up as the oracle's (pinned to the reference's own search) say.  The planes handed over
@@ -231,7 +232,8 @@ def test_restoration_search_adapter(H, orc, adapt, w, h, bd, sb, kw):
     g = S.make_geom(w, h, bd, sb)
     src = H.synth_picture(g, 14000 + w, noise=10)
     cur = H.synth_source(g, src, 14001, amp=6)
-    cfg = H.lr_search_cfg(**kw)
+    prev = H.synth_lr(g, 14002, p_none=0.3, p_wiener=0.5)[1] if kw.pop("prev", 0) else None
+    cfg = H.lr_search_cfg(prev_units=prev, **kw)
     got = H._lr_search_call(adapt.adapt_lr_search, g, cur, src, cfg)
     vis = lambda pl: [np.ascontiguousarray(p[: (g.height + s) >> s, : (g.width + s) >> s]) for p, s in zip(pl, (0, 1, 1))]
     exp = orc.lr_search(g, vis(cur), vis(src), cfg)

@@ -92,6 +92,16 @@ def test_lr_search_matches_oracle(H, orc, w, h, bd, sb, seed, kw):
         assert any(t != 0 for t in ftype)
 
 
+@pytest.mark.parametrize("w,h,bd,sb,seed,kw", [(136, 104, 10, 2, 31, {}), (200, 72, 8, 1, 32, {"sg": 1, "one_step": 1})])
+def test_lr_search_prev_frame_coeffs(H, orc, w, h, bd, sb, seed, kw):
+    g, cur, src = search_case(H, w, h, bd, sb, seed)
+    _, prev = H.synth_lr(g, 900 + seed, p_none=0.3, p_wiener=0.5)
+    cfg = H.lr_search_cfg(prev_units=prev, **kw)
+    ctx = ctx_with(H, g, cur, src)
+    ftype, units, search = ctx.restoration_search(cfg)
+    assert H.lr_search_sig(g, cfg, ftype, units, search, ctx.sg_frame_ep_cnt) == orc.lr_search(g, vis(g, cur), vis(g, src), cfg)
+
+
 def test_lr_search_then_apply_lowers_error(H):
     """Property at a larger size: applying what the search returns must not raise the squared error of any searched plane
     (without stripe boundaries the search's own SSE is what the frame filter would give; with them it stays close)."""

@@ -73,6 +73,19 @@ def test_oracle_lr_search_matches_reference(H, orc, ref, w, h, bd, sb, seed, kw)
     assert a[3] == b[3], "sg_frame_ep_cnt"
 
 
+@pytest.mark.parametrize("w,h,bd,sb,seed,kw", [(136, 104, 10, 2, 31, {}), (200, 72, 8, 1, 32, {"sg": 1, "one_step": 1})])
+def test_oracle_lr_search_prev_frame_coeffs(H, orc, ref, w, h, bd, sb, seed, kw):
+    """wn_filter_ctrls.use_prev_frame_coeffs on an inter frame: units that were RESTORE_WIENER in the reference picture start
+    from its taps (no statistics, no score check), the others are solved."""
+    g, cur, src = search_case(H, w, h, bd, sb, seed)
+    _, prev = H.synth_lr(g, 900 + seed, p_none=0.3, p_wiener=0.5)
+    cfg = H.lr_search_cfg(prev_units=prev, **kw)
+    a = orc.lr_search(g, vis(g, cur), vis(g, src), cfg)
+    b = ref.lr_search(g, vis(g, cur), vis(g, src), cfg)
+    assert a == b
+    assert a != orc.lr_search(g, vis(g, cur), vis(g, src), H.lr_search_cfg(**kw))
+
+
 def test_product_host_solve_matches_oracle(H, orc):
     """svtf_lr_wiener_from_stats (the product's host code, no GPU needed) against the oracle on real and on degenerate statistics."""
     S = H.S
