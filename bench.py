@@ -223,7 +223,7 @@ def lf_search_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
-def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
+def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu, more_ctxs=()):
     """Loop-restoration filter search, Wiener tools (restoration_seg_search + rest_finish_search): statistics of every unit,
     host solve, refinement trials of all units in lock-step; the reference's C on a smaller picture."""
     src = H.synth_source(geom, wl["rec"], 0xB200F1, amp=6)
@@ -257,6 +257,21 @@ def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu):
            "value": round(geom.width * geom.height / dt / 1e6, 1), "unit": "Mpixel/s", "ms_per_picture": round(dt * 1e3, 3),
            "gpu_launches_per_picture": wn_launches, "luma_stats_ms_incl_download": round(dts * 1e3, 3),
            "frame_types": ftype, "wiener_and_self_guided": both, "cpu_baseline": None}
+    if more_ctxs:  # several pictures in flight: one context + submitting host thread each (the encoder keeps pictures in flight)
+        from concurrent.futures import ThreadPoolExecutor
+
+        pool_ctxs = [ctx] + list(more_ctxs)
+        for c in pool_ctxs[1:]:
+            c.begin(geom)
+            c.upload(src)
+            c.upload_source(wl["rec"])
+        with ThreadPoolExecutor(len(pool_ctxs)) as pool:
+            list(pool.map(lambda c: c.restoration_search(cfg), pool_ctxs))
+            t0 = time.perf_counter()
+            list(pool.map(lambda c: [c.restoration_search(cfg) for _ in range(n)], pool_ctxs))
+            dtp = (time.perf_counter() - t0) / (n * len(pool_ctxs))
+        res["pictures_in_flight"] = {"n": len(pool_ctxs), "value": round(geom.width * geom.height / dtp / 1e6, 1), "unit": "Mpixel/s",
+                                     "ms_per_picture": round(dtp * 1e3, 3)}
     if with_cpu and H.ref_available():
         g2 = S.make_geom(960, 544, BD)
         rec = H.synth_picture(g2, 0xF11)
@@ -846,7 +861,7 @@ def main():
     side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
     hand = handoff_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
-    lrs = lr_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
+    lrs = lr_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu, ctxs[1:4]) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
