@@ -237,9 +237,16 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
                 continue;
             T *o = out + (size_t)(y0 + rb) * op + x0 + c;
             if (c < wv) {
-                int x[14];
+                int x[14], sv[8];
+                if (SSE) { // the source samples first: their latency hides behind the filter arithmetic
 #pragma unroll
-                for (int t = 0; t < 14; t++) x[t] = rb + t < h + 6 ? tmp[(rb + t) * TW + c] : 0;
+                    for (int j = 0; j < 8; j++) sv[j] = rb + j < h ? (int)srcp[(size_t)(y0 + rb + j) * sp + x0 + c] : 0;
+                }
+                // rows beyond h + 6 of the last segment are never-written shared memory inside s_buf: they only feed outputs
+                // rb + j >= h, which are dropped
+                const uint16_t *tp = tmp + rb * TW + c;
+#pragma unroll
+                for (int t = 0; t < 14; t++) x[t] = tp[t * TW];
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
                     if (rb + j >= h)
@@ -249,7 +256,7 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
                     for (int t = 0; t < 7; t++) sum += x[j + t] * vf[t];
                     const int v = min(max(lr_rnd(sum, r1), 0), maxv);
                     if (SSE) {
-                        const int d = v - (int)srcp[(size_t)(y0 + rb + j) * sp + x0 + c];
+                        const int d = v - sv[j];
                         my_sse += (unsigned)(d * d);
                     } else
                         o[(size_t)j * op] = (T)v;
