@@ -404,6 +404,23 @@ int svtf_cdef_pick_table(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, const u
 int svtf_cdef_pick_host(const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
                         svtf_cdef_params *out_params, int8_t *fb_strength_idx);
 
+/* ---- super-resolution: the normative upscale between CDEF and loop restoration ----------------
+ * svt_av1_superres_upscale_frame (Encoder/Codec/EbRestProcess.c:405; decoder svt_av1_superres_upscale,
+ * Decoder/Codec/EbDecSuperRes.c:119) = svt_av1_upscale_normative_rows (Common/Codec/EbSuperRes.c:214) on every plane:
+ * an 8-tap horizontal filter with 64 phases, position step ((in << 14) + out / 2) / out, restarted per tile column
+ * (:223-283), left / right frame edge replicated (upscale_normative_rect :102).  The current picture and, when one is
+ * kept, the picture before CDEF (the restoration stripe borders, EbRestoration.c:1545-1560) are upscaled; the context's
+ * geometry becomes upscaled_width x height (it must fit the geometry the context was created for).  The mode info no
+ * longer matches the picture afterwards: only loop restoration, the hand-off and downloads follow. */
+typedef struct svtf_superres_params {
+    int32_t        upscaled_width;        /* cm->frm_size.superres_upscaled_width                                  */
+    int32_t        superres_denominator;  /* cm->frm_size.superres_denominator, 9..16 (8 = unscaled: nothing to do) */
+    int32_t        tile_cols;             /* cm->tiles_info.tile_cols, 1..64                                       */
+    int32_t        tile_col_start_mi[65]; /* cm->tiles_info.tile_col_start_mi[0..tile_cols] of the coded picture   */
+    const int16_t *filters;               /* av1_resize_filter_normative[64][8] (Common/Codec/EbSuperRes.h:22)     */
+} svtf_superres_params;
+int svtf_superres_upscale_frame(svtf_ctx *ctx, const svtf_superres_params *sr);
+
 /* ---- device-side access for multi-GPU stripe exchange and device-resident benches ----------- */
 typedef struct svtf_dev_plane {
     void   *ptr;   /* device pointer to sample (0,0) */

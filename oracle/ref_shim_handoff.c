@@ -39,3 +39,29 @@ void ref_convert_8_to_16(const uint8_t *src, int32_t src_stride, uint16_t *dst, 
 void ref_convert_16_to_8(const uint16_t *src, int32_t src_stride, uint8_t *dst, int32_t dst_stride, int32_t width, int32_t height) {
     svt_convert_16bit_to_8bit_c((uint16_t *)src, src_stride, dst, dst_stride, width, height);
 }
+
+/* ---- super-resolution upscale of one plane through the reference's own svt_av1_upscale_normative_rows
+ * (Common/Codec/EbSuperRes.c, compiled where it lies) ---- */
+#include "EbInterPrediction.h"
+#include "EbSuperRes.h"
+#include "Av1Common.h"
+__attribute__((visibility("default"))) const int16_t *ref_superres_filters(void) { return &av1_resize_filter_normative[0][0]; }
+__attribute__((visibility("default"))) int ref_superres_plane(const void *src, int sst, void *dst, int dstst, int sb, int bd, int rows, int src_cw,
+                                                              int ds_frame_w, int up_frame_w, int denom, int ss, int mi_cols, int tile_cols,
+                                                              const int32_t *tile_col_start_mi) {
+    Av1Common *cm = calloc(1, sizeof(*cm));
+    if (!cm)
+        return -1;
+    cm->frm_size.frame_width = (uint16_t)ds_frame_w, cm->frm_size.superres_upscaled_width = (uint16_t)up_frame_w;
+    cm->frm_size.superres_denominator = (uint8_t)denom;
+    cm->mi_cols                       = mi_cols;
+    cm->tiles_info.tile_cols          = (uint8_t)tile_cols;
+    for (int j = 0; j <= tile_cols; j++) cm->tiles_info.tile_col_start_mi[j] = (uint16_t)tile_col_start_mi[j];
+    /* the function pads 5 columns left and right of the coded plane in place: give it room */
+    const int stride = src_cw + 32;
+    uint8_t  *buf    = calloc((size_t)stride * rows, sb);
+    for (int y = 0; y < rows; y++) memcpy(buf + ((size_t)y * stride + 16) * sb, (const uint8_t *)src + (size_t)y * sst * sb, (size_t)src_cw * sb);
+    svt_av1_upscale_normative_rows(cm, buf + 16 * sb, stride, (uint8_t *)dst, dstst, rows, ss, bd, sb == 2);
+    free(buf), free(cm);
+    return 0;
+}

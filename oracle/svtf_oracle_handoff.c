@@ -67,3 +67,38 @@ ORC_API void svtf_orc_convert_16_to_8(const uint16_t *src, int32_t src_stride, u
     for (int32_t y = 0; y < height; y++)
         for (int32_t x = 0; x < width; x++) dst[(size_t)y * dst_stride + x] = (uint8_t)src[(size_t)y * src_stride + x];
 }
+
+/* ---- super-resolution upscale of one plane: svt_av1_upscale_normative_rows (Common/Codec/EbSuperRes.c:214) with
+ * av1_[highbd_]convolve_horiz_rs_c (:60 / :80) and the edge replication of upscale_normative_rect (:102).
+ * src: coded plane (src_cw = mi_cols * 4 >> ss columns), ds_w / up_w: visible plane widths before / after, filters:
+ * av1_resize_filter_normative[64][8] handed in by the caller (Common/Codec/EbSuperRes.h:22). ---- */
+ORC_API void svtf_orc_superres_plane(const void *src, int sst, void *dst, int dstst, int sb, int bd, int rows, int src_cw, int ds_w, int up_w,
+                                     int denom, int ss, int mi_cols, int tile_cols, const int32_t *tile_col_start_mi, const int16_t *filters) {
+    const int step = ((ds_w << 14) + up_w / 2) / up_w;
+    const int err  = up_w * step - (ds_w << 14);
+    int       x0   = (int)((unsigned)((-((up_w - ds_w) << 13) + up_w / 2) / up_w + (1 << 7) - err / 2) & 16383u);
+    for (int j = 0; j < tile_cols; j++) {
+        const int end = tile_col_start_mi[j + 1] < mi_cols ? tile_col_start_mi[j + 1] : mi_cols;
+        const int ds0 = tile_col_start_mi[j] << (2 - ss), ds1 = end << (2 - ss);
+        const int up0 = ds0 * denom / 8, up1 = j == tile_cols - 1 ? up_w : ds1 * denom / 8;
+        for (int y = 0; y < rows; y++) {
+            int xq = x0;
+            for (int x = up0; x < up1; x++, xq += step) {
+                const int16_t *f = filters + ((xq & 16383) >> 8) * 8;
+                int            sum = 0;
+                for (int k = 0; k < 8; k++) {
+                    int c = ds0 - 4 + (xq >> 14) + k;
+                    c     = c < 0 ? 0 : (c > src_cw - 1 ? src_cw - 1 : c);
+                    sum += (sb == 1 ? ((const uint8_t *)src)[(size_t)y * sst + c] : ((const uint16_t *)src)[(size_t)y * sst + c]) * f[k];
+                }
+                int v = (sum + 64) >> 7;
+                v     = v < 0 ? 0 : (v > (1 << bd) - 1 ? (1 << bd) - 1 : v);
+                if (sb == 1)
+                    ((uint8_t *)dst)[(size_t)y * dstst + x] = (uint8_t)v;
+                else
+                    ((uint16_t *)dst)[(size_t)y * dstst + x] = (uint16_t)v;
+            }
+        }
+        x0 += (up1 - up0) * step - ((ds1 - ds0) << 14);
+    }
+}

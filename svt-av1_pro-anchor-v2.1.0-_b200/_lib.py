@@ -79,6 +79,12 @@ class LrUnitSearch(C.Structure):
                 ("sgr_xqd", C.c_int32 * 2), ("reserved", C.c_int32)]
 
 
+class SuperresParams(C.Structure):
+    """svtf_superres_params"""
+    _fields_ = [("upscaled_width", C.c_int32), ("superres_denominator", C.c_int32), ("tile_cols", C.c_int32), ("tile_col_start_mi", C.c_int32 * 65),
+                ("filters", C.c_void_p)]
+
+
 class LfSearchCfg(C.Structure):
     _fields_ = [("dlf_avg", C.c_int32), ("early_exit_convergence", C.c_int32), ("only_4x4", C.c_int32), ("search_chroma", C.c_int32)]
 
@@ -100,7 +106,7 @@ EXPORTS = [
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
     "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
-    "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats",
+    "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
 ]
 
 _lib = None
@@ -143,6 +149,7 @@ def load():
     lib.svtf_lr_apply_frame.argtypes = [vp, C.POINTER(LrParams), C.POINTER(C.c_void_p)]
     lib.svtf_lr_search_frame.argtypes = [vp, C.POINTER(LrSearchCfg), C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                          C.POINTER(C.c_int32)]
+    lib.svtf_superres_upscale_frame.argtypes = [vp, C.POINTER(SuperresParams)]
     lib.svtf_lr_wiener_stats.argtypes = [vp, i32, i32, i32, vp, vp]
     lib.svtf_lr_wiener_from_stats.argtypes = [i32, vp, vp, C.POINTER(C.c_int16), C.POINTER(C.c_int16)]
     lib.svtf_deblock_frame.argtypes = [vp, C.POINTER(LfParams), i32, i32]

@@ -28,6 +28,7 @@
 #include "svtf_lr.cuh"
 #include "svtf_lrs.cuh"
 #include "svtf_handoff.cuh"
+#include "svtf_superres.cuh"
 
 namespace svtf {
 
@@ -1696,6 +1697,95 @@ extern "C" int svtf_lr_apply_frame(svtf_ctx *c, const svtf_lr_params *lr, const 
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
     c->cur = 3;
+    return SVTF_OK;
+}
+
+// ---- super-resolution upscale (svtf_superres.cuh) --------------------------------------------------------------------
+extern "C" int svtf_superres_upscale_frame(svtf_ctx *c, const svtf_superres_params *sr) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_superres_upscale_frame: NULL context");
+    if (!sr || !sr->filters || sr->tile_cols < 1 || sr->tile_cols > 64 || sr->superres_denominator < 8 || sr->superres_denominator > 16)
+        return c->fail(SVTF_E_ARG, "svtf_superres_upscale_frame: bad argument");
+    if (!c->have_frame)
+        return c->fail(SVTF_E_STATE, "svtf_superres_upscale_frame: upload a picture first");
+    if (c->striped)
+        return c->fail(SVTF_E_STATE, "svtf_superres_upscale_frame: not available on a striped context");
+    if (sr->superres_denominator == 8)
+        return SVTF_OK; // av1_superres_unscaled
+    svtf_geom ng = c->geom;
+    ng.width     = sr->upscaled_width;
+    ng.mi_cols   = 2 * ((sr->upscaled_width + 7) >> 3);
+    if (sr->upscaled_width < c->geom.width || ng.mi_cols > c->max_geom.mi_cols)
+        return c->fail(SVTF_E_ARG, "svtf_superres_upscale_frame: the upscaled width must lie between the picture's and the context's width");
+    for (int j = 0; j <= sr->tile_cols; j++)
+        if (sr->tile_col_start_mi[j] < 0 || (j && sr->tile_col_start_mi[j] <= sr->tile_col_start_mi[j - 1]))
+            return c->fail(SVTF_E_ARG, "svtf_superres_upscale_frame: tile_col_start_mi must increase");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (!c->surf[3].base[0]) {
+        cudaError_t e = alloc_surface(c->surf[3], c->max_geom);
+        if (e != cudaSuccess)
+            return c->cuda_fail(e, "cudaMalloc(restoration surface)");
+    }
+    if (c->cur == 3)
+        return c->fail(SVTF_E_STATE, "svtf_superres_upscale_frame: the current picture is already a restoration output");
+    if (int r = handoff_reserve(c, sizeof(SuperresTables)))
+        return r;
+    // per plane and tile column: where the tile starts in both pictures and the sub-sample offset it starts with (:223-283)
+    SuperresTables tab;
+    SuperresArgs   a;
+    std::memcpy(tab.filt, sr->filters, sizeof(tab.filt));
+    a.base[0] = 0;
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        const int ds_w = (c->geom.width + ss) >> ss, up_w = (sr->upscaled_width + ss) >> ss; // ROUND_POWER_OF_TWO(width, sub_x)
+        a.step[p]      = ((ds_w << 14) + up_w / 2) / up_w; // av1_get_upscale_convolve_step
+        const int err  = up_w * a.step[p] - (ds_w << 14);
+        int       x0   = (-((up_w - ds_w) << 13) + up_w / 2) / up_w + (1 << 7) - err / 2; // get_upscale_convolve_x0
+        x0             = (int)((unsigned)x0 & 16383u);
+        for (int j = 0; j < sr->tile_cols; j++) {
+            const int ds0 = sr->tile_col_start_mi[j] << (2 - ss), ds1 = std::min(sr->tile_col_start_mi[j + 1], c->geom.mi_cols) << (2 - ss);
+            const int up0 = ds0 * sr->superres_denominator / 8;
+            const int up1 = j == sr->tile_cols - 1 ? up_w : ds1 * sr->superres_denominator / 8;
+            tab.up_x0[p][j] = up0, tab.ds_x0[p][j] = ds0, tab.x0_qn[p][j] = x0;
+            x0 += (up1 - up0) * a.step[p] - ((ds1 - ds0) << 14);
+            tab.up_x0[p][j + 1] = up1;
+        }
+        a.src_w[p] = (c->geom.mi_cols * 4) >> ss, a.dst_w[p] = up_w, a.dst_cw[p] = (ng.mi_cols * 4) >> ss, a.rows[p] = (c->geom.mi_rows * 4) >> ss;
+        a.base[p + 1] = a.base[p] + (long long)a.dst_cw[p] * a.rows[p];
+    }
+    a.tile_cols = sr->tile_cols, a.bd = c->geom.bit_depth;
+    a.tab       = reinterpret_cast<const SuperresTables *>(c->d_handoff);
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_handoff, &tab, sizeof(tab), cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream)); // `tab` is on the stack
+    const int blocks = (int)std::min<long long>((a.base[3] + 255) / 256, (long long)std::max(1, c->sm_count) * 16);
+    auto      launch = [&](int from, int to) -> int {
+        a.src = c->surf[from].planes(), a.dst = c->surf[to].planes();
+        if (c->geom.sample_bytes == 1)
+            superres_kernel<uint8_t><<<blocks, 256, 0, c->stream>>>(a);
+        else
+            superres_kernel<uint16_t><<<blocks, 256, 0, c->stream>>>(a);
+        CUDA_TRY(c, cudaGetLastError());
+        c->launches++;
+        return SVTF_OK;
+    };
+    // surfaces: the current picture goes to a free one; the picture before CDEF goes through surface 3 (the restoration
+    // output) back into its own surface, so that loop restoration still finds surface 3 free
+    int free_s = 0;
+    while (free_s == c->cur || free_s == c->pre_cdef) free_s++;
+    if (int r = launch(c->cur, free_s))
+        return r;
+    if (c->pre_cdef >= 0 && c->pre_cdef != c->cur) {
+        if (int r = launch(c->pre_cdef, 3))
+            return r;
+        for (int p = 0; p < 3; p++) {
+            const size_t bytes = (size_t)c->surf[3].pitch[p] * a.rows[p] * c->geom.sample_bytes;
+            CUDA_TRY(c, cudaMemcpyAsync(c->surf[c->pre_cdef].base[p], c->surf[3].base[p], bytes, cudaMemcpyDeviceToDevice, c->stream));
+        }
+    } else if (c->pre_cdef == c->cur)
+        c->pre_cdef = free_s;
+    c->cur     = free_s;
+    c->geom    = ng;
+    c->have_mi = c->have_search = c->have_source = false;
     return SVTF_OK;
 }
 

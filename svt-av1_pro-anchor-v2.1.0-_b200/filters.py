@@ -396,6 +396,22 @@ class FilterContext:
         up = (C.c_void_p * 3)(*[C.cast(u, C.c_void_p) if u is not None else None for u in units])
         self._chk(self._lib.svtf_lr_apply_frame(self._h, C.byref(lr), up))
 
+    def superres_upscale_frame(self, upscaled_width, denominator, filters, tile_col_start_mi=None):
+        """svt_av1_superres_upscale_frame (Encoder/Codec/EbRestProcess.c:405) on the current picture (and the picture before CDEF):
+        svtf_superres_upscale_frame.  filters: int16 [64][8] = av1_resize_filter_normative.  Afterwards self.geom is the
+        upscaled geometry."""
+        sr = L.SuperresParams()
+        starts = list(tile_col_start_mi) if tile_col_start_mi is not None else [0, self.geom.mi_cols]
+        sr.upscaled_width, sr.superres_denominator, sr.tile_cols = upscaled_width, denominator, len(starts) - 1
+        for j, v in enumerate(starts):
+            sr.tile_col_start_mi[j] = v
+        f = np.ascontiguousarray(filters, dtype=np.int16)
+        sr.filters = f.ctypes.data
+        self._chk(self._lib.svtf_superres_upscale_frame(self._h, C.byref(sr)))
+        if denominator != 8:
+            self.geom = make_geom_coded(upscaled_width, self.geom.height, 2 * ((upscaled_width + 7) >> 3), self.geom.mi_rows, self.geom.bit_depth,
+                                        self.geom.sample_bytes)
+
     def restoration_search(self, cfg):
         """restoration_seg_search + rest_finish_search (Encoder/Codec/EbRestorationPick.c:1471/1555, Wiener tools) on the
         current picture against the uploaded source (svtf_lr_search_frame).  cfg: LrSearchCfg.  Returns (frame types,
