@@ -357,6 +357,27 @@ API int adapt_lr_frame(const svtf_geom *g, void *y, int sy, void *cb, int scb, v
     return 0;
 }
 
+/* svt_av1_superres_upscale_frame on the reference's own structures: the planes (strides wide enough for the upscaled picture)
+ * are upscaled in place */
+void svt_av1_superres_upscale_frame(struct Av1Common *cm, PictureControlSet *pcs, SequenceControlSet *scs);
+API int adapt_superres(const svtf_geom *g, void *y, int sy, void *cb, int scb, void *cr, int scr, int up_w, int denom, int tile_cols,
+                       const int32_t *tile_col_start_mi) {
+    harness    h;
+    ref_mi_soa soa = {NULL, NULL, NULL, NULL, NULL, NULL, g->mi_cols};
+    if (harness_init(&h, g, &soa, y, sy, cb, scb, cr, scr))
+        return -1;
+    h.cm->frm_size.frame_width = (uint16_t)g->width, h.cm->frm_size.frame_height = (uint16_t)g->height;
+    h.cm->frm_size.superres_upscaled_width = (uint16_t)up_w, h.cm->frm_size.superres_upscaled_height = (uint16_t)g->height;
+    h.cm->frm_size.superres_denominator    = (uint8_t)denom;
+    h.cm->tiles_info.tile_cols             = (uint8_t)tile_cols;
+    for (int j = 0; j <= tile_cols; j++) h.cm->tiles_info.tile_col_start_mi[j] = (uint16_t)tile_col_start_mi[j];
+    svtf_adapter_set_resident(0);
+    svt_av1_superres_upscale_frame(h.cm, h.pcs, h.scs);
+    svtf_adapter_release(h.pcs);
+    harness_free(&h);
+    return 0;
+}
+
 /* restoration_seg_search (segment 0) + rest_finish_search on the reference's own structures */
 void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, const Yv12BufferConfig *src, Yv12BufferConfig *trial_frame_rst,
                             PictureControlSet *pcs, uint32_t segment_index);

@@ -34,6 +34,8 @@
 #include "EbCcso.h"
 #include "EbPickccso.h"
 #include "EbRestoration.h"
+#include "EbInterPrediction.h"
+#include "EbSuperRes.h"
 
 #include "../include/svtfilt_b200.h"
 #include "../include/svtfilt_b200_adapters.h"
@@ -72,6 +74,9 @@ static svtf_geom geom_of(const PictureControlSet *pcs) {
     svtf_geom                 g;
     /* unpadded size: the width/height svt_av1_setup_dst_planes gives the deblock (EbDeblockingFilter.c:99-101) */
     g.width        = scs->max_input_luma_width - scs->max_input_pad_right;
+    /* a frame coded with super-resolution is narrower than the input: cm->frm_size carries its width (and mi_cols matches) */
+    if (cm->frm_size.frame_width && cm->frm_size.superres_denominator > SCALE_NUMERATOR)
+        g.width = cm->frm_size.frame_width;
     g.height       = scs->max_input_luma_height - scs->max_input_pad_bottom;
     g.mi_cols      = cm->mi_cols;
     g.mi_rows      = cm->mi_rows;
@@ -100,7 +105,13 @@ static CtxSlot *slot_for(const PictureControlSet *pcs) {
         s->pcs      = pcs;
         s->geom     = geom_of(pcs);
         s->resident = 0;
-        if (svtf_ctx_create(g_device, &s->geom, &s->ctx) != SVTF_OK)
+        svtf_geom        mg = s->geom; /* room for the super-resolution upscale */
+        const Av1Common *cm = pcs->ppcs->av1_cm;
+        if (cm->frm_size.superres_denominator > SCALE_NUMERATOR && cm->frm_size.superres_upscaled_width > mg.width) {
+            mg.width   = cm->frm_size.superres_upscaled_width;
+            mg.mi_cols = 2 * ((mg.width + 7) >> 3);
+        }
+        if (svtf_ctx_create(g_device, &mg, &s->ctx) != SVTF_OK)
             die("svtf_ctx_create", NULL);
     }
     pthread_mutex_unlock(&g_lock);
@@ -606,6 +617,43 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
     CHECK(svtf_download_frame(s->ctx, fp[0], fst[0], fp[1], fst[1], fp[2], fst[2]), s->ctx);
     s->resident = 0;
     for (int p = 0; p < 3; p++) free(units[p]);
+}
+
+/* ----------------------------------------------------------------------------------------------------
+ * svt_av1_superres_upscale_frame (Encoder/Codec/EbRestProcess.c:405), called by the CDEF kernel after CDEF / CCSO when the
+ * frame was coded with super-resolution (Encoder/Codec/EbCdefProcess.c:675-677): the recon picture is upscaled in place
+ * (the reference copies it aside and runs svt_av1_upscale_normative_rows per plane).  Resident chain: the picture on the
+ * device is upscaled (with the deblocked picture loop restoration takes its stripe borders from) and stays there;
+ * stand-alone: recon is uploaded, upscaled and written back into the same buffers.
+ * ---------------------------------------------------------------------------------------------------- */
+void svt_av1_superres_upscale_frame(struct Av1Common *cm, PictureControlSet *pcs, SequenceControlSet *scs) {
+    EbPictureBufferDesc *recon;
+    svt_aom_get_recon_pic(pcs, &recon, scs->is_16bit_pipeline);
+    CtxSlot *s = slot_for(pcs);
+    void    *p[3];
+    int32_t  st[3];
+    plane_ptrs(recon, s->geom.sample_bytes, p, st);
+    const int resident = g_resident && s->resident;
+    if (!resident) {
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    }
+    svtf_superres_params sr;
+    memset(&sr, 0, sizeof(sr));
+    sr.upscaled_width       = cm->frm_size.superres_upscaled_width;
+    sr.superres_denominator = cm->frm_size.superres_denominator;
+    sr.tile_cols            = cm->tiles_info.tile_cols;
+    for (int j = 0; j <= sr.tile_cols && j < 65; j++) sr.tile_col_start_mi[j] = cm->tiles_info.tile_col_start_mi[j];
+    sr.filters = &av1_resize_filter_normative[0][0];
+    CHECK(svtf_superres_upscale_frame(s->ctx, &sr), s->ctx);
+    if (sr.superres_denominator > SCALE_NUMERATOR) { /* the picture of this pcs is the upscaled one from here on */
+        s->geom.width   = sr.upscaled_width;
+        s->geom.mi_cols = 2 * ((sr.upscaled_width + 7) >> 3);
+    }
+    if (!resident) {
+        CHECK(svtf_download_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+        s->resident = 0;
+    }
 }
 
 /* ----------------------------------------------------------------------------------------------------

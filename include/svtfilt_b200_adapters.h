@@ -33,7 +33,9 @@ void svtf_cdef_search_picture(struct PictureControlSet *pcs, struct SequenceCont
  * recon buffer uploaded first).  pad_ref_and_set_flags calls it in place of its lines 1604-1744 and keeps its bookkeeping. */
 void svtf_pad_ref_pictures(struct PictureControlSet *pcs, struct SequenceControlSet *scs);
 
-/* Also provided with the reference's own names and signatures (Encoder/Codec/EbRestorationPick.c:1471 / :1555):
+/* Also provided with the reference's own name and signature (Encoder/Codec/EbRestProcess.c:405):
+ *   void svt_av1_superres_upscale_frame(struct Av1Common *cm, PictureControlSet *pcs, SequenceControlSet *scs);
+ * and (Encoder/Codec/EbRestorationPick.c:1471 / :1555):
  *   void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, const Yv12BufferConfig *src,
  *                               Yv12BufferConfig *trial_frame_rst, PictureControlSet *pcs, uint32_t segment_index);
  *   void rest_finish_search(PictureControlSet *pcs);

@@ -242,3 +242,29 @@ def test_restoration_search_adapter(H, orc, adapt, w, h, bd, sb, kw):
         assert got[p][2] == exp[p][2], ("unit search", p)
         assert got[p][1] == exp[p][1], ("unit info", p)
     assert got[3] == exp[3], "sg_frame_ep_cnt"
+
+
+def test_superres_adapter(H, orc, adapt):
+    """svt_av1_superres_upscale_frame(cm, pcs, scs) on the reference's own structures: the recon planes are upscaled in place."""
+    from test_superres_oracle import ref_filters, upscale_cpu
+
+    if not H.ref_available():
+        pytest.skip("the filter table comes from the reference")
+    S = H.S
+    f = ref_filters(H.Ref())
+    for (w, h, bd, sb, denom, starts) in [(200, 72, 10, 2, 11, None), (328, 40, 8, 1, 16, (0, 32, 64, 82))]:
+        g = S.make_geom(w, h, bd, sb)
+        pic = H.synth_picture(g, 15200 + w, noise=12)
+        up_w = (w * denom + 4) // 8
+        st = list(starts) if starts else [0, g.mi_cols]
+        cw = 2 * ((up_w + 7) >> 3) * 4
+        bufs = []
+        for p in range(3):
+            b = np.zeros((pic[p].shape[0], cw >> (1 if p else 0)), pic[p].dtype)
+            b[:, : pic[p].shape[1]] = pic[p]
+            bufs.append(b)
+        arr = (C.c_int32 * len(st))(*st)
+        assert adapt.adapt_superres(C.byref(g), *H._planes(bufs), up_w, denom, len(st) - 1, arr) == 0
+        for p in range(3):
+            exp = upscale_cpu(H, orc.lib.svtf_orc_superres_plane, g, pic[p], p, up_w, denom, st, f)
+            assert np.array_equal(bufs[p][:, : exp.shape[1]], exp), p
