@@ -223,6 +223,37 @@ def lf_search_leg(H, S, geom, wl, ctx, np, with_cpu):
     return res
 
 
+def superres_leg(H, S, np):
+    """Normative super-resolution upscale (svt_av1_superres_upscale_frame) of a picture coded at half width: 1920x2160 -> 3840x2160,
+    10-bit, picture resident.  Bandwidth-bound stage: reads b, writes 2b bytes per coded sample (denominator 16)."""
+    if not H.ref_available():
+        return None  # the 64 x 8 filter table is the caller's (av1_resize_filter_normative); the harness takes it from oracle/_ref
+    import ctypes as C
+
+    ref = H.Ref()
+    ref.lib.ref_superres_filters.restype = C.POINTER(C.c_int16)
+    filt = np.ctypeslib.as_array(ref.lib.ref_superres_filters(), shape=(64, 8)).copy()
+    g = S.make_geom(1920, 2160, BD)
+    gu = S.make_geom(3840, 2160, BD)
+    pic = H.synth_picture(g, 0xB20051)
+    with S.FilterContext(gu) as ctx:
+        stream = None
+        n, ts = 10, []
+        for i in range(n + 2):
+            ctx.begin(g)
+            ctx.upload(pic)
+            ctx.sync()
+            t0 = time.perf_counter()
+            ctx.superres_upscale_frame(3840, 16, filt)
+            ctx.sync()
+            ts.append(time.perf_counter() - t0)
+        dt = sorted(ts[2:])[len(ts[2:]) // 2]
+    alg = 1.5 * 1920 * 2160 * 2 * 3  # read b + write 2b per coded sample, b = 2
+    return {"metric": "super-resolution upscale 1920x2160 -> 3840x2160 10-bit, ms per picture (call + sync, picture resident)",
+            "ms": round(dt * 1e3, 4), "alg_bytes": int(alg), "alg_GBps": round(alg / dt / 1e9, 1),
+            "note": "includes the 6 KB table upload and a stream synchronisation per call"}
+
+
 def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu, more_ctxs=()):
     """Loop-restoration filter search, Wiener tools (restoration_seg_search + rest_finish_search): statistics of every unit,
     host solve, refinement trials of all units in lock-step; the reference's C on a smaller picture."""
@@ -861,6 +892,7 @@ def main():
     side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
     hand = handoff_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lfs = lf_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
+    sres = superres_leg(H, S, np) if rank == 0 else None
     lrs = lr_search_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu, ctxs[1:4]) if rank == 0 else None
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -881,7 +913,7 @@ def main():
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + mi_bytes) * B, "d2h_bytes_per_step": frame_bytes * B,
                     "inflight": nin, "matches_device_path": bool(e2e_ok)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "lr_search": lrs, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "lr_search": lrs, "superres": sres, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5,
         }
         print(json.dumps(line))
     for p in pins_in + pins_out + pins_mi:
