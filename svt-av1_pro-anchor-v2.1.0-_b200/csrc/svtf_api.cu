@@ -1734,7 +1734,7 @@ extern "C" int svtf_superres_upscale_frame(svtf_ctx *c, const svtf_superres_para
     SuperresTables tab;
     SuperresArgs   a;
     std::memcpy(tab.filt, sr->filters, sizeof(tab.filt));
-    a.base[0] = 0;
+    a.row_base[0] = 0;
     for (int p = 0; p < 3; p++) {
         const int ss = p ? 1 : 0;
         const int ds_w = (c->geom.width + ss) >> ss, up_w = (sr->upscaled_width + ss) >> ss; // ROUND_POWER_OF_TWO(width, sub_x)
@@ -1751,13 +1751,14 @@ extern "C" int svtf_superres_upscale_frame(svtf_ctx *c, const svtf_superres_para
             tab.up_x0[p][j + 1] = up1;
         }
         a.src_w[p] = (c->geom.mi_cols * 4) >> ss, a.dst_w[p] = up_w, a.dst_cw[p] = (ng.mi_cols * 4) >> ss, a.rows[p] = (c->geom.mi_rows * 4) >> ss;
-        a.base[p + 1] = a.base[p] + (long long)a.dst_cw[p] * a.rows[p];
+        a.row_base[p + 1] = a.row_base[p] + a.rows[p];
+        a.x0_qn_first[p] = tab.x0_qn[p][0], a.up_x1_first[p] = tab.up_x0[p][1];
     }
     a.tile_cols = sr->tile_cols, a.bd = c->geom.bit_depth;
     a.tab       = reinterpret_cast<const SuperresTables *>(c->d_handoff);
+    // pageable source: the runtime stages the 6 KB before the call returns, so `tab` may leave scope
     CUDA_TRY(c, cudaMemcpyAsync(c->d_handoff, &tab, sizeof(tab), cudaMemcpyHostToDevice, c->stream));
-    CUDA_TRY(c, cudaStreamSynchronize(c->stream)); // `tab` is on the stack
-    const int blocks = (int)std::min<long long>((a.base[3] + 255) / 256, (long long)std::max(1, c->sm_count) * 16);
+    const dim3 blocks((a.dst_cw[0] + 256 * SR_PER - 1) / (256 * SR_PER), a.row_base[3]);
     auto      launch = [&](int from, int to) -> int {
         a.src = c->surf[from].planes(), a.dst = c->surf[to].planes();
         if (c->geom.sample_bytes == 1)
