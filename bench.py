@@ -226,13 +226,8 @@ def lf_search_leg(H, S, geom, wl, ctx, np, with_cpu):
 def superres_leg(H, S, np):
     """Normative super-resolution upscale (svt_av1_superres_upscale_frame) of a picture coded at half width: 1920x2160 -> 3840x2160,
     10-bit, picture resident.  Bandwidth-bound stage: reads b, writes 2b bytes per coded sample (denominator 16)."""
-    if not H.ref_available():
-        return None  # the 64 x 8 filter table is the caller's (av1_resize_filter_normative); the harness takes it from oracle/_ref
-    import ctypes as C
-
-    ref = H.Ref()
-    ref.lib.ref_superres_filters.restype = C.POINTER(C.c_int16)
-    filt = np.ctypeslib.as_array(ref.lib.ref_superres_filters(), shape=(64, 8)).copy()
+    # the 64 x 8 filter table is the caller's (av1_resize_filter_normative); here the committed fixture (oracle/make_superres_table.py)
+    filt = np.load(os.path.join(ROOT, "tests", "golden", "superres_filters.npy"))
     g = S.make_geom(1920, 2160, BD)
     gu = S.make_geom(3840, 2160, BD)
     pic = H.synth_picture(g, 0xB20051)

@@ -3,16 +3,16 @@ tests/test_superres_oracle.py), alone and between CDEF and loop restoration."""
 import numpy as np
 import pytest
 
-from test_superres_oracle import CASES, ref_filters, upscale_cpu
+from test_superres_oracle import CASES, upscale_cpu
 
 pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(scope="module")
 def filters(H):
-    if not H.ref_available():
-        pytest.skip("oracle/_ref not built: the filter table comes from the reference")
-    return ref_filters(H.Ref())
+    import os
+
+    return np.load(os.path.join(H.ROOT, "tests", "golden", "superres_filters.npy"))
 
 
 def up_geom(S, g, up_w):

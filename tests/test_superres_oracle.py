@@ -45,3 +45,10 @@ def test_oracle_superres_matches_reference(H, orc, ref, w, h, bd, sb, denom, sta
         b = upscale_cpu(H, ref.lib.ref_superres_plane, g, pic[p], p, up_w, denom, starts)
         assert np.array_equal(a, b), (p, np.argwhere(a != b)[:4])
         assert a.max() > 0
+
+
+def test_filter_fixture_is_the_reference_table(H, ref):
+    """tests/golden/superres_filters.npy (oracle/make_superres_table.py) = av1_resize_filter_normative of the reference."""
+    import os
+
+    assert np.array_equal(np.load(os.path.join(H.ROOT, "tests", "golden", "superres_filters.npy")), ref_filters(ref))

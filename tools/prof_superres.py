@@ -11,9 +11,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import harness as H  # noqa: E402
 
 S = H.S
-ref = H.Ref()
-ref.lib.ref_superres_filters.restype = C.POINTER(C.c_int16)
-filt = np.ctypeslib.as_array(ref.lib.ref_superres_filters(), shape=(64, 8)).copy()
+filt = np.load(os.path.join(ROOT, "tests", "golden", "superres_filters.npy"))
 g, gu = S.make_geom(1920, 2160, 10), S.make_geom(3840, 2160, 10)
 pic = H.synth_picture(g, 0xB20051)
 with S.FilterContext(gu) as ctx:
