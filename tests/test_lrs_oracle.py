@@ -60,6 +60,10 @@ def test_oracle_wiener_solve_on_degenerate_stats(H, orc, ref):
     (200, 72, 8, 2, 11, {"sg": 1, "chroma": 0, "sg_ep": ((2, 12, 3, 1), (8, 16, 2, 1))}),
     (134, 70, 10, 2, 12, {"sg": 1, "sg_chroma": 0, "rdmult": 60000}),
     (136, 72, 10, 2, 13, {"sg": 1, "rdmult": 300, "sw_cost": (20, 40, 30), "sg_cost": (15, 50)}),
+    # one restoration unit per plane (RESTORE_SWITCHABLE is not a frame type then, :1590), tiny pictures
+    (64, 64, 8, 1, 14, {"sg": 1}),
+    (40, 24, 10, 2, 15, {"sg": 1, "sg_ep": ((0, 16, 2, 1), (0, 16, 2, 1))}),
+    (16, 16, 8, 1, 16, {"sg": 1, "unit_size": (256, 128, 128)}),
 ])
 def test_oracle_lr_search_matches_reference(H, orc, ref, w, h, bd, sb, seed, kw):
     g, cur, src = search_case(H, w, h, bd, sb, seed)
