@@ -125,3 +125,38 @@ def test_lr_search_then_apply_lowers_error(H):
         before = int(((c[p].astype(np.int64) - s[p]) ** 2).sum())
         after = int(((o[p].astype(np.int64) - s[p]) ** 2).sum())
         assert after < before, (p, before, after)
+
+
+def test_lr_search_8k_properties(H):
+    """BASELINE's largest size (8K 10-bit): the search runs with both tool sets, the per-unit SSEs it reports for RESTORE_NONE sum
+    to the picture's squared error, every unit gets a self-guided candidate, and applying the result lowers the error of every
+    plane (size-independent properties; the oracle is too slow here)."""
+    S = H.S
+    g = S.make_geom(7680, 4320, 10, 2)
+    rng = np.random.default_rng(8)
+    base = H.synth_picture(S.make_geom(960, 544, 10, 2), 13900, noise=10)
+    src = [np.ascontiguousarray(np.tile(p, (8, 8))[: (g.mi_rows * 4) >> s, : (g.mi_cols * 4) >> s]) for p, s in zip(base, (0, 1, 1))]
+    cur = [np.clip(p.astype(np.int32) + rng.integers(-6, 7, p.shape), 0, 1023).astype(np.uint16) for p in src]
+    cfg = H.lr_search_cfg(unit_size=(256, 128, 128), sg=1, sg_ep=((0, 16, 5, 1), (10, 16, 3, 1)))
+    with S.FilterContext(g) as ctx:
+        ctx.begin(g)
+        ctx.upload(cur)
+        ctx.upload_source(src)
+        ftype, units, search = ctx.restoration_search(cfg)
+        assert sum(ctx.sg_frame_ep_cnt) == sum(len(u) for u in units)
+        for p in range(3):
+            ss = 1 if p else 0
+            c, s_ = cur[p][: (g.height + ss) >> ss, : (g.width + ss) >> ss].astype(np.int64), src[p][: (g.height + ss) >> ss, : (g.width + ss) >> ss]
+            assert sum(u.sse[0] for u in search[p]) == int(((c - s_) ** 2).sum())
+            assert all(u.sse[2] > 0 for u in search[p])
+        assert all(t != 0 for t in ftype)
+        lr = S._lib.LrParams()
+        for p in range(3):
+            lr.frame_restoration_type[p], lr.restoration_unit_size[p] = ftype[p], cfg.restoration_unit_size[p]
+        lr.optimized_lr = 1  # no deblocked picture on this context: borders from the picture itself
+        ctx.loop_restoration_filter_frame(lr, units)
+        out = ctx.download()
+    for p in range(3):
+        ss = 1 if p else 0
+        v = lambda a: a[: (g.height + ss) >> ss, : (g.width + ss) >> ss].astype(np.int64)
+        assert ((v(out[p]) - v(src[p])) ** 2).sum() < ((v(cur[p]) - v(src[p])) ** 2).sum(), p
