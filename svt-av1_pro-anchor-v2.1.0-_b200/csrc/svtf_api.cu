@@ -1949,7 +1949,7 @@ int lrs_check(svtf_ctx *c, const char *fn) {
 }
 template <class F>
 void host_parallel_for(int n, F fn) {
-    const int nt = std::max(1, std::min({(int)std::thread::hardware_concurrency(), 8, n / 8}));
+    const int nt = std::max(1, std::min({(int)std::thread::hardware_concurrency(), 16, n / 8}));
     std::atomic<int> next{0};
     auto             worker = [&] {
         for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) fn(i);
