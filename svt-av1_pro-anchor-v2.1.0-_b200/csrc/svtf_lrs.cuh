@@ -302,8 +302,10 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_proj_err_kernel(const __grid_
     unsigned err32[LRS_CAND];
 #pragma unroll
     for (int j = 0; j < LRS_CAND; j++) err32[j] = 0;
-    for (int i = threadIdx.x; i < t.w * t.h; i += LRS_THREADS) {
-        const int    r = i / t.w, c = i - r * t.w;
+    // tiles are at most 64 wide: a thread keeps its column and walks every fourth row (no division per sample).  Issuing the
+    // loads of four rows together was measured slower (12.5 against 11.4 ms for the whole self-guided search).
+    const int c = threadIdx.x & (LRS_T - 1);
+    for (int r = threadIdx.x / LRS_T; r < t.h && c < t.w; r += LRS_THREADS / LRS_T) {
         const size_t o = (size_t)(t.y0 + r) * cp + t.x0 + c;
         const int    uu = (int)cur[o] << 4, d0 = f0[o], d1 = f1[o], sv = (int)src[(size_t)(t.y0 + r) * sp + t.x0 + c];
 #pragma unroll
