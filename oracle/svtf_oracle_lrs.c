@@ -421,8 +421,11 @@ ORC_API int orc_lr_search_frame(const svtf_geom *g, const void *y, int sy, const
     int       n0;
     {
         int hu, vu;
-        orc_lr_units(g, 0, cfg->restoration_unit_size[0], &hu, &vu);
-        n0 = hu * vu;
+        n0 = 0; /* the reference sizes the array for luma and asserts ntiles[1] <= ntiles[0] (:1567) */
+        for (int p = 0; p < 3; p++) {
+            orc_lr_units(g, p, cfg->restoration_unit_size[p], &hu, &vu);
+            n0 = IMAX(n0, hu * vu);
+        }
     }
     finish_unit *fu = calloc(n0, sizeof(*fu));
     if (sg_frame_ep_cnt)

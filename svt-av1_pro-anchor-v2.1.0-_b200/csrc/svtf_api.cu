@@ -2290,7 +2290,9 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
         int     sgr_ep, sgr_xqd[2];
         int     best[3]; // best_rtype[WIENER - 1], [SGRPROJ - 1], [SWITCHABLE - 1]
     };
-    std::vector<FinishUnit> fu(plan.planes[0].hu * plan.planes[0].vu);
+    size_t most = 0; // the reference sizes the array for luma and asserts that chroma has no more units (:1567); be safe anyway
+    for (const LrsPlane &pl : plan.planes) most = std::max(most, (size_t)pl.hu * pl.vu);
+    std::vector<FinishUnit> fu(most);
     std::memset(fu.data(), 0, sizeof(FinishUnit) * fu.size());
     const int force = wn ? (sg ? 4 : 1) : (sg ? 2 : 0); // force_restore_type_d; 4 = RESTORE_TYPES: all
     for (const LrsPlane &pl : plan.planes) {
