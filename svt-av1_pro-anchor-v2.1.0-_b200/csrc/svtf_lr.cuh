@@ -239,8 +239,9 @@ __global__ void __launch_bounds__(LR_THREADS) lr_kernel(const __grid_constant__ 
             if (c < wv) {
                 int x[14], sv[8];
                 if (SSE) { // the source samples first: their latency hides behind the filter arithmetic
+                    const T *sq = srcp + (size_t)(y0 + rb) * sp + x0 + c;
 #pragma unroll
-                    for (int j = 0; j < 8; j++) sv[j] = rb + j < h ? (int)srcp[(size_t)(y0 + rb + j) * sp + x0 + c] : 0;
+                    for (int j = 0; j < 8; j++) sv[j] = rb + j < h ? (int)sq[j * sp] : 0;
                 }
                 // rows beyond h + 6 of the last segment are never-written shared memory inside s_buf: they only feed outputs
                 // rb + j >= h, which are dropped
