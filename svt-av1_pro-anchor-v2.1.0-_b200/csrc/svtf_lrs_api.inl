@@ -405,6 +405,7 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
     });
     const auto t_solved = now();
     int        rounds = 0, sg_rounds = 0;
+    long long  pending_total = 0; // unit trials over all Wiener rounds (timing output)
     uint8_t   *d = c->d_lrs;
     LrUnitDev *host = reinterpret_cast<LrUnitDev *>(c->h_lrs + plan.o_units);
     const unsigned long long *trial = reinterpret_cast<const unsigned long long *>(c->h_lrs + plan.o_trial);
@@ -435,7 +436,7 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
             }
             if (!pending)
                 break;
-            rounds++;
+            rounds++, pending_total += pending;
             if (int r = round_trip([&] { return lrs_launch_lr<LR_SSE>(c, a, grid); }))
                 return r;
             for (int u = 0; u < plan.units; u++)
@@ -581,8 +582,10 @@ extern "C" int svtf_lr_search_frame(svtf_ctx *c, const svtf_lr_search_cfg *cfg, 
                 us[u].sse[2] = (int64_t)trial[u];
     }
     if (timing)
-        std::fprintf(stderr, "svtf_lr_search_frame: plan+stats %.3f ms, host solve %.3f ms, %d Wiener rounds %.3f ms, self-guided (%d rounds) %.3f ms\n",
-                     ms(t_start, t_measured), ms(t_measured, t_solved), rounds, ms(t_solved, t_wiener), sg_rounds, ms(t_wiener, now()));
+        std::fprintf(stderr, "svtf_lr_search_frame: plan+stats %.3f ms, host solve %.3f ms, %d Wiener rounds (%lld unit trials of %d units) %.3f ms, "
+                     "self-guided (%d rounds) %.3f ms\n",
+                     ms(t_start, t_measured), ms(t_measured, t_solved), rounds, pending_total, plan.units, ms(t_solved, t_wiener), sg_rounds,
+                     ms(t_wiener, now()));
     // ---- rest_finish_search :1555: the cost of every frame type that applies; per-unit decisions in raster order.  The
     //      reference's per-unit array is allocated and zeroed once BEFORE the plane loop (:1570-1577), so what a plane does not
     //      refresh (e.g. the Wiener entries of a chroma plane searched with the self-guided tools only) still holds the previous
