@@ -250,7 +250,7 @@ def superres_leg(H, S, np):
 
 
 def lr_search_leg(H, S, geom, wl, ctx, np, with_cpu, more_ctxs=()):
-    """Loop-restoration filter search, Wiener tools (restoration_seg_search + rest_finish_search): statistics of every unit,
+    """Loop-restoration filter search (restoration_seg_search + rest_finish_search), Wiener tools first, then with the self-guided tools: statistics of every unit,
     host solve, refinement trials of all units in lock-step; the reference's C on a smaller picture."""
     src = H.synth_source(geom, wl["rec"], 0xB200F1, amp=6)
     cfg = H.lr_search_cfg(unit_size=(256, 128, 128))

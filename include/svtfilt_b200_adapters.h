@@ -39,7 +39,7 @@ void svtf_pad_ref_pictures(struct PictureControlSet *pcs, struct SequenceControl
  *   void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, const Yv12BufferConfig *src,
  *                               Yv12BufferConfig *trial_frame_rst, PictureControlSet *pcs, uint32_t segment_index);
  *   void rest_finish_search(PictureControlSet *pcs);
- * (Wiener tools; segment 0 searches the whole picture on the GPU, the other segments return.) */
+ * (Wiener and self-guided tools; segment 0 searches the whole picture on the GPU, the other segments return.) */
 
 /* CUDA device used by contexts the adapters create (default 0). */
 void svtf_adapter_set_device(int device);

@@ -1,5 +1,5 @@
 /*
- * svtf_oracle_lrs.c — CPU restatement of the reference's loop-restoration filter SEARCH with the Wiener tools.
+ * svtf_oracle_lrs.c — CPU restatement of the reference's loop-restoration filter SEARCH (Wiener and self-guided tools, switchable).
  * TEST INFRASTRUCTURE ONLY: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may use it.
  *
  * Follows Encoder/Codec/EbRestorationPick.c:
@@ -10,6 +10,9 @@
  *   finalize_sym_filter :977, compute_score :937, finer_tile_search_wiener_seg :1042, count_wiener_bits :1008 with
  *   svt_aom_count_primitive_refsubexpfin (Encoder/Codec/EbEntropyCoding.c:2876-3022);
  *   try_restoration_unit_seg :129 = svtf_oracle_lr.c's orc_lr_try_unit (filter without stripe boundaries + SSE).
+ *   search_sgrproj_seg :1220 / search_selfguided_restoration :550 (apply_sgr :522 = svtf_oracle_lr.c's orc_lr_sgr_unit_flt,
+ *   svt_get_proj_subspace_c :417, encode_xq :508, finer_search_pixel_proj_error :320, get_pixel_proj_error :305),
+ *   search_sgrproj_finish :1267, count_sgrproj_bits :655, search_switchable :1148, use_prev_frame_coeffs :1313-1319.
  * Units: foreach_rest_unit_in_tile (Common/Codec/EbRestoration.c:1250) — raster order, the last unit of a row / column
  * takes the remainder (up to 1.5 units), rows shifted up by 8 luma samples.
  * Pinned against the reference's own code through oracle/ref_shim_lrs.c (tests/test_lrs_oracle.py).

@@ -1,4 +1,5 @@
-// svtf_lrs.cuh — device half of the loop-restoration filter search (Wiener tools): per-unit sums and the Wiener statistics.
+// svtf_lrs.cuh — device half of the loop-restoration filter search: per-unit sums, the Wiener statistics, and the projection
+// error of the self-guided coefficient search (the guided-filter outputs themselves: lr_kernel<T, LR_FLT>, svtf_lr.cuh).
 //
 // Reference: svt_av1_compute_stats_c / _highbd_c (Encoder/Codec/EbRestorationPick.c:671 / :708), find_average[_highbd]
 // (EbRestorationPick.h:24-43), search_norestore_seg :1432 (sse_restoration_unit :56).  The trial filtering + SSE of

@@ -93,7 +93,7 @@ extern "C" int svtf_superres_upscale_frame(svtf_ctx *c, const svtf_superres_para
     return SVTF_OK;
 }
 
-// ---- loop-restoration filter search, Wiener tools (svtf_lrs.cuh, svtf_lrs_host.cpp) -----------------------------------
+// ---- loop-restoration filter search, Wiener + self-guided tools (svtf_lrs.cuh, svtf_lrs_host.cpp) -----------------------------------
 namespace {
 struct LrsPlane { // one searched plane
     int plane, win, unit, hu, vu, first; // first: index of its unit 0 in the per-call unit arrays

@@ -1,4 +1,4 @@
-// svtf_lrs_host.cpp — host half of the loop-restoration filter search (Wiener tools).  Pure C++ (no CUDA), part of
+// svtf_lrs_host.cpp — host half of the loop-restoration filter search (Wiener and self-guided tools).  Pure C++ (no CUDA), part of
 // libsvtfilt_b200.so; the per-sample work (statistics, trial filtering + SSE) is in svtf_lrs.cuh / svtf_lr.cuh.
 //
 // Reference (relative to Source/Lib/): Encoder/Codec/EbRestorationPick.c — wiener_decompose_sep_sym :906 with

@@ -1,4 +1,4 @@
-"""Loop-restoration filter search (Wiener tools): the oracle's restatement (oracle/svtf_oracle_lrs.c) against the reference's
+"""Loop-restoration filter search (Wiener and self-guided tools): the oracle's restatement (oracle/svtf_oracle_lrs.c) against the reference's
 own Encoder/Codec/EbRestorationPick.c (restoration_seg_search + rest_finish_search, svt_av1_compute_stats[_highbd]_c,
 wiener_decompose_sep_sym / finalize_sym_filter / compute_score) compiled into oracle/_ref (oracle/ref_shim_lrs.c)."""
 import numpy as np
