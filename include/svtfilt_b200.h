@@ -400,6 +400,18 @@ int svtf_cdef_pick(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, svtf_cdef_par
  * filter block, then runs as svtf_cdef_pick. */
 int svtf_cdef_pick_table(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
                          svtf_cdef_params *out_params, int8_t *fb_strength_idx);
+/* svtf_cdef_pick_table WITHOUT any allocation, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * Same arguments, same results as svtf_cdef_pick_table; every device buffer the pick needs (table copy, skip
+ * flags, search state, totals, per-block result) lives in one file-scope `static __device__` array of
+ * SVTF_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until the process exits.  nfb above
+ * SVTF_NOALLOC_MAX_FB is rejected with SVTF_E_ARG.  The array is shared by all calls on a GPU and keeps the previous
+ * call's contents (the call clears what must start at zero); calls that overlap on one GPU would race on it, so the
+ * library serialises them per device inside the process (the call returns only after its stream has drained). */
+#define SVTF_NOALLOC_MAX_FB 8192                       /* filter blocks; an 8K picture has 120 x 68 = 8160 */
+#define SVTF_NOALLOC_SCRATCH_BYTES (8u * 1024u * 1024u + 64u * 1024u)
+int svtf_cdef_pick_table_noalloc(svtf_ctx *ctx, const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
+                                 svtf_cdef_params *out_params, int8_t *fb_strength_idx);
 /* Pure host implementation of the same pick (single thread, as the reference runs it); no context needed. */
 int svtf_cdef_pick_host(const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
                         svtf_cdef_params *out_params, int8_t *fb_strength_idx);

@@ -106,7 +106,7 @@ EXPORTS = [
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
     "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
-    "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
+    "svtf_cdef_pick_table_noalloc", "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
 ]
 
 _lib = None
@@ -162,6 +162,7 @@ def load():
     lib.svtf_ccso_derive_frame.argtypes = [vp, i32, i32, i32, C.POINTER(CcsoParams), vp]
     lib.svtf_cdef_pick.argtypes = [vp, C.POINTER(CdefSearchCfg), C.POINTER(CdefParams), vp]
     lib.svtf_cdef_pick_table.argtypes = [vp, C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]
+    lib.svtf_cdef_pick_table_noalloc.argtypes = [vp, C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]
     lib.svtf_cdef_pick_host.argtypes = [C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]
     lib.svtf_dev_planes.argtypes = [vp, C.c_int, C.POINTER(DevPlane)]
     lib.svtf_cuda_stream.argtypes = [vp]

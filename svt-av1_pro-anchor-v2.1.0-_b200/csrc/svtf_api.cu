@@ -1841,3 +1841,5 @@ extern "C" int svtf_lf_search_frame(svtf_ctx *c, const svtf_lf_params *start, co
     out_levels[0] = out_levels[1] = y, out_levels[2] = u, out_levels[3] = v;
     return SVTF_OK;
 }
+
+#include "svtf_noalloc_api.inl" // svtf_cdef_pick_table_noalloc: the pick on a static device scratch array (no allocation)

@@ -470,6 +470,15 @@ class FilterContext:
         self._chk(self._lib.svtf_cdef_pick_table(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), skip.size, C.byref(out), _ptr(idx)))
         return out, idx
 
+    def pick_table_noalloc(self, cfg, mse, skip):
+        """svtf_cdef_pick_table_noalloc: the same pick on the library's static device scratch array (no allocation)."""
+        mse = np.ascontiguousarray(mse, dtype=np.uint64)
+        skip = np.ascontiguousarray(skip, dtype=np.uint8)
+        out = L.CdefParams()
+        idx = np.empty(skip.size, dtype=np.int8)
+        self._chk(self._lib.svtf_cdef_pick_table_noalloc(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), skip.size, C.byref(out), _ptr(idx)))
+        return out, idx
+
     def finish_cdef_search(self, cfg):
         g = self.geom
         nfb = ((g.mi_rows + 15) // 16) * ((g.mi_cols + 15) // 16)
