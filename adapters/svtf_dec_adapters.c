@@ -69,6 +69,28 @@ static void die(const char *where, svtf_ctx *ctx) {
             die(#call, ctx);   \
     } while (0)
 
+/* Call counters, printed at exit when SVTF_ADAPTER_STATS is set (see svtf_enc_adapters.c). */
+enum { DS_LF, DS_CDEF, DS_CCSO, DS_LR, DS_N };
+static const char *const g_stat_name[DS_N] = {"dec_loop_filter_frame", "dec_cdef_frame", "dec_ccso_frame", "dec_loop_restoration_filter_frame"};
+static unsigned long     g_stat[DS_N];
+static pthread_once_t    g_stat_once = PTHREAD_ONCE_INIT;
+static void              stat_print(void) {
+    if (!getenv("SVTF_ADAPTER_STATS"))
+        return;
+    unsigned long launches = 0;
+    for (int i = 0; i < SVTF_DEC_MAX_CACHED; i++)
+        if (g_slots[i].ctx)
+            launches += (unsigned long)svtf_launch_count(g_slots[i].ctx);
+    fprintf(stderr, "svtfilt_b200 adapter stats:");
+    for (int i = 0; i < DS_N; i++) fprintf(stderr, " %s=%lu", g_stat_name[i], g_stat[i]);
+    fprintf(stderr, " gpu_launches=%lu\n", launches);
+}
+static void stat_init(void) { atexit(stat_print); }
+static void stat_hit(int which) {
+    pthread_once(&g_stat_once, stat_init);
+    __sync_fetch_and_add(&g_stat[which], 1);
+}
+
 static svtf_geom geom_of(const EbDecHandle *dec, const EbPictureBufferDesc *pic) {
     const FrameHeader *fh = &dec->frame_header;
     svtf_geom          g;
@@ -225,6 +247,7 @@ void svt_aom_dec_av1_loop_filter_frame(EbDecHandle *dec_handle_ptr, EbPictureBuf
     (void)is_mt;
     if (!enable_flag)
         return;
+    stat_hit(DS_LF);
     DecSlot       *s = slot_for(dec_handle_ptr, recon_picture_buf);
     svtf_lf_params lf;
     lf_of(dec_handle_ptr, &lf);
@@ -252,6 +275,7 @@ void svt_aom_dec_av1_loop_filter_frame(EbDecHandle *dec_handle_ptr, EbPictureBuf
 void svt_cdef_frame(EbDecHandle *dec_handle, int enable_flag) {
     if (!enable_flag)
         return;
+    stat_hit(DS_CDEF);
     EbPictureBufferDesc *recon = dec_handle->cur_pic_buf[0]->ps_pic_buf;
     DecSlot             *s     = slot_for(dec_handle, recon);
     const FrameHeader   *fh    = &dec_handle->frame_header;
@@ -301,6 +325,7 @@ void svt_cdef_frame(EbDecHandle *dec_handle, int enable_flag) {
  * applies the common definition.
  */
 void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle *dec_handle, uint16_t *ext_rec_y) {
+    stat_hit(DS_CCSO);
     DecSlot           *s  = slot_for(dec_handle, frame);
     const FrameHeader *fh = &dec_handle->frame_header;
     const CcsoInfo    *ci = &fh->ccso_info;
@@ -415,6 +440,7 @@ void svt_aom_dec_av1_loop_restoration_save_boundary_lines(EbDecHandle *dec_handl
 void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int optimized_lr, int enable_flag) {
     if (!enable_flag)
         return;
+    stat_hit(DS_LR);
     EbPictureBufferDesc *pic = dec_handle->cur_pic_buf[0]->ps_pic_buf;
     DecSlot             *s   = slot_for(dec_handle, pic);
     const LrCtxt        *lc  = (const LrCtxt *)dec_handle->pv_lr_ctxt;

@@ -46,8 +46,9 @@ void svt_aom_get_recon_pic(PictureControlSet *pcs, EbPictureBufferDesc **recon_p
 typedef struct {
     const PictureControlSet *pcs;
     svtf_ctx                *ctx;
-    svtf_geom                geom;
+    svtf_geom                geom, max_geom;
     int                      resident; /* picture of this pcs currently on the device */
+    uint64_t                 launches_seen;
 } CtxSlot;
 static CtxSlot         g_slots[SVTF_MAX_CACHED];
 static pthread_mutex_t g_lock     = PTHREAD_MUTEX_INITIALIZER;
@@ -68,6 +69,34 @@ static void die(const char *where, svtf_ctx *ctx) {
             die(#call, ctx);   \
     } while (0)
 
+/* Call counters, printed at exit when SVTF_ADAPTER_STATS is set in the environment: lets a test of the real application prove
+ * which stages ran on the GPU (`name=calls` pairs on one stderr line), and how many kernel launches they issued. */
+enum { ST_DLF, ST_DLF_SB_LAST, ST_LF_SEARCH, ST_CDEF_SEARCH, ST_CDEF_PICK, ST_CDEF_PICK_REFFS, ST_CDEF_APPLY, ST_CCSO, ST_CCSO_SEARCH, ST_LR_APPLY, ST_LR_SEARCH,
+       ST_SUPERRES, ST_PAD_REF, ST_N };
+static const char *const g_stat_name[ST_N] = {"loop_filter_frame", "loop_filter_sb_last", "pick_filter_level_full", "cdef_search_picture", "finish_cdef_search",
+                                              "finish_cdef_search_ref_fs", "cdef_frame", "ccso_frame", "ccso_search", "loop_restoration_filter_frame",
+                                              "restoration_search", "superres_upscale_frame", "pad_ref_pictures"};
+static unsigned long   g_stat[ST_N];
+static unsigned long   g_stat_launches;
+static pthread_once_t  g_stat_once = PTHREAD_ONCE_INIT;
+static void            stat_print(void) {
+    if (!getenv("SVTF_ADAPTER_STATS"))
+        return;
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < SVTF_MAX_CACHED; i++)
+        if (g_slots[i].ctx)
+            g_stat_launches += (unsigned long)svtf_launch_count(g_slots[i].ctx) - g_slots[i].launches_seen, g_slots[i].launches_seen = svtf_launch_count(g_slots[i].ctx);
+    pthread_mutex_unlock(&g_lock);
+    fprintf(stderr, "svtfilt_b200 adapter stats:");
+    for (int i = 0; i < ST_N; i++) fprintf(stderr, " %s=%lu", g_stat_name[i], g_stat[i]);
+    fprintf(stderr, " gpu_launches=%lu\n", g_stat_launches);
+}
+static void stat_init(void) { atexit(stat_print); }
+static void stat_hit(int which) {
+    pthread_once(&g_stat_once, stat_init);
+    __sync_fetch_and_add(&g_stat[which], 1);
+}
+
 static svtf_geom geom_of(const PictureControlSet *pcs) {
     const SequenceControlSet *scs = pcs->scs;
     const Av1Common          *cm  = pcs->ppcs->av1_cm;
@@ -85,7 +114,22 @@ static svtf_geom geom_of(const PictureControlSet *pcs) {
     return g;
 }
 
+/* Geometry a context must hold for this picture (room for the super-resolution upscale included). */
+static svtf_geom max_geom_of(const PictureControlSet *pcs, const svtf_geom *g) {
+    svtf_geom        mg = *g;
+    const Av1Common *cm = pcs->ppcs->av1_cm;
+    if (cm->frm_size.superres_denominator > SCALE_NUMERATOR && cm->frm_size.superres_upscaled_width > mg.width) {
+        mg.width   = cm->frm_size.superres_upscaled_width;
+        mg.mi_cols = 2 * ((mg.width + 7) >> 3);
+    }
+    return mg;
+}
+
+/* The GPU context of a picture.  Contexts are cached per pcs pointer — the pipeline recycles a small pool of PictureControlSets, so
+ * a recycled pcs finds its surfaces allocated — but the geometry is recomputed on EVERY entry: a recycled pcs may carry another
+ * super-resolution / resize width, and then the context is rebuilt and nothing stale (resident picture included) survives. */
 static CtxSlot *slot_for(const PictureControlSet *pcs) {
+    const svtf_geom g = geom_of(pcs), mg = max_geom_of(pcs, &g);
     pthread_mutex_lock(&g_lock);
     CtxSlot *free_slot = NULL, *s = NULL;
     for (int i = 0; i < SVTF_MAX_CACHED; i++) {
@@ -96,6 +140,12 @@ static CtxSlot *slot_for(const PictureControlSet *pcs) {
         if (!g_slots[i].pcs && !free_slot)
             free_slot = &g_slots[i];
     }
+    if (s && (mg.mi_cols > s->max_geom.mi_cols || mg.mi_rows > s->max_geom.mi_rows || mg.sample_bytes != s->max_geom.sample_bytes)) {
+        g_stat_launches += (unsigned long)svtf_launch_count(s->ctx) - s->launches_seen;
+        svtf_ctx_destroy(s->ctx); /* the picture no longer fits: rebuild */
+        memset(s, 0, sizeof(*s));
+        free_slot = s, s = NULL;
+    }
     if (!s) {
         if (!free_slot) {
             fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: more than %d pictures in flight\n", SVTF_MAX_CACHED);
@@ -103,17 +153,14 @@ static CtxSlot *slot_for(const PictureControlSet *pcs) {
         }
         s           = free_slot;
         s->pcs      = pcs;
-        s->geom     = geom_of(pcs);
+        s->max_geom = mg;
         s->resident = 0;
-        svtf_geom        mg = s->geom; /* room for the super-resolution upscale */
-        const Av1Common *cm = pcs->ppcs->av1_cm;
-        if (cm->frm_size.superres_denominator > SCALE_NUMERATOR && cm->frm_size.superres_upscaled_width > mg.width) {
-            mg.width   = cm->frm_size.superres_upscaled_width;
-            mg.mi_cols = 2 * ((mg.width + 7) >> 3);
-        }
         if (svtf_ctx_create(g_device, &mg, &s->ctx) != SVTF_OK)
             die("svtf_ctx_create", NULL);
     }
+    if (memcmp(&s->geom, &g, sizeof(g))) /* another picture size on the same pcs: whatever is on the device is not this picture */
+        s->resident = 0;
+    s->geom = g;
     pthread_mutex_unlock(&g_lock);
     return s;
 }
@@ -123,6 +170,7 @@ void svtf_adapter_release(const PictureControlSet *pcs) {
     pthread_mutex_lock(&g_lock);
     for (int i = 0; i < SVTF_MAX_CACHED; i++)
         if (g_slots[i].pcs == pcs) {
+            g_stat_launches += (unsigned long)svtf_launch_count(g_slots[i].ctx) - g_slots[i].launches_seen;
             svtf_ctx_destroy(g_slots[i].ctx);
             memset(&g_slots[i], 0, sizeof(g_slots[i]));
         }
@@ -214,6 +262,7 @@ static void lf_of(const PictureControlSet *pcs, svtf_lf_params *out) {
 
 void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControlSet *pcs, int32_t plane_start,
                                int32_t plane_end) {
+    stat_hit(ST_DLF);
     CtxSlot       *s = slot_for(pcs);
     svtf_lf_params lf;
     lf_of(pcs, &lf);
@@ -221,6 +270,27 @@ void svt_av1_loop_filter_frame(EbPictureBufferDesc *frame_buffer, PictureControl
     CHECK(svtf_deblock_frame(s->ctx, &lf, plane_start, plane_end), s->ctx);
     if (!g_resident)
         end_picture(s, frame_buffer), s->resident = 0;
+}
+
+/* svt_av1_loop_filter_init (Encoder/Codec/EbDeblockingFilter.c:35): the limits / thresholds it fills in pcs->ppcs->lf_info are
+ * rebuilt on every deblock call from the frame header (svtf_lf_build_tables), so only the flag the per-SB filter reads stays. */
+void svt_av1_loop_filter_init(PictureControlSet *pcs) { pcs->ppcs->frm_hdr.loop_filter_params.combine_vert_horz_lf = 1; }
+
+/* svt_aom_loop_filter_sb (Encoder/Codec/EbDeblockingFilter.c:547), the per-superblock deblock EncDec runs right after a superblock is
+ * reconstructed (Encoder/Codec/EbCodingLoop.c:2260-2281, dlf_level >= 3: presets M6 and up).  The GPU filters whole pictures: the call
+ * is a no-op until the LAST superblock of the picture arrives — EncDec walks superblocks in wavefront order (a superblock starts after
+ * its left and top-right neighbours), so the bottom-right one comes last, when every superblock's reconstruction and mode info are
+ * final — and then the whole picture is filtered in one launch.  The per-SB and the per-frame order give the same pixels: edges of one
+ * pass never overlap, and every horizontal edge reads the column-pass result of all samples it touches in both orders. */
+void svt_aom_loop_filter_sb(EbPictureBufferDesc *frame_buffer, PictureControlSet *pcs, int32_t mi_row, int32_t mi_col, int32_t plane_start,
+                            int32_t plane_end, uint8_t last_col) {
+    const Av1Common *cm    = pcs->ppcs->av1_cm;
+    const int        sb_mi = pcs->scs->sb_size >> 2;
+    (void)mi_col;
+    if (!last_col || mi_row + sb_mi < cm->mi_rows)
+        return;
+    stat_hit(ST_DLF_SB_LAST);
+    svt_av1_loop_filter_frame(frame_buffer, pcs, plane_start, plane_end);
 }
 
 /* svt_av1_pick_filter_level (Encoder/Codec/EbDeblockingFilter.c:1129).  LPF_PICK_MINIMAL_LPF and LPF_PICK_FROM_Q are
@@ -277,6 +347,7 @@ EbErrorType svt_av1_pick_filter_level(EbPictureBufferDesc *srcBuffer, PictureCon
     cfg.only_4x4               = fh->tx_mode == ONLY_4X4;
     cfg.search_chroma          = !(pcs->ppcs->dlf_ctrls.dlf_avg_uv && pcs->temporal_layer_index > 0); /* :1218 */
     int32_t out[4];
+    stat_hit(ST_LF_SEARCH);
     CHECK(svtf_lf_search_frame(s->ctx, &lf, &cfg, out), s->ctx);
     l->filter_level[0] = out[0], l->filter_level[1] = out[1], l->filter_level_u = out[2], l->filter_level_v = out[3];
     if (!g_resident)
@@ -292,6 +363,7 @@ static void fb_indices(const PictureControlSet *pcs, const svtf_geom *g, int8_t 
 }
 
 void svt_av1_cdef_frame(SequenceControlSet *scs, PictureControlSet *pcs) {
+    stat_hit(ST_CDEF_APPLY);
     CtxSlot             *s = slot_for(pcs);
     EbPictureBufferDesc *recon;
     svt_aom_get_recon_pic(pcs, &recon, scs->is_16bit_pipeline);
@@ -333,6 +405,7 @@ static void search_cfg_of(const PictureControlSet *pcs, svtf_cdef_search_cfg *c)
 /* cdef_seg_search over the whole picture (the first CDEF segment to arrive calls this, the others no-op):
  * fills pcs->mse_seg, pcs->skip_cdef_seg and pcs->cdef_dir_data like the reference. */
 void svtf_cdef_search_picture(PictureControlSet *pcs, SequenceControlSet *scs) {
+    stat_hit(ST_CDEF_SEARCH);
     CtxSlot             *s = slot_for(pcs);
     EbPictureBufferDesc *recon;
     svt_aom_get_recon_pic(pcs, &recon, scs->is_16bit_pipeline);
@@ -359,28 +432,86 @@ void svtf_cdef_search_picture(PictureControlSet *pcs, SequenceControlSet *scs) {
     free(mse), free(dir), free(var);
 }
 
+/* 64x64 filter blocks that the reference folds into the first filter block of a 128-wide / 128-high coding block
+ * (Encoder/Codec/EbCdefProcess.c:186-189, Encoder/Codec/EbEncCdef.c:756-759, :822-826): the right / lower quadrants are neither
+ * searched nor picked on their own — the first quadrant carries the distortion of the whole block and its index is copied to them. */
+static int fb_folded(const PictureControlSet *pcs, int fbr, int fbc) {
+    const BlockSize bs = pcs->mi_grid_base[16 * fbr * pcs->mi_stride + 16 * fbc]->mbmi.block_mi.bsize;
+    return ((fbc & 1) && (bs == BLOCK_128X128 || bs == BLOCK_128X64)) || ((fbr & 1) && (bs == BLOCK_128X128 || bs == BLOCK_64X128));
+}
+/* "we generate param only for the first 64x64 ... we need to duplicate data" (EbEncCdef.c:779-793, :884-905) */
+static void fb_set_strength(PictureControlSet *pcs, int fbr, int fbc, int8_t gi) {
+    const int  at = 16 * fbr * pcs->mi_stride + 16 * fbc;
+    ModeInfo **g  = pcs->mi_grid_base;
+    g[at]->mbmi.cdef_strength = gi;
+    switch (g[at]->mbmi.block_mi.bsize) {
+    case BLOCK_128X128:
+        g[at + 16]->mbmi.cdef_strength                       = gi;
+        g[at + 16 * pcs->mi_stride]->mbmi.cdef_strength      = gi;
+        g[at + 16 * pcs->mi_stride + 16]->mbmi.cdef_strength = gi;
+        break;
+    case BLOCK_128X64: g[at + 16]->mbmi.cdef_strength = gi; break;
+    case BLOCK_64X128: g[at + 16 * pcs->mi_stride]->mbmi.cdef_strength = gi; break;
+    default: break;
+    }
+}
+
 void finish_cdef_search(PictureControlSet *pcs) {
     CtxSlot                 *s    = slot_for(pcs);
     PictureParentControlSet *ppcs = pcs->ppcs;
     FrameHeader             *fh   = &ppcs->frm_hdr;
-    svtf_cdef_search_cfg     cfg;
+    const CdefControls      *cc   = &ppcs->cdef_ctrls;
+    const int nvfb = (s->geom.mi_rows + 15) / 16, nhfb = (s->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
+    if (cc->use_reference_cdef_fs) {
+        /* EbEncCdef.c:744-793: no search ran; one strength pair predicted from the reference frames, index 0 for every filter block
+         * that is not all-skip.  Pure bookkeeping on the host — no pixel work, so nothing for the GPU to do. */
+        stat_hit(ST_CDEF_PICK_REFFS);
+        for (int fbr = 0; fbr < nvfb; fbr++)
+            for (int fbc = 0; fbc < nhfb; fbc++) {
+                if (fb_folded(pcs, fbr, fbc))
+                    continue;
+                int all_skip = 1; /* svt_sb_all_skip (:219-235) */
+                const int maxr = s->geom.mi_rows - 16 * fbr < 16 ? s->geom.mi_rows - 16 * fbr : 16;
+                const int maxc = s->geom.mi_cols - 16 * fbc < 16 ? s->geom.mi_cols - 16 * fbc : 16;
+                for (int r = 0; r < maxr && all_skip; r++)
+                    for (int c = 0; c < maxc; c++)
+                        if (!pcs->mi_grid_base[(16 * fbr + r) * pcs->mi_stride + 16 * fbc + c]->mbmi.block_mi.skip) {
+                            all_skip = 0;
+                            break;
+                        }
+                if (!all_skip)
+                    fb_set_strength(pcs, fbr, fbc, 0);
+            }
+        fh->cdef_params.cdef_bits           = 0;
+        ppcs->nb_cdef_strengths             = 1;
+        fh->cdef_params.cdef_damping        = (uint8_t)(3 + (fh->quantization_params.base_q_idx >> 6));
+        fh->cdef_params.cdef_y_strength[0]  = cc->pred_y_f;
+        fh->cdef_params.cdef_uv_strength[0] = cc->pred_uv_f;
+        return;
+    }
+    stat_hit(ST_CDEF_PICK);
+    svtf_cdef_search_cfg cfg;
     search_cfg_of(pcs, &cfg);
     uint32_t fast_lambda = 0, full_lambda = 0;
     (*svt_aom_av1_lambda_assignment_function_table[ppcs->pred_structure])(
         pcs, &fast_lambda, &full_lambda, (uint8_t)ppcs->enhanced_pic->bit_depth, fh->quantization_params.base_q_idx, FALSE);
-    cfg.lambda    = full_lambda;
-    const int nvfb = (s->geom.mi_rows + 15) / 16, nhfb = (s->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
+    cfg.lambda = full_lambda;
     /* the table lives in pcs->mse_seg (the reference's bias pass edits it in place; so do we) */
-    uint64_t *mse = (uint64_t *)malloc(sizeof(uint64_t) * 128 * (size_t)nfb);
+    uint64_t *mse  = (uint64_t *)malloc(sizeof(uint64_t) * 128 * (size_t)nfb);
+    uint8_t  *skip = (uint8_t *)malloc(nfb);
+    int8_t   *idx  = (int8_t *)malloc(nfb);
+    if (!mse || !skip || !idx)
+        die("malloc(finish_cdef_search)", s->ctx);
     memcpy(mse, pcs->mse_seg[0], sizeof(uint64_t) * 64 * (size_t)nfb);
     memcpy(mse + (size_t)64 * nfb, pcs->mse_seg[1], sizeof(uint64_t) * 64 * (size_t)nfb);
+    for (int fbr = 0; fbr < nvfb; fbr++) /* folded quadrants take no part in the pick (:822-826) */
+        for (int fbc = 0; fbc < nhfb; fbc++) skip[fbr * nhfb + fbc] = fb_folded(pcs, fbr, fbc) ? 1 : pcs->skip_cdef_seg[fbr * nhfb + fbc];
     svtf_cdef_params out;
-    int8_t          *idx = (int8_t *)malloc(nfb);
     /* GPU pick from the caller's table: 75 svt_search_one_dual passes without a host round trip */
-    CHECK(svtf_cdef_pick_table(s->ctx, &cfg, mse, pcs->skip_cdef_seg, nfb, &out, idx), s->ctx);
+    CHECK(svtf_cdef_pick_table(s->ctx, &cfg, mse, skip, nfb, &out, idx), s->ctx);
     if (cfg.zero_fs_cost_bias)
         for (int fb = 0; fb < nfb; fb++)
-            if (!pcs->skip_cdef_seg[fb]) {
+            if (!skip[fb]) {
                 pcs->mse_seg[0][fb][0] = ((uint16_t)cfg.zero_fs_cost_bias * pcs->mse_seg[0][fb][0]) >> 6;
                 pcs->mse_seg[1][fb][0] = ((uint16_t)cfg.zero_fs_cost_bias * pcs->mse_seg[1][fb][0]) >> 6;
             }
@@ -394,11 +525,17 @@ void finish_cdef_search(PictureControlSet *pcs) {
     for (int fbr = 0; fbr < nvfb; fbr++)
         for (int fbc = 0; fbc < nhfb; fbc++)
             if (idx[fbr * nhfb + fbc] >= 0)
-                pcs->mi_grid_base[16 * fbr * pcs->mi_stride + 16 * fbc]->mbmi.cdef_strength = idx[fbr * nhfb + fbc];
-    free(mse), free(idx);
+                fb_set_strength(pcs, fbr, fbc, idx[fbr * nhfb + fbc]);
+    free(mse), free(skip), free(idx);
 }
 
+/* extend_ccso_border (Common/Codec/EbCcso.c:185) replicates the frame edge of the classifier luma into a 5-sample border of the
+ * caller's ext_rec_y so that the CPU kernels may read taps beyond the picture.  The GPU kernels clamp tap coordinates to the picture
+ * instead (same values), and ccso_frame / ccso_search below read only the interior of ext_rec_y: nothing to materialise. */
+void extend_ccso_border(uint16_t *buf, const int d, MacroblockdPlane *pd) { (void)buf, (void)d, (void)pd; }
+
 void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdPlane *pd, uint16_t *ext_rec_y) {
+    stat_hit(ST_CCSO);
     (void)pd;
     CtxSlot        *s  = slot_for(pcs);
     const CcsoInfo *ci = &pcs->ppcs->frm_hdr.ccso_info;
@@ -465,6 +602,7 @@ void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdP
  * staged on the picture's context (classifier luma as the "pre-CDEF" picture, rec as the current picture, org as the
  * source), svtf_ccso_derive_frame runs the search, the result goes where the reference writes it. */
 void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const uint16_t *ext_rec_y, uint16_t *rec_uv[3], uint16_t *org_uv[3]) {
+    stat_hit(ST_CCSO_SEARCH);
     (void)pd;
     FrameHeader  *fh     = &pcs->ppcs->frm_hdr;
     int           weight = fh->quantization_params.base_q_idx;
@@ -552,6 +690,7 @@ void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const
  * in rst_info[p].boundaries (two above and two below every 64-row stripe, :1522-1574) are written into an otherwise
  * empty picture that is uploaded as the pre-CDEF picture — only those rows are ever read. */
 void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig *frame, Av1Common *cm, int32_t optimized_lr) {
+    stat_hit(ST_LR_APPLY);
     (void)rst_tmpbuf;
     PictureControlSet *pcs = cm->child_pcs;
     CtxSlot           *s   = slot_for(pcs);
@@ -627,6 +766,7 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
  * stand-alone: recon is uploaded, upscaled and written back into the same buffers.
  * ---------------------------------------------------------------------------------------------------- */
 void svt_av1_superres_upscale_frame(struct Av1Common *cm, PictureControlSet *pcs, SequenceControlSet *scs) {
+    stat_hit(ST_SUPERRES);
     EbPictureBufferDesc *recon;
     svt_aom_get_recon_pic(pcs, &recon, scs->is_16bit_pipeline);
     CtxSlot *s = slot_for(pcs);
@@ -694,6 +834,7 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     (void)rst_tmpbuf, (void)trial_frame_rst;
     if (segment_index != 0)
         return;
+    stat_hit(ST_LR_SEARCH);
     Av1Common        *cm = pcs->ppcs->av1_cm;
     const Macroblock *x  = pcs->ppcs->av1x;
     CtxSlot          *s  = slot_for(pcs);
@@ -827,6 +968,7 @@ void rest_finish_search(PictureControlSet *pcs) {
  * allocation width including columns its padding did not write; this function writes the padded rectangle only.)
  * ---------------------------------------------------------------------------------------------------- */
 void svtf_pad_ref_pictures(PictureControlSet *pcs, SequenceControlSet *scs) {
+    stat_hit(ST_PAD_REF);
     EbPictureBufferDesc *ref8, *ref16;
     svt_aom_get_recon_pic(pcs, &ref8, 0);
     svt_aom_get_recon_pic(pcs, &ref16, 1);

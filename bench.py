@@ -40,11 +40,11 @@ UNFUSED = os.environ.get("SVTF_CHAIN_UNFUSED") is not None  # A/B: CDEF and CCSO
 UNIT = "Mpixel/s"
 
 
-def workload(H, geom, seed):
+def workload(H, geom, seed, with_mi=True):
     S = H.S
     rec = H.synth_picture(geom, seed)
     soa = H.synth_mode_info(geom, seed + 1, p_split=0.5, p_skip=0.3, p_inter=0.7)
-    mi = H.pack_mi(soa)
+    mi = H.pack_mi(soa) if with_mi else None  # packed words: the product's input (and the oracle port's); the reference reads `soa`
     lf = S.lf_params((24, 24), 12, 12)
     cdef, idx = H.synth_cdef(geom, seed + 2, n_strengths=8, damping=5)
     ccso, flags = H.synth_ccso(geom, seed + 3, quant_idx=(0, 0, 0), support=(0, 1, 2), edge_clf=(0, 0, 0), band_log2=(2, 2, 2), p_on=0.8)
@@ -79,17 +79,22 @@ def bind_to_gpu_cpus(torch, local):
     return "not bound"
 
 
-def cpu_chain_runner(H):
-    """Returns (kind, fn(geom, wl) -> None) running deblock->CDEF->CCSO on the CPU."""
+def cpu_chain_runner(H, simd=True):
+    """Returns (kind, fn(geom, wl) -> None) running deblock->CDEF->CCSO on the CPU with the reference's own code:
+    simd=True  oracle/_ref/libsvtref_simd.so — the SSE2 / AVX2 kernels the reference's RTCD selects on this host (its real fast path;
+               tests/test_ref_simd.py pins it equal to the C-only build), kind "reference-avx2";
+    simd=False oracle/_ref/libsvtref.so — the `_c` kernels, kind "reference (C only, no SIMD)";
+    neither library present: the oracle port."""
     if H.ref_available():
-        ref = H.Ref()
+        use_simd = simd and H.ref_simd_available()
+        ref = H.Ref(simd=use_simd)
 
         def run(geom, wl):
             a = ref.deblock(geom, wl["rec"], wl["soa"], wl["lf"])
             b = ref.cdef_apply(geom, a, wl["soa"], wl["cdef"], wl["idx"])
             ref.ccso_apply(geom, b, a[0], wl["ccso"], wl["flags"])
 
-        return "reference", run
+        return ("reference-avx2" if use_simd else "reference (C only, no SIMD)"), run
     orc = H.Oracle()
 
     def run(geom, wl):
@@ -100,15 +105,20 @@ def cpu_chain_runner(H):
     return "port", run
 
 
-def cpu_measure(H, band_h, threads, steps, warmup):
-    """Each step: `threads` host threads each filter one 3840 x band_h 10-bit band (ctypes releases the GIL)."""
+CPU_SAMPLE_H = 2160  # every host thread filters one whole 3840x2160 10-bit picture per step — the same sample in both arms
+
+
+def cpu_measure(H, band_h, threads, steps, warmup, simd=True):
+    """Each step: `threads` host threads each filter one 3840 x band_h 10-bit picture (ctypes releases the GIL).  Four distinct
+    pictures are cycled over the threads (the inputs are read-only; every call filters its own copy)."""
     S = H.S
     geom = S.make_geom(W4K, band_h, BD)
-    wls = [workload(H, geom, 0xC2 + 16 * t) for t in range(threads)]
-    kind, run = cpu_chain_runner(H)
+    kind, run = cpu_chain_runner(H, simd)
+    nd = min(threads, 4)
+    wls = [workload(H, geom, 0xC2 + 16 * t, with_mi=(kind == "port")) for t in range(nd)]
 
     def step():
-        th = [threading.Thread(target=run, args=(geom, wls[t])) for t in range(threads)]
+        th = [threading.Thread(target=run, args=(geom, wls[t % nd])) for t in range(threads)]
         for t in th:
             t.start()
         for t in th:
@@ -121,7 +131,7 @@ def cpu_measure(H, band_h, threads, steps, warmup):
         step()
     dt = time.perf_counter() - t0
     mpix = threads * W4K * band_h * steps / 1e6
-    return kind, mpix / dt, dt / steps, f"{threads} threads x one 3840x{band_h} 10-bit band per step, {steps} steps"
+    return kind, mpix / dt, dt / steps, f"{threads} threads x one 3840x{band_h} 10-bit picture per step, {steps} steps"
 
 
 def cpu_search_measure(H, band_h, threads):
@@ -137,7 +147,8 @@ def cpu_search_measure(H, band_h, threads):
         soa = H.synth_mode_info(geom, 0xC3 + 16 * t + 1)
         items.append((rec, H.synth_source(geom, rec, 0xC3 + 16 * t + 2), soa, H.pack_mi(soa)))
     if H.ref_available():
-        ref, kind = H.Ref(), "reference"
+        use_simd = H.ref_simd_available()
+        ref, kind = H.Ref(simd=use_simd), ("reference-avx2" if use_simd else "reference (C only, no SIMD)")
 
         def run(it):
             mse, skip, _, _ = ref.cdef_search(geom, it[0], it[1], it[2], cfg)
@@ -578,27 +589,26 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    # the reference's CPU code alone: this process neither imports the product's Python package nor maps libsvtfilt_b200.so
+    os.environ["SVTF_HARNESS_NO_PRODUCT"] = "1"
     import harness as H
 
     threads = os.cpu_count() or 1
-    band_h = 256
-    # one untimed probe step sizes the band so K+W steps stay within ~2.5 minutes
-    _, _, probe, _ = cpu_measure(H, band_h, threads, 1, 0)
-    budget = 150.0 / max(1, args.steps + args.warmup)
-    while band_h < 2160 and probe * 2 < budget:
-        band_h = min(2160, band_h * 2)
-        probe *= 2
-    while band_h > 64 and probe > budget:
-        band_h //= 2
-        probe /= 2
-    band_h = 2160 if band_h > 2160 else band_h // 8 * 8
-    kind, val, per_step, sample = cpu_measure(H, band_h, threads, args.steps, args.warmup)
+    kind, val, per_step, sample = cpu_measure(H, CPU_SAMPLE_H, threads, args.steps, args.warmup, simd=True)
+    c_only = None
+    if kind == "reference-avx2":  # the C-only build (the parity checker) beside it, one step
+        k2, v2, _, s2 = cpu_measure(H, CPU_SAMPLE_H, threads, 1, 0, simd=False)
+        c_only = {"value": round(v2, 3), "unit": UNIT, "cores": threads, "kind": k2, "sample": s2}
+    with open("/proc/self/maps") as f:
+        product_loaded = "libsvtfilt_b200" in f.read() or "svtfilt_b200" in sys.modules
     line = {
         "impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(per_step * 1e3, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u16", "data": "synthetic",
-        "config": {"workload": "decoder post-recon filter chain, 4K (3840x2160) 10-bit 4:2:0, deblock+CDEF+CCSO", "sample": sample},
+        "config": {"workload": "decoder post-recon filter chain, 4K (3840x2160) 10-bit 4:2:0, deblock+CDEF+CCSO", "sample": sample,
+                   "product_library_loaded": bool(product_loaded)},
         "cpu_baseline": {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "cpu_baseline_c_only": c_only,
         "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -892,8 +902,11 @@ def main():
     cpu = search_cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        kind, val, per_step, sample = cpu_measure(H, 272, threads, 3, 1)
+        kind, val, per_step, sample = cpu_measure(H, CPU_SAMPLE_H, threads, 3, 1, simd=True)
         cpu = {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": kind, "sample": sample}
+        if kind == "reference-avx2":
+            k2, v2, _, s2 = cpu_measure(H, CPU_SAMPLE_H, threads, 1, 0, simd=False)
+            cpu["c_only"] = {"value": round(v2, 3), "unit": UNIT, "kind": k2, "sample": s2}
         search_cpu = cpu_search_measure(H, 64, threads)
 
     if rank == 0:

@@ -1,0 +1,32 @@
+#!/usr/bin/env bash
+# Builds the reference applications twice, out of tree, from /root/reference (read-only):
+#   integration/_bin/SvtAv1EncApp_ref,  SvtAv1DecApp_ref   — the unmodified reference (C only: there is no nasm/yasm in this image)
+#   integration/_bin/SvtAv1EncApp_b200, SvtAv1DecApp_b200  — the same tree + integration/svt_b200.patch (-DSVT_B200_FILTERS=ON): the
+#       filter stages call adapters/svtf_*_adapters.c over libsvtfilt_b200.so
+# The patched tree is a COPY under integration/_build/src_b200 (git- and gpurun-ignored); the binaries travel to the GPU box.
+# Needs: cmake, ninja, gcc, patch; the reference tree at $REF; the CUDA library already built (__graft_entry__.build()).
+set -euo pipefail
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+ROOT="$(dirname "$HERE")"
+REF="${REF:-/root/reference}"
+B="$HERE/_build"
+mkdir -p "$B" "$HERE/_bin"
+COMMON=(-G Ninja -DCMAKE_BUILD_TYPE=Release -DCOMPILE_C_ONLY=ON -DBUILD_SHARED_LIBS=OFF -DBUILD_TESTING=OFF)
+
+if [ ! -x "$HERE/_bin/SvtAv1EncApp_ref" ] || [ "${FORCE:-0}" = 1 ]; then
+  cmake "${COMMON[@]}" -S "$REF" -B "$B/ref" -DCMAKE_OUTPUT_DIRECTORY="$B/ref/bin/" > "$B/ref_cmake.log" 2>&1
+  ninja -C "$B/ref" > "$B/ref_ninja.log" 2>&1
+  cp "$B/ref/bin/SvtAv1EncApp" "$HERE/_bin/SvtAv1EncApp_ref"
+  cp "$B/ref/bin/SvtAv1DecApp" "$HERE/_bin/SvtAv1DecApp_ref"
+fi
+
+# patched copy: only the directories the build needs
+rm -rf "$B/src_b200"
+mkdir -p "$B/src_b200"
+for t in CMakeLists.txt Source cmake third_party Config; do cp -r "$REF/$t" "$B/src_b200/"; done
+patch -s -p1 -d "$B/src_b200" < "$HERE/svt_b200.patch"
+cmake "${COMMON[@]}" -S "$B/src_b200" -B "$B/b200" -DSVT_B200_FILTERS=ON -DSVTFILT_DIR="$ROOT" -DCMAKE_OUTPUT_DIRECTORY="$B/b200/bin/" > "$B/b200_cmake.log" 2>&1
+ninja -C "$B/b200" > "$B/b200_ninja.log" 2>&1
+cp "$B/b200/bin/SvtAv1EncApp" "$HERE/_bin/SvtAv1EncApp_b200"
+cp "$B/b200/bin/SvtAv1DecApp" "$HERE/_bin/SvtAv1DecApp_b200"
+ls -la "$HERE/_bin"

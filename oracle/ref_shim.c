@@ -37,13 +37,29 @@
 
 #define REF_API __attribute__((visibility("default")))
 
-/* ---- RTCD pointers -> C kernels (Common/Codec/common_dsp_rtcd.c:626-658, Encoder aom_dsp_rtcd.c) ---- */
+/* ---- RTCD pointers (Common/Codec/common_dsp_rtcd.c:626-658, Encoder/Codec/aom_dsp_rtcd.c:187,188,478) ----
+ * Default build (libsvtref.so, the parity checker): the `_c` kernels, what svt_aom_setup_common_rtcd_internal(0) selects.
+ * -DSVTF_REF_SIMD=1 (libsvtref_simd.so, the TIMED CPU baseline): the variants the same tables select on an AVX2 host —
+ * SET_SSE2 for the loop-filter edges, SET_SSE41_AVX2 / SET_AVX2 for CDEF, the CDEF distortion, the strength pick and CCSO.
+ * Their sources (Common/ASM_AVX2/cdef_block_avx2.c, ccso_avx2.c, Common/ASM_SSE2/EbDeblockingFilter_Intrinsic_SSE2.c,
+ * Encoder/ASM_AVX2/EbCdef_AVX2.c) are C intrinsics and are compiled where they lie by oracle/Makefile. */
+#ifndef SVTF_REF_SIMD
+#define SVTF_REF_SIMD 0
+#endif
+#if SVTF_REF_SIMD
+#define LPF_SFX(n) n##_sse2
+#define AVX2_OR_C(n_c, n_avx2) n_avx2
+#else
+#define LPF_SFX(n) n##_c
+#define AVX2_OR_C(n_c, n_avx2) n_c
+#endif
+REF_API int ref_is_simd(void) { return SVTF_REF_SIMD; }
 #define LPF_DECL(n)                                                                                                   \
-    void svt_aom_lpf_##n##_c(uint8_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *);                  \
-    void (*svt_aom_lpf_##n)(uint8_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *) = svt_aom_lpf_##n##_c; \
-    void svt_aom_highbd_lpf_##n##_c(uint16_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *, int32_t); \
+    void LPF_SFX(svt_aom_lpf_##n)(uint8_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *);             \
+    void (*svt_aom_lpf_##n)(uint8_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *) = LPF_SFX(svt_aom_lpf_##n); \
+    void LPF_SFX(svt_aom_highbd_lpf_##n)(uint16_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *, int32_t); \
     void (*svt_aom_highbd_lpf_##n)(uint16_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *, int32_t) = \
-        svt_aom_highbd_lpf_##n##_c;
+        LPF_SFX(svt_aom_highbd_lpf_##n);
 LPF_DECL(horizontal_4)
 LPF_DECL(horizontal_6)
 LPF_DECL(horizontal_8)
@@ -53,46 +69,59 @@ LPF_DECL(vertical_6)
 LPF_DECL(vertical_8)
 LPF_DECL(vertical_14)
 
-uint8_t svt_aom_cdef_find_dir_c(const uint16_t *img, int32_t stride, int32_t *var, int32_t coeff_shift);
-void    svt_aom_cdef_find_dir_dual_c(const uint16_t *img1, const uint16_t *img2, int stride, int32_t *var1, int32_t *var2,
-                                     int32_t coeff_shift, uint8_t *out1, uint8_t *out2);
-void    svt_cdef_filter_block_c(uint8_t *dst8, uint16_t *dst16, int32_t dstride, const uint16_t *in, int32_t pri_strength,
-                                int32_t sec_strength, int32_t dir, int32_t pri_damping, int32_t sec_damping, int32_t bsize,
-                                int32_t coeff_shift, uint8_t subsampling_factor);
-void    svt_aom_copy_rect8_8bit_to_16bit_c(uint16_t *dst, int32_t dstride, const uint8_t *src, int32_t sstride, int32_t v,
-                                           int32_t h);
-uint64_t svt_aom_compute_cdef_dist_c(const uint16_t *dst, int32_t dstride, const uint16_t *src, const CdefList *dlist,
-                                     int32_t cdef_count, BlockSize bsize, int32_t coeff_shift, int32_t pli,
-                                     uint8_t subsampling_factor);
-uint64_t svt_aom_compute_cdef_dist_8bit_c(const uint8_t *dst8, int32_t dstride, const uint8_t *src8, const CdefList *dlist,
-                                          int32_t cdef_count, BlockSize bsize, int32_t coeff_shift, int32_t pli,
-                                          uint8_t subsampling_factor);
-uint64_t svt_search_one_dual_c(int *lev0, int *lev1, int nb_strengths, uint64_t **mse[2], int sb_count, int start_gi,
-                               int end_gi);
+#define FIND_DIR AVX2_OR_C(svt_aom_cdef_find_dir_c, svt_aom_cdef_find_dir_avx2)
+#define FIND_DIR_DUAL AVX2_OR_C(svt_aom_cdef_find_dir_dual_c, svt_aom_cdef_find_dir_dual_avx2)
+#define FILTER_BLOCK AVX2_OR_C(svt_cdef_filter_block_c, svt_cdef_filter_block_avx2)
+#define COPY_RECT8 AVX2_OR_C(svt_aom_copy_rect8_8bit_to_16bit_c, svt_aom_copy_rect8_8bit_to_16bit_avx2)
+#define CDEF_DIST16 AVX2_OR_C(svt_aom_compute_cdef_dist_c, svt_aom_compute_cdef_dist_16bit_avx2)
+#define CDEF_DIST8 AVX2_OR_C(svt_aom_compute_cdef_dist_8bit_c, svt_aom_compute_cdef_dist_8bit_avx2)
+#define SEARCH_ONE_DUAL AVX2_OR_C(svt_search_one_dual_c, svt_search_one_dual_avx2)
+#define CCSO_WO_BUF AVX2_OR_C(ccso_filter_block_hbd_wo_buf_c, ccso_filter_block_hbd_wo_buf_avx2)
 
-uint8_t (*svt_aom_cdef_find_dir)(const uint16_t *, int32_t, int32_t *, int32_t) = svt_aom_cdef_find_dir_c;
+uint8_t FIND_DIR(const uint16_t *img, int32_t stride, int32_t *var, int32_t coeff_shift);
+void    FIND_DIR_DUAL(const uint16_t *img1, const uint16_t *img2, int stride, int32_t *var1, int32_t *var2, int32_t coeff_shift,
+                      uint8_t *out1, uint8_t *out2);
+void    FILTER_BLOCK(uint8_t *dst8, uint16_t *dst16, int32_t dstride, const uint16_t *in, int32_t pri_strength, int32_t sec_strength,
+                     int32_t dir, int32_t pri_damping, int32_t sec_damping, int32_t bsize, int32_t coeff_shift,
+                     uint8_t subsampling_factor);
+void    COPY_RECT8(uint16_t *dst, int32_t dstride, const uint8_t *src, int32_t sstride, int32_t v, int32_t h);
+uint64_t CDEF_DIST16(const uint16_t *dst, int32_t dstride, const uint16_t *src, const CdefList *dlist, int32_t cdef_count,
+                     BlockSize bsize, int32_t coeff_shift, int32_t pli, uint8_t subsampling_factor);
+uint64_t CDEF_DIST8(const uint8_t *dst8, int32_t dstride, const uint8_t *src8, const CdefList *dlist, int32_t cdef_count,
+                    BlockSize bsize, int32_t coeff_shift, int32_t pli, uint8_t subsampling_factor);
+uint64_t SEARCH_ONE_DUAL(int *lev0, int *lev1, int nb_strengths, uint64_t **mse[2], int sb_count, int start_gi, int end_gi);
+
+uint8_t (*svt_aom_cdef_find_dir)(const uint16_t *, int32_t, int32_t *, int32_t) = FIND_DIR;
 void (*svt_aom_cdef_find_dir_dual)(const uint16_t *, const uint16_t *, int, int32_t *, int32_t *, int32_t, uint8_t *,
-                                   uint8_t *)                                   = svt_aom_cdef_find_dir_dual_c;
+                                   uint8_t *)                                   = FIND_DIR_DUAL;
 void (*svt_cdef_filter_block)(uint8_t *, uint16_t *, int32_t, const uint16_t *, int32_t, int32_t, int32_t, int32_t, int32_t,
-                              int32_t, int32_t, uint8_t)                        = svt_cdef_filter_block_c;
+                              int32_t, int32_t, uint8_t)                        = FILTER_BLOCK;
 void (*svt_aom_copy_rect8_8bit_to_16bit)(uint16_t *, int32_t, const uint8_t *, int32_t, int32_t,
-                                         int32_t)                               = svt_aom_copy_rect8_8bit_to_16bit_c;
+                                         int32_t)                               = COPY_RECT8;
 uint64_t (*svt_compute_cdef_dist_16bit)(const uint16_t *, int32_t, const uint16_t *, const CdefList *, int32_t, BlockSize,
-                                        int32_t, int32_t, uint8_t)              = svt_aom_compute_cdef_dist_c;
+                                        int32_t, int32_t, uint8_t)              = CDEF_DIST16;
 uint64_t (*svt_compute_cdef_dist_8bit)(const uint8_t *, int32_t, const uint8_t *, const CdefList *, int32_t, BlockSize,
-                                       int32_t, int32_t, uint8_t)               = svt_aom_compute_cdef_dist_8bit_c;
-uint64_t (*svt_search_one_dual)(int *, int *, int, uint64_t **[2], int, int, int) = svt_search_one_dual_c;
+                                       int32_t, int32_t, uint8_t)               = CDEF_DIST8;
+uint64_t (*svt_search_one_dual)(int *, int *, int, uint64_t **[2], int, int, int) = SEARCH_ONE_DUAL;
 
-void ccso_filter_block_hbd_wo_buf_c(const uint16_t *src_y, uint16_t *dst_yuv, const int x, const int y,
-                                    const int pic_width, const int pic_height, int *src_cls, const int8_t *offset_buf,
-                                    const int src_y_stride, const int dst_stride, const int y_uv_hscale,
-                                    const int y_uv_vscale, const int thr, const int neg_thr, const int *src_loc,
-                                    const int max_val, const int blk_size, const bool isSingleBand,
-                                    const uint8_t shift_bits, const int edge_clf, const uint8_t ccso_bo_only);
+#if SVTF_REF_SIMD
+/* svt_cdef_filter_block_avx2 dispatches its 16-bit 8xN case through this pointer (common_dsp_rtcd.c:629-630) */
+void svt_cdef_filter_block_8xn_16_avx2(const uint16_t *const in, const int32_t pri_strength, const int32_t sec_strength, const int32_t dir,
+                                       int32_t pri_damping, int32_t sec_damping, const int32_t coeff_shift, uint16_t *const dst,
+                                       const int32_t dstride, uint8_t height, uint8_t subsampling_factor);
+void (*svt_cdef_filter_block_8xn_16)(const uint16_t *const, const int32_t, const int32_t, const int32_t, int32_t, int32_t, const int32_t,
+                                     uint16_t *const, const int32_t, uint8_t, uint8_t) = svt_cdef_filter_block_8xn_16_avx2;
+#endif
+
+void CCSO_WO_BUF(const uint16_t *src_y, uint16_t *dst_yuv, const int x, const int y, const int pic_width, const int pic_height,
+                 int *src_cls, const int8_t *offset_buf, const int src_y_stride, const int dst_stride, const int y_uv_hscale,
+                 const int y_uv_vscale, const int thr, const int neg_thr, const int *src_loc, const int max_val,
+                 const int blk_size, const bool isSingleBand, const uint8_t shift_bits, const int edge_clf,
+                 const uint8_t ccso_bo_only);
 void (*ccso_filter_block_hbd_wo_buf)(const uint16_t *, uint16_t *, const int, const int, const int, const int, int *,
                                      const int8_t *, const int, const int, const int, const int, const int, const int,
                                      const int *, const int, const int, const bool, const uint8_t, const int,
-                                     const uint8_t) = ccso_filter_block_hbd_wo_buf_c;
+                                     const uint8_t) = CCSO_WO_BUF;
 /* the per-plane apply functions are global in Common/Codec/EbCcso.c:297,375,455,542 but not declared in EbCcso.h */
 #define CCSO_APPLY_DECL(n)                                                                                            \
     void n(PictureControlSet *pcs, MacroblockdPlane *pd, const int plane, const uint16_t *src_y, uint16_t *dst_yuv,   \
@@ -381,40 +410,41 @@ REF_API int ref_ccso_derive_plane(const svtf_geom *g, int plane, const uint16_t 
  * leaf-level wrappers (the functions the reference's own unit tests exercise)
  * ======================================================================================= */
 /* svt_aom_[highbd_]lpf_{horizontal,vertical}_{4,6,8,14}_c — test/DeblockTest.cc:95-309 */
+/* (all leaf wrappers go through the RTCD pointers above: the `_c` kernels in libsvtref.so, the SSE2/AVX2 ones in libsvtref_simd.so) */
 REF_API void ref_lpf(void *s, int sample_bytes, int pitch, int vertical, int len, int bd, uint8_t blimit, uint8_t limit,
                      uint8_t thresh) {
     uint8_t bl[16], li[16], th[16];
     memset(bl, blimit, 16), memset(li, limit, 16), memset(th, thresh, 16);
     if (sample_bytes == 1) {
         void (*f)(uint8_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *) =
-            vertical ? (len == 4 ? svt_aom_lpf_vertical_4_c : len == 6 ? svt_aom_lpf_vertical_6_c : len == 8 ? svt_aom_lpf_vertical_8_c : svt_aom_lpf_vertical_14_c)
-                     : (len == 4 ? svt_aom_lpf_horizontal_4_c : len == 6 ? svt_aom_lpf_horizontal_6_c : len == 8 ? svt_aom_lpf_horizontal_8_c : svt_aom_lpf_horizontal_14_c);
+            vertical ? (len == 4 ? svt_aom_lpf_vertical_4 : len == 6 ? svt_aom_lpf_vertical_6 : len == 8 ? svt_aom_lpf_vertical_8 : svt_aom_lpf_vertical_14)
+                     : (len == 4 ? svt_aom_lpf_horizontal_4 : len == 6 ? svt_aom_lpf_horizontal_6 : len == 8 ? svt_aom_lpf_horizontal_8 : svt_aom_lpf_horizontal_14);
         f(s, pitch, bl, li, th);
     } else {
         void (*f)(uint16_t *, int32_t, const uint8_t *, const uint8_t *, const uint8_t *, int32_t) =
-            vertical ? (len == 4 ? svt_aom_highbd_lpf_vertical_4_c : len == 6 ? svt_aom_highbd_lpf_vertical_6_c : len == 8 ? svt_aom_highbd_lpf_vertical_8_c : svt_aom_highbd_lpf_vertical_14_c)
-                     : (len == 4 ? svt_aom_highbd_lpf_horizontal_4_c : len == 6 ? svt_aom_highbd_lpf_horizontal_6_c : len == 8 ? svt_aom_highbd_lpf_horizontal_8_c : svt_aom_highbd_lpf_horizontal_14_c);
+            vertical ? (len == 4 ? svt_aom_highbd_lpf_vertical_4 : len == 6 ? svt_aom_highbd_lpf_vertical_6 : len == 8 ? svt_aom_highbd_lpf_vertical_8 : svt_aom_highbd_lpf_vertical_14)
+                     : (len == 4 ? svt_aom_highbd_lpf_horizontal_4 : len == 6 ? svt_aom_highbd_lpf_horizontal_6 : len == 8 ? svt_aom_highbd_lpf_horizontal_8 : svt_aom_highbd_lpf_horizontal_14);
         f(s, pitch, bl, li, th, bd);
     }
 }
 /* svt_cdef_filter_block_c — test/CdefTest.cc:94-411.  `in` is inside a CDEF_BSTRIDE tile. */
 REF_API void ref_cdef_filter_block(uint16_t *dst16, int dstride, const uint16_t *in, int pri, int sec, int dir, int pri_damping,
                                    int sec_damping, int bsize, int coeff_shift, int subsampling) {
-    svt_cdef_filter_block_c(NULL, dst16, dstride, in, pri, sec, dir, pri_damping, sec_damping, bsize, coeff_shift,
+    svt_cdef_filter_block(NULL, dst16, dstride, in, pri, sec, dir, pri_damping, sec_damping, bsize, coeff_shift,
                             (uint8_t)subsampling);
 }
 REF_API int ref_cdef_bstride(void) { return CDEF_BSTRIDE; }
 /* svt_aom_cdef_find_dir_c — test/CdefTest.cc:435-665 */
 REF_API int ref_cdef_find_dir(const uint16_t *img, int stride, int32_t *var, int coeff_shift) {
-    return svt_aom_cdef_find_dir_c(img, stride, var, coeff_shift);
+    return svt_aom_cdef_find_dir(img, stride, var, coeff_shift);
 }
 /* svt_aom_compute_cdef_dist_c / _8bit_c — test/CdefTest.cc:760-980 */
 REF_API uint64_t ref_cdef_dist(const void *dst, int dstride, const void *src, const uint8_t *by, const uint8_t *bx, int count,
                                int bsize, int coeff_shift, int pli, int subsampling, int is16) {
     CdefList dl[256];
     for (int i = 0; i < count; i++) dl[i].by = by[i], dl[i].bx = bx[i];
-    return is16 ? svt_aom_compute_cdef_dist_c(dst, dstride, src, dl, count, (BlockSize)bsize, coeff_shift, pli, (uint8_t)subsampling)
-                : svt_aom_compute_cdef_dist_8bit_c(dst, dstride, src, dl, count, (BlockSize)bsize, coeff_shift, pli,
+    return is16 ? svt_compute_cdef_dist_16bit(dst, dstride, src, dl, count, (BlockSize)bsize, coeff_shift, pli, (uint8_t)subsampling)
+                : svt_compute_cdef_dist_8bit(dst, dstride, src, dl, count, (BlockSize)bsize, coeff_shift, pli,
                                                    (uint8_t)subsampling);
 }
 /* table probes used to pin svtf_pack_mi_enc: get_transform_size (Encoder/Codec/EbDeblockingFilter.c:143-160)

@@ -17,11 +17,19 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
-import svtfilt_b200 as S  # noqa: E402
-from svtfilt_b200 import _lib as L  # noqa: E402
+# SVTF_HARNESS_NO_PRODUCT=1 (set by `bench.py --impl reference`): the CPU checkers alone, in a process that neither imports the
+# product's Python package nor maps libsvtfilt_b200.so; the parameter structs then come from tests/ref_abi.py
+NO_PRODUCT = os.environ.get("SVTF_HARNESS_NO_PRODUCT") == "1"
+if NO_PRODUCT:
+    import ref_abi as S  # noqa: E402
+    L = S
+else:
+    import svtfilt_b200 as S  # noqa: E402
+    from svtfilt_b200 import _lib as L  # noqa: E402
 
 ORC_PATH = os.path.join(ROOT, "oracle", "liborc.so")
 REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libsvtref.so")
+REF_SIMD_PATH = os.path.join(ROOT, "oracle", "_ref", "libsvtref_simd.so")  # the same sources + the reference's SSE2/AVX2 kernels
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
@@ -515,10 +523,28 @@ def ref_available():
     return os.path.exists(REF_PATH)
 
 
+def cpu_has_avx2():
+    try:
+        with open("/proc/cpuinfo") as f:
+            return " avx2 " in f.read().replace("\n", " ") + " "
+    except OSError:
+        return False
+
+
+def ref_simd_available():
+    return os.path.exists(REF_SIMD_PATH) and cpu_has_avx2()
+
+
 class Ref:
-    def __init__(self):
-        self.lib = C.CDLL(REF_PATH)
+    """simd=False: oracle/_ref/libsvtref.so, RTCD pointers -> the `_c` kernels (the parity checker).
+    simd=True: oracle/_ref/libsvtref_simd.so, RTCD pointers -> the SSE2 / AVX2 kernels the reference selects on an AVX2 host
+    (the timed CPU baseline)."""
+
+    def __init__(self, simd=False):
+        self.simd = simd
+        self.lib = C.CDLL(REF_SIMD_PATH if simd else REF_PATH)
         self.lib.ref_cdef_dist.restype = C.c_uint64
+        assert self.lib.ref_is_simd() == int(simd)
 
     @staticmethod
     def _soa(soa):

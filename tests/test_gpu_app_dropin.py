@@ -1,0 +1,118 @@
+"""GPU: the drop-in dropped in.  The reference's own applications, built twice by integration/build.sh — unmodified
+(SvtAv1EncApp_ref / SvtAv1DecApp_ref) and with integration/svt_b200.patch, i.e. the filter stages replaced by
+adapters/svtf_*_adapters.c over libsvtfilt_b200.so (SvtAv1EncApp_b200 / SvtAv1DecApp_b200) — run on the same synthetic clips;
+the `-o` reconstruction AND the bitstream must be byte-identical (md5), and the adapters' call counters (SVTF_ADAPTER_STATS)
+must show that the stages really ran on the GPU.  This is the only test in which the real encoder's mode-info grid, filter
+levels (svt_av1_pick_filter_level_by_q / the full-image search) and searched CDEF strengths reach the kernels.
+
+  BASELINE configs[0]: --preset 8, 1080p 8-bit: per-superblock deblock path (Encoder/Codec/EbCodingLoop.c:2258-2281 ->
+                       svt_aom_loop_filter_sb adapter -> one frame launch), CDEF search + pick + apply
+  a preset <= 4 run:   DLF stage (Encoder/Codec/EbDlfProcess.c:99-107: full-image level search + frame deblock), segment search
+                       (EbCdefProcess.c:400-403), finish + apply (:506-516), loop-restoration search + apply
+  BASELINE configs[1]: SvtAv1DecApp on a 4K 10-bit stream (Decoder/Codec/EbDecParseObu.c:2382-2455)
+CCSO: the reference encoder never calls ccso_search / ccso_frame (the calls are commented out, EbCdefProcess.c:622-623) and
+never signals it, so neither application exercises CCSO; its parity is pinned at the function level (test_gpu_adapters.py)."""
+import hashlib
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "integration", "_bin")
+sys.path.insert(0, os.path.join(ROOT, "integration"))
+
+
+def _bin(name):
+    p = os.path.join(BIN, name)
+    if not os.path.exists(p):
+        pytest.skip(f"{p} not built (integration/build.sh needs the reference tree and cmake)")
+    return p
+
+
+def _md5(path):
+    h = hashlib.md5()
+    with open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 22), b""):
+            h.update(blk)
+    return h.hexdigest()
+
+
+def _stats(stderr_text):
+    m = re.search(r"svtfilt_b200 adapter stats:(.*)", stderr_text)
+    assert m, "the patched application printed no adapter statistics:\n" + stderr_text[-2000:]
+    return {k: int(v) for k, v in re.findall(r"(\w+)=(\d+)", m.group(1))}
+
+
+def _encode(app, clip, w, h, frames, depth, preset, out_prefix, extra=()):
+    env = dict(os.environ, SVTF_ADAPTER_STATS="1")
+    cmd = [_bin(app), "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", str(preset), "--input-depth",
+           str(depth), "-b", out_prefix + ".ivf", "-o", out_prefix + ".yuv", *extra]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return r.stderr
+
+
+def _decode(app, ivf, out):
+    env = dict(os.environ, SVTF_ADAPTER_STATS="1")
+    r = subprocess.run([_bin(app), "-i", ivf, "-o", out], capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return r.stderr
+
+
+def _clip(tmp_path, w, h, frames, depth):
+    import synth_yuv
+
+    p = str(tmp_path / f"clip_{w}x{h}_{depth}.yuv")
+    synth_yuv.write_clip(p, w, h, frames, depth)
+    return p
+
+
+def _encode_both(tmp_path, w, h, frames, depth, preset, extra=()):
+    clip = _clip(tmp_path, w, h, frames, depth)
+    _encode("SvtAv1EncApp_ref", clip, w, h, frames, depth, preset, str(tmp_path / "ref"), extra)
+    err = _encode("SvtAv1EncApp_b200", clip, w, h, frames, depth, preset, str(tmp_path / "b200"), extra)
+    assert _md5(str(tmp_path / "ref.yuv")) == _md5(str(tmp_path / "b200.yuv")), "reconstruction (-o) differs"
+    assert _md5(str(tmp_path / "ref.ivf")) == _md5(str(tmp_path / "b200.ivf")), "bitstream differs"
+    assert os.path.getsize(str(tmp_path / "ref.yuv")) == frames * w * h * 3 // 2 * (1 if depth == 8 else 2)
+    return _stats(err)
+
+
+def test_encoder_preset8_1080p_8bit_recon_and_bitstream_identical(tmp_path):
+    """BASELINE configs[0] (8 of its 60 frames; bench.py's `app` leg runs all 60)."""
+    st = _encode_both(tmp_path, 1920, 1080, 8, 8, 8)
+    assert st["loop_filter_sb_last"] >= 1 and st["loop_filter_frame"] >= 1, st  # per-SB path -> one frame launch per filtered picture
+    assert st["cdef_search_picture"] >= 1 and st["finish_cdef_search"] + st["finish_cdef_search_ref_fs"] >= 8, st
+    assert st["gpu_launches"] > 0, st
+
+
+@pytest.mark.parametrize("preset,w,h,frames", [(4, 640, 360, 6), (2, 416, 240, 5)])
+def test_encoder_low_preset_dlf_stage_and_segment_search_identical(tmp_path, preset, w, h, frames):
+    st = _encode_both(tmp_path, w, h, frames, 8, preset)
+    assert st["loop_filter_frame"] >= 1 and st["loop_filter_sb_last"] == 0, st  # DLF stage (frame call), not the per-SB path
+    assert st["pick_filter_level_full"] >= 1, st                                 # LPF_PICK_FROM_FULL_IMAGE on the GPU
+    assert st["cdef_search_picture"] >= 1 and st["finish_cdef_search"] >= 1 and st["cdef_frame"] >= 1, st
+    # the restoration apply only runs on pictures whose search kept a filter (rest kernel, Encoder/Codec/EbRestProcess.c:615-640)
+    assert st["restoration_search"] >= 1, st
+
+
+def test_encoder_10bit_identical(tmp_path):
+    st = _encode_both(tmp_path, 640, 360, 5, 10, 6)
+    assert st["loop_filter_frame"] >= 1 and st["cdef_search_picture"] >= 1, st
+
+
+def test_decoder_4k_10bit_stream_identical(tmp_path):
+    """BASELINE configs[1] on a real stream: a 4K 10-bit clip encoded by the unmodified reference encoder, decoded by both decoders."""
+    w, h, frames = 3840, 2160, 3
+    clip = _clip(tmp_path, w, h, frames, 10)
+    _encode("SvtAv1EncApp_ref", clip, w, h, frames, 10, 9, str(tmp_path / "s"))
+    _decode("SvtAv1DecApp_ref", str(tmp_path / "s.ivf"), str(tmp_path / "dec_ref.yuv"))
+    err = _decode("SvtAv1DecApp_b200", str(tmp_path / "s.ivf"), str(tmp_path / "dec_b200.yuv"))
+    assert _md5(str(tmp_path / "dec_ref.yuv")) == _md5(str(tmp_path / "dec_b200.yuv"))
+    assert _md5(str(tmp_path / "dec_ref.yuv")) == _md5(str(tmp_path / "s.yuv")), "decoder output differs from the encoder's reconstruction"
+    st = _stats(err)
+    assert st["dec_loop_filter_frame"] >= 1 and st["dec_cdef_frame"] >= 1 and st["gpu_launches"] > 0, st
