@@ -424,10 +424,20 @@ void svtf_cdef_search_picture(PictureControlSet *pcs, SequenceControlSet *scs) {
     CHECK(svtf_cdef_search_frame(s->ctx, &cfg, mse, pcs->skip_cdef_seg, dir, var), s->ctx);
     memcpy(pcs->mse_seg[0], mse, sizeof(uint64_t) * 64 * (size_t)nfb);
     memcpy(pcs->mse_seg[1], mse + (size_t)64 * nfb, sizeof(uint64_t) * 64 * (size_t)nfb);
-    for (int fb = 0; fb < nfb; fb++)
-        for (int b = 0; b < 64; b++) {
-            pcs->cdef_dir_data[fb].dir[b >> 3][b & 7] = dir[fb * 64 + b];
-            pcs->cdef_dir_data[fb].var[b >> 3][b & 7] = var[fb * 64 + b];
+    /* directions / variances: the 16x16 CdefDirData of a 128-wide / 128-high coding block belongs to its first quadrant */
+    const int nhfb = (s->geom.mi_cols + 15) / 16, nvfb = (s->geom.mi_rows + 15) / 16;
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++) {
+            const BlockSize bs = pcs->mi_grid_base[16 * fbr * pcs->mi_stride + 16 * fbc]->mbmi.block_mi.bsize;
+            const int       dc = (fbc & 1) && (bs == BLOCK_128X128 || bs == BLOCK_128X64);
+            const int       dr = (fbr & 1) && (bs == BLOCK_128X128 || bs == BLOCK_64X128);
+            const int       fb = fbr * nhfb + fbc, ofb = (fbr - dr) * nhfb + fbc - dc;
+            for (int b = 0; b < 64; b++) {
+                if ((dr || dc) && !dir[fb * 64 + b] && !var[fb * 64 + b])
+                    continue; /* a block the search did not list: the first quadrant's array keeps what it had */
+                pcs->cdef_dir_data[ofb].dir[(b >> 3) + 8 * dr][(b & 7) + 8 * dc] = dir[fb * 64 + b];
+                pcs->cdef_dir_data[ofb].var[(b >> 3) + 8 * dr][(b & 7) + 8 * dc] = var[fb * 64 + b];
+            }
         }
     free(mse), free(dir), free(var);
 }

@@ -240,12 +240,22 @@ REF_API int ref_cdef_search_frame(const svtf_geom *g, void *ry, int rsy, void *r
     memcpy(mse + (size_t)64 * nfb, h.pcs->mse_seg[1], sizeof(uint64_t) * 64 * nfb);
     if (skip)
         memcpy(skip, h.pcs->skip_cdef_seg, nfb);
-    if (dir)
-        for (int fb = 0; fb < nfb; fb++)
-            for (int b = 0; b < 64; b++) {
-                dir[fb * 64 + b] = h.pcs->cdef_dir_data[fb].dir[b >> 3][b & 7];
-                var[fb * 64 + b] = h.pcs->cdef_dir_data[fb].var[b >> 3][b & 7];
+    if (dir) {
+        /* per filter block, its own 8x8 grid.  A 128-wide / 128-high coding block is searched as one filter block whose CdefDirData
+         * (16x16 entries) belongs to its first quadrant (EbCdefProcess.c:186-211): read the other quadrants' entries from there. */
+        const int nhfb = (g->mi_cols + 15) / 16, nvfb = (g->mi_rows + 15) / 16;
+        for (int fbr = 0; fbr < nvfb; fbr++)
+            for (int fbc = 0; fbc < nhfb; fbc++) {
+                const BlockSize bs  = h.mi[16 * fbr * soa->mi_stride + 16 * fbc].mbmi.block_mi.bsize;
+                const int       dc  = (fbc & 1) && (bs == BLOCK_128X128 || bs == BLOCK_128X64);
+                const int       dr  = (fbr & 1) && (bs == BLOCK_128X128 || bs == BLOCK_64X128);
+                const int       fb  = fbr * nhfb + fbc, ofb = (fbr - dr) * nhfb + fbc - dc;
+                for (int b = 0; b < 64; b++) {
+                    dir[fb * 64 + b] = h.pcs->cdef_dir_data[ofb].dir[(b >> 3) + 8 * dr][(b & 7) + 8 * dc];
+                    var[fb * 64 + b] = h.pcs->cdef_dir_data[ofb].var[(b >> 3) + 8 * dr][(b & 7) + 8 * dc];
+                }
             }
+    }
     harness_free(&h);
     return 0;
 }

@@ -94,6 +94,7 @@ struct svtf_ctx {
     bool   popen = false;
     size_t plo = 0, phi = 0;
     uint64_t    *d_mse = nullptr;  // [2][nfb][64]
+    unsigned long long *d_mse_raw = nullptr; // [3][nfb][64] raw sums of 128-wide / 128-high coding blocks (svtf_search.cuh), then [nfb] flags
     uint8_t     *d_skip = nullptr; // [nfb]
     uint8_t     *d_dir = nullptr;  // [nfb][64]
     int32_t     *d_var = nullptr;  // [nfb][64]
@@ -216,6 +217,8 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
         if ((e = cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
     if ((e = cudaMalloc(&c->d_mse, sizeof(uint64_t) * 2 * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(mse)");
+    if ((e = cudaMalloc(&c->d_mse_raw, (sizeof(unsigned long long) * 3 * 64 + sizeof(unsigned)) * (size_t)c->max_nfb)) != cudaSuccess)
+        return bail(e, "cudaMalloc(mse raw)");
     if ((e = cudaMalloc(&c->d_skip, c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(skip)");
     if ((e = cudaMalloc(&c->d_dir, 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(dir)");
     if ((e = cudaMalloc(&c->d_var, sizeof(int32_t) * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(var)");
@@ -240,7 +243,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
         if (sl.h) cudaFreeHost(sl.h);
         if (sl.ev) cudaEventDestroy(sl.ev);
     }
-    cudaFree(c->d_mse), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
+    cudaFree(c->d_mse), cudaFree(c->d_mse_raw), cudaFree(c->d_skip), cudaFree(c->d_dir), cudaFree(c->d_var);
     derive_scratch_free(c->derive_scratch);
     cudaFree(c->d_pick_state), cudaFree(c->d_pick_tot), cudaFree(c->d_pick_idx), cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
     cudaFree(c->d_sb_lvl), cudaFree(c->d_mi_soa), cudaFree(c->d_lr_units), cudaFree(c->d_handoff), cudaFree(c->d_lrs), cudaFree(c->d_lrs_flt);
@@ -976,7 +979,9 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
     const int fbr0 = c->own_lo / 64;
     dim3      grid(nhfb, (c->own_hi + 63) / 64 - fbr0);
     (void)nvfb;
+#ifdef SVTF_AB_KERNELS
     static const bool use_v1 = getenv("SVTF_CDEF_SCALAR") != nullptr; // A/B switch: the round-1 scalar kernel
+    static const bool use_v2 = getenv("SVTF_CDEF_V2") != nullptr;     // A/B switch: the round-1b kernel
     if (use_v1 && !cc) {
         CdefArgs a;
         a.in = c->surf[c->cur].planes(), a.out = c->surf[nxt].planes();
@@ -987,7 +992,9 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
             cdef_kernel<uint8_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
         else
             cdef_kernel<uint16_t><<<grid, CDEF_THREADS, 0, c->stream>>>(a);
-    } else {
+    } else
+#endif
+    {
         Cdef2Args b;
         b.in = c->surf[c->cur].planes(), b.out = c->surf[nxt].planes();
         b.mi = c->d_mi, b.mi_stride = c->mi_stride, b.d = dims_of(c->geom), b.fb_idx = c->d_fb_idx, b.fbr0 = fbr0, b.damping = cp->cdef_damping;
@@ -996,14 +1003,15 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
         memset(&b.ccso, 0, sizeof(b.ccso));
         if (cc)
             ccso_fill(c, cc, blk_flags, b.ccso);
-        // A/B switches: SVTF_CDEF_V2 = the round-1b kernel, SVTF_CDEF_INT = cdef3 with packed-integer taps at every bit depth
-        static const bool use_v2 = getenv("SVTF_CDEF_V2") != nullptr, force_int = getenv("SVTF_CDEF_INT") != nullptr;
+#ifdef SVTF_AB_KERNELS
         if (use_v2) {
             if (c->geom.sample_bytes == 1)
                 cdef2_kernel<uint8_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
             else
                 cdef2_kernel<uint16_t><<<grid, C2_THREADS, 0, c->stream>>>(b);
-        } else {
+        } else
+#endif
+        {
             constexpr int smem_i = C3_SMEM_WORDS_I * 4, smem_f = C3_SMEM_WORDS_F * 4;
             if (!c->cdef3_ready) {
                 CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
@@ -1012,7 +1020,9 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
                 CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
                 c->cdef3_ready = true;
             }
-            // fp16 taps are exact for samples < 1024 and luma damping + (bit_depth - 8) <= 9 (svtf_cdef3.cuh)
+            // fp16 taps are exact for samples < 1024 and luma damping + (bit_depth - 8) <= 9 (svtf_cdef3.cuh); otherwise (12-bit pictures,
+            // or SVTF_CDEF_INT=1 to force it) the packed-integer taps
+            static const bool force_int = getenv("SVTF_CDEF_INT") != nullptr;
             const bool fp = !force_int && c->geom.bit_depth <= 10 && cp->cdef_damping + (c->geom.bit_depth - 8) <= 9;
             if (c->geom.sample_bytes == 1) {
                 if (fp)
@@ -1109,7 +1119,7 @@ extern "C" int svtf_filter_chain(svtf_ctx *c, const svtf_lf_params *lf, const sv
     if (!c->have_frame)
         return c->fail(SVTF_E_STATE, "svtf_filter_chain: no picture uploaded");
     int r = SVTF_OK;
-    static const bool unfused = getenv("SVTF_CHAIN_UNFUSED") != nullptr || getenv("SVTF_CDEF_SCALAR") != nullptr;
+    static const bool unfused = getenv("SVTF_CHAIN_UNFUSED") != nullptr;
     const bool        ccso_on = ccso && (ccso->ccso_enable[0] | ccso->ccso_enable[1] | ccso->ccso_enable[2]);
     if (ccso && (r = ccso_check(c, ccso, "svtf_filter_chain")) != SVTF_OK)
         return r;
@@ -1187,6 +1197,11 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
     a.mse = c->d_mse, a.skip = c->d_skip, a.dir = c->d_dir, a.var = c->d_var;
     a.nfb  = nfb;
     a.fbr0 = c->own_lo / 64;
+    a.raw  = c->d_mse_raw;
+    a.fold = reinterpret_cast<unsigned *>(c->d_mse_raw + (size_t)3 * 64 * nfb);
+    a.fbr_par = (c->glob_row0 / 64) & 1;
+    CUDA_TRY(c, cudaMemsetAsync(c->d_mse_raw, 0, (sizeof(unsigned long long) * 3 * 64 + sizeof(unsigned)) * (size_t)nfb, c->stream));
+    CUDA_TRY(c, cudaMemsetAsync(c->d_skip, 0, (size_t)nfb, c->stream)); // quadrants folded into a 128 block are never written (as in the reference)
     CUDA_TRY(c, cudaMemsetAsync(c->d_dir, 0, 64 * (size_t)nfb, c->stream));
     CUDA_TRY(c, cudaMemsetAsync(c->d_var, 0, sizeof(int32_t) * 64 * (size_t)nfb, c->stream));
     CUDA_TRY(c, cudaMemsetAsync(c->d_mse, 0, sizeof(uint64_t) * 128 * (size_t)nfb, c->stream));
@@ -1207,13 +1222,16 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
             if (a.fs_uv[gi] != -1)
                 b.present_uv |= 1ull << (a.fs[gi] & 63);
         }
+#ifdef SVTF_AB_KERNELS
         static const bool use_v2 = getenv("SVTF_SEARCH_V2") != nullptr; // A/B switch: packed-integer taps (svtf_search2.cuh)
         if (use_v2) {
             if (c->geom.sample_bytes == 1)
                 cdef_search2_kernel<uint8_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
             else
                 cdef_search2_kernel<uint16_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
-        } else { // fp16 taps (svtf_search3.cuh); search damping = 3 + (base_q_idx >> 6) <= 6, inside the exactness bound
+        } else
+#endif
+        { // fp16 taps (svtf_search3.cuh); search damping = 3 + (base_q_idx >> 6) <= 6, inside the exactness bound
             constexpr int smem = S3_SMEM_WORDS * 4;
             if (!c->search3_ready) {
                 CUDA_TRY(c, cudaFuncSetAttribute(cdef_search3_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -1228,6 +1246,13 @@ extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *c
     }
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
+    {
+        SearchArgs f = a;
+        f.fbr0       = 0;
+        search_fold_kernel<<<nfb, 64, 0, c->stream>>>(f); // rows of 128-wide / 128-high coding blocks (returns at once where there are none)
+        CUDA_TRY(c, cudaGetLastError());
+        c->launches++;
+    }
     c->have_search = true;
     // outputs are WHOLE-PICTURE arrays; this context fills the filter-block rows it owns
     const size_t l0 = (size_t)a.fbr0 * nhfb, ln = (size_t)grid.y * nhfb;           // local first fb, count

@@ -265,6 +265,7 @@ __device__ __forceinline__ int ccso2_px(const uint16_t *lum16, const int pitch16
     return min(max(v + (int)q.lut[(band << 4) + (c0 << 2) + c1] - 128, 0), (int)(q.maxv2 & 0xffff));
 }
 
+#ifdef SVTF_AB_KERNELS // superseded kernel, kept for A/B measurements only (not in the product build)
 template <typename T>
 // (C2_THREADS, 4) = 64 registers with 28 bytes of spills was measured: no gain (106 vs 105 us at 4K), occupancy is not the limiter
 __global__ void __launch_bounds__(C2_THREADS, 3) cdef2_kernel(const __grid_constant__ Cdef2Args a) {
@@ -474,5 +475,6 @@ __global__ void __launch_bounds__(C2_THREADS, 3) cdef2_kernel(const __grid_const
         }
     }
 }
+#endif // SVTF_AB_KERNELS
 
 } // namespace svtf

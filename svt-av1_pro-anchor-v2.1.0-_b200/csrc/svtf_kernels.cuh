@@ -508,6 +508,7 @@ __device__ __forceinline__ void cdef_stage(uint16_t *tile, const int pitch, cons
 // svt_av1_cdef_frame — Encoder/Codec/EbEncCdef.c:284-612 + svt_cdef_filter_fb Common/Codec/EbCdef.c:339-430
 // (== decoder svt_cdef_frame, Decoder/Codec/EbDecCdef.c:507).  Out of place: every tap reads the
 // pre-CDEF picture, which is what the reference's line/column buffers emulate.
+#ifdef SVTF_AB_KERNELS // superseded kernel, kept for A/B measurements only (not in the product build)
 template <typename T>
 __global__ void __launch_bounds__(CDEF_THREADS) cdef_kernel(const __grid_constant__ CdefArgs a) {
     __shared__ __align__(16) uint16_t ytile[CDEF_YROWS * CDEF_YP];
@@ -677,6 +678,7 @@ __global__ void __launch_bounds__(CDEF_THREADS) cdef_kernel(const __grid_constan
         }
     }
 }
+#endif // SVTF_AB_KERNELS
 
 // =================================================================================================
 // CCSO apply

@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_sums_kernel(const __grid_cons
     }
 }
 
+#ifdef SVTF_AB_KERNELS // superseded kernel, kept for A/B measurements only (not in the product build)
 template <typename T, int WIN>
 __global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_constant__ LrsArgs a) {
     constexpr int WIN2 = WIN * WIN, HW = WIN / 2, NB = WIN * (WIN + 1) / 2, G = 32 / NB, NACC = WIN2 * WIN2 + WIN2;
@@ -148,6 +149,7 @@ __global__ void __launch_bounds__(LRS_THREADS) lrs_stats_kernel(const __grid_con
         if (s_acc[i])
             atomicAdd(reinterpret_cast<unsigned long long *>(out + i), (unsigned long long)s_acc[i]);
 }
+#endif // SVTF_AB_KERNELS
 
 // ---- statistics, second form: one product image per window-offset DIFFERENCE --------------------------------------------
 // H[(c1,r1),(c2,r2)] = sum over the tile of d(p + o1) d(p + o2) depends on o1 and on delta = o2 - o1 only: with

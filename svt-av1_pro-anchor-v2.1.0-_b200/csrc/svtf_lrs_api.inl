@@ -212,8 +212,12 @@ int lrs_measure(svtf_ctx *c, LrsPlan &plan, const bool stats_of[3], const unsign
             LrsArgs b = a;
             b.tiles   = a.tiles + t0;
             const int n = t1 - t0;
+#ifdef SVTF_AB_KERNELS
             static const bool v1 = std::getenv("SVTF_LRS_STATS_V1") != nullptr;
 #define LRS_LAUNCH(T, W) (v1 ? lrs_stats_kernel<T, W><<<n, LRS_THREADS, 0, c->stream>>>(b) : lrs_stats2_kernel<T, W><<<n, LRS_THREADS, 0, c->stream>>>(b))
+#else
+#define LRS_LAUNCH(T, W) (lrs_stats2_kernel<T, W><<<n, LRS_THREADS, 0, c->stream>>>(b))
+#endif
             if (pl.win == 7)
                 b8 ? LRS_LAUNCH(uint8_t, 7) : LRS_LAUNCH(uint16_t, 7);
             else if (pl.win == 5)

@@ -33,7 +33,58 @@ struct SearchArgs {
     int32_t         *var;  // [nfb][64]
     int              nfb;
     int              fbr0; // first filter-block row of the launch (stripe window)
+    // 128-wide / 128-high coding blocks (sb_size 128): the reference searches such a block as ONE filter block whose table row
+    // belongs to its first 64x64 quadrant (Encoder/Codec/EbCdefProcess.c:186-203).  Quadrant CTAs add their raw sums here and
+    // search_fold_kernel turns them into the first quadrant's row afterwards (the >> 2*coeff_shift comes after the sum over the
+    // whole block, so per-quadrant rows cannot simply be added for 10/12-bit pictures).
+    unsigned long long *raw;  // [3][nfb][64] raw sums (Y, U, V) per first quadrant, zero on entry
+    unsigned           *fold; // [nfb] bit 0: first quadrant of a folded block; bit 1: some 8x8 block of it is not skipped; zero on entry
+    int                 fbr_par; // parity of the picture's filter-block row of local row 0 (stripes)
 };
+
+// Which filter block carries the table row of filter block (fbr, fbc)?  `folded`: it lies in a 128-wide / 128-high coding block.
+struct SearchFold {
+    bool folded;
+    int  ofb; // the block's first quadrant (== fb when !folded)
+};
+__device__ __forceinline__ SearchFold search_fold(const SearchArgs &a, const int fbr, const int fbc, const int nhfb) {
+    const svtf_mi_t m  = __ldg(a.mi + (size_t)(fbr * 16) * a.mi_stride + fbc * 16);
+    const bool      w5 = mi_bdim(m, 0) == 5, h5 = mi_bdim(m, 1) == 5; // log2(128) - 2
+    SearchFold      f;
+    f.folded      = w5 || h5;
+    const int ofr = h5 && ((fbr + a.fbr_par) & 1) ? fbr - 1 : fbr, ofc = w5 && (fbc & 1) ? fbc - 1 : fbc;
+    f.ofb         = max(ofr, 0) * nhfb + ofc;
+    return f;
+}
+// One table entry of one filter block: plain store, or the raw sums added to the folded block's first quadrant.
+__device__ __forceinline__ void search_store(const SearchArgs &a, const int fb, const SearchFold &f, const int gi, const unsigned long long y,
+                                             const unsigned long long u, const unsigned long long v, const int cs) {
+    if (f.folded) {
+        atomicAdd(&a.raw[((size_t)0 * a.nfb + f.ofb) * 64 + gi], y);
+        atomicAdd(&a.raw[((size_t)1 * a.nfb + f.ofb) * 64 + gi], u);
+        atomicAdd(&a.raw[((size_t)2 * a.nfb + f.ofb) * 64 + gi], v);
+        return;
+    }
+    const int sub = min(a.subsampling, 4);
+    a.mse[(size_t)fb * 64 + gi]             = (y >> (2 * cs)) * (unsigned long long)sub;
+    a.mse[((size_t)a.nfb + fb) * 64 + gi] = a.fs_uv[gi] == -1 ? 1040400ull * 64 : (u >> (2 * cs)) + (v >> (2 * cs));
+}
+// After the search kernel: rows and skip flags of the folded blocks' first quadrants.  One CTA of 64 threads per filter block.
+__global__ void __launch_bounds__(64) search_fold_kernel(const __grid_constant__ SearchArgs a) {
+    const int      fb = blockIdx.x, gi = threadIdx.x;
+    const unsigned fl = a.fold[fb];
+    if (!(fl & 1u))
+        return;
+    if (gi == 0)
+        a.skip[fb] = (fl & 2u) ? 0 : 1;
+    if (!(fl & 2u) || gi >= a.n) // nothing to filter in the whole block: the row stays zero (EbCdefProcess.c:203-207)
+        return;
+    const int cs = a.d.bit_depth - 8, sub = min(a.subsampling, 4);
+    a.mse[(size_t)fb * 64 + gi] = (a.raw[((size_t)0 * a.nfb + fb) * 64 + gi] >> (2 * cs)) * (unsigned long long)sub;
+    a.mse[((size_t)a.nfb + fb) * 64 + gi] =
+        a.fs_uv[gi] == -1 ? 1040400ull * 64
+                          : (a.raw[((size_t)1 * a.nfb + fb) * 64 + gi] >> (2 * cs)) + (a.raw[((size_t)2 * a.nfb + fb) * 64 + gi] >> (2 * cs));
+}
 
 // dist_8xn_16bit_c / dist_8xn_8bit_c — Encoder/Codec/EbEncCdef.c:23-48, :76-101
 __device__ __forceinline__ unsigned long long cdef_dist_8x8(unsigned long long sum_s, unsigned long long sum_d,
@@ -73,14 +124,16 @@ __global__ void __launch_bounds__(SEARCH_THREADS) cdef_search_kernel(const __gri
         s_active[tid] = (uint8_t)act;
     }
     for (int i = tid; i < 3 * SVTF_TOTAL_STRENGTHS; i += SEARCH_THREADS) (&s_acc[0][0])[i] = 0;
-    const int any_active = __syncthreads_or(act);
-    if (!any_active) { // skip_cdef_seg = 1 (EbCdefProcess.c:203-207); mse rows stay zero
-        if (tid == 0)
-            a.skip[fb] = 1;
-        return;
+    const int        any_active = __syncthreads_or(act);
+    const SearchFold fold       = search_fold(a, fbr, fbc, gridDim.x);
+    if (tid == 0) {
+        if (fold.folded)
+            atomicOr(&a.fold[fold.ofb], any_active ? 3u : 1u);
+        else
+            a.skip[fb] = any_active ? 0 : 1;
     }
-    if (tid == 0)
-        a.skip[fb] = 0;
+    if (!any_active) // skip_cdef_seg = 1 (EbCdefProcess.c:203-207); mse rows stay zero
+        return;
 
     cdef_stage<T>(ytile, CDEF_YP, CDEF_YROWS, 34, static_cast<const T *>(a.rec.p[0]), a.rec.pitch[0], x0, y0, cw, ch, tid);
     cdef_stage<T>(ctile[0], CDEF_CP, CDEF_CROWS, 18, static_cast<const T *>(a.rec.p[1]), a.rec.pitch[1], x0 / 2, y0 / 2, cw / 2, ch / 2, tid);
@@ -228,12 +281,8 @@ __global__ void __launch_bounds__(SEARCH_THREADS) cdef_search_kernel(const __gri
     __syncthreads();
     // mse_seg[0][fb][gi] = (sum >> 2cs) * sub ; mse_seg[1][fb][gi] = U + V (EbCdefProcess.c:297-300),
     // masked chroma strengths -> default_mse_uv * 64 (:86,:258-261)
-    if (tid < a.n) {
-        const int sub = min(a.subsampling, 4);
-        a.mse[(size_t)fb * 64 + tid] = (s_acc[0][tid] >> (2 * cs)) * (unsigned long long)sub;
-        a.mse[((size_t)a.nfb + fb) * 64 + tid] =
-            a.fs_uv[tid] == -1 ? 1040400ull * 64 : (s_acc[1][tid] >> (2 * cs)) + (s_acc[2][tid] >> (2 * cs));
-    }
+    if (tid < a.n)
+        search_store(a, fb, fold, tid, s_acc[0][tid], s_acc[1][tid], s_acc[2][tid], cs);
 }
 
 } // namespace svtf

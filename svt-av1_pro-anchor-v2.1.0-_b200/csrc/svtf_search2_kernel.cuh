@@ -71,6 +71,7 @@ __device__ __forceinline__ void s2_chroma(const Search2Args &a, const int p, con
     }
 }
 
+#ifdef SVTF_AB_KERNELS // superseded kernel, kept for A/B measurements only (not in the product build)
 template <typename T>
 __global__ void __launch_bounds__(S2_THREADS, 2) cdef_search2_kernel(const __grid_constant__ Search2Args a) {
     __shared__ __align__(16) uint32_t yA[C2_YROWS * C2_YPW], yB[C2_YROWS * C2_YPW];
@@ -170,5 +171,6 @@ __global__ void __launch_bounds__(S2_THREADS, 2) cdef_search2_kernel(const __gri
             a.s.fs_uv[tid] == -1 ? 1040400ull * 64 : (s_acc[1][f] >> (2 * cs)) + (s_acc[2][f] >> (2 * cs));
     }
 }
+#endif // SVTF_AB_KERNELS
 
 } // namespace svtf

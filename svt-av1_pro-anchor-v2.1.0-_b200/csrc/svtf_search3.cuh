@@ -321,14 +321,16 @@ __global__ void __launch_bounds__(S2_THREADS, 2) cdef_search3_kernel(const __gri
         s_off[pt][dd][k] = make_int2((odd ? bd : 0) + dy * pw + ((dx - odd) >> 1), (odd ? bd : 0) - dy * pw + ((-dx - odd) >> 1));
     }
     for (int i = tid; i < 3 * 64; i += S2_THREADS) (&s_acc[0][0])[i] = 0;
-    const int any_active = __syncthreads_or(act);
-    if (!any_active) { // skip_cdef_seg = 1 (EbCdefProcess.c:203-207); mse rows stay zero
-        if (tid == 0)
-            a.s.skip[fb] = 1;
-        return;
+    const int        any_active = __syncthreads_or(act);
+    const SearchFold fold       = search_fold(a.s, fbr, fbc, gridDim.x);
+    if (tid == 0) {
+        if (fold.folded) // part of a 128-wide / 128-high coding block: the first quadrant's row carries the whole block
+            atomicOr(&a.s.fold[fold.ofb], any_active ? 3u : 1u);
+        else
+            a.s.skip[fb] = any_active ? 0 : 1;
     }
-    if (tid == 0)
-        a.s.skip[fb] = 0;
+    if (!any_active) // skip_cdef_seg = 1 (EbCdefProcess.c:203-207); mse rows stay zero
+        return;
 
     {
         C3Chunk ky[3], kc[2];
@@ -396,11 +398,8 @@ __global__ void __launch_bounds__(S2_THREADS, 2) cdef_search3_kernel(const __gri
     // mse_seg[0][fb][gi] = (sum >> 2cs) * sub ; mse_seg[1][fb][gi] = U + V (EbCdefProcess.c:297-300),
     // masked chroma strengths -> default_mse_uv * 64 (:86,:258-261)
     if (tid < a.s.n) {
-        const int sub = min(a.s.subsampling, 4);
-        const int f   = a.s.fs[tid];
-        a.s.mse[(size_t)fb * 64 + tid] = (s_acc[0][f] >> (2 * cs)) * (unsigned long long)sub;
-        a.s.mse[((size_t)a.s.nfb + fb) * 64 + tid] =
-            a.s.fs_uv[tid] == -1 ? 1040400ull * 64 : (s_acc[1][f] >> (2 * cs)) + (s_acc[2][f] >> (2 * cs));
+        const int f = a.s.fs[tid];
+        search_store(a.s, fb, fold, tid, s_acc[0][f], s_acc[1][f], s_acc[2][f], cs);
     }
 }
 

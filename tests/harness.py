@@ -89,10 +89,9 @@ def synth_source(geom, recon, seed, amp=8):
             for r in recon]
 
 
-def synth_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=False):
-    """Valid AV1 partition of every 64x64 superblock (NONE / SPLIT / HORZ / VERT / HORZ_4 / VERT_4), with a
-    uniform tx_depth, skip, ref_frame, mode and segment per block.  Returns a dict of (mi_rows, mi_cols)
-    uint8 arrays."""
+def synth_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=False, sb_size=64):
+    """Valid AV1 partition of every 64x64 (or, sb_size=128, 128x128) superblock (NONE / SPLIT / HORZ / VERT / HORZ_4 / VERT_4),
+    with a uniform tx_depth, skip, ref_frame, mode and segment per block.  Returns a dict of (mi_rows, mi_cols) uint8 arrays."""
     rng = np.random.default_rng(seed)
     R, Cc = geom.mi_rows, geom.mi_cols
     soa = {k: np.zeros((R, Cc), dtype=np.uint8) for k in ("bsize", "tx_depth", "skip", "ref_frame0", "mode", "segment_id")}
@@ -124,7 +123,7 @@ def synth_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=
                 for dr, dc in ((0, 0), (0, h // 4), (h // 4, 0), (h // 4, h // 4)):
                     part(r + dr, c + dc, h)
         else:
-            k = rng.integers(0, 4 if s >= 16 else 2)
+            k = rng.integers(0, 4 if 16 <= s <= 64 else 2)  # no 4:1 partitions of 8x8 or 128x128
             if k == 0:  # HORZ
                 put(r, c, s, s // 2), put(r + s // 8, c, s, s // 2)
             elif k == 1:  # VERT
@@ -136,9 +135,9 @@ def synth_mode_info(geom, seed, p_split=0.55, p_skip=0.3, p_inter=0.7, segments=
                 for i in range(4):
                     put(r, c + i * s // 16, s // 4, s)
 
-    for r in range(0, R, 16):
-        for c in range(0, Cc, 16):
-            part(r, c, 64)
+    for r in range(0, R, sb_size // 4):
+        for c in range(0, Cc, sb_size // 4):
+            part(r, c, sb_size)
     return soa
 
 

@@ -90,7 +90,7 @@ def test_encoder_preset8_1080p_8bit_recon_and_bitstream_identical(tmp_path):
     assert st["gpu_launches"] > 0, st
 
 
-@pytest.mark.parametrize("preset,w,h,frames", [(4, 640, 360, 6), (2, 416, 240, 5)])
+@pytest.mark.parametrize("preset,w,h,frames", [(4, 640, 360, 6), (2, 416, 240, 5), (1, 512, 384, 3)])  # preset 1: 128x128 superblocks
 def test_encoder_low_preset_dlf_stage_and_segment_search_identical(tmp_path, preset, w, h, frames):
     st = _encode_both(tmp_path, w, h, frames, 8, preset)
     assert st["loop_filter_frame"] >= 1 and st["loop_filter_sb_last"] == 0, st  # DLF stage (frame call), not the per-SB path
