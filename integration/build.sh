@@ -20,11 +20,14 @@ if [ ! -x "$HERE/_bin/SvtAv1EncApp_ref" ] || [ "${FORCE:-0}" = 1 ]; then
   cp "$B/ref/bin/SvtAv1DecApp" "$HERE/_bin/SvtAv1DecApp_ref"
 fi
 
-# patched copy: only the directories the build needs
-rm -rf "$B/src_b200"
-mkdir -p "$B/src_b200"
-for t in CMakeLists.txt Source cmake third_party Config; do cp -r "$REF/$t" "$B/src_b200/"; done
-patch -s -p1 -d "$B/src_b200" < "$HERE/svt_b200.patch"
+# patched copy: only the directories the build needs; re-created only when the patch changed (keeps the ninja build incremental)
+if [ ! -f "$B/src_b200/.patched" ] || [ "$HERE/svt_b200.patch" -nt "$B/src_b200/.patched" ]; then
+  rm -rf "$B/src_b200"
+  mkdir -p "$B/src_b200"
+  for t in CMakeLists.txt Source cmake third_party Config; do cp -rp "$REF/$t" "$B/src_b200/"; done
+  patch -s -p1 -d "$B/src_b200" < "$HERE/svt_b200.patch"
+  touch "$B/src_b200/.patched"
+fi
 cmake "${COMMON[@]}" -S "$B/src_b200" -B "$B/b200" -DSVT_B200_FILTERS=ON -DSVTFILT_DIR="$ROOT" -DCMAKE_OUTPUT_DIRECTORY="$B/b200/bin/" > "$B/b200_cmake.log" 2>&1
 ninja -C "$B/b200" > "$B/b200_ninja.log" 2>&1
 cp "$B/b200/bin/SvtAv1EncApp" "$HERE/_bin/SvtAv1EncApp_b200"
