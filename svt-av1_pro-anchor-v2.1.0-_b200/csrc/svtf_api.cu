@@ -23,6 +23,7 @@
 #include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
 #include "svtf_cdef3.cuh"
+#include "svtf_cdef4.cuh"
 #include "svtf_search3.cuh"
 #include "svtf_mi_pack.cuh"
 #include "svtf_lr.cuh"
@@ -126,6 +127,8 @@ struct svtf_ctx {
     size_t       handoff_cap = 0;
     bool         search3_ready = false;    // same for cdef_search3_kernel
     bool         cdef3_ready = false;      // dynamic shared-memory opt-in of cdef3_kernel done on this device
+    unsigned    *d_sched = nullptr;        // tile scheduler of the persistent kernels: {next tile, CTAs done}, zero between launches
+    int          cdef4_ctas_per_sm[4] = {0, 0, 0, 0}; // cdef4_kernel<u8/u16, int/fp16>: resident CTAs per SM (0 = not set up yet)
     std::string  err;
 
     int fail(int code, const std::string &m) {
@@ -224,6 +227,8 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
     if ((e = cudaMalloc(&c->d_var, sizeof(int32_t) * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(var)");
     if ((e = cudaMalloc(&c->d_pick_state, sizeof(PickState))) != cudaSuccess) return bail(e, "cudaMalloc(pick state)");
     if ((e = cudaMalloc(&c->d_pick_tot, sizeof(uint64_t) * 64 * 64)) != cudaSuccess) return bail(e, "cudaMalloc(pick tot)");
+    if ((e = cudaMalloc(&c->d_sched, 64)) != cudaSuccess) return bail(e, "cudaMalloc(sched)");
+    if ((e = cudaMemset(c->d_sched, 0, 64)) != cudaSuccess) return bail(e, "cudaMemset(sched)");
     cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
     *out = c;
     return SVTF_OK;
@@ -238,7 +243,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     for (int i = 0; i < 4; i++)
         for (int p = 0; p < 3; p++) cudaFree(c->surf[i].base[p]);
     for (int p = 0; p < 3; p++) cudaFree(c->source.base[p]);
-    cudaFree(c->d_mi), cudaFree(c->d_params);
+    cudaFree(c->d_mi), cudaFree(c->d_params), cudaFree(c->d_sched);
     for (auto &sl : c->pslot) {
         if (sl.h) cudaFreeHost(sl.h);
         if (sl.ev) cudaEventDestroy(sl.ev);
@@ -957,6 +962,73 @@ static int fb_idx_check(svtf_ctx *c, const int8_t *fb_strength_idx) {
     return SVTF_OK;
 }
 
+// ---- cdef4_kernel: persistent CTAs fed by TMA (svtf_cdef4.cuh) ---------------------------------------------------------------
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (the library does not link libcuda).
+typedef CUresult (*svtf_encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                         const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static svtf_encode_tiled_fn encode_tiled_fn() {
+    static svtf_encode_tiled_fn fn = [] {
+        void                           *p = nullptr;
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<svtf_encode_tiled_fn>(p);
+    }();
+    return fn;
+}
+// Tensor map of one plane: dims = the coded plane (TMA zero-fills what a box reads beyond it), box = one staged tile.
+static int plane_tensor_map(svtf_ctx *c, CUtensorMap *tm, void *base, int pitch, int w, int h, int box_w, int box_h) {
+    svtf_encode_tiled_fn enc = encode_tiled_fn();
+    if (!enc)
+        return c->fail(SVTF_E_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    const size_t     sb = c->geom.sample_bytes;
+    const cuuint64_t dims[2] = {(cuuint64_t)w, (cuuint64_t)h}, strides[1] = {(cuuint64_t)pitch * sb};
+    const cuuint32_t box[2] = {(cuuint32_t)box_w, (cuuint32_t)box_h}, es[2] = {1, 1};
+    const CUresult   r = enc(tm, sb == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, base, dims, strides, box, es,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char msg[96];
+        snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+        return c->fail(SVTF_E_CUDA, msg);
+    }
+    return SVTF_OK;
+}
+template <typename T, bool FP>
+static int cdef4_launch_t(svtf_ctx *c, const Cdef4Args &g, int which) {
+    constexpr int smem = c4_smem_bytes<T, FP>();
+    if (!c->cdef4_ctas_per_sm[which]) {
+        CUDA_TRY(c, cudaFuncSetAttribute(cdef4_kernel<T, FP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_TRY(c, cudaFuncSetAttribute(cdef4_kernel<T, FP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        int n = 0;
+        CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cdef4_kernel<T, FP>, C2_THREADS, smem));
+        c->cdef4_ctas_per_sm[which] = std::max(n, 1);
+    }
+    // one CTA per SM slot; tiles beyond the first of each CTA are drawn from a counter
+    const int ctas = std::min(g.ntiles, std::max(1, c->sm_count) * c->cdef4_ctas_per_sm[which]);
+    cdef4_kernel<T, FP><<<ctas, C2_THREADS, smem, c->stream>>>(g);
+    return SVTF_OK;
+}
+static int cdef4_launch(svtf_ctx *c, const Cdef2Args &b, bool fp, int nhfb, int nvfb_launch) {
+    Cdef4Args g;
+    g.c      = b;
+    g.nhfb   = nhfb;
+    g.ntiles = nhfb * nvfb_launch;
+    g.sched  = c->d_sched;
+    if (g.ntiles <= 0)
+        return SVTF_OK;
+    const Planes in = b.in;
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        if (int r = plane_tensor_map(c, &g.tm[p], in.p[p], in.pitch[p], (c->geom.mi_cols * 4) >> ss, (c->geom.mi_rows * 4) >> ss,
+                                     c->geom.sample_bytes == 1 ? (p ? C4Raw<uint8_t>::C_W : C4Raw<uint8_t>::Y_W) : (p ? C4Raw<uint16_t>::C_W : C4Raw<uint16_t>::Y_W),
+                                     p ? C4_CBOX_H : C4_YBOX_H))
+            return r;
+    }
+    if (c->geom.sample_bytes == 1)
+        return fp ? cdef4_launch_t<uint8_t, true>(c, g, 0) : cdef4_launch_t<uint8_t, false>(c, g, 1);
+    return fp ? cdef4_launch_t<uint16_t, true>(c, g, 2) : cdef4_launch_t<uint16_t, false>(c, g, 3);
+}
+
 // CDEF apply; with `cc` the CCSO pass of the same picture runs in the kernel's epilogue (one launch, one write).
 static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t *fb_strength_idx, const svtf_ccso_params *cc,
                            const uint8_t *const blk_flags[3], const char *who, bool staged) {
@@ -1012,29 +1084,36 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
         } else
 #endif
         {
-            constexpr int smem_i = C3_SMEM_WORDS_I * 4, smem_f = C3_SMEM_WORDS_F * 4;
-            if (!c->cdef3_ready) {
-                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
-                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
-                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
-                CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
-                c->cdef3_ready = true;
-            }
             // fp16 taps are exact for samples < 1024 and luma damping + (bit_depth - 8) <= 9 (svtf_cdef3.cuh); otherwise (12-bit pictures,
             // or SVTF_CDEF_INT=1 to force it) the packed-integer taps
             static const bool force_int = getenv("SVTF_CDEF_INT") != nullptr;
             const bool fp = !force_int && c->geom.bit_depth <= 10 && cp->cdef_damping + (c->geom.bit_depth - 8) <= 9;
-            if (c->geom.sample_bytes == 1) {
-                if (fp)
-                    cdef3_kernel<uint8_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
-                else
-                    cdef3_kernel<uint8_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
-            } else {
-                if (fp)
-                    cdef3_kernel<uint16_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
-                else
-                    cdef3_kernel<uint16_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
-            }
+            // SVTF_CDEF_TMA=1: cdef4_kernel (svtf_cdef4.cuh) — the same arithmetic in persistent CTAs fed by TMA.  Measured SLOWER than
+            // cdef3 on the 4K 10-bit workload (95 vs 86 us alone), so it is not the default; kept selectable and parity-tested.
+            static const bool use_tma = getenv("SVTF_CDEF_TMA") != nullptr;
+            if (!use_tma) {
+                constexpr int smem_i = C3_SMEM_WORDS_I * 4, smem_f = C3_SMEM_WORDS_F * 4;
+                if (!c->cdef3_ready) {
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
+                    c->cdef3_ready = true;
+                }
+                if (c->geom.sample_bytes == 1) {
+                    if (fp)
+                        cdef3_kernel<uint8_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
+                    else
+                        cdef3_kernel<uint8_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
+                } else {
+                    if (fp)
+                        cdef3_kernel<uint16_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
+                    else
+                        cdef3_kernel<uint16_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
+                }
+            } else
+            if (int r = cdef4_launch(c, b, fp, (int)grid.x, (int)grid.y))
+                return r;
         }
     }
     CUDA_TRY(c, cudaGetLastError());
