@@ -20,6 +20,7 @@
 #include "svtf_search.cuh"
 #include "svtf_search2_kernel.cuh"
 #include "svtf_pick.cuh"
+#include "svtf_pick2.cuh"
 #include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
 #include "svtf_cdef3.cuh"
@@ -108,6 +109,7 @@ struct svtf_ctx {
     uint8_t     *d_tab_skip = nullptr;
     int          pick_cap = 0, tab_cap = 0;
     int          sm_count = 0;
+    size_t       max_smem_optin = 0;
     LrUnitDev   *d_lr_units = nullptr;   // restoration units of the three planes (svtf_lr_apply_frame)
     size_t       lr_units_cap = 0;
     int         *h_mi_bad = nullptr;     // pinned: "invalid enum" flag of the last svtf_set_mi_soa_*
@@ -1364,11 +1366,30 @@ static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint6
     PickArgs a;
     a.mse = d_mse, a.skip = d_skip, a.nfb = nfb, a.end_gi = end_gi, a.bias = cfg->zero_fs_cost_bias;
     a.st = c->d_pick_state, a.tot = c->d_pick_tot;
-    CUDA_TRY(c, pick_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->sm_count, c->stream, &c->launches));
+    // The 75 dependent svt_search_one_dual passes: one launch per pass, enqueued back to back (svtf_pick.cuh).  SVTF_PICK_CLUSTER=1: ONE
+    // launch, a 16-CTA cluster stays resident for all passes (svtf_pick2.cuh; measured slower in throughput, see its header) when the table
+    // fits its shared memory and is narrow (every entry < 2^31; the kernel reports wide == 2 otherwise and the per-pass form runs).
+    static const bool per_pass = getenv("SVTF_PICK_CLUSTER") == nullptr;
+    if (!c->max_smem_optin) {
+        int v = 0;
+        CUDA_TRY(c, cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
+        c->max_smem_optin = (size_t)v;
+    }
     PickState st;
-    CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    bool      done = false;
+    if (!per_pass && pick2_fits(nfb, c->max_smem_optin)) {
+        CUDA_TRY(c, pick2_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
+        CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        done = st.wide != 2;
+    }
+    if (!done) {
+        CUDA_TRY(c, pick_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->sm_count, c->stream, &c->launches));
+        CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    }
     memset(out, 0, sizeof(*out));
     out->cdef_bits = st.best_bits;
     auto map = [&](int i) { // index -> strength byte through the luma lists (Encoder/Codec/EbEncCdef.c:911-919)
