@@ -433,6 +433,34 @@ typedef struct svtf_superres_params {
 } svtf_superres_params;
 int svtf_superres_upscale_frame(svtf_ctx *ctx, const svtf_superres_params *sr);
 
+/* ---- one picture across several GPUs (BASELINE configs[3]: an 8K picture split by superblock-row stripes) ----------------
+ * One context per GPU in stripe mode (svtf_stripe_begin), one process or thread per context.  The two inter-GPU steps of the path run
+ * device to device over NVLink through NCCL (bound at run time from libnccl.so.2; SVTF_E_STATE when it cannot be loaded) and never touch
+ * host memory.  They stand in for what the reference does inside one address space: its deblock / CDEF segment threads read each other's
+ * rows of the same recon picture, and finish_cdef_search joins the segments' mse_seg rows under cdef_search_mutex
+ * (Encoder/Codec/EbCdefProcess.c:406, :730). */
+typedef struct svtf_comm svtf_comm;
+/* ncclGetUniqueId on one rank; the caller distributes the 128 bytes to the others (any transport). */
+int  svtf_comm_unique_id(void *id128);
+/* ncclCommInitRank: collective over the nranks callers.  device = this rank's CUDA device. */
+int  svtf_comm_create(int device, int nranks, int rank, const void *id128, svtf_comm **out);
+void svtf_comm_destroy(svtf_comm *comm);
+/* A picture that reaches the GPUs already split: only the rows the stripe OWNS (no halo) of the whole-picture arrays are copied. */
+int svtf_upload_frame_own(svtf_ctx *ctx, const void *y, int32_t stride_y, const void *cb, int32_t stride_cb, const void *cr, int32_t stride_cr);
+int svtf_set_mi_own(svtf_ctx *ctx, const svtf_mi_t *mi, int32_t mi_stride);
+/* Halo exchange of the current picture with the stripes above / below (rank_up / rank_down; -1 where the stripe touches the picture
+ * edge): the 8 luma / 4 chroma input rows and the 2 mode-info rows on either side of each interior boundary go to the neighbour's halo
+ * rows and the neighbour's come here — what every later stage of the stripe reads beyond its own rows (the boundary deblock edge reads
+ * <= 7 and writes <= 6 rows per side, Common/Codec/EbDeblockingCommon.c:787-823; CDEF taps reach 2 rows, Common/Codec/EbCdef.c:99-120).
+ * Stream-ordered on the context's stream; all ranks of the picture must call it (it is a grouped ncclSend / ncclRecv). */
+int svtf_stripe_exchange(svtf_ctx *ctx, svtf_comm *comm, int32_t rank_up, int32_t rank_down);
+/* finish_cdef_search (Encoder/Codec/EbEncCdef.c:728) of a picture whose stripes were searched on different GPUs (svtf_cdef_search_frame on
+ * each striped context, host outputs NULL): every rank's filter-block rows of mse / skip are gathered from device table to device table
+ * (ragged all-gather = one NCCL group of broadcasts), then every rank runs the same pick on its device.  first_sb_row / num_sb_rows:
+ * the stripe of every rank ([nranks]); fb_strength_idx: WHOLE-picture array (nfb entries); identical results on all ranks. */
+int svtf_cdef_search_gather_pick(svtf_ctx *ctx, svtf_comm *comm, const svtf_cdef_search_cfg *cfg, const int32_t *first_sb_row,
+                                 const int32_t *num_sb_rows, svtf_cdef_params *out_params, int8_t *fb_strength_idx);
+
 /* ---- device-side access for multi-GPU stripe exchange and device-resident benches ----------- */
 typedef struct svtf_dev_plane {
     void   *ptr;   /* device pointer to sample (0,0) */

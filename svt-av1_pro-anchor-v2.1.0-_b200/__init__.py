@@ -6,9 +6,9 @@ The directory name is not a Python identifier; import it as ``svtfilt_b200`` (th
 the repository root registers this package under that name).
 """
 from . import _lib, stripes
-from .filters import (FilterContext, PinnedArray, PinnedPicture, SvtfError, ccso_params, cdef_params, cdef_pick_host, cdef_search_cfg,
+from .filters import (Comm, FilterContext, PinnedArray, PinnedPicture, SvtfError, ccso_params, cdef_params, cdef_pick_host, cdef_search_cfg,
                       lf_params, make_geom, make_geom_coded, pack_mi_dec, pack_mi_enc, wiener_from_stats)
 from .stripes import StripeFilter
 
-__all__ = ["FilterContext", "PinnedArray", "PinnedPicture", "SvtfError", "ccso_params", "cdef_params", "cdef_pick_host", "cdef_search_cfg",
+__all__ = ["Comm", "FilterContext", "PinnedArray", "PinnedPicture", "SvtfError", "ccso_params", "cdef_params", "cdef_pick_host", "cdef_search_cfg",
            "lf_params", "make_geom", "make_geom_coded", "pack_mi_dec", "pack_mi_enc", "wiener_from_stats", "StripeFilter", "stripes", "_lib"]

@@ -106,7 +106,7 @@ EXPORTS = [
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
     "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
-    "svtf_cdef_pick_table_noalloc", "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
+    "svtf_cdef_pick_table_noalloc", "svtf_comm_unique_id", "svtf_comm_create", "svtf_comm_destroy", "svtf_upload_frame_own", "svtf_set_mi_own", "svtf_stripe_exchange", "svtf_cdef_search_gather_pick", "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
 ]
 
 _lib = None
@@ -163,6 +163,14 @@ def load():
     lib.svtf_cdef_pick.argtypes = [vp, C.POINTER(CdefSearchCfg), C.POINTER(CdefParams), vp]
     lib.svtf_cdef_pick_table.argtypes = [vp, C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]
     lib.svtf_cdef_pick_table_noalloc.argtypes = [vp, C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]
+    lib.svtf_comm_unique_id.argtypes = [vp]
+    lib.svtf_comm_create.argtypes = [C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp)]
+    lib.svtf_comm_destroy.argtypes = [vp]
+    lib.svtf_comm_destroy.restype = None
+    lib.svtf_upload_frame_own.argtypes = [vp, vp, i32, vp, i32, vp, i32]
+    lib.svtf_set_mi_own.argtypes = [vp, vp, i32]
+    lib.svtf_stripe_exchange.argtypes = [vp, vp, i32, i32]
+    lib.svtf_cdef_search_gather_pick.argtypes = [vp, vp, C.POINTER(CdefSearchCfg), vp, vp, C.POINTER(CdefParams), vp]
     lib.svtf_cdef_pick_host.argtypes = [C.POINTER(CdefSearchCfg), vp, vp, i32, C.POINTER(CdefParams), vp]
     lib.svtf_dev_planes.argtypes = [vp, C.c_int, C.POINTER(DevPlane)]
     lib.svtf_cuda_stream.argtypes = [vp]

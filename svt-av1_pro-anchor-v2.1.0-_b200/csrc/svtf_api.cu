@@ -1967,4 +1967,5 @@ extern "C" int svtf_lf_search_frame(svtf_ctx *c, const svtf_lf_params *start, co
     return SVTF_OK;
 }
 
+#include "svtf_multi_api.inl"   // one picture across several GPUs: NCCL halo exchange and search-table gather
 #include "svtf_noalloc_api.inl" // svtf_cdef_pick_table_noalloc: the pick on a static device scratch array (no allocation)

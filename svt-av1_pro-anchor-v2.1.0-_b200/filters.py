@@ -149,6 +149,33 @@ def wiener_from_stats(win, M, H):
     return r, tuple(vf), tuple(hf)
 
 
+class Comm:
+    """svtf_comm: an NCCL communicator owned by the library (svtf_comm_create).  `unique_id()` on one rank, the 128 bytes go to the
+    others by any transport (torch.distributed broadcast, a pipe, ...), then every rank constructs Comm(device, nranks, rank, id)."""
+
+    @staticmethod
+    def unique_id():
+        lib = L.load()
+        buf = C.create_string_buffer(128)
+        r = lib.svtf_comm_unique_id(buf)
+        if r:
+            raise SvtfError(r, lib.svtf_last_error(None).decode())
+        return buf.raw
+
+    def __init__(self, device, nranks, rank, uid):
+        self._lib = L.load()
+        h = C.c_void_p()
+        r = self._lib.svtf_comm_create(device, nranks, rank, uid, C.byref(h))
+        if r:
+            raise SvtfError(r, self._lib.svtf_last_error(None).decode())
+        self.handle, self.nranks, self.rank = h, nranks, rank
+
+    def close(self):
+        if self.handle:
+            self._lib.svtf_comm_destroy(self.handle)
+            self.handle = None
+
+
 class PinnedPicture:
     """Three planes in page-locked host memory (svtf_host_alloc), exposed as numpy arrays."""
 
@@ -468,6 +495,28 @@ class FilterContext:
         out = L.CdefParams()
         idx = np.empty(skip.size, dtype=np.int8)
         self._chk(self._lib.svtf_cdef_pick_table(self._h, C.byref(cfg), _ptr(mse), _ptr(skip), skip.size, C.byref(out), _ptr(idx)))
+        return out, idx
+
+    def upload_own(self, planes):
+        """svtf_upload_frame_own: only the rows this (striped) context owns."""
+        self._chk(self._lib.svtf_upload_frame_own(self._h, *self._planes_args(planes)))
+
+    def set_mi_own(self, mi):
+        mi = np.ascontiguousarray(mi, dtype=np.uint32)
+        self._keep_mi = mi
+        self._chk(self._lib.svtf_set_mi_own(self._h, _ptr(mi), mi.shape[1]))
+
+    def stripe_exchange(self, comm, rank_up, rank_down):
+        """svtf_stripe_exchange: halo rows to / from the neighbouring stripes' GPUs (NCCL send / recv)."""
+        self._chk(self._lib.svtf_stripe_exchange(self._h, comm.handle, rank_up, rank_down))
+
+    def search_gather_pick(self, comm, cfg, parts, nfb_full):
+        """svtf_cdef_search_gather_pick: device-to-device gather of every rank's mse / skip rows, then the pick."""
+        first = np.ascontiguousarray([p[0] for p in parts], dtype=np.int32)
+        count = np.ascontiguousarray([p[1] for p in parts], dtype=np.int32)
+        out = L.CdefParams()
+        idx = np.empty(nfb_full, dtype=np.int8)
+        self._chk(self._lib.svtf_cdef_search_gather_pick(self._h, comm.handle, C.byref(cfg), _ptr(first), _ptr(count), C.byref(out), _ptr(idx)))
         return out, idx
 
     def pick_table_noalloc(self, cfg, mse, skip):
