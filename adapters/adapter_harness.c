@@ -548,3 +548,109 @@ API int adapt_pad_ref(const svtf_geom *g, void *pad[3], const int pst[3], uint8_
     harness_free(&h);
     return 0;
 }
+
+/* ---- the whole chain through the reference's own entry points on ONE long-lived PictureControlSet (bench.py's end-to-end leg) ----
+ * adapt_chain_open builds the structures once: the recon picture is an ordinary malloc'ed (pageable) EbPictureBufferDesc allocation of
+ * the harness, the mode info a real pointer grid (ModeInfo behind mi_grid_base), the frame header carries the loop-filter levels, the
+ * CDEF strengths (+ per-block indices in mbmi.cdef_strength) and the CCSO parameters (+ block flags in mbmi.ccso_blk_*).
+ * adapt_chain_run = what the pipeline's DLF and CDEF stages call for one picture:
+ *     svt_av1_loop_filter_frame(recon, pcs, 0, 3); svt_av1_cdef_frame(scs, pcs); ccso_frame(recon, pcs, pd, ext_rec_y);
+ * with the adapters in resident mode (one upload, one download).  adapt_chain_load copies a fresh reconstruction into the picture
+ * (what EncDec would have left there); adapt_chain_planes exposes the picture for checking. */
+typedef struct {
+    harness   h;
+    svtf_geom g;
+    uint8_t  *plane[3];
+    int       stride[3], rows[3];
+} chain_handle;
+
+API void *adapt_chain_open(const svtf_geom *g, const ref_mi_soa *soa, const svtf_lf_params *lf, const svtf_cdef_params *cp, const int8_t *fb_strength_idx,
+                           const svtf_ccso_params *cc, const uint8_t *const blk_flags[3]) {
+    chain_handle *c = calloc(1, sizeof(*c));
+    if (!c)
+        return NULL;
+    c->g = *g;
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        c->stride[p] = ((g->mi_cols * 4) >> ss) + 64; /* a stride that is NOT the device pitch: a 2-D copy, like a padded recon picture */
+        c->rows[p]   = (g->mi_rows * 4) >> ss;
+        c->plane[p]  = malloc((size_t)c->stride[p] * c->rows[p] * g->sample_bytes);
+        if (!c->plane[p])
+            return NULL;
+    }
+    if (harness_init(&c->h, g, soa, c->plane[0], c->stride[0], c->plane[1], c->stride[1], c->plane[2], c->stride[2]))
+        return NULL;
+    c->h.recon->height = (uint16_t)g->height; /* allocation rows = coded rows (org_y = 0): what pin_picture sizes the lock by */
+    fill_lf(&c->h, lf);
+    FrameHeader *fh              = &c->h.ppcs->frm_hdr;
+    fh->cdef_params.cdef_damping = (uint8_t)cp->cdef_damping;
+    fh->cdef_params.cdef_bits    = (uint8_t)cp->cdef_bits;
+    for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++) {
+        fh->cdef_params.cdef_y_strength[i]  = cp->cdef_y_strength[i];
+        fh->cdef_params.cdef_uv_strength[i] = cp->cdef_uv_strength[i];
+    }
+    const int nvfb = (g->mi_rows + 15) / 16, nhfb = (g->mi_cols + 15) / 16;
+    for (int fbr = 0; fbr < nvfb; fbr++)
+        for (int fbc = 0; fbc < nhfb; fbc++) {
+            const int8_t idx = fb_strength_idx[fbr * nhfb + fbc];
+            c->h.mi[16 * fbr * soa->mi_stride + 16 * fbc].mbmi.cdef_strength = idx < 0 ? 0 : idx;
+        }
+    CcsoInfo *ci = &fh->ccso_info;
+    for (int p = 0; p < 3; p++) {
+        ci->ccso_enable[p] = cc->ccso_enable[p], ci->ccso_bo_only[p] = cc->ccso_bo_only[p], ci->quant_idx[p] = cc->quant_idx[p];
+        ci->ext_filter_support[p] = cc->ext_filter_support[p], ci->edge_clf[p] = cc->edge_clf[p];
+        ci->max_band_log2[p] = cc->max_band_log2[p];
+        memcpy(ci->filter_offset[p], cc->filter_offset[p], SVTF_CCSO_LUT_SIZE);
+        const int pw = g->width >> (p ? 1 : 0), ph = g->height >> (p ? 1 : 0), bl = p ? 7 : 8;
+        const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
+        for (int by = 0; by < nby; by++)
+            for (int bx = 0; bx < nbx; bx++) {
+                const int   f = (blk_flags && blk_flags[p]) ? blk_flags[p][by * nbx + bx] : 1;
+                MbModeInfo *m = &c->h.mi[64 * by * soa->mi_stride + 64 * bx].mbmi;
+                if (p == 0) m->ccso_blk_y = f;
+                if (p == 1) m->ccso_blk_u = f;
+                if (p == 2) m->ccso_blk_v = f;
+            }
+    }
+    return c;
+}
+
+API void adapt_chain_load(void *handle, const void *y, int sy, const void *cb, int scb, const void *cr, int scr) {
+    chain_handle *c      = handle;
+    const void   *src[3] = {y, cb, cr};
+    const int     st[3]  = {sy, scb, scr};
+    const int     sb     = c->g.sample_bytes;
+    for (int p = 0; p < 3; p++) {
+        const int w = (c->g.mi_cols * 4) >> (p ? 1 : 0);
+        for (int r = 0; r < c->rows[p]; r++)
+            memcpy(c->plane[p] + (size_t)r * c->stride[p] * sb, (const uint8_t *)src[p] + (size_t)r * st[p] * sb, (size_t)w * sb);
+    }
+}
+
+API void adapt_chain_run(void *handle) {
+    chain_handle           *c = handle;
+    struct MacroblockdPlane pd[3];
+    memset(pd, 0, sizeof(pd));
+    svt_av1_loop_filter_frame(c->h.recon, c->h.pcs, 0, 3);
+    svt_av1_cdef_frame(c->h.scs, c->h.pcs);
+    ccso_frame(c->h.recon, c->h.pcs, pd, NULL); /* resident chain: the classifier luma is the pre-CDEF surface on the device */
+}
+
+API void adapt_chain_planes(void *handle, void *out[3], int stride[3]) {
+    chain_handle *c = handle;
+    for (int p = 0; p < 3; p++) out[p] = c->plane[p], stride[p] = c->stride[p];
+}
+
+API void adapt_chain_close(void *handle) {
+    chain_handle *c = handle;
+    svtf_adapter_release(c->h.pcs);
+    harness_free(&c->h);
+    for (int p = 0; p < 3; p++) free(c->plane[p]);
+    free(c);
+}
+
+API void adapt_set_modes(int resident, int pin, int mi_threads) {
+    svtf_adapter_set_resident(resident);
+    svtf_adapter_set_pin_pictures(pin);
+    svtf_adapter_set_mi_threads(mi_threads);
+}

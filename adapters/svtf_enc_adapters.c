@@ -49,14 +49,24 @@ typedef struct {
     svtf_geom                geom, max_geom;
     int                      resident; /* picture of this pcs currently on the device */
     uint64_t                 launches_seen;
+    uint8_t                 *mi_stage;   /* pinned staging of the six side-info byte planes (svtf_host_alloc), reused per picture */
+    size_t                   mi_stage_cap;
+    int8_t                  *idx_stage;  /* per-filter-block strength indices handed to svtf_cdef_apply_frame */
+    size_t                   idx_cap;
+    void                    *reg[8];     /* host ranges this slot page-locked (svtf_adapter_set_pin_pictures) */
+    int                      nreg;
 } CtxSlot;
 static CtxSlot         g_slots[SVTF_MAX_CACHED];
 static pthread_mutex_t g_lock     = PTHREAD_MUTEX_INITIALIZER;
 static int             g_device   = 0;
 static int             g_resident = 0;
+static int             g_pin      = 0;
+static int             g_mi_threads = 8;
 
 void svtf_adapter_set_device(int device) { g_device = device; }
 void svtf_adapter_set_resident(int on) { g_resident = on; }
+void svtf_adapter_set_pin_pictures(int on) { g_pin = on; }
+void svtf_adapter_set_mi_threads(int n) { g_mi_threads = n < 1 ? 1 : (n > 32 ? 32 : n); }
 
 static void die(const char *where, svtf_ctx *ctx) {
     fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: %s failed: %s (no CPU fallback on this path)\n", where,
@@ -114,6 +124,19 @@ static svtf_geom geom_of(const PictureControlSet *pcs) {
     return g;
 }
 
+/* Frees everything a slot owns (context, staging, page-locks).  g_lock held. */
+static void slot_teardown(CtxSlot *s) {
+    if (s->ctx) {
+        g_stat_launches += (unsigned long)svtf_launch_count(s->ctx) - s->launches_seen;
+        svtf_ctx_destroy(s->ctx);
+    }
+    if (s->mi_stage)
+        svtf_host_free(s->mi_stage);
+    free(s->idx_stage);
+    for (int i = 0; i < s->nreg; i++) svtf_host_unregister(s->reg[i]);
+    memset(s, 0, sizeof(*s));
+}
+
 /* Geometry a context must hold for this picture (room for the super-resolution upscale included). */
 static svtf_geom max_geom_of(const PictureControlSet *pcs, const svtf_geom *g) {
     svtf_geom        mg = *g;
@@ -141,9 +164,7 @@ static CtxSlot *slot_for(const PictureControlSet *pcs) {
             free_slot = &g_slots[i];
     }
     if (s && (mg.mi_cols > s->max_geom.mi_cols || mg.mi_rows > s->max_geom.mi_rows || mg.sample_bytes != s->max_geom.sample_bytes)) {
-        g_stat_launches += (unsigned long)svtf_launch_count(s->ctx) - s->launches_seen;
-        svtf_ctx_destroy(s->ctx); /* the picture no longer fits: rebuild */
-        memset(s, 0, sizeof(*s));
+        slot_teardown(s); /* the picture no longer fits: rebuild */
         free_slot = s, s = NULL;
     }
     if (!s) {
@@ -169,35 +190,86 @@ static CtxSlot *slot_for(const PictureControlSet *pcs) {
 void svtf_adapter_release(const PictureControlSet *pcs) {
     pthread_mutex_lock(&g_lock);
     for (int i = 0; i < SVTF_MAX_CACHED; i++)
-        if (g_slots[i].pcs == pcs) {
-            g_stat_launches += (unsigned long)svtf_launch_count(g_slots[i].ctx) - g_slots[i].launches_seen;
-            svtf_ctx_destroy(g_slots[i].ctx);
-            memset(&g_slots[i], 0, sizeof(g_slots[i]));
-        }
+        if (g_slots[i].pcs == pcs)
+            slot_teardown(&g_slots[i]);
     pthread_mutex_unlock(&g_lock);
 }
 
-/* mi_grid_base -> packed words (the fields set_lpf_parameters and svt_sb_compute_cdef_list read:
- * EbDeblockingFilter.c:187-260, EbEncCdef.c:267-270). */
+/* mi_grid_base -> six byte planes (the fields set_lpf_parameters and svt_sb_compute_cdef_list read: EbDeblockingFilter.c:187-260,
+ * EbEncCdef.c:267-270), gathered by a few threads into the slot's PINNED staging block and sent with one asynchronous DMA per plane;
+ * the words are packed on the device (svtf_set_mi_soa_enc).  No allocation and no synchronisation per picture: the staging block is
+ * reused, and it is not rewritten before the picture's final download has drained the stream.  (An encoder that keeps these six
+ * planes next to mi_grid_base — written where EncDec updates the mode info of a block — passes them directly and this pass disappears.) */
+typedef struct {
+    const PictureControlSet *pcs;
+    uint8_t                 *soa;
+    int                      rows, cols, r0, r1;
+} MiGatherJob;
+static void *mi_gather_rows(void *arg) {
+    const MiGatherJob *j = (const MiGatherJob *)arg;
+    const size_t       n = (size_t)j->rows * j->cols;
+    uint8_t *bsize = j->soa, *txd = j->soa + n, *skip = j->soa + 2 * n, *ref0 = j->soa + 3 * n, *mode = j->soa + 4 * n, *seg = j->soa + 5 * n;
+    for (int r = j->r0; r < j->r1; r++) {
+        ModeInfo *const *row = j->pcs->mi_grid_base + (size_t)r * j->pcs->mi_stride;
+        const size_t     o   = (size_t)r * j->cols;
+        for (int c = 0; c < j->cols; c++) {
+            const BlockModeInfoEnc *b = &row[c]->mbmi.block_mi;
+            bsize[o + c] = (uint8_t)b->bsize, txd[o + c] = b->tx_depth, skip[o + c] = b->skip;
+            ref0[o + c] = (uint8_t)b->ref_frame[0], mode[o + c] = (uint8_t)b->mode, seg[o + c] = (uint8_t)b->segment_id;
+        }
+    }
+    return NULL;
+}
 static void send_mi(CtxSlot *s, const PictureControlSet *pcs) {
     const int    rows = s->geom.mi_rows, cols = s->geom.mi_cols;
     const size_t n    = (size_t)rows * cols;
-    uint8_t     *soa  = (uint8_t *)malloc(6 * n);
-    if (!soa)
-        die("malloc(mi)", s->ctx);
-    uint8_t *bsize = soa, *txd = soa + n, *skip = soa + 2 * n, *ref0 = soa + 3 * n, *mode = soa + 4 * n, *seg = soa + 5 * n;
-    for (int r = 0; r < rows; r++)
-        for (int c = 0; c < cols; c++) {
-            const BlockModeInfoEnc *b = &pcs->mi_grid_base[r * pcs->mi_stride + c]->mbmi.block_mi;
-            const size_t            i = (size_t)r * cols + c;
-            bsize[i] = (uint8_t)b->bsize, txd[i] = b->tx_depth, skip[i] = b->skip;
-            ref0[i] = (uint8_t)b->ref_frame[0], mode[i] = (uint8_t)b->mode, seg[i] = (uint8_t)b->segment_id;
-        }
-    /* byte planes up, packed on the device (an encoder that keeps these six planes next to mi_grid_base — written where
-     * EncDec updates the mode info of a block — passes them here directly and this loop disappears) */
-    CHECK(svtf_set_mi_soa_enc(s->ctx, bsize, txd, skip, ref0, mode, seg, cols), s->ctx);
-    CHECK(svtf_sync(s->ctx), s->ctx); /* soa is freed below */
-    free(soa);
+    if (s->mi_stage_cap < 6 * n) {
+        if (s->mi_stage)
+            svtf_host_free(s->mi_stage);
+        s->mi_stage     = (uint8_t *)svtf_host_alloc(6 * n);
+        s->mi_stage_cap = s->mi_stage ? 6 * n : 0;
+        if (!s->mi_stage)
+            die("svtf_host_alloc(mi staging)", s->ctx);
+    }
+    uint8_t *soa = s->mi_stage;
+    int      nt  = g_mi_threads;
+    if (rows < 64 * nt)
+        nt = rows / 64 > 0 ? rows / 64 : 1; /* small pictures: a thread per >= 64 rows */
+    MiGatherJob job[32];
+    pthread_t   th[32];
+    for (int t = 0; t < nt; t++) {
+        job[t].pcs = pcs, job[t].soa = soa, job[t].rows = rows, job[t].cols = cols;
+        job[t].r0 = (int)((long)rows * t / nt), job[t].r1 = (int)((long)rows * (t + 1) / nt);
+    }
+    int created[32] = {0};
+    for (int t = 1; t < nt; t++) created[t] = pthread_create(&th[t], NULL, mi_gather_rows, &job[t]) == 0;
+    mi_gather_rows(&job[0]);
+    for (int t = 1; t < nt; t++) {
+        if (created[t])
+            pthread_join(th[t], NULL);
+        else
+            mi_gather_rows(&job[t]); /* could not start the thread: do its rows here */
+    }
+    CHECK(svtf_set_mi_soa_enc(s->ctx, soa, soa + n, soa + 2 * n, soa + 3 * n, soa + 4 * n, soa + 5 * n, cols), s->ctx);
+}
+
+/* svtf_adapter_set_pin_pictures(1): page-lock the picture's plane allocations in place on first sight (the recon pictures of the
+ * encoder live in a long-lived pool), so that the upload and the download are direct DMA.  Unlocked when the slot is torn down. */
+static void pin_picture(CtxSlot *s, const EbPictureBufferDesc *pic, int sb) {
+    if (!g_pin)
+        return;
+    const int vis = pic->height > s->geom.mi_rows * 4 ? pic->height : s->geom.mi_rows * 4; /* the copies cover the coded rows */
+    const int ph  = vis + 2 * pic->org_y; /* rows of the allocation; chroma: half */
+    void     *base[3] = {pic->buffer_y, pic->buffer_cb, pic->buffer_cr};
+    size_t    len[3]  = {(size_t)pic->stride_y * ph * sb, (size_t)pic->stride_cb * ((ph + 1) >> 1) * sb, (size_t)pic->stride_cr * ((ph + 1) >> 1) * sb};
+    for (int p = 0; p < 3; p++) {
+        int seen = 0;
+        for (int i = 0; i < s->nreg; i++) seen |= s->reg[i] == base[p];
+        if (seen || !base[p] || s->nreg >= 8)
+            continue;
+        if (svtf_host_register(base[p], len[p]) == SVTF_OK)
+            s->reg[s->nreg++] = base[p];
+    }
 }
 
 static void plane_ptrs(const EbPictureBufferDesc *pic, int sb, void *p[3], int32_t st[3]) {
@@ -214,9 +286,10 @@ static void begin_picture(CtxSlot *s, const PictureControlSet *pcs, const EbPict
     void   *p[3];
     int32_t st[3];
     plane_ptrs(pic, s->geom.sample_bytes, p, st);
+    pin_picture(s, pic, s->geom.sample_bytes);
     CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
-    CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
-    send_mi(s, pcs);
+    CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx); /* asynchronous from page-locked memory */
+    send_mi(s, pcs);                                                                /* gathers while the picture is on its way */
     s->resident = 1;
 }
 
@@ -374,16 +447,21 @@ void svt_av1_cdef_frame(SequenceControlSet *scs, PictureControlSet *pcs) {
     for (int i = 0; i < CDEF_MAX_STRENGTHS && i < SVTF_CDEF_MAX_STRENGTHS; i++)
         p.cdef_y_strength[i] = cp->cdef_y_strength[i], p.cdef_uv_strength[i] = cp->cdef_uv_strength[i];
     const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
-    int8_t   *idx = (int8_t *)malloc(nfb);
+    if (s->idx_cap < (size_t)nfb) {
+        free(s->idx_stage);
+        s->idx_stage = (int8_t *)malloc(nfb);
+        s->idx_cap   = s->idx_stage ? (size_t)nfb : 0;
+        if (!s->idx_stage)
+            die("malloc(cdef indices)", s->ctx);
+    }
+    int8_t *idx = s->idx_stage;
     fb_indices(pcs, &s->geom, idx);
     /* the reference reads a stale index for all-skip fbs and then skips them; clamp it into range */
     for (int i = 0; i < nfb; i++)
         if (idx[i] >= (1 << p.cdef_bits) || idx[i] < 0)
             idx[i] = 0;
     begin_picture(s, pcs, recon);
-    CHECK(svtf_cdef_apply_frame(s->ctx, &p, idx), s->ctx);
-    CHECK(svtf_sync(s->ctx), s->ctx);
-    free(idx);
+    CHECK(svtf_cdef_apply_frame(s->ctx, &p, idx), s->ctx); /* copies the indices into its own staging: nothing to wait for */
     if (!g_resident)
         end_picture(s, recon), s->resident = 0;
 }

@@ -162,6 +162,12 @@ uint64_t svtf_launch_count(const svtf_ctx *ctx);
 void *svtf_host_alloc(size_t bytes);
 void  svtf_host_free(void *p);
 
+/* Page-lock a caller-owned buffer in place (cudaHostRegister; already-registered buffers are accepted): the recon pictures of an
+ * encoder / decoder live in long-lived pools (EbPictureBufferDesc allocations), so registering each once makes every later
+ * svtf_upload_frame / svtf_download_frame on it a direct DMA instead of a staged pageable copy. */
+int svtf_host_register(void *p, size_t bytes);
+int svtf_host_unregister(void *p);
+
 /* Start a picture: sets the geometry (must fit max_geom) and resets the surface chain. */
 int svtf_frame_begin(svtf_ctx *ctx, const svtf_geom *geom);
 

@@ -47,6 +47,12 @@ void svtf_adapter_set_device(int device);
  * intermediate download/upload); ccso_frame (or svtf_adapter_fetch) brings it back.  0 (default): every entry
  * point uploads and downloads, i.e. each is a stand-alone drop-in. */
 void svtf_adapter_set_resident(int on);
+/* 1: page-lock (svtf_host_register) the plane allocations of the pictures the adapters see, once per allocation — the recon pictures
+ * of the encoder live in a long-lived pool — so uploads and downloads are direct DMA.  Only for callers whose picture buffers outlive
+ * the adapter's slot for that pcs (svtf_adapter_release unlocks them).  0 (default): plain (staged) copies from pageable memory. */
+void svtf_adapter_set_pin_pictures(int on);
+/* Host threads that gather mi_grid_base into the side-info byte planes (default 8). */
+void svtf_adapter_set_mi_threads(int n);
 /* Copy the resident picture of `pcs` back into `pic` (EbPictureBufferDesc *) — the end of a resident chain that does
  * not finish with ccso_frame. */
 void svtf_adapter_fetch(const struct PictureControlSet *pcs, void *pic);

@@ -105,7 +105,7 @@ EXPORTS = [
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
     "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
-    "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
+    "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_host_register", "svtf_host_unregister", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
     "svtf_cdef_pick_table_noalloc", "svtf_comm_unique_id", "svtf_comm_create", "svtf_comm_destroy", "svtf_upload_frame_own", "svtf_set_mi_own", "svtf_stripe_exchange", "svtf_cdef_search_gather_pick", "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
 ]
 
@@ -178,6 +178,8 @@ def load():
     lib.svtf_ctx_set_stream.argtypes = [vp, vp]
     lib.svtf_host_alloc.argtypes = [C.c_size_t]
     lib.svtf_host_alloc.restype = vp
+    lib.svtf_host_register.argtypes = [vp, C.c_size_t]
+    lib.svtf_host_unregister.argtypes = [vp]
     lib.svtf_host_free.argtypes = [vp]
     lib.svtf_host_free.restype = None
     _lib = lib

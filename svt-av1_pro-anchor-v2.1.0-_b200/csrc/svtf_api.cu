@@ -293,6 +293,31 @@ extern "C" void svtf_host_free(void *p) {
         cudaFreeHost(p);
 }
 
+// Page-lock a caller-owned buffer in place (cudaHostRegister) so that uploads from / downloads into it are asynchronous DMA at full
+// PCIe rate; a buffer that is already registered is fine.  Long-lived picture buffers (an encoder's recon pool) are registered once.
+extern "C" int svtf_host_register(void *p, size_t bytes) {
+    if (!p || !bytes)
+        return set_global_error(SVTF_E_ARG, "svtf_host_register: NULL buffer");
+    const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        cudaGetLastError();
+        return SVTF_OK;
+    }
+    if (e != cudaSuccess)
+        return set_global_error(SVTF_E_CUDA, (std::string("cudaHostRegister: ") + cudaGetErrorString(e)).c_str());
+    return SVTF_OK;
+}
+extern "C" int svtf_host_unregister(void *p) {
+    if (!p)
+        return set_global_error(SVTF_E_ARG, "svtf_host_unregister: NULL buffer");
+    const cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_global_error(SVTF_E_CUDA, (std::string("cudaHostUnregister: ") + cudaGetErrorString(e)).c_str());
+    }
+    return SVTF_OK;
+}
+
 extern "C" int svtf_frame_begin(svtf_ctx *c, const svtf_geom *g) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_frame_begin: NULL context");
