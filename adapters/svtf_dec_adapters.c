@@ -6,9 +6,11 @@
  *   Decoder/Codec/EbDecCdef.c:507  svt_cdef_frame
  *   Decoder/Codec/EbDecCcso.c:384  dec_ccso_frame
  *   Decoder/Codec/EbDecRestoration.c:429 / :473  svt_aom_dec_av1_loop_restoration_filter_frame / _save_boundary_lines
- * (decoder section).  The multi-threaded row variants (svt_aom_dec_loop_filter_row EbDecLF.c:650,
+ *   Decoder/Codec/EbDecProcess.c:668 / :810 / :1022  the three `_mt` stage functions every decoder thread calls when
+ *                                   EbSvtAv1DecConfiguration.threads > 1 (end of this file)
+ * (decoder section).  The multi-threaded row workers (svt_aom_dec_loop_filter_row EbDecLF.c:650,
  * svt_cdef_sb_row_mt EbDecCdef.c:385) exist to spread the CPU loops over worker threads with spin-wait row counters; with
- * the filters on the GPU the frame-level call is made once, from the thread that finishes the frame's reconstruction.
+ * the filters on the GPU the frame-level call is made once, from the thread that called the decoder.
  *
  * What an adapter does: (1) flatten the decoder's SB -> block -> transform-unit side info into one packed word per 4x4
  * (svtf_set_mi_soa_dec: block size / skip / ref / mode / segment from the covering BlockModeInfo through FrameMiMap, the
@@ -499,4 +501,86 @@ void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int 
     if (!g_resident)
         end_frame(s, pic), s->resident = 0;
     for (int p = 0; p < 3; p++) free(units[p]);
+}
+
+/* ----------------------------------------------------------------------------------------------------
+ * Multi-threaded decoding (dec_config.threads > 1).  The reference gives every thread — the caller (thread_ctxt == NULL,
+ * EbDecParseObu.c:2382-2453) and the workers (dec_all_stage_kernel, EbDecProcess.c:1167-1203) — the same three calls per
+ * frame, and the bodies share superblock rows through job counters and spin-wait row maps:
+ *   Decoder/Codec/EbDecProcess.c:668   svt_aom_dec_av1_loop_filter_frame_mt            (+ the LR boundary rows per SB row)
+ *   Decoder/Codec/EbDecProcess.c:810   svt_cdef_frame_mt
+ *   Decoder/Codec/EbDecProcess.c:1022  svt_aom_dec_av1_loop_restoration_filter_frame_mt (+ the picture padding per SB row)
+ * On the device a stage is one launch over the whole picture, so here the CALLING thread runs the frame-level adapter above
+ * once the stage's input is complete, and the workers pass straight through to the frame-end barrier in the third call
+ * (num_threads_lred, :1150-1165), which is kept as the reference has it — it is what keeps a worker from entering the next
+ * frame early and what clears the start_* flags.  The row maps these bodies used among themselves (lf_row_map,
+ * cdef_completed_for_row_map, lr_row_map) have no other reader and are left untouched.
+ */
+#include <sched.h>
+#include "EbDecProcess.h"
+
+static int dec_do_lr(const EbDecHandle *dec) {
+    const LrParams *lp = dec->frame_header.lr_params;
+    return !dec->frame_header.allow_intrabc &&
+        (lp[0].frame_restoration_type != RESTORE_NONE || lp[1].frame_restoration_type != RESTORE_NONE ||
+         lp[2].frame_restoration_type != RESTORE_NONE);
+}
+
+void svt_aom_dec_av1_loop_filter_frame_mt(EbDecHandle *dec_handle, EbPictureBufferDesc *recon_picture_buf, LfCtxt *lf_ctxt,
+                                          int32_t plane_start, int32_t plane_end, DecThreadCtxt *thread_ctxt) {
+    DecMtFrameData *mt = &dec_handle->main_frame_buf.cur_frame_bufs[0].dec_mt_frame_data;
+    volatile Bool  *start = &mt->start_lf_frame;
+    while (*start != TRUE) svt_block_on_semaphore(thread_ctxt ? thread_ctxt->thread_semaphore : dec_handle->thread_semaphore);
+    if (thread_ctxt)
+        return;
+    /* every tile's every SB row reconstructed (the per-row wait of :741-763, over the whole picture) */
+    const int                n   = mt->sb_rows * dec_handle->frame_header.tiles_info.tile_cols;
+    volatile const uint32_t *map = (volatile const uint32_t *)mt->sb_recon_row_map;
+    for (int i = 0; i < n; i++)
+        while (!map[i] && !mt->end_flag) sched_yield();
+    const FrameHeader *fh = &dec_handle->frame_header;
+    lf_ctxt->delta_lf_stride = dec_handle->main_frame_buf.sb_cols * FRAME_LF_COUNT;
+    svt_aom_dec_av1_loop_filter_frame(dec_handle, recon_picture_buf, lf_ctxt, plane_start, plane_end, /*is_mt*/ 1,
+                                      !fh->allow_intrabc && (fh->loop_filter_params.filter_level[0] || fh->loop_filter_params.filter_level[1]));
+    /* dec_save_lf_boundary_lines_sb_row (:600-629) per SB row == the frame-level save after the loop filter */
+    if (dec_do_lr(dec_handle))
+        svt_aom_dec_av1_loop_restoration_save_boundary_lines(dec_handle, 0);
+}
+
+void svt_cdef_frame_mt(EbDecHandle *dec_handle_ptr, DecThreadCtxt *thread_ctxt) {
+    DecMtFrameData *mt = &dec_handle_ptr->main_frame_buf.cur_frame_bufs[0].dec_mt_frame_data;
+    volatile Bool  *start = &mt->start_cdef_frame;
+    while (*start != TRUE) svt_block_on_semaphore(thread_ctxt ? thread_ctxt->thread_semaphore : dec_handle_ptr->thread_semaphore);
+    const FrameHeader *fh = &dec_handle_ptr->frame_header;
+    if (!thread_ctxt)
+        svt_cdef_frame(dec_handle_ptr,
+                       !fh->allow_intrabc && !fh->coded_lossless &&
+                           (fh->cdef_params.cdef_bits || fh->cdef_params.cdef_y_strength[0] || fh->cdef_params.cdef_uv_strength[0]));
+    /* :938-945 — with superres every thread waits here until CDEF is over, because the caller upscales next */
+    svt_block_on_mutex(mt->temp_mutex);
+    mt->num_threads_cdefed++;
+    svt_release_mutex(mt->temp_mutex);
+    if (!fh->allow_intrabc && !av1_superres_unscaled(&fh->frame_size)) {
+        volatile uint32_t *done = &mt->num_threads_cdefed;
+        while (*done != dec_handle_ptr->dec_config.threads && !mt->end_flag) sched_yield();
+    }
+}
+
+void svt_aom_dec_av1_loop_restoration_filter_frame_mt(EbDecHandle *dec_handle, DecThreadCtxt *thread_ctxt) {
+    DecMtFrameData *mt = &dec_handle->main_frame_buf.cur_frame_bufs[0].dec_mt_frame_data;
+    volatile Bool  *start = &mt->start_lr_frame;
+    while (*start != TRUE) svt_block_on_semaphore(thread_ctxt ? thread_ctxt->thread_semaphore : dec_handle->thread_semaphore);
+    if (!thread_ctxt && !mt->end_flag) {
+        svt_aom_dec_av1_loop_restoration_filter_frame(dec_handle, 0, dec_do_lr(dec_handle));
+        svt_aom_pad_pic(dec_handle); /* pad_pre_lr + pad_post_lr (:968-1020) over all rows == the single-threaded padding */
+    }
+    svt_block_on_mutex(mt->temp_mutex);
+    mt->num_threads_lred++;
+    if (dec_handle->dec_config.threads == mt->num_threads_lred) {
+        mt->start_motion_proj = FALSE, mt->start_parse_frame = FALSE, mt->start_decode_frame = FALSE;
+        mt->start_lf_frame = FALSE, mt->start_cdef_frame = FALSE, mt->start_lr_frame = FALSE;
+    }
+    svt_release_mutex(mt->temp_mutex);
+    volatile uint32_t *done = &mt->num_threads_lred;
+    while (*done != dec_handle->dec_config.threads && FALSE == mt->end_flag) sched_yield();
 }

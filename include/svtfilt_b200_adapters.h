@@ -66,6 +66,12 @@ void svtf_adapter_release(const struct PictureControlSet *pcs);
  *   void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle*, uint16_t *ext_rec_y);          Decoder/Codec/EbDecCcso.c:384
  *   void svt_aom_dec_av1_loop_restoration_save_boundary_lines(EbDecHandle*, int after_cdef);     Decoder/Codec/EbDecRestoration.c:473
  *   void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle*, int optimized_lr, int enable_flag);           :429
+ * and, for EbSvtAv1DecConfiguration.threads > 1 (every decoder thread calls these; the calling thread launches, the workers
+ * pass through to the frame-end barrier):
+ *   void svt_aom_dec_av1_loop_filter_frame_mt(EbDecHandle*, EbPictureBufferDesc *recon, LfCtxt*, int32_t plane_start,
+ *                                             int32_t plane_end, DecThreadCtxt*);                Decoder/Codec/EbDecProcess.c:668
+ *   void svt_cdef_frame_mt(EbDecHandle*, DecThreadCtxt*);                                                            :810
+ *   void svt_aom_dec_av1_loop_restoration_filter_frame_mt(EbDecHandle*, DecThreadCtxt*);                             :1022
  */
 struct EbDecHandle;
 void svtf_dec_adapter_set_device(int device);

@@ -32,4 +32,9 @@ cmake "${COMMON[@]}" -S "$B/src_b200" -B "$B/b200" -DSVT_B200_FILTERS=ON -DSVTFI
 ninja -C "$B/b200" > "$B/b200_ninja.log" 2>&1
 cp "$B/b200/bin/SvtAv1EncApp" "$HERE/_bin/SvtAv1EncApp_b200"
 cp "$B/b200/bin/SvtAv1DecApp" "$HERE/_bin/SvtAv1DecApp_b200"
+# the decoder's multi-threaded path is not reachable from SvtAv1DecApp (-threads is disabled there): a minimal API client
+LIBDIR="$ROOT/svt-av1_pro-anchor-v2.1.0-_b200/lib"
+gcc -O2 -I"$REF/Source/API" -o "$HERE/_bin/dec_threads_ref" "$HERE/dec_threads_main.c" "$B/ref/bin/libSvtAv1Dec.a" -lpthread -lm
+gcc -O2 -I"$REF/Source/API" -o "$HERE/_bin/dec_threads_b200" "$HERE/dec_threads_main.c" "$B/b200/bin/libSvtAv1Dec.a" \
+    "$LIBDIR/libsvtfilt_b200.so" -Wl,-rpath,"$LIBDIR" -lpthread -lm
 ls -la "$HERE/_bin"

@@ -145,6 +145,15 @@ def main():
         s = guard_function(s, sig)
     write(rel, s)
 
+    # the multi-threaded variants (every thread calls them; the adapters run the frame-level launch on the calling thread)
+    rel = "Source/Lib/Decoder/Codec/EbDecProcess.c"
+    s = read(rel)
+    for sig in ("void svt_aom_dec_av1_loop_filter_frame_mt(EbDecHandle *dec_handle, EbPictureBufferDesc *recon_picture_buf,",
+                "void svt_cdef_frame_mt(EbDecHandle *dec_handle_ptr, DecThreadCtxt *thread_ctxt) {",
+                "void svt_aom_dec_av1_loop_restoration_filter_frame_mt(EbDecHandle *dec_handle, DecThreadCtxt *thread_ctxt) {"):
+        s = guard_function(s, sig)
+    write(rel, s)
+
     out = os.path.join(HERE, "svt_b200.patch")
     # file by file over the copy (the copy holds only the directories the build needs)
     txt = subprocess.run(["bash", "-c", f"cd {DST} && for f in $(find . -type f | sort); do diff -uN --label a/${{f#./}} --label b/${{f#./}} {REF}/$f $f; done"],

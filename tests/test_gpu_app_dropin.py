@@ -116,3 +116,25 @@ def test_decoder_4k_10bit_stream_identical(tmp_path):
     assert _md5(str(tmp_path / "dec_ref.yuv")) == _md5(str(tmp_path / "s.yuv")), "decoder output differs from the encoder's reconstruction"
     st = _stats(err)
     assert st["dec_loop_filter_frame"] >= 1 and st["dec_cdef_frame"] >= 1 and st["gpu_launches"] > 0, st
+
+
+@pytest.mark.parametrize("w,h,frames,depth,preset,threads", [(640, 360, 6, 8, 4, 4), (1280, 720, 4, 10, 8, 3)])
+def test_decoder_multithreaded_entries_identical(tmp_path, w, h, frames, depth, preset, threads):
+    """The decoder's `_mt` stage functions (Decoder/Codec/EbDecProcess.c:668 / :810 / :1022), which every decoder thread calls
+    when EbSvtAv1DecConfiguration.threads > 1.  SvtAv1DecApp cannot reach them (its -threads option is disabled), so
+    integration/dec_threads_main.c drives the public decoder API; both builds decode with worker threads, and the result
+    must equal the single-threaded reference decode and the encoder's reconstruction."""
+    clip = _clip(tmp_path, w, h, frames, depth)
+    _encode("SvtAv1EncApp_ref", clip, w, h, frames, depth, preset, str(tmp_path / "s"), ("--crf", "55"))  # coarse: every filter stage on
+    ivf = str(tmp_path / "s.ivf")
+    outs = {}
+    for name, app, t in (("ref1", "dec_threads_ref", 1), ("refN", "dec_threads_ref", threads), ("b200N", "dec_threads_b200", threads)):
+        outs[name] = str(tmp_path / f"{name}.yuv")
+        r = subprocess.run([_bin(app), ivf, outs[name], str(t)], capture_output=True, text=True, timeout=600, env=dict(os.environ, SVTF_ADAPTER_STATS="1"))
+        assert r.returncode == 0, r.stderr[-3000:]
+        err = r.stderr
+    want = _md5(str(tmp_path / "s.yuv"))
+    assert _md5(outs["ref1"]) == want and _md5(outs["refN"]) == want
+    assert _md5(outs["b200N"]) == want, "multi-threaded decode through the adapters differs"
+    st = _stats(err)
+    assert st["dec_loop_filter_frame"] >= 1 and st["dec_cdef_frame"] >= 1 and st["gpu_launches"] > 0, st
