@@ -132,3 +132,15 @@ API int adaptdec_chain_lr_resident(const svtf_geom *g, void *y, int sy, void *cb
     dec_harness_free(&h);
     return 0;
 }
+
+/* The multi-threaded stage entries of svtf_dec_adapters.c use the decoder library's thread primitives and its picture padding;
+ * this harness drives single-threaded frame calls only (the `_mt` entries are exercised by the real decoder library in
+ * tests/test_gpu_app_dropin.py), so here they only have to resolve. */
+static void harness_unreachable(const char *what) {
+    fprintf(stderr, "adapter_harness_dec: %s is not available in the test harness\n", what);
+    abort();
+}
+EbErrorType svt_block_on_semaphore(EbHandle h) { (void)h; harness_unreachable("svt_block_on_semaphore"); return EB_ErrorNone; }
+EbErrorType svt_block_on_mutex(EbHandle h) { (void)h; harness_unreachable("svt_block_on_mutex"); return EB_ErrorNone; }
+EbErrorType svt_release_mutex(EbHandle h) { (void)h; harness_unreachable("svt_release_mutex"); return EB_ErrorNone; }
+void        svt_aom_pad_pic(EbDecHandle *d) { (void)d; harness_unreachable("svt_aom_pad_pic"); }

@@ -25,6 +25,7 @@
 #include "svtf_cdef2.cuh"
 #include "svtf_cdef3.cuh"
 #include "svtf_cdef4.cuh"
+#include "svtf_cdef5.cuh"
 #include "svtf_search3.cuh"
 #include "svtf_mi_pack.cuh"
 #include "svtf_lr.cuh"
@@ -128,6 +129,7 @@ struct svtf_ctx {
     uint8_t     *d_handoff = nullptr;      // staging of svtf_download_ref_padded / svtf_upload_frame_8as16, allocated on first use
     size_t       handoff_cap = 0;
     bool         search3_ready = false;    // same for cdef_search3_kernel
+    bool         cdef5_ready = false;
     bool         cdef3_ready = false;      // dynamic shared-memory opt-in of cdef3_kernel done on this device
     unsigned    *d_sched = nullptr;        // tile scheduler of the persistent kernels: {next tile, CTAs done}, zero between launches
     int          cdef4_ctas_per_sm[4] = {0, 0, 0, 0}; // cdef4_kernel<u8/u16, int/fp16>: resident CTAs per SM (0 = not set up yet)
@@ -1118,26 +1120,50 @@ static int cdef_apply_impl(svtf_ctx *c, const svtf_cdef_params *cp, const int8_t
             // SVTF_CDEF_TMA=1: cdef4_kernel (svtf_cdef4.cuh) — the same arithmetic in persistent CTAs fed by TMA.  Measured SLOWER than
             // cdef3 on the 4K 10-bit workload (95 vs 86 us alone), so it is not the default; kept selectable and parity-tested.
             static const bool use_tma = getenv("SVTF_CDEF_TMA") != nullptr;
+            // fp16 taps: cdef5_kernel (svtf_cdef5.cuh).  SVTF_CDEF_V3=1 (builds with -DSVTF_AB_KERNELS only) selects its predecessor
+            // cdef3_kernel<T, true> for A/B runs; cdef3_kernel<T, false> stays the integer path.
+#ifdef SVTF_AB_KERNELS
+            static const bool use_v5 = getenv("SVTF_CDEF_V3") == nullptr;
+#else
+            constexpr bool use_v5 = true;
+#endif
+            if (use_v5 && fp && !use_tma) {
+                constexpr int smem5 = C5_SMEM_WORDS * 4;
+                if (!c->cdef5_ready) {
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef5_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem5));
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef5_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem5));
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef5_kernel<uint8_t>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+                    CUDA_TRY(c, cudaFuncSetAttribute(cdef5_kernel<uint16_t>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+                    c->cdef5_ready = true;
+                }
+                if (c->geom.sample_bytes == 1)
+                    cdef5_kernel<uint8_t><<<grid, C2_THREADS, smem5, c->stream>>>(b);
+                else
+                    cdef5_kernel<uint16_t><<<grid, C2_THREADS, smem5, c->stream>>>(b);
+            } else
             if (!use_tma) {
                 constexpr int smem_i = C3_SMEM_WORDS_I * 4, smem_f = C3_SMEM_WORDS_F * 4;
                 if (!c->cdef3_ready) {
                     CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
                     CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_i));
+#ifdef SVTF_AB_KERNELS
                     CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint8_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
                     CUDA_TRY(c, cudaFuncSetAttribute(cdef3_kernel<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
+#endif
                     c->cdef3_ready = true;
                 }
-                if (c->geom.sample_bytes == 1) {
-                    if (fp)
+#ifdef SVTF_AB_KERNELS
+                if (fp) {
+                    if (c->geom.sample_bytes == 1)
                         cdef3_kernel<uint8_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
                     else
-                        cdef3_kernel<uint8_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
-                } else {
-                    if (fp)
                         cdef3_kernel<uint16_t, true><<<grid, C2_THREADS, smem_f, c->stream>>>(b);
-                    else
-                        cdef3_kernel<uint16_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
-                }
+                } else
+#endif
+                if (c->geom.sample_bytes == 1)
+                    cdef3_kernel<uint8_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
+                else
+                    cdef3_kernel<uint16_t, false><<<grid, C2_THREADS, smem_i, c->stream>>>(b);
             } else
             if (int r = cdef4_launch(c, b, fp, (int)grid.x, (int)grid.y))
                 return r;

@@ -16,7 +16,8 @@ for i in range(3):
     ccso, flags = H.synth_ccso(g, seed + 3, quant_idx=(0, 0, 0), support=(0, 1, 2), edge_clf=(0, 0, 0), band_log2=(2, 2, 2), p_on=0.8)
     wls.append((rec, mi, S.lf_params((24, 24), 12, 12), cdef, idx, ccso, flags))
 B = 12
-streams = [torch.cuda.Stream() for _ in range(4)]
+NS = int(os.environ.get("NS", "4"))
+streams = [torch.cuda.Stream() for _ in range(NS)]
 ctxs = []
 for i in range(B):
     c = S.FilterContext(g); c.begin(g); w = wls[i % 3]; c.upload(w[0]); c.set_mi(w[1]); c.sync(); ctxs.append(c)
@@ -32,7 +33,7 @@ def serial():
     return [statistics.mean(e[k].elapsed_time(e[k + 1]) for e in ev) * 1e3 for k in range(2)]
 serial(); a = serial(); b = serial()
 for i, c in enumerate(ctxs):
-    c.set_stream(streams[i % 4].cuda_stream)
+    c.set_stream(streams[i % NS].cuda_stream)
 def step():
     for i, c in enumerate(ctxs):
         w = wls[i % 3]; c.rewind(); c.filter_chain(w[2], w[3], w[4], w[5], w[6])
@@ -47,4 +48,4 @@ for s in streams[1:]:
     e = torch.cuda.Event(); e.record(s); st.wait_event(e)
 e1.record(st); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1)
-print(f"deblock {min(a[0], b[0]):.1f} us, cdef+ccso {min(a[1], b[1]):.1f} us alone; 4 streams: {ms / K / B * 1e3:.1f} us per picture, {B * 3840 * 2160 * K / ms / 1e3:.0f} Mpixel/s")
+print(f"deblock {min(a[0], b[0]):.1f} us, cdef+ccso {min(a[1], b[1]):.1f} us alone; {NS} streams: {ms / K / B * 1e3:.1f} us per picture, {B * 3840 * 2160 * K / ms / 1e3:.0f} Mpixel/s")
