@@ -41,6 +41,13 @@ __device__ __forceinline__ __half2  u2h(const uint32_t u) { return *reinterpret_
 __device__ __forceinline__ uint32_t pk_i2h(const uint32_t w) { return h2u(__hsub2(u2h(w | 0x64006400u), u2h(0x64006400u))); }
 __device__ __forceinline__ uint32_t pk_h2i(const uint32_t f) { return h2u(__hadd2(u2h(f), u2h(0x64006400u))) & 0x03FF03FFu; }
 
+// sign(a) ^ sign(b) applied to min(|a|, |b|), per half (HMNMX2.XORSIGN)
+__device__ __forceinline__ uint32_t pk_xsmin(const uint32_t a, const uint32_t b) {
+    uint32_t d;
+    asm("min.xorsign.abs.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+
 // Staging is split in two so that every global load of a thread (tile chunks, CCSO LUT, side info) is in flight before
 // the first one is consumed: c3_load fetches one 8-sample chunk + the sample that follows it into registers, c3_store
 // writes it as A (even pair alignment), B (odd: word i = samples 2i+1, 2i+2) and, FP only, I (the integer pairs; A/B

@@ -33,13 +33,6 @@ constexpr uint32_t C5_SENT       = 0xF800F800u; // -32768.0 per half: outside th
 constexpr uint32_t C5_MASK       = 0x03FF03FFu;
 constexpr int      C5_SMEM_WORDS = 2 * C3_YSZ + 4 * C3_CSZ;
 
-// sign(a) ^ sign(b) applied to min(|a|, |b|), per half
-__device__ __forceinline__ uint32_t c5_xsmin(const uint32_t a, const uint32_t b) {
-    uint32_t d;
-    asm("min.xorsign.abs.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
-    return d;
-}
-
 // tap-class constants as they sit in shared memory: x = -2^-s, y = C (svtf_cdef3.cuh: t + 0.5 - 2^-(s+1)), z = first tap weight,
 // w = second tap weight (low half) | on << 16 | luma direction << 20 | chroma direction << 24
 __device__ __forceinline__ uint4 c5_tap_consts(const int t, const int damp, const uint32_t w0, const uint32_t w1) {
@@ -84,7 +77,7 @@ __device__ __forceinline__ void cdef5_row(const uint32_t *ctr, const int2 (&o)[6
                         const __half2 d = __hsub2(u2h(e ? p1 : p0), u2h(x[j]));
                         const __half2 r = __hadd2(__hfma2(__habs2(d), t.nsc, t.C), k1024);
                         const __half2 v = __hfma2_relu(r, kone, kn1024);
-                        acc[j]          = __hfma2(u2h(c5_xsmin(h2u(d), h2u(v))), w, acc[j]);
+                        acc[j]          = __hfma2(u2h(pk_xsmin(h2u(d), h2u(v))), w, acc[j]);
                     }
                 }
                 mx[j] = __vimax3_s16x2(mx[j], p0, p1); // the sentinel is negative as a signed halfword, 0x6400 | n is not
@@ -97,7 +90,7 @@ __device__ __forceinline__ void cdef5_row(const uint32_t *ctr, const int2 (&o)[6
     for (int j = 0; j < NP; j++) {
         // (8 + sum - (sum < 0)) >> 4 = sign(sum) * floor((|sum| + 8) / 16) = sign(sum) * RN(|sum|/16 + 1/32)  (<= |sum|)
         const __half2 q = __hadd2(__hadd2(__hfma2(__habs2(acc[j]), k16, k32), k1024), kn1024);
-        const __half2 y = __hmin2(__hmax2(__hadd2(u2h(x[j]), u2h(c5_xsmin(h2u(acc[j]), h2u(q)))), u2h(mn[j])), u2h(mx[j]));
+        const __half2 y = __hmin2(__hmax2(__hadd2(u2h(x[j]), u2h(pk_xsmin(h2u(acc[j]), h2u(q)))), u2h(mn[j])), u2h(mx[j]));
         outw[j]         = h2u(y) & C5_MASK;
     }
 }

@@ -91,6 +91,7 @@ extern "C" int svtf_cdef_pick_table_noalloc(svtf_ctx *c, const svtf_cdef_search_
     a.st  = reinterpret_cast<PickState *>(base + NA_OFF_STATE);
     a.tot = reinterpret_cast<uint64_t *>(base + NA_OFF_TOT);
     // pick_enqueue clears the state block (cudaMemsetAsync); pick_init_kernel zeroes the totals
+    CUDA_TRY(c, pick_prepare()); // a function attribute, not an allocation
     CUDA_TRY(c, pick_enqueue(a, d_idx, (int64_t)cfg->lambda, c->sm_count, c->stream, &c->launches));
     PickState st;
     CUDA_TRY(c, cudaMemcpyAsync(&st, a.st, sizeof(st), cudaMemcpyDeviceToHost, c->stream));

@@ -11,6 +11,7 @@
 // the greedy lists live in device memory.  All arithmetic is u64/i64 integer, identical to the C code.
 #pragma once
 #include <cstdint>
+#include <type_traits>
 #include <cuda_runtime.h>
 
 namespace svtf {
@@ -74,8 +75,11 @@ __global__ void __launch_bounds__(PICK_THREADS) pick_init_kernel(const PickArgs 
 // svt_search_one_dual_c, argmin part (first (j,k) in raster order wins ties) + list update + re-zeroing of tot.
 // pos: list slot that receives the pick; rot: rotate the list first; bits >= 0: this was the last call for that
 // cdef_bits -> RD cost and best-so-far update (EbEncCdef.c:845-876).  Runs in the last CTA of an accumulate launch.
-constexpr int PT_THREADS = 128; // 8 groups of 4 rows x 16 groups of 4 columns: a 32 x 64 slab of tot per CTA
-constexpr int PT_CHUNK   = 32;  // filter blocks per CTA
+constexpr int PT_THREADS = 256;       // 8 warps = 8 subsets of the CTA's filter blocks; a warp covers the CTA's 8 x 64 slab of tot
+constexpr int PT_CHUNK_N = 128;       // filter blocks per CTA, narrow table (32-bit rows in shared memory)
+constexpr int PT_CHUNK_W = 64;        // filter blocks per CTA, wide table (64-bit rows): the same 64 KB
+constexpr int PT_ROWS    = 8;         // rows of tot (luma strengths) per CTA
+constexpr int PT_SMEM    = 64 * 1024 + PT_CHUNK_N * 8; // table rows of the chunk + best_so_far
 
 __device__ __forceinline__ void pick_argmin_body(const PickArgs &a, const int pos, const int rot, const int bits, const int64_t lambda,
                                                  uint64_t *s_v, int *s_i) {
@@ -135,103 +139,136 @@ __device__ __forceinline__ void pick_argmin_body(const PickArgs &a, const int po
     }
 }
 
-// svt_search_one_dual_c, accumulation part: tot[j][k] += min(best_so_far(fb), mse0[fb][j] + mse1[fb][k]) over the
-// searched filter blocks.  nb entries of the list are fixed; `rot` = 1 reads them one position further (the refinement
-// step drops entry 0, EbEncCdef.c:717-722).  CTA (half, chunk): rows [32*half, 32*half+32) of tot over PT_CHUNK filter
-// blocks; a thread keeps a 4 x 4 register tile of tot, so one filter block costs it 5 shared loads and 16 min-adds.
-//
-// The 75 calls of a picture are a dependent chain, so the latency of one call is what counts:
-//  * the table rows of the chunk do not depend on the previous call: they are staged (16-byte loads, all in flight) BEFORE
-//    cudaGridDependencySynchronize(), and every launch carries the programmatic-stream-serialization attribute, so launch
-//    latency and staging overlap the previous call's atomics / argmin tail;
-//  * after the dependency only the 16 list entries are read from global memory; best_so_far comes from shared memory.
-// narrow (every table entry below 2^31, PickState.wide == 0): the sum fits 32 bits and min(a + b, best) is one VIADDMNMX;
-// the totals are u64 either way, so both variants give the C code's numbers.
+// One call for the CTA's chunk of PT_CHUNK_N filter blocks.  NARROW: every table entry is below 2^31 (PickState.wide == 0), rows are
+// kept as 32-bit words and min(a + b, best) is one VIADDMNMX; else 64-bit rows, staged and accumulated in two halves of PT_CHUNK_W
+// blocks through the same 64 KB (the second half is staged after the dependency: the rare case pays for it).  Totals are u64 either way.
 template <bool NARROW>
-__device__ __forceinline__ void pick_tot_loop(const uint64_t (*srow)[128], const uint64_t *sbest, const int jt, uint64_t (&acc)[4][4]) {
-    const int tid = threadIdx.x, tj = tid >> 4, tk = tid & 15;
-#pragma unroll 2
-    for (int f = 0; f < PT_CHUNK; f++) {
-        uint64_t av[4], bv[4];
+__device__ __forceinline__ void pick_tot_body(const PickArgs &a, const int nb, const int rot, unsigned char *pt_dyn) {
+    typedef typename std::conditional<NARROW, uint32_t, uint64_t>::type E;
+    constexpr int CH = NARROW ? PT_CHUNK_N : PT_CHUNK_W;
+    E(*srow)[128]    = reinterpret_cast<E(*)[128]>(pt_dyn); // [fb][plane 0: 64 strengths | plane 1: 64 strengths]
+    E *sbest         = reinterpret_cast<E *>(pt_dyn + 64 * 1024);
+    const int tid = threadIdx.x, jt = blockIdx.x * PT_ROWS;
+    uint64_t  acc[4][4];
 #pragma unroll
-        for (int r = 0; r < 4; r++) av[r] = srow[f][jt + tj * 4 + r], bv[r] = srow[f][64 + tk * 4 + r];
-        const uint64_t bst = sbest[f];
+    for (int r = 0; r < 4; r++)
 #pragma unroll
-        for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 4; c++) acc[r][c] = 0;
+#pragma unroll 1
+    for (int half = 0; half < PT_CHUNK_N / CH; half++) {
+        const int fb0 = blockIdx.y * PT_CHUNK_N + half * CH;
+        if (half)
+            __syncthreads(); // the first half's rows have been read
+        // rows of the chunk, skipped or not (a skipped block gets best = 0 below and then adds min(0, .) = 0); the whole luma row is
+        // staged, not only this CTA's 8 entries: best_so_far reads whichever entries the greedy lists name
+        constexpr int VPT = CH * 64 / PT_THREADS; // 16-byte vectors per thread
 #pragma unroll
-            for (int c = 0; c < 4; c++) {
-                if (NARROW)
-                    acc[r][c] += __viaddmin_u32((unsigned)av[r], (unsigned)bv[c], (unsigned)bst);
-                else
-                    acc[r][c] += min(bst, av[r] + bv[c]);
+        for (int n0 = 0; n0 < VPT; n0 += 8) {
+            ulonglong2 v[8];
+#pragma unroll
+            for (int n = 0; n < 8; n++) {
+                const int i = tid + (n0 + n) * PT_THREADS, f = i >> 6, e = i & 63, fb = min(fb0 + f, a.nfb - 1);
+                v[n] = __ldg(reinterpret_cast<const ulonglong2 *>(a.mse + ((size_t)(e >> 5) * a.nfb + fb) * 64) + (e & 31));
             }
-    }
-}
-
-// The CTA that finishes last (ticket counter, no waiting) runs the argmin + list update of the same call.
-__global__ void __launch_bounds__(PT_THREADS) pick_tot_kernel(const PickArgs a, const int nb, const int rot, const int pos, const int bits,
-                                                              const int64_t lambda) {
-    __shared__ __align__(16) uint64_t srow[PT_CHUNK][128]; // [fb][plane 0: 64 strengths | plane 1: 64 strengths]
-    __shared__ uint64_t               sbest[PT_CHUNK];
-    __shared__ int                    s_last;
-    const int  tid = threadIdx.x, jt = blockIdx.x * 32, fb0 = blockIdx.y * PT_CHUNK;
-    const bool active = jt < a.end_gi;
-    if (active) {
-        // rows of the chunk, skipped or not (a skipped block gets best = 0 below and then adds min(0, .) = 0)
-        constexpr int VPT = PT_CHUNK * 64 / PT_THREADS; // 16-byte vectors per thread
-        ulonglong2    v[VPT];
 #pragma unroll
-        for (int n = 0; n < VPT; n++) {
-            const int i = tid + n * PT_THREADS, f = i >> 6, e = i & 63, fb = min(fb0 + f, a.nfb - 1);
-            v[n] = __ldg(reinterpret_cast<const ulonglong2 *>(a.mse + ((size_t)(e >> 5) * a.nfb + fb) * 64) + (e & 31));
+            for (int n = 0; n < 8; n++) {
+                const int i = tid + (n0 + n) * PT_THREADS, f = i >> 6, e = i & 63;
+                if (a.bias && (e & 31) == 0)
+                    v[n].x = ((uint64_t)(uint16_t)a.bias * v[n].x) >> 6; // entry 0 of a row, EbEncCdef.c:776-789
+                if (NARROW)
+                    *reinterpret_cast<uint2 *>(&srow[f][2 * e]) = make_uint2((uint32_t)v[n].x, (uint32_t)v[n].y);
+                else
+                    *reinterpret_cast<ulonglong2 *>(&srow[f][2 * e]) = v[n];
+            }
         }
-#pragma unroll
-        for (int n = 0; n < VPT; n++) {
-            const int i = tid + n * PT_THREADS, f = i >> 6, e = i & 63;
-            if (a.bias && (e & 31) == 0)
-                v[n].x = ((uint64_t)(uint16_t)a.bias * v[n].x) >> 6; // entry 0 of a row, EbEncCdef.c:776-789
-            *reinterpret_cast<ulonglong2 *>(&srow[f][2 * e]) = v[n];
-        }
-    }
-    uint8_t skp = 1;
-    if (tid < PT_CHUNK && fb0 + tid < a.nfb)
-        skp = a.skip[fb0 + tid];
-    cudaGridDependencySynchronize(); // the previous call's list update and the re-zeroed tot are visible from here on
-    if (active) {
+        uint8_t skp = 1;
+        if (tid < CH && fb0 + tid < a.nfb)
+            skp = a.skip[fb0 + tid];
+        if (!half)
+            cudaGridDependencySynchronize(); // the previous call's list update and the re-zeroed tot are visible from here on
         __syncthreads();
-        const bool narrow = !a.st->wide;
-        if (tid < PT_CHUNK) {
-            uint64_t best = 0;
+        if (tid < CH) {
+            E best = 0;
             if (!skp) {
-                best = narrow ? 0xffffffffull : PICK_INF;
+                best = NARROW ? (E)0xffffffffu : (E)PICK_INF;
 #pragma unroll
                 for (int g = 0; g < 8; g++)
                     if (g < nb)
-                        best = min(best, srow[tid][a.st->lev0[min(g + rot, 7)]] + srow[tid][64 + a.st->lev1[min(g + rot, 7)]]);
+                        best = min(best, (E)(srow[tid][a.st->lev0[min(g + rot, 7)]] + srow[tid][64 + a.st->lev1[min(g + rot, 7)]]));
             }
             sbest[tid] = best;
         }
         __syncthreads();
-        uint64_t acc[4][4];
+        const int lane = tid & 31, f0 = (tid >> 5) * (CH / 8), tj = lane >> 4, tk = lane & 15;
+#pragma unroll 2
+        for (int f = f0; f < f0 + CH / 8; f++) {
+            E av[4], bv[4];
 #pragma unroll
-        for (int r = 0; r < 4; r++)
+            for (int r = 0; r < 4; r++) av[r] = srow[f][jt + tj * 4 + r], bv[r] = srow[f][64 + tk * 4 + r];
+            const E bst = sbest[f];
 #pragma unroll
-            for (int c = 0; c < 4; c++) acc[r][c] = 0;
-        if (narrow)
-            pick_tot_loop<true>(srow, sbest, jt, acc);
-        else
-            pick_tot_loop<false>(srow, sbest, jt, acc);
-        cudaTriggerProgrammaticLaunchCompletion(); // the next call may launch and stage its rows now
-        const int tj = tid >> 4, tk = tid & 15;
+            for (int r = 0; r < 4; r++)
 #pragma unroll
-        for (int r = 0; r < 4; r++)
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                const int j = jt + tj * 4 + r, k = tk * 4 + c;
-                if (j < a.end_gi && k < a.end_gi && acc[r][c])
-                    atomicAdd(reinterpret_cast<unsigned long long *>(&a.tot[j * 64 + k]), (unsigned long long)acc[r][c]);
-            }
+                for (int c = 0; c < 4; c++) {
+                    if (NARROW)
+                        acc[r][c] += __viaddmin_u32((unsigned)av[r], (unsigned)bv[c], (unsigned)bst);
+                    else
+                        acc[r][c] += min((uint64_t)bst, (uint64_t)av[r] + (uint64_t)bv[c]);
+                }
+        }
     }
+    cudaTriggerProgrammaticLaunchCompletion(); // the next call may launch and stage its rows now
+    // the eight warps' partial slabs -> one 8 x 64 slab (through the rows' shared memory), then one atomic per entry and CTA
+    __syncthreads();
+    uint64_t *red = reinterpret_cast<uint64_t *>(pt_dyn); // [8 warps][8 * 64]
+    {
+        const int w = tid >> 5, lane = tid & 31, tj = lane >> 4, tk = lane & 15;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            ulonglong2 *d = reinterpret_cast<ulonglong2 *>(&red[w * 512 + (tj * 4 + r) * 64 + tk * 4]);
+            d[0] = make_ulonglong2(acc[r][0], acc[r][1]), d[1] = make_ulonglong2(acc[r][2], acc[r][3]);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int i = tid + h * PT_THREADS, j = jt + (i >> 6), k = i & 63;
+        uint64_t  v = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) v += red[w * 512 + i];
+        if (j < a.end_gi && k < a.end_gi && v)
+            atomicAdd(reinterpret_cast<unsigned long long *>(&a.tot[j * 64 + k]), (unsigned long long)v);
+    }
+}
+
+// svt_search_one_dual_c, accumulation part: tot[j][k] += min(best_so_far(fb), mse0[fb][j] + mse1[fb][k]) over the searched filter
+// blocks.  nb entries of the list are fixed; `rot` = 1 reads them one position further (the refinement step drops entry 0,
+// EbEncCdef.c:717-722).  CTA (x, y): rows [8x, 8x + 8) of tot over the y-th chunk of filter blocks; warp w takes an eighth of the chunk
+// and covers the 8 x 64 slab with 4 x 4 register tiles (a filter block costs a thread three shared loads and 16 min-adds); the warps'
+// slabs are summed through shared memory, so a CTA issues 512 atomics per call (round 1: 2 048 from a 32-block chunk — the atomics
+// and the fence behind them were most of a call's 13 us).
+//
+// The 75 calls of a picture are a dependent chain, so the latency of one call is what counts:
+//  * the table rows of the chunk do not depend on the previous call: they are staged (16-byte loads, all in flight) BEFORE
+//    cudaGridDependencySynchronize(), and every launch carries the programmatic-stream-serialization attribute, so launch latency and
+//    staging overlap the previous call's atomics / argmin tail (64 KB of rows per CTA: the next call's CTA fits beside the running one);
+//  * after the dependency only the 16 list entries are read from global memory; best_so_far comes from shared memory.
+// The CTA that finishes last (ticket counter, no waiting) runs the argmin + list update of the same call.
+__global__ void __launch_bounds__(PT_THREADS) pick_tot_kernel(const PickArgs a, const int nb, const int rot, const int pos, const int bits,
+                                                              const int64_t lambda) {
+    extern __shared__ __align__(16) unsigned char pt_dyn[];
+    __shared__ int s_last;
+    const int      tid = threadIdx.x;
+    // PickState.wide is written by pick_init_kernel, which has completed before the first call starts (it never triggers early)
+    const bool narrow = !a.st->wide;
+    const bool active = blockIdx.x * PT_ROWS < a.end_gi;
+    if (active) {
+        if (narrow)
+            pick_tot_body<true>(a, nb, rot, pt_dyn);
+        else
+            pick_tot_body<false>(a, nb, rot, pt_dyn);
+    } else
+        cudaGridDependencySynchronize();
     __threadfence();
     __syncthreads();
     if (tid == 0)
@@ -239,7 +276,7 @@ __global__ void __launch_bounds__(PT_THREADS) pick_tot_kernel(const PickArgs a, 
     __syncthreads();
     if (s_last) {
         __threadfence();
-        pick_argmin_body(a, pos, rot, bits, lambda, &srow[0][0], reinterpret_cast<int *>(&srow[1][0]));
+        pick_argmin_body(a, pos, rot, bits, lambda, reinterpret_cast<uint64_t *>(pt_dyn), reinterpret_cast<int *>(pt_dyn + 1024));
     }
 }
 
@@ -264,6 +301,9 @@ __global__ void __launch_bounds__(PICK_THREADS) pick_assign_kernel(const PickArg
     fb_idx[fb] = (int8_t)bg;
 }
 
+// Once per device before the first pick_enqueue (not a stream operation: kept out of pick_enqueue so that the schedule can be captured).
+inline cudaError_t pick_prepare() { return cudaFuncSetAttribute(pick_tot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_SMEM); }
+
 // Enqueues the whole schedule of finish_cdef_search on `stream` (77 small launches, no host synchronisation).
 inline cudaError_t pick_enqueue(const PickArgs &a, int8_t *d_fb_idx, int64_t lambda, int sm_count, cudaStream_t stream, uint64_t *launches) {
     cudaError_t e = cudaMemsetAsync(a.st, 0, sizeof(PickState), stream);
@@ -275,9 +315,10 @@ inline cudaError_t pick_enqueue(const PickArgs &a, int8_t *d_fb_idx, int64_t lam
     attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim            = dim3(2, (a.nfb + PT_CHUNK - 1) / PT_CHUNK);
+    cfg.gridDim            = dim3((a.end_gi + PT_ROWS - 1) / PT_ROWS, (a.nfb + PT_CHUNK_N - 1) / PT_CHUNK_N);
     cfg.blockDim           = dim3(PT_THREADS);
-    cfg.dynamicSmemBytes   = 0;
+    cfg.dynamicSmemBytes   = PT_SMEM;
+
     cfg.stream             = stream;
     cfg.attrs              = attr;
     cfg.numAttrs           = 1;

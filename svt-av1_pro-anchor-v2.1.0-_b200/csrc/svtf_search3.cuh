@@ -22,10 +22,9 @@ constexpr int S3_SMEM_WORDS = C3_SMEM_WORDS_F;
 // one tap on a pair, fp16: acc += w * constrain(p - x)   (svtf_cdef3.cuh, cdef3_row_f)
 __device__ __forceinline__ __half2 s3_constrain(const __half2 d, const Tap3F &t) {
     const __half2 k1024 = u2h(0x64006400u), kn1024 = u2h(0xE400E400u), kone = u2h(0x3C003C00u);
-    const __half2 a = __habs2(d);
-    const __half2 u = __hmin2(a, __hfma2(a, t.nsc, t.C));
-    const __half2 v = __hfma2_relu(__hadd2(u, k1024), kone, kn1024);
-    return u2h(h2u(v) | (h2u(d) & 0x80008000u));
+    // min(a, ceil(z)) = ceil(min(a, z)) for integer a: the min follows the rounding and takes the sign along (svtf_cdef5.cuh)
+    const __half2 v = __hfma2_relu(__hadd2(__hfma2(__habs2(d), t.nsc, t.C), k1024), kone, kn1024);
+    return u2h(pk_xsmin(h2u(d), h2u(v)));
 }
 
 // One row of NP pairs: secondary sums for the three non-zero secondary strengths and the clamp bounds
