@@ -806,13 +806,44 @@ def gpu_search_leg(H, S, geom, wl, ctxs, steps, np):
     for _ in range(steps):
         resident(ctxs[0])
     single = round(nfb * steps / (time.perf_counter() - t0), 1)
+    # the search kernel alone (device time between two syncs; launch included), for the issue roofline below
+    ctxs[0].sync()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ctxs[0].cdef_seg_search(cfg, want_outputs=False)
+    ctxs[0].sync()
+    kernel_ms = (time.perf_counter() - t0) / steps * 1e3
     pin_rec.close()
     pin_src.close()
     pin_mi.close()
     return {"metric": "CDEF-search filter blocks/s (64 strengths, 3 planes, + finish_cdef_search)", "value": out["value"], "e2e": out["e2e"],
-            "unit": "filter blocks/s", "pictures_in_flight": len(ctxs), "one_picture_at_a_time": single,
+            "unit": "filter blocks/s", "pictures_in_flight": len(ctxs), "one_picture_at_a_time": single, "search_kernel_ms": round(kernel_ms, 4),
             "workload": "4K 10-bit, cdef_level 1 list (16 primary + 48 secondary), subsampling 1",
             "picked_cdef_bits": int(picks[0][0].cdef_bits)}
+
+
+def search_roofline(search, geom, sms, clocks):
+    """SURVEY 8(d) for the search: it is compute-bound (93 tap evaluations per compulsory byte), so the roofline is instruction issue.
+    Live: the search kernel's time (this run) -> warp instructions per second against SMs x 4 schedulers x the SM clock sampled during the
+    run, and the reference-equivalent tap evaluations per second (a separable kernel is credited with what cdef_seg_search would do:
+    samples x strengths x 12).  From the committed ncu capture of the same kernel (profiles/search_roofline.json): the instruction count
+    per launch and the issue-slot / ALU-pipe / FMA-pipe utilisation."""
+    path = os.path.join(ROOT, "profiles", "search_roofline.json")
+    ncu = json.load(open(path)) if os.path.exists(path) else {}
+    nfb = ((geom.mi_rows + 15) // 16) * ((geom.mi_cols + 15) // 16)
+    samples = geom.mi_rows * 4 * geom.mi_cols * 4 * 3 // 2
+    tap_evals = samples * 64 * 12
+    t = search["search_kernel_ms"] * 1e-3
+    mhz = (clocks or {}).get("sm_mhz") or ncu.get("sm_mhz_assumed", 1965)
+    peak = sms * 4 * mhz * 1e6
+    wi = ncu.get("warp_instructions_per_launch")
+    return {"bound": "issue", "kernel": "cdef_search3_kernel", "search_kernel_ms": search["search_kernel_ms"],
+            "warp_instructions_per_launch": wi, "achieved": round(wi / t / 1e9, 1) if wi else None, "peak": round(peak / 1e9, 1),
+            "unit": "G warp-instructions/s", "frac": round(wi / t / peak, 4) if wi else None,
+            "ncu": {k: ncu.get(k) for k in ("issue_active_pct", "alu_pipe_pct", "fma_pipe_pct", "lsu_pipe_pct", "source")},
+            "reference_equivalent_tap_evals_per_picture": tap_evals,
+            "tap_evals_per_s_kernel": round(tap_evals / t / 1e9, 1), "tap_evals_per_s_with_pick_pipelined": round(search["value"] / nfb * tap_evals / 1e9, 1),
+            "tap_unit": "G tap evaluations/s (samples x 64 strengths x 12 taps, what cdef_seg_search evaluates)"}
 
 
 def run_reference_arm(args):
@@ -1035,10 +1066,10 @@ def main():
     # against the sum of the stages it replaces (3b + 4b = 7b), as 8(d) says; chain_frac is the whole chain against the 8(d) sum.
     survey_bytes = ((3 * b + 0.5) + 3 * b + 4 * b) * npx
     if UNFUSED:
-        names = ["deblock_kernel", "cdef3_kernel", "ccso_kernel"]
+        names = ["deblock_kernel", "cdef5_kernel", "ccso_kernel"]
         alg_bytes = [(3 * b + 0.5) * npx, 3 * b * npx, 4 * b * npx]
     else:
-        names = ["deblock_kernel", "cdef3_kernel+ccso"]
+        names = ["deblock_kernel", "cdef5_kernel+ccso"]
         alg_bytes = [(3 * b + 0.5) * npx, (3 * b + 4 * b) * npx]  # a fused launch is scored against the sum of the stages it replaces (8(d))
     nst = len(names)
     stage_ms = [statistics.mean(e[k].elapsed_time(e[k + 1]) for e in stage_events) for k in range(nst)]
@@ -1142,6 +1173,8 @@ def main():
     c5 = streams_1080p_leg(H, S, torch, dist, dev, local, rank, world, max(5, args.steps))
     s8k = None if args.no_stripes else stripes_8k_leg(H, S, torch, dist, dev, local, rank, world, np, args.steps)
     search = gpu_search_leg(H, S, geom, wls[0], ctxs[:args.search_inflight], max(3, args.steps // 2), np) if rank == 0 else None
+    if search:
+        search["roofline"] = search_roofline(search, geom, torch.cuda.get_device_properties(dev).multi_processor_count, clocks)
     derive = ccso_derive_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     lrl = lr_leg(H, S, geom, wls[0], ctxs[0], np, world == 1 and not args.no_cpu) if rank == 0 else None
     side = side_info_leg(H, S, geom, ctxs[0], np) if rank == 0 else None
