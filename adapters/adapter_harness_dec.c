@@ -144,3 +144,8 @@ EbErrorType svt_block_on_semaphore(EbHandle h) { (void)h; harness_unreachable("s
 EbErrorType svt_block_on_mutex(EbHandle h) { (void)h; harness_unreachable("svt_block_on_mutex"); return EB_ErrorNone; }
 EbErrorType svt_release_mutex(EbHandle h) { (void)h; harness_unreachable("svt_release_mutex"); return EB_ErrorNone; }
 void        svt_aom_pad_pic(EbDecHandle *d) { (void)d; harness_unreachable("svt_aom_pad_pic"); }
+void        svt_av1_upscale_normative_rows(const Av1Common *cm, const uint8_t *src, int src_stride, uint8_t *dst, int dst_stride, int rows, int sub_x,
+                                           int bd, Bool is_16bit_pipeline) { /* super-resolution streams: application test only */
+    (void)cm, (void)src, (void)src_stride, (void)dst, (void)dst_stride, (void)rows, (void)sub_x, (void)bd, (void)is_16bit_pipeline;
+    harness_unreachable("svt_av1_upscale_normative_rows");
+}

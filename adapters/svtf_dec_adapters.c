@@ -46,7 +46,8 @@
 typedef struct {
     const EbDecHandle *dec;
     svtf_ctx          *ctx;
-    svtf_geom          geom;
+    svtf_geom          geom;     /* of the stage running: the coded (narrow) picture up to CCSO, the upscaled one behind super-resolution */
+    svtf_geom          max_geom; /* what the context was created for: the upscaled width */
     int                resident;  /* the frame being decoded is on the device */
     int                have_tx;   /* the mi words on the device carry the transform sizes (set by the LF call) */
     uint8_t           *dbk[3];    /* stand-alone loop restoration: the deblocked rows around the stripe boundaries */
@@ -72,8 +73,8 @@ static void die(const char *where, svtf_ctx *ctx) {
     } while (0)
 
 /* Call counters, printed at exit when SVTF_ADAPTER_STATS is set (see svtf_enc_adapters.c). */
-enum { DS_LF, DS_CDEF, DS_CCSO, DS_LR, DS_N };
-static const char *const g_stat_name[DS_N] = {"dec_loop_filter_frame", "dec_cdef_frame", "dec_ccso_frame", "dec_loop_restoration_filter_frame"};
+enum { DS_LF, DS_CDEF, DS_CCSO, DS_LR, DS_SUPERRES, DS_N };
+static const char *const g_stat_name[DS_N] = {"dec_loop_filter_frame", "dec_cdef_frame", "dec_ccso_frame", "dec_loop_restoration_filter_frame", "dec_superres_upscale"};
 static unsigned long     g_stat[DS_N];
 static pthread_once_t    g_stat_once = PTHREAD_ONCE_INIT;
 static void              stat_print(void) {
@@ -93,22 +94,27 @@ static void stat_hit(int which) {
     __sync_fetch_and_add(&g_stat[which], 1);
 }
 
-static svtf_geom geom_of(const EbDecHandle *dec, const EbPictureBufferDesc *pic) {
+/* after_superres: the picture as the stages behind the super-resolution upscale see it (loop restoration, EbDecParseObu.c:2434-2455) */
+static svtf_geom geom_of(const EbDecHandle *dec, const EbPictureBufferDesc *pic, int after_superres) {
     const FrameHeader *fh = &dec->frame_header;
     svtf_geom          g;
     g.width        = fh->frame_size.frame_width; /* the deblock limit, EbDecLF.c:119-124 */
     g.height       = fh->frame_size.frame_height;
     g.mi_cols      = fh->mi_cols;
     g.mi_rows      = fh->mi_rows;
+    if (after_superres && fh->frame_size.superres_upscaled_width > fh->frame_size.frame_width) {
+        g.width   = fh->frame_size.superres_upscaled_width;
+        g.mi_cols = 2 * ((g.width + 7) >> 3);
+    }
     g.bit_depth    = pic->bit_depth;
     g.sample_bytes = (pic->bit_depth > EB_EIGHT_BIT || dec->is_16bit_pipeline) ? 2 : 1;
     return g;
 }
 
-static DecSlot *slot_for(const EbDecHandle *dec, const EbPictureBufferDesc *pic) {
+static DecSlot *slot_for_at(const EbDecHandle *dec, const EbPictureBufferDesc *pic, int after_superres) {
     pthread_mutex_lock(&g_lock);
     DecSlot        *free_slot = NULL, *s = NULL;
-    const svtf_geom g = geom_of(dec, pic);
+    const svtf_geom g = geom_of(dec, pic, 1), now = geom_of(dec, pic, after_superres);
     for (int i = 0; i < SVTF_DEC_MAX_CACHED; i++) {
         if (g_slots[i].dec == dec) {
             s = &g_slots[i];
@@ -117,7 +123,7 @@ static DecSlot *slot_for(const EbDecHandle *dec, const EbPictureBufferDesc *pic)
         if (!g_slots[i].dec && !free_slot)
             free_slot = &g_slots[i];
     }
-    if (s && memcmp(&s->geom, &g, sizeof(g))) { /* a new sequence / frame size on the same handle */
+    if (s && memcmp(&s->max_geom, &g, sizeof(g))) { /* a new sequence / frame size on the same handle */
         svtf_ctx_destroy(s->ctx);
         for (int p = 0; p < 3; p++) free(s->dbk[p]);
         memset(s, 0, sizeof(*s));
@@ -128,15 +134,19 @@ static DecSlot *slot_for(const EbDecHandle *dec, const EbPictureBufferDesc *pic)
             fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: more than %d decoder handles\n", SVTF_DEC_MAX_CACHED);
             abort();
         }
-        s       = free_slot;
-        s->dec  = dec;
-        s->geom = g;
-        if (svtf_ctx_create(g_device, &s->geom, &s->ctx) != SVTF_OK)
+        s           = free_slot;
+        s->dec      = dec;
+        s->max_geom = g;
+        if (svtf_ctx_create(g_device, &s->max_geom, &s->ctx) != SVTF_OK)
             die("svtf_ctx_create", NULL);
     }
+    if (memcmp(&s->geom, &now, sizeof(now))) /* another picture size: nothing on the device is this picture */
+        s->resident = 0;
+    s->geom = now;
     pthread_mutex_unlock(&g_lock);
     return s;
 }
+static DecSlot *slot_for(const EbDecHandle *dec, const EbPictureBufferDesc *pic) { return slot_for_at(dec, pic, 0); }
 
 void svtf_dec_adapter_release(const struct EbDecHandle *dec) {
     pthread_mutex_lock(&g_lock);
@@ -212,7 +222,14 @@ static void end_frame(DecSlot *s, const EbPictureBufferDesc *pic) {
 
 /* Copy the resident frame back into `pic` (the end of a resident chain). */
 void svtf_dec_adapter_fetch(const struct EbDecHandle *dec, void *pic) {
-    DecSlot *s = slot_for(dec, (const EbPictureBufferDesc *)pic);
+    DecSlot *s = NULL; /* whatever is resident: after a super-resolution upscale that is the wide picture */
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < SVTF_DEC_MAX_CACHED; i++)
+        if (g_slots[i].dec == dec)
+            s = &g_slots[i];
+    pthread_mutex_unlock(&g_lock);
+    if (!s)
+        s = slot_for(dec, (const EbPictureBufferDesc *)pic);
     if (!s->resident) {
         fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: svtf_dec_adapter_fetch: no resident frame for this handle\n");
         abort();
@@ -404,15 +421,24 @@ void dec_ccso_frame(EbPictureBufferDesc *frame, EbDecHandle *dec_handle, uint16_
  * Restoration units: LrCtxt.lr_unit[plane][unit_row * lr_stride + unit_col] (:341; written by the parser,
  * EbDecParseBlock.c:2692) -> the dense [vert][horz] array of svtf_lr_apply_frame; the decoder's "use the previous unit when
  * less than half a unit remains" (:333-338) is the same count as svtf_lr_units.
- * Superres is not supported (the reference upscales between CDEF and the second save; that stage is not on the device).
+ * Super-resolution: svt_av1_superres_upscale below; loop restoration then runs on the upscaled picture, its stripe borders are the
+ * deblocked rows upscaled (lr_stripe_rows stand-alone; on the device in a resident chain).
  */
-static void lr_stripe_rows(DecSlot *s, const EbPictureBufferDesc *pic) {
+void svt_av1_upscale_normative_rows(const Av1Common *cm, const uint8_t *src, int src_stride, uint8_t *dst, int dst_stride, int rows,
+                                    int sub_x, int bd, Bool is_16bit_pipeline); /* Common/Codec/EbSuperRes.c:214 */
+
+/* Stand-alone loop restoration: the two deblocked rows above and below every 64-row stripe, kept in an adapter-owned sparse picture
+ * of the size loop restoration works on.  With super-resolution that is the UPSCALED size and the rows are upscaled on the way in,
+ * as svt_aom_save_deblock_boundary_lines does (Common/Codec/EbRestoration.c:1547-1560) — with the reference's own row function: four
+ * rows per stripe are not worth a launch. */
+static void lr_stripe_rows(DecSlot *s, const EbDecHandle *dec, const EbPictureBufferDesc *pic) {
     const int sb = s->geom.sample_bytes;
+    const int sr = s->max_geom.width > s->geom.width; /* s->geom: the coded picture (this runs after the loop filter) */
     void     *pp[3];
     int32_t   st[3];
     plane_ptrs(pic, sb, pp, st);
     for (int p = 0; p < 3; p++) {
-        const int ss = p ? 1 : 0, cw = (s->geom.mi_cols * 4) >> ss, chh = (s->geom.mi_rows * 4) >> ss;
+        const int ss = p ? 1 : 0, cw = (s->max_geom.mi_cols * 4) >> ss, chh = (s->max_geom.mi_rows * 4) >> ss;
         const int pw = (s->geom.width + ss) >> ss, ph = (s->geom.height + ss) >> ss, sh = 64 >> ss, off = 8 >> ss;
         if (!s->dbk[p] && !(s->dbk[p] = (uint8_t *)calloc((size_t)cw * chh, sb)))
             die("malloc(deblocked rows)", s->ctx);
@@ -421,10 +447,19 @@ static void lr_stripe_rows(DecSlot *s, const EbPictureBufferDesc *pic) {
             if (y0 >= ph)
                 break;
             for (int i = 0; i < RESTORATION_CTX_VERT; i++) {
+                int rows[2], n = 0;
                 if (k > 0)
-                    memcpy(s->dbk[p] + (size_t)(y0 - 2 + i) * cw * sb, (uint8_t *)pp[p] + (size_t)(y0 - 2 + i) * st[p] * sb, (size_t)pw * sb);
+                    rows[n++] = y0 - 2 + i;
                 if (y1 + i < ph)
-                    memcpy(s->dbk[p] + (size_t)(y1 + i) * cw * sb, (uint8_t *)pp[p] + (size_t)(y1 + i) * st[p] * sb, (size_t)pw * sb);
+                    rows[n++] = y1 + i;
+                for (int j = 0; j < n; j++) {
+                    uint8_t       *d   = s->dbk[p] + (size_t)rows[j] * cw * sb;
+                    const uint8_t *src = (const uint8_t *)pp[p] + (size_t)rows[j] * st[p] * sb;
+                    if (sr)
+                        svt_av1_upscale_normative_rows(&dec->cm, src, st[p], d, cw, 1, ss, s->geom.bit_depth, sb == 2);
+                    else
+                        memcpy(d, src, (size_t)pw * sb);
+                }
             }
         }
     }
@@ -433,10 +468,12 @@ static void lr_stripe_rows(DecSlot *s, const EbPictureBufferDesc *pic) {
 
 void svt_aom_dec_av1_loop_restoration_save_boundary_lines(EbDecHandle *dec_handle, int after_cdef) {
     EbPictureBufferDesc *pic = dec_handle->cur_pic_buf[0]->ps_pic_buf;
-    DecSlot             *s   = slot_for(dec_handle, pic);
-    if (after_cdef || (g_resident && s->resident))
+    if (after_cdef)
         return;
-    lr_stripe_rows(s, pic);
+    DecSlot *s = slot_for(dec_handle, pic);
+    if (g_resident && s->resident)
+        return;
+    lr_stripe_rows(s, dec_handle, pic);
 }
 
 void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int optimized_lr, int enable_flag) {
@@ -444,13 +481,9 @@ void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int 
         return;
     stat_hit(DS_LR);
     EbPictureBufferDesc *pic = dec_handle->cur_pic_buf[0]->ps_pic_buf;
-    DecSlot             *s   = slot_for(dec_handle, pic);
+    DecSlot             *s   = slot_for_at(dec_handle, pic, 1); /* the upscaled picture when the frame uses super-resolution */
     const LrCtxt        *lc  = (const LrCtxt *)dec_handle->pv_lr_ctxt;
     const FrameHeader   *fh  = &dec_handle->frame_header;
-    if (fh->frame_size.superres_upscaled_width != fh->frame_size.frame_width) {
-        fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: loop restoration with superres is not supported\n");
-        abort();
-    }
     svtf_lr_params lr;
     svtf_lr_unit  *units[3] = {NULL, NULL, NULL};
     memset(&lr, 0, sizeof(lr));
@@ -489,7 +522,7 @@ void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int 
                                 "(svt_aom_dec_av1_loop_restoration_save_boundary_lines(dec, 0) was not called for this frame)\n");
                 abort();
             }
-            const int cw = s->geom.mi_cols * 4;
+            const int cw = s->max_geom.mi_cols * 4;
             CHECK(svtf_upload_pre_cdef(s->ctx, s->dbk[0], cw, s->dbk[1], cw >> 1, s->dbk[2], cw >> 1), s->ctx);
             CHECK(svtf_sync(s->ctx), s->ctx);
         }
@@ -501,6 +534,49 @@ void svt_aom_dec_av1_loop_restoration_filter_frame(EbDecHandle *dec_handle, int 
     if (!g_resident)
         end_frame(s, pic), s->resident = 0;
     for (int p = 0; p < 3; p++) free(units[p]);
+}
+
+/* ----------------------------------------------------------------------------------------------------
+ * svt_av1_superres_upscale (Decoder/Codec/EbDecSuperRes.c:119), called between CDEF / CCSO and loop restoration
+ * (EbDecParseObu.c:2434-2438): the reference copies the picture aside, clears it and runs svt_av1_upscale_normative_rows per plane
+ * into the same buffers, then calls the picture `superres_upscaled_width` wide.  Here: one launch per plane on the device
+ * (svtf_superres_upscale_frame: the picture, and in a resident chain the deblocked picture loop restoration borrows its stripe
+ * borders from); stand-alone the picture is uploaded narrow and written back wide.  The padding the reference zeroes is rewritten
+ * by the padding that follows loop restoration (svt_aom_pad_pic / the `_mt` restoration stage).
+ * `cm` is EbDecHandle.cm (the only caller passes &dec_handle_ptr->cm), which is how the handle is found.
+ * ---------------------------------------------------------------------------------------------------- */
+#include <stddef.h>
+#include "EbInterPrediction.h" /* RS_SUBPEL_BITS for the table below */
+#include "EbSuperRes.h"
+void svt_av1_superres_upscale(Av1Common *cm, FrameHeader *frm_hdr, SeqHeader *seq_hdr, EbPictureBufferDesc *recon_picture_src, int enable_flag) {
+    (void)seq_hdr;
+    if (!enable_flag || av1_superres_unscaled(&frm_hdr->frame_size))
+        return;
+    stat_hit(DS_SUPERRES);
+    const EbDecHandle *dec = (const EbDecHandle *)((const char *)cm - offsetof(EbDecHandle, cm));
+    DecSlot           *s   = slot_for(dec, recon_picture_src);
+    void              *p[3];
+    int32_t            st[3];
+    plane_ptrs(recon_picture_src, s->geom.sample_bytes, p, st);
+    const int resident = g_resident && s->resident;
+    if (!resident) {
+        CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
+        CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    }
+    svtf_superres_params sr;
+    memset(&sr, 0, sizeof(sr));
+    sr.upscaled_width       = frm_hdr->frame_size.superres_upscaled_width;
+    sr.superres_denominator = frm_hdr->frame_size.superres_denominator;
+    sr.tile_cols            = cm->tiles_info.tile_cols;
+    for (int j = 0; j <= sr.tile_cols && j < 65; j++) sr.tile_col_start_mi[j] = cm->tiles_info.tile_col_start_mi[j];
+    sr.filters = &av1_resize_filter_normative[0][0];
+    CHECK(svtf_superres_upscale_frame(s->ctx, &sr), s->ctx);
+    s->geom = s->max_geom; /* the picture of this frame is the upscaled one from here on */
+    recon_picture_src->width = (uint16_t)sr.upscaled_width;
+    if (!resident) {
+        CHECK(svtf_download_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+        s->resident = 0;
+    }
 }
 
 /* ----------------------------------------------------------------------------------------------------

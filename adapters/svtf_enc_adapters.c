@@ -151,8 +151,13 @@ static svtf_geom max_geom_of(const PictureControlSet *pcs, const svtf_geom *g) {
 /* The GPU context of a picture.  Contexts are cached per pcs pointer — the pipeline recycles a small pool of PictureControlSets, so
  * a recycled pcs finds its surfaces allocated — but the geometry is recomputed on EVERY entry: a recycled pcs may carry another
  * super-resolution / resize width, and then the context is rebuilt and nothing stale (resident picture included) survives. */
-static CtxSlot *slot_for(const PictureControlSet *pcs) {
-    const svtf_geom g = geom_of(pcs), mg = max_geom_of(pcs, &g);
+static CtxSlot *slot_for_at(const PictureControlSet *pcs, int after_superres) {
+    svtf_geom       g  = geom_of(pcs);
+    const svtf_geom mg = max_geom_of(pcs, &g);
+    /* the stages behind the super-resolution upscale (EbCdefProcess.c:675-677: restoration search and apply, reference padding) see
+     * the upscaled picture; cm->frm_size.frame_width and cm->mi_cols keep describing the coded (narrow) one */
+    if (after_superres)
+        g.width = mg.width, g.mi_cols = mg.mi_cols;
     pthread_mutex_lock(&g_lock);
     CtxSlot *free_slot = NULL, *s = NULL;
     for (int i = 0; i < SVTF_MAX_CACHED; i++) {
@@ -185,6 +190,8 @@ static CtxSlot *slot_for(const PictureControlSet *pcs) {
     pthread_mutex_unlock(&g_lock);
     return s;
 }
+
+static CtxSlot *slot_for(const PictureControlSet *pcs) { return slot_for_at(pcs, 0); }
 
 /* Release the cached context of a picture (call where the reference recycles the pcs). */
 void svtf_adapter_release(const PictureControlSet *pcs) {
@@ -301,7 +308,15 @@ static void end_picture(CtxSlot *s, const EbPictureBufferDesc *pic) {
 }
 
 void svtf_adapter_fetch(const PictureControlSet *pcs, void *pic) {
-    CtxSlot *s = slot_for(pcs);
+    /* whatever is resident: after a super-resolution upscale that is the wide picture */
+    CtxSlot *s = NULL;
+    pthread_mutex_lock(&g_lock);
+    for (int i = 0; i < SVTF_MAX_CACHED; i++)
+        if (g_slots[i].pcs == pcs)
+            s = &g_slots[i];
+    pthread_mutex_unlock(&g_lock);
+    if (!s)
+        s = slot_for(pcs);
     if (!s->resident) {
         fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: svtf_adapter_fetch: no resident picture for this pcs\n");
         abort();
@@ -781,7 +796,7 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
     stat_hit(ST_LR_APPLY);
     (void)rst_tmpbuf;
     PictureControlSet *pcs = cm->child_pcs;
-    CtxSlot           *s   = slot_for(pcs);
+    CtxSlot           *s   = slot_for_at(pcs, 1);
     const int          sb  = s->geom.sample_bytes;
     svtf_lr_params     lr;
     svtf_lr_unit      *units[3] = {NULL, NULL, NULL};
@@ -925,7 +940,7 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     stat_hit(ST_LR_SEARCH);
     Av1Common        *cm = pcs->ppcs->av1_cm;
     const Macroblock *x  = pcs->ppcs->av1x;
-    CtxSlot          *s  = slot_for(pcs);
+    CtxSlot          *s  = slot_for_at(pcs, 1);
     if (cm->use_boundaries_in_rest_search) {
         fprintf(stderr, "Svt[error]: svtfilt_b200 adapter: restoration_seg_search needs use_boundaries_in_rest_search = 0\n");
         abort();
@@ -1062,7 +1077,7 @@ void svtf_pad_ref_pictures(PictureControlSet *pcs, SequenceControlSet *scs) {
     svt_aom_get_recon_pic(pcs, &ref16, 1);
     const Bool is_16bit = scs->static_config.encoder_bit_depth > EB_EIGHT_BIT;
     const Bool pipe16   = scs->is_16bit_pipeline;
-    CtxSlot   *s        = slot_for(pcs);
+    CtxSlot   *s        = slot_for_at(pcs, 1);
     if (!(g_resident && s->resident)) { /* stand-alone: the filtered picture is in the recon buffer */
         const EbPictureBufferDesc *pic = (is_16bit || pipe16) ? ref16 : ref8;
         void                      *p[3];

@@ -145,6 +145,8 @@ def main():
         s = guard_function(s, sig)
     write(rel, s)
 
+    rel = "Source/Lib/Decoder/Codec/EbDecSuperRes.c"
+    write(rel, guard_function(read(rel), "void svt_av1_superres_upscale(Av1Common *cm, FrameHeader *frm_hdr, SeqHeader *seq_hdr,"))
     # the multi-threaded variants (every thread calls them; the adapters run the frame-level launch on the calling thread)
     rel = "Source/Lib/Decoder/Codec/EbDecProcess.c"
     s = read(rel)
