@@ -113,10 +113,12 @@ static svtf_geom geom_of(const PictureControlSet *pcs) {
     svtf_geom                 g;
     /* unpadded size: the width/height svt_av1_setup_dst_planes gives the deblock (EbDeblockingFilter.c:99-101) */
     g.width        = scs->max_input_luma_width - scs->max_input_pad_right;
-    /* a frame coded with super-resolution is narrower than the input: cm->frm_size carries its width (and mi_cols matches) */
-    if (cm->frm_size.frame_width && cm->frm_size.superres_denominator > SCALE_NUMERATOR)
-        g.width = cm->frm_size.frame_width;
     g.height       = scs->max_input_luma_height - scs->max_input_pad_bottom;
+    /* a frame coded with super-resolution is narrower than the input, one coded with reference scaling (resize_mode) narrower and
+     * lower: the picture the stages work on is ppcs->enhanced_pic (what svt_av1_filter_block_plane_vert/_horz cut their ranges to,
+     * EbDeblockingFilter.c:305-322), and cm->mi_cols / mi_rows match it */
+    if (pcs->ppcs->frame_superres_enabled || pcs->ppcs->frame_resize_enabled)
+        g.width = pcs->ppcs->enhanced_pic->width, g.height = pcs->ppcs->enhanced_pic->height;
     g.mi_cols      = cm->mi_cols;
     g.mi_rows      = cm->mi_rows;
     g.bit_depth    = scs->static_config.encoder_bit_depth;

@@ -248,7 +248,9 @@ static const lf_tables *lvl_tab(const lf_tables *t, const sb_tables *sbt, int mi
 static int lpf_params(const svtf_geom *g, const svtf_mi_t *mi, int mi_stride, const lf_tables *t, const sb_tables *sbt, int plane,
                       int dir, int x, int y, int *level, int *tx_dim_log2) {
     const int ss = plane ? 1 : 0;
-    const int pw = g->width >> ss, ph = g->height >> ss;
+    /* a chroma unit has edges while its LUMA position is inside the picture: (w + 1) >> 1, not w >> 1, when a super-resolution frame is
+     * odd-sized (Encoder/Codec/EbDeblockingFilter.c:305-322, Decoder/Codec/EbDecLF.c:116-121; unscaled encoder pictures are even) */
+    const int pw = (g->width + ss) >> ss, ph = (g->height + ss) >> ss;
     *tx_dim_log2 = 2;
     if (x >= pw || y >= ph)
         return 0;

@@ -819,6 +819,14 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
     a.mi        = c->d_mi;
     a.mi_stride = c->mi_stride;
     a.d         = dims_of(c->geom);
+    // "no deblocking is required" limit of set_lpf_parameters: a chroma unit has edges while its LUMA position is inside the picture, i.e.
+    // up to (w + 1) >> 1 — one 4x4 column more than w >> 1 when a super-resolution frame is 8k + 1 samples wide.  Encoder: the x_range /
+    // y_range cut of svt_av1_filter_block_plane_vert/_horz for scaled frames (Encoder/Codec/EbDeblockingFilter.c:305-322; unscaled pictures
+    // have even sizes); decoder: dec_set_lpf_parameters tests luma coordinates against frame_width / frame_height (EbDecLF.c:116-121).
+    for (int p = 0; p < 3; p++) {
+        const int ss = p ? 1 : 0;
+        a.lim_w[p] = (c->geom.width + ss) >> ss, a.lim_h[p] = (c->geom.height + ss) >> ss;
+    }
     int total   = 0;
     // rows to produce: the stripe's own plus the 8 beyond each interior boundary that its CDEF/CCSO read (tile t
     // of a plane writes rows [64t-8, 64t+56) of that plane)

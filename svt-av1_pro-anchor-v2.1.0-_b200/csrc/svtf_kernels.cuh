@@ -108,6 +108,7 @@ struct DeblockArgs {
     int              tiles_x[3], tiles_y[3], tile_base[3]; // linearised (plane, ty, tx) grid
     int              ty0[3];                               // first tile row of the launch (stripe window)
     unsigned         plane_mask;                           // bit p: plane p is filtered (else copied)
+    int              lim_w[3], lim_h[3];                   // units at or beyond these plane coordinates have no edges (set_lpf_parameters :175)
     LfTables         t;
     // per-superblock level tables [sb][plane][256] (delta_lf_present with the decoder's per-SB deltas) or nullptr
     const uint8_t *sb_lvl;
@@ -245,7 +246,7 @@ __global__ void __launch_bounds__(DBK_THREADS, 8) deblock_kernel(const __grid_co
     const int ty  = tyl + a.ty0[plane];
     const int ss = plane ? 1 : 0;
     const int cw = (a.d.mi_cols * 4) >> ss, ch = (a.d.mi_rows * 4) >> ss;
-    const int pw = a.d.width >> ss, ph = a.d.height >> ss;
+    const int pw = a.lim_w[plane], ph = a.lim_h[plane];
     const int X0 = tx * DBK_TILE - 16, Y0 = ty * DBK_TILE - 16;
     const T  *in    = static_cast<const T *>(a.in.p[plane]);
     T        *out   = static_cast<T *>(a.out.p[plane]);

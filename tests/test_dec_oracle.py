@@ -13,7 +13,9 @@ def refdec(H):
 
 
 @pytest.mark.parametrize("w,h,bd,sb,seed", [(136, 72, 8, 1, 1), (200, 136, 10, 2, 2), (64, 64, 8, 1, 3), (328, 200, 10, 2, 4), (72, 200, 12, 2, 5),
-                                            (264, 136, 8, 2, 6)])
+                                            (264, 136, 8, 2, 6),
+                                            # odd sizes = frames coded with super-resolution / reference scaling; 145 = 8k + 1: the chroma unit at x = 72 has edges
+                                            (145, 81, 8, 1, 7), (137, 75, 10, 2, 8)])
 def test_decoder_deblock_matches_oracle(H, orc, refdec, w, h, bd, sb, seed):
     S = H.S
     g = S.make_geom(w, h, bd, sb)

@@ -152,11 +152,13 @@ def test_encoder_superres_identical(tmp_path, depth):
     assert st["superres_upscale_frame"] >= 4 and st["restoration_search"] >= 1, st
 
 
-def test_decoder_superres_stream_identical(tmp_path):
+@pytest.mark.parametrize("denom", [12, 11])  # 11: the coded picture is 465 = 8k + 1 samples wide (one more chroma 4x4 column has edges)
+def test_decoder_superres_stream_identical(tmp_path, denom):
     """svt_av1_superres_upscale (Decoder/Codec/EbDecSuperRes.c:119) and loop restoration behind it, single- and multi-threaded."""
     w, h, frames = 640, 360, 4
     clip = _clip(tmp_path, w, h, frames, 8)
-    _encode("SvtAv1EncApp_ref", clip, w, h, frames, 8, 6, str(tmp_path / "s"), SUPERRES)
+    _encode("SvtAv1EncApp_ref", clip, w, h, frames, 8, 6, str(tmp_path / "s"),
+            ("--superres-mode", "1", "--superres-denom", str(denom), "--superres-kf-denom", str(denom), "--crf", "50"))
     ivf, want = str(tmp_path / "s.ivf"), _md5(str(tmp_path / "s.yuv"))
     _decode("SvtAv1DecApp_ref", ivf, str(tmp_path / "dec_ref.yuv"))
     err = _decode("SvtAv1DecApp_b200", ivf, str(tmp_path / "dec_b200.yuv"))
@@ -166,3 +168,28 @@ def test_decoder_superres_stream_identical(tmp_path):
     r = subprocess.run([_bin("dec_threads_b200"), ivf, str(tmp_path / "mt.yuv"), "3"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     assert _md5(str(tmp_path / "mt.yuv")) == want
+
+
+MATRIX = {
+    "aq-mode 1 (segmentation features reach the level tables)": (640, 360, 8, 5, 6, ("--aq-mode", "1", "--crf", "45")),
+    "aq-mode 2 (delta q)": (640, 360, 8, 5, 6, ("--aq-mode", "2", "--crf", "45")),
+    "2x2 tiles": (640, 360, 8, 5, 6, ("--tile-rows", "1", "--tile-columns", "1", "--crf", "45")),
+    "2 tile columns + superres 8/11 (465 = 8k + 1 samples wide)": (640, 360, 8, 4, 6, ("--tile-columns", "1", "--superres-mode", "1", "--superres-denom", "11",
+                                                                                        "--superres-kf-denom", "11", "--crf", "50")),
+    "superres 8/9 (569 wide)": (640, 360, 8, 3, 6, ("--superres-mode", "1", "--superres-denom", "9", "--superres-kf-denom", "9", "--crf", "50")),
+    "superres with a random denominator per frame": (640, 360, 8, 5, 6, ("--superres-mode", "2", "--crf", "50")),
+    "reference scaling (resize-mode 1, 8/12)": (640, 360, 8, 4, 6, ("--resize-mode", "1", "--resize-denom", "12", "--resize-kf-denom", "12", "--crf", "45")),
+    "250x150 10-bit, preset 4": (250, 150, 10, 4, 4, ("--crf", "45")),
+    "low delay, preset 10": (640, 360, 8, 6, 10, ("--pred-struct", "1", "--crf", "45")),
+    "screen content (intra block copy switches the filters off)": (640, 360, 8, 3, 6, ("--scm", "1", "--crf", "45")),
+}
+
+
+@pytest.mark.parametrize("name", list(MATRIX))
+def test_encoder_option_matrix_identical(tmp_path, name):
+    """Encoder options that change what reaches the filter stages: segmentation and delta-q level tables, tiles, super-resolution widths
+    of every residue, reference scaling (both dimensions change per frame on recycled picture control sets), odd sizes.  Round 2 found two
+    defects with this matrix: the chroma deblock limit of odd-width pictures (w >> 1 instead of (w + 1) >> 1) and the geometry of
+    scaled frames."""
+    w, h, depth, frames, preset, extra = MATRIX[name]
+    _encode_both(tmp_path, w, h, frames, depth, preset, extra)

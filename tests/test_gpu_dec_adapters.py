@@ -24,7 +24,8 @@ def refdec(H):
     return H.DecDriver() if H.refdec_available() else None
 
 
-@pytest.mark.parametrize("w,h,bd,sb,seed", [(136, 72, 8, 1, 1), (200, 136, 10, 2, 2), (328, 200, 10, 2, 3), (264, 136, 8, 2, 4), (72, 200, 12, 2, 5)])
+@pytest.mark.parametrize("w,h,bd,sb,seed", [(136, 72, 8, 1, 1), (200, 136, 10, 2, 2), (328, 200, 10, 2, 3), (264, 136, 8, 2, 4), (72, 200, 12, 2, 5),
+                                            (145, 81, 8, 1, 6), (137, 75, 10, 2, 7)])  # odd: super-resolution frames (chroma limit (w + 1) >> 1)
 def test_dec_loop_filter_adapter(H, orc, adaptdec, refdec, w, h, bd, sb, seed):
     S = H.S
     g = S.make_geom(w, h, bd, sb)

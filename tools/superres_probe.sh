@@ -9,7 +9,7 @@ PY
 run() { # name, extra args
   local name=$1; shift
   for app in ref b200; do
-    SVTF_ADAPTER_STATS=1 timeout 600 $B/SvtAv1EncApp_$app -i $T/c.yuv -w $W -h $H --fps 30 -n $N --preset ${PRESET:-6} --input-depth 8 --crf 50 "$@" -b $T/$app.ivf -o $T/$app.yuv > $T/$app.log 2>&1 || echo "enc $app failed"
+    SVTF_ADAPTER_STATS=1 timeout 600 $B/SvtAv1EncApp_$app -i $T/c.yuv -w $W -h $H --fps 30 -n $N --preset ${PRESET:-6} --input-depth 8 --crf 50 ${EXTRA:-} "$@" -b $T/$app.ivf -o $T/$app.yuv > $T/$app.log 2>&1 || echo "enc $app failed"
   done
   python - <<PY
 import numpy as np
@@ -27,7 +27,7 @@ print("$name:", "IDENTICAL" if not msg and len(a)==len(b) else ("sizes %d %d; "%
 PY
   grep -o "loop_restoration_filter_frame=[0-9]* restoration_search=[0-9]* superres_upscale_frame=[0-9]*" $T/b200.log
 }
-SR="--superres-mode 1 --superres-denom 12 --superres-kf-denom 12"
+SR=${SR:-"--superres-mode 1 --superres-denom 12 --superres-kf-denom 12"}
 run "no superres"
 run "superres" $SR
 run "superres, no restoration" $SR --enable-restoration 0
