@@ -193,3 +193,32 @@ def test_encoder_option_matrix_identical(tmp_path, name):
     scaled frames."""
     w, h, depth, frames, preset, extra = MATRIX[name]
     _encode_both(tmp_path, w, h, frames, depth, preset, extra)
+
+
+DEC_MATRIX = {
+    "aq-mode 1 (segmentation)": (640, 360, 8, 5, 6, ("--aq-mode", "1", "--crf", "45")),
+    "2x2 tiles": (640, 360, 8, 5, 6, ("--tile-rows", "1", "--tile-columns", "1", "--crf", "45")),
+    "superres, random denominator per frame": (640, 360, 8, 6, 6, ("--superres-mode", "2", "--crf", "50")),
+    "reference scaling, random size per frame": (640, 360, 8, 6, 6, ("--resize-mode", "3", "--crf", "45")),
+    "10-bit superres 8/13, preset 4": (640, 360, 10, 3, 4, ("--superres-mode", "1", "--superres-denom", "13", "--superres-kf-denom", "13", "--crf", "50")),
+    "128x128 superblocks (preset 1)": (512, 384, 8, 3, 1, ("--crf", "45")),
+}
+
+
+@pytest.mark.parametrize("name", list(DEC_MATRIX))
+def test_decoder_option_matrix_identical(tmp_path, name):
+    """Streams of the unmodified encoder over options that change what the decoder's filter stages see (level tables, tiles, frame sizes that
+    change per frame on one decoder handle, superblock size): both decoders and the 3-thread API client must produce the encoder's reconstruction."""
+    w, h, depth, frames, preset, extra = DEC_MATRIX[name]
+    clip = _clip(tmp_path, w, h, frames, depth)
+    _encode("SvtAv1EncApp_ref", clip, w, h, frames, depth, preset, str(tmp_path / "s"), extra)
+    ivf, want = str(tmp_path / "s.ivf"), _md5(str(tmp_path / "s.yuv"))
+    _decode("SvtAv1DecApp_ref", ivf, str(tmp_path / "dec_ref.yuv"))
+    err = _decode("SvtAv1DecApp_b200", ivf, str(tmp_path / "dec_b200.yuv"))
+    assert _md5(str(tmp_path / "dec_ref.yuv")) == _md5(str(tmp_path / "dec_b200.yuv"))
+    if "scaling" not in name:  # with reference scaling the encoder's -o file holds the scaled pictures, the decoder writes what it decodes
+        assert _md5(str(tmp_path / "dec_b200.yuv")) == want
+    assert _stats(err)["gpu_launches"] > 0
+    r = subprocess.run([_bin("dec_threads_b200"), ivf, str(tmp_path / "mt.yuv"), "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert _md5(str(tmp_path / "mt.yuv")) == _md5(str(tmp_path / "dec_ref.yuv"))
