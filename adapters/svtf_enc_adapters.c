@@ -73,6 +73,19 @@ static void die(const char *where, svtf_ctx *ctx) {
             svtf_last_error(ctx));
     abort();
 }
+/* checked allocations: an adapter has no way to report failure (the replaced functions return void) */
+static void *xmalloc(size_t n, svtf_ctx *ctx) {
+    void *p = malloc(n ? n : 1);
+    if (!p)
+        die("malloc", ctx);
+    return p;
+}
+static void *xcalloc(size_t n, size_t m, svtf_ctx *ctx) {
+    void *p = calloc(n ? n : 1, m ? m : 1);
+    if (!p)
+        die("calloc", ctx);
+    return p;
+}
 #define CHECK(call, ctx)       \
     do {                       \
         if ((call) != SVTF_OK) \
@@ -513,9 +526,9 @@ void svtf_cdef_search_picture(PictureControlSet *pcs, SequenceControlSet *scs) {
     int32_t st[3];
     plane_ptrs(input, s->geom.sample_bytes, p, st);
     CHECK(svtf_upload_source(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
-    uint64_t *mse = (uint64_t *)malloc(sizeof(uint64_t) * 128 * (size_t)nfb);
-    uint8_t  *dir = (uint8_t *)malloc(64 * (size_t)nfb);
-    int32_t  *var = (int32_t *)malloc(sizeof(int32_t) * 64 * (size_t)nfb);
+    uint64_t *mse = (uint64_t *)xmalloc(sizeof(uint64_t) * 128 * (size_t)nfb, s->ctx);
+    uint8_t  *dir = (uint8_t *)xmalloc(64 * (size_t)nfb, s->ctx);
+    int32_t  *var = (int32_t *)xmalloc(sizeof(int32_t) * 64 * (size_t)nfb, s->ctx);
     CHECK(svtf_cdef_search_frame(s->ctx, &cfg, mse, pcs->skip_cdef_seg, dir, var), s->ctx);
     memcpy(pcs->mse_seg[0], mse, sizeof(uint64_t) * 64 * (size_t)nfb);
     memcpy(pcs->mse_seg[1], mse + (size_t)64 * nfb, sizeof(uint64_t) * 64 * (size_t)nfb);
@@ -654,7 +667,7 @@ void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdP
         memcpy(p.filter_offset[pl], ci->filter_offset[pl], SVTF_CCSO_LUT_SIZE);
         const int pw = s->geom.width >> (pl ? 1 : 0), ph = s->geom.height >> (pl ? 1 : 0), bl = pl ? 7 : 8;
         const int nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl;
-        flags[pl] = (uint8_t *)malloc((size_t)nbx * nby);
+        flags[pl] = (uint8_t *)xmalloc((size_t)nbx * nby, s->ctx);
         for (int by = 0; by < nby; by++)
             for (int bx = 0; bx < nbx; bx++) { /* Common/Codec/EbCcso.c:317-322 */
                 const MbModeInfo *m = &pcs->mi_grid_base[64 * by * pcs->mi_stride + 64 * bx]->mbmi;
@@ -671,7 +684,7 @@ void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdP
         void           *pp[3];
         int32_t         st[3];
         plane_ptrs(frame, sb, pp, st);
-        uint8_t *ly = (uint8_t *)malloc((size_t)cw * chh * sb);
+        uint8_t *ly = (uint8_t *)xmalloc((size_t)cw * chh * sb, s->ctx);
         for (int r = 0; r < chh; r++)
             for (int c = 0; c < cw; c++) {
                 const uint16_t v = ext_rec_y[(size_t)(5 + (r < H ? r : H - 1)) * es + 5 + (c < W ? c : W - 1)];
@@ -686,7 +699,7 @@ void ccso_frame(EbPictureBufferDesc *frame, PictureControlSet *pcs, MacroblockdP
         svtf_cdef_params idp;
         memset(&idp, 0, sizeof(idp));
         const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
-        int8_t   *idx = (int8_t *)calloc(nfb, 1);
+        int8_t   *idx = (int8_t *)xcalloc(nfb, 1, s->ctx);
         CHECK(svtf_cdef_apply_frame(s->ctx, &idp, idx), s->ctx); /* strengths 0: copies, marks the pre-CDEF surface */
         CHECK(svtf_sync(s->ctx), s->ctx);
         free(idx), free(ly);
@@ -724,7 +737,7 @@ void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const
     for (int k = 0; k < 3; k++)
         for (int p = 0; p < 3; p++) {
             const int pw = cw >> (p ? 1 : 0), ph = chh >> (p ? 1 : 0), vw = W >> (p ? 1 : 0), vh = H >> (p ? 1 : 0);
-            buf[k][p]    = (uint8_t *)calloc((size_t)pw * ph, sb);
+            buf[k][p]    = (uint8_t *)xcalloc((size_t)pw * ph, sb, s->ctx);
             for (int r = 0; r < ph; r++)
                 for (int c = 0; c < pw; c++) {
                     const int rr = r < vh ? r : vh - 1, cc = c < vw ? c : vw - 1;
@@ -745,7 +758,7 @@ void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const
     svtf_cdef_params idp;
     memset(&idp, 0, sizeof(idp));
     const int nfb = ((s->geom.mi_rows + 15) / 16) * ((s->geom.mi_cols + 15) / 16);
-    int8_t   *idx = (int8_t *)calloc(nfb, 1);
+    int8_t   *idx = (int8_t *)xcalloc(nfb, 1, s->ctx);
     CHECK(svtf_cdef_apply_frame(s->ctx, &idp, idx), s->ctx); /* strengths 0: copies, marks the pre-CDEF surface */
     CHECK(svtf_overwrite_current(s->ctx, buf[1][0], cw, buf[1][1], cw / 2, buf[1][2], cw / 2), s->ctx);
     CHECK(svtf_upload_source(s->ctx, buf[2][0], cw, buf[2][1], cw / 2, buf[2][2], cw / 2), s->ctx);
@@ -756,7 +769,7 @@ void ccso_search(PictureControlSet *pcs, MacroblockdPlane *pd, int rdmult, const
     for (int p = 0; p < 3; p++) {
         const int pw = W >> (p ? 1 : 0), ph = H >> (p ? 1 : 0), bl = p ? 7 : 8;
         nbx[p] = (pw + (1 << bl) - 1) >> bl, nby[p] = (ph + (1 << bl) - 1) >> bl;
-        flags[p] = (uint8_t *)calloc((size_t)nbx[p] * nby[p], 1);
+        flags[p] = (uint8_t *)xcalloc((size_t)nbx[p] * nby[p], 1, s->ctx);
     }
     CHECK(svtf_ccso_derive_frame(s->ctx, (int)rd, 0, 3, &out, flags), s->ctx);
     CcsoInfo *ci = &fh->ccso_info;
@@ -810,7 +823,7 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
         lr.restoration_unit_size[p]  = rsi->restoration_unit_size;
         if (rsi->frame_restoration_type == RESTORE_NONE)
             continue;
-        units[p] = (svtf_lr_unit *)calloc(rsi->units_per_tile, sizeof(svtf_lr_unit));
+        units[p] = (svtf_lr_unit *)xcalloc(rsi->units_per_tile, sizeof(svtf_lr_unit), s->ctx);
         for (int u = 0; u < rsi->units_per_tile; u++) {
             const RestorationUnitInfo *ri = &rsi->unit_info[u];
             units[p][u].restoration_type  = ri->restoration_type == RESTORE_WIENER ? SVTF_RESTORE_WIENER
@@ -837,7 +850,7 @@ void svt_av1_loop_restoration_filter_frame(int32_t *rst_tmpbuf, Yv12BufferConfig
                 const int ss = p ? 1 : 0, cw = (s->geom.mi_cols * 4) >> ss, chh = (s->geom.mi_rows * 4) >> ss;
                 const int pw = (s->geom.width + ss) >> ss, ph = (s->geom.height + ss) >> ss, sh = 64 >> ss, off = 8 >> ss;
                 const RestorationStripeBoundaries *b = &pcs->rst_info[p].boundaries;
-                dbk[p] = (uint8_t *)calloc((size_t)cw * chh, sb), dst[p] = cw;
+                dbk[p] = (uint8_t *)xcalloc((size_t)cw * chh, sb, s->ctx), dst[p] = cw;
                 for (int k = 0;; k++) {
                     const int y0 = k * sh - off > 0 ? k * sh - off : 0, y1 = (k + 1) * sh - off < ph ? (k + 1) * sh - off : ph;
                     if (y0 >= ph)
@@ -990,7 +1003,7 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     if (cm->wn_filter_ctrls.enabled && cm->wn_filter_ctrls.use_prev_frame_coeffs && pcs->ppcs->frm_hdr.frame_type != KEY_FRAME &&
         pcs->ppcs->frm_hdr.frame_type != INTRA_ONLY_FRAME)
         for (int p = 0; p < 3; p++) {
-            prev[p] = (svtf_lr_unit *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit));
+            prev[p] = (svtf_lr_unit *)xcalloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit), s->ctx);
             for (int u = 0; u < pcs->rst_info[p].units_per_tile; u++) {
                 const RestorationUnitInfo *ri = &pcs->rst_info[p].unit_info[u];
                 prev[p][u].restoration_type   = ri->restoration_type == RESTORE_WIENER ? SVTF_RESTORE_WIENER : SVTF_RESTORE_NONE;
@@ -1007,8 +1020,8 @@ void restoration_seg_search(int32_t *rst_tmpbuf, Yv12BufferConfig *org_fts, cons
     }
     for (int p = 0; p < 3; p++) {
         free(r->units[p]);
-        r->units[p] = (svtf_lr_unit *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit));
-        us[p]       = (svtf_lr_unit_search *)calloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit_search));
+        r->units[p] = (svtf_lr_unit *)xcalloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit), s->ctx);
+        us[p]       = (svtf_lr_unit_search *)xcalloc(pcs->rst_info[p].units_per_tile, sizeof(svtf_lr_unit_search), s->ctx);
     }
     int32_t ep_cnt[16];
     CHECK(svtf_lr_search_frame(s->ctx, &cfg, r->frame_type, r->units, us, ep_cnt), s->ctx);

@@ -388,7 +388,10 @@ static int copy_planes(svtf_ctx *c, Surface &s, const void *const src[3], const 
         const size_t sb = g.sample_bytes;
         uint8_t     *dev = static_cast<uint8_t *>(s.base[p]) + (size_t)r0 * s.pitch[p] * sb;
         uint8_t     *hst = static_cast<uint8_t *>(const_cast<void *>(src[p])) + ((size_t)(c->glob_row0 >> ss) + r0) * stride[p] * sb;
-        if (stride[p] == s.pitch[p]) { // same pitch on both sides: one linear DMA instead of a 2-D copy
+        // same pitch on both sides: one linear DMA instead of a 2-D copy — for uploads, where the bytes between the coded width and the pitch
+        // land in device padding; a download only when there are none (the host's columns [w, stride) are the caller's: picture border,
+        // a neighbouring region)
+        if (stride[p] == s.pitch[p] && (to_device || w == s.pitch[p])) {
             const size_t bytes = ((size_t)(h - 1) * s.pitch[p] + w) * sb;
             if (to_device)
                 CUDA_TRY(c, cudaMemcpyAsync(dev, hst, bytes, cudaMemcpyHostToDevice, c->stream));
