@@ -1151,7 +1151,9 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     e2e_tier1_val = world * B * EP * npx * args.steps / float(tt.item()) / 1e6
     # ---- e2e through the PLUGIN call: the reference's own entry points (Tier-2 adapters) on PictureControlSet structures ----
-    adapter = adapter_e2e_leg(H, S, geom, wls, nsrc, B, args.steps, barrier, local, np)
+    # B * EP pictures per pass, like the Tier-1 leg: with only 12 the host threads all upload, then all download (every pass starts cold)
+    os.environ.setdefault("SVTF_BENCH_ADAPTER_THREADS", "8" if world == 1 else "6")
+    adapter = adapter_e2e_leg(H, S, geom, wls, nsrc, B * EP, max(3, args.steps // 2), barrier, local, np)
     e2e_val = e2e_tier1_val
     if adapter is not None:
         ta = torch.tensor([adapter["seconds"]], dtype=torch.float64, device=dev)
@@ -1201,8 +1203,8 @@ def main():
                        "pictures_per_gpu_per_step": B * P, "passes_per_step": P, "l2": f"inputs larger than L2: {B} pictures x 3 surfaces x {frame_bytes / 1e6:.1f} MB resident",
                        "streams_per_gpu": NS, "host_affinity": numa,
                        "sharding": f"{world} rank(s), pictures sharded by stream, no collective"},
-            "e2e": ({"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + 6 * mi_bytes // 4) * B, "d2h_bytes_per_step": frame_bytes * B,
-                     "pictures_per_step": B, "path": "Tier-2 adapters: svt_av1_loop_filter_frame -> svt_av1_cdef_frame -> ccso_frame on PictureControlSet structures "
+            "e2e": ({"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": (frame_bytes + 6 * mi_bytes // 4) * B * EP, "d2h_bytes_per_step": frame_bytes * B * EP,
+                     "pictures_per_step": B * EP, "path": "Tier-2 adapters: svt_av1_loop_filter_frame -> svt_av1_cdef_frame -> ccso_frame on PictureControlSet structures "
                      "(malloc'ed recon picture page-locked in place once, mode info gathered from the mi_grid_base pointer grid per picture)",
                      "host_threads": adapter["host_threads"], "ms_per_picture": adapter["ms_per_picture"], "matches_device_path": adapter["matches_device_path"]}
                     if adapter is not None else
