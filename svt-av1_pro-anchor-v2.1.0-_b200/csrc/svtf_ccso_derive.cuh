@@ -11,6 +11,9 @@
 //                     (coarser band counts are sums of these: band = Y >> (bd - log2)), ccso_pre_compute_class_err(_bo)
 //   ccso_try_kernel   trial filter + per-block SSE for up to 8 LUTs in one pass (the band settings of a group train
 //                     in lock-step, their loops are independent), ccso_try_*_filter + compute_distortion
+// Both take a batch of configuration groups in gridDim.z (CdGroup): the 49 groups of a plane are independent of each other, so one
+// launch builds all their histograms and one launch per training round tries every LUT still in training (round 2: 18 launches and
+// host round trips per plane instead of ~280).
 // Classes are recomputed per sample from the luma surface (cal_filter_support, Common/Codec/EbCcso.c:238-259, taps from
 // derive_ccso_sample_pos :204-234, replicate border = clamped coordinates) instead of materialising class planes.
 #pragma once
@@ -18,8 +21,17 @@
 
 namespace svtf {
 
-constexpr int CD_THREADS = 256;
-constexpr int CD_MAX_LUT = 8;
+constexpr int CD_THREADS    = 256;
+constexpr int CD_MAX_LUT    = 8;
+constexpr int CD_MAX_GROUPS = 49; // 1 band-only group + 6 supports x 4 quantisers x 2 classifiers
+
+// One configuration group of a batched launch (blockIdx.z): the classifier of the group, where its histograms go, and for the
+// trial kernel its LUTs — slot z uses luts[z][CD_MAX_LUT][2048] and dist[z][CD_MAX_LUT][nfb].
+struct CdGroup {
+    int dy, dx, thr, edge_clf, bo;
+    int hist_shift, nidx, hoff; // hoff: offset of the group's [nfb][nidx] histograms in herr / hcnt
+    int nl, shift[CD_MAX_LUT];
+};
 
 struct CcsoDeriveArgs {
     const void *luma, *rec, *org; // classifier luma plane; plane to modify; source plane
@@ -37,7 +49,26 @@ struct CcsoDeriveArgs {
     int                 shift[CD_MAX_LUT];
     const int8_t       *luts; // [nl][2048]
     unsigned long long *dist; // [nl][nfb]
+    // batched form: gridDim.z groups, the fields above that a group owns come from groups[blockIdx.z]
+    const CdGroup *groups;
 };
+
+// the launch arguments as group blockIdx.z sees them
+__device__ __forceinline__ CcsoDeriveArgs cd_group_args(const CcsoDeriveArgs &a) {
+    CcsoDeriveArgs b = a;
+    if (a.groups) {
+        const CdGroup &g   = a.groups[blockIdx.z];
+        const int      nfb = a.nbx * ((a.ph + (1 << a.blk_log2) - 1) >> a.blk_log2);
+        b.dy = g.dy, b.dx = g.dx, b.thr = g.thr, b.edge_clf = g.edge_clf, b.bo = g.bo;
+        b.hist_shift = g.hist_shift, b.nidx = g.nidx, b.herr = a.herr + g.hoff, b.hcnt = a.hcnt + g.hoff;
+        b.nl = g.nl;
+#pragma unroll
+        for (int l = 0; l < CD_MAX_LUT; l++) b.shift[l] = g.shift[l];
+        b.luts = a.luts + (size_t)blockIdx.z * CD_MAX_LUT * 2048;
+        b.dist = a.dist + (size_t)blockIdx.z * CD_MAX_LUT * nfb;
+    }
+    return b;
+}
 
 template <typename T>
 __device__ __forceinline__ void cd_sample(const CcsoDeriveArgs &a, const int x, const int y, int &yv, int &c0, int &c1) {
@@ -60,7 +91,8 @@ __device__ __forceinline__ void cd_sample(const CcsoDeriveArgs &a, const int x, 
 
 // CTA = one 64x64 tile of the plane (always inside one filter block: blocks are 128 or 256 samples).
 template <typename T>
-__global__ void __launch_bounds__(CD_THREADS) ccso_hist_kernel(const __grid_constant__ CcsoDeriveArgs a) {
+__global__ void __launch_bounds__(CD_THREADS) ccso_hist_kernel(const __grid_constant__ CcsoDeriveArgs a0) {
+    const CcsoDeriveArgs a = cd_group_args(a0);
     __shared__ int s_err[2048], s_cnt[2048];
     const int tid = threadIdx.x, x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
     for (int i = tid; i < a.nidx; i += CD_THREADS) s_err[i] = 0, s_cnt[i] = 0;
@@ -86,7 +118,8 @@ __global__ void __launch_bounds__(CD_THREADS) ccso_hist_kernel(const __grid_cons
 }
 
 template <typename T>
-__global__ void __launch_bounds__(CD_THREADS) ccso_try_kernel(const __grid_constant__ CcsoDeriveArgs a) {
+__global__ void __launch_bounds__(CD_THREADS) ccso_try_kernel(const __grid_constant__ CcsoDeriveArgs a0) {
+    const CcsoDeriveArgs a = cd_group_args(a0);
     __shared__ int8_t             s_lut[CD_MAX_LUT][2048];
     __shared__ unsigned long long s_sum[CD_MAX_LUT];
     const int tid = threadIdx.x, x0 = blockIdx.x * 64, y0 = blockIdx.y * 64;
