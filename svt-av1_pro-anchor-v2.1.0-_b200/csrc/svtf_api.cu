@@ -1315,865 +1315,10 @@ extern "C" int svtf_dev_planes(svtf_ctx *c, int which, svtf_dev_plane out[3]) {
     return SVTF_OK;
 }
 
-// ---- CDEF strength search ------------------------------------------------------------------------
-extern "C" int svtf_cdef_search_frame(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, uint64_t *mse, uint8_t *skip, uint8_t *dir,
-                                      int32_t *var) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_cdef_search_frame: NULL context");
-    if (!cfg)
-        return c->fail(SVTF_E_ARG, "svtf_cdef_search_frame: NULL cfg");
-    if (int r = need_frame_mi(c, "svtf_cdef_search_frame"))
-        return r;
-    if (!c->have_source)
-        return c->fail(SVTF_E_STATE, "svtf_cdef_search_frame: upload the source picture first");
-    const int n = cfg->first_pass_fs_num + cfg->default_second_pass_fs_num;
-    if (n <= 0 || n > SVTF_TOTAL_STRENGTHS || cfg->first_pass_fs_num < 0 || cfg->default_second_pass_fs_num < 0 ||
-        (cfg->subsampling_factor != 1 && cfg->subsampling_factor != 2 && cfg->subsampling_factor != 4))
-        return c->fail(SVTF_E_ARG, "svtf_cdef_search_frame: bad strength counts or subsampling factor");
-    CUDA_TRY(c, cudaSetDevice(c->device));
-    const int nvfb = (c->geom.mi_rows + 15) / 16, nhfb = (c->geom.mi_cols + 15) / 16, nfb = nvfb * nhfb;
-    SearchArgs a;
-    a.rec = c->surf[c->cur].planes();
-    a.src = c->source.planes();
-    a.mi = c->d_mi, a.mi_stride = c->mi_stride;
-    a.d = dims_of(c->geom);
-    a.n = n;
-    for (int gi = 0; gi < n; gi++) {
-        const bool first = gi < cfg->first_pass_fs_num;
-        a.fs[gi]    = first ? cfg->default_first_pass_fs[gi] : cfg->default_second_pass_fs[gi - cfg->first_pass_fs_num];
-        a.fs_uv[gi] = first ? cfg->default_first_pass_fs_uv[gi] : cfg->default_second_pass_fs_uv[gi - cfg->first_pass_fs_num];
-    }
-    a.damping = 3 + (cfg->base_q_idx >> 6);
-    a.subsampling = cfg->subsampling_factor;
-    a.mse = c->d_mse, a.skip = c->d_skip, a.dir = c->d_dir, a.var = c->d_var;
-    a.nfb  = nfb;
-    a.fbr0 = c->own_lo / 64;
-    a.raw  = c->d_mse_raw;
-    a.fold = reinterpret_cast<unsigned *>(c->d_mse_raw + (size_t)3 * 64 * nfb);
-    a.fbr_par = (c->glob_row0 / 64) & 1;
-    CUDA_TRY(c, cudaMemsetAsync(c->d_mse_raw, 0, (sizeof(unsigned long long) * 3 * 64 + sizeof(unsigned)) * (size_t)nfb, c->stream));
-    CUDA_TRY(c, cudaMemsetAsync(c->d_skip, 0, (size_t)nfb, c->stream)); // quadrants folded into a 128 block are never written (as in the reference)
-    CUDA_TRY(c, cudaMemsetAsync(c->d_dir, 0, 64 * (size_t)nfb, c->stream));
-    CUDA_TRY(c, cudaMemsetAsync(c->d_var, 0, sizeof(int32_t) * 64 * (size_t)nfb, c->stream));
-    CUDA_TRY(c, cudaMemsetAsync(c->d_mse, 0, sizeof(uint64_t) * 128 * (size_t)nfb, c->stream));
-    dim3 grid(nhfb, (c->own_hi + 63) / 64 - a.fbr0);
-    // 8/10-bit: separable packed kernel (svtf_search2.cuh); 12-bit (filtered-minus-input does not fit int8) and the
-    // SVTF_SEARCH_SCALAR=1 A/B switch: the direct per-strength kernel
-    static const bool scalar = getenv("SVTF_SEARCH_SCALAR") != nullptr;
-    if (scalar || c->geom.bit_depth > 10) {
-        if (c->geom.sample_bytes == 1)
-            cdef_search_kernel<uint8_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
-        else
-            cdef_search_kernel<uint16_t><<<grid, SEARCH_THREADS, 0, c->stream>>>(a);
-    } else {
-        Search2Args b;
-        b.s = a, b.present_y = 0, b.present_uv = 0;
-        for (int gi = 0; gi < n; gi++) {
-            b.present_y |= 1ull << (a.fs[gi] & 63);
-            if (a.fs_uv[gi] != -1)
-                b.present_uv |= 1ull << (a.fs[gi] & 63);
-        }
-#ifdef SVTF_AB_KERNELS
-        static const bool use_v2 = getenv("SVTF_SEARCH_V2") != nullptr; // A/B switch: packed-integer taps (svtf_search2.cuh)
-        if (use_v2) {
-            if (c->geom.sample_bytes == 1)
-                cdef_search2_kernel<uint8_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
-            else
-                cdef_search2_kernel<uint16_t><<<grid, S2_THREADS, 0, c->stream>>>(b);
-        } else
-#endif
-        { // fp16 taps (svtf_search3.cuh); search damping = 3 + (base_q_idx >> 6) <= 6, inside the exactness bound
-            constexpr int smem = S3_SMEM_WORDS * 4;
-            if (!c->search3_ready) {
-                CUDA_TRY(c, cudaFuncSetAttribute(cdef_search3_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-                CUDA_TRY(c, cudaFuncSetAttribute(cdef_search3_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-                c->search3_ready = true;
-            }
-            if (c->geom.sample_bytes == 1)
-                cdef_search3_kernel<uint8_t><<<grid, S2_THREADS, smem, c->stream>>>(b);
-            else
-                cdef_search3_kernel<uint16_t><<<grid, S2_THREADS, smem, c->stream>>>(b);
-        }
-    }
-    CUDA_TRY(c, cudaGetLastError());
-    c->launches++;
-    {
-        SearchArgs f = a;
-        f.fbr0       = 0;
-        search_fold_kernel<<<nfb, 64, 0, c->stream>>>(f); // rows of 128-wide / 128-high coding blocks (returns at once where there are none)
-        CUDA_TRY(c, cudaGetLastError());
-        c->launches++;
-    }
-    c->have_search = true;
-    // outputs are WHOLE-PICTURE arrays; this context fills the filter-block rows it owns
-    const size_t l0 = (size_t)a.fbr0 * nhfb, ln = (size_t)grid.y * nhfb;           // local first fb, count
-    const size_t g0 = l0 + (size_t)(c->glob_row0 / 64) * nhfb;                      // same fb in the picture
-    const size_t nfb_full = (size_t)((c->full.mi_rows + 15) / 16) * nhfb;
-    if (mse)
-        for (int pl = 0; pl < 2; pl++)
-            CUDA_TRY(c, cudaMemcpyAsync(mse + ((size_t)pl * nfb_full + g0) * 64, c->d_mse + ((size_t)pl * nfb + l0) * 64, sizeof(uint64_t) * 64 * ln,
-                                        cudaMemcpyDeviceToHost, c->stream));
-    if (skip) CUDA_TRY(c, cudaMemcpyAsync(skip + g0, c->d_skip + l0, ln, cudaMemcpyDeviceToHost, c->stream));
-    if (dir) CUDA_TRY(c, cudaMemcpyAsync(dir + g0 * 64, c->d_dir + l0 * 64, 64 * ln, cudaMemcpyDeviceToHost, c->stream));
-    if (var) CUDA_TRY(c, cudaMemcpyAsync(var + g0 * 64, c->d_var + l0 * 64, sizeof(int32_t) * 64 * ln, cudaMemcpyDeviceToHost, c->stream));
-    if (mse || skip || dir || var)
-        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    return SVTF_OK;
-}
-
-// finish_cdef_search on the device (svtf_pick.cuh) over a table that is already in device memory.
-static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint64_t *d_mse, const uint8_t *d_skip, int nfb,
-                       svtf_cdef_params *out, int8_t *fb_strength_idx, const char *who) {
-    const int end_gi = cfg->first_pass_fs_num + cfg->default_second_pass_fs_num;
-    if (end_gi <= 0 || end_gi > SVTF_TOTAL_STRENGTHS || cfg->first_pass_fs_num < 0 || cfg->default_second_pass_fs_num < 0)
-        return c->fail(SVTF_E_ARG, std::string(who) + ": bad strength counts");
-    if (nfb > c->pick_cap) {
-        cudaFree(c->d_pick_idx);
-        c->d_pick_idx = nullptr, c->pick_cap = 0;
-        CUDA_TRY(c, cudaMalloc(&c->d_pick_idx, nfb));
-        c->pick_cap = nfb;
-    }
-    PickArgs a;
-    a.mse = d_mse, a.skip = d_skip, a.nfb = nfb, a.end_gi = end_gi, a.bias = cfg->zero_fs_cost_bias;
-    a.st = c->d_pick_state, a.tot = c->d_pick_tot;
-    // The 75 dependent svt_search_one_dual passes: one launch per pass, enqueued back to back (svtf_pick.cuh).  SVTF_PICK_CLUSTER=1: ONE
-    // launch, a 16-CTA cluster stays resident for all passes (svtf_pick2.cuh; measured slower in throughput, see its header) when the table
-    // fits its shared memory and is narrow (every entry < 2^31; the kernel reports wide == 2 otherwise and the per-pass form runs).
-    static const bool per_pass = getenv("SVTF_PICK_CLUSTER") == nullptr;
-    if (!c->max_smem_optin) {
-        int v = 0;
-        CUDA_TRY(c, cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
-        c->max_smem_optin = (size_t)v;
-    }
-    PickState st;
-    bool      done = false;
-    if (!per_pass && pick2_fits(nfb, c->max_smem_optin)) {
-        CUDA_TRY(c, pick2_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
-        CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-        done = st.wide != 2;
-    }
-    if (!done) {
-        // (Replaying the schedule as one captured graph was measured: 3 % faster one picture at a time, 30 % slower with 8 pictures in
-        //  flight — graph launches from several streams do not interleave like plain launches — so the launches stay plain.)
-        CUDA_TRY(c, pick_prepare());
-        CUDA_TRY(c, pick_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->sm_count, c->stream, &c->launches));
-        CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    }
-    memset(out, 0, sizeof(*out));
-    out->cdef_bits = st.best_bits;
-    auto map = [&](int i) { // index -> strength byte through the luma lists (Encoder/Codec/EbEncCdef.c:911-919)
-        return i < cfg->first_pass_fs_num ? cfg->default_first_pass_fs[i] : cfg->default_second_pass_fs[i - cfg->first_pass_fs_num];
-    };
-    for (int g = 0; g < (1 << st.best_bits); g++) {
-        out->cdef_y_strength[g]  = map(st.out0[g]);
-        out->cdef_uv_strength[g] = map(st.out1[g]);
-    }
-    out->cdef_damping = 3 + (cfg->base_q_idx >> 6);
-    return SVTF_OK;
-}
-
-extern "C" int svtf_cdef_pick(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, svtf_cdef_params *out_params, int8_t *fb_strength_idx) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_cdef_pick: NULL context");
-    if (!cfg || !out_params || !fb_strength_idx)
-        return c->fail(SVTF_E_ARG, "svtf_cdef_pick: NULL argument");
-    if (!c->have_search)
-        return c->fail(SVTF_E_STATE, "svtf_cdef_pick: run svtf_cdef_search_frame first");
-    if (c->striped)
-        return c->fail(SVTF_E_STATE, "svtf_cdef_pick: this context holds one stripe; gather mse/skip and call svtf_cdef_pick_table");
-    CUDA_TRY(c, cudaSetDevice(c->device));
-    const int nfb = ((c->geom.mi_rows + 15) / 16) * ((c->geom.mi_cols + 15) / 16);
-    return pick_device(c, cfg, c->d_mse, c->d_skip, nfb, out_params, fb_strength_idx, "svtf_cdef_pick");
-}
-
-extern "C" int svtf_cdef_pick_table(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint64_t *mse, const uint8_t *skip, int32_t nfb,
-                                    svtf_cdef_params *out_params, int8_t *fb_strength_idx) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_cdef_pick_table: NULL context");
-    if (!cfg || !mse || !skip || !out_params || !fb_strength_idx || nfb <= 0)
-        return c->fail(SVTF_E_ARG, "svtf_cdef_pick_table: bad argument");
-    CUDA_TRY(c, cudaSetDevice(c->device));
-    if (nfb > c->tab_cap) {
-        cudaFree(c->d_tab_mse), cudaFree(c->d_tab_skip);
-        c->d_tab_mse = nullptr, c->d_tab_skip = nullptr, c->tab_cap = 0;
-        CUDA_TRY(c, cudaMalloc(&c->d_tab_mse, sizeof(uint64_t) * 128 * (size_t)nfb));
-        CUDA_TRY(c, cudaMalloc(&c->d_tab_skip, nfb));
-        c->tab_cap = nfb;
-    }
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_tab_mse, mse, sizeof(uint64_t) * 128 * (size_t)nfb, cudaMemcpyHostToDevice, c->stream));
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_tab_skip, skip, nfb, cudaMemcpyHostToDevice, c->stream));
-    return pick_device(c, cfg, c->d_tab_mse, c->d_tab_skip, nfb, out_params, fb_strength_idx, "svtf_cdef_pick_table");
-}
-
-// ---- CCSO filter derivation ----------------------------------------------------------------------
-// ccso_search / derive_ccso_filter (Encoder/Codec/EbPickccso.c:464-782, :785-812).  Kernels: svtf_ccso_derive.cuh.
-// The host keeps the reference's sequential decisions verbatim (float LUT rounding :431-461, double RD cost
-// EbPickccso.h:9 + EbRestoration.h:346, per-block on/off :71-121 whose CDF rate never reaches the caller's cost,
-// LUT bit count :360-379).  The 4 (band-only: 8) band settings of one (bo, support, quantiser, classifier) group have
-// independent training loops, so they run in lock-step: one trial launch per round evaluates every LUT still training.
-namespace {
-
-const int     kCcsoOffset[8] = {-10, -7, -3, -1, 0, 1, 3, 7};
-const uint8_t kCcsoQuant[4]  = {16, 8, 32, 64};
-
-struct DeriveScratch { // device + pinned host buffers of one context, grown on demand
-    int                *d_herr = nullptr, *d_hcnt = nullptr, *h_herr = nullptr, *h_hcnt = nullptr; // [all groups][nfb][nidx]
-    unsigned long long *d_dist = nullptr, *h_dist = nullptr;                                       // [slot][CD_MAX_LUT][nfb]
-    int8_t             *d_luts = nullptr, *h_luts = nullptr;                                       // [slot][CD_MAX_LUT][2048]
-    CdGroup            *d_groups = nullptr, *h_groups = nullptr;                                   // [slot]
-    int                 nfb_cap = 0;
-};
-constexpr int CD_HIST_ENTRIES = 2048 + (CD_MAX_GROUPS - 1) * 128; // histogram entries per filter block over all groups
-
-int ccso_lut_bits(const int8_t *lut, int band_log2, int intervals, int bo) {
-    static const int reordered[8] = {0, 1, -1, 3, -3, 7, -7, -10};
-    int              bits = 0, n = bo ? 1 : intervals;
-    for (int d0 = 0; d0 < n; d0++)
-        for (int d1 = 0; d1 < n; d1++)
-            for (int b = 0; b < (1 << band_log2); b++)
-                for (int i = 0; i < 7; i++) {
-                    bits++;
-                    if (reordered[i] == lut[(b << 4) + (d0 << 2) + d1])
-                        break;
-                }
-    return bits;
-}
-
-void ccso_lut_from_means(int8_t *lut, const int *err, const int *cnt, int band_log2, int intervals, int bo) {
-    const int n = bo ? 1 : intervals;
-    for (int d0 = 0; d0 < n; d0++)
-        for (int d1 = 0; d1 < n; d1++)
-            for (int b = 0; b < (1 << band_log2); b++) {
-                const int i = (b << 4) + (d0 << 2) + d1;
-                if (!cnt[i])
-                    continue;
-                const float t = (float)err[i] / cnt[i];
-                if (t < kCcsoOffset[0] || t >= kCcsoOffset[7]) {
-                    lut[i] = (int8_t)std::min(std::max((int)t, kCcsoOffset[0]), kCcsoOffset[7]);
-                } else {
-                    for (int k = 0; k < 7; k++)
-                        if (t >= kCcsoOffset[k] && t <= kCcsoOffset[k + 1]) {
-                            lut[i] = (int8_t)(fabs(t - kCcsoOffset[k]) > fabs(t - kCcsoOffset[k + 1]) ? kCcsoOffset[k + 1] : kCcsoOffset[k]);
-                            break;
-                        }
-                }
-            }
-}
-
-double ccso_rd_cost(int rdmult, int bits, uint64_t dist, int bd) {
-    return (((double)bits) * rdmult) / (double)(1 << 9) + ((double)(dist >> (2 * (bd - 8))) * (1 << 7));
-}
-
-struct BandState { // one band_log2 training loop
-    bool                 enable = true, keep = true;
-    double               prev_cost = DBL_MAX, best_cost = DBL_MAX;
-    int                  iter = 0;
-    int8_t               lut[2048], best_lut[2048];
-    std::vector<uint8_t> ctl, best_ctl;
-    std::vector<int>     herr, hcnt; // [nfb][entries] at this band count
-};
-
-} // namespace
-
-static void derive_scratch_release(DeriveScratch *s) {
-    cudaFree(s->d_herr), cudaFree(s->d_hcnt), cudaFree(s->d_dist), cudaFree(s->d_luts), cudaFree(s->d_groups);
-    cudaFreeHost(s->h_herr), cudaFreeHost(s->h_hcnt), cudaFreeHost(s->h_dist), cudaFreeHost(s->h_luts), cudaFreeHost(s->h_groups);
-}
-static void derive_scratch_free(void *p) {
-    DeriveScratch *s = static_cast<DeriveScratch *>(p);
-    if (!s)
-        return;
-    derive_scratch_release(s);
-    delete s;
-}
-
-static DeriveScratch *derive_scratch(svtf_ctx *c, int plane, int nfb) {
-    if (!c->derive_scratch[plane])
-        c->derive_scratch[plane] = new DeriveScratch();
-    DeriveScratch *s = static_cast<DeriveScratch *>(c->derive_scratch[plane]);
-    if (nfb > s->nfb_cap) {
-        derive_scratch_release(s);
-        *s              = DeriveScratch();
-        const size_t hb = sizeof(int) * CD_HIST_ENTRIES * (size_t)nfb, db = sizeof(unsigned long long) * CD_MAX_GROUPS * CD_MAX_LUT * (size_t)nfb;
-        const size_t lb = (size_t)CD_MAX_GROUPS * CD_MAX_LUT * 2048, gb = sizeof(CdGroup) * CD_MAX_GROUPS;
-        bool         ok = cudaMalloc(&s->d_herr, hb) == cudaSuccess && cudaMalloc(&s->d_hcnt, hb) == cudaSuccess &&
-            cudaMalloc(&s->d_dist, db) == cudaSuccess && cudaMalloc(&s->d_luts, lb) == cudaSuccess && cudaMalloc(&s->d_groups, gb) == cudaSuccess &&
-            cudaHostAlloc(reinterpret_cast<void **>(&s->h_herr), hb, cudaHostAllocDefault) == cudaSuccess &&
-            cudaHostAlloc(reinterpret_cast<void **>(&s->h_hcnt), hb, cudaHostAllocDefault) == cudaSuccess &&
-            cudaHostAlloc(reinterpret_cast<void **>(&s->h_dist), db, cudaHostAllocDefault) == cudaSuccess &&
-            cudaHostAlloc(reinterpret_cast<void **>(&s->h_luts), lb, cudaHostAllocDefault) == cudaSuccess &&
-            cudaHostAlloc(reinterpret_cast<void **>(&s->h_groups), gb, cudaHostAllocDefault) == cudaSuccess;
-        if (!ok)
-            return nullptr;
-        s->nfb_cap = nfb;
-    }
-    return s;
-}
-
-template <typename T>
-static void launch_hist(const CcsoDeriveArgs &a, dim3 grid, cudaStream_t s) { ccso_hist_kernel<T><<<grid, CD_THREADS, 0, s>>>(a); }
-template <typename T>
-static void launch_try(const CcsoDeriveArgs &a, dim3 grid, cudaStream_t s) { ccso_try_kernel<T><<<grid, CD_THREADS, 0, s>>>(a); }
-
-// fn(i) for i in [0, n) on a few host threads (the groups of the CCSO derivation are independent of each other)
-template <typename F>
-static void ccso_parallel_for(int n, F fn) {
-    const int nt = std::max(1, std::min({n, 8, (int)std::thread::hardware_concurrency()}));
-    if (nt == 1) {
-        for (int i = 0; i < n; i++) fn(i);
-        return;
-    }
-    std::atomic<int>         next(0);
-    std::vector<std::thread> th;
-    for (int t = 0; t < nt; t++)
-        th.emplace_back([&] {
-            for (int i = next++; i < n; i = next++) fn(i);
-        });
-    for (auto &t : th) t.join();
-}
-
-// derive_ccso_filter for one plane on the context's surfaces: classifier = pre-CDEF luma, rec = current picture,
-// org = uploaded source.  The 49 configuration groups (band-only; 6 supports x 4 quantisers x 2 classifiers) are independent of each
-// other and so are the band settings inside a group, so they all train in lock-step: ONE launch builds every group's histograms, then
-// one launch per training round tries every LUT that is still in training (<= 16 rounds).  The decisions between the rounds (float LUT
-// rounding, per-block on/off, double RD cost) stay on the host, per (group, band) exactly as the C code has them, and the final choice
-// walks the groups in the reference's order (strict "<": the earlier setting wins ties).
-static int ccso_derive_plane(svtf_ctx *c, int plane, int rdmult, svtf_ccso_params *out, uint8_t *flags, cudaStream_t stream, uint64_t *launches) {
-    const svtf_geom &g  = c->geom;
-    const int        ss = plane ? 1 : 0, bd = g.bit_depth;
-    const int        pw = g.width >> ss, ph = g.height >> ss, bl = plane ? 7 : 8;
-    const int        nbx = (pw + (1 << bl) - 1) >> bl, nby = (ph + (1 << bl) - 1) >> bl, nfb = nbx * nby;
-    DeriveScratch   *sc  = derive_scratch(c, plane, nfb);
-    if (!sc)
-        return c->fail(SVTF_E_NOMEM, "svtf_ccso_derive_frame: scratch allocation failed");
-    const Surface &lum = c->surf[c->pre_cdef >= 0 ? c->pre_cdef : c->cur], &cur = c->surf[c->cur];
-    CcsoDeriveArgs a;
-    memset(&a, 0, sizeof(a));
-    a.luma = lum.base[0], a.luma_pitch = lum.pitch[0];
-    a.rec = cur.base[plane], a.rec_pitch = cur.pitch[plane];
-    a.org = c->source.base[plane], a.org_pitch = c->source.pitch[plane];
-    a.W = g.width, a.H = g.height, a.pw = pw, a.ph = ph, a.ss = ss, a.blk_log2 = bl, a.nbx = nbx, a.max_val = (1 << bd) - 1;
-    a.herr = sc->d_herr, a.hcnt = sc->d_hcnt, a.luts = sc->d_luts, a.dist = sc->d_dist, a.groups = sc->d_groups;
-    const int  tiles_x = (pw + 63) / 64, tiles_y = (ph + 63) / 64;
-    const bool u8 = g.sample_bytes == 1;
-
-    // trial filter + per-block SSE for the `ns` slots described in sc->h_groups / sc->h_luts; results in sc->h_dist[(slot*8 + l)*nfb + fb]
-    auto run_try = [&](int ns) -> int {
-        CUDA_TRY(c, cudaMemcpyAsync(sc->d_groups, sc->h_groups, sizeof(CdGroup) * (size_t)ns, cudaMemcpyHostToDevice, stream));
-        CUDA_TRY(c, cudaMemcpyAsync(sc->d_luts, sc->h_luts, (size_t)ns * CD_MAX_LUT * 2048, cudaMemcpyHostToDevice, stream));
-        CUDA_TRY(c, cudaMemsetAsync(sc->d_dist, 0, sizeof(unsigned long long) * (size_t)ns * CD_MAX_LUT * nfb, stream));
-        const dim3 grid(tiles_x, tiles_y, ns);
-        if (u8)
-            launch_try<uint8_t>(a, grid, stream);
-        else
-            launch_try<uint16_t>(a, grid, stream);
-        CUDA_TRY(c, cudaGetLastError());
-        (*launches)++;
-        CUDA_TRY(c, cudaMemcpyAsync(sc->h_dist, sc->d_dist, sizeof(unsigned long long) * (size_t)ns * CD_MAX_LUT * nfb, cudaMemcpyDeviceToHost, stream));
-        CUDA_TRY(c, cudaStreamSynchronize(stream));
-        return SVTF_OK;
-    };
-
-    // unfiltered distortion: the trial kernel with an all-zero LUT (band-only so no classes are evaluated)
-    std::vector<uint64_t> unf(nfb);
-    {
-        memset(sc->h_luts, 0, 2048);
-        CdGroup &z = sc->h_groups[0];
-        memset(&z, 0, sizeof(z));
-        z.bo = 1, z.nl = 1, z.shift[0] = bd;
-        if (int r = run_try(1))
-            return r;
-        for (int i = 0; i < nfb; i++) unf[i] = sc->h_dist[i];
-    }
-    uint64_t unf_total = 0;
-    for (int i = 0; i < nfb; i++) unf_total += unf[i];
-    const double unfiltered_cost = ccso_rd_cost(rdmult, 1, unf_total, bd);
-    const int    frame_bits = 10, frame_bits_bo = 5; // EbPickccso.c:531-546 with CONFIG_CCSO_SIGFIX
-    static const int taps[6][2] = {{-1, 0}, {-1, -1}, {0, -1}, {1, -1}, {0, -3}, {0, -5}}; // derive_ccso_sample_pos
-
-    // ---- the groups, in the reference's loop order ----
-    struct Group {
-        int                    bo, sup, q, clf, intervals, nbands, fine;
-        CdGroup                dev;
-        std::vector<BandState> st;
-    };
-    std::vector<Group> groups;
-    int                hoff = 0;
-    for (int bo = 0; bo < 2; bo++)
-        for (int sup = 0; sup < (bo ? 1 : 6); sup++)
-            for (int q = 0; q < (bo ? 1 : 4); q++)
-                for (int clf = 0; clf < (bo ? 1 : 2); clf++) {
-                    Group gr;
-                    gr.bo = bo, gr.sup = sup, gr.q = q, gr.clf = clf;
-                    gr.intervals = clf ? 2 : 3, gr.nbands = bo ? 8 : 4, gr.fine = gr.nbands - 1; // finest band_log2 of the group
-                    memset(&gr.dev, 0, sizeof(gr.dev));
-                    gr.dev.bo = bo, gr.dev.dy = taps[sup][0], gr.dev.dx = taps[sup][1], gr.dev.thr = kCcsoQuant[q], gr.dev.edge_clf = clf;
-                    gr.dev.hist_shift = bd - gr.fine, gr.dev.nidx = bo ? 2048 : 128, gr.dev.hoff = hoff;
-                    hoff += gr.dev.nidx * nfb;
-                    groups.push_back(std::move(gr));
-                }
-    const int ng = (int)groups.size();
-
-    static const bool timing = getenv("SVTF_CCSO_TIMING") != nullptr;
-    auto              tnow   = [] { return std::chrono::steady_clock::now(); };
-    auto              tms    = [](std::chrono::steady_clock::time_point a0, std::chrono::steady_clock::time_point b0) {
-        return std::chrono::duration<double, std::milli>(b0 - a0).count();
-    };
-    double     t_hist = 0, t_fold = 0, t_lut = 0, t_try = 0, t_post = 0;
-    int        rounds = 0;
-    const auto t0 = tnow();
-    // ---- every group's histograms at its finest band split: one launch ----
-    {
-        for (int k = 0; k < ng; k++) sc->h_groups[k] = groups[k].dev;
-        const size_t hbytes = sizeof(int) * (size_t)hoff;
-        CUDA_TRY(c, cudaMemcpyAsync(sc->d_groups, sc->h_groups, sizeof(CdGroup) * (size_t)ng, cudaMemcpyHostToDevice, stream));
-        CUDA_TRY(c, cudaMemsetAsync(sc->d_herr, 0, hbytes, stream));
-        CUDA_TRY(c, cudaMemsetAsync(sc->d_hcnt, 0, hbytes, stream));
-        const dim3 grid(tiles_x, tiles_y, ng);
-        if (u8)
-            launch_hist<uint8_t>(a, grid, stream);
-        else
-            launch_hist<uint16_t>(a, grid, stream);
-        CUDA_TRY(c, cudaGetLastError());
-        (*launches)++;
-        CUDA_TRY(c, cudaMemcpyAsync(sc->h_herr, sc->d_herr, hbytes, cudaMemcpyDeviceToHost, stream));
-        CUDA_TRY(c, cudaMemcpyAsync(sc->h_hcnt, sc->d_hcnt, hbytes, cudaMemcpyDeviceToHost, stream));
-        CUDA_TRY(c, cudaStreamSynchronize(stream));
-    }
-    const auto t1 = tnow();
-    t_hist = tms(t0, t1);
-    // per band count: histograms at that granularity (band = finest band >> (fine - log2))
-    // (finest first, every coarser band count from the next finer one: band j of b = bands 2j and 2j+1 of b+1)
-    ccso_parallel_for(ng, [&](int gi) {
-        Group &gr = groups[gi];
-        gr.st.resize(gr.nbands);
-        const int *herr = sc->h_herr + gr.dev.hoff, *hcnt = sc->h_hcnt + gr.dev.hoff;
-        for (int b = gr.fine; b >= 0; b--) {
-            BandState &s = gr.st[b];
-            s.ctl.assign(nfb, 1), s.best_ctl.assign(nfb, 0);
-            memset(s.lut, 0, sizeof(s.lut)), memset(s.best_lut, 0, sizeof(s.best_lut));
-            const int ne = 16 << b; // LUT indices < (1<<b) << 4
-            s.herr.resize((size_t)nfb * ne), s.hcnt.resize((size_t)nfb * ne);
-            if (b == gr.fine) { // ne == nidx for the band-only group (2048); the edge groups keep 128 entries per block on the device
-                for (int fb = 0; fb < nfb; fb++) {
-                    memcpy(&s.herr[(size_t)fb * ne], herr + (size_t)fb * gr.dev.nidx, sizeof(int) * ne);
-                    memcpy(&s.hcnt[(size_t)fb * ne], hcnt + (size_t)fb * gr.dev.nidx, sizeof(int) * ne);
-                }
-                continue;
-            }
-            const BandState &f  = gr.st[b + 1];
-            const int        nf = 16 << (b + 1);
-            for (int fb = 0; fb < nfb; fb++)
-                for (int j = 0; j < (1 << b); j++)
-                    for (int k = 0; k < 16; k++) {
-                        s.herr[(size_t)fb * ne + (j << 4) + k] = f.herr[(size_t)fb * nf + ((2 * j) << 4) + k] + f.herr[(size_t)fb * nf + ((2 * j + 1) << 4) + k];
-                        s.hcnt[(size_t)fb * ne + (j << 4) + k] = f.hcnt[(size_t)fb * nf + ((2 * j) << 4) + k] + f.hcnt[(size_t)fb * nf + ((2 * j + 1) << 4) + k];
-                    }
-        }
-    });
-    t_fold = tms(t1, tnow());
-    // ---- lock-step training rounds over every (group, band) still in training ----
-    for (;;) {
-        const auto r0 = tnow();
-        int slot_group[CD_MAX_GROUPS], slot_band[CD_MAX_GROUPS][CD_MAX_LUT], ns = 0;
-        int task_g[CD_MAX_GROUPS * CD_MAX_LUT], task_b[CD_MAX_GROUPS * CD_MAX_LUT], ntask = 0;
-        for (int k = 0; k < ng; k++)
-            for (int b = 0; b < groups[k].nbands; b++)
-                if (groups[k].st[b].keep && groups[k].st[b].enable)
-                    task_g[ntask] = k, task_b[ntask] = b, ntask++;
-        ccso_parallel_for(ntask, [&](int t) { // ccso_compute_class_err + derive_lut_offset of every band still enabled
-            Group     &gr = groups[task_g[t]];
-            const int  b  = task_b[t], ne = 16 << b;
-            BandState &s  = gr.st[b];
-            int        err[2048], cnt[2048];
-            memset(err, 0, sizeof(int) * ne), memset(cnt, 0, sizeof(int) * ne);
-            memset(s.lut, 0, sizeof(s.lut));
-            const int n = gr.bo ? 1 : gr.intervals;
-            for (int fb = 0; fb < nfb; fb++) {
-                if (!s.ctl[fb])
-                    continue;
-                const int *he = &s.herr[(size_t)fb * ne], *hc = &s.hcnt[(size_t)fb * ne];
-                for (int bn = 0; bn < (1 << b); bn++)
-                    for (int d0 = 0; d0 < n; d0++)
-                        for (int d1 = 0; d1 < n; d1++) {
-                            const int i = (bn << 4) + (d0 << 2) + d1;
-                            err[i] += he[i], cnt[i] += hc[i];
-                        }
-            }
-            ccso_lut_from_means(s.lut, err, cnt, b, gr.intervals, gr.bo);
-        });
-        for (int k = 0; k < ng; k++) {
-            Group &gr = groups[k];
-            int    na = 0;
-            for (int b = 0; b < gr.nbands; b++) {
-                BandState &s = gr.st[b];
-                if (!s.keep)
-                    continue;
-                memcpy(sc->h_luts + ((size_t)ns * CD_MAX_LUT + na) * 2048, s.lut, 2048);
-                gr.dev.shift[na] = bd - b, slot_band[ns][na] = b, na++;
-            }
-            if (!na)
-                continue;
-            gr.dev.nl          = na;
-            sc->h_groups[ns]   = gr.dev;
-            slot_group[ns]     = k, ns++;
-        }
-        if (!ns)
-            break;
-        const auto r1 = tnow();
-        if (int r = run_try(ns))
-            return r;
-        const auto r2 = tnow();
-        rounds++;
-        ccso_parallel_for(ns, [&](int sl) {
-            Group &gr = groups[slot_group[sl]];
-            for (int k = 0; k < sc->h_groups[sl].nl; k++) {
-                BandState      &s   = gr.st[slot_band[sl][k]];
-                const uint64_t *trn = reinterpret_cast<const uint64_t *>(sc->h_dist) + ((size_t)sl * CD_MAX_LUT + k) * nfb;
-                bool            improvement = false;
-                uint64_t        cur_dist = 0;
-                if (s.enable) { // derive_blk_md
-                    bool any = false;
-                    for (int fb = 0; fb < nfb; fb++) {
-                        const bool on = trn[fb] < unf[fb];
-                        s.ctl[fb]     = on;
-                        cur_dist += on ? trn[fb] : unf[fb];
-                        any |= on;
-                    }
-                    s.enable = any;
-                }
-                if (s.enable) {
-                    const int    bits = ccso_lut_bits(s.lut, slot_band[sl][k], gr.intervals, gr.bo) + (gr.bo ? frame_bits_bo : frame_bits) + nfb;
-                    const double cost = ccso_rd_cost(rdmult, bits, cur_dist, bd);
-                    if (cost < s.prev_cost)
-                        s.prev_cost = cost, improvement = true;
-                    if (cost < s.best_cost) {
-                        s.best_cost = cost;
-                        memcpy(s.best_lut, s.lut, sizeof(s.lut));
-                        s.best_ctl = s.ctl;
-                    }
-                }
-                s.iter++;
-                if (!improvement || s.iter > 15) // CCSO_MAX_ITERATIONS
-                    s.keep = false;
-            }
-        });
-        t_lut += tms(r0, r1), t_try += tms(r1, r2), t_post += tms(r2, tnow());
-    }
-    if (timing)
-        fprintf(stderr, "ccso_derive_plane %d: histograms %.2f ms, fold %.2f, %d rounds: luts %.2f, try %.2f, decisions %.2f\n", plane, t_hist, t_fold,
-                rounds, t_lut, t_try, t_post);
-    // ---- the reference's order: strict "<" keeps the earlier setting on ties ----
-    double               final_cost      = DBL_MAX;
-    int8_t               final_lut[2048] = {0};
-    std::vector<uint8_t> final_ctl(nfb, 0);
-    int                  final_clf = 0, final_q = 0, final_sup = 0, final_bo = 0, final_band = 0;
-    for (const Group &gr : groups)
-        for (int b = 0; b < gr.nbands; b++)
-            if (gr.st[b].best_cost < final_cost) {
-                final_cost = gr.st[b].best_cost;
-                final_q = gr.q, final_sup = gr.sup, final_bo = gr.bo, final_band = b, final_clf = gr.clf;
-                memcpy(final_lut, gr.st[b].best_lut, sizeof(final_lut));
-                final_ctl = gr.st[b].best_ctl;
-            }
-    const bool on = !(unfiltered_cost < final_cost);
-    out->ccso_enable[plane] = on;
-    memset(flags, 0, nfb);
-    if (on) {
-        memcpy(flags, final_ctl.data(), nfb);
-        memcpy(out->filter_offset[plane], final_lut, 2048);
-        out->quant_idx[plane] = (uint8_t)final_q, out->ext_filter_support[plane] = (uint8_t)final_sup;
-        out->ccso_bo_only[plane] = (uint8_t)final_bo, out->max_band_log2[plane] = (uint8_t)final_band;
-        out->edge_clf[plane] = (uint8_t)final_clf;
-    }
-    return SVTF_OK;
-}
-
-extern "C" int svtf_ccso_derive_frame(svtf_ctx *c, int32_t rdmult, int32_t plane_start, int32_t plane_end, svtf_ccso_params *out,
-                                      uint8_t *const blk_flags[3]) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_ccso_derive_frame: NULL context");
-    if (!out || !blk_flags || plane_start < 0 || plane_end > 3 || plane_start > plane_end || rdmult < 0)
-        return c->fail(SVTF_E_ARG, "svtf_ccso_derive_frame: bad argument");
-    if (!c->have_frame || !c->have_source)
-        return c->fail(SVTF_E_STATE, "svtf_ccso_derive_frame: upload the picture and the source first");
-    if (c->striped)
-        return c->fail(SVTF_E_STATE, "svtf_ccso_derive_frame: not available on a striped context");
-    CUDA_TRY(c, cudaSetDevice(c->device));
-    for (int p = plane_start; p < plane_end; p++)
-        if (!blk_flags[p])
-            return c->fail(SVTF_E_ARG, "svtf_ccso_derive_frame: NULL flag array for a requested plane");
-    // the planes are independent (each writes its own fields of *out): one host thread and one stream per plane, behind what is queued
-    // on the context's stream.  SVTF_CCSO_SERIAL=1: one plane after the other on the context's stream.
-    static const bool serial = getenv("SVTF_CCSO_SERIAL") != nullptr;
-    uint64_t          nl[3]  = {0, 0, 0};
-    int               rc[3]  = {SVTF_OK, SVTF_OK, SVTF_OK};
-    if (serial || plane_end - plane_start < 2) {
-        for (int p = plane_start; p < plane_end; p++) {
-            rc[p] = ccso_derive_plane(c, p, rdmult, out, blk_flags[p], c->stream, &nl[p]);
-            c->launches += nl[p];
-            if (rc[p])
-                return rc[p];
-        }
-        return SVTF_OK;
-    }
-    if (!c->derive_ev)
-        CUDA_TRY(c, cudaEventCreateWithFlags(&c->derive_ev, cudaEventDisableTiming));
-    CUDA_TRY(c, cudaEventRecord(c->derive_ev, c->stream));
-    for (int p = plane_start; p < plane_end; p++) {
-        if (!c->derive_stream[p])
-            CUDA_TRY(c, cudaStreamCreateWithFlags(&c->derive_stream[p], cudaStreamNonBlocking));
-        CUDA_TRY(c, cudaStreamWaitEvent(c->derive_stream[p], c->derive_ev, 0));
-    }
-    std::vector<std::thread> th;
-    for (int p = plane_start; p < plane_end; p++)
-        th.emplace_back([&, p] {
-            if (cudaSetDevice(c->device) != cudaSuccess) {
-                rc[p] = SVTF_E_CUDA;
-                return;
-            }
-            rc[p] = ccso_derive_plane(c, p, rdmult, out, blk_flags[p], c->derive_stream[p], &nl[p]);
-        });
-    for (auto &t : th) t.join();
-    for (int p = plane_start; p < plane_end; p++) c->launches += nl[p];
-    for (int p = plane_start; p < plane_end; p++)
-        if (rc[p])
-            return rc[p]; // the plane's own message is in svtf_last_error (every round ends with a stream synchronisation)
-    return SVTF_OK;
-}
-
-
-// ---- deblocking level search -------------------------------------------------------------------------
-// ---- loop restoration (svtf_lr.cuh) --------------------------------------------------------------------
-extern "C" int svtf_lr_apply_frame(svtf_ctx *c, const svtf_lr_params *lr, const svtf_lr_unit *const units[3]) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_lr_apply_frame: NULL context");
-    if (!lr || !units)
-        return c->fail(SVTF_E_ARG, "svtf_lr_apply_frame: NULL argument");
-    if (!c->have_frame)
-        return c->fail(SVTF_E_STATE, "svtf_lr_apply_frame: upload a picture first");
-    if (c->striped)
-        return c->fail(SVTF_E_STATE, "svtf_lr_apply_frame: not available on a striped context");
-    bool any = false;
-    int  hu[3], vu[3], first[3], total = 0;
-    for (int p = 0; p < 3; p++) {
-        const int us = lr->restoration_unit_size[p], ft = lr->frame_restoration_type[p];
-        hu[p] = vu[p] = 0, first[p] = total;
-        if (ft == SVTF_RESTORE_NONE)
-            continue;
-        if ((us != 32 && us != 64 && us != 128 && us != 256) || (p == 0 && us == 32) || !units[p])
-            return c->fail(SVTF_E_ARG, "svtf_lr_apply_frame: bad restoration unit size or NULL unit array");
-        svtf_lr_units(&c->geom, p, us, &hu[p], &vu[p]);
-        for (int u = 0; u < hu[p] * vu[p]; u++) {
-            const svtf_lr_unit &x = units[p][u];
-            if (x.restoration_type < 0 || x.restoration_type > SVTF_RESTORE_SGRPROJ ||
-                (x.restoration_type == SVTF_RESTORE_SGRPROJ && (x.sgr_ep < 0 || x.sgr_ep > 15)))
-                return c->fail(SVTF_E_ARG, "svtf_lr_apply_frame: bad restoration unit");
-        }
-        total += hu[p] * vu[p];
-        any = true;
-    }
-    if (!any)
-        return SVTF_OK; // nothing to restore: the picture stays where it is
-    CUDA_TRY(c, cudaSetDevice(c->device));
-    if (!c->surf[3].base[0]) {
-        cudaError_t e = alloc_surface(c->surf[3], c->max_geom);
-        if (e != cudaSuccess)
-            return c->cuda_fail(e, "cudaMalloc(restoration surface)");
-    }
-    if (c->lr_units_cap < (size_t)total) {
-        if (c->d_lr_units)
-            cudaFree(c->d_lr_units);
-        c->d_lr_units = nullptr, c->lr_units_cap = 0;
-        CUDA_TRY(c, cudaMalloc(&c->d_lr_units, sizeof(LrUnitDev) * total));
-        c->lr_units_cap = total;
-    }
-    std::vector<LrUnitDev> host(total);
-    for (int p = 0; p < 3; p++)
-        for (int u = 0; u < hu[p] * vu[p]; u++) {
-            const svtf_lr_unit &x = units[p][u];
-            LrUnitDev          &d = host[first[p] + u];
-            d.type = x.restoration_type, d.ep = x.sgr_ep, d.xqd[0] = x.sgr_xqd[0], d.xqd[1] = x.sgr_xqd[1];
-            for (int t = 0; t < 8; t++) d.vf[t] = x.wiener_vfilter[t], d.hf[t] = x.wiener_hfilter[t];
-        }
-    CUDA_TRY(c, cudaMemcpyAsync(c->d_lr_units, host.data(), sizeof(LrUnitDev) * total, cudaMemcpyHostToDevice, c->stream));
-    CUDA_TRY(c, cudaStreamSynchronize(c->stream)); // `host` goes out of scope
-    LrArgs a;
-    a.cur = c->surf[c->cur].planes();
-    a.dbk = c->surf[c->pre_cdef >= 0 ? c->pre_cdef : c->cur].planes();
-    a.out = c->surf[3].planes();
-    if (c->cur == 3)
-        return c->fail(SVTF_E_STATE, "svtf_lr_apply_frame: the current picture is already a restoration output");
-    int grid = 0;
-    for (int p = 0; p < 3; p++) {
-        const int ss = p ? 1 : 0;
-        a.pw[p] = (c->geom.width + ss) >> ss, a.ph[p] = (c->geom.height + ss) >> ss;
-        a.cw[p] = (c->geom.mi_cols * 4) >> ss, a.chh[p] = (c->geom.mi_rows * 4) >> ss;
-        a.unit[p] = lr->restoration_unit_size[p], a.hu[p] = hu[p], a.vu[p] = vu[p];
-        a.units[p]      = c->d_lr_units + first[p];
-        a.frame_type[p] = lr->frame_restoration_type[p];
-        const int sh = 64 >> ss, off = 8 >> ss;
-        a.chunks[p]  = (a.cw[p] + (LR_MAXW >> ss) - 1) / (LR_MAXW >> ss);
-        a.stripes[p] = (a.ph[p] + off + sh - 1) / sh + 1; // + the tail below the visible picture
-        a.base[p]    = grid;
-        grid += a.chunks[p] * a.stripes[p];
-    }
-    a.opt = lr->optimized_lr != 0, a.bd = c->geom.bit_depth;
-    if (c->geom.sample_bytes == 1)
-        lr_kernel<uint8_t><<<grid, LR_THREADS, 0, c->stream>>>(a);
-    else
-        lr_kernel<uint16_t><<<grid, LR_THREADS, 0, c->stream>>>(a);
-    CUDA_TRY(c, cudaGetLastError());
-    c->launches++;
-    c->cur = 3;
-    return SVTF_OK;
-}
-
+#include "svtf_search_api.inl"
+#include "svtf_ccso_derive_api.inl"
+#include "svtf_lr_api.inl"
 #include "svtf_lrs_api.inl" // super-resolution upscale + loop-restoration filter search entry points
-
-// svt_av1_pick_filter_level(LPF_PICK_FROM_FULL_IMAGE) (Encoder/Codec/EbDeblockingFilter.c:1129-1252):
-// search_filter_level (:886-985) per plane with try_filter_frame (:841-880) = deblock one plane with a trial level,
-// picture_sse_calculations (:716-835) against the source, restore.  On the device a trial is ONE launch: the deblock kernel's
-// SSE instantiation filters that plane's tiles in shared memory and measures them against the source instead of writing
-// them; nothing is restored because the unfiltered picture is never overwritten.
-// search_filter_level (Encoder/Codec/EbDeblockingFilter.c:886-985) for one plane as a state machine (dir 2 = both luma
-// directions, as svt_av1_pick_filter_level calls it): `wanted()` names the levels the next step of the reference's loop
-// would try (filt_low and filt_high are tried independently of each other's result), `advance()` is the loop body once
-// their errors are known.  The three planes' searches are independent of one another (a plane's trial filters that plane
-// alone, with that plane's level), so svtf_lf_search_frame runs them in lock-step: one batch of trials = up to six
-// deblock+SSE launches and ONE host round trip, instead of one round trip per trial.
-struct LfPlaneSearch {
-    int     plane, filt_mid, step, filt_best, direction = 0, convergence = 0;
-    int64_t best_err = 0, ss_err[64];
-    bool    started = false;
-    void init(int p, int lvl) {
-        plane    = p;
-        filt_mid = std::min(std::max(lvl, 0), 63); // MAX_LOOP_FILTER
-        step     = filt_mid < 16 ? 4 : filt_mid / 4;
-        for (int i = 0; i < 64; i++) ss_err[i] = -1;
-        filt_best = filt_mid;
-    }
-    bool done() const { return started && step <= 0; }
-    int  low() const { return std::max(filt_mid - step, 0); }
-    int  high() const { return std::min(filt_mid + step, 63); }
-    int  wanted(int lv[2]) const {
-        int n = 0;
-        if (!started) {
-            lv[n++] = filt_mid;
-            return n;
-        }
-        if (direction <= 0 && low() != filt_mid && ss_err[low()] < 0)
-            lv[n++] = low();
-        if (direction >= 0 && high() != filt_mid && ss_err[high()] < 0 && !(n && lv[0] == high()))
-            lv[n++] = high();
-        return n;
-    }
-    void advance(const svtf_lf_search_cfg *cfg) {
-        if (!started) {
-            started  = true;
-            best_err = ss_err[filt_mid];
-            return;
-        }
-        const int filt_high = high(), filt_low = low();
-        int64_t   bias      = (best_err >> (15 - (filt_mid / 8))) * step; // bias against raising the level
-        if (!cfg->only_4x4)
-            bias >>= 1;
-        if (direction <= 0 && filt_low != filt_mid) {
-            if (ss_err[filt_low] < best_err + bias) {
-                if (ss_err[filt_low] < best_err)
-                    best_err = ss_err[filt_low];
-                filt_best = filt_low;
-            }
-        }
-        if (direction >= 0 && filt_high != filt_mid) {
-            if (ss_err[filt_high] < best_err - bias) {
-                best_err  = ss_err[filt_high];
-                filt_best = filt_high;
-            }
-        }
-        if (filt_best == filt_mid) {
-            convergence++;
-            if (convergence == cfg->early_exit_convergence)
-                step = 0;
-            else
-                step /= 2;
-            direction = 0;
-        } else {
-            direction = filt_best < filt_mid ? -1 : 1;
-            filt_mid  = filt_best;
-        }
-    }
-};
-
-extern "C" int svtf_lf_search_frame(svtf_ctx *c, const svtf_lf_params *start, const svtf_lf_search_cfg *cfg, int32_t out_levels[4]) {
-    if (!c)
-        return set_global_error(SVTF_E_ARG, "svtf_lf_search_frame: NULL context");
-    if (!start || !cfg || !out_levels)
-        return c->fail(SVTF_E_ARG, "svtf_lf_search_frame: NULL argument");
-    if (int r = need_frame_mi(c, "svtf_lf_search_frame"))
-        return r;
-    if (!c->have_source)
-        return c->fail(SVTF_E_STATE, "svtf_lf_search_frame: upload the source picture first");
-    if (c->striped)
-        return c->fail(SVTF_E_STATE, "svtf_lf_search_frame: not available on a striped context");
-    CUDA_TRY(c, cudaSetDevice(c->device));
-    const int32_t last[4] = {start->filter_level[0], start->filter_level[1], start->filter_level_u, start->filter_level_v};
-    int32_t       y = 0, u = last[2], v = last[3];
-    LfPlaneSearch ps[3];
-    // luma is searched with dir = 2 and the start level is last_frame_filter_level[dir] unless dlf_avg: index 2 is the U
-    // level (:903-909) — kept as the reference has it
-    ps[0].init(0, cfg->dlf_avg ? last[0] : last[2]);
-    ps[1].init(1, last[2]);
-    ps[2].init(2, last[3]);
-    const int           nplanes = cfg->search_chroma ? 3 : 1;
-    unsigned long long *d_out   = reinterpret_cast<unsigned long long *>(c->d_pick_tot); // 48 bytes of an idle scratch buffer
-    for (;;) {
-        int trial_plane[6], trial_level[6], nt = 0;
-        for (int p = 0; p < nplanes; p++) {
-            if (ps[p].done())
-                continue;
-            int       lv[2];
-            const int n = ps[p].wanted(lv);
-            for (int k = 0; k < n; k++) trial_plane[nt] = p, trial_level[nt] = lv[k], nt++;
-        }
-        if (nt) {
-            CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out) * 6, c->stream));
-            for (int t = 0; t < nt; t++) { // try_filter_frame (:841-880): this plane, this level
-                svtf_lf_params lf = *start;
-                if (trial_plane[t] == 0)
-                    lf.filter_level[0] = lf.filter_level[1] = trial_level[t];
-                else if (trial_plane[t] == 1)
-                    lf.filter_level_u = trial_level[t];
-                else
-                    lf.filter_level_v = trial_level[t];
-                if (int r = deblock_impl(c, &lf, trial_plane[t], trial_plane[t] + 1, true, nullptr, 0, 0, d_out + t))
-                    return r;
-            }
-            unsigned long long res[6] = {0, 0, 0, 0, 0, 0};
-            CUDA_TRY(c, cudaMemcpyAsync(res, d_out, sizeof(*d_out) * 6, cudaMemcpyDeviceToHost, c->stream));
-            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-            for (int t = 0; t < nt; t++) ps[trial_plane[t]].ss_err[trial_level[t]] = (int64_t)res[t];
-        }
-        bool all_done = true;
-        for (int p = 0; p < nplanes; p++)
-            if (!ps[p].done()) {
-                ps[p].advance(cfg);
-                all_done = all_done && ps[p].done();
-            }
-        if (all_done)
-            break;
-    }
-    CUDA_TRY(c, cudaMemsetAsync(d_out, 0, sizeof(*d_out) * 6, c->stream)); // the pick expects a zeroed tot
-    y = ps[0].filt_best;
-    if (cfg->search_chroma)
-        u = ps[1].filt_best, v = ps[2].filt_best;
-    out_levels[0] = out_levels[1] = y, out_levels[2] = u, out_levels[3] = v;
-    return SVTF_OK;
-}
-
+#include "svtf_lf_search_api.inl"
 #include "svtf_multi_api.inl"   // one picture across several GPUs: NCCL halo exchange and search-table gather
 #include "svtf_noalloc_api.inl" // svtf_cdef_pick_table_noalloc: the pick on a static device scratch array (no allocation)
