@@ -85,12 +85,14 @@ __device__ __forceinline__ void cdef5_row(const uint32_t *ctr, const int2 (&o)[6
             }
         }
     }
-    const __half2 k16 = u2h(0x2C002C00u), k32 = u2h(0x28002800u); // 1/16, 1/32
+    const __half2 k16b = u2h(0x2C012C01u), k1536 = u2h(0x66006600u), kn1536 = u2h(0xE600E600u);
 #pragma unroll
     for (int j = 0; j < NP; j++) {
-        // (8 + sum - (sum < 0)) >> 4 = sign(sum) * floor((|sum| + 8) / 16) = sign(sum) * RN(|sum|/16 + 1/32)  (<= |sum|)
-        const __half2 q = __hadd2(__hadd2(__hfma2(__habs2(acc[j]), k16, k32), k1024), kn1024);
-        const __half2 y = __hmin2(__hmax2(__hadd2(u2h(x[j]), u2h(pk_xsmin(h2u(acc[j]), h2u(q)))), u2h(mn[j])), u2h(mx[j]));
+        // (8 + sum - (sum < 0)) >> 4 = sum/16 rounded to the nearest integer, halves away from zero = RN(sum * (1/16 + 2^-14) + 1536) - 1536:
+        // the fma is exact before its single rounding to the integer grid of [1024, 2048); the 2^-14 term breaks halves away from zero and
+        // is too small (|sum| <= 912) to carry anything else across one (svtf_search3.cuh, s3_err).  x + delta = (x - 1536) + t, exact.
+        const __half2 t = __hfma2(acc[j], k16b, k1536);
+        const __half2 y = __hmin2(__hmax2(__hadd2(__hadd2(u2h(x[j]), kn1536), t), u2h(mn[j])), u2h(mx[j]));
         outw[j]         = h2u(y) & C5_MASK;
     }
 }

@@ -6,8 +6,8 @@
 // primary taps per primary strength and the 8 secondary taps per secondary strength once (svtf_search2.cuh explains
 // why that is the same as filtering once per (pri,sec) pair); a combination is then
 //   s  = Ap + S                                   HADD2   (exact: |s| <= 912)
-//   r  = (8 + s - (s < 0)) >> 4 = RN(s/16 + copysign(1/32, s))
-//   e' = clamp(r, min - x, max - x) + 1536        LOP3, HFMA2, HADD2 (+1536: rounds to the integer), HMNMX2 x2
+//   r  = (8 + s - (s < 0)) >> 4 = s/16 rounded half away from zero = RN(s * (1/16 + 2^-14) + 1536) - 1536   (s3_err)
+//   e' = clamp(r, min - x, max - x) + 1536        HFMA2 (rounds to the integer), HMNMX2 x2
 // and because 1536 + e (|e| <= 57) lies in [1024, 2048), the low byte of each fp16 half IS e as int8: one PRMT packs
 // four errors for the DP4A / DP2A moments, which stay integer exactly as in search2.  A primary tap costs 7
 // instructions per pair (12 in search2), a secondary tap 1 + 3*6 (4 + 3*8), a combination 6 + the moments (9 + ...).
@@ -94,9 +94,11 @@ __device__ __forceinline__ void s3_row_primary(const uint32_t *ctr, const int2 o
 
 // filtered - unfiltered for one pair: fp16 halves 1536 + e, whose low bytes are e as int8
 __device__ __forceinline__ uint32_t s3_err(const __half2 s, const __half2 lo, const __half2 hi) {
-    const __half2 k16 = u2h(0x2C002C00u), k1536 = u2h(0x66006600u);
-    const __half2 c   = u2h((h2u(s) & 0x80008000u) | 0x28002800u); // copysign(1/32, s)
-    const __half2 t   = __hadd2(__hfma2(s, k16, c), k1536);
+    // (8 + s - (s < 0)) >> 4 is s/16 rounded to the nearest integer, halves away from zero.  ONE fma does it: s * (1/16 + 2^-14) + 1536
+    // is computed exactly and rounded once to the fp16 grid of [1024, 2048), i.e. to an integer; the 2^-14 term pushes a half away from
+    // zero (|s| * 2^-14 > 0) and never carries a non-half across one (|s| * 2^-14 <= 912 / 16384 < 1/16, the spacing of s/16).
+    const __half2 k16b = u2h(0x2C012C01u), k1536 = u2h(0x66006600u);
+    const __half2 t    = __hfma2(s, k16b, k1536);
     return h2u(__hmin2(__hmax2(t, lo), hi));
 }
 
