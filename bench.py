@@ -180,6 +180,7 @@ def ccso_derive_leg(H, S, geom, wl, ctx, np, with_cpu):
     ctx.set_mi(wl["mi"])
     ctx.cdef_frame(wl["cdef"], wl["idx"])
     ctx.sync()
+    ctx.ccso_search(4000)  # the first call allocates the derivation's device and pinned buffers
     l0 = ctx.launch_count
     t0 = time.perf_counter()
     out, _ = ctx.ccso_search(4000)
