@@ -874,7 +874,7 @@ def run_reference_arm(args):
         "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit_line(line)
     return 0
 
 
@@ -935,7 +935,30 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+_STDOUT_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries below this script write there too (NCCL prints its version line from C when a
+    communicator is created), so file descriptor 1 is pointed at stderr for the whole run and the line goes out through a saved copy."""
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_STDOUT_FD, data)
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -1217,7 +1240,7 @@ def main():
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
             "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "lr_search": lrs, "superres": sres, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5, "stripes_8k": s8k, "pcie": pcie,
         }
-        print(json.dumps(line))
+        emit_line(line)
     for p in pins_in + pins_out + pins_mi:
         p.close()
     for c in ctxs:
