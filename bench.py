@@ -718,6 +718,53 @@ def adapter_e2e_leg(H, S, geom, wls, nsrc, B, steps, barrier, device, np):
     return {"seconds": secs, "pictures": B * passes, "host_threads": NT, "matches_device_path": ok, "ms_per_picture": round(secs / (B * passes) * 1e3, 4)}
 
 
+def app_leg(frames):
+    """BASELINE configs[0] for context: the reference's own SvtAv1EncApp --preset 8 on a 1080p 8-bit clip, unmodified and with the filter
+    stages replaced by the adapters over libsvtfilt_b200.so (integration/build.sh builds both; C-only builds, the image has no nasm), then
+    both SvtAv1DecApp builds on the resulting stream.  Reports frames per second of the four runs and whether reconstruction and bitstream
+    are byte-identical — the applications are dominated by mode decision on the host, so the fps are context, not a result."""
+    import hashlib
+    import subprocess
+    import tempfile
+
+    bins = os.path.join(ROOT, "integration", "_bin")
+    need = ["SvtAv1EncApp_ref", "SvtAv1EncApp_b200", "SvtAv1DecApp_ref", "SvtAv1DecApp_b200"]
+    if not all(os.path.exists(os.path.join(bins, b)) for b in need):
+        return None
+    sys.path.insert(0, os.path.join(ROOT, "integration"))
+    import synth_yuv
+
+    def md5(path):
+        h = hashlib.md5()
+        with open(path, "rb") as f:
+            for blk in iter(lambda: f.read(1 << 22), b""):
+                h.update(blk)
+        return h.hexdigest()
+
+    w, h = 1920, 1080
+    out = {"workload": f"SvtAv1EncApp --preset 8, {w}x{h} 8-bit, {frames} synthetic frames; SvtAv1DecApp on that stream", "build": "C only (no nasm in the image)"}
+    with tempfile.TemporaryDirectory() as td:
+        clip = os.path.join(td, "c.yuv")
+        synth_yuv.write_clip(clip, w, h, frames, 8)
+        for tag in ("ref", "b200"):
+            cmd = [os.path.join(bins, "SvtAv1EncApp_" + tag), "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", "8",
+                   "--input-depth", "8", "-b", os.path.join(td, tag + ".ivf"), "-o", os.path.join(td, tag + ".yuv")]
+            t0 = time.perf_counter()
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+            out["enc_fps_" + tag] = round(frames / (time.perf_counter() - t0), 2) if r.returncode == 0 else None
+        ok = all(out["enc_fps_" + t] for t in ("ref", "b200"))
+        out["recon_identical"] = ok and md5(os.path.join(td, "ref.yuv")) == md5(os.path.join(td, "b200.yuv"))
+        out["bitstream_identical"] = ok and md5(os.path.join(td, "ref.ivf")) == md5(os.path.join(td, "b200.ivf"))
+        if ok:
+            for tag in ("ref", "b200"):
+                t0 = time.perf_counter()
+                r = subprocess.run([os.path.join(bins, "SvtAv1DecApp_" + tag), "-i", os.path.join(td, "ref.ivf"), "-o", os.path.join(td, "dec_" + tag + ".yuv")],
+                                   capture_output=True, text=True, timeout=900)
+                out["dec_fps_" + tag] = round(frames / (time.perf_counter() - t0), 2) if r.returncode == 0 else None
+            out["decoded_identical"] = bool(out["dec_fps_ref"] and out["dec_fps_b200"]) and md5(os.path.join(td, "dec_ref.yuv")) == md5(os.path.join(td, "dec_b200.yuv"))
+    return out
+
+
 def pcie_probe_leg(torch, dist, dev, world):
     """What bounds the end-to-end numbers as ranks are added: every rank copies 25 MB blocks (one 4K 10-bit picture) between pinned host
     memory and its GPU — H2D alone, D2H alone, both at once — ALL RANKS AT THE SAME TIME; per-rank GB/s from the slowest rank's time and
@@ -1196,6 +1243,7 @@ def main():
     clocks = sampler.stop() if sampler else None
 
     pcie = pcie_probe_leg(torch, dist, dev, world)
+    app = app_leg(int(os.environ.get("SVTF_BENCH_APP_FRAMES", "20")))  # configs[0] has 60 frames: SVTF_BENCH_APP_FRAMES=60 (minutes on C-only builds) if rank == 0 and world == 1 and not args.no_cpu else None
     c5 = streams_1080p_leg(H, S, torch, dist, dev, local, rank, world, max(5, args.steps))
     s8k = None if args.no_stripes else stripes_8k_leg(H, S, torch, dist, dev, local, rank, world, np, args.steps)
     search = gpu_search_leg(H, S, geom, wls[0], ctxs[:args.search_inflight], max(3, args.steps // 2), np) if rank == 0 else None
@@ -1238,7 +1286,7 @@ def main():
                           "pictures_per_step": B * EP, "inflight": nin, "matches_device_path": bool(e2e_ok),
                           "path": "Tier-1 C ABI from pinned host buffers, mode-info words packed outside the timed region"},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
-            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "lr_search": lrs, "superres": sres, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5, "stripes_8k": s8k, "pcie": pcie,
+            "search": dict(search, cpu_baseline=search_cpu) if search else None, "ccso_derive": derive, "lf_search": lfs, "lr_search": lrs, "superres": sres, "side_info": side, "loop_restoration": lrl, "handoff": hand, "streams_1080p": c5, "stripes_8k": s8k, "pcie": pcie, "app": app,
         }
         emit_line(line)
     for p in pins_in + pins_out + pins_mi:
