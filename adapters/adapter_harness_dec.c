@@ -149,3 +149,20 @@ void        svt_av1_upscale_normative_rows(const Av1Common *cm, const uint8_t *s
     (void)cm, (void)src, (void)src_stride, (void)dst, (void)dst_stride, (void)rows, (void)sub_x, (void)bd, (void)is_16bit_pipeline;
     harness_unreachable("svt_av1_upscale_normative_rows");
 }
+
+/* tests/test_dec_adapter_formats.py: the adapter's answer to a stream format it has no kernels for (expected: message + abort, before
+ * any device call) */
+void harness_dec_format_probe(int mono, int ssx, int ssy) {
+    EbDecHandle         *d = calloc(1, sizeof(*d));
+    EbPictureBufferDesc *r = calloc(1, sizeof(*r));
+    LfCtxt               lf;
+    memset(&lf, 0, sizeof(lf));
+    d->seq_header.color_config.mono_chrome   = (Bool)mono;
+    d->seq_header.color_config.subsampling_x = (uint8_t)ssx;
+    d->seq_header.color_config.subsampling_y = (uint8_t)ssy;
+    d->frame_header.frame_size.frame_width = d->frame_header.frame_size.superres_upscaled_width = 64;
+    d->frame_header.frame_size.frame_height = d->frame_header.frame_size.superres_upscaled_height = 64;
+    d->frame_header.mi_cols = d->frame_header.mi_rows = 16;
+    r->bit_depth = EB_EIGHT_BIT;
+    svt_aom_dec_av1_loop_filter_frame(d, r, &lf, 0, mono ? 1 : 3, 0, 1);
+}

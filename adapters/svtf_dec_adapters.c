@@ -96,8 +96,16 @@ static void stat_hit(int which) {
 
 /* after_superres: the picture as the stages behind the super-resolution upscale see it (loop restoration, EbDecParseObu.c:2434-2455) */
 static svtf_geom geom_of(const EbDecHandle *dec, const EbPictureBufferDesc *pic, int after_superres) {
-    const FrameHeader *fh = &dec->frame_header;
-    svtf_geom          g;
+    const FrameHeader   *fh = &dec->frame_header;
+    const EbColorConfig *cc = &dec->seq_header.color_config;
+    svtf_geom            g;
+    /* the device path is 4:2:0 with three planes (what the reference ENCODER writes, Encoder/Codec/EbEncCdef.c:324-329); the other
+     * formats the reference decoder reads (4:0:0, 4:2:2, 4:4:4: Decoder/Codec/EbDecCdef.c:172-173) have no kernels and no fallback */
+    if (cc->mono_chrome || cc->subsampling_x != 1 || cc->subsampling_y != 1) {
+        fprintf(stderr, "Svt[error]: svtfilt_b200 decoder adapter: only 4:2:0 streams are supported (mono_chrome %d, subsampling %d/%d); "
+                        "no CPU fallback on this path\n", (int)cc->mono_chrome, (int)cc->subsampling_x, (int)cc->subsampling_y);
+        abort();
+    }
     g.width        = fh->frame_size.frame_width; /* the deblock limit, EbDecLF.c:119-124 */
     g.height       = fh->frame_size.frame_height;
     g.mi_cols      = fh->mi_cols;
