@@ -255,6 +255,13 @@ int svtf_rewind(svtf_ctx *ctx);
  * (Encoder/Codec/EbDeblockingFilter.c:624) == svt_aom_dec_av1_loop_filter_frame
  * (Decoder/Codec/EbDecLF.c:697) on the same side info. */
 int svtf_deblock_frame(svtf_ctx *ctx, const svtf_lf_params *lf, int32_t plane_start, int32_t plane_end);
+/* The part of set_lpf_parameters (Encoder/Codec/EbDeblockingFilter.c:162-285) that depends on the mode info alone — transform-edge
+ * alignment, the skip / prediction-block rule, the filter length, the two level keys — is evaluated once per mode-info upload into
+ * two edge-code planes (one word per 4x4 unit; luma, chroma) that every deblock launch on that mode info reads: svtf_set_mi and
+ * svtf_set_mi_soa_* launch that kernel behind their copy (one launch, ~6 us at 4K).  This call rebuilds the planes from the mode
+ * info on the device (stream-ordered) — for timing, and for callers that assemble the grid from pieces (svtf_set_mi_own +
+ * svtf_stripe_exchange), where otherwise the first svtf_deblock_frame* / svtf_lf_search_frame does it. */
+int svtf_deblock_prepare(svtf_ctx *ctx);
 /* The same with per-superblock loop-filter deltas, as the DECODER keeps them (SBInfo.sb_delta_lf, read by
  * dec_set_lpf_parameters through svt_aom_get_filter_level_delta_lf, Decoder/Codec/EbDecLF.c:159-193,357,548):
  * sb_delta_lf[sb_rows*sb_cols][4] (FRAME_LF_COUNT entries per superblock, raster order) replaces lf->curr_delta_lf for

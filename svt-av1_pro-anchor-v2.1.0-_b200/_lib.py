@@ -103,7 +103,7 @@ class DevPlane(C.Structure):
 EXPORTS = [
     "svtf_pack_mi_enc", "svtf_pack_mi_dec", "svtf_set_mi_soa_enc", "svtf_set_mi_soa_dec", "svtf_get_mi", "svtf_upload_pre_cdef", "svtf_lr_units", "svtf_lr_apply_frame", "svtf_lf_build_tables", "svtf_ctx_create", "svtf_ctx_destroy", "svtf_last_error", "svtf_sync",
     "svtf_launch_count", "svtf_frame_begin", "svtf_stripe_begin", "svtf_upload_frame", "svtf_upload_source", "svtf_overwrite_current", "svtf_set_mi",
-    "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
+    "svtf_download_frame", "svtf_download_frame_async", "svtf_rewind", "svtf_deblock_frame", "svtf_deblock_prepare", "svtf_deblock_frame_sb_delta", "svtf_cdef_apply_frame", "svtf_ccso_apply_frame",
     "svtf_filter_chain", "svtf_lf_search_frame", "svtf_ccso_derive_frame", "svtf_cdef_search_frame", "svtf_cdef_pick", "svtf_cdef_pick_table", "svtf_cdef_pick_host", "svtf_dev_planes",
     "svtf_cuda_stream", "svtf_ctx_set_stream", "svtf_host_alloc", "svtf_host_free", "svtf_host_register", "svtf_host_unregister", "svtf_download_ref_padded", "svtf_upload_frame_8as16",
     "svtf_cdef_pick_table_noalloc", "svtf_comm_unique_id", "svtf_comm_create", "svtf_comm_destroy", "svtf_upload_frame_own", "svtf_set_mi_own", "svtf_stripe_exchange", "svtf_cdef_search_gather_pick", "svtf_lr_search_frame", "svtf_lr_wiener_stats", "svtf_lr_wiener_from_stats", "svtf_superres_upscale_frame",
@@ -153,6 +153,7 @@ def load():
     lib.svtf_lr_wiener_stats.argtypes = [vp, i32, i32, i32, vp, vp]
     lib.svtf_lr_wiener_from_stats.argtypes = [i32, vp, vp, C.POINTER(C.c_int16), C.POINTER(C.c_int16)]
     lib.svtf_deblock_frame.argtypes = [vp, C.POINTER(LfParams), i32, i32]
+    lib.svtf_deblock_prepare.argtypes = [vp]
     lib.svtf_deblock_frame_sb_delta.argtypes = [vp, C.POINTER(LfParams), i32, i32, vp, i32, i32]
     lib.svtf_cdef_apply_frame.argtypes = [vp, C.POINTER(CdefParams), vp]
     lib.svtf_ccso_apply_frame.argtypes = [vp, C.POINTER(CcsoParams), C.POINTER(vp)]

@@ -78,6 +78,8 @@ struct svtf_ctx {
     int          pre_cdef = -1; // surface holding the picture before the last CDEF (-1: none)
     svtf_mi_t   *d_mi = nullptr;
     int          mi_stride = 0; // device mi stride == geom.mi_cols rounded
+    uint32_t    *d_edge[2] = {nullptr, nullptr}; // deblock edge-code planes of d_mi (dbk_edge_plane_kernel): luma units, chroma units
+    bool         edge_valid = false;             // false whenever d_mi was written since the planes were computed
     // Small per-picture parameters (CDEF strength index per filter block, CCSO LUT and block flags) live in ONE device
     // block and are sent with ONE DMA from a pinned staging slot, issued before the first kernel of a chain: a small
     // copy queued between two kernels would stall the H2D engine (and the next picture's upload behind it) until the
@@ -212,6 +214,9 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
     c->max_nfb     = nvfb * nhfb;
     c->mi_stride   = round_up(max_geom->mi_cols, 32);
     if ((e = cudaMalloc(&c->d_mi, sizeof(svtf_mi_t) * (size_t)c->mi_stride * max_geom->mi_rows)) != cudaSuccess) return bail(e, "cudaMalloc(mi)");
+    if ((e = cudaMalloc(&c->d_edge[0], sizeof(uint32_t) * (size_t)c->mi_stride * max_geom->mi_rows)) != cudaSuccess) return bail(e, "cudaMalloc(edge)");
+    if ((e = cudaMalloc(&c->d_edge[1], sizeof(uint32_t) * (size_t)(c->mi_stride / 2) * ((max_geom->mi_rows + 1) / 2))) != cudaSuccess)
+        return bail(e, "cudaMalloc(edge)");
     // flags are indexed in whole-picture coordinates even when the context holds one stripe: size for 16K rows
     c->max_ccso_blocks = ((max_geom->width + 255) / 256) * std::max((max_geom->height + 255) / 256, 64);
     c->poff_lut        = (size_t)round_up(c->max_nfb, 16);
@@ -249,7 +254,7 @@ extern "C" void svtf_ctx_destroy(svtf_ctx *c) {
     for (int i = 0; i < 4; i++)
         for (int p = 0; p < 3; p++) cudaFree(c->surf[i].base[p]);
     for (int p = 0; p < 3; p++) cudaFree(c->source.base[p]);
-    cudaFree(c->d_mi), cudaFree(c->d_params), cudaFree(c->d_sched);
+    cudaFree(c->d_mi), cudaFree(c->d_edge[0]), cudaFree(c->d_edge[1]), cudaFree(c->d_params), cudaFree(c->d_sched);
     for (auto &sl : c->pslot) {
         if (sl.h) cudaFreeHost(sl.h);
         if (sl.ev) cudaEventDestroy(sl.ev);
@@ -473,6 +478,8 @@ extern "C" int svtf_upload_source(svtf_ctx *c, const void *y, int32_t sy, const 
     return r;
 }
 
+static int edge_planes(svtf_ctx *c, bool force);
+
 extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) {
     if (!c)
         return set_global_error(SVTF_E_ARG, "svtf_set_mi: NULL context");
@@ -488,7 +495,7 @@ extern "C" int svtf_set_mi(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stride) 
         CUDA_TRY(c, cudaMemcpy2DAsync(c->d_mi, sizeof(svtf_mi_t) * c->mi_stride, mi, sizeof(svtf_mi_t) * mi_stride,
                                       sizeof(svtf_mi_t) * c->geom.mi_cols, c->geom.mi_rows, cudaMemcpyHostToDevice, c->stream));
     c->have_mi = true;
-    return SVTF_OK;
+    return edge_planes(c, true); // the mode info's second half: the deblocking edge-code planes, behind the upload on the stream
 }
 
 // ---- side info as byte planes, packed on the device (svtf_mi_pack.cuh) --------------------------------------
@@ -576,7 +583,7 @@ static int set_mi_soa(svtf_ctx *c, const uint8_t *const planes[7], int nplanes, 
         CUDA_TRY(c, cudaMallocHost(&c->h_mi_bad, sizeof(int)));
     CUDA_TRY(c, cudaMemcpyAsync(c->h_mi_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     c->have_mi = true;
-    return SVTF_OK;
+    return edge_planes(c, true); // the mode info's second half: the deblocking edge-code planes, behind the upload on the stream
 }
 
 static int mi_soa_check(svtf_ctx *c) { // after a stream synchronisation
@@ -797,6 +804,31 @@ static int need_frame_mi(svtf_ctx *c, const char *fn) {
     return SVTF_OK;
 }
 
+// Step 1 of set_lpf_parameters (svtf_kernels.cuh, dbk_edge_entry): once per mode-info upload (svtf_set_mi / svtf_set_mi_soa_* launch it
+// behind the copy; where the grid is assembled from pieces — stripes, halo exchange — the first deblock launch does); every deblock
+// launch on that mode info (24 level-search trials + the final one) reads the planes.
+static int edge_planes(svtf_ctx *c, bool force) {
+    if (c->edge_valid && !force)
+        return SVTF_OK;
+    EdgePlaneArgs ea;
+    ea.mi = c->d_mi, ea.mi_stride = c->mi_stride, ea.mi_cols = c->geom.mi_cols, ea.mi_rows = c->geom.mi_rows;
+    ea.ey = c->d_edge[0], ea.ec = c->d_edge[1], ea.ey_pitch = c->mi_stride, ea.ec_pitch = c->mi_stride / 2;
+    dbk_edge_plane_kernel<<<dim3((c->geom.mi_cols + 63) / 64, (c->geom.mi_rows + 3) / 4), 256, 0, c->stream>>>(ea);
+    CUDA_TRY(c, cudaGetLastError());
+    c->launches++;
+    c->edge_valid = true;
+    return SVTF_OK;
+}
+
+extern "C" int svtf_deblock_prepare(svtf_ctx *c) {
+    if (!c)
+        return set_global_error(SVTF_E_ARG, "svtf_deblock_prepare: NULL context");
+    if (!c->have_mi)
+        return c->fail(SVTF_E_STATE, "svtf_deblock_prepare: upload the mi grid first");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    return edge_planes(c, true);
+}
+
 // only_selected: launch no tiles for planes outside the mask (their samples in the output surface are then undefined;
 // used by the level search, which measures the filtered plane alone) instead of copying them through
 // sse_out: level-search trial — ONE plane (plane_start) is filtered (or, at level 0, left alone) and measured against the source
@@ -830,6 +862,9 @@ static int deblock_impl(svtf_ctx *c, const svtf_lf_params *lf, int32_t plane_sta
     a.mi        = c->d_mi;
     a.mi_stride = c->mi_stride;
     a.d         = dims_of(c->geom);
+    if (int r = edge_planes(c, false))
+        return r;
+    a.edge[0] = c->d_edge[0], a.edge[1] = c->d_edge[1], a.edge_pitch[0] = c->mi_stride, a.edge_pitch[1] = c->mi_stride / 2;
     // "no deblocking is required" limit of set_lpf_parameters: a chroma unit has edges while its LUMA position is inside the picture, i.e.
     // up to (w + 1) >> 1 — one 4x4 column more than w >> 1 when a super-resolution frame is 8k + 1 samples wide.  Encoder: the x_range /
     // y_range cut of svt_av1_filter_block_plane_vert/_horz for scaled frames (Encoder/Codec/EbDeblockingFilter.c:305-322; unscaled pictures

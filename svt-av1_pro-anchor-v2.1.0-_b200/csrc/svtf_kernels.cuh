@@ -109,6 +109,10 @@ struct DeblockArgs {
     int              ty0[3];                               // first tile row of the launch (stripe window)
     unsigned         plane_mask;                           // bit p: plane p is filtered (else copied)
     int              lim_w[3], lim_h[3];                   // units at or beyond these plane coordinates have no edges (set_lpf_parameters :175)
+    // edge-code planes (dbk_edge_plane_kernel): one word per 4x4 unit of the luma plane [0] / of a chroma plane [1], vertical edge in the
+    // low half, horizontal edge in the high half
+    const uint32_t *edge[2];
+    int             edge_pitch[2];
     LfTables         t;
     // per-superblock level tables [sb][plane][256] (delta_lf_present with the decoder's per-SB deltas) or nullptr
     const uint8_t *sb_lvl;
@@ -193,37 +197,51 @@ __device__ __forceinline__ void lpf_line(uint16_t *s, const int st, const int le
     s[-2 * st]    = (uint16_t)(min(max(ps1 + f, lo), hi) + off);
 }
 
-// set_lpf_parameters — Encoder/Codec/EbDeblockingFilter.c:162-285, evaluated independently per 4-sample
-// unit (the reference walks by transform size; skipped units are never on a transform edge).  `cur` is the unit's mode
-// info, already known to lie on a transform edge in direction `dir` (coord = x or y of the edge, != 0); `prv` its left /
-// top neighbour.  Returns (level << 2) | code, code 0 = no filter, 1 = 4-tap, 2 = 8-tap (luma) / 6-tap (chroma), 3 = 14-tap.
-__device__ __forceinline__ unsigned dbk_edge_decide(const svtf_mi_t cur, const svtf_mi_t prv, const int ts,
-                                                    const uint8_t *lvl /* [seg][dir][ref][mlf] of this plane */, const int plane,
-                                                    const int dir, const int coord, const int mi_row, const int mi_col,
-                                                    const uint8_t *__restrict__ sb_lvl, const int sb_cols, const int sb_shift) {
-    const int ss = plane ? 1 : 0;
-    // lvl index: ((seg*2+dir)*8+ref)*2+mlf ; key = ref | mlf<<3 | seg<<4
-    // with per-superblock deltas the table of the superblock that CONTAINS the unit is used, for the current unit and
-    // for its left/top neighbour alike (sb_delta_lf / sb_delta_lf_left / _above, Decoder/Codec/EbDecLF.c:357,548)
-    auto level_of = [&](svtf_mi_t m, int r, int c) {
-        const int key = mi_lvl_key(m), idx = (((key >> 4) * 2 + dir) * 8 + (key & 7)) * 2 + ((key >> 3) & 1);
-        if (sb_lvl)
-            return (int)__ldg(sb_lvl + ((size_t)((r >> sb_shift) * sb_cols + (c >> sb_shift)) * 3 + plane) * 256 + idx);
-        return (int)lvl[idx];
-    };
-    const int cur_lvl = level_of(cur, mi_row, mi_col);
-    const int pv_lvl  = dir == 0 ? level_of(prv, mi_row, mi_col - (1 << ss)) : level_of(prv, mi_row - (1 << ss), mi_col);
-    int       bdim    = 4 << mi_bdim(cur, dir);
-    if (ss)
+// set_lpf_parameters — Encoder/Codec/EbDeblockingFilter.c:162-285, evaluated independently per 4-sample unit (the reference walks by
+// transform size; skipped units are never on a transform edge), in two steps.
+// Step 1, once per mode-info upload (dbk_edge_plane_kernel): what depends on the mode info alone — is the unit's left / top boundary
+// (coord = its x or y) a transform edge, does the skip / prediction-block rule let it filter, which filter length.  Entry, 16 bits per
+// direction:  bits 0-1  0 = no edge, 1 = 4-tap, 2 = 8-tap (luma) / 6-tap (chroma), 3 = 14-tap;  bits 2-8 / 9-15  level key of the unit /
+// of its left / top neighbour.  One word per unit (vertical edge low half, horizontal high half); one plane for luma, one for U and V
+// (same transform sizes and mode info, only the level tables differ).
+// Step 2, in every tile of every deblock launch (the level search runs 24 per picture): the levels of the two keys (frame table or
+// per-superblock table) and level != 0.
+__device__ __forceinline__ uint32_t dbk_edge_entry(const svtf_mi_t cur, const svtf_mi_t prv, const int plane, const int dir, const int coord) {
+    const int ts = mi_tx(cur, plane, dir);
+    if (coord == 0 || (coord & ((4 << ts) - 1)))
+        return 0;
+    int bdim = 4 << mi_bdim(cur, dir);
+    if (plane)
         bdim = max(4, bdim >> 1);
     const bool pu_edge = !(coord & (bdim - 1));
-    if ((cur_lvl || pv_lvl) && (!mi_skip_inter(prv) || !mi_skip_inter(cur) || pu_edge)) {
-        const int min_ts = min(ts, mi_tx(prv, plane, dir));
-        const int level  = cur_lvl ? cur_lvl : pv_lvl;
-        const int code   = min_ts == 0 ? 1 : (plane ? 2 : (min_ts == 1 ? 2 : 3));
-        return (unsigned)(level << 2) | code;
+    if (mi_skip_inter(prv) && mi_skip_inter(cur) && !pu_edge)
+        return 0;
+    const int min_ts = min(ts, mi_tx(prv, plane, dir));
+    const int code   = min_ts == 0 ? 1 : (plane ? 2 : (min_ts == 1 ? 2 : 3));
+    return (uint32_t)code | ((uint32_t)mi_lvl_key(cur) << 2) | ((uint32_t)mi_lvl_key(prv) << 9);
+}
+struct EdgePlaneArgs {
+    const svtf_mi_t *mi;
+    int              mi_stride, mi_cols, mi_rows;
+    uint32_t        *ey, *ec;
+    int              ey_pitch, ec_pitch;
+};
+// thread = one mode-info word: its luma entry and, at odd (row, col), the entry of the chroma unit it stands for (deblock_kernel's
+// mi_row = 1 | 2 * unit row)
+__global__ void __launch_bounds__(256) dbk_edge_plane_kernel(const EdgePlaneArgs a) {
+    const int c = blockIdx.x * 64 + (threadIdx.x & 63), r = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (r >= a.mi_rows || c >= a.mi_cols)
+        return;
+    const svtf_mi_t *mp = a.mi + r * a.mi_stride + c;
+    const bool       ch = r & c & 1;
+    // all loads first (independent), neighbours outside the picture read as the unit itself: their edges have coord 0
+    const svtf_mi_t cur = __ldg(mp), lft = __ldg(c ? mp - 1 : mp), top = __ldg(r ? mp - a.mi_stride : mp);
+    const svtf_mi_t lft2 = ch && c > 1 ? __ldg(mp - 2) : cur, top2 = ch && r > 1 ? __ldg(mp - 2 * a.mi_stride) : cur;
+    a.ey[r * a.ey_pitch + c] = dbk_edge_entry(cur, lft, 0, 0, 4 * c) | (dbk_edge_entry(cur, top, 0, 1, 4 * r) << 16);
+    if (ch) {
+        const int cr = r >> 1, cc = c >> 1;
+        a.ec[cr * a.ec_pitch + cc] = dbk_edge_entry(cur, lft2, 1, 0, 4 * cc) | (dbk_edge_entry(cur, top2, 1, 1, 4 * cr) << 16);
     }
-    return 0;
 }
 
 // SBLVL: per-superblock level tables (decoder delta_lf); SSE: measure against the source instead of writing (level search).
@@ -264,7 +282,8 @@ __global__ void __launch_bounds__(DBK_THREADS, 8) deblock_kernel(const __grid_co
         d[0] = v.x, d[1] = v.y, d[2] = v.z, d[3] = v.w;
     }
     if (filter) {
-        s_lvl[tid] = (&a.t.lvl[plane][0][0][0][0])[tid];
+        // frame level table re-indexed [dir][key], key = ref | mode_lf << 3 | segment << 4 as the edge entries hold it
+        s_lvl[tid] = (&a.t.lvl[plane][0][0][0][0])[((((tid >> 4) & 7) * 2 + (tid >> 7)) * 8 + (tid & 7)) * 2 + ((tid >> 3) & 1)];
         if (tid < 64) {
             s_thr[0][tid] = a.t.lim[tid];
             s_thr[1][tid] = a.t.mblim[tid];
@@ -282,24 +301,34 @@ __global__ void __launch_bounds__(DBK_THREADS, 8) deblock_kernel(const __grid_co
             const int x = X0 + 4 * uc, y = Y0 + 4 * ur;
             if (x < 0 || y < 0 || x >= pw || y >= ph)
                 continue;
-            const int       mi_row = ss | ((y << ss) >> 2), mi_col = ss | ((x << ss) >> 2);
-            const svtf_mi_t *mp    = a.mi + mi_row * a.mi_stride + mi_col;
-            const svtf_mi_t  cur   = __ldg(mp);
-            const int        tsv = mi_tx(cur, plane, 0), tsh = mi_tx(cur, plane, 1);
-            if (x != 0 && !(x & ((4 << tsv) - 1))) {
-                const unsigned pr = dbk_edge_decide(cur, __ldg(mp - (1 << ss)), tsv, s_lvl, plane, 0, x, mi_row, mi_col, SBLVL ? a.sb_lvl : nullptr,
-                                                    a.sb_cols, a.sb_shift);
-                if (pr & 3) {
-                    const int code = (pr & 3) - 1;
-                    s_list[0][code][atomicAdd(&s_cnt[0][code], 1)] = (uint16_t)(((pr >> 2) << 10) | ((ur - 1) << 5) | (uc - 2));
+            const int      mi_row = ss | ((y << ss) >> 2), mi_col = ss | ((x << ss) >> 2);
+            const uint32_t e      = __ldg(a.edge[ss] + (y >> 2) * a.edge_pitch[ss] + (x >> 2));
+            // level of a key: frame table, or the table of the superblock that CONTAINS the unit (for the unit and for its left / top
+            // neighbour alike: sb_delta_lf / sb_delta_lf_left / _above, Decoder/Codec/EbDecLF.c:357,548)
+            auto level_of = [&](const int key, const int dir, const int r, const int c) {
+                if (SBLVL) {
+                    const int idx = (((key >> 4) * 2 + dir) * 8 + (key & 7)) * 2 + ((key >> 3) & 1);
+                    return (int)__ldg(a.sb_lvl + ((size_t)((r >> a.sb_shift) * a.sb_cols + (c >> a.sb_shift)) * 3 + plane) * 256 + idx);
+                }
+                return (int)s_lvl[dir * 128 + key];
+            };
+            const uint32_t ev = e & 0xffffu, eh = e >> 16;
+            if (ev & 3) {
+                int lv = level_of((ev >> 2) & 127, 0, mi_row, mi_col);
+                if (!lv)
+                    lv = level_of((ev >> 9) & 127, 0, mi_row, mi_col - (1 << ss));
+                if (lv) {
+                    const int code = (ev & 3) - 1;
+                    s_list[0][code][atomicAdd(&s_cnt[0][code], 1)] = (uint16_t)((lv << 10) | ((ur - 1) << 5) | (uc - 2));
                 }
             }
-            if (ur >= 2 && uc <= 17 && y != 0 && !(y & ((4 << tsh) - 1))) {
-                const unsigned pr = dbk_edge_decide(cur, __ldg(mp - (1 << ss) * a.mi_stride), tsh, s_lvl, plane, 1, y, mi_row, mi_col,
-                                                    SBLVL ? a.sb_lvl : nullptr, a.sb_cols, a.sb_shift);
-                if (pr & 3) {
-                    const int code = (pr & 3) - 1;
-                    s_list[1][code][atomicAdd(&s_cnt[1][code], 1)] = (uint16_t)(((pr >> 2) << 10) | ((uc - 2) << 5) | (ur - 2));
+            if (ur >= 2 && uc <= 17 && (eh & 3)) {
+                int lv = level_of(eh >> 2 & 127, 1, mi_row, mi_col);
+                if (!lv)
+                    lv = level_of(eh >> 9, 1, mi_row - (1 << ss), mi_col);
+                if (lv) {
+                    const int code = (eh & 3) - 1;
+                    s_list[1][code][atomicAdd(&s_cnt[1][code], 1)] = (uint16_t)((lv << 10) | ((uc - 2) << 5) | (ur - 2));
                 }
             }
         }

@@ -89,7 +89,7 @@ extern "C" int svtf_superres_upscale_frame(svtf_ctx *c, const svtf_superres_para
         c->pre_cdef = free_s;
     c->cur     = free_s;
     c->geom    = ng;
-    c->have_mi = c->have_search = c->have_source = false;
+    c->have_mi = c->have_search = c->have_source = c->edge_valid = false;
     return SVTF_OK;
 }
 

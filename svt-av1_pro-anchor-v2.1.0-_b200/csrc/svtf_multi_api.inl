@@ -146,7 +146,7 @@ extern "C" int svtf_set_mi_own(svtf_ctx *c, const svtf_mi_t *mi, int32_t mi_stri
     mi += (size_t)(c->glob_row0 / 4 + r0) * mi_stride; // whole-picture grid -> this context's own rows
     CUDA_TRY(c, cudaMemcpy2DAsync(c->d_mi + (size_t)r0 * c->mi_stride, sizeof(svtf_mi_t) * c->mi_stride, mi, sizeof(svtf_mi_t) * mi_stride,
                                   sizeof(svtf_mi_t) * c->geom.mi_cols, r1 - r0, cudaMemcpyHostToDevice, c->stream));
-    c->have_mi = true;
+    c->have_mi = true, c->edge_valid = false;
     return SVTF_OK;
 }
 
@@ -194,6 +194,7 @@ extern "C" int svtf_stripe_exchange(svtf_ctx *c, svtf_comm *comm, int32_t rank_u
         }
     }
     NCCL_TRY(c, n.GroupEnd());
+    c->edge_valid = false; // the halo mode-info rows changed
     return SVTF_OK;
 }
 

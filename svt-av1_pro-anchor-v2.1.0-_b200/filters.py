@@ -378,6 +378,10 @@ class FilterContext:
         d = np.ascontiguousarray(sb_delta_lf, dtype=np.int32)
         self._chk(self._lib.svtf_deblock_frame_sb_delta(self._h, C.byref(lf), plane_start, plane_end, _ptr(d), d.shape[1], sb_size_log2))
 
+    def deblock_prepare(self):
+        """svtf_deblock_prepare: build the edge-code planes of the uploaded mode info now (one launch)."""
+        self._chk(self._lib.svtf_deblock_prepare(self._h))
+
     def cdef_frame(self, cdef, fb_strength_idx):
         idx = np.ascontiguousarray(fb_strength_idx, dtype=np.int8)
         self._chk(self._lib.svtf_cdef_apply_frame(self._h, C.byref(cdef), _ptr(idx)))
