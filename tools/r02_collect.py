@@ -7,11 +7,12 @@ G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
 for f in os.listdir(G):
     if f.startswith(tag + "_") and f.endswith((".json", ".csv")) and "b_" not in f:
         shutil.copy(os.path.join(G, f), os.path.join(P, f))
-for n in ("chain_batch", "search"):
+for n in ("chain_batch", "search", "edge_plane"):
     rep = os.path.join(G, f"{tag}_{n}.ncu-rep")
     if os.path.exists(rep):
         open(os.path.join(P, f"{tag}_{n}_ncu_raw.csv"), "w").write(subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout)
-rows = list(csv.reader(open(os.path.join(P, f"{tag}_search_ncu_raw.csv"))))
+have_search = os.path.exists(os.path.join(P, f"{tag}_search_ncu_raw.csv"))  # a chain-only run (SKIP_SEARCH=1) leaves the search files alone
+rows = list(csv.reader(open(os.path.join(P, f"{tag}_search_ncu_raw.csv")))) if have_search else [[], []]
 h = rows[0]
 for r in rows[2:]:
     d = dict(zip(h, r))
@@ -27,7 +28,7 @@ for r in rows[2:]:
         print(out)
         break
 agg = collections.defaultdict(lambda: collections.defaultdict(list))
-for f in (f"{tag}_traffic_batch.csv", f"{tag}_traffic_search.csv"):
+for f in (f"{tag}_traffic_batch.csv",) + ((f"{tag}_traffic_search.csv",) if have_search else ()):
     rows = [r for r in csv.reader(open(os.path.join(P, f))) if len(r) > 10]
     h = rows[0]
     for r in rows[1:]:
@@ -35,7 +36,7 @@ for f in (f"{tag}_traffic_batch.csv", f"{tag}_traffic_search.csv"):
         agg[d["Kernel Name"].replace("void ", "").split("<")[0].split("(")[0]][d["Metric Name"]].append(float(d["Metric Value"].replace(",", "")))
 m = {k: {a: sum(b) / len(b) for a, b in v.items()} for k, v in agg.items()}
 t = json.load(open(os.path.join(P, "traffic.json")))
-for k, name in (("deblock_kernel", "deblock_kernel"), ("cdef5_kernel", "cdef5_kernel+ccso"), ("cdef_search3_kernel", "cdef_search3_kernel")):
+for k, name in (("deblock_kernel", "deblock_kernel"), ("cdef5_kernel", "cdef5_kernel+ccso")) + ((("cdef_search3_kernel", "cdef_search3_kernel"),) if have_search else ()):
     t[name] = int(m[k]["dram__bytes_read.sum"] + m[k]["dram__bytes_write.sum"])
     t[f"{tag}_{name}"] = {"read": int(m[k]["dram__bytes_read.sum"]), "write": int(m[k]["dram__bytes_write.sum"]), "gpu_time_ns": int(m[k]["gpu__time_duration.sum"])}
 t["_note_" + tag] = t.get("_note_r02f", "").replace("r02f", tag)
