@@ -21,6 +21,7 @@
 #include "svtf_search2_kernel.cuh"
 #include "svtf_pick.cuh"
 #include "svtf_pick2.cuh"
+#include "svtf_pick3.cuh"
 #include "svtf_ccso_derive.cuh"
 #include "svtf_cdef2.cuh"
 #include "svtf_cdef3.cuh"
@@ -106,7 +107,7 @@ struct svtf_ctx {
     int          max_nfb = 0;
     // device-side pick (svtf_pick.cuh)
     PickState   *d_pick_state = nullptr;
-    uint64_t    *d_pick_tot = nullptr;   // [64*64]
+    uint64_t    *d_pick_tot = nullptr;   // [3][64*64] (the per-call pick uses the first)
     int8_t      *d_pick_idx = nullptr;   // [pick_cap]
     uint64_t    *d_tab_mse = nullptr;    // table uploaded by svtf_cdef_pick_table, [2][pick_cap][64]
     uint8_t     *d_tab_skip = nullptr;
@@ -237,7 +238,7 @@ extern "C" int svtf_ctx_create(int device, const svtf_geom *max_geom, svtf_ctx *
     if ((e = cudaMalloc(&c->d_dir, 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(dir)");
     if ((e = cudaMalloc(&c->d_var, sizeof(int32_t) * 64 * (size_t)c->max_nfb)) != cudaSuccess) return bail(e, "cudaMalloc(var)");
     if ((e = cudaMalloc(&c->d_pick_state, sizeof(PickState))) != cudaSuccess) return bail(e, "cudaMalloc(pick state)");
-    if ((e = cudaMalloc(&c->d_pick_tot, sizeof(uint64_t) * 64 * 64)) != cudaSuccess) return bail(e, "cudaMalloc(pick tot)");
+    if ((e = cudaMalloc(&c->d_pick_tot, sizeof(uint64_t) * 3 * 64 * 64)) != cudaSuccess) return bail(e, "cudaMalloc(pick tot)");
     if ((e = cudaMalloc(&c->d_sched, 64)) != cudaSuccess) return bail(e, "cudaMalloc(sched)");
     if ((e = cudaMemset(c->d_sched, 0, 64)) != cudaSuccess) return bail(e, "cudaMemset(sched)");
     cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);

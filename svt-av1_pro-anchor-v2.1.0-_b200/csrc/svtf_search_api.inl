@@ -121,7 +121,7 @@ static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint6
     PickArgs a;
     a.mse = d_mse, a.skip = d_skip, a.nfb = nfb, a.end_gi = end_gi, a.bias = cfg->zero_fs_cost_bias;
     a.st = c->d_pick_state, a.tot = c->d_pick_tot;
-    // The 75 dependent svt_search_one_dual passes: one launch per pass, enqueued back to back (svtf_pick.cuh).  SVTF_PICK_CLUSTER=1: ONE
+    // The 75 dependent svt_search_one_dual passes.  Per-pass form: one launch per pass, enqueued back to back (svtf_pick.cuh).  SVTF_PICK_CLUSTER=1: ONE
     // launch, a 16-CTA cluster stays resident for all passes (svtf_pick2.cuh; measured slower in throughput, see its header) when the table
     // fits its shared memory and is narrow (every entry < 2^31; the kernel reports wide == 2 otherwise and the per-pass form runs).
     static const bool per_pass = getenv("SVTF_PICK_CLUSTER") == nullptr;
@@ -130,9 +130,19 @@ static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint6
         CUDA_TRY(c, cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
         c->max_smem_optin = (size_t)v;
     }
+    // Default: ONE cooperative launch over the whole device (svtf_pick3.cuh) when its grid fits the device at once (up to ~4 700 filter
+    // blocks: everything below 8K) and the table is narrow; else, or with SVTF_PICK_GRID=0, the per-pass launches.  Measured, 4K 10-bit,
+    // 64 strengths: pick 0.635 -> 0.463 ms; search + pick one picture at a time 1.87 -> 2.21 M filter blocks/s, 8 in flight 2.82 -> 2.99 M.
+    static const bool grid_form = getenv("SVTF_PICK_GRID") == nullptr || atoi(getenv("SVTF_PICK_GRID")) != 0;
     PickState st;
     bool      done = false;
-    if (!per_pass && pick2_fits(nfb, c->max_smem_optin)) {
+    if (per_pass && grid_form && pick3_fits(nfb, end_gi, c->sm_count)) {
+        CUDA_TRY(c, pick3_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
+        CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        done = st.wide == 0;
+    } else if (!per_pass && pick2_fits(nfb, c->max_smem_optin)) {
         CUDA_TRY(c, pick2_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
         CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));

@@ -38,9 +38,30 @@ SCRIPT = textwrap.dedent("""
 
 
 def test_cluster_pick_matches_host_pick():
-    env = dict(os.environ, SVTF_PICK_CLUSTER="1")
+    env = dict(os.environ, SVTF_PICK_CLUSTER="1", SVTF_PICK_GRID="0")
     r = subprocess.run([sys.executable, "-c", SCRIPT], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
     launches = {int(l.split()[1]): int(l.split()[3]) for l in r.stdout.splitlines() if l.startswith("case")}
     assert launches[3] == 1, launches          # narrow table: one launch
     assert launches[6] > 70, launches          # entries >= 2^31: the cluster kernel declines, the per-pass launches run
+
+
+def test_grid_pick_matches_host_pick():
+    """The cooperative whole-device form (pick_grid_kernel, svtf_pick3.cuh; the default) on the same cases."""
+    env = dict(os.environ)
+    env.pop("SVTF_PICK_CLUSTER", None), env.pop("SVTF_PICK_GRID", None)
+    r = subprocess.run([sys.executable, "-c", SCRIPT], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+    launches = {int(l.split()[1]): int(l.split()[3]) for l in r.stdout.splitlines() if l.startswith("case")}
+    assert launches[3] == 1 and launches[5] == 1, launches   # narrow tables that fit the device: one launch
+    assert launches[6] > 70, launches                        # entries >= 2^31: declined, the per-pass launches run
+
+
+def test_per_pass_pick_matches_host_pick():
+    """The per-pass form (pick_tot_kernel, svtf_pick.cuh; what 8K tables and wide tables run) forced on the same cases."""
+    env = dict(os.environ, SVTF_PICK_GRID="0")
+    env.pop("SVTF_PICK_CLUSTER", None)
+    r = subprocess.run([sys.executable, "-c", SCRIPT], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+    launches = {int(l.split()[1]): int(l.split()[3]) for l in r.stdout.splitlines() if l.startswith("case")}
+    assert min(launches.values()) > 70, launches
