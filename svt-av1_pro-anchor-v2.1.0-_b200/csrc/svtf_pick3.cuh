@@ -15,7 +15,8 @@
 // cooperative (cudaLaunchCooperativeKernel), so all CTAs are resident or the launch fails and the per-call form runs.  The wait is
 // bounded: a CTA that polls for 2 s sets bit 1 of PickState.wide and every CTA leaves — no hang, the host runs the per-call form.
 // Preconditions as for the cluster form: every entry the pick reads is below 2^31 (else bit 0 of wide: "not handled"), and the grid fits the
-// device (4K: 128 CTAs of 98 KB; 8K needs 512 and does not fit 148 SMs x 2: per-call form).
+// device (4K: 128 CTAs of 97 KB; 8K: 256 CTAs with two row groups per CTA, RG = 2; 148 SMs x 2 CTAs is the limit).
+// Partial sums are 32-bit when every entry the pick reads is below 2^26 (two instructions per entry and block instead of three).
 // All results are the u64 / i64 integer arithmetic of the C code (first (j, k) in raster order wins ties).
 #pragma once
 #include "svtf_pick.cuh"
@@ -24,7 +25,7 @@ namespace svtf {
 
 constexpr int PG_THREADS = 256;
 constexpr int PG_CHUNK   = 128;                                 // filter blocks per CTA
-constexpr int PG_ROWS    = 8;                                   // rows of tot per CTA
+constexpr int PG_ROWS    = 8;                                   // rows of tot per row group; a CTA covers RG of them (template)
 constexpr int PG_SMEM    = PG_CHUNK * 128 * 4 + 8 * 512 * 8 + PG_CHUNK * 4; // rows (u32) + the warps' slabs (u64) + best_so_far
 
 __device__ __forceinline__ unsigned pg_ld_acquire(const unsigned *p) {
@@ -62,6 +63,37 @@ __device__ __forceinline__ bool pg_grid_barrier(PickState *st, const unsigned ta
     return *s_ok != 0;
 }
 
+// The accumulate step of one warp: filter blocks [f_lo, f_hi) of the chunk into the warp's 8 x 64 slab (rows jr .., 4 x 4 per thread).
+// ACC = uint32_t when every entry the pick reads is below 2^26 (a + b < 2^27, at most 32 blocks per warp: no overflow), else uint64_t.
+template <typename ACC>
+__device__ __forceinline__ void pg_accumulate(const uint32_t (*srow)[128], const uint32_t *sbest, const int f_lo, const int f_hi, const int jr,
+                                              const int tj, const int tk, uint64_t *slab) {
+    ACC acc[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) acc[r][c] = 0;
+#pragma unroll 2
+    for (int f = f_lo; f < f_hi; f++) {
+        const uint4    av  = *reinterpret_cast<const uint4 *>(&srow[f][jr + tj * 4]);
+        const uint4    bv  = *reinterpret_cast<const uint4 *>(&srow[f][64 + tk * 4]);
+        const unsigned bst = sbest[f];
+        const unsigned aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[r][c] += __viaddmin_u32(aa[r], bb[c], bst);
+    }
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        ulonglong2 *d = reinterpret_cast<ulonglong2 *>(&slab[(tj * 4 + r) * 64 + tk * 4]);
+        d[0] = make_ulonglong2(acc[r][0], acc[r][1]), d[1] = make_ulonglong2(acc[r][2], acc[r][3]);
+    }
+}
+
+// RG: row groups (of 8 rows of tot) per CTA.  RG = 1: grid (end_gi / 8) x chunks, a warp takes 16 filter blocks; RG = 2: half as many
+// CTAs, a warp takes 32 filter blocks of one of the two row groups — for tables whose RG = 1 grid does not fit the device (8K).
+template <int RG>
 __global__ void __launch_bounds__(PG_THREADS, 2) pick_grid_kernel(const PickArgs a, const int64_t lambda, int8_t *fb_idx) {
     extern __shared__ __align__(16) unsigned char pg_dyn[];
     uint32_t(*srow)[128] = reinterpret_cast<uint32_t(*)[128]>(pg_dyn);                                      // [fb][luma 64 | chroma 64]
@@ -71,12 +103,13 @@ __global__ void __launch_bounds__(PG_THREADS, 2) pick_grid_kernel(const PickArgs
     __shared__ int      s_lev0[8], s_lev1[8], s_ok, s_pick[2];
     __shared__ uint64_t s_v[PG_THREADS / 32];
     __shared__ int      s_i[PG_THREADS / 32];
-    const int      tid = threadIdx.x, jt = blockIdx.x * PG_ROWS, fb0 = blockIdx.y * PG_CHUNK;
+    constexpr int  FGW = 8 / RG; // warps (= subsets of the chunk's filter blocks) per row group
+    const int      tid = threadIdx.x, jt = blockIdx.x * PG_ROWS * RG, fb0 = blockIdx.y * PG_CHUNK;
     const unsigned nct = gridDim.x * gridDim.y, bid = blockIdx.y * gridDim.x + blockIdx.x;
     PickState     *st  = a.st;
 
     // ---- once: the chunk's rows (whole rows: best_so_far reads whichever entries the lists name), width test, searched-block count ----
-    unsigned wide = 0;
+    unsigned wide = 0; // bit 0: an entry >= 2^31 (not handled), bit 2: an entry >= 2^26 (64-bit partial sums)
 #pragma unroll
     for (int n0 = 0; n0 < PG_CHUNK * 64 / PG_THREADS; n0 += 8) {
         ulonglong2 v[8];
@@ -92,8 +125,8 @@ __global__ void __launch_bounds__(PG_THREADS, 2) pick_grid_kernel(const PickArgs
                 v[n].x = ((uint64_t)(uint16_t)a.bias * v[n].x) >> 6; // entry 0 of a row, EbEncCdef.c:776-789
             const int  s0   = 2 * (e & 31); // strength index of v.x within its plane
             const bool live = fb0 + f < a.nfb && !a.skip[min(fb0 + f, a.nfb - 1)];
-            if (live && ((s0 < a.end_gi && (v[n].x >> 31)) || (s0 + 1 < a.end_gi && (v[n].y >> 31))))
-                wide = 1;
+            const uint64_t m = live ? ((s0 < a.end_gi ? v[n].x : 0) | (s0 + 1 < a.end_gi ? v[n].y : 0)) : 0;
+            wide |= (m >> 31 ? 1u : 0u) | (m >> 26 ? 4u : 0u);
             *reinterpret_cast<uint2 *>(&srow[f][2 * e]) = make_uint2((uint32_t)v[n].x, (uint32_t)v[n].y);
         }
     }
@@ -104,16 +137,21 @@ __global__ void __launch_bounds__(PG_THREADS, 2) pick_grid_kernel(const PickArgs
         cnt             = !s;
     }
     cnt = __syncthreads_count(cnt);
-    if (__syncthreads_or((int)wide) && tid == 0)
-        atomicOr(&st->wide, 1);
+    {
+        const int w1 = __syncthreads_or((int)(wide & 1)), w4 = __syncthreads_or((int)(wide & 4));
+        if ((w1 || w4) && tid == 0)
+            atomicOr(&st->wide, (w1 ? 1 : 0) | (w4 ? 4 : 0));
+    }
     if (tid == 0 && blockIdx.x == 0 && cnt)
         atomicAdd(&st->count, cnt);
     for (unsigned i = bid * PG_THREADS + tid; i < 3u * 64 * 64; i += nct * PG_THREADS) a.tot[i] = 0;
     unsigned target = nct;
     if (!pg_grid_barrier(st, target, &s_ok))
         return;
-    if (__ldcg(&st->wide) & 1) // uniform over the grid: every CTA's flag landed before the barrier, nobody clears it
+    const int flags = __ldcg(&st->wide); // uniform over the grid: every CTA's flags landed before the barrier, nobody clears them
+    if (flags & 1)
         return;
+    const bool small = !(flags & 4);
     const int count = __ldcg(&st->count);
 
     uint64_t tot_mse = PICK_INF, best_cost = PICK_INF; // thread 0's bookkeeping, identical in every CTA
@@ -143,36 +181,20 @@ __global__ void __launch_bounds__(PG_THREADS, 2) pick_grid_kernel(const PickArgs
                 sbest[tid] = best;
             }
             __syncthreads();
-            uint64_t acc[4][4];
-#pragma unroll
-            for (int r = 0; r < 4; r++)
-#pragma unroll
-                for (int c = 0; c < 4; c++) acc[r][c] = 0;
-            if (jt < a.end_gi) {
-#pragma unroll 2
-                for (int f = warp * (PG_CHUNK / 8); f < (warp + 1) * (PG_CHUNK / 8); f++) {
-                    const uint4    av = *reinterpret_cast<const uint4 *>(&srow[f][jt + tj * 4]);
-                    const uint4    bv = *reinterpret_cast<const uint4 *>(&srow[f][64 + tk * 4]);
-                    const unsigned bst = sbest[f];
-                    const unsigned aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-                    for (int r = 0; r < 4; r++)
-#pragma unroll
-                        for (int c = 0; c < 4; c++) acc[r][c] += __viaddmin_u32(aa[r], bb[c], bst);
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                ulonglong2 *d = reinterpret_cast<ulonglong2 *>(&red[warp * 512 + (tj * 4 + r) * 64 + tk * 4]);
-                d[0] = make_ulonglong2(acc[r][0], acc[r][1]), d[1] = make_ulonglong2(acc[r][2], acc[r][3]);
+            {
+                const int rg = warp / FGW, fg = warp - rg * FGW, jr = jt + rg * PG_ROWS;
+                if (small)
+                    pg_accumulate<uint32_t>(srow, sbest, fg * (PG_CHUNK / FGW), (fg + 1) * (PG_CHUNK / FGW), jr, tj, tk, red + warp * 512);
+                else
+                    pg_accumulate<uint64_t>(srow, sbest, fg * (PG_CHUNK / FGW), (fg + 1) * (PG_CHUNK / FGW), jr, tj, tk, red + warp * 512);
             }
             __syncthreads();
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int i = tid + h * PG_THREADS, j = jt + (i >> 6), k = i & 63;
+            for (int h = 0; h < 2 * RG; h++) {
+                const int e = tid + h * PG_THREADS, rg = e >> 9, i = e & 511, j = jt + rg * PG_ROWS + (i >> 6), k = i & 63;
                 uint64_t  v = 0;
 #pragma unroll
-                for (int w = 0; w < 8; w++) v += red[w * 512 + i];
+                for (int w = 0; w < FGW; w++) v += red[(rg * FGW + w) * 512 + i];
                 if (j < a.end_gi && k < a.end_gi && v)
                     atomicAdd(reinterpret_cast<unsigned long long *>(&tot[j * 64 + k]), (unsigned long long)v);
             }
@@ -262,21 +284,32 @@ __global__ void __launch_bounds__(PG_THREADS, 2) pick_grid_kernel(const PickArgs
     }
 }
 
-// Does the grid of a table of nfb filter blocks fit the device at once?  (cached per process: one device kind)
-inline bool pick3_fits(int nfb, int end_gi, int sm_count) {
+// Row groups per CTA for a table of nfb filter blocks: 1, 2 (the whole grid must fit the device at once) or 0 = does not fit.
+// (cached per process: one device kind)
+inline int pick3_fits(int nfb, int end_gi, int sm_count) {
     static int per_sm = -1;
     if (per_sm < 0) {
-        if (cudaFuncSetAttribute(pick_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PG_SMEM) != cudaSuccess ||
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pick_grid_kernel, PG_THREADS, PG_SMEM) != cudaSuccess)
-            per_sm = 0;
+        int n1 = 0, n2 = 0;
+        if (cudaFuncSetAttribute(pick_grid_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PG_SMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(pick_grid_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PG_SMEM) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n1, pick_grid_kernel<1>, PG_THREADS, PG_SMEM) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n2, pick_grid_kernel<2>, PG_THREADS, PG_SMEM) != cudaSuccess)
+            n1 = n2 = 0;
+        per_sm = n1 < n2 ? n1 : n2;
     }
-    const long ctas = (long)((end_gi + PG_ROWS - 1) / PG_ROWS) * ((nfb + PG_CHUNK - 1) / PG_CHUNK);
-    return per_sm > 0 && ctas <= (long)per_sm * sm_count;
+    if (per_sm <= 0)
+        return 0;
+    const long chunks = (nfb + PG_CHUNK - 1) / PG_CHUNK, cap = (long)per_sm * sm_count;
+    for (int rg = 1; rg <= 2; rg++)
+        if ((long)((end_gi + PG_ROWS * rg - 1) / (PG_ROWS * rg)) * chunks <= cap)
+            return rg;
+    return 0;
 }
 
-// One cooperative launch of the whole pick on `stream`; a.tot must hold 3 x 64 x 64 entries.  PickState.wide afterwards: 0 = done,
-// bit 0 = wide table, bit 1 = barrier gave up (either: not handled, run the per-call form).
-inline cudaError_t pick3_enqueue(const PickArgs &a, int8_t *d_fb_idx, int64_t lambda, cudaStream_t stream, uint64_t *launches) {
+// One cooperative launch of the whole pick on `stream` (rg from pick3_fits); a.tot must hold 3 x 64 x 64 entries.  PickState.wide
+// afterwards: bit 0 = wide table, bit 1 = barrier gave up (either: not handled, run the per-call form); bit 2 is informational
+// (64-bit partial sums were used).
+inline cudaError_t pick3_enqueue(const PickArgs &a, int rg, int8_t *d_fb_idx, int64_t lambda, cudaStream_t stream, uint64_t *launches) {
     cudaError_t e = cudaMemsetAsync(a.st, 0, sizeof(PickState), stream);
     if (e != cudaSuccess)
         return e;
@@ -284,8 +317,9 @@ inline cudaError_t pick3_enqueue(const PickArgs &a, int8_t *d_fb_idx, int64_t la
     int64_t  lam   = lambda;
     int8_t  *idx   = d_fb_idx;
     void    *args[] = {&aa, &lam, &idx};
-    const dim3 grid((a.end_gi + PG_ROWS - 1) / PG_ROWS, (a.nfb + PG_CHUNK - 1) / PG_CHUNK);
-    e = cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(pick_grid_kernel), grid, dim3(PG_THREADS), args, PG_SMEM, stream);
+    const dim3 grid((a.end_gi + PG_ROWS * rg - 1) / (PG_ROWS * rg), (a.nfb + PG_CHUNK - 1) / PG_CHUNK);
+    const void *fn = rg == 1 ? reinterpret_cast<const void *>(pick_grid_kernel<1>) : reinterpret_cast<const void *>(pick_grid_kernel<2>);
+    e = cudaLaunchCooperativeKernel(fn, grid, dim3(PG_THREADS), args, PG_SMEM, stream);
     if (e == cudaSuccess && launches)
         *launches += 1;
     return e;

@@ -130,18 +130,19 @@ static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint6
         CUDA_TRY(c, cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
         c->max_smem_optin = (size_t)v;
     }
-    // Default: ONE cooperative launch over the whole device (svtf_pick3.cuh) when its grid fits the device at once (up to ~4 700 filter
-    // blocks: everything below 8K) and the table is narrow; else, or with SVTF_PICK_GRID=0, the per-pass launches.  Measured, 4K 10-bit,
+    // Default: ONE cooperative launch over the whole device (svtf_pick3.cuh) when its grid fits the device at once (up to ~9 400 filter
+    // blocks: 8K included) and the table is narrow; else, or with SVTF_PICK_GRID=0, the per-pass launches.  Measured, 4K 10-bit,
     // 64 strengths: pick 0.635 -> 0.463 ms; search + pick one picture at a time 1.87 -> 2.21 M filter blocks/s, 8 in flight 2.82 -> 2.99 M.
     static const bool grid_form = getenv("SVTF_PICK_GRID") == nullptr || atoi(getenv("SVTF_PICK_GRID")) != 0;
     PickState st;
     bool      done = false;
-    if (per_pass && grid_form && pick3_fits(nfb, end_gi, c->sm_count)) {
-        CUDA_TRY(c, pick3_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
+    const int rg = per_pass && grid_form ? pick3_fits(nfb, end_gi, c->sm_count) : 0;
+    if (rg) {
+        CUDA_TRY(c, pick3_enqueue(a, rg, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
         CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
         CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-        done = st.wide == 0;
+        done = (st.wide & 3) == 0;
     } else if (!per_pass && pick2_fits(nfb, c->max_smem_optin)) {
         CUDA_TRY(c, pick2_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
         CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));

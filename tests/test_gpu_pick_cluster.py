@@ -22,7 +22,8 @@ SCRIPT = textwrap.dedent("""
     sig = lambda p: [p.cdef_bits, p.cdef_damping, *p.cdef_y_strength, *p.cdef_uv_strength]
     with S.FilterContext(S.make_geom(64, 64, 8)) as ctx:
         for it, (nfb, n1, n2, bias, pskip, hi) in enumerate(((1, 16, 48, 0, 0.0, 22), (7, 3, 3, 0, 0.2, 22), (60, 16, 48, 40, 0.2, 22), (2040, 16, 48, 0, 0.1, 22),
-                                                            (500, 16, 20, 70, 1.0, 22), (4080, 16, 48, 0, 0.3, 30), (300, 16, 48, 0, 0.1, 40))):
+                                                            (500, 16, 20, 70, 1.0, 22), (4080, 16, 48, 0, 0.3, 30), (300, 16, 48, 0, 0.1, 40),
+                                                            (8160, 16, 48, 0, 0.1, 22), (8160, 11, 30, 30, 0.2, 28))):
             cfg = S.cdef_search_cfg(first[:n1], second[:n2], base_q_idx=int(rng.integers(0, 256)), zero_fs_cost_bias=bias, lambda_=int(rng.integers(1, 50000)))
             mse = rng.integers(0, 1 << hi, (2, nfb, 64)).astype(np.uint64)
             if it == 3:
@@ -54,6 +55,7 @@ def test_grid_pick_matches_host_pick():
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
     launches = {int(l.split()[1]): int(l.split()[3]) for l in r.stdout.splitlines() if l.startswith("case")}
     assert launches[3] == 1 and launches[5] == 1, launches   # narrow tables that fit the device: one launch
+    assert launches[7] == 1 and launches[8] == 1, launches   # 8K: two row groups per CTA (32-bit and 64-bit partial sums)
     assert launches[6] > 70, launches                        # entries >= 2^31: declined, the per-pass launches run
 
 
