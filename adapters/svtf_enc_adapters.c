@@ -21,6 +21,7 @@
  * svtf_adapter_set_resident(1) skips the intermediate download/upload pairs).
  */
 #include <pthread.h>
+#include <time.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -101,6 +102,24 @@ static const char *const g_stat_name[ST_N] = {"loop_filter_frame", "loop_filter_
                                               "restoration_search", "superres_upscale_frame", "pad_ref_pictures"};
 static unsigned long   g_stat[ST_N];
 static unsigned long   g_stat_launches;
+/* host wall time spent in the phases of a picture's round trip (ns, summed over threads), same switch: where an end-to-end run waits */
+enum { TP_UPLOAD_CALL, TP_GATHER, TP_SET_MI_CALL, TP_DOWNLOAD, TP_N };
+static const char *const g_tp_name[TP_N] = {"upload_call", "mi_gather", "set_mi_call", "download_wait"};
+static unsigned long long g_tp[TP_N], g_tp_pictures;
+static int                g_tp_on = -1;
+static inline unsigned long long tp_now(void) {
+    if (g_tp_on < 0)
+        g_tp_on = getenv("SVTF_ADAPTER_STATS") != NULL;
+    if (!g_tp_on)
+        return 0;
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return (unsigned long long)t.tv_sec * 1000000000ull + (unsigned long long)t.tv_nsec;
+}
+static inline void tp_add(int which, unsigned long long t0) {
+    if (g_tp_on > 0)
+        __sync_fetch_and_add(&g_tp[which], tp_now() - t0);
+}
 static pthread_once_t  g_stat_once = PTHREAD_ONCE_INIT;
 static void            stat_print(void) {
     if (!getenv("SVTF_ADAPTER_STATS"))
@@ -113,6 +132,11 @@ static void            stat_print(void) {
     fprintf(stderr, "svtfilt_b200 adapter stats:");
     for (int i = 0; i < ST_N; i++) fprintf(stderr, " %s=%lu", g_stat_name[i], g_stat[i]);
     fprintf(stderr, " gpu_launches=%lu\n", g_stat_launches);
+    if (g_tp_pictures) {
+        fprintf(stderr, "svtfilt_b200 adapter host time per uploaded picture (ms):");
+        for (int i = 0; i < TP_N; i++) fprintf(stderr, " %s=%.3f", g_tp_name[i], (double)g_tp[i] / (double)g_tp_pictures * 1e-6);
+        fprintf(stderr, " pictures=%llu\n", g_tp_pictures);
+    }
 }
 static void stat_init(void) { atexit(stat_print); }
 static void stat_hit(int which) {
@@ -263,6 +287,7 @@ static void send_mi(CtxSlot *s, const PictureControlSet *pcs) {
         job[t].pcs = pcs, job[t].soa = soa, job[t].rows = rows, job[t].cols = cols;
         job[t].r0 = (int)((long)rows * t / nt), job[t].r1 = (int)((long)rows * (t + 1) / nt);
     }
+    unsigned long long t0 = tp_now();
     int created[32] = {0};
     for (int t = 1; t < nt; t++) created[t] = pthread_create(&th[t], NULL, mi_gather_rows, &job[t]) == 0;
     mi_gather_rows(&job[0]);
@@ -272,7 +297,10 @@ static void send_mi(CtxSlot *s, const PictureControlSet *pcs) {
         else
             mi_gather_rows(&job[t]); /* could not start the thread: do its rows here */
     }
+    tp_add(TP_GATHER, t0);
+    t0 = tp_now();
     CHECK(svtf_set_mi_soa_enc(s->ctx, soa, soa + n, soa + 2 * n, soa + 3 * n, soa + 4 * n, soa + 5 * n, cols), s->ctx);
+    tp_add(TP_SET_MI_CALL, t0);
 }
 
 /* svtf_adapter_set_pin_pictures(1): page-lock the picture's plane allocations in place on first sight (the recon pictures of the
@@ -309,9 +337,13 @@ static void begin_picture(CtxSlot *s, const PictureControlSet *pcs, const EbPict
     int32_t st[3];
     plane_ptrs(pic, s->geom.sample_bytes, p, st);
     pin_picture(s, pic, s->geom.sample_bytes);
+    unsigned long long t0 = tp_now();
     CHECK(svtf_frame_begin(s->ctx, &s->geom), s->ctx);
     CHECK(svtf_upload_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx); /* asynchronous from page-locked memory */
-    send_mi(s, pcs);                                                                /* gathers while the picture is on its way */
+    tp_add(TP_UPLOAD_CALL, t0);
+    send_mi(s, pcs); /* gathers while the picture is on its way */
+    if (g_tp_on > 0)
+        __sync_fetch_and_add(&g_tp_pictures, 1);
     s->resident = 1;
 }
 
@@ -319,7 +351,9 @@ static void end_picture(CtxSlot *s, const EbPictureBufferDesc *pic) {
     void   *p[3];
     int32_t st[3];
     plane_ptrs(pic, s->geom.sample_bytes, p, st);
+    const unsigned long long t0 = tp_now();
     CHECK(svtf_download_frame(s->ctx, p[0], st[0], p[1], st[1], p[2], st[2]), s->ctx);
+    tp_add(TP_DOWNLOAD, t0);
 }
 
 void svtf_adapter_fetch(const PictureControlSet *pcs, void *pic) {

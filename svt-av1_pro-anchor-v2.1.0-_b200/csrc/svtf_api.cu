@@ -122,7 +122,8 @@ struct svtf_ctx {
     size_t       max_smem_optin = 0;
     LrUnitDev   *d_lr_units = nullptr;   // restoration units of the three planes (svtf_lr_apply_frame)
     size_t       lr_units_cap = 0;
-    int         *h_mi_bad = nullptr;     // pinned: "invalid enum" flag of the last svtf_set_mi_soa_*
+    int         *h_mi_bad = nullptr;     // pinned + mapped: "invalid enum" flag of svtf_set_mi_soa_*, written by the pack kernel itself
+    int         *d_mi_bad = nullptr;     // its device alias
     uint8_t     *d_mi_soa = nullptr;     // byte planes of svtf_set_mi_soa_* (7 x mi_rows x mi_stride) + 4 bytes error flag
     size_t       mi_soa_cap = 0;
     uint8_t     *d_sb_lvl = nullptr;     // per-superblock deblock level tables (svtf_deblock_frame_sb_delta)
@@ -558,7 +559,7 @@ static int set_mi_soa(svtf_ctx *c, const uint8_t *const planes[7], int nplanes, 
         return c->fail(SVTF_E_ARG, std::string(who) + ": stride smaller than mi_cols");
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int    rows = c->geom.mi_rows, cols = c->geom.mi_cols;
-    const size_t plane_bytes = (size_t)rows * cols, need = 7 * plane_bytes + 16;
+    const size_t plane_bytes = (size_t)rows * cols, need = 7 * plane_bytes;
     if (c->mi_soa_cap < need) {
         if (c->d_mi_soa)
             cudaFree(c->d_mi_soa);
@@ -566,8 +567,14 @@ static int set_mi_soa(svtf_ctx *c, const uint8_t *const planes[7], int nplanes, 
         CUDA_TRY(c, cudaMalloc(&c->d_mi_soa, need));
         c->mi_soa_cap = need;
     }
-    int *d_bad = reinterpret_cast<int *>(c->d_mi_soa + ((7 * plane_bytes + 3) & ~(size_t)3));
-    CUDA_TRY(c, cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
+    // The "invalid enum" flag lives in mapped host memory and is stored by the kernel directly (only when something IS invalid): no
+    // memset ahead of the copies and no 4-byte read-back behind the kernel — either would sit at the head of the shared, in-order
+    // copy queues until this picture's own upload has finished and hold every other context's transfers behind it.
+    if (!c->h_mi_bad) {
+        CUDA_TRY(c, cudaHostAlloc(reinterpret_cast<void **>(&c->h_mi_bad), sizeof(int), cudaHostAllocMapped));
+        *c->h_mi_bad = 0;
+        CUDA_TRY(c, cudaHostGetDevicePointer(reinterpret_cast<void **>(&c->d_mi_bad), c->h_mi_bad, 0));
+    }
     for (int p = 0; p < nplanes; p++) {
         const uint8_t *src = planes[p] + (size_t)(c->glob_row0 / 4) * stride; // whole-picture planes -> this context's rows
         if (stride == cols)
@@ -584,15 +591,12 @@ static int set_mi_soa(svtf_ctx *c, const uint8_t *const planes[7], int nplanes, 
     else
         a.tx0 = d + plane_bytes, a.tx1 = nullptr, a.skip = d + 2 * plane_bytes, a.ref0 = d + 3 * plane_bytes, a.mode = d + 4 * plane_bytes,
         a.seg = d + 5 * plane_bytes;
-    a.in_pitch = cols, a.rows = rows, a.cols = cols, a.out = c->d_mi, a.out_pitch = c->mi_stride, a.dec = dec, a.bad = d_bad;
+    a.in_pitch = cols, a.rows = rows, a.cols = cols, a.out = c->d_mi, a.out_pitch = c->mi_stride, a.dec = dec, a.bad = c->d_mi_bad;
     a.t = mi_pack_tables();
     mi_pack_kernel<<<dim3((cols + MP_THREADS - 1) / MP_THREADS, rows), MP_THREADS, 0, c->stream>>>(a);
     CUDA_TRY(c, cudaGetLastError());
     c->launches++;
-    // no host synchronisation here: the flag lands in pinned memory and is looked at by the next svtf_sync / download
-    if (!c->h_mi_bad)
-        CUDA_TRY(c, cudaMallocHost(&c->h_mi_bad, sizeof(int)));
-    CUDA_TRY(c, cudaMemcpyAsync(c->h_mi_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    // no host synchronisation here: the flag is looked at by the next svtf_sync / download
     c->have_mi = true;
     return edge_planes(c, true); // the mode info's second half: the deblocking edge-code planes, behind the upload on the stream
 }
