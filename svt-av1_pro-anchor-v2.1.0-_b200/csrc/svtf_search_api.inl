@@ -138,11 +138,16 @@ static int pick_device(svtf_ctx *c, const svtf_cdef_search_cfg *cfg, const uint6
     bool      done = false;
     const int rg = per_pass && grid_form ? pick3_fits(nfb, end_gi, c->sm_count) : 0;
     if (rg) {
-        CUDA_TRY(c, pick3_enqueue(a, rg, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
-        CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-        done = (st.wide & 3) == 0;
+        const cudaError_t e = pick3_enqueue(a, rg, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches);
+        if (e == cudaErrorCooperativeLaunchTooLarge || e == cudaErrorNotSupported) {
+            (void)cudaGetLastError(); // fewer SMs than the occupancy query promised (a partitioned device): the per-pass form runs
+        } else {
+            CUDA_TRY(c, e);
+            CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaMemcpyAsync(fb_strength_idx, c->d_pick_idx, nfb, cudaMemcpyDeviceToHost, c->stream));
+            CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+            done = (st.wide & 3) == 0;
+        }
     } else if (!per_pass && pick2_fits(nfb, c->max_smem_optin)) {
         CUDA_TRY(c, pick2_enqueue(a, c->d_pick_idx, (int64_t)cfg->lambda, c->stream, &c->launches));
         CUDA_TRY(c, cudaMemcpyAsync(&st, c->d_pick_state, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
